@@ -1,0 +1,161 @@
+/* stk_cuda.h — C-ABI of libstk_cuda.so, the B200-native sampling backend for
+ * Stochaskell (the `Language.CUDA` counterpart of `Language.CC`).
+ *
+ * What this boundary replaces in the reference (davidar/stochaskell):
+ *   - compileCC / runCC            stochaskell/src/Language/CC.hs:459-498
+ *       (IR -> C++ text -> g++ -> one process per transition, state through
+ *        stdin/stdout text).  Here: IR -> CUDA text (stkc / Language.CUDA) ->
+ *        NVRTC sm_100a cubin (SHA1-keyed cache like CC.hs:471-479) -> one
+ *        resident module, state resident in HBM, thousands of chains per call.
+ *   - runStep / simulate           stochaskell/src/Data/Program.hs:1350-1359, 1038
+ *   - hmcStan / hmcStanInit / runStan  stochaskell/src/Language/Stan.hs:443-500
+ *       (static-HMC semantics of cmdstan .../hmc/static/base_static_hmc.hpp:42-72)
+ *
+ * There is no FFI in the reference (its boundary is process + text), so these
+ * entry points are what `foreign import ccall` in haskell/Language/CUDA.hs
+ * binds; see INTEGRATION.md for the reference-side stubs.
+ *
+ * Conventions
+ *   - every function returns 0 on success, <0 on error; the message is in
+ *     stk_last_error() (thread-local).  No exception crosses the boundary.
+ *   - handles are opaque; host pointers are borrowed for the call only; device
+ *     memory is owned by the library.
+ *   - one stk_ctx per GPU; a ctx is not thread-safe (serialise per ctx).
+ *   - chain state is structure-of-arrays: field f with per-chain length L is
+ *     stored [L][n_chains] (element-major, chain-minor) so that loads of one
+ *     parameter across neighbouring chains coalesce.  Host-side get/set use
+ *     the same [L][n_chains] layout.
+ *   - there is NO CPU fallback: without a CUDA device every compute entry
+ *     point fails with STK_ERR_CUDA.
+ */
+#ifndef STK_CUDA_H
+#define STK_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct stk_ctx stk_ctx;
+typedef struct stk_module stk_module;
+typedef struct stk_chains stk_chains;
+typedef void* stk_stream; /* cudaStream_t; NULL = the ctx's own stream */
+
+#define STK_OK 0
+#define STK_ERR_ARG (-1)     /* bad argument / unknown field / size mismatch  */
+#define STK_ERR_CUDA (-2)    /* CUDA runtime / driver error, or no device     */
+#define STK_ERR_COMPILE (-3) /* NVRTC compilation failed (log in last_error)  */
+#define STK_ERR_IO (-4)      /* cache directory / file error                  */
+#define STK_ERR_UNSUPPORTED (-5)
+
+#define STK_ABI_VERSION 1
+
+/* -------- diagnostics ---------------------------------------------------- */
+const char* stk_last_error(void);
+int stk_abi_version(void);
+/* number of kernel launches issued by this library since load (bench.py's
+ * "gpu_launches" claim is read from here, not guessed). */
+int64_t stk_launch_count(void);
+
+/* -------- context (one per GPU) ------------------------------------------ */
+int stk_ctx_create(int device, stk_ctx** out);
+int stk_ctx_destroy(stk_ctx* ctx);
+/* the ctx's stream as a cudaStream_t (so a harness can record CUDA events on
+ * the stream the kernels are launched on). */
+int stk_ctx_stream(stk_ctx* ctx, stk_stream* out);
+
+/* -------- modules: compiled models --------------------------------------- */
+/* Compile generated CUDA source to an sm_100a cubin with NVRTC, without
+ * touching a device (mirrors the "does it build" half of compileCC,
+ * CC.hs:481-492).  The cubin is written to
+ * <cache_dir>/stk_<sha1(source)>.cubin and its path copied to path_out.
+ * A cache hit skips compilation (CC.hs:476-479).  include_dir is where
+ * stk_device.cuh lives (NULL = the directory baked in at build time). */
+int stk_compile(const char* cuda_src, const char* cache_dir,
+                const char* include_dir, char* path_out, size_t path_cap);
+
+/* Load a module on ctx's device.  `spec` is one of
+ *   "builtin:<name>"   a hand-tuned model shipped with the library
+ *   "<path>.cubin"     a cubin produced by stk_compile / nvcc
+ *   anything else      CUDA source text: stk_compile + load
+ */
+int stk_module_load(stk_ctx* ctx, const char* spec, const char* cache_dir,
+                    stk_module** out);
+int stk_module_destroy(stk_module* mod);
+/* the module's descriptor text (fields, kernels, launch geometry) */
+int stk_module_describe(stk_module* mod, char* buf, size_t cap);
+/* field / kernel / parameter lookup by name: index >= 0, or STK_ERR_ARG */
+int stk_module_field(stk_module* mod, const char* name);
+int stk_module_kernel(stk_module* mod, const char* name);
+
+/* -------- chains: batched state ------------------------------------------ */
+/* cudaMalloc the SoA state for n_chains chains.  `seed` keys the Philox
+ * stream; draws of global chain c at transition t are a pure function of
+ * (seed, c, t, slot), so results do not depend on how chains are sharded. */
+int stk_chains_create(stk_module* mod, int64_t n_chains, uint64_t seed,
+                      stk_chains** out);
+int stk_chains_destroy(stk_chains* ch);
+/* global index of this shard's first chain (multi-GPU: rank * n_chains) */
+int stk_chains_set_offset(stk_chains* ch, int64_t first_global_chain);
+/* capacity of a dynamically sized data field must be set before set_data */
+int stk_set_data(stk_chains* ch, int field, const void* host, size_t bytes);
+/* broadcast != 0: `host` holds ONE chain's value, replicated to all chains
+ * (the hmcStanInit analogue, Stan.hs:498-500). */
+int stk_set_state(stk_chains* ch, int field, const void* host, size_t bytes,
+                  int broadcast);
+int stk_get_state(stk_chains* ch, int field, void* host, size_t bytes);
+/* raw device pointer of a field (zero-copy interop with torch tensors) */
+int stk_device_ptr(stk_chains* ch, int field, void** dptr, size_t* bytes);
+/* scalar tunables by name: "eps", "L", "rw_scale", ... (CudaMethod record,
+ * mirroring StanMethod, Stan.hs:378-440) */
+int stk_set_param(stk_chains* ch, const char* name, double value);
+int stk_get_param(stk_chains* ch, const char* name, double* value);
+
+/* -------- compute -------------------------------------------------------- */
+/* joint log-density of each chain's current state (parity tier 1);
+ * lp_host[n_chains].  Program.hs:787-812 (`lpdf`). */
+int stk_logp(stk_chains* ch, double* lp_host);
+/* log-density and gradient w.r.t. the unconstrained parameters;
+ * grad_host is [P][n_chains]. */
+int stk_logp_grad(stk_chains* ch, double* lp_host, double* grad_host);
+/* n_transitions fused transitions of kernel `kernel_id` (MH / RJ / HMC) for
+ * every chain, in ONE launch; asynchronous on `stream`. */
+int stk_step(stk_chains* ch, int kernel_id, int64_t n_transitions,
+             stk_stream stream);
+/* forward simulation from the prior (simulate, Program.hs:1038) */
+int stk_simulate(stk_chains* ch, stk_stream stream);
+/* draws ring: keep every `thin`-th state of the next stk_step calls in a
+ * device buffer [n_slots][P][n_chains]; n_slots = 0 disables. */
+int stk_record(stk_chains* ch, int64_t n_slots, int64_t thin);
+/* copy recorded draws [n_recorded][P][n_chains] to host; returns count in
+ * *n_recorded (host may be NULL to query). */
+int stk_get_draws(stk_chains* ch, double* host, size_t bytes,
+                  int64_t* n_recorded);
+/* per-parameter cross-chain diagnostics of the recorded draws on this GPU:
+ * mean[P], var[P], rhat[P], ess[P] (any may be NULL).  `moments4` (may be
+ * NULL) receives the additive [4][P] buffer (count, sum of chain means, sum
+ * of squared chain means, sum of chain variances) that ranks all-reduce with
+ * NCCL for the global R-hat. */
+int stk_moments(stk_chains* ch, double* mean, double* var, double* rhat,
+                double* ess, double* moments4);
+/* the same diagnostics in two halves for multi-GPU runs: every rank fills the
+ * additive buffer ([4][P] moments, then [P][max_lag+1] autocovariance sums;
+ * bytes = 8*P*(4+max_lag+1); max_lag < 0 means n_recorded-1), ranks all-reduce
+ * it (sum), and any rank finishes on the host. */
+int stk_diag_partial(stk_chains* ch, int64_t max_lag, double* buf, size_t bytes);
+int stk_diag_finish(const double* buf, int P, int64_t n_draws, int64_t max_lag,
+                    double* mean, double* var, double* rhat, double* ess);
+int stk_sync(stk_chains* ch);
+/* doubles per recorded draw per chain (P_rec), valid after stk_record */
+int stk_num_recorded_values(stk_chains* ch);
+
+/* number of unconstrained parameters P and chains */
+int stk_num_params(stk_chains* ch);
+int64_t stk_num_chains(stk_chains* ch);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* STK_CUDA_H */

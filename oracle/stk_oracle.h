@@ -1,0 +1,73 @@
+// stk_oracle.h — CPU ORACLE (test infrastructure, NOT product code).
+//
+// A plain C++ restatement of the reference's algorithms for the sampling hot
+// path, used only by tests/, __graft_entry__.smoke() and bench.py's
+// cpu_baseline / --impl reference legs as the CHECKER.  The product path
+// (libstk_cuda.so) never links, loads or calls anything in oracle/.
+//
+// Parity status: PINNED for the pieces noted below, "parity unpinned" for the
+// rest:
+//   * lpdf formulas: restated from Abstract.hs / Const.hs; pinned against the
+//     vendored Boost.Math (the CC backend's own arithmetic, CC.hs:206-228) by
+//     oracle/ref_cc/*.cc compiled from the reference headers, and against the
+//     vendored Stan (lp + gradient via `diagnose`) through tests/golden/.
+//   * Philox4x32-10: pinned by the Random123 known-answer vectors.
+//   * soccer RJ kernel: pinned against the reference's own generated C++
+//     (rj.ipynb cell 10) compiled into oracle/_ref/.
+//   * coal RJ kernel: restated node by node from the kernel IR preserved in
+//     rj-coal.ipynb cell 8; the reference can only run it through the Haskell
+//     interpreter (no GHC here) -> statistical pins only.
+#ifndef STK_ORACLE_H
+#define STK_ORACLE_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+// ---- RNG: same counter layout as stk_device.cuh ------------------------------
+void orc_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]);
+// k-th block of (seed, chain, step): words -> two uniforms / two normals
+void orc_u01x2(uint64_t seed, uint64_t chain, uint64_t step, uint32_t slot, double* a, double* b);
+void orc_normal2(uint64_t seed, uint64_t chain, uint64_t step, uint32_t slot, double* a, double* b);
+// stateful stream mirroring stk::Rng
+typedef struct { uint32_t k0, k1, c0, c1, c2, slot; } orc_rng;
+void orc_rng_init(orc_rng* g, uint64_t seed, uint64_t chain, uint64_t step);
+double orc_u01(orc_rng* g);
+double orc_normal(orc_rng* g);
+int orc_draw_discrete_uniform(orc_rng* g, int a, int b);
+int orc_draw_bernoulli(orc_rng* g, double p);
+int orc_draw_pmf(orc_rng* g, const double* ps, int n);
+int orc_draw_poisson(orc_rng* g, double l);
+double orc_draw_gamma(orc_rng* g, double a, double b);
+double orc_draw_cauchy(orc_rng* g, double m, double s);
+
+// ---- log densities (Abstract.hs:68-167, Const.hs:90-106) ---------------------
+double orc_normal_lpdf(double x, double m, double s);
+double orc_gamma_lpdf(double x, double a, double b);
+double orc_inv_gamma_lpdf(double x, double a, double b);
+double orc_geometric_lpdf(int k, double p);
+double orc_neg_binomial_lpdf(int k, double a, double b);
+double orc_poisson_lpdf(int k, double l);
+double orc_uniform_lpdf(double x, double a, double b);
+double orc_uniform_cdf(double x, double a, double b);
+double orc_discrete_uniform_lpdf(int x, int a, int b);
+double orc_bernoulli_logit_lpdf(int b, double l);
+double orc_cauchy_lpdf(double x, double m, double s);
+double orc_log_factorial(int k);
+
+// ---- C1 linreg (linreg.ipynb cell 1, d-dimensional) --------------------------
+// q = (b, w[d], log sigma); X row-major [n][d].  Returns lp; grad[d+2] if non-NULL.
+double orc_linreg_logp(const double* X, const double* y, int n, int d, const double* q, double* grad);
+// one static-HMC transition (base_static_hmc.hpp:42-72) with the same Philox
+// consumption as linreg_hmc; q updated in place; returns 1 if accepted.
+int orc_linreg_hmc_step(const double* X, const double* y, int n, int d, double* q, double eps, int L,
+                        uint64_t seed, uint64_t chain, uint64_t step, double* lp_out);
+int orc_linreg_mh_step(const double* X, const double* y, int n, int d, double* q, double rw,
+                       uint64_t seed, uint64_t chain, uint64_t step, double* lp_io);
+// forward simulation: q[d+2] and ysim[n]
+void orc_linreg_simulate(const double* X, int n, int d, uint64_t seed, uint64_t chain, double* q, double* ysim);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

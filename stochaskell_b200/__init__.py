@@ -1,0 +1,9 @@
+"""stochaskell_b200 — B200-native sampling backend for Stochaskell (Language.CUDA).
+
+Only what the hot path needs: the C-ABI library + CUDA kernels in
+csrc/, the host-side mirror of compileCC/runCC/runStep/simulate/hmcStan in api.py,
+the IR -> CUDA code generator in stkc.py, and the diagnostics plumbing.
+"""
+from ._lib import LIB_PATH, StkError, lib  # noqa: F401
+from .api import (Chains, Context, CudaMethod, Module, Sampler, compile_source,  # noqa: F401
+                  compileCUDA, diag_finish, hmcCUDA, runCUDA)

@@ -1,0 +1,291 @@
+"""Host-side mirror of the reference's entry points for the sampling hot path.
+
+Reference interface (davidar/stochaskell)          ->  here
+  compileCC :: (s -> P t) -> IO (s -> IO t)   CC.hs:465   compileCUDA(model) -> Sampler
+  runCC                                       CC.hs:459   runCUDA
+  runStep / simulate          Program.hs:1350, 1038       Sampler.step / Sampler.simulate
+  hmcStan n / hmcStanInit n p x0     Stan.hs:493-500      hmcCUDA(method, model, init)
+  StanMethod record                  Stan.hs:378-440      CudaMethod dataclass
+
+Everything below is plumbing over the C-ABI in include/stk_cuda.h: numpy arrays
+in HOST memory go in and out; all arithmetic happens in the CUDA kernels.  A
+missing library / device raises StkError (no fallback).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import dataclasses
+import os
+from typing import Dict, Optional, Sequence
+
+import numpy as np
+
+from ._lib import CSRC_DIR, StkError, check, lib
+
+DEFAULT_CACHE = os.environ.get("STOCHASKELL_DIRECTORY", os.getcwd()) + "/cache/cuda"  # Stochaskell.hs:160-162
+
+
+def _ptr(a: np.ndarray):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class Context:
+    """One per GPU (stk_ctx)."""
+
+    def __init__(self, device: int = 0):
+        h = C.c_void_p()
+        check(lib().stk_ctx_create(device, C.byref(h)))
+        self._h = h
+        self.device = device
+
+    @property
+    def stream(self) -> int:
+        s = C.c_void_p()
+        check(lib().stk_ctx_stream(self._h, C.byref(s)))
+        return s.value or 0
+
+    def close(self):
+        if self._h:
+            lib().stk_ctx_destroy(self._h)
+            self._h = None
+
+    def __del__(self):  # pragma: no cover
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def compile_source(cuda_src: str, cache_dir: Optional[str] = None, include_dir: Optional[str] = None) -> str:
+    """NVRTC-compile generated CUDA text to an sm_100a cubin (no GPU needed). Returns the cubin path."""
+    buf = C.create_string_buffer(4096)
+    check(lib().stk_compile(cuda_src.encode(), (cache_dir or DEFAULT_CACHE).encode(),
+                            (include_dir or CSRC_DIR).encode(), buf, len(buf)))
+    return buf.value.decode()
+
+
+class Module:
+    """A compiled model (stk_module): 'builtin:<name>', a .cubin path, or CUDA source text."""
+
+    def __init__(self, ctx: Context, spec: str, cache_dir: Optional[str] = None):
+        self.ctx = ctx
+        if not spec.startswith("builtin:") and not spec.endswith(".cubin"):
+            spec = compile_source(spec, cache_dir)  # python side passes the in-tree include dir
+        h = C.c_void_p()
+        check(lib().stk_module_load(ctx._h, spec.encode(), (cache_dir or DEFAULT_CACHE).encode(), C.byref(h)))
+        self._h = h
+        buf = C.create_string_buffer(1 << 16)
+        check(lib().stk_module_describe(h, buf, len(buf)))
+        self.descriptor = buf.value.decode()
+        self.fields: Dict[str, dict] = {}
+        self.kernels = []
+        self.params = {}
+        self.nparam = 0
+        self.name = ""
+        for line in self.descriptor.splitlines():
+            t = line.split()
+            if not t:
+                continue
+            if t[0] == "field":
+                self.fields[t[1]] = dict(index=len(self.fields), state=(t[2] == "state"),
+                                         dtype=np.int32 if t[3] == "i32" else np.float64, len=t[4])
+            elif t[0] == "kernel":
+                self.kernels.append(t[1])
+            elif t[0] == "param":
+                self.params[t[1]] = float(t[2])
+            elif t[0] == "nparam":
+                self.nparam = int(t[1])
+            elif t[0] == "name":
+                self.name = t[1]
+
+    def kernel_id(self, name: str) -> int:
+        return check(lib().stk_module_kernel(self._h, name.encode()))
+
+    def close(self):
+        if self._h:
+            lib().stk_module_destroy(self._h)
+            self._h = None
+
+
+class Chains:
+    """Batched chain state resident on the GPU (stk_chains)."""
+
+    def __init__(self, module: Module, n_chains: int, seed: int = 0, first_global_chain: int = 0):
+        self.module = module
+        self.n = int(n_chains)
+        h = C.c_void_p()
+        check(lib().stk_chains_create(module._h, self.n, C.c_uint64(seed), C.byref(h)))
+        self._h = h
+        if first_global_chain:
+            check(lib().stk_chains_set_offset(h, first_global_chain))
+
+    # -- data / state ---------------------------------------------------------
+    def _field(self, name: str) -> dict:
+        try:
+            return self.module.fields[name]
+        except KeyError:
+            raise StkError(-1, f"module {self.module.name} has no field {name!r}") from None
+
+    def set_data(self, name: str, value) -> None:
+        f = self._field(name)
+        a = np.ascontiguousarray(value, dtype=f["dtype"])
+        check(lib().stk_set_data(self._h, f["index"], _ptr(a), a.nbytes))
+
+    def set_state(self, name: str, value, broadcast: bool = False) -> None:
+        """value: [L][n_chains] (or [L] with broadcast=True, the hmcStanInit analogue)."""
+        f = self._field(name)
+        a = np.ascontiguousarray(value, dtype=f["dtype"])
+        check(lib().stk_set_state(self._h, f["index"], _ptr(a), a.nbytes, 1 if broadcast else 0))
+
+    def get_state(self, name: str) -> np.ndarray:
+        f = self._field(name)
+        d = C.c_void_p(); nb = C.c_size_t()
+        check(lib().stk_device_ptr(self._h, f["index"], C.byref(d), C.byref(nb)))
+        out = np.empty(nb.value // np.dtype(f["dtype"]).itemsize, dtype=f["dtype"])
+        check(lib().stk_get_state(self._h, f["index"], _ptr(out), out.nbytes))
+        return out.reshape(-1, self.n) if f["state"] else out
+
+    def device_ptr(self, name: str):
+        f = self._field(name)
+        d = C.c_void_p(); nb = C.c_size_t()
+        check(lib().stk_device_ptr(self._h, f["index"], C.byref(d), C.byref(nb)))
+        return d.value, nb.value
+
+    def set_param(self, name: str, value: float) -> None:
+        check(lib().stk_set_param(self._h, name.encode(), float(value)))
+
+    # -- compute --------------------------------------------------------------
+    def logp(self) -> np.ndarray:
+        out = np.empty(self.n)
+        check(lib().stk_logp(self._h, _ptr(out)))
+        return out
+
+    def logp_grad(self):
+        lp = np.empty(self.n)
+        g = np.empty((self.module.nparam, self.n))
+        check(lib().stk_logp_grad(self._h, _ptr(lp), _ptr(g)))
+        return lp, g
+
+    def step(self, kernel: str | int, n_transitions: int = 1, stream: int = 0) -> None:
+        kid = kernel if isinstance(kernel, int) else self.module.kernel_id(kernel)
+        check(lib().stk_step(self._h, kid, int(n_transitions), C.c_void_p(stream)))
+
+    def simulate(self, stream: int = 0) -> None:
+        check(lib().stk_simulate(self._h, C.c_void_p(stream)))
+
+    def record(self, n_slots: int, thin: int = 1) -> None:
+        check(lib().stk_record(self._h, int(n_slots), int(thin)))
+
+    def draws(self) -> np.ndarray:
+        """[n_recorded][P_rec][n_chains]"""
+        n = C.c_int64()
+        check(lib().stk_get_draws(self._h, None, 0, C.byref(n)))
+        p = lib().stk_num_recorded_values(self._h)
+        out = np.empty((n.value, p, self.n))
+        check(lib().stk_get_draws(self._h, _ptr(out), out.nbytes, C.byref(n)))
+        return out
+
+    def moments(self):
+        p = lib().stk_num_recorded_values(self._h)
+        mean, var, rhat, ess = (np.empty(p) for _ in range(4))
+        m4 = np.empty((4, p))
+        check(lib().stk_moments(self._h, _ptr(mean), _ptr(var), _ptr(rhat), _ptr(ess), _ptr(m4)))
+        return dict(mean=mean, var=var, rhat=rhat, ess=ess, moments4=m4)
+
+    def diag_partial(self, max_lag: int) -> np.ndarray:
+        p = lib().stk_num_recorded_values(self._h)
+        buf = np.empty(p * (4 + max_lag + 1))
+        check(lib().stk_diag_partial(self._h, int(max_lag), _ptr(buf), buf.nbytes))
+        return buf
+
+    def sync(self) -> None:
+        check(lib().stk_sync(self._h))
+
+    def close(self):
+        if self._h:
+            lib().stk_chains_destroy(self._h)
+            self._h = None
+
+
+def diag_finish(buf: np.ndarray, P: int, n_draws: int, max_lag: int):
+    mean, var, rhat, ess = (np.empty(P) for _ in range(4))
+    buf = np.ascontiguousarray(buf, dtype=np.float64)
+    check(lib().stk_diag_finish(_ptr(buf), P, n_draws, max_lag, _ptr(mean), _ptr(var), _ptr(rhat), _ptr(ess)))
+    return dict(mean=mean, var=var, rhat=rhat, ess=ess)
+
+
+# ---------------------------------------------------------------------------
+# reference-shaped entry points
+# ---------------------------------------------------------------------------
+@dataclasses.dataclass
+class CudaMethod:
+    """Mirrors StanMethod / StanHMCEngine (Stan.hs:378-440) for the static-HMC engine of
+    benchStanHMC (app/benchmark/Main.hs:248-262): num_samples draws, num_warmup discarded,
+    int_time = num_leapfrog * step_size, unit_e metric, no adaptation."""
+    num_chains: int = 4096
+    num_samples: int = 1000
+    num_warmup: int = 0
+    thin: int = 1
+    step_size: float = 0.01
+    num_leapfrog: int = 10
+    seed: int = 1
+    device: int = 0
+    kernel: str = "hmc"
+
+
+class Sampler:
+    """What compileCC returns (a closure state -> IO state), batched over chains."""
+
+    def __init__(self, module_spec: str, n_chains: int, data: Optional[dict] = None, seed: int = 1,
+                 device: int = 0, first_global_chain: int = 0, ctx: Optional[Context] = None):
+        self.ctx = ctx or Context(device)
+        self.module = Module(self.ctx, module_spec)
+        self.chains = Chains(self.module, n_chains, seed, first_global_chain)
+        for k, v in (data or {}).items():
+            self.chains.set_data(k, v)
+
+    def __call__(self, state: Optional[dict] = None, kernel: str | int = 0, n_transitions: int = 1) -> dict:
+        """runCC semantics: upload `state` (if given), run transitions, download the new state."""
+        if state:
+            for k, v in state.items():
+                self.chains.set_state(k, v, broadcast=(np.ndim(v) < 2 and np.size(v) != self.chains.n))
+        self.chains.step(kernel, n_transitions)
+        return {k: self.chains.get_state(k) for k, f in self.module.fields.items()
+                if f["state"] and not str(f["len"]).startswith("@")}
+
+    def simulate(self) -> dict:
+        self.chains.simulate()
+        self.chains.sync()
+        return {k: self.chains.get_state(k) for k, f in self.module.fields.items() if f["state"]}
+
+
+def compileCUDA(module_spec: str, n_chains: int = 1, data: Optional[dict] = None, **kw) -> Sampler:
+    """compileCC analogue (CC.hs:465-498); n_chains = 1 degenerates to its exact shape."""
+    return Sampler(module_spec, n_chains, data, **kw)
+
+
+def runCUDA(module_spec: str, state: dict, n_chains: int = 1, data: Optional[dict] = None, **kw) -> dict:
+    """runCC analogue (CC.hs:459-462): compile, run one transition, return the new state."""
+    return compileCUDA(module_spec, n_chains, data, **kw)(state)
+
+
+def hmcCUDA(method: CudaMethod, module_spec: str, data: dict, init: Optional[Sequence[float]] = None,
+            first_global_chain: int = 0) -> np.ndarray:
+    """hmcStan / hmcStanInit analogue (Stan.hs:493-500): returns draws [num_samples][P][num_chains]
+    on the unconstrained scale of the module's `q` field."""
+    s = Sampler(module_spec, method.num_chains, data, seed=method.seed, device=method.device,
+                first_global_chain=first_global_chain)
+    ch = s.chains
+    if "eps" in s.module.params:
+        ch.set_param("eps", method.step_size)
+        ch.set_param("L", method.num_leapfrog)
+    if init is not None:
+        ch.set_state("q", np.asarray(init, dtype=np.float64), broadcast=True)
+    if method.num_warmup:
+        ch.step(method.kernel, method.num_warmup)
+    ch.record(method.num_samples, method.thin)
+    ch.step(method.kernel, method.num_samples * method.thin)
+    out = ch.draws()
+    s.last_chains = ch
+    hmcCUDA.last_sampler = s
+    return out

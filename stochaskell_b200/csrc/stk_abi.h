@@ -1,0 +1,52 @@
+/* stk_abi.h — the contract between libstk_cuda's host runtime and a compiled
+ * model module (a cubin: either a hand-tuned builtin or NVRTC output of the
+ * CUDA text that stkc / Language.CUDA generates).  Plain C, no includes, so
+ * that NVRTC can compile it without a host toolchain.
+ *
+ * A module exports
+ *   __device__ const char stk_desc[]   the descriptor text (grammar below)
+ *   extern "C" __global__ kernels      each taking ONE argument: StkArgs by
+ *                                      value (__grid_constant__)
+ *
+ * Descriptor grammar (one record per line, blank-separated):
+ *   stk-module 1
+ *   name   <model name>
+ *   nparam <P>                       unconstrained parameter count (0 if n/a)
+ *   field  <name> <state|data> <f64|i32> <len>     len 0 = sized by set_data
+ *   param  <name> <default>          scalar tunable -> StkArgs.par[i]
+ *   record <field> ...               fields (as doubles) that make up a draw
+ *   kernel <name> <symbol> <block> <chains_per_block> <smem_fixed> <smem_field|-> <smem_bytes_per_elem>
+ *          transition kernels, kernel_id = order of appearance
+ *   entry  <logp|logp_grad|simulate> <symbol> <block> <chains_per_block> <smem_fixed> <smem_field|-> <smem_bytes_per_elem>
+ * Launch geometry: grid = ceil(n_chains / chains_per_block) CTAs of <block>
+ * threads, dynamic smem = smem_fixed + flen[smem_field] * bytes_per_elem.
+ *
+ * State layout in HBM: field f of per-chain length L is [L][n_chains]
+ * (chain-minor) — structure-of-arrays, coalesced across chains.
+ */
+#ifndef STK_ABI_H
+#define STK_ABI_H
+
+#define STK_MAX_FIELDS 24
+#define STK_MAX_PARAMS 16
+
+struct StkArgs {
+  long long n_chains;          /* chains in this shard                        */
+  long long chain0;            /* global index of the shard's first chain     */
+  unsigned long long seed;     /* Philox key                                  */
+  unsigned long long step0;    /* transition counter at launch start          */
+  long long n_steps;           /* transitions to run in this launch           */
+  void* field[STK_MAX_FIELDS]; /* device pointers, descriptor order           */
+  long long flen[STK_MAX_FIELDS]; /* per-chain length (state) / total (data)  */
+  double par[STK_MAX_PARAMS];  /* scalar tunables, descriptor order           */
+  double* draws;               /* [draw_slots][P_rec][n_chains] or NULL       */
+  long long draw_slots;        /* capacity of the ring                        */
+  long long draw_thin;         /* keep every thin-th transition               */
+  long long draw_base;         /* transitions recorded before this launch     */
+  long long n_rec;             /* doubles per draw per chain (P_rec)          */
+  double* out_lp;              /* [n_chains]   (logp / logp_grad entries)     */
+  double* out_grad;            /* [P][n_chains]                               */
+  unsigned long long* accept;  /* [n_chains] accepted-transition counters     */
+};
+
+#endif /* STK_ABI_H */

@@ -1,0 +1,760 @@
+// stk_runtime.cpp — host runtime of libstk_cuda.so (see include/stk_cuda.h).
+//
+// Plays the role of compileCC's closure (stochaskell/src/Language/CC.hs:465-498)
+// for the CUDA backend: compile-once (NVRTC, SHA1-keyed cubin cache like
+// CC.hs:471-479), then keep the module and the chains' state resident on the
+// GPU and run thousands of transitions per call instead of one process per
+// transition.
+//
+// CUDA runtime API only (static cudart: the library loads on a machine with
+// no driver; every compute entry point then fails loudly with STK_ERR_CUDA).
+// No torch types, no CPU fallback.
+#include "../../include/stk_cuda.h"
+#include "stk_abi.h"
+
+#include <cuda_runtime_api.h>
+#include <nvrtc.h>
+
+#include <dlfcn.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
+#include <atomic>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <fstream>
+#include <sstream>
+#include <string>
+#include <vector>
+
+namespace {
+
+thread_local std::string g_err;
+std::atomic<long long> g_launches{0};
+
+int fail(int code, const char* fmt, ...) {
+  char buf[4096];
+  va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof buf, fmt, ap); va_end(ap);
+  g_err = buf;
+  return code;
+}
+#define CU(call)                                                                   \
+  do {                                                                             \
+    cudaError_t e_ = (call);                                                       \
+    if (e_ != cudaSuccess)                                                         \
+      return fail(STK_ERR_CUDA, "%s: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+  } while (0)
+
+// ---- SHA1 (cache key, as CC.hs:472 `SHA1.hash code`) ------------------------
+struct Sha1 {
+  uint32_t h[5] = {0x67452301u, 0xEFCDAB89u, 0x98BADCFEu, 0x10325476u, 0xC3D2E1F0u};
+  static uint32_t rol(uint32_t v, int b) { return (v << b) | (v >> (32 - b)); }
+  void block(const uint8_t* p) {
+    uint32_t w[80];
+    for (int i = 0; i < 16; ++i) w[i] = (p[4 * i] << 24) | (p[4 * i + 1] << 16) | (p[4 * i + 2] << 8) | p[4 * i + 3];
+    for (int i = 16; i < 80; ++i) w[i] = rol(w[i - 3] ^ w[i - 8] ^ w[i - 14] ^ w[i - 16], 1);
+    uint32_t a = h[0], b = h[1], c = h[2], d = h[3], e = h[4];
+    for (int i = 0; i < 80; ++i) {
+      uint32_t f, k;
+      if (i < 20) { f = (b & c) | (~b & d); k = 0x5A827999u; }
+      else if (i < 40) { f = b ^ c ^ d; k = 0x6ED9EBA1u; }
+      else if (i < 60) { f = (b & c) | (b & d) | (c & d); k = 0x8F1BBCDCu; }
+      else { f = b ^ c ^ d; k = 0xCA62C1D6u; }
+      uint32_t t = rol(a, 5) + f + e + k + w[i];
+      e = d; d = c; c = rol(b, 30); b = a; a = t;
+    }
+    h[0] += a; h[1] += b; h[2] += c; h[3] += d; h[4] += e;
+  }
+  static std::string hex(const std::string& s) {
+    Sha1 x;
+    std::vector<uint8_t> m(s.begin(), s.end());
+    uint64_t bits = (uint64_t)m.size() * 8;
+    m.push_back(0x80);
+    while (m.size() % 64 != 56) m.push_back(0);
+    for (int i = 7; i >= 0; --i) m.push_back((uint8_t)(bits >> (8 * i)));
+    for (size_t i = 0; i < m.size(); i += 64) x.block(&m[i]);
+    char out[41];
+    for (int i = 0; i < 5; ++i) snprintf(out + 8 * i, 9, "%08x", x.h[i]);
+    return std::string(out, 40);
+  }
+};
+
+bool file_exists(const std::string& p) { struct stat st; return stat(p.c_str(), &st) == 0 && S_ISREG(st.st_mode); }
+bool read_file(const std::string& p, std::string* out) {
+  std::ifstream f(p, std::ios::binary);
+  if (!f) return false;
+  std::ostringstream ss; ss << f.rdbuf(); *out = ss.str();
+  return true;
+}
+int mkdirs(const std::string& p) {
+  std::string cur;
+  for (size_t i = 0; i <= p.size(); ++i) {
+    if (i == p.size() || p[i] == '/') {
+      if (!cur.empty() && cur != "/") { if (mkdir(cur.c_str(), 0777) != 0 && errno != EEXIST) return -1; }
+    }
+    if (i < p.size()) cur.push_back(p[i]);
+  }
+  return 0;
+}
+std::string lib_dir() {
+  Dl_info info;
+  if (dladdr((void*)&stk_last_error, &info) && info.dli_fname) {
+    std::string p(info.dli_fname);
+    size_t s = p.rfind('/');
+    return s == std::string::npos ? std::string(".") : p.substr(0, s);
+  }
+  return ".";
+}
+
+struct FieldDesc { std::string name; bool is_state; bool is_i32; long long len; std::string len_ref; };
+struct KernelDesc {
+  std::string name, symbol;
+  int block = 0, cpb = 1; long long smem_fixed = 0; std::string smem_field; long long smem_per = 0;
+  cudaKernel_t k = nullptr;
+};
+
+}  // namespace
+
+struct stk_ctx {
+  int device; cudaStream_t stream;
+  cudaLibrary_t diag_lib = nullptr; cudaKernel_t k_moments = nullptr, k_acov = nullptr;
+};
+
+struct stk_module {
+  stk_ctx* ctx = nullptr;
+  cudaLibrary_t lib = nullptr;
+  std::string desc, name;
+  int nparam = 0;
+  std::vector<FieldDesc> fields;
+  std::vector<std::pair<std::string, double>> params;
+  std::vector<int> record;
+  std::vector<KernelDesc> kernels;
+  KernelDesc entry[3];  // logp, logp_grad, simulate
+  bool has_entry[3] = {false, false, false};
+};
+
+struct stk_chains {
+  stk_module* mod = nullptr;
+  long long n = 0, chain0 = 0;
+  unsigned long long seed = 0, step = 0;
+  std::vector<void*> dptr;
+  std::vector<long long> flen;
+  std::vector<double> par;
+  double* draws = nullptr; long long slots = 0, thin = 1, recorded = 0, nrec = 0;
+  double* out_lp = nullptr; double* out_grad = nullptr;
+  unsigned long long* accept = nullptr;
+};
+
+namespace {
+
+int field_index(const stk_module* m, const std::string& n) {
+  for (size_t i = 0; i < m->fields.size(); ++i) if (m->fields[i].name == n) return (int)i;
+  return -1;
+}
+
+int parse_kernel_line(std::istringstream& ls, KernelDesc* k) {
+  std::string sf;
+  if (!(ls >> k->name >> k->symbol >> k->block >> k->cpb >> k->smem_fixed >> sf >> k->smem_per)) return -1;
+  k->smem_field = (sf == "-") ? "" : sf;
+  return 0;
+}
+
+int parse_desc(stk_module* m) {
+  std::istringstream in(m->desc);
+  std::string line;
+  bool header = false;
+  while (std::getline(in, line)) {
+    std::istringstream ls(line);
+    std::string kw;
+    if (!(ls >> kw)) continue;
+    if (kw == "stk-module") { int v; ls >> v; if (v != 1) return fail(STK_ERR_ARG, "descriptor version %d unsupported", v); header = true; }
+    else if (kw == "name") ls >> m->name;
+    else if (kw == "nparam") ls >> m->nparam;
+    else if (kw == "field") {
+      FieldDesc f; std::string kind, ty, len;
+      if (!(ls >> f.name >> kind >> ty >> len)) return fail(STK_ERR_ARG, "bad field line: %s", line.c_str());
+      f.is_state = (kind == "state"); f.is_i32 = (ty == "i32");
+      if (!len.empty() && len[0] == '@') { f.len = 0; f.len_ref = len.substr(1); }
+      else f.len = atoll(len.c_str());
+      if ((int)m->fields.size() >= STK_MAX_FIELDS) return fail(STK_ERR_ARG, "too many fields");
+      m->fields.push_back(f);
+    } else if (kw == "param") {
+      std::string n; double v; ls >> n >> v;
+      if ((int)m->params.size() >= STK_MAX_PARAMS) return fail(STK_ERR_ARG, "too many params");
+      m->params.push_back({n, v});
+    } else if (kw == "record") {
+      std::string n;
+      while (ls >> n) { int i = field_index(m, n); if (i < 0) return fail(STK_ERR_ARG, "record: unknown field %s", n.c_str()); m->record.push_back(i); }
+    } else if (kw == "kernel") {
+      KernelDesc k; if (parse_kernel_line(ls, &k)) return fail(STK_ERR_ARG, "bad kernel line: %s", line.c_str());
+      m->kernels.push_back(k);
+    } else if (kw == "entry") {
+      KernelDesc k; if (parse_kernel_line(ls, &k)) return fail(STK_ERR_ARG, "bad entry line: %s", line.c_str());
+      int e = k.name == "logp" ? 0 : k.name == "logp_grad" ? 1 : k.name == "simulate" ? 2 : -1;
+      if (e < 0) return fail(STK_ERR_ARG, "unknown entry %s", k.name.c_str());
+      m->entry[e] = k; m->has_entry[e] = true;
+    }
+  }
+  if (!header) return fail(STK_ERR_ARG, "module has no stk-module header");
+  return STK_OK;
+}
+
+long long state_len(const stk_chains* c, int f) {
+  const FieldDesc& fd = c->mod->fields[f];
+  if (fd.len > 0) return fd.len;
+  if (!fd.len_ref.empty()) { int r = field_index(c->mod, fd.len_ref); if (r >= 0) return c->flen[r]; }
+  return c->flen[f];
+}
+size_t elem_size(const FieldDesc& f) { return f.is_i32 ? 4 : 8; }
+
+// allocate deferred-size state fields whose size is now known
+int ensure_fields(stk_chains* c) {
+  for (size_t f = 0; f < c->mod->fields.size(); ++f) {
+    const FieldDesc& fd = c->mod->fields[f];
+    if (!fd.is_state || c->dptr[f]) continue;
+    long long L = state_len(c, (int)f);
+    if (L <= 0) continue;
+    size_t bytes = (size_t)L * (size_t)c->n * elem_size(fd);
+    CU(cudaMalloc(&c->dptr[f], bytes));
+    CU(cudaMemsetAsync(c->dptr[f], 0, bytes, c->mod->ctx->stream));
+    c->flen[f] = L;
+  }
+  return STK_OK;
+}
+
+int launch(stk_chains* c, KernelDesc& k, long long n_steps, cudaStream_t st) {
+  stk_module* m = c->mod;
+  int rc = ensure_fields(c);
+  if (rc) return rc;
+  StkArgs a;
+  memset(&a, 0, sizeof a);
+  a.n_chains = c->n; a.chain0 = c->chain0; a.seed = c->seed; a.step0 = c->step; a.n_steps = n_steps;
+  for (size_t f = 0; f < m->fields.size(); ++f) { a.field[f] = c->dptr[f]; a.flen[f] = c->flen[f]; }
+  for (size_t p = 0; p < c->par.size(); ++p) a.par[p] = c->par[p];
+  a.draws = c->draws; a.draw_slots = c->slots; a.draw_thin = c->thin; a.draw_base = c->recorded; a.n_rec = c->nrec;
+  a.out_lp = c->out_lp; a.out_grad = c->out_grad; a.accept = c->accept;
+  long long smem = k.smem_fixed;
+  if (!k.smem_field.empty()) {
+    int f = field_index(m, k.smem_field);
+    if (f < 0) return fail(STK_ERR_ARG, "kernel %s: unknown smem field %s", k.name.c_str(), k.smem_field.c_str());
+    if (c->flen[f] <= 0) return fail(STK_ERR_ARG, "kernel %s: data field %s not set", k.name.c_str(), k.smem_field.c_str());
+    smem += c->flen[f] * k.smem_per;
+  }
+  if (smem > 227 * 1024) return fail(STK_ERR_UNSUPPORTED, "kernel %s needs %lld B shared memory (> 227 KB)", k.name.c_str(), smem);
+  int block = k.block;
+  if (const char* ob = getenv("STK_BLOCK_OVERRIDE")) {  // tuning knob for kernels that size smem by block
+    (void)ob;
+  }
+  if (smem > 48 * 1024)
+    CU(cudaFuncSetAttribute((const void*)k.k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  long long grid = (c->n + k.cpb - 1) / k.cpb;
+  void* params[1] = {&a};
+  CU(cudaLaunchKernel((const void*)k.k, dim3((unsigned)grid), dim3((unsigned)block), params, (size_t)smem, st));
+  g_launches.fetch_add(1);
+  return STK_OK;
+}
+
+int need_device(stk_ctx* ctx) {
+  if (!ctx) return fail(STK_ERR_ARG, "null ctx");
+  CU(cudaSetDevice(ctx->device));
+  return STK_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* stk_last_error(void) { return g_err.c_str(); }
+int stk_abi_version(void) { return STK_ABI_VERSION; }
+int64_t stk_launch_count(void) { return g_launches.load(); }
+
+int stk_ctx_create(int device, stk_ctx** out) {
+  if (!out) return fail(STK_ERR_ARG, "null out");
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n <= 0)
+    return fail(STK_ERR_CUDA, "no CUDA device available (%s); libstk_cuda has no CPU fallback",
+                e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+  if (device < 0 || device >= n) return fail(STK_ERR_ARG, "device %d out of range (0..%d)", device, n - 1);
+  CU(cudaSetDevice(device));
+  stk_ctx* c = new stk_ctx; c->device = device; c->stream = nullptr;
+  cudaError_t e2 = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+  if (e2 != cudaSuccess) { delete c; return fail(STK_ERR_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(e2)); }
+  *out = c;
+  return STK_OK;
+}
+
+int stk_ctx_destroy(stk_ctx* ctx) {
+  if (!ctx) return STK_OK;
+  cudaSetDevice(ctx->device);
+  cudaStreamDestroy(ctx->stream);
+  if (ctx->diag_lib) cudaLibraryUnload(ctx->diag_lib);
+  delete ctx;
+  return STK_OK;
+}
+
+int stk_ctx_stream(stk_ctx* ctx, stk_stream* out) {
+  if (!ctx || !out) return fail(STK_ERR_ARG, "null argument");
+  *out = (stk_stream)ctx->stream;
+  return STK_OK;
+}
+
+int stk_compile(const char* cuda_src, const char* cache_dir, const char* include_dir,
+                char* path_out, size_t path_cap) {
+  if (!cuda_src || !path_out) return fail(STK_ERR_ARG, "null argument");
+  std::string src(cuda_src);
+  std::string dir = cache_dir && *cache_dir ? cache_dir : "cache/cuda";
+  std::string inc = include_dir && *include_dir ? include_dir : lib_dir();
+  // the device library is part of the program text: hash it too, so that a
+  // changed stk_device.cuh never resurrects a stale cubin
+  std::string devlib, abi;
+  read_file(inc + "/stk_device.cuh", &devlib);
+  read_file(inc + "/stk_abi.h", &abi);
+  std::string key = Sha1::hex(src + "\n//--\n" + devlib + "\n//--\n" + abi);
+  std::string path = dir + "/stk_" + key + ".cubin";
+  if ((size_t)path.size() + 1 > path_cap) return fail(STK_ERR_ARG, "path buffer too small");
+  if (!file_exists(path)) {
+    if (mkdirs(dir) != 0) return fail(STK_ERR_IO, "cannot create cache dir %s", dir.c_str());
+    nvrtcProgram prog;
+    if (nvrtcCreateProgram(&prog, src.c_str(), "stk_model.cu", 0, nullptr, nullptr) != NVRTC_SUCCESS)
+      return fail(STK_ERR_COMPILE, "nvrtcCreateProgram failed");
+    std::string iopt = "-I" + inc;
+    const char* opts[] = {"--gpu-architecture=sm_100a", "--std=c++17", "-lineinfo", "--fmad=true",
+                          "-default-device", iopt.c_str(), "-I/usr/local/cuda/include"};
+    nvrtcResult r = nvrtcCompileProgram(prog, (int)(sizeof opts / sizeof opts[0]), opts);
+    if (r != NVRTC_SUCCESS) {
+      size_t n = 0; nvrtcGetProgramLogSize(prog, &n);
+      std::string log(n, '\0'); if (n) nvrtcGetProgramLog(prog, &log[0]);
+      nvrtcDestroyProgram(&prog);
+      return fail(STK_ERR_COMPILE, "NVRTC: %s\n%s", nvrtcGetErrorString(r), log.c_str());
+    }
+    size_t n = 0;
+    if (nvrtcGetCUBINSize(prog, &n) != NVRTC_SUCCESS || n == 0) { nvrtcDestroyProgram(&prog); return fail(STK_ERR_COMPILE, "NVRTC produced no cubin"); }
+    std::string bin(n, '\0');
+    nvrtcGetCUBIN(prog, &bin[0]);
+    nvrtcDestroyProgram(&prog);
+    std::string tmp = path + ".tmp." + std::to_string((long long)getpid());
+    { std::ofstream f(tmp, std::ios::binary); if (!f) return fail(STK_ERR_IO, "cannot write %s", tmp.c_str()); f.write(bin.data(), (std::streamsize)bin.size()); }
+    { std::ofstream f(dir + "/stk_" + key + ".cu"); f << src; }  // keep the text beside it, like sampler_<hash>.cc
+    if (rename(tmp.c_str(), path.c_str()) != 0) return fail(STK_ERR_IO, "rename %s failed", tmp.c_str());
+  }
+  memcpy(path_out, path.c_str(), path.size() + 1);
+  return STK_OK;
+}
+
+int stk_module_load(stk_ctx* ctx, const char* spec, const char* cache_dir, stk_module** out) {
+  if (!spec || !out) return fail(STK_ERR_ARG, "null argument");
+  int rc = need_device(ctx);
+  if (rc) return rc;
+  std::string s(spec), path;
+  if (s.rfind("builtin:", 0) == 0) {
+    path = lib_dir() + "/cubin/" + s.substr(8) + ".cubin";
+    if (!file_exists(path)) return fail(STK_ERR_IO, "builtin module %s not built (%s missing; run __graft_entry__.build())", s.c_str() + 8, path.c_str());
+  } else if (s.size() > 6 && s.compare(s.size() - 6, 6, ".cubin") == 0 && s.find('\n') == std::string::npos) {
+    path = s;
+    if (!file_exists(path)) return fail(STK_ERR_IO, "cubin %s not found", path.c_str());
+  } else {
+    char buf[4096];
+    rc = stk_compile(spec, cache_dir, nullptr, buf, sizeof buf);
+    if (rc) return rc;
+    path = buf;
+  }
+  std::string bin;
+  if (!read_file(path, &bin)) return fail(STK_ERR_IO, "cannot read %s", path.c_str());
+  stk_module* m = new stk_module;
+  m->ctx = ctx;
+  cudaError_t e = cudaLibraryLoadData(&m->lib, bin.data(), nullptr, nullptr, 0, nullptr, nullptr, 0);
+  if (e != cudaSuccess) { delete m; return fail(STK_ERR_CUDA, "cudaLibraryLoadData(%s): %s", path.c_str(), cudaGetErrorString(e)); }
+  void* dptr = nullptr; size_t bytes = 0;
+  e = cudaLibraryGetGlobal(&dptr, &bytes, m->lib, "stk_desc");
+  if (e != cudaSuccess) { cudaLibraryUnload(m->lib); delete m; return fail(STK_ERR_ARG, "module %s exports no stk_desc: %s", path.c_str(), cudaGetErrorString(e)); }
+  m->desc.assign(bytes, '\0');
+  e = cudaMemcpy(&m->desc[0], dptr, bytes, cudaMemcpyDeviceToHost);
+  if (e != cudaSuccess) { cudaLibraryUnload(m->lib); delete m; return fail(STK_ERR_CUDA, "read stk_desc: %s", cudaGetErrorString(e)); }
+  while (!m->desc.empty() && m->desc.back() == '\0') m->desc.pop_back();
+  rc = parse_desc(m);
+  if (rc) { cudaLibraryUnload(m->lib); delete m; return rc; }
+  auto resolve = [&](KernelDesc& k) -> int {
+    cudaError_t e3 = cudaLibraryGetKernel(&k.k, m->lib, k.symbol.c_str());
+    if (e3 != cudaSuccess) return fail(STK_ERR_ARG, "module %s: kernel symbol %s: %s", m->name.c_str(), k.symbol.c_str(), cudaGetErrorString(e3));
+    return STK_OK;
+  };
+  for (auto& k : m->kernels) if ((rc = resolve(k))) { cudaLibraryUnload(m->lib); delete m; return rc; }
+  for (int i = 0; i < 3; ++i) if (m->has_entry[i] && (rc = resolve(m->entry[i]))) { cudaLibraryUnload(m->lib); delete m; return rc; }
+  *out = m;
+  return STK_OK;
+}
+
+int stk_module_destroy(stk_module* m) {
+  if (!m) return STK_OK;
+  cudaSetDevice(m->ctx->device);
+  cudaLibraryUnload(m->lib);
+  delete m;
+  return STK_OK;
+}
+
+int stk_module_describe(stk_module* m, char* buf, size_t cap) {
+  if (!m || !buf) return fail(STK_ERR_ARG, "null argument");
+  if (m->desc.size() + 1 > cap) return fail(STK_ERR_ARG, "buffer too small (%zu needed)", m->desc.size() + 1);
+  memcpy(buf, m->desc.c_str(), m->desc.size() + 1);
+  return STK_OK;
+}
+
+int stk_module_field(stk_module* m, const char* name) {
+  if (!m || !name) return fail(STK_ERR_ARG, "null argument");
+  int i = field_index(m, name);
+  return i >= 0 ? i : fail(STK_ERR_ARG, "unknown field %s", name);
+}
+
+int stk_module_kernel(stk_module* m, const char* name) {
+  if (!m || !name) return fail(STK_ERR_ARG, "null argument");
+  for (size_t i = 0; i < m->kernels.size(); ++i) if (m->kernels[i].name == name) return (int)i;
+  return fail(STK_ERR_ARG, "unknown kernel %s", name);
+}
+
+int stk_chains_create(stk_module* m, int64_t n_chains, uint64_t seed, stk_chains** out) {
+  if (!m || !out) return fail(STK_ERR_ARG, "null argument");
+  if (n_chains <= 0) return fail(STK_ERR_ARG, "n_chains must be positive");
+  int rc = need_device(m->ctx);
+  if (rc) return rc;
+  stk_chains* c = new stk_chains;
+  c->mod = m; c->n = n_chains; c->seed = seed;
+  c->dptr.assign(m->fields.size(), nullptr);
+  c->flen.assign(m->fields.size(), 0);
+  for (auto& p : m->params) c->par.push_back(p.second);
+  for (size_t f = 0; f < m->fields.size(); ++f) if (m->fields[f].is_state) c->flen[f] = m->fields[f].len;
+  rc = ensure_fields(c);
+  if (rc) { stk_chains_destroy(c); return rc; }
+  cudaError_t e = cudaMalloc((void**)&c->accept, sizeof(unsigned long long) * (size_t)n_chains);
+  if (e == cudaSuccess) e = cudaMemset(c->accept, 0, sizeof(unsigned long long) * (size_t)n_chains);
+  if (e == cudaSuccess) e = cudaMalloc((void**)&c->out_lp, sizeof(double) * (size_t)n_chains);
+  if (e == cudaSuccess && m->nparam > 0) e = cudaMalloc((void**)&c->out_grad, sizeof(double) * (size_t)n_chains * (size_t)m->nparam);
+  if (e != cudaSuccess) { stk_chains_destroy(c); return fail(STK_ERR_CUDA, "cudaMalloc: %s", cudaGetErrorString(e)); }
+  for (int f : m->record) c->nrec += 0 * f;  // sized at stk_record time (capacities may be deferred)
+  *out = c;
+  return STK_OK;
+}
+
+int stk_chains_destroy(stk_chains* c) {
+  if (!c) return STK_OK;
+  cudaSetDevice(c->mod->ctx->device);
+  cudaStreamSynchronize(c->mod->ctx->stream);
+  for (void* p : c->dptr) if (p) cudaFree(p);
+  if (c->draws) cudaFree(c->draws);
+  if (c->out_lp) cudaFree(c->out_lp);
+  if (c->out_grad) cudaFree(c->out_grad);
+  if (c->accept) cudaFree(c->accept);
+  delete c;
+  return STK_OK;
+}
+
+int stk_chains_set_offset(stk_chains* c, int64_t first) {
+  if (!c || first < 0) return fail(STK_ERR_ARG, "bad argument");
+  c->chain0 = first;
+  return STK_OK;
+}
+
+int stk_set_data(stk_chains* c, int field, const void* host, size_t bytes) {
+  if (!c || !host) return fail(STK_ERR_ARG, "null argument");
+  stk_module* m = c->mod;
+  if (field < 0 || field >= (int)m->fields.size() || m->fields[field].is_state) return fail(STK_ERR_ARG, "field %d is not a data field", field);
+  int rc = need_device(m->ctx);
+  if (rc) return rc;
+  const FieldDesc& fd = m->fields[field];
+  size_t es = elem_size(fd);
+  if (bytes % es) return fail(STK_ERR_ARG, "data field %s: %zu bytes is not a multiple of %zu", fd.name.c_str(), bytes, es);
+  long long len = (long long)(bytes / es);
+  if (fd.len > 0 && len != fd.len) return fail(STK_ERR_ARG, "data field %s expects %lld elements, got %lld", fd.name.c_str(), fd.len, len);
+  if (c->dptr[field] && c->flen[field] != len) { CU(cudaStreamSynchronize(m->ctx->stream)); CU(cudaFree(c->dptr[field])); c->dptr[field] = nullptr; }
+  if (!c->dptr[field]) CU(cudaMalloc(&c->dptr[field], bytes ? bytes : 8));
+  c->flen[field] = len;
+  CU(cudaMemcpyAsync(c->dptr[field], host, bytes, cudaMemcpyHostToDevice, m->ctx->stream));
+  CU(cudaStreamSynchronize(m->ctx->stream));
+  return STK_OK;
+}
+
+int stk_set_state(stk_chains* c, int field, const void* host, size_t bytes, int broadcast) {
+  if (!c || !host) return fail(STK_ERR_ARG, "null argument");
+  stk_module* m = c->mod;
+  if (field < 0 || field >= (int)m->fields.size() || !m->fields[field].is_state) return fail(STK_ERR_ARG, "field %d is not a state field", field);
+  int rc = need_device(m->ctx);
+  if (rc) return rc;
+  if ((rc = ensure_fields(c))) return rc;
+  const FieldDesc& fd = m->fields[field];
+  long long L = c->flen[field];
+  if (L <= 0 || !c->dptr[field]) return fail(STK_ERR_ARG, "state field %s has no size yet", fd.name.c_str());
+  size_t es = elem_size(fd);
+  if (broadcast) {
+    if (bytes != (size_t)L * es) return fail(STK_ERR_ARG, "state field %s (broadcast) expects %zu bytes, got %zu", fd.name.c_str(), (size_t)L * es, bytes);
+    std::vector<char> tmp((size_t)L * (size_t)c->n * es);
+    for (long long e = 0; e < L; ++e)
+      for (long long k = 0; k < c->n; ++k) memcpy(&tmp[((size_t)e * c->n + k) * es], (const char*)host + e * es, es);
+    CU(cudaMemcpyAsync(c->dptr[field], tmp.data(), tmp.size(), cudaMemcpyHostToDevice, m->ctx->stream));
+    CU(cudaStreamSynchronize(m->ctx->stream));
+  } else {
+    size_t want = (size_t)L * (size_t)c->n * es;
+    if (bytes != want) return fail(STK_ERR_ARG, "state field %s expects %zu bytes ([%lld][%lld]), got %zu", fd.name.c_str(), want, L, c->n, bytes);
+    CU(cudaMemcpyAsync(c->dptr[field], host, bytes, cudaMemcpyHostToDevice, m->ctx->stream));
+    CU(cudaStreamSynchronize(m->ctx->stream));
+  }
+  return STK_OK;
+}
+
+int stk_get_state(stk_chains* c, int field, void* host, size_t bytes) {
+  if (!c || !host) return fail(STK_ERR_ARG, "null argument");
+  stk_module* m = c->mod;
+  if (field < 0 || field >= (int)m->fields.size()) return fail(STK_ERR_ARG, "bad field %d", field);
+  int rc = need_device(m->ctx);
+  if (rc) return rc;
+  const FieldDesc& fd = m->fields[field];
+  size_t want = (size_t)c->flen[field] * elem_size(fd) * (fd.is_state ? (size_t)c->n : 1);
+  if (!c->dptr[field] || want == 0) return fail(STK_ERR_ARG, "field %s is empty", fd.name.c_str());
+  if (bytes != want) return fail(STK_ERR_ARG, "field %s holds %zu bytes, buffer is %zu", fd.name.c_str(), want, bytes);
+  CU(cudaMemcpyAsync(host, c->dptr[field], bytes, cudaMemcpyDeviceToHost, m->ctx->stream));
+  CU(cudaStreamSynchronize(m->ctx->stream));
+  return STK_OK;
+}
+
+int stk_device_ptr(stk_chains* c, int field, void** dptr, size_t* bytes) {
+  if (!c) return fail(STK_ERR_ARG, "null argument");
+  stk_module* m = c->mod;
+  if (field < 0 || field >= (int)m->fields.size()) return fail(STK_ERR_ARG, "bad field %d", field);
+  int rc = ensure_fields(c);
+  if (rc) return rc;
+  const FieldDesc& fd = m->fields[field];
+  if (dptr) *dptr = c->dptr[field];
+  if (bytes) *bytes = (size_t)c->flen[field] * elem_size(fd) * (fd.is_state ? (size_t)c->n : 1);
+  return STK_OK;
+}
+
+int stk_set_param(stk_chains* c, const char* name, double v) {
+  if (!c || !name) return fail(STK_ERR_ARG, "null argument");
+  for (size_t i = 0; i < c->mod->params.size(); ++i) if (c->mod->params[i].first == name) { c->par[i] = v; return STK_OK; }
+  return fail(STK_ERR_ARG, "module %s has no parameter %s", c->mod->name.c_str(), name);
+}
+
+int stk_get_param(stk_chains* c, const char* name, double* v) {
+  if (!c || !name || !v) return fail(STK_ERR_ARG, "null argument");
+  for (size_t i = 0; i < c->mod->params.size(); ++i) if (c->mod->params[i].first == name) { *v = c->par[i]; return STK_OK; }
+  return fail(STK_ERR_ARG, "module %s has no parameter %s", c->mod->name.c_str(), name);
+}
+
+static int run_entry(stk_chains* c, int e, const char* what) {
+  if (!c) return fail(STK_ERR_ARG, "null chains");
+  if (!c->mod->has_entry[e]) return fail(STK_ERR_UNSUPPORTED, "module %s has no %s entry", c->mod->name.c_str(), what);
+  int rc = need_device(c->mod->ctx);
+  if (rc) return rc;
+  return launch(c, c->mod->entry[e], 0, c->mod->ctx->stream);
+}
+
+int stk_logp(stk_chains* c, double* lp_host) {
+  int rc = run_entry(c, 0, "logp");
+  if (rc) return rc;
+  if (lp_host) CU(cudaMemcpyAsync(lp_host, c->out_lp, sizeof(double) * (size_t)c->n, cudaMemcpyDeviceToHost, c->mod->ctx->stream));
+  CU(cudaStreamSynchronize(c->mod->ctx->stream));
+  return STK_OK;
+}
+
+int stk_logp_grad(stk_chains* c, double* lp_host, double* grad_host) {
+  int rc = run_entry(c, 1, "logp_grad");
+  if (rc) return rc;
+  cudaStream_t st = c->mod->ctx->stream;
+  if (lp_host) CU(cudaMemcpyAsync(lp_host, c->out_lp, sizeof(double) * (size_t)c->n, cudaMemcpyDeviceToHost, st));
+  if (grad_host) CU(cudaMemcpyAsync(grad_host, c->out_grad, sizeof(double) * (size_t)c->n * (size_t)c->mod->nparam, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  return STK_OK;
+}
+
+int stk_step(stk_chains* c, int kernel_id, int64_t n_transitions, stk_stream stream) {
+  if (!c) return fail(STK_ERR_ARG, "null chains");
+  if (kernel_id < 0 || kernel_id >= (int)c->mod->kernels.size()) return fail(STK_ERR_ARG, "kernel_id %d out of range", kernel_id);
+  if (n_transitions < 0) return fail(STK_ERR_ARG, "negative n_transitions");
+  if (n_transitions == 0) return STK_OK;
+  int rc = need_device(c->mod->ctx);
+  if (rc) return rc;
+  cudaStream_t st = stream ? (cudaStream_t)stream : c->mod->ctx->stream;
+  rc = launch(c, c->mod->kernels[kernel_id], n_transitions, st);
+  if (rc) return rc;
+  if (c->draws && c->slots > 0) {
+    unsigned long long a = c->step, b = c->step + (unsigned long long)n_transitions;
+    long long add = (long long)(b / (unsigned long long)c->thin - a / (unsigned long long)c->thin);
+    c->recorded = std::min(c->slots, c->recorded + add);
+  }
+  c->step += (unsigned long long)n_transitions;
+  return STK_OK;
+}
+
+int stk_simulate(stk_chains* c, stk_stream stream) {
+  if (!c) return fail(STK_ERR_ARG, "null chains");
+  if (!c->mod->has_entry[2]) return fail(STK_ERR_UNSUPPORTED, "module %s has no simulate entry", c->mod->name.c_str());
+  int rc = need_device(c->mod->ctx);
+  if (rc) return rc;
+  cudaStream_t st = stream ? (cudaStream_t)stream : c->mod->ctx->stream;
+  return launch(c, c->mod->entry[2], 0, st);
+}
+
+int stk_record(stk_chains* c, int64_t n_slots, int64_t thin) {
+  if (!c || n_slots < 0 || thin < 1) return fail(STK_ERR_ARG, "bad argument");
+  int rc = need_device(c->mod->ctx);
+  if (rc) return rc;
+  CU(cudaStreamSynchronize(c->mod->ctx->stream));
+  if (c->draws) { CU(cudaFree(c->draws)); c->draws = nullptr; }
+  c->slots = 0; c->recorded = 0; c->thin = thin;
+  if (n_slots == 0) return STK_OK;
+  if ((rc = ensure_fields(c))) return rc;
+  long long nrec = 0;
+  for (int f : c->mod->record) nrec += c->flen[f];
+  if (nrec <= 0) return fail(STK_ERR_UNSUPPORTED, "module %s records nothing", c->mod->name.c_str());
+  c->nrec = nrec;
+  CU(cudaMalloc((void**)&c->draws, sizeof(double) * (size_t)n_slots * (size_t)nrec * (size_t)c->n));
+  c->slots = n_slots;
+  return STK_OK;
+}
+
+int stk_get_draws(stk_chains* c, double* host, size_t bytes, int64_t* n_recorded) {
+  if (!c) return fail(STK_ERR_ARG, "null chains");
+  if (n_recorded) *n_recorded = c->recorded;
+  if (!host) return STK_OK;
+  int rc = need_device(c->mod->ctx);
+  if (rc) return rc;
+  size_t want = sizeof(double) * (size_t)c->recorded * (size_t)c->nrec * (size_t)c->n;
+  if (bytes < want) return fail(STK_ERR_ARG, "draws need %zu bytes, buffer is %zu", want, bytes);
+  if (want) CU(cudaMemcpyAsync(host, c->draws, want, cudaMemcpyDeviceToHost, c->mod->ctx->stream));
+  CU(cudaStreamSynchronize(c->mod->ctx->stream));
+  return STK_OK;
+}
+
+int stk_sync(stk_chains* c) {
+  if (!c) return fail(STK_ERR_ARG, "null chains");
+  int rc = need_device(c->mod->ctx);
+  if (rc) return rc;
+  CU(cudaStreamSynchronize(c->mod->ctx->stream));
+  return STK_OK;
+}
+
+int stk_num_params(stk_chains* c) { return c ? c->mod->nparam : fail(STK_ERR_ARG, "null chains"); }
+int64_t stk_num_chains(stk_chains* c) { return c ? c->n : (int64_t)fail(STK_ERR_ARG, "null chains"); }
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------
+// diagnostics (R-hat / ESS); kernels in models/diag.cu
+// ---------------------------------------------------------------------------
+static int load_diag(stk_ctx* ctx) {
+  if (ctx->diag_lib) return STK_OK;
+  std::string path = lib_dir() + "/cubin/diag.cubin", bin;
+  if (!read_file(path, &bin)) return fail(STK_ERR_IO, "%s missing; run __graft_entry__.build()", path.c_str());
+  CU(cudaLibraryLoadData(&ctx->diag_lib, bin.data(), nullptr, nullptr, 0, nullptr, nullptr, 0));
+  CU(cudaLibraryGetKernel(&ctx->k_moments, ctx->diag_lib, "diag_moments"));
+  CU(cudaLibraryGetKernel(&ctx->k_acov, ctx->diag_lib, "diag_acov"));
+  return STK_OK;
+}
+
+extern "C" {
+
+// additive diagnostics buffer of this shard: [4][P] moments then [P][max_lag+1]
+// mean-over-chains autocovariance SUMS.  bytes = 8 * P * (4 + max_lag + 1).
+int stk_diag_partial(stk_chains* c, int64_t max_lag, double* buf, size_t bytes) {
+  if (!c || !buf) return fail(STK_ERR_ARG, "null argument");
+  if (!c->draws || c->recorded < 2) return fail(STK_ERR_ARG, "need at least 2 recorded draws (stk_record + stk_step)");
+  int rc = need_device(c->mod->ctx);
+  if (rc) return rc;
+  stk_ctx* ctx = c->mod->ctx;
+  if ((rc = load_diag(ctx))) return rc;
+  long long N = c->recorded, C = c->n; int P = (int)c->nrec;
+  if (max_lag < 0 || max_lag > N - 1) max_lag = N - 1;
+  size_t want = sizeof(double) * (size_t)P * (size_t)(4 + max_lag + 1);
+  if (bytes != want) return fail(STK_ERR_ARG, "diag buffer must be %zu bytes, got %zu", want, bytes);
+  double *d_buf = nullptr, *d_mean = nullptr;
+  CU(cudaMalloc((void**)&d_buf, want));
+  cudaError_t e = cudaMalloc((void**)&d_mean, sizeof(double) * (size_t)P * (size_t)C);
+  if (e != cudaSuccess) { cudaFree(d_buf); return fail(STK_ERR_CUDA, "cudaMalloc: %s", cudaGetErrorString(e)); }
+  cudaStream_t st = ctx->stream;
+  cudaMemsetAsync(d_buf, 0, want, st);
+  const double* draws = c->draws;
+  {
+    void* args[] = {(void*)&draws, &N, &P, &C, &d_mean, &d_buf};
+    dim3 grid((unsigned)((C + 255) / 256), (unsigned)P);
+    e = cudaLaunchKernel((const void*)ctx->k_moments, grid, dim3(256), args, 0, st);
+    g_launches.fetch_add(1);
+  }
+  if (e == cudaSuccess) {
+    int CB = 32;
+    while (CB > 1 && (size_t)N * CB * 8 > 200 * 1024) CB >>= 1;
+    size_t smem = (size_t)N * CB * 8;
+    if (smem > 227 * 1024) { cudaFree(d_buf); cudaFree(d_mean); return fail(STK_ERR_UNSUPPORTED, "too many draws (%lld) for the ESS kernel; thin the record", N); }
+    if (smem > 48 * 1024) e = cudaFuncSetAttribute((const void*)ctx->k_acov, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    double* d_acov = d_buf + 4 * (size_t)P;
+    long long ml = max_lag;
+    void* args[] = {(void*)&draws, &d_mean, &N, &P, &C, &CB, &ml, &d_acov};
+    dim3 grid((unsigned)((C + CB - 1) / CB), (unsigned)P);
+    if (e == cudaSuccess) e = cudaLaunchKernel((const void*)ctx->k_acov, grid, dim3(256), args, smem, st);
+    g_launches.fetch_add(1);
+  }
+  if (e == cudaSuccess) e = cudaMemcpyAsync(buf, d_buf, want, cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  cudaFree(d_buf); cudaFree(d_mean);
+  if (e != cudaSuccess) return fail(STK_ERR_CUDA, "diagnostics: %s", cudaGetErrorString(e));
+  return STK_OK;
+}
+
+// host-side finish on an (all-reduced) additive buffer.  Pure arithmetic on
+// O(P * max_lag) numbers: Gelman-Rubin R-hat and Geyer initial-monotone ESS,
+// compute_effective_sample_size.hpp:47-118.
+int stk_diag_finish(const double* buf, int P, int64_t n_draws, int64_t max_lag,
+                    double* mean, double* var, double* rhat, double* ess) {
+  if (!buf || P <= 0 || n_draws < 2 || max_lag < 1) return fail(STK_ERR_ARG, "bad argument");
+  const double N = (double)n_draws;
+  for (int r = 0; r < P; ++r) {
+    double M = buf[0 * P + r], sm = buf[1 * P + r], sm2 = buf[2 * P + r], sv = buf[3 * P + r];
+    if (M < 1) return fail(STK_ERR_ARG, "empty diagnostics buffer");
+    const double* ac = buf + 4 * (size_t)P + (size_t)r * (size_t)(max_lag + 1);  // sums over chains
+    double mean_var = sv / M;
+    double var_plus = mean_var * (N - 1) / N;
+    if (M > 1) var_plus += (sm2 - sm * sm / M) / (M - 1);
+    if (mean) mean[r] = sm / M;
+    if (var) var[r] = var_plus;
+    if (rhat) rhat[r] = std::sqrt(var_plus / mean_var);
+    if (ess) {
+      std::vector<double> rho((size_t)max_lag + 3, 0.0);
+      auto rho_at = [&](long long t) { return 1.0 - (mean_var - ac[t] / M) / var_plus; };
+      double even = 1.0, odd = rho_at(1);
+      rho[0] = even; rho[1] = odd;
+      long long s = 1;
+      while (s < n_draws - 4 && s + 2 <= max_lag && even + odd > 0) {
+        even = rho_at(s + 1); odd = rho_at(s + 2);
+        if (even + odd >= 0) { rho[s + 1] = even; rho[s + 2] = odd; }
+        s += 2;
+      }
+      long long max_s = s;
+      if (even > 0) rho[max_s + 1] = even;
+      for (long long k = 1; k <= max_s - 3; k += 2)
+        if (rho[k + 1] + rho[k + 2] > rho[k - 1] + rho[k]) { rho[k + 1] = (rho[k - 1] + rho[k]) / 2; rho[k + 2] = rho[k + 1]; }
+      double tau = -1.0;
+      for (long long k = 0; k < max_s; ++k) tau += 2 * rho[k];
+      tau += rho[max_s + 1];
+      double tot = M * N;
+      ess[r] = std::min(tot / tau, tot * std::log10(tot));
+    }
+  }
+  return STK_OK;
+}
+
+int stk_moments(stk_chains* c, double* mean, double* var, double* rhat, double* ess, double* moments4) {
+  if (!c) return fail(STK_ERR_ARG, "null chains");
+  long long N = c->recorded; int P = (int)c->nrec;
+  if (N < 4) return fail(STK_ERR_ARG, "need at least 4 recorded draws");
+  long long max_lag = N - 1;
+  std::vector<double> buf((size_t)P * (size_t)(4 + max_lag + 1));
+  int rc = stk_diag_partial(c, max_lag, buf.data(), buf.size() * sizeof(double));
+  if (rc) return rc;
+  if (moments4) memcpy(moments4, buf.data(), sizeof(double) * 4 * (size_t)P);
+  return stk_diag_finish(buf.data(), P, N, max_lag, mean, var, rhat, ess);
+}
+
+}  // extern "C"
+
+extern "C" int stk_num_recorded_values(stk_chains* c) { return c ? (int)c->nrec : fail(STK_ERR_ARG, "null chains"); }

@@ -1,0 +1,345 @@
+#!/usr/bin/env python
+"""bench.py — MCMC chain-transitions/sec on B200 (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload coal_rj|linreg_hmc|...]
+  python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...
+  python bench.py --impl reference ...      # the CPU arm (oracle / oracle/_ref), host cores only
+
+One "step" = one launch of the fused transition kernel: `--transitions` transitions of every
+chain of this GPU's shard (4096 chains per GPU, weak scaling: chains are independent, no
+data-path collective).  `value` = chains x transitions x steps / device time,
+whole job, inputs resident in HBM.  `e2e` = the same through the public API with HOST buffers
+(runCC semantics: state uploaded, transitions run, state downloaded — every step).
+Prints ONE JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "mcmc_chain_transitions_per_sec"
+UNIT = "transitions/s"
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(hbm_gbs=float(d["hbm_gbs"]), bf16_tflops=float(d.get("bf16_tflops", 1585.2)), source="measured")
+    return dict(hbm_gbs=6650.0, bf16_tflops=1590.0, source="fallback")
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks + throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        super().__init__(daemon=True)
+        self.index = index
+        self.rows = []
+        self.proc = None
+
+    def run(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            for line in self.proc.stdout:
+                self.rows.append([t.strip() for t in line.split(",")])
+        except Exception:
+            pass
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+        self.join(timeout=2)
+        sm, mx, reasons = [], 0.0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx = max(mx, float(r[1]))
+                for k, nm in enumerate(names):
+                    if r[3 + k].lower().startswith("active"):
+                        reasons.add(nm)
+            except Exception:
+                continue
+        return dict(sm_mhz=float(np.median(sm)) if sm else None, sm_max_mhz=mx or None,
+                    reasons=sorted(reasons), samples=len(sm))
+
+
+# ---------------------------------------------------------------------------
+# workloads (BASELINE.json configs; synthetic inputs of SURVEY 8d)
+# ---------------------------------------------------------------------------
+class LinregHMC:
+    """C1: Bayesian linear regression n=1000, d=10, static HMC eps=0.01 L=10 (benchStanHMC shape)."""
+    name = "linreg_hmc"
+    module = "builtin:linreg"
+    kernel = "hmc"
+    symbol = "linreg_hmc"
+    dtype = "f64"
+    n, d, L, eps = 1000, 10, 10, 0.01
+    state_fields = ("q",)
+
+    def __init__(self):
+        rng = np.random.default_rng(20261104)
+        self.X = rng.standard_normal((self.n, self.d))
+        w = rng.standard_normal(self.d)
+        self.y = self.X @ w + 0.5 + rng.standard_normal(self.n)
+        # per logp+grad evaluation per chain: 8(nd+n) data + 8*2P state
+        self.bytes_per_eval = 8 * (self.n * self.d + self.n) + 8 * 2 * (self.d + 2)
+        self.bytes_per_transition = (self.L + 1) * self.bytes_per_eval
+        self.describe = (f"C1 linreg n={self.n} d={self.d}, static HMC eps={self.eps} L={self.L} unit_e "
+                         f"(configs[0] shape at 4096 chains/GPU)")
+
+    def data(self):
+        return dict(X=self.X, y=self.y)
+
+    def params(self):
+        return dict(eps=self.eps, L=self.L)
+
+    def init_state(self, C, chain0):
+        rng = np.random.default_rng(1234 + chain0)
+        return dict(q=np.ascontiguousarray(0.1 * rng.standard_normal((self.d + 2, C))))
+
+    def cpu_run(self, orc, state, T, seed, chain0, step0, nthreads):
+        return orc.linreg_hmc_run(self.X, self.y, state["q"], T, self.eps, self.L, seed, chain0, step0, nthreads)
+
+
+WORKLOADS = {"linreg_hmc": LinregHMC}
+DEFAULT_WORKLOAD = "linreg_hmc"
+
+
+def cpu_arm(wl, orc, C, T, steps, warmup, nthreads):
+    """The reference arm / cpu_baseline: the CPU restatement on host cores, bounded sample."""
+    st = wl.init_state(C, 0)
+    for w in range(warmup):
+        wl.cpu_run(orc, st, 1, 1, 0, w, nthreads)
+    t0 = time.perf_counter()
+    for k in range(steps):
+        wl.cpu_run(orc, st, T, 1, 0, warmup + k * T, nthreads)
+    dt = time.perf_counter() - t0
+    return C * T * steps / dt, dt
+
+
+def host_threads():
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def reference_arm(args, wl):
+    """--impl reference: the reference's CPU implementation of the path on the host cores
+    (oracle port; `kind` says which), same metric/config, bounded sample per step."""
+    from tests.oracle_binding import oracle
+    orc = oracle()
+    nt = host_threads()
+    C = 2 * nt
+    # calibrate so that the whole run (steps + warmup) stays within ~2 minutes
+    st = wl.init_state(C, 0)
+    t0 = time.perf_counter(); wl.cpu_run(orc, st, 4, 1, 0, 0, nt); dt = time.perf_counter() - t0
+    per_tr = dt / 4
+    budget = 90.0 / max(1, args.steps + args.warmup)
+    T = int(max(1, min(args.transitions, budget / max(per_tr, 1e-9))))
+    for w in range(args.warmup):
+        wl.cpu_run(orc, st, T, 1, 0, 10 + w * T, nt)
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        wl.cpu_run(orc, st, T, 1, 0, 10 + (args.warmup + k) * T, nt)
+    dt = time.perf_counter() - t0
+    val = C * T * args.steps / dt
+    sample = f"{C} chains x {T} transitions per step on {nt} host threads (one sequential chain per thread)"
+    out = dict(metric=METRIC, value=val, unit=UNIT, impl="reference", n_gpus=args.gpus, steps=args.steps,
+               warmup=args.warmup, ms_per_step=1e3 * dt / args.steps, higher_is_better=True, scaling="weak",
+               vs_baseline=None, dtype=wl.dtype, data="synthetic",
+               config=dict(workload=wl.describe, chains_per_step=C, transitions_per_step=T),
+               cpu_baseline=dict(value=val, unit=UNIT, cores=nt, kind=wl_kind(wl), sample=sample),
+               e2e=dict(value=val, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0), gpu_launches=0)
+    print(json.dumps(out), flush=True)
+
+
+def wl_kind(wl):
+    return getattr(wl, "cpu_kind", "port")
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--chains", type=int, default=4096, help="chains per GPU")
+    ap.add_argument("--transitions", type=int, default=0, help="fused transitions per step (0 = workload default)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    wl = WORKLOADS[args.workload]()
+    if args.transitions <= 0:
+        args.transitions = getattr(wl, "transitions_per_step", 100)
+    args.warmup = max(args.warmup, 3) if args.impl == "native" else args.warmup
+
+    if args.impl == "reference":
+        if rank == 0:
+            reference_arm(args, wl)
+        return 0
+
+    import torch
+    import torch.distributed as dist
+    from stochaskell_b200 import Sampler, lib
+    if not torch.cuda.is_available():
+        print(json.dumps(dict(error="no CUDA device; libstk_cuda has no CPU fallback")), flush=True)
+        return 2
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dev = torch.device("cuda", local)
+    C, T, K, W = args.chains, args.transitions, args.steps, args.warmup
+    chain0 = rank * C
+    s = Sampler(wl.module, C, wl.data(), seed=20261104, device=local, first_global_chain=chain0)
+    ch = s.chains
+    for k, v in wl.params().items():
+        ch.set_param(k, v)
+    st0 = wl.init_state(C, chain0)
+    for k, v in st0.items():
+        ch.set_state(k, v)
+    stream = torch.cuda.ExternalStream(s.ctx.stream, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+
+    def barrier():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    with torch.cuda.stream(stream):
+        for _ in range(W):
+            flush.zero_(); ch.step(wl.kernel, T)
+        barrier()
+        clocks = ClockSampler(local) if rank == 0 else None
+        if clocks:
+            clocks.start()
+        l0 = lib().stk_launch_count()
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+        barrier()
+        t_wall = time.perf_counter()
+        for k in range(K):
+            flush.zero_()
+            ev[k][0].record(stream)
+            ch.step(wl.kernel, T)
+            ev[k][1].record(stream)
+        barrier()
+        t_wall = time.perf_counter() - t_wall
+        launches = lib().stk_launch_count() - l0
+        dev_ms = sum(a.elapsed_time(b) for a, b in ev)
+        clk = clocks.stop() if clocks else None
+    tm = torch.tensor([dev_ms, t_wall * 1e3], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+    dev_ms, wall_ms = float(tm[0]), float(tm[1])
+    value = world * C * T * K / (dev_ms * 1e-3)
+
+    # ---- e2e: public API, HOST (pinned) buffers, H2D + kernel + D2H inside the timed region -----
+    e2e = None
+    if not args.no_e2e:
+        fields = [f for f, d in s.module.fields.items() if d["state"] and not str(d["len"]).startswith("@")]
+        host_in = {k: torch.from_numpy(v.copy()).pin_memory().numpy() for k, v in st0.items()}
+        host_out = {}
+        for f in fields:
+            _, nb = ch.device_ptr(f)
+            dt = s.module.fields[f]["dtype"]
+            host_out[f] = torch.empty(nb // np.dtype(dt).itemsize, dtype=torch.from_numpy(np.empty(0, dt)).dtype).pin_memory().numpy()
+        h2d = sum(v.nbytes for v in host_in.values()); d2h = sum(v.nbytes for v in host_out.values())
+
+        def e2e_step():
+            for k, v in host_in.items():
+                ch.set_state(k, v)
+            ch.step(wl.kernel, T)
+            for f in fields:
+                ch.get_state(f, out=host_out[f])
+            for k in host_in:  # next step starts from the downloaded state, like a runCC loop
+                host_in[k][...] = host_out[k].reshape(host_in[k].shape)
+        for _ in range(2):
+            e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(K):
+            e2e_step()
+        barrier()
+        te = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        e2e = dict(value=world * C * T * K / float(te[0]), unit=UNIT, h2d_bytes_per_step=h2d, d2h_bytes_per_step=d2h)
+
+    # ---- cross-chain diagnostics: the ONE collective of the path (R-hat/ESS moments) --
+    diag = None
+    try:
+        ch.record(32, 1)
+        ch.step(wl.kernel, 32)
+        max_lag = 31
+        buf = torch.from_numpy(ch.diag_partial(max_lag)).to(dev)
+        if world > 1:
+            dist.all_reduce(buf, op=dist.ReduceOp.SUM)  # NCCL over NVLink
+        from stochaskell_b200 import diag_finish
+        P = lib().stk_num_recorded_values(ch._h)
+        r = diag_finish(buf.cpu().numpy(), P, 32, max_lag)
+        diag = dict(rhat_max=float(np.nanmax(r["rhat"])), ess_min=float(np.nanmin(r["ess"])), draws=32,
+                    chains=world * C, collective="nccl all_reduce(sum) of [P*(4+max_lag+1)] f64" if world > 1 else "none (1 GPU)")
+    except Exception as e:  # diagnostics are not part of the timed path
+        diag = dict(error=str(e)[:200])
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    peaks = measured_peaks()
+    ms_per_launch = dev_ms / K
+    alg_bytes = C * T * wl.bytes_per_transition
+    achieved = alg_bytes / (ms_per_launch * 1e-3) / 1e9
+    roofline = dict(bound="hbm", achieved=achieved, peak=peaks["hbm_gbs"], unit="GB/s", frac=achieved / peaks["hbm_gbs"],
+                    traffic=getattr(wl, "ncu_traffic_bytes", None), kernel=wl.symbol, peak_source=peaks["source"],
+                    algorithmic_bytes_per_transition=wl.bytes_per_transition,
+                    note=getattr(wl, "roofline_note", "observed data is shared by all chains and staged in shared "
+                                 "memory once per launch, so algorithmic bytes exceed physical DRAM traffic"))
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        from tests.oracle_binding import oracle
+        orc = oracle()
+        nt = host_threads()
+        Cs = 2 * nt
+        stc = wl.init_state(Cs, 0)
+        t0 = time.perf_counter(); wl.cpu_run(orc, stc, 4, 1, 0, 0, nt); per_tr = (time.perf_counter() - t0) / 4
+        Ts = int(max(1, min(100000, 12.0 / max(per_tr, 1e-9))))
+        v, dt = cpu_arm(wl, orc, Cs, Ts, 1, 0, nt)
+        cpu = dict(value=v, unit=UNIT, cores=nt, kind=wl_kind(wl),
+                   sample=f"{Cs} chains x {Ts} transitions of the same workload on {nt} host threads ({dt:.1f} s)")
+    out = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=K, warmup=W, ms_per_step=ms_per_launch,
+               higher_is_better=True, scaling="weak", vs_baseline=None, dtype=wl.dtype, data="synthetic",
+               config=dict(workload=wl.describe, chains_per_gpu=C, transitions_per_step=T, parallelism=f"chains-sharded x{world}",
+                           l2="flushed (256 MiB memset) before every step, outside the per-step CUDA events",
+                           wall_ms_per_step_incl_flush=wall_ms / K),
+               roofline=roofline, cpu_baseline=cpu, e2e=e2e, gpu_launches=int(launches), clocks=clk, diagnostics=diag)
+    print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

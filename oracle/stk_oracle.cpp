@@ -231,3 +231,34 @@ extern "C" void orc_linreg_simulate(const double* X, int n, int d, uint64_t seed
     ysim[i] = mu + sigma * orc_normal(&g2);
   }
 }
+
+// ---------------------------------------------------------------------------
+// CPU-baseline driver (bench.py cpu_baseline / --impl reference): C chains x T
+// static-HMC transitions, one chain at a time per host thread (the reference's
+// own execution shape: one sequential chain per process/core).  q is [P][C].
+// ---------------------------------------------------------------------------
+#include <atomic>
+#include <thread>
+extern "C" long long orc_linreg_hmc_run(const double* X, const double* y, int n, int d, double* q, long long C,
+                                        long long T, double eps, int L, uint64_t seed, uint64_t chain0,
+                                        uint64_t step0, int nthreads) {
+  const int P = d + 2;
+  std::atomic<long long> next{0}, accepted{0};
+  auto work = [&]() {
+    std::vector<double> qc(P);
+    for (;;) {
+      long long c = next.fetch_add(1);
+      if (c >= C) break;
+      for (int j = 0; j < P; ++j) qc[j] = q[(size_t)j * C + c];
+      long long acc = 0;
+      for (long long t = 0; t < T; ++t) acc += orc_linreg_hmc_step(X, y, n, d, qc.data(), eps, L, seed, chain0 + c, step0 + t, nullptr);
+      for (int j = 0; j < P; ++j) q[(size_t)j * C + c] = qc[j];
+      accepted.fetch_add(acc);
+    }
+  };
+  if (nthreads <= 1) { work(); return accepted.load(); }
+  std::vector<std::thread> th;
+  for (int i = 0; i < nthreads; ++i) th.emplace_back(work);
+  for (auto& t : th) t.join();
+  return accepted.load();
+}

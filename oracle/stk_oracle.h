@@ -66,6 +66,9 @@ int orc_linreg_mh_step(const double* X, const double* y, int n, int d, double* q
                        uint64_t seed, uint64_t chain, uint64_t step, double* lp_io);
 // forward simulation: q[d+2] and ysim[n]
 void orc_linreg_simulate(const double* X, int n, int d, uint64_t seed, uint64_t chain, double* q, double* ysim);
+// CPU-baseline driver: C chains x T transitions on nthreads host threads; q is [P][C]; returns #accepted
+long long orc_linreg_hmc_run(const double* X, const double* y, int n, int d, double* q, long long C, long long T,
+                             double eps, int L, uint64_t seed, uint64_t chain0, uint64_t step0, int nthreads);
 
 #ifdef __cplusplus
 }

@@ -137,11 +137,13 @@ class Chains:
         a = np.ascontiguousarray(value, dtype=f["dtype"])
         check(lib().stk_set_state(self._h, f["index"], _ptr(a), a.nbytes, 1 if broadcast else 0))
 
-    def get_state(self, name: str) -> np.ndarray:
+    def get_state(self, name: str, out: Optional[np.ndarray] = None) -> np.ndarray:
+        """download a field; `out` (flat, right dtype, e.g. a pinned buffer) avoids the allocation"""
         f = self._field(name)
-        d = C.c_void_p(); nb = C.c_size_t()
-        check(lib().stk_device_ptr(self._h, f["index"], C.byref(d), C.byref(nb)))
-        out = np.empty(nb.value // np.dtype(f["dtype"]).itemsize, dtype=f["dtype"])
+        if out is None:
+            d = C.c_void_p(); nb = C.c_size_t()
+            check(lib().stk_device_ptr(self._h, f["index"], C.byref(d), C.byref(nb)))
+            out = np.empty(nb.value // np.dtype(f["dtype"]).itemsize, dtype=f["dtype"])
         check(lib().stk_get_state(self._h, f["index"], _ptr(out), out.nbytes))
         return out.reshape(-1, self.n) if f["state"] else out
 

@@ -33,6 +33,9 @@ class Oracle:
         l.orc_linreg_mh_step.argtypes = [P, P, C.c_int, C.c_int, P, D, C.c_uint64, C.c_uint64, C.c_uint64, P]
         l.orc_linreg_simulate.restype = None
         l.orc_linreg_simulate.argtypes = [P, C.c_int, C.c_int, C.c_uint64, C.c_uint64, P, P]
+        l.orc_linreg_hmc_run.restype = C.c_longlong
+        l.orc_linreg_hmc_run.argtypes = [P, P, C.c_int, C.c_int, P, C.c_longlong, C.c_longlong, D, C.c_int,
+                                         C.c_uint64, C.c_uint64, C.c_uint64, C.c_int]
         l.orc_philox4x32_10.restype = None
         l.orc_philox4x32_10.argtypes = [P, P, P]
         l.orc_u01x2.restype = None
@@ -78,6 +81,13 @@ class Oracle:
         q = np.empty(d + 2); ys = np.empty(n)
         self.l.orc_linreg_simulate(_p(X), n, d, seed, chain, _p(q), _p(ys))
         return q, ys
+
+    def linreg_hmc_run(self, X, y, q, T, eps, L, seed, chain0=0, step0=0, nthreads=1):
+        """q [P][C] float64 contiguous, updated in place; returns #accepted"""
+        X = np.ascontiguousarray(X, dtype=np.float64); y = np.ascontiguousarray(y, dtype=np.float64)
+        n, d = X.shape
+        assert q.flags.c_contiguous and q.dtype == np.float64 and q.shape[0] == d + 2
+        return self.l.orc_linreg_hmc_run(_p(X), _p(y), n, d, _p(q), q.shape[1], T, eps, L, seed, chain0, step0, nthreads)
 
     def philox(self, ctr, key):
         c = np.asarray(ctr, dtype=np.uint32); k = np.asarray(key, dtype=np.uint32); o = np.empty(4, dtype=np.uint32)

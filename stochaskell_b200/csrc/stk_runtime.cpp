@@ -16,6 +16,8 @@
 #include <nvrtc.h>
 
 #include <dlfcn.h>
+#include <execinfo.h>
+#include <signal.h>
 #include <sys/stat.h>
 #include <unistd.h>
 
@@ -34,6 +36,20 @@ namespace {
 
 thread_local std::string g_err;
 std::atomic<long long> g_launches{0};
+
+void segv_handler(int sig) {
+  void* bt[64]; int n = backtrace(bt, 64);
+  fprintf(stderr, "[stk] signal %d, native backtrace:\n", sig);
+  backtrace_symbols_fd(bt, n, 2);
+  _exit(139);
+}
+bool init_trace() {
+  bool on = getenv("STK_TRACE") != nullptr;
+  if (on) signal(SIGSEGV, segv_handler);
+  return on;
+}
+bool g_trace = init_trace();
+#define TRACE(...) do { if (g_trace) { fprintf(stderr, "[stk] " __VA_ARGS__); fputc('\n', stderr); fflush(stderr); } } while (0)
 
 int fail(int code, const char* fmt, ...) {
   char buf[4096];
@@ -169,6 +185,7 @@ int parse_desc(stk_module* m) {
   while (std::getline(in, line)) {
     std::istringstream ls(line);
     std::string kw;
+    TRACE("desc line: %s", line.c_str());
     if (!(ls >> kw)) continue;
     if (kw == "stk-module") { int v; ls >> v; if (v != 1) return fail(STK_ERR_ARG, "descriptor version %d unsupported", v); header = true; }
     else if (kw == "name") ls >> m->name;
@@ -251,6 +268,7 @@ int launch(stk_chains* c, KernelDesc& k, long long n_steps, cudaStream_t st) {
   if (smem > 48 * 1024)
     CU(cudaFuncSetAttribute((const void*)k.k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   long long grid = (c->n + k.cpb - 1) / k.cpb;
+  TRACE("launch %s grid=%lld block=%d smem=%lld steps=%lld", k.symbol.c_str(), grid, block, smem, n_steps);
   void* params[1] = {&a};
   CU(cudaLaunchKernel((const void*)k.k, dim3((unsigned)grid), dim3((unsigned)block), params, (size_t)smem, st));
   g_launches.fetch_add(1);
@@ -366,18 +384,24 @@ int stk_module_load(stk_ctx* ctx, const char* spec, const char* cache_dir, stk_m
   if (!read_file(path, &bin)) return fail(STK_ERR_IO, "cannot read %s", path.c_str());
   stk_module* m = new stk_module;
   m->ctx = ctx;
+  TRACE("module_load %s (%zu bytes)", path.c_str(), bin.size());
   cudaError_t e = cudaLibraryLoadData(&m->lib, bin.data(), nullptr, nullptr, 0, nullptr, nullptr, 0);
   if (e != cudaSuccess) { delete m; return fail(STK_ERR_CUDA, "cudaLibraryLoadData(%s): %s", path.c_str(), cudaGetErrorString(e)); }
+  TRACE("library loaded");
   void* dptr = nullptr; size_t bytes = 0;
   e = cudaLibraryGetGlobal(&dptr, &bytes, m->lib, "stk_desc");
   if (e != cudaSuccess) { cudaLibraryUnload(m->lib); delete m; return fail(STK_ERR_ARG, "module %s exports no stk_desc: %s", path.c_str(), cudaGetErrorString(e)); }
+  TRACE("stk_desc at %p, %zu bytes", dptr, bytes);
   m->desc.assign(bytes, '\0');
   e = cudaMemcpy(&m->desc[0], dptr, bytes, cudaMemcpyDeviceToHost);
   if (e != cudaSuccess) { cudaLibraryUnload(m->lib); delete m; return fail(STK_ERR_CUDA, "read stk_desc: %s", cudaGetErrorString(e)); }
   while (!m->desc.empty() && m->desc.back() == '\0') m->desc.pop_back();
+  TRACE("descriptor read:\n%s", m->desc.c_str());
   rc = parse_desc(m);
   if (rc) { cudaLibraryUnload(m->lib); delete m; return rc; }
+  TRACE("descriptor parsed: %zu fields, %zu kernels", m->fields.size(), m->kernels.size());
   auto resolve = [&](KernelDesc& k) -> int {
+    TRACE("resolve %s", k.symbol.c_str());
     cudaError_t e3 = cudaLibraryGetKernel(&k.k, m->lib, k.symbol.c_str());
     if (e3 != cudaSuccess) return fail(STK_ERR_ARG, "module %s: kernel symbol %s: %s", m->name.c_str(), k.symbol.c_str(), cudaGetErrorString(e3));
     return STK_OK;

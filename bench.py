@@ -289,8 +289,9 @@ def main():
     # ---- cross-chain diagnostics: the ONE collective of the path (R-hat/ESS moments) --
     diag = None
     try:
-        ch.record(32, 1)
-        ch.step(wl.kernel, 32)
+        ch.step(wl.kernel, getattr(wl, "diag_warmup", 300))  # move off the synthetic init before judging mixing
+        ch.record(32, getattr(wl, "diag_thin", 4))
+        ch.step(wl.kernel, 32 * getattr(wl, "diag_thin", 4))
         max_lag = 31
         buf = torch.from_numpy(ch.diag_partial(max_lag)).to(dev)
         if world > 1:

@@ -132,7 +132,9 @@ def test_posterior_moments_and_diagnostics(ctx):
     X, y = make_data(n, d)
     s = sampler(ctx, C, X, y, seed=21)
     ch = s.chains
-    ch.set_param("eps", 0.02); ch.set_param("L", 10)
+    # int_time = 0.07 ~ a quarter period of the w directions (sd ~ n^-1/2): static HMC with int_time near a full
+    # period of any direction does not mix in it (the first version used 0.2 = the period of log sigma)
+    ch.set_param("eps", 0.007); ch.set_param("L", 10)
     A = np.c_[np.ones(n), X]
     ols = np.linalg.lstsq(A, y, rcond=None)[0]
     q0 = np.zeros((12, C)); q0[:11] = ols[:, None]

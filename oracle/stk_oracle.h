@@ -70,6 +70,19 @@ void orc_linreg_simulate(const double* X, int n, int d, uint64_t seed, uint64_t 
 long long orc_linreg_hmc_run(const double* X, const double* y, int n, int d, double* q, long long C, long long T,
                              double eps, int L, uint64_t seed, uint64_t chain0, uint64_t step0, int nthreads);
 
+// ---- C2 coal-mining RJ (app/rj/Main.hs:115-238; rj-coal.ipynb cell 8) ---------
+double orc_coal_logp(int n, const double* s, const double* g, const double* y, int ny, double t, int lam, double a, double b);
+void orc_coal_move_probs(int n, int lam, int nmax, double* pr4);
+int orc_coal_trans_ratio(int n, const double* s, const double* g, int n2, const double* s2, const double* g2,
+                         double t, int lam, int nmax, double* out3);
+int orc_coal_rj_step(int* n_io, double* s, double* g, const double* y, int ny, double t, int lam, int nmax,
+                     double a, double b, uint64_t seed, uint64_t chain, uint64_t step, double* info8);
+void orc_coal_simulate(uint64_t seed, uint64_t chain, double t, int lam, int nmax, double a, double b,
+                       int* n_out, double* s, double* g);
+long long orc_coal_rj_run(int* n, double* s, double* g, long long C, long long T, const double* y, int ny,
+                          double t, int lam, int nmax, double a, double b, uint64_t seed, uint64_t chain0,
+                          uint64_t step0, int nthreads);
+
 #ifdef __cplusplus
 }
 #endif

@@ -51,6 +51,65 @@ class Oracle:
             f.restype = D
             f.argtypes = args
 
+        I = C.c_int; U = C.c_uint64
+        l.orc_coal_logp.restype = D
+        l.orc_coal_logp.argtypes = [I, P, P, P, I, D, I, D, D]
+        l.orc_coal_move_probs.restype = None
+        l.orc_coal_move_probs.argtypes = [I, I, I, P]
+        l.orc_coal_trans_ratio.restype = I
+        l.orc_coal_trans_ratio.argtypes = [I, P, P, I, P, P, D, I, I, P]
+        l.orc_coal_rj_step.restype = I
+        l.orc_coal_rj_step.argtypes = [P, P, P, P, I, D, I, I, D, D, U, U, U, P]
+        l.orc_coal_simulate.restype = None
+        l.orc_coal_simulate.argtypes = [U, U, D, I, I, D, D, P, P, P]
+        l.orc_coal_rj_run.restype = C.c_longlong
+        l.orc_coal_rj_run.argtypes = [P, P, P, C.c_longlong, C.c_longlong, P, I, D, I, I, D, D, U, U, U, I]
+
+    # -- coal RJ (defaults = app/rj/Main.hs:117,198-199,228) -----------------------
+    COAL = dict(t=40907.0, lam=3, nmax=30, a=1.0, b=200.0)
+
+    def coal_logp(self, n, s, g, y, **kw):
+        k = dict(self.COAL, **kw)
+        s = np.ascontiguousarray(s, dtype=np.float64); g = np.ascontiguousarray(g, dtype=np.float64)
+        y = np.ascontiguousarray(y, dtype=np.float64)
+        return self.l.orc_coal_logp(int(n), _p(s), _p(g), _p(y), len(y), k["t"], k["lam"], k["a"], k["b"])
+
+    def coal_move_probs(self, n, lam=3, nmax=30):
+        pr = np.empty(4)
+        self.l.orc_coal_move_probs(int(n), lam, nmax, _p(pr))
+        return pr
+
+    def coal_trans_ratio(self, n, s, g, n2, s2, g2, **kw):
+        k = dict(self.COAL, **kw)
+        a = [np.ascontiguousarray(v, dtype=np.float64) for v in (s, g, s2, g2)]
+        out = np.empty(3)
+        kind = self.l.orc_coal_trans_ratio(int(n), _p(a[0]), _p(a[1]), int(n2), _p(a[2]), _p(a[3]), k["t"], k["lam"], k["nmax"], _p(out))
+        return kind, out
+
+    def coal_rj_step(self, n, s, g, y, seed, chain, step, **kw):
+        """s[nmax], g[nmax+1] float64 buffers updated in place; returns (n_new, info[8])"""
+        k = dict(self.COAL, **kw)
+        y = np.ascontiguousarray(y, dtype=np.float64)
+        nn = C.c_int(int(n)); info = np.empty(8)
+        self.l.orc_coal_rj_step(C.byref(nn), _p(s), _p(g), _p(y), len(y), k["t"], k["lam"], k["nmax"], k["a"], k["b"],
+                                seed, chain, step, _p(info))
+        return nn.value, info
+
+    def coal_simulate(self, seed, chain, **kw):
+        k = dict(self.COAL, **kw)
+        s = np.zeros(k["nmax"]); g = np.zeros(k["nmax"] + 1); nn = C.c_int()
+        self.l.orc_coal_simulate(seed, chain, k["t"], k["lam"], k["nmax"], k["a"], k["b"], C.byref(nn), _p(s), _p(g))
+        return nn.value, s, g
+
+    def coal_rj_run(self, n, s, g, y, T, seed, chain0=0, step0=0, nthreads=1, **kw):
+        """n int32[C], s [nmax][C], g [nmax+1][C] updated in place; returns #accepted"""
+        k = dict(self.COAL, **kw)
+        y = np.ascontiguousarray(y, dtype=np.float64)
+        assert n.dtype == np.int32 and s.flags.c_contiguous and g.flags.c_contiguous
+        assert s.shape == (k["nmax"], len(n)) and g.shape == (k["nmax"] + 1, len(n))
+        return self.l.orc_coal_rj_run(_p(n), _p(s), _p(g), len(n), T, _p(y), len(y), k["t"], k["lam"], k["nmax"],
+                                      k["a"], k["b"], seed, chain0, step0, nthreads)
+
     # -- linreg ---------------------------------------------------------------
     def linreg_logp(self, X, y, q, grad=True):
         X = np.ascontiguousarray(X, dtype=np.float64); y = np.ascontiguousarray(y, dtype=np.float64)

@@ -117,8 +117,59 @@ class LinregHMC:
         return orc.linreg_hmc_run(self.X, self.y, state["q"], T, self.eps, self.L, seed, chain0, step0, nthreads)
 
 
-WORKLOADS = {"linreg_hmc": LinregHMC}
-DEFAULT_WORKLOAD = "linreg_hmc"
+class CoalRJ:
+    """C2: coal-mining reversible-jump change-point sampler, 4096 chains (BASELINE.json configs[1]);
+    coal t `rjmc` coalMove' t of app/rj/Main.hs:115-238 on the 191 disaster dates."""
+    name = "coal_rj"
+    module = "builtin:coal"
+    kernel = "rj"
+    symbol = "coal_rj"
+    dtype = "f64"
+    transitions_per_step = 2000
+    burnin = 4000
+    diag_warmup = 0
+    diag_thin = 50
+    state_fields = ("n", "s", "g")
+    # SURVEY 8d: state read+write 2*492 B + one pass over y (191*8 B) per transition
+    bytes_per_transition = 2 * 492 + 1528
+    roofline_note = ("latency/issue-bound kernel: chain state and y live in shared memory for the whole launch, "
+                     "so the algorithmic bytes (2,512 B/transition, SURVEY 8d) are not DRAM traffic")
+
+    def __init__(self):
+        from stochaskell_b200.fixtures import COAL_T, coal_days
+        self.y = coal_days()
+        self.t = COAL_T
+        self.describe = ("C2 coal-mining RJMCMC (rj-coal): 191 events, t=40907, nMax=30, moves rate/position/birth/death "
+                         "(configs[1], 4096 chains/GPU)")
+
+    def data(self):
+        return dict(y=self.y)
+
+    def params(self):
+        return {}
+
+    def init_state(self, C, chain0):
+        """draws from coalPrior (numpy; the same host arrays feed the CUDA arm and the CPU arm)"""
+        rng = np.random.default_rng(4321 + chain0)
+        n = np.zeros(C, dtype=np.int32)
+        while True:
+            bad = (n < 1) | (n > 30)
+            if not bad.any():
+                break
+            n[bad] = rng.poisson(3.0, size=int(bad.sum()))
+        s = np.zeros((30, C)); g = np.zeros((31, C))
+        for c in range(C):
+            u = np.sort(rng.uniform(0, self.t, 2 * n[c] + 1))
+            s[:n[c], c] = u[1::2]
+            g[:n[c] + 1, c] = rng.gamma(1.0, 1 / 200.0, n[c] + 1)
+        return dict(n=n.reshape(1, C), s=s, g=g)
+
+    def cpu_run(self, orc, state, T, seed, chain0, step0, nthreads):
+        return orc.coal_rj_run(state["n"].reshape(-1), state["s"], state["g"], self.y, T, seed, chain0, step0, nthreads)
+
+
+WORKLOADS = {"linreg_hmc": LinregHMC, "coal_rj": CoalRJ}
+DEFAULT_WORKLOAD = "coal_rj"
 
 
 def cpu_arm(wl, orc, C, T, steps, warmup, nthreads):
@@ -174,42 +225,13 @@ def wl_kind(wl):
     return getattr(wl, "cpu_kind", "port")
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
-    ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="native", choices=["native", "reference"])
-    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
-    ap.add_argument("--chains", type=int, default=4096, help="chains per GPU")
-    ap.add_argument("--transitions", type=int, default=0, help="fused transitions per step (0 = workload default)")
-    ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-e2e", action="store_true")
-    args = ap.parse_args()
-    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    wl = WORKLOADS[args.workload]()
-    if args.transitions <= 0:
-        args.transitions = getattr(wl, "transitions_per_step", 100)
-    args.warmup = max(args.warmup, 3) if args.impl == "native" else args.warmup
-
-    if args.impl == "reference":
-        if rank == 0:
-            reference_arm(args, wl)
-        return 0
-
-    import torch
-    import torch.distributed as dist
-    from stochaskell_b200 import Sampler, lib
-    if not torch.cuda.is_available():
-        print(json.dumps(dict(error="no CUDA device; libstk_cuda has no CPU fallback")), flush=True)
-        return 2
-    torch.cuda.set_device(local)
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+def run_native(args, wl, rank, world, local, torch, dist):
+    """One workload on this rank's GPU; returns the result dict on rank 0 (None elsewhere)."""
+    from stochaskell_b200 import Sampler, diag_finish, lib
     dev = torch.device("cuda", local)
-    C, T, K, W = args.chains, args.transitions, args.steps, args.warmup
+    C, K, W = args.chains, args.steps, args.warmup
+    T = args.transitions if args.transitions > 0 else getattr(wl, "transitions_per_step", 100)
+    kernel = args.kernel or wl.kernel
     chain0 = rank * C
     s = Sampler(wl.module, C, wl.data(), seed=20261104, device=local, first_global_chain=chain0)
     ch = s.chains
@@ -228,8 +250,10 @@ def main():
         torch.cuda.synchronize(dev)
 
     with torch.cuda.stream(stream):
+        if getattr(wl, "burnin", 0):
+            ch.step(kernel, wl.burnin)          # reach the stationary mix of dimensions before timing
         for _ in range(W):
-            flush.zero_(); ch.step(wl.kernel, T)
+            flush.zero_(); ch.step(kernel, T)
         barrier()
         clocks = ClockSampler(local) if rank == 0 else None
         if clocks:
@@ -241,7 +265,7 @@ def main():
         for k in range(K):
             flush.zero_()
             ev[k][0].record(stream)
-            ch.step(wl.kernel, T)
+            ch.step(kernel, T)
             ev[k][1].record(stream)
         barrier()
         t_wall = time.perf_counter() - t_wall
@@ -258,7 +282,8 @@ def main():
     e2e = None
     if not args.no_e2e:
         fields = [f for f, d in s.module.fields.items() if d["state"] and not str(d["len"]).startswith("@")]
-        host_in = {k: torch.from_numpy(v.copy()).pin_memory().numpy() for k, v in st0.items()}
+        cur = {k: ch.get_state(k) for k in st0}   # continue from the (burnt-in) device state
+        host_in = {k: torch.from_numpy(np.ascontiguousarray(v)).pin_memory().numpy() for k, v in cur.items()}
         host_out = {}
         for f in fields:
             _, nb = ch.device_ptr(f)
@@ -269,7 +294,7 @@ def main():
         def e2e_step():
             for k, v in host_in.items():
                 ch.set_state(k, v)
-            ch.step(wl.kernel, T)
+            ch.step(kernel, T)
             for f in fields:
                 ch.get_state(f, out=host_out[f])
             for k in host_in:  # next step starts from the downloaded state, like a runCC loop
@@ -289,32 +314,37 @@ def main():
     # ---- cross-chain diagnostics: the ONE collective of the path (R-hat/ESS moments) --
     diag = None
     try:
-        ch.step(wl.kernel, getattr(wl, "diag_warmup", 300))  # move off the synthetic init before judging mixing
-        ch.record(32, getattr(wl, "diag_thin", 4))
-        ch.step(wl.kernel, 32 * getattr(wl, "diag_thin", 4))
+        thin = getattr(wl, "diag_thin", 4)
+        ch.step(kernel, getattr(wl, "diag_warmup", 300))  # move off the synthetic init before judging mixing
+        ch.record(32, thin)
+        t0 = time.perf_counter()
+        ch.step(kernel, 32 * thin)
+        ch.sync()
+        dt_draws = time.perf_counter() - t0
         max_lag = 31
         buf = torch.from_numpy(ch.diag_partial(max_lag)).to(dev)
         if world > 1:
             dist.all_reduce(buf, op=dist.ReduceOp.SUM)  # NCCL over NVLink
-        from stochaskell_b200 import diag_finish
         P = lib().stk_num_recorded_values(ch._h)
         r = diag_finish(buf.cpu().numpy(), P, 32, max_lag)
-        diag = dict(rhat_max=float(np.nanmax(r["rhat"])), ess_min=float(np.nanmin(r["ess"])), draws=32,
-                    chains=world * C, collective="nccl all_reduce(sum) of [P*(4+max_lag+1)] f64" if world > 1 else "none (1 GPU)")
+        ok = np.isfinite(r["rhat"]) & np.isfinite(r["ess"])
+        diag = dict(rhat_max=float(np.max(r["rhat"][ok])) if ok.any() else None,
+                    ess_min=float(np.min(r["ess"][ok])) if ok.any() else None,
+                    ess_per_sec_min=float(np.min(r["ess"][ok]) / dt_draws) if ok.any() else None,
+                    params_finite=int(ok.sum()), params=int(P), draws=32, thin=thin, chains=world * C,
+                    collective="nccl all_reduce(sum) of [P*(4+max_lag+1)] f64" if world > 1 else "none (1 GPU)")
     except Exception as e:  # diagnostics are not part of the timed path
         diag = dict(error=str(e)[:200])
 
     if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return 0
-
+        return None
     peaks = measured_peaks()
     ms_per_launch = dev_ms / K
     alg_bytes = C * T * wl.bytes_per_transition
     achieved = alg_bytes / (ms_per_launch * 1e-3) / 1e9
     roofline = dict(bound="hbm", achieved=achieved, peak=peaks["hbm_gbs"], unit="GB/s", frac=achieved / peaks["hbm_gbs"],
-                    traffic=getattr(wl, "ncu_traffic_bytes", None), kernel=wl.symbol, peak_source=peaks["source"],
+                    traffic=getattr(wl, "ncu_traffic_bytes", None), kernel=wl.symbol if not args.kernel else f"{wl.module[8:]}_{kernel}",
+                    peak_source=peaks["source"],
                     algorithmic_bytes_per_transition=wl.bytes_per_transition,
                     note=getattr(wl, "roofline_note", "observed data is shared by all chains and staged in shared "
                                  "memory once per launch, so algorithmic bytes exceed physical DRAM traffic"))
@@ -326,17 +356,69 @@ def main():
         Cs = 2 * nt
         stc = wl.init_state(Cs, 0)
         t0 = time.perf_counter(); wl.cpu_run(orc, stc, 4, 1, 0, 0, nt); per_tr = (time.perf_counter() - t0) / 4
-        Ts = int(max(1, min(100000, 12.0 / max(per_tr, 1e-9))))
+        Ts = int(max(1, min(1000000, 12.0 / max(per_tr, 1e-9))))
         v, dt = cpu_arm(wl, orc, Cs, Ts, 1, 0, nt)
         cpu = dict(value=v, unit=UNIT, cores=nt, kind=wl_kind(wl),
                    sample=f"{Cs} chains x {Ts} transitions of the same workload on {nt} host threads ({dt:.1f} s)")
-    out = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=K, warmup=W, ms_per_step=ms_per_launch,
-               higher_is_better=True, scaling="weak", vs_baseline=None, dtype=wl.dtype, data="synthetic",
-               config=dict(workload=wl.describe, chains_per_gpu=C, transitions_per_step=T, parallelism=f"chains-sharded x{world}",
-                           l2="flushed (256 MiB memset) before every step, outside the per-step CUDA events",
-                           wall_ms_per_step_incl_flush=wall_ms / K),
-               roofline=roofline, cpu_baseline=cpu, e2e=e2e, gpu_launches=int(launches), clocks=clk, diagnostics=diag)
-    print(json.dumps(out), flush=True)
+    return dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=K, warmup=W, ms_per_step=ms_per_launch,
+                higher_is_better=True, scaling="weak", vs_baseline=None, dtype=wl.dtype, data="synthetic",
+                config=dict(workload=wl.describe, chains_per_gpu=C, transitions_per_step=T, parallelism=f"chains-sharded x{world}",
+                            l2="flushed (256 MiB memset) before every step, outside the per-step CUDA events",
+                            wall_ms_per_step_incl_flush=wall_ms / K),
+                roofline=roofline, cpu_baseline=cpu, e2e=e2e, gpu_launches=int(launches), clocks=clk, diagnostics=diag)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--also", default="auto", help="comma list of further workloads reported under 'also' "
+                    "(auto = the other north-star models when the headline workload runs; none = off)")
+    ap.add_argument("--kernel", default="", help="transition kernel variant of the module (e.g. rj16, rj8)")
+    ap.add_argument("--chains", type=int, default=4096, help="chains per GPU")
+    ap.add_argument("--transitions", type=int, default=0, help="fused transitions per step (0 = workload default)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    wl = WORKLOADS[args.workload]()
+    args.warmup = max(args.warmup, 3) if args.impl == "native" else args.warmup
+
+    if args.impl == "reference":
+        if rank == 0:
+            if args.transitions <= 0:
+                args.transitions = getattr(wl, "transitions_per_step", 100)
+            reference_arm(args, wl)
+        return 0
+
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        print(json.dumps(dict(error="no CUDA device; libstk_cuda has no CPU fallback")), flush=True)
+        return 2
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    out = run_native(args, wl, rank, world, local, torch, dist)
+    also = [w for w in WORKLOADS if w != args.workload] if (args.also == "auto" and args.workload == DEFAULT_WORKLOAD
+                                                          and not args.kernel and args.transitions <= 0) \
+        else [w for w in args.also.split(",") if w in WORKLOADS and w != args.workload]
+    extra = {}
+    for name in also:
+        r = run_native(args, WORKLOADS[name](), rank, world, local, torch, dist)
+        if r is not None:
+            extra[name] = {k: r[k] for k in ("value", "unit", "ms_per_step", "dtype", "config", "roofline", "cpu_baseline",
+                                             "e2e", "gpu_launches", "diagnostics")}
+    if rank == 0:
+        if extra:
+            out["gpu_launches"] += sum(v["gpu_launches"] for v in extra.values())
+            out["also"] = extra
+        print(json.dumps(out), flush=True)
     if world > 1:
         dist.destroy_process_group()
     return 0

@@ -12,7 +12,8 @@
  *   stk-module 1
  *   name   <model name>
  *   nparam <P>                       unconstrained parameter count (0 if n/a)
- *   field  <name> <state|data> <f64|i32> <len>     len 0 = sized by set_data
+ *   field  <name> <state|data> <f64|i32> <len> [sorted]   len 0 = sized by set_data; @f = as field f;
+ *                                    sorted = the runtime uploads an ascending copy of the data
  *   param  <name> <default>          scalar tunable -> StkArgs.par[i]
  *   record <field> ...               fields (as doubles) that make up a draw
  *   kernel <name> <symbol> <block> <chains_per_block> <smem_fixed> <smem_field|-> <smem_bytes_per_elem>

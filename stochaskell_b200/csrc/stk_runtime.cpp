@@ -21,6 +21,7 @@
 #include <sys/stat.h>
 #include <unistd.h>
 
+#include <algorithm>
 #include <atomic>
 #include <cmath>
 #include <cstdarg>
@@ -125,7 +126,7 @@ std::string lib_dir() {
   return ".";
 }
 
-struct FieldDesc { std::string name; bool is_state; bool is_i32; long long len; std::string len_ref; };
+struct FieldDesc { std::string name; bool is_state; bool is_i32; long long len; std::string len_ref; bool sorted = false; };
 struct KernelDesc {
   std::string name, symbol;
   int block = 0, cpb = 1; long long smem_fixed = 0; std::string smem_field; long long smem_per = 0;
@@ -196,6 +197,7 @@ int parse_desc(stk_module* m) {
       f.is_state = (kind == "state"); f.is_i32 = (ty == "i32");
       if (!len.empty() && len[0] == '@') { f.len = 0; f.len_ref = len.substr(1); }
       else f.len = atoll(len.c_str());
+      { std::string attr; while (ls >> attr) if (attr == "sorted") f.sorted = true; }
       if ((int)m->fields.size() >= STK_MAX_FIELDS) return fail(STK_ERR_ARG, "too many fields");
       m->fields.push_back(f);
     } else if (kw == "param") {
@@ -495,6 +497,14 @@ int stk_set_data(stk_chains* c, int field, const void* host, size_t bytes) {
   if (c->dptr[field] && c->flen[field] != len) { CU(cudaStreamSynchronize(m->ctx->stream)); CU(cudaFree(c->dptr[field])); c->dptr[field] = nullptr; }
   if (!c->dptr[field]) CU(cudaMalloc(&c->dptr[field], bytes ? bytes : 8));
   c->flen[field] = len;
+  // `sorted` data fields (kernels that binary-search them; a sum over the observations does not depend on
+  // their order): upload an ascending copy.
+  std::vector<double> tmp;
+  if (fd.sorted && !fd.is_i32 && !std::is_sorted((const double*)host, (const double*)host + len)) {
+    tmp.assign((const double*)host, (const double*)host + len);
+    std::sort(tmp.begin(), tmp.end());
+    host = tmp.data();
+  }
   CU(cudaMemcpyAsync(c->dptr[field], host, bytes, cudaMemcpyHostToDevice, m->ctx->stream));
   CU(cudaStreamSynchronize(m->ctx->stream));
   return STK_OK;

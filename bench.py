@@ -123,7 +123,7 @@ class CoalRJ:
     name = "coal_rj"
     module = "builtin:coal"
     kernel = "rj"
-    symbol = "coal_rj"
+    symbol = "coal_rj8"
     dtype = "f64"
     transitions_per_step = 2000
     burnin = 4000

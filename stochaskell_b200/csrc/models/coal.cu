@@ -301,9 +301,13 @@ __device__ __forceinline__ void rj_body(const StkArgs& a) {
 
 }  // namespace
 
-extern "C" __global__ void __launch_bounds__(BLOCK) coal_rj(const __grid_constant__ StkArgs a) { rj_body<32>(a); }
-extern "C" __global__ void __launch_bounds__(BLOCK) coal_rj16(const __grid_constant__ StkArgs a) { rj_body<16>(a); }
+// G = 8 lanes per chain is the default (`rj`): at 4096 chains per GPU it is the best trade between lanes that idle
+// when n+1 < G and warps per scheduler (B200: G=32 874 M, G=16 1168 M, G=8 1285 M, G=4 1000 M transitions/s;
+// profiles/r01_coal_rj.md).
 extern "C" __global__ void __launch_bounds__(BLOCK) coal_rj8(const __grid_constant__ StkArgs a) { rj_body<8>(a); }
+extern "C" __global__ void __launch_bounds__(BLOCK) coal_rj32(const __grid_constant__ StkArgs a) { rj_body<32>(a); }
+extern "C" __global__ void __launch_bounds__(BLOCK) coal_rj16(const __grid_constant__ StkArgs a) { rj_body<16>(a); }
+extern "C" __global__ void __launch_bounds__(BLOCK) coal_rj4(const __grid_constant__ StkArgs a) { rj_body<4>(a); }
 
 // joint log-density of every chain's current state (stk_logp; `lpdf`, Program.hs:787-812)
 extern "C" __global__ void __launch_bounds__(BLOCK) coal_logp(const __grid_constant__ StkArgs a) {
@@ -368,8 +372,9 @@ extern "C" __device__ const char stk_desc[] =
     "param a 1\n"
     "param b 200\n"
     "record n s g\n"
-    "kernel rj coal_rj 128 4 4640 y 8\n"
+    "kernel rj coal_rj8 128 16 10784 y 8\n"
+    "kernel rj32 coal_rj32 128 4 4640 y 8\n"
     "kernel rj16 coal_rj16 128 8 6688 y 8\n"
-    "kernel rj8 coal_rj8 128 16 10784 y 8\n"
+    "kernel rj4 coal_rj4 128 32 18976 y 8\n"
     "entry logp coal_logp 128 4 4640 y 8\n"
     "entry simulate coal_simulate 128 4 4640 y 8\n";

@@ -126,7 +126,9 @@ extern "C" double orc_uniform_lpdf(double x, double a, double b) {  // :161-162
   return std::log(1 / (b - a));
 }
 extern "C" double orc_uniform_cdf(double x, double a, double b) {  // :163-165
-  if (x < a) return 0; if (x > b) return 1; return (x - a) / (b - a);
+  if (x < a) return 0;
+  if (x > b) return 1;
+  return (x - a) / (b - a);
 }
 extern "C" double orc_discrete_uniform_lpdf(int x, int a, int b) {  // :166-167
   if (x < a || b < x) return -std::numeric_limits<double>::infinity();

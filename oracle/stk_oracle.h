@@ -83,6 +83,11 @@ long long orc_coal_rj_run(int* n, double* s, double* g, long long C, long long T
                           double t, int lam, int nmax, double a, double b, uint64_t seed, uint64_t chain0,
                           uint64_t step0, int nthreads);
 
+// ---- soccer RJ (rj.ipynb; pinned against the reference's generated C++ in oracle/_ref) -----
+double orc_soccer_accept_prob(int tag, double lam, double kappa, const int* y, int ny, double x, double* kappa_prop);
+int orc_soccer_rj_step(int tag, double lam, double* kappa, const int* y, int ny,
+                       uint64_t seed, uint64_t chain, uint64_t step, double* p_out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -65,6 +65,25 @@ class Oracle:
         l.orc_coal_rj_run.restype = C.c_longlong
         l.orc_coal_rj_run.argtypes = [P, P, P, C.c_longlong, C.c_longlong, P, I, D, I, I, D, D, U, U, U, I]
 
+        l.orc_soccer_accept_prob.restype = D
+        l.orc_soccer_accept_prob.argtypes = [I, D, D, P, I, D, P]
+        l.orc_soccer_rj_step.restype = I
+        l.orc_soccer_rj_step.argtypes = [I, D, P, P, I, U, U, U, P]
+
+    # -- soccer RJ (rj.ipynb) ---------------------------------------------------------
+    def soccer_accept_prob(self, tag, lam, kappa, y, x):
+        y = np.ascontiguousarray(y, dtype=np.int32)
+        kp = D()
+        p = self.l.orc_soccer_accept_prob(int(tag), lam, kappa, _p(y), len(y), x, C.byref(kp))
+        return p, kp.value
+
+    def soccer_rj_step(self, tag, lam, kappa, y, seed, chain, step):
+        """returns (new tag, kappa, acceptance probability)"""
+        y = np.ascontiguousarray(y, dtype=np.int32)
+        k = D(kappa); p = D()
+        t = self.l.orc_soccer_rj_step(int(tag), lam, C.byref(k), _p(y), len(y), seed, chain, step, C.byref(p))
+        return t, k.value, p.value
+
     # -- coal RJ (defaults = app/rj/Main.hs:117,198-199,228) -----------------------
     COAL = dict(t=40907.0, lam=3, nmax=30, a=1.0, b=200.0)
 

@@ -76,6 +76,19 @@ int stk_ctx_stream(stk_ctx* ctx, stk_stream* out);
 int stk_compile(const char* cuda_src, const char* cache_dir,
                 const char* include_dir, char* path_out, size_t path_cap);
 
+/* The Language.CUDA lowering (stkc): Stochaskell IR text -> CUDA source of a module.
+ * Replaces ccProgram / ccDAG / ccNode / ccPNode (CC.hs:123-432).  `ir_text` is what
+ * `showPBlock` prints (Program.hs:181-187) — the text Language.CC embeds at the top of
+ * every generated file (CC.hs:400-402) and runStep traces (Program.hs:1351).
+ * `input_types` lists the kernel inputs' types in showType syntax (Expression.hs:437-453),
+ * separated by `;` (empty = a model to forward-simulate: entry `simulate`, outputs out<k>);
+ * a transition kernel  t -> P t  becomes kernel `step` over state fields in<k>...
+ * (layout in csrc/stkc.cpp).  `options`: blank-separated key=value (name, veccap, block,
+ * level).  Writes a NUL-terminated string; *needed (may be NULL) receives its size.
+ * Unsupported IR constructs fail with STK_ERR_UNSUPPORTED naming the construct.  No GPU needed. */
+int stk_ir_to_cuda(const char* ir_text, const char* input_types, const char* options,
+                   char* out, size_t cap, size_t* needed);
+
 /* Load a module on ctx's device.  `spec` is one of
  *   "builtin:<name>"   a hand-tuned model shipped with the library
  *   "<path>.cubin"     a cubin produced by stk_compile / nvcc

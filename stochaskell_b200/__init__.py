@@ -6,4 +6,4 @@ the IR -> CUDA code generator in stkc.py, and the diagnostics plumbing.
 """
 from ._lib import LIB_PATH, StkError, lib  # noqa: F401
 from .api import (Chains, Context, CudaMethod, Module, Sampler, compile_source,  # noqa: F401
-                  compileCUDA, diag_finish, hmcCUDA, runCUDA)
+                  compileCUDA, diag_finish, hmcCUDA, ir_to_cuda, runCUDA)

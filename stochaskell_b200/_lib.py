@@ -32,6 +32,7 @@ SIGNATURES = {
     "stk_ctx_destroy": (C.c_int, [C.c_void_p]),
     "stk_ctx_stream": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
     "stk_compile": (C.c_int, [C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_size_t]),
+    "stk_ir_to_cuda": (C.c_int, [C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t)]),
     "stk_module_load": (C.c_int, [C.c_void_p, C.c_char_p, C.c_char_p, C.POINTER(C.c_void_p)]),
     "stk_module_destroy": (C.c_int, [C.c_void_p]),
     "stk_module_describe": (C.c_int, [C.c_void_p, C.c_char_p, C.c_size_t]),

@@ -64,6 +64,17 @@ def compile_source(cuda_src: str, cache_dir: Optional[str] = None, include_dir: 
     return buf.value.decode()
 
 
+def ir_to_cuda(ir_text: str, input_types: Sequence[str] = (), **options) -> str:
+    """The Language.CUDA lowering (stkc, csrc/stkc.cpp): IR text as printed by showPBlock -> CUDA module source."""
+    need = C.c_size_t()
+    opts = " ".join(f"{k}={v}" for k, v in options.items()).encode()
+    types = ";".join(input_types).encode()
+    check(lib().stk_ir_to_cuda(ir_text.encode(), types, opts, None, 0, C.byref(need)))
+    buf = C.create_string_buffer(need.value)
+    check(lib().stk_ir_to_cuda(ir_text.encode(), types, opts, buf, len(buf), None))
+    return buf.value.decode()
+
+
 class Module:
     """A compiled model (stk_module): 'builtin:<name>', a .cubin path, or CUDA source text."""
 

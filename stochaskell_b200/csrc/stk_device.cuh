@@ -221,6 +221,37 @@ STK_DEV int find_sorted_insert_index(double e, const double* v, int n) {
   return j;
 }
 
+// ---- vectors of the generated (stkc) kernels ---------------------------------
+// A view: 1-based `at`, element stride in elements (n_chains for a state field stored [len][chain], 1 for
+// a per-thread buffer).  Matrix<.., Dynamic, 1> of the C++ backend (CC.hs:77), without ownership.
+template <class T>
+struct Vec {
+  T* p; long long stride; int len;
+  STK_DEV Vec() : p(nullptr), stride(1), len(0) {}
+  STK_DEV Vec(T* p_, long long s_, int n_) : p(p_), stride(s_), len(n_) {}
+  STK_DEV T at(int i) const { return p[(long long)(i - 1) * stride]; }
+};
+typedef Vec<double> VecD;
+typedef Vec<int> VecI;
+// next-transition feed: make the state vector `dst` hold `src` (no copy when it already does)
+template <class T>
+STK_DEV void assign_vec(Vec<T>& dst, const Vec<T>& src, int cap) {
+  const int n = src.len < cap ? src.len : cap;
+  if (src.p != dst.p) for (int i = 0; i < n; ++i) dst.p[(long long)i * dst.stride] = src.p[(long long)i * src.stride];
+  dst.len = n;
+}
+template <class T>
+STK_DEV void store_vec(const Vec<T>& v, T* dst, long long stride, int cap, int* len_out) {
+  const int n = v.len < cap ? v.len : cap;
+  if (v.p != dst) for (int i = 0; i < n; ++i) dst[(long long)i * stride] = v.p[(long long)i * v.stride];
+  *len_out = n;
+}
+STK_DEV int find_sorted_insert_index_v(double e, const VecD& v) {     // CC.hs:192-197
+  int j = v.len + 1;
+  for (int i = 1; i <= v.len; ++i) if (e < v.at(i)) { j = i; break; }
+  return j;
+}
+
 // ---- sub-warp reductions ---------------------------------------------------
 // sum over the G consecutive lanes of a chain's lane group (G = 1,2,4,...,32).
 template <int G>

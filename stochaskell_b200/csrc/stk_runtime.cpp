@@ -288,6 +288,7 @@ int need_device(stk_ctx* ctx) {
 extern "C" {
 
 const char* stk_last_error(void) { return g_err.c_str(); }
+int stk_set_error_(int code, const char* msg) { return fail(code, "%s", msg ? msg : ""); }  // for stkc.cpp
 int stk_abi_version(void) { return STK_ABI_VERSION; }
 int64_t stk_launch_count(void) { return g_launches.load(); }
 
@@ -518,9 +519,16 @@ int stk_set_state(stk_chains* c, int field, const void* host, size_t bytes, int 
   if (rc) return rc;
   if ((rc = ensure_fields(c))) return rc;
   const FieldDesc& fd = m->fields[field];
+  size_t es = elem_size(fd);
+  if (c->flen[field] <= 0 && fd.len == 0 && fd.len_ref.empty()) {
+    // a state field declared with length 0 (vectors of stkc-generated modules) takes its capacity from the first upload
+    size_t per = broadcast ? es : es * (size_t)c->n;
+    if (bytes == 0 || bytes % per) return fail(STK_ERR_ARG, "state field %s: %zu bytes is not a whole number of %s", fd.name.c_str(), bytes, broadcast ? "elements" : "[.][n_chains] rows");
+    c->flen[field] = (long long)(bytes / per);
+    if ((rc = ensure_fields(c))) return rc;
+  }
   long long L = c->flen[field];
   if (L <= 0 || !c->dptr[field]) return fail(STK_ERR_ARG, "state field %s has no size yet", fd.name.c_str());
-  size_t es = elem_size(fd);
   if (broadcast) {
     if (bytes != (size_t)L * es) return fail(STK_ERR_ARG, "state field %s (broadcast) expects %zu bytes, got %zu", fd.name.c_str(), (size_t)L * es, bytes);
     std::vector<char> tmp((size_t)L * (size_t)c->n * es);

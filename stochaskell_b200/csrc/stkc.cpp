@@ -1,0 +1,1050 @@
+// stkc.cpp — the `Language.CUDA` lowering: Stochaskell IR (a probabilistic program printed by
+// `showPBlock`, Data/Program.hs:181-187) -> CUDA source text of a module for libstk_cuda
+// (descriptor + kernels over stk_device.cuh), compiled by stk_compile (NVRTC, sm_100a).
+//
+// This is the counterpart of Language.CC's code generator, construct by construct:
+//   ccProgram  CC.hs:398-432   -> emit_module   (prelude, state load, transition loop, state store)
+//   ccDAG      CC.hs:327-346   -> Gen::body     (one statement per node, dependency order)
+//   ccNode     CC.hs:123-274   -> Gen::def      (Apply / Array / FoldScan / Case templates)
+//   ccPNode'   CC.hs:276-321   -> Gen::pnode    (draws, SubrangeT rejection loop, Switch over a union)
+//   ccRead/ccPrint :353-396    -> the SoA state fields of the descriptor (no text round trip)
+// The input is the text the reference itself embeds at the top of every generated C++ file
+// (CC.hs:400-402) and prints from `runStep` (Program.hs:1351): grammar in SURVEY.md Appendix A
+// (showLet' Expression.hs:207-213, showNode :221-258, showNodeRef :141-161, showType :437-453,
+// Show PNode Program.hs:133-161).  Kernel inputs are the Dummy ids `i_<L>_<k>` (L = 0 for
+// compileCC, 9 for runStep); their types are not part of the printed IR and are passed beside it.
+//
+// Execution shape of the generated module: ONE THREAD PER CHAIN, the whole transition loop inside
+// the kernel, state in registers/local memory between transitions, Philox counter =
+// (global chain, transition, slot) with slot = 256*level + 16*pointer of the drawing PNode — a draw
+// is a pure function of (seed, chain, transition, PNode), whatever the sharding.
+// Hand-tuned builtins (models/*.cu) exist for the benchmark configs; this is the generic path.
+#include "../../include/stk_cuda.h"
+
+#include <cctype>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <memory>
+#include <set>
+#include <sstream>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+namespace stkc {
+
+struct Error : std::runtime_error { using std::runtime_error::runtime_error; };
+[[noreturn]] static void die(const std::string& m) { throw Error(m); }
+
+// ---------------------------------------------------------------------------------------------
+// types (showType, Expression.hs:437-453)
+// ---------------------------------------------------------------------------------------------
+struct Type {
+  enum K { Z, R, B, Vec, Mat, Tuple, Union, Unknown } k = Unknown;
+  std::vector<Type> sub;  // Vec/Mat: element; Tuple: members; Union: one Tuple per constructor
+  bool scalar() const { return k == Z || k == R || k == B; }
+  bool integral() const { return k == Z || k == B; }
+  std::string str() const {
+    switch (k) {
+      case Z: return "Z"; case R: return "R"; case B: return "B";
+      case Vec: return sub[0].str() + "Vec"; case Mat: return sub[0].str() + "Mat";
+      case Tuple: { std::string s = "("; for (size_t i = 0; i < sub.size(); ++i) s += (i ? ", " : "") + sub[i].str(); return s + ")"; }
+      case Union: { std::string s = "Union["; for (size_t i = 0; i < sub.size(); ++i) s += (i ? ", " : "") + sub[i].str(); return s + "]"; }
+      default: return "???";
+    }
+  }
+  bool operator==(const Type& o) const { return str() == o.str(); }
+};
+static Type scalarT(Type::K k) { Type t; t.k = k; return t; }
+static Type vecT(Type e) { Type t; t.k = Type::Vec; t.sub.push_back(e); return t; }
+
+// ---------------------------------------------------------------------------------------------
+// tokens
+// ---------------------------------------------------------------------------------------------
+struct Tok { std::string s; int line, col; bool first; enum K { Id, Num, Sym, End } k; };
+
+static std::vector<Tok> lex(const std::string& src) {
+  std::vector<Tok> out;
+  int line = 1, col = 0; bool first = true;
+  size_t i = 0, n = src.size();
+  auto push = [&](const std::string& s, Tok::K k, int c) { out.push_back({s, line, c, first, k}); first = false; };
+  while (i < n) {
+    char ch = src[i];
+    if (ch == '\n') { ++line; col = 0; first = true; ++i; continue; }
+    if (ch == ' ' || ch == '\t' || ch == '\r') { ++col; ++i; continue; }
+    if (ch == '/' && i + 1 < n && src[i + 1] == '*' && first) { i += 2; col += 2; continue; }   // the CC comment frame
+    if (ch == '*' && i + 1 < n && src[i + 1] == '/' && first) break;
+    int c0 = col;
+    auto adv = [&](size_t k) { i += k; col += (int)k; };
+    bool prev_space = i == 0 || strchr(" \t\n[,(", src[i - 1]) != nullptr;
+    if (isdigit((unsigned char)ch) || (ch == '-' && prev_space && i + 1 < n && isdigit((unsigned char)src[i + 1]))) {
+      size_t j = i + 1;
+      while (j < n && isdigit((unsigned char)src[j])) ++j;
+      // a fraction, but not the `...` of a range and not the `.T_F` of an Extract
+      if (j + 1 < n && src[j] == '.' && isdigit((unsigned char)src[j + 1])) {
+        size_t k = j + 1; while (k < n && isdigit((unsigned char)src[k])) ++k;
+        if (!(k < n && src[k] == '_')) j = k;
+      }
+      if (j < n && (src[j] == 'e' || src[j] == 'E')) {
+        size_t k = j + 1; if (k < n && (src[k] == '-' || src[k] == '+')) ++k;
+        if (k < n && isdigit((unsigned char)src[k])) { while (k < n && isdigit((unsigned char)src[k])) ++k; j = k; }
+      }
+      std::string s = src.substr(i, j - i); adv(j - i); push(s, Tok::Num, c0); continue;
+    }
+    if (isalpha((unsigned char)ch) || ch == '_') {
+      size_t j = i + 1;
+      while (j < n && (isalnum((unsigned char)src[j]) || src[j] == '_' || src[j] == '\'')) ++j;
+      std::string s = src.substr(i, j - i); adv(j - i);
+      if (ch == '-' ) {}
+      push(s, Tok::Id, c0); continue;
+    }
+    if (ch == '-' && prev_space && src.compare(i, 9, "-Infinity") == 0) { adv(9); push("-Infinity", Tok::Num, c0); continue; }
+    // punctuation and operators
+    static const char* multi[] = {"...", "::", "<-", "->", "=>", "==", "/=", "<=", ">=", "&&s", "&&", "||", "**", "<>", "#>", "<.>", "<\\>", "+s", "*s", ".?", nullptr};
+    bool done = false;
+    for (int m = 0; multi[m]; ++m) {
+      size_t L = strlen(multi[m]);
+      if (src.compare(i, L, multi[m]) == 0) {
+        // "+s" / "*s" only when a blank follows (otherwise `+` then an identifier starting with s)
+        if ((!strcmp(multi[m], "+s") || !strcmp(multi[m], "*s") || !strcmp(multi[m], "&&s")) && !(i + L < n && (src[i + L] == ' ' || src[i + L] == '\n'))) continue;
+        adv(L); push(multi[m], Tok::Sym, c0); done = true; break;
+      }
+    }
+    if (done) continue;
+    adv(1); push(std::string(1, ch), Tok::Sym, c0);
+  }
+  out.push_back({"", line + 1, 0, true, Tok::End});
+  return out;
+}
+
+// ---------------------------------------------------------------------------------------------
+// IR (NodeRef Expression.hs:67-78, Node :175-205, PNode Program.hs:44-86)
+// ---------------------------------------------------------------------------------------------
+struct Ref;
+using RefP = std::shared_ptr<Ref>;
+struct Ref {
+  enum K { Var, Num, Index, Extract, TagOf, Data, List } k = Var;
+  std::string name;          // Var: id; Num: literal text
+  RefP base;                 // Index / Extract / TagOf
+  std::vector<RefP> args;    // Index: subscripts (outermost first); Data: fields; List: elements
+  int tag = 0, field = 0;    // Extract (.tag_field), Data (C<tag>)
+  Type type;                 // Data: the annotated union type
+};
+struct Def;
+struct PNode;
+struct Body {                // `let defs in (do pnodes return rets | rets)`
+  std::vector<Def> defs;
+  std::vector<PNode> pnodes;
+  std::vector<RefP> rets;
+};
+struct Alt { std::vector<std::string> inputs; Body body; };
+struct Node {
+  enum K { Apply, Array, Fold, Case } k = Apply;
+  std::string f;                                  // Apply name; Fold: foldl/foldr/scanl/scanr
+  std::vector<RefP> args;                         // Apply args; Fold: seed, list; Case: head
+  std::vector<std::string> params;                // Array: index ids; Fold: acc, elem
+  std::vector<std::pair<RefP, RefP>> shape;       // Array bounds
+  std::shared_ptr<Body> lam;                      // Array / Fold body
+  std::vector<Alt> alts;                          // Case
+  Type type;
+};
+struct Def { std::string id; Node node; };
+struct PNode {
+  enum K { Dist, Switch, Loop } k = Dist;
+  std::string id, dist;
+  std::vector<RefP> args;     // Dist args; Switch: head
+  std::vector<Alt> alts;      // Switch
+  std::vector<std::string> params; std::vector<std::pair<RefP, RefP>> shape; std::shared_ptr<PNode> inner; std::shared_ptr<Body> lam;  // Loop
+  Type type;
+};
+
+// ---------------------------------------------------------------------------------------------
+// parser
+// ---------------------------------------------------------------------------------------------
+struct Parser {
+  std::vector<Tok> t; size_t p = 0;
+  explicit Parser(const std::string& src) : t(lex(src)) {}
+  const Tok& peek(size_t k = 0) const { return t[std::min(p + k, t.size() - 1)]; }
+  bool is(const char* s, size_t k = 0) const { return peek(k).k != Tok::End && peek(k).s == s; }
+  [[noreturn]] void fail(const std::string& m) const {
+    die("IR parse error at line " + std::to_string(peek().line) + " col " + std::to_string(peek().col + 1) + " near `" + peek().s + "`: " + m);
+  }
+  Tok next() { Tok x = peek(); if (x.k == Tok::End) fail("unexpected end of input"); ++p; return x; }
+  void expect(const char* s) { if (!is(s)) fail(std::string("expected `") + s + "`"); ++p; }
+  bool accept(const char* s) { if (is(s)) { ++p; return true; } return false; }
+
+  static bool ctor_name(const std::string& s, int* tag) {
+    if (s.size() < 2 || s[0] != 'C') return false;
+    for (size_t i = 1; i < s.size(); ++i) if (!isdigit((unsigned char)s[i])) return false;
+    if (tag) *tag = atoi(s.c_str() + 1);
+    return true;
+  }
+
+  Type type() {
+    if (accept("(")) {
+      Type tu; tu.k = Type::Tuple;
+      if (!accept(")")) { do tu.sub.push_back(type()); while (accept(",")); expect(")"); }
+      if (tu.sub.size() == 1) return tu.sub[0];
+      return tu;
+    }
+    Tok x = next();
+    if (x.s == "Z") return scalarT(Type::Z);
+    if (x.s == "R") return scalarT(Type::R);
+    if (x.s == "B") return scalarT(Type::B);
+    if (x.s == "ZVec" || x.s == "RVec" || x.s == "BVec") return vecT(scalarT(x.s[0] == 'Z' ? Type::Z : x.s[0] == 'R' ? Type::R : Type::B));
+    if (x.s == "ZMat" || x.s == "RMat") { Type m; m.k = Type::Mat; m.sub.push_back(scalarT(x.s[0] == 'Z' ? Type::Z : Type::R)); return m; }
+    if (x.s == "vector") return vecT(type());
+    if (x.s == "matrix") { Type m; m.k = Type::Mat; m.sub.push_back(type()); return m; }
+    if (x.s == "Array") {            // Array lo...hi[, lo...hi] T   (1-D only)
+      ref(); expect("..."); ref();
+      if (accept(",")) fail("multi-dimensional Array types are not supported by the CUDA lowering");
+      return vecT(type());
+    }
+    if (x.s == "Subrange") { Type b = type(); ref(); ref(); return b; }
+    if (x.s == "Union") {
+      expect("[");
+      Type u; u.k = Type::Union;
+      do {
+        expect("(");
+        Type tu; tu.k = Type::Tuple;
+        if (!accept(")")) { do tu.sub.push_back(type()); while (accept(",")); expect(")"); }
+        u.sub.push_back(tu);
+      } while (accept(","));
+      expect("]");
+      return u;
+    }
+    --p; fail("unknown type");
+  }
+
+  // primary [.T_F | .?]* [! primary[.T_F]*]*
+  RefP atom() {
+    RefP r = std::make_shared<Ref>();
+    if (accept("(")) {
+      int tag;
+      if (peek().k == Tok::Id && ctor_name(peek().s, &tag)) {       // (C<k> fields :: Union[..])
+        next(); r->k = Ref::Data; r->tag = tag;
+        while (!is("::")) r->args.push_back(ref());
+        expect("::"); r->type = type(); expect(")");
+      } else { r = ref(); expect(")"); }
+    } else if (accept("[")) {
+      r->k = Ref::List;
+      if (!accept("]")) { do r->args.push_back(ref()); while (accept(",")); expect("]"); }
+    } else {
+      Tok x = next();
+      if (x.k == Tok::Num || x.s == "Infinity" || x.s == "NaN") { r->k = Ref::Num; r->name = x.s; }
+      else if (x.k == Tok::Id) { r->k = Ref::Var; r->name = x.s; }
+      else { --p; fail("expected a reference"); }
+    }
+    for (;;) {
+      if (is(".") && peek(1).k == Tok::Num && peek(1).col == peek().col + 1) {   // .T_F  (lexed as `.`, `T`, then `_F` glued: handle both spellings)
+        next(); Tok a = next();
+        RefP e = std::make_shared<Ref>(); e->k = Ref::Extract; e->base = r; e->tag = atoi(a.s.c_str());
+        if (peek().k == Tok::Id && peek().s[0] == '_' && peek().col == a.col + (int)a.s.size()) { e->field = atoi(next().s.c_str() + 1); }
+        else fail("malformed Extract");
+        r = e; continue;
+      }
+      if (is(".?")) { next(); RefP e = std::make_shared<Ref>(); e->k = Ref::TagOf; e->base = r; r = e; continue; }
+      break;
+    }
+    return r;
+  }
+  RefP ref() {
+    RefP r = atom();
+    if (is("!")) {
+      RefP ix = std::make_shared<Ref>(); ix->k = Ref::Index; ix->base = r;
+      while (accept("!")) ix->args.push_back(atom());
+      return ix;
+    }
+    return r;
+  }
+
+  static bool binop(const std::string& s) {
+    static const char* ops[] = {"+", "-", "*", "/", "**", "==", "/=", "<", "<=", ">", ">=", "&&", "||", "<>", "#>", "<.>", "<\\>", nullptr};
+    for (int i = 0; ops[i]; ++i) if (s == ops[i]) return true;
+    return false;
+  }
+
+  // let-block body: [let defs in] (do ... | ret | [rets])
+  Body body(bool list_rets) {
+    Body b;
+    if (accept("let")) {
+      while (!is("in")) b.defs.push_back(def());
+      expect("in");
+    }
+    if (accept("do")) {
+      while (!is("return")) b.pnodes.push_back(pnode());
+      expect("return");
+      expect("[");
+      if (!accept("]")) { do b.rets.push_back(ref()); while (accept(",")); expect("]"); }
+    } else if (list_rets && is("[")) {
+      next();
+      if (!accept("]")) { do b.rets.push_back(ref()); while (accept(",")); expect("]"); }
+    } else {
+      b.rets.push_back(ref());
+    }
+    return b;
+  }
+
+  void array_params(std::vector<std::string>* ids, std::vector<std::pair<RefP, RefP>>* sh) {
+    do {
+      Tok i = next(); if (i.k != Tok::Id) fail("expected an index id");
+      expect("<-"); RefP lo = ref(); expect("..."); RefP hi = ref();
+      ids->push_back(i.s); sh->push_back({lo, hi});
+    } while (accept(","));
+  }
+
+  std::vector<Alt> alts(bool probabilistic) {
+    std::vector<Alt> out;
+    for (;;) {
+      const Tok& h = peek();
+      int tag;
+      bool int_alt = h.k == Tok::Num && is("->", 1);
+      bool ctor_alt = h.k == Tok::Id && ctor_name(h.s, &tag) && h.first;
+      if (!int_alt && !ctor_alt) break;
+      Alt a; next();
+      if (ctor_alt) while (!is("->")) { Tok i = next(); if (i.k != Tok::Id) fail("expected a constructor field id"); a.inputs.push_back(i.s); }
+      expect("->");
+      a.body = body(!probabilistic);
+      out.push_back(std::move(a));
+    }
+    if (out.empty()) fail("case/switch without alternatives");
+    return out;
+  }
+
+  Def def() {
+    Def d; Tok id = next();
+    if (id.k != Tok::Id) { --p; fail("expected a definition"); }
+    d.id = id.s; expect("=");
+    Node& n = d.node;
+    if (is("[") ) {                                  // Array comprehension
+      next(); n.k = Node::Array;
+      n.lam = std::make_shared<Body>(body(false));
+      expect("|"); array_params(&n.params, &n.shape); expect("]");
+    } else if (is("foldl") || is("foldr") || is("scanl") || is("scanr") || is("scan")) {
+      n.k = Node::Fold; n.f = next().s;
+      n.args.push_back(ref()); n.args.push_back(ref());
+      expect("$"); expect("\\");
+      n.params.push_back(next().s); n.params.push_back(next().s);   // printed (acc elem) for foldl, showNode Expression.hs:228-241
+      expect("->");
+      n.lam = std::make_shared<Body>(body(false));
+    } else if (accept("case")) {
+      n.k = Node::Case; n.args.push_back(ref()); expect("of");
+      n.alts = alts(false);
+    } else if (is("\\")) {
+      fail("Function nodes are not supported by the CUDA lowering");
+    } else {
+      n.k = Node::Apply;
+      size_t save = p;
+      bool infix = false;
+      if (!(peek().k == Tok::Sym && (is("+s") || is("*s") || is("&&s")))) {
+        if (peek().k != Tok::Id || peek().s.find('_') != std::string::npos || is("(") || peek(1).k == Tok::Sym) {
+          // try `a op b`
+          try {
+            RefP a = ref();
+            if (peek().k == Tok::Sym && binop(peek().s)) {
+              n.f = next().s; n.args.push_back(a); n.args.push_back(ref()); infix = true;
+            }
+          } catch (const Error&) {}
+        }
+      }
+      if (!infix) {
+        p = save;
+        Tok f = next(); n.f = f.s;
+        int line = f.line;
+        while (!is("::") && peek().k != Tok::End && peek().line == line) n.args.push_back(ref());
+      }
+    }
+    if (accept("::")) n.type = type();
+    return d;
+  }
+
+  PNode pnode() {
+    PNode q; Tok id = next();
+    if (id.k != Tok::Id) { --p; fail("expected `x <- ...`"); }
+    q.id = id.s; expect("<-");
+    if (accept("switch")) {
+      q.k = PNode::Switch; q.args.push_back(ref()); expect("of");
+      q.alts = alts(true);
+    } else if (accept("[")) {                          // joint: [ [let .. in] dist args :: P T | i <- lo...hi ] :: T
+      q.k = PNode::Loop;
+      q.lam = std::make_shared<Body>();
+      if (accept("let")) { while (!is("in")) q.lam->defs.push_back(def()); expect("in"); }
+      q.inner = std::make_shared<PNode>();
+      q.inner->id = q.id;
+      dist(q.inner.get());
+      expect("|"); array_params(&q.params, &q.shape); expect("]");
+      expect("::"); q.type = type();
+    } else if (is("chain") || is("unfoldP") || is("foldP") || is("AnamorphismP") || is("CatamorphismP")) {
+      fail("Chain / RecursionScheme PNodes are not supported by the CUDA lowering");
+    } else {
+      dist(&q);
+    }
+    return q;
+  }
+  void dist(PNode* q) {
+    Tok f = next(); if (f.k != Tok::Id) { --p; fail("expected a distribution name"); }
+    q->k = PNode::Dist; q->dist = f.s;
+    if (is("(") && peek(1).k == Tok::Id && !ctor_name(peek(1).s, nullptr) && peek(1).s.find('_') == std::string::npos)
+      fail("higher-order distributions (" + f.s + ") are not supported by the CUDA lowering");
+    while (!is("::")) q->args.push_back(ref());
+    expect("::");
+    if (!(peek().k == Tok::Id && peek().s == "P")) fail("expected `P <type>`");
+    next(); q->type = type();
+  }
+
+  Body program() {
+    if (is("[") && peek(1).s == "runStep") { next(); next(); expect("]"); }
+    if (is("\\")) { next(); next(); expect("->"); }      // `\input ->` header of Show (a -> P b)
+    Body b = body(true);
+    if (peek().k != Tok::End) fail("trailing input after the program");
+    return b;
+  }
+};
+
+// ---------------------------------------------------------------------------------------------
+// state layout: kernel input k of type T -> descriptor fields (ccRead/ccPrint, CC.hs:353-396)
+//   Z/B  -> in<k>           i32 [1]
+//   R    -> in<k>           f64 [1]
+//   vector -> in<k> f64|i32 [cap] + in<k>_len i32 [1]
+//   Union[..] -> in<k>_tag i32 + one slot per (scalar kind | vector kind, occurrence) shared by all
+//              constructors: in<k>_r<j>, in<k>_z<j>, in<k>_rv<j>(+_len), in<k>_zv<j>(+_len)
+// ---------------------------------------------------------------------------------------------
+struct Slot { std::string name; Type type; };
+struct UnionLayout { std::vector<Slot> slots; std::vector<std::vector<int>> ctor; };  // ctor[c][field] -> slot
+
+static UnionLayout union_layout(const std::string& prefix, const Type& u) {
+  UnionLayout L;
+  std::map<std::string, std::vector<int>> byKind;
+  for (const Type& c : u.sub) {
+    std::map<std::string, int> used;
+    std::vector<int> f;
+    for (const Type& t : c.sub) {
+      std::string kind;
+      if (t.k == Type::R) kind = "r"; else if (t.integral()) kind = "z";
+      else if (t.k == Type::Vec && t.sub[0].k == Type::R) kind = "rv";
+      else if (t.k == Type::Vec && t.sub[0].integral()) kind = "zv";
+      else die("union field of type " + t.str() + " is not supported by the CUDA lowering");
+      int j = used[kind]++;
+      auto& v = byKind[kind];
+      if ((int)v.size() <= j) {
+        Slot s; s.name = prefix + "_" + kind + std::to_string(j);
+        s.type = (kind == "r") ? scalarT(Type::R) : (kind == "z") ? scalarT(Type::Z) : vecT(scalarT(kind == "rv" ? Type::R : Type::Z));
+        v.push_back((int)L.slots.size()); L.slots.push_back(s);
+      }
+      f.push_back(v[j]);
+    }
+    L.ctor.push_back(f);
+  }
+  return L;
+}
+
+// ---------------------------------------------------------------------------------------------
+// code generator
+// ---------------------------------------------------------------------------------------------
+struct Val {               // what an IR id denotes in the emitted code
+  Type type;
+  std::string expr;        // scalar: C expression; vector: name of a VecD/VecI view; union: name of a struct variable
+  const Node* array = nullptr;   // un-materialised Array node (inlined at its use)
+  std::vector<std::string> tuple;  // Case with several returns: one expr per member
+};
+
+struct Gen {
+  std::ostringstream out, decls;   // decls: per-thread vector buffers, hoisted to function scope
+  int ind = 2;
+  int veccap = 64;
+  int uniq = 0;
+  std::vector<std::map<std::string, Val>> scopes;
+  std::map<std::string, UnionLayout> unions;   // by type string
+  std::map<std::string, std::string> union_cname;
+
+  void line(const std::string& s) { out << std::string(ind, ' ') << s << "\n"; }
+  void push() { scopes.emplace_back(); }
+  void pop() { scopes.pop_back(); }
+  void bind(const std::string& id, const Val& v) { scopes.back()[id] = v; }
+  const Val& lookup(const std::string& id) const {
+    for (size_t i = scopes.size(); i-- > 0;) { auto it = scopes[i].find(id); if (it != scopes[i].end()) return it->second; }
+    die("unbound identifier " + id + " (is it a kernel input whose type was not given?)");
+  }
+  std::string fresh(const std::string& b) { return b + "_" + std::to_string(uniq++); }
+
+  static std::string ctype(const Type& t) {
+    if (t.k == Type::R) return "double";
+    if (t.integral()) return "int";
+    if (t.k == Type::Vec) return t.sub[0].k == Type::R ? "VecD" : "VecI";
+    die("no C type for " + t.str());
+  }
+  std::string union_struct(const Type& u) {
+    std::string key = u.str();
+    auto it = union_cname.find(key);
+    if (it != union_cname.end()) return it->second;
+    std::string nm = "U" + std::to_string(union_cname.size());
+    union_cname[key] = nm; unions[key] = union_layout("f", u);
+    return nm;
+  }
+
+  static std::string num(const std::string& s, bool as_real) {
+    if (s == "Infinity") return "stk::pos_inf()";
+    if (s == "-Infinity") return "stk::neg_inf()";
+    if (s == "NaN") return "(0.0/0.0)";
+    bool isreal = s.find('.') != std::string::npos || s.find('e') != std::string::npos || s.find('E') != std::string::npos;
+    if (as_real && !isreal) return s + ".0";
+    return s;
+  }
+
+  Type type_of(const RefP& r) {
+    switch (r->k) {
+      case Ref::Num: { bool isreal = r->name.find_first_of(".eEIN") != std::string::npos; return scalarT(isreal ? Type::R : Type::Z); }
+      case Ref::Var: return lookup(r->name).type;
+      case Ref::Index: { Type b = type_of(r->base); if (b.k != Type::Vec) die("indexing a non-vector (" + b.str() + ")"); return b.sub[0]; }
+      case Ref::Extract: { Type b = type_of(r->base); if (b.k == Type::Tuple) return b.sub.at(r->field); if (r->field == 0) return b; die("Extract of a non-tuple"); }
+      case Ref::TagOf: return scalarT(Type::Z);
+      case Ref::Data: return r->type;
+      case Ref::List: return vecT(r->args.empty() ? scalarT(Type::R) : type_of(r->args[0]));
+    }
+    return Type();
+  }
+
+  // scalar / view expression for a reference (ccNodeRef, CC.hs:47-60)
+  std::string rv(const RefP& r, bool want_real = false) {
+    switch (r->k) {
+      case Ref::Num: return num(r->name, want_real);
+      case Ref::Var: {
+        const Val& v = lookup(r->name);
+        if (v.array) die("array " + r->name + " is used where it would have to be materialised; not supported");
+        if (want_real && v.type.integral()) return "(double)" + v.expr;
+        return v.expr;
+      }
+      case Ref::Index: {
+        if (r->args.size() != 1) die("only 1-D indexing is supported");
+        RefP b = r->base;
+        if (b->k == Ref::Var && lookup(b->name).array) return inline_array_at(*lookup(b->name).array, rv(r->args[0]));
+        std::string e = rv(b) + ".at(" + rv(r->args[0]) + ")";
+        if (want_real && type_of(r).integral()) return "(double)" + e;
+        return e;
+      }
+      case Ref::Extract: {
+        if (r->base->k == Ref::Var) {
+          const Val& v = lookup(r->base->name);
+          if (!v.tuple.empty()) return v.tuple.at(r->field);
+          if (r->field == 0) return v.expr;
+        }
+        die("unsupported Extract");
+      }
+      case Ref::TagOf: return rv(r->base) + ".tag";
+      case Ref::Data: die("union construction is only supported as an ifThenElse branch or a return value");
+      case Ref::List: die("list literal is only supported as a pmf argument");
+    }
+    return "";
+  }
+
+  // Array node evaluated at one index without materialising it (only for bodies that are a bare reference)
+  std::string inline_array_at(const Node& a, const std::string& idx) {
+    if (!a.lam->defs.empty() || a.params.size() != 1) die("indexing a computed array is not supported");
+    push(); Val v; v.type = scalarT(Type::Z); v.expr = "(" + idx + ")"; bind(a.params[0], v);
+    std::string e = rv(a.lam->rets[0]); pop();
+    return e;
+  }
+
+  // ---- union values ------------------------------------------------------------------------
+  // assign `dst` (a union struct variable) from a Data ref or a union-typed variable
+  void assign_union(const std::string& dst, const Type& ut, const RefP& src) {
+    if (src->k == Ref::Data) {
+      const UnionLayout& L = unions[ut.str()];
+      if (src->tag >= (int)L.ctor.size() || L.ctor[src->tag].size() != src->args.size()) die("constructor C" + std::to_string(src->tag) + " does not fit " + ut.str());
+      line(dst + ".tag = " + std::to_string(src->tag) + ";");
+      for (size_t j = 0; j < src->args.size(); ++j) {
+        const Slot& s = L.slots[L.ctor[src->tag][j]];
+        line(dst + "." + s.name + " = " + rv(src->args[j], s.type.k == Type::R) + ";");
+      }
+    } else {
+      line(dst + " = " + rv(src) + ";");
+    }
+  }
+
+  // ---- nodes (ccNode, CC.hs:123-274) ----------------------------------------------------------
+  static const char* c_binop(const std::string& f) {
+    static const std::pair<const char*, const char*> ops[] = {{"+", "+"}, {"-", "-"}, {"*", "*"}, {"==", "=="}, {"/=", "!="},
+      {">", ">"}, {">=", ">="}, {"<", "<"}, {"<=", "<="}, {"&&", "&&"}, {"||", "||"}};   // ccOperators, CC.hs:92-107
+    for (auto& o : ops) if (f == o.first) return o.second;
+    return nullptr;
+  }
+
+  void def(const Def& d) {
+    const Node& n = d.node;
+    Val v; v.type = n.type;
+    if (n.k == Node::Array) {                      // kept symbolic; consumers inline it (CC.hs:231-235 materialises)
+      if (v.type.k == Type::Unknown) v.type = vecT(scalarT(Type::R));
+      v.array = &n; bind(d.id, v); return;
+    }
+    if (n.k == Node::Fold) { fold(d); return; }
+    if (n.k == Node::Case) { case_node(d); return; }
+    const std::string& f = n.f;
+    auto arg = [&](size_t i, bool real = false) { return rv(n.args.at(i), real); };
+    bool rt = n.type.k == Type::R;
+    if (f == "getExternal") {                      // alias of a PNode's value (CC.hs:124-125 emits the draw here)
+      ensure_drawn(n.args.at(0)->name);
+      bind(d.id, lookup(n.args.at(0)->name)); return;
+    }
+    if (n.type.k == Type::Union) {                 // only ifThenElse / id over unions
+      std::string st = union_struct(n.type);
+      line(st + " " + d.id + " = " + st + "();");
+      if (f == "ifThenElse") {
+        line("if (" + arg(0) + ") {"); ind += 2; assign_union(d.id, n.type, n.args[1]); ind -= 2;
+        line("} else {"); ind += 2; assign_union(d.id, n.type, n.args[2]); ind -= 2; line("}");
+      } else if (f == "id") assign_union(d.id, n.type, n.args[0]);
+      else die("node `" + f + "` producing a union is not supported");
+      v.expr = d.id; bind(d.id, v); return;
+    }
+    if (n.type.k == Type::Vec) { vector_node(d); return; }
+    if (!n.type.scalar()) die("definition " + d.id + " has unsupported type " + n.type.str());
+    std::string e;
+    if (f == "+s" || f == "*s" || f == "&&s") {    // CC.hs:129-132: left-to-right in operand order
+      const char* op = f == "+s" ? " + " : f == "*s" ? " * " : " && ";
+      for (size_t i = 0; i < n.args.size(); ++i) e = i ? "(" + e + op + arg(i, rt) + ")" : arg(i, rt);
+    } else if (f == "/" && rt) e = "(double)" + arg(0) + " / (double)" + arg(1);          // CC.hs:133-134
+    else if (f == "/") e = arg(0) + " / " + arg(1);
+    else if (const char* op = c_binop(f)) {
+      bool anyreal = type_of(n.args.at(0)).k == Type::R || type_of(n.args.at(1)).k == Type::R;
+      e = arg(0, anyreal) + " " + op + " " + arg(1, anyreal);
+    }
+    else if (f == "**") e = "pow(" + arg(0, true) + ", " + arg(1, true) + ")";             // CC.hs:155-156
+    else if (f == "ifThenElse") e = arg(0) + " ? " + arg(1, rt) + " : " + arg(2, rt);      // CC.hs:141-143
+    else if (f == "negate") e = "-" + arg(0);
+    else if (f == "id") e = arg(0, rt);
+    else if (f == "not") e = "!" + arg(0);
+    else if (f == "min" || f == "max") {
+      // interpreter semantics (Const.hs:81-82): min a b = if a < b then a else b.  On NaN this keeps b, so an
+      // acceptance ratio `min 1 NaN` stays NaN and the bernoulli rejects; the C++ template min<double>(1, NaN)
+      // (CC.hs:146-147) would yield 1 and accept.  DESIGN.md 3 lists the divergence.
+      std::string a0 = arg(0, rt), a1 = arg(1, rt);
+      e = "(" + a0 + (f == "min" ? " < " : " > ") + a1 + " ? " + a0 + " : " + a1 + ")";
+    }
+    else if (f == "vectorSize") {                                                          // CC.hs:144-145
+      const RefP& a = n.args.at(0);
+      if (a->k == Ref::Var && lookup(a->name).array) {
+        const Node& an = *lookup(a->name).array;
+        e = "(" + rv(an.shape[0].second) + " - " + rv(an.shape[0].first) + " + 1)";
+      } else e = arg(0) + ".len";
+    }
+    else if (f == "findSortedInsertIndex") e = "stk::find_sorted_insert_index_v(" + arg(0, true) + ", " + arg(1) + ")";   // CC.hs:192-197
+    else if (f == "logFactorial") e = "stk::log_factorial(" + arg(0) + ")";               // CC.hs:167-168
+    else if (f == "pmf_lpdf" || f == "categorical_lpdf") {                                 // Const.hs:94
+      const RefP& ps = n.args.at(1);
+      if (ps->k != Ref::List) die(f + " needs a literal probability list");
+      std::string tab = fresh("ps");
+      std::string init; for (size_t i = 0; i < ps->args.size(); ++i) init += (i ? ", " : "") + rv(ps->args[i], true);
+      line("const double " + tab + "[] = {" + init + "};");
+      e = "stk::pmf_lpdf(" + arg(0) + ", " + tab + ")";
+    }
+    else if (f.size() > 5 && f.compare(f.size() - 5, 5, "_lpdf") == 0) {                    // CC.hs:198-228, log-space forms of stk_device.cuh
+      static const std::set<std::string> intx = {"poisson_lpdf", "neg_binomial_lpdf", "geometric_lpdf", "bernoulli_lpdf", "bernoulliLogit_lpdf", "discreteUniform_lpdf"};
+      static const std::map<std::string, std::string> rename = {{"bernoulliLogit_lpdf", "bernoulli_logit_lpdf"}, {"discreteUniform_lpdf", "discrete_uniform_lpdf"}};
+      static const std::set<std::string> known = {"normal_lpdf", "gamma_lpdf", "inv_gamma_lpdf", "geometric_lpdf", "neg_binomial_lpdf", "poisson_lpdf", "uniform_lpdf",
+        "discreteUniform_lpdf", "bernoulli_lpdf", "bernoulliLogit_lpdf", "cauchy_lpdf", "logistic_lpdf", "beta_lpdf"};
+      if (!known.count(f)) die("log-density `" + f + "` is not in the device library");
+      auto it = rename.find(f);
+      e = "stk::" + (it == rename.end() ? f : it->second) + "(" + arg(0, !intx.count(f));
+      for (size_t i = 1; i < n.args.size(); ++i) e += ", " + arg(i, f != "discreteUniform_lpdf");
+      e += ")";
+    }
+    else if (f == "uniform_cdf") e = "stk::uniform_cdf(" + arg(0, true) + ", " + arg(1, true) + ", " + arg(2, true) + ")";
+    else {
+      static const std::set<std::string> math1 = {"exp", "log", "sqrt", "abs", "sin", "cos", "tan", "tanh", "sinh", "cosh", "floor", "ceil", "lgamma", "log1p", "expm1", "asin", "acos", "atan"};
+      if (math1.count(f)) {
+        e = (f == "abs" ? std::string(rt ? "fabs" : "abs") : f) + "(" + arg(0, rt) + ")";    // CC.hs:229-230 (generic call)
+      } else die("node `" + f + "` is not supported by the CUDA lowering");
+    }
+    line("const " + ctype(n.type) + " " + d.id + " = " + e + ";");
+    v.expr = d.id; bind(d.id, v);
+  }
+
+  // vectors that must exist as storage: replaceIndex / insertIndex / deleteIndex (CC.hs:169-191)
+  void vector_node(const Def& d) {
+    const Node& n = d.node; const std::string& f = n.f;
+    bool real = n.type.sub[0].k == Type::R;
+    std::string ct = real ? "double" : "int", buf = fresh(d.id + "_buf");
+    decls << "  " << ct << " " << buf << "[STK_VECCAP];\n";
+    std::string src = rv(n.args.at(0)), i = fresh("i");
+    if (f == "replaceIndex") {
+      line("for (int " + i + " = 1; " + i + " <= " + src + ".len; ++" + i + ") " + buf + "[" + i + " - 1] = " + src + ".at(" + i + ");");
+      line(buf + "[" + rv(n.args.at(1)) + " - 1] = " + rv(n.args.at(2), real) + ";");
+      line("const " + ctype(n.type) + " " + d.id + "(" + buf + ", 1, " + src + ".len);");
+    } else if (f == "insertIndex") {
+      std::string j = rv(n.args.at(1)), e = rv(n.args.at(2), real);
+      line("for (int " + i + " = 1; " + i + " <= " + src + ".len + 1; ++" + i + ") " + buf + "[" + i + " - 1] = " + i + " < " + j + " ? " + src + ".at(" + i + ") : (" + i + " == " + j + " ? " + e + " : " + src + ".at(" + i + " - 1));");
+      line("const " + ctype(n.type) + " " + d.id + "(" + buf + ", 1, " + src + ".len + 1);");
+    } else if (f == "deleteIndex") {
+      std::string j = rv(n.args.at(1));
+      line("for (int " + i + " = 1; " + i + " <= " + src + ".len - 1; ++" + i + ") " + buf + "[" + i + " - 1] = " + i + " < " + j + " ? " + src + ".at(" + i + ") : " + src + ".at(" + i + " + 1);");
+      line("const " + ctype(n.type) + " " + d.id + "(" + buf + ", 1, " + src + ".len - 1);");
+    } else if (f == "id") {
+      line("const " + ctype(n.type) + " " + d.id + " = " + src + ";");
+    } else die("vector node `" + f + "` is not supported by the CUDA lowering");
+    Val v; v.type = n.type; v.expr = d.id; bind(d.id, v);
+  }
+
+  // FoldScan (CC.hs:236-262): sequential loop, left/right; the list is a vector view or an inlined Array
+  void fold(const Def& d) {
+    const Node& n = d.node;
+    if (n.f != "foldl" && n.f != "foldr") die("scans are not supported by the CUDA lowering");
+    if (!n.type.scalar() && n.type.k != Type::Unknown) die("fold producing " + n.type.str() + " is not supported");
+    Type at = n.type.k == Type::Unknown ? type_of(n.args[0]) : n.type;
+    bool rt = at.k == Type::R;
+    line(ctype(at) + " " + d.id + " = " + rv(n.args[0], rt) + ";");
+    const RefP& ls = n.args[1];
+    std::string it = fresh("k");
+    const Node* arr = (ls->k == Ref::Var && lookup(ls->name).array) ? lookup(ls->name).array : nullptr;
+    // showNode prints the lambda inputs reversed for foldl: \acc elem
+    std::string acc = n.f == "foldl" ? n.params[0] : n.params[1], elem = n.f == "foldl" ? n.params[1] : n.params[0];
+    std::string lo, hi;
+    if (arr) { if (arr->params.size() != 1) die("fold over a multi-dimensional array"); lo = rv(arr->shape[0].first); hi = rv(arr->shape[0].second); }
+    else { lo = "1"; hi = rv(ls) + ".len"; }
+    if (n.f == "foldl") line("for (int " + it + " = " + lo + "; " + it + " <= " + hi + "; ++" + it + ") {");
+    else line("for (int " + it + " = " + hi + "; " + it + " >= " + lo + "; --" + it + ") {");
+    ind += 2; push();
+    Val ev;
+    if (arr) {
+      Val iv; iv.type = scalarT(Type::Z); iv.expr = it; bind(arr->params[0], iv);
+      for (const Def& ad : arr->lam->defs) def(ad);
+      ev.type = lookup(ls->name).type.sub[0];
+      if (ev.type.k == Type::Unknown) ev.type = type_of(arr->lam->rets[0]);
+      line("const " + ctype(ev.type) + " " + elem + " = " + rv(arr->lam->rets[0], ev.type.k == Type::R) + ";");
+    } else {
+      ev.type = type_of(ls).sub[0];
+      line("const " + ctype(ev.type) + " " + elem + " = " + rv(ls) + ".at(" + it + ");");
+    }
+    ev.expr = elem; bind(elem, ev);
+    Val av; av.type = at; av.expr = acc;
+    line("const " + ctype(at) + " " + acc + " = " + d.id + ";");
+    bind(acc, av);
+    for (const Def& bd : n.lam->defs) def(bd);
+    line(d.id + " = " + rv(n.lam->rets[0], rt) + ";");
+    pop(); ind -= 2; line("}");
+    Val v; v.type = at; v.expr = d.id; bind(d.id, v);
+  }
+
+  // Case on an integer head, alternatives 1..n (CC.hs:263-273)
+  void case_node(const Def& d) {
+    const Node& n = d.node;
+    std::vector<Type> ts;
+    if (n.type.k == Type::Tuple) ts = n.type.sub; else if (n.type.k != Type::Unknown) ts.push_back(n.type);
+    else { push(); for (auto& r : n.alts[0].body.rets) ts.push_back(r->k == Ref::Num ? type_of(r) : scalarT(Type::R)); pop(); }
+    Val v; v.type = n.type.k == Type::Unknown ? (ts.size() == 1 ? ts[0] : Type()) : n.type;
+    if (v.type.k == Type::Unknown) { v.type.k = Type::Tuple; v.type.sub = ts; }
+    for (size_t j = 0; j < ts.size(); ++j) {
+      if (!ts[j].scalar()) die("case alternatives returning " + ts[j].str() + " are not supported");
+      std::string nm = ts.size() == 1 ? d.id : d.id + "_" + std::to_string(j);
+      line(ctype(ts[j]) + " " + nm + " = 0;");
+      v.tuple.push_back(nm);
+    }
+    v.expr = v.tuple[0];
+    if (ts.size() == 1) v.tuple.clear();
+    line("switch (" + rv(n.args[0]) + ") {");
+    for (size_t a = 0; a < n.alts.size(); ++a) {
+      if (!n.alts[a].inputs.empty()) die("case over an algebraic data type is not supported (CC.hs:268 neither)");
+      line("case " + std::to_string(a + 1) + ": {"); ind += 2; push();
+      for (const Def& bd : n.alts[a].body.defs) def(bd);
+      if (n.alts[a].body.rets.size() != ts.size()) die("case alternative arity mismatch");
+      for (size_t j = 0; j < ts.size(); ++j)
+        line((ts.size() == 1 ? d.id : d.id + "_" + std::to_string(j)) + " = " + rv(n.alts[a].body.rets[j], ts[j].k == Type::R) + ";");
+      line("break;"); pop(); ind -= 2; line("}");
+    }
+    line("}");
+    bind(d.id, v);
+  }
+
+  // ---- PNodes (ccPNode', CC.hs:276-321) ------------------------------------------------------------
+  std::map<std::string, const PNode*> pending;       // not yet emitted draws of the current do-block chain
+  std::vector<std::map<std::string, const PNode*>> pending_stack;
+
+  static void id_level_ptr(const std::string& id, int* level, int* ptr) {
+    // x_<ns>_<L>_<P>
+    size_t b = id.rfind('_'); size_t a = id.rfind('_', b - 1);
+    if (b == std::string::npos || a == std::string::npos) die("malformed PNode id " + id);
+    *ptr = atoi(id.c_str() + b + 1); *level = atoi(id.c_str() + a + 1);
+  }
+
+  void ensure_drawn(const std::string& id) {
+    for (size_t i = pending_stack.size(); i-- > 0;) {
+      auto it = pending_stack[i].find(id);
+      if (it != pending_stack[i].end()) { const PNode* q = it->second; pending_stack[i].erase(it); pnode(*q); return; }
+    }
+  }
+  void need(const RefP& r) {       // draw any PNode the reference depends on before it is used
+    if (!r) return;
+    if (r->k == Ref::Var) ensure_drawn(r->name);
+    need(r->base);
+    for (auto& a : r->args) need(a);
+  }
+
+  void need_body(const Body& b) {  // draws referenced from inside a lambda body must precede the loop
+    for (const Def& d : b.defs) {
+      for (auto& a : d.node.args) need(a);
+      for (auto& sh : d.node.shape) { need(sh.first); need(sh.second); }
+      if (d.node.lam) need_body(*d.node.lam);
+      for (auto& al : d.node.alts) need_body(al.body);
+    }
+    for (auto& r : b.rets) need(r);
+  }
+
+  void pnode(const PNode& q) {
+    int level, ptr; id_level_ptr(q.id, &level, &ptr);
+    std::string slot = std::to_string(256 * level + 16 * ptr) + "u";
+    if (q.k == PNode::Switch) { switch_node(q); return; }
+    if (q.k == PNode::Loop) die("joint (Loop) PNodes are not supported by the CUDA lowering yet");
+    for (auto& a : q.args) need(a);
+    auto arg = [&](size_t i, bool real = true) { return rv(q.args.at(i), real); };
+    std::string g = fresh("g");
+    line("stk::Rng " + g + " = rng; " + g + ".slot = " + slot + ";");
+    const std::string& f = q.dist;
+    std::string e;
+    if (f == "normal") e = "stk::draw_normal(" + g + ", " + arg(0) + ", " + arg(1) + ")";                 // CC.hs:278
+    else if (f == "uniform") e = "stk::draw_uniform(" + g + ", " + arg(0) + ", " + arg(1) + ")";          // :280
+    else if (f == "bernoulli") e = "stk::draw_bernoulli(" + g + ", " + arg(0) + ")";                      // :290-291
+    else if (f == "bernoulliLogit") e = "stk::draw_bernoulli(" + g + ", 1.0 / (1.0 + exp(-(" + arg(0) + "))))";
+    else if (f == "gamma") e = "stk::draw_gamma(" + g + ", " + arg(0) + ", " + arg(1) + ")";              // :294-296
+    else if (f == "poisson") e = "stk::draw_poisson(" + g + ", " + arg(0) + ")";                          // :279
+    else if (f == "discreteUniform") e = "stk::draw_discrete_uniform(" + g + ", " + arg(0, false) + ", " + arg(1, false) + ")";   // :277
+    else if (f == "cauchy") e = "stk::draw_cauchy(" + g + ", " + arg(0) + ", " + arg(1) + ")";
+    else if (f == "pmf" || f == "categorical") {                                                          // :292-293
+      const RefP& ps = q.args.at(0);
+      if (ps->k != Ref::List) die("pmf needs a literal probability list");
+      std::string tab = fresh("ps"), init;
+      for (size_t i = 0; i < ps->args.size(); ++i) init += (i ? ", " : "") + rv(ps->args[i], true);
+      line("const double " + tab + "[] = {" + init + "};");
+      e = "stk::draw_pmf(" + g + ", " + tab + ", " + std::to_string(ps->args.size()) + ")";
+    } else die("distribution `" + f + "` is not supported by the CUDA lowering");
+    if (!q.type.scalar()) die("draw of type " + q.type.str() + " is not supported");
+    line("const " + ctype(q.type) + " " + q.id + " = " + e + ";");
+    Val v; v.type = q.type; v.expr = q.id; bind(q.id, v);
+  }
+
+  // Switch over a union-typed head (CC.hs:306-316): one case per constructor, fields tied to ids
+  void switch_node(const PNode& q) {
+    need(q.args[0]);
+    Type ut = type_of(q.args[0]);
+    if (ut.k != Type::Union) die("switch head is not a union");
+    // `Show PNode` prints no type for a Switch (Program.hs:142-153): take it from the first alternative's
+    // return when that is a constructor, else the head's own type (a kernel t -> P t)
+    Type qt = q.type;
+    if (qt.k == Type::Unknown) {
+      const RefP& r0 = q.alts.at(0).body.rets.at(0);
+      qt = ut;
+      if (r0->k == Ref::Data) qt = r0->type;
+      else for (const Def& d0 : q.alts[0].body.defs) if (r0->k == Ref::Var && d0.id == r0->name && d0.node.type.k == Type::Union) qt = d0.node.type;
+    }
+    std::string st = union_struct(qt), hd = rv(q.args[0]);
+    const UnionLayout& L = unions[ut.str()];
+    line(st + " " + q.id + " = " + (qt == ut ? hd : st + "()") + ";");
+    line("switch (" + hd + ".tag) {");
+    for (size_t c = 0; c < q.alts.size(); ++c) {
+      const Alt& a = q.alts[c];
+      if (a.inputs.size() != L.ctor[c].size()) die("switch alternative C" + std::to_string(c) + " arity mismatch");
+      line("case " + std::to_string(c) + ": {"); ind += 2; push();
+      for (size_t j = 0; j < a.inputs.size(); ++j) {
+        const Slot& s = L.slots[L.ctor[c][j]];
+        line("const " + ctype(s.type) + " " + a.inputs[j] + " = " + hd + "." + s.name + ";");
+        Val v; v.type = s.type; v.expr = a.inputs[j]; bind(a.inputs[j], v);
+      }
+      body(a.body);
+      if (a.body.rets.size() != 1) die("switch alternative must return one value");
+      assign_union(q.id, qt, a.body.rets[0]);
+      line("break;"); pop(); ind -= 2; line("}");
+    }
+    line("}");
+    Val v; v.type = qt; v.expr = q.id; bind(q.id, v);
+  }
+
+  // ccDAG (CC.hs:327-346): definitions in pointer order; a PNode is drawn right before its first use
+  // (the reference places the draw at the node's `getExternal`), the rest at the end of the block.
+  void body(const Body& b) {
+    pending_stack.emplace_back();
+    for (const PNode& q : b.pnodes) pending_stack.back()[q.id] = &q;
+    for (const Def& d : b.defs) {
+      for (auto& a : d.node.args) need(a);
+      if (d.node.k != Node::Array && d.node.lam) need_body(*d.node.lam);
+      for (auto& al : d.node.alts) need_body(al.body);
+      if (d.node.k == Node::Fold && d.node.args[1]->k == Ref::Var) {
+        const Val& lv = lookup(d.node.args[1]->name);
+        if (lv.array) { need_body(*lv.array->lam); for (auto& sh : lv.array->shape) { need(sh.first); need(sh.second); } }
+      }
+      def(d);
+    }
+    for (const PNode& q : b.pnodes) ensure_drawn(q.id);
+    for (auto& r : b.rets) need(r);
+    pending_stack.pop_back();
+  }
+};
+
+// ---------------------------------------------------------------------------------------------
+// whole module (ccProgram, CC.hs:398-432)
+// ---------------------------------------------------------------------------------------------
+struct Field { std::string name; bool i32; std::string len; };
+
+static std::vector<Type> parse_types(const std::string& s) {
+  std::vector<Type> ts;
+  Parser p(s);
+  while (p.peek().k != Tok::End) { ts.push_back(p.type()); p.accept(";"); p.accept(","); }
+  return ts;
+}
+
+static std::map<std::string, std::string> parse_opts(const char* o) {
+  std::map<std::string, std::string> m;
+  std::istringstream in(o ? o : "");
+  std::string kv;
+  while (in >> kv) { size_t e = kv.find('='); if (e == std::string::npos) m[kv] = "1"; else m[kv.substr(0, e)] = kv.substr(e + 1); }
+  return m;
+}
+
+static std::string generate(const std::string& ir, const std::string& input_types, const char* options) {
+  auto opt = parse_opts(options);
+  Parser P(ir);
+  Body prog = P.program();
+  std::vector<Type> its = parse_types(input_types);
+  int level = opt.count("level") ? atoi(opt["level"].c_str()) : -1;
+  std::string name = opt.count("name") ? opt["name"] : "ir";
+  int veccap = opt.count("veccap") ? atoi(opt["veccap"].c_str()) : 64;
+  int block = opt.count("block") ? atoi(opt["block"].c_str()) : 128;
+  bool kernel = !its.empty();
+  if (level < 0) {                                  // find the Dummy level of the inputs: i_0_k (compileCC) or i_9_k (runStep)
+    level = ir.find("i_9_0") != std::string::npos ? 9 : 0;
+  }
+  Gen g; g.veccap = veccap;
+  g.push();
+  // ---- state fields ----
+  std::vector<Field> fields;
+  std::ostringstream load, store, rec;
+  std::vector<std::string> in_names;
+  for (size_t k = 0; k < its.size(); ++k) {
+    const Type& t = its[k];
+    std::string id = "i_" + std::to_string(level) + "_" + std::to_string(k), fn = "in" + std::to_string(k);
+    Val v; v.type = t;
+    auto F = [&](const std::string& nm) { return "F_" + nm; };
+    auto add_scalar = [&](const std::string& nm, bool i32, const std::string& cvar) {
+      fields.push_back({nm, i32, "1"});
+      load << "  " << (i32 ? "int " : "double ") << cvar << " = ((const " << (i32 ? "int" : "double") << "*)a.field[" << F(nm) << "])[chain];\n";
+      store << "  ((" << (i32 ? "int" : "double") << "*)a.field[" << F(nm) << "])[chain] = " << cvar << ";\n";
+      rec << " " << nm;
+    };
+    auto add_vec = [&](const std::string& nm, bool i32, const std::string& cvar) {
+      fields.push_back({nm, i32, "0"}); fields.push_back({nm + "_len", true, "1"});
+      load << "  " << (i32 ? "VecI " : "VecD ") << cvar << "((" << (i32 ? "int" : "double") << "*)a.field[" << F(nm) << "] + chain, a.n_chains, ((const int*)a.field[" << F(nm + "_len") << "])[chain]);\n";
+      store << "  store_vec(" << cvar << ", (" << (i32 ? "int" : "double") << "*)a.field[" << F(nm) << "] + chain, a.n_chains, (int)a.flen[" << F(nm) << "], (int*)a.field[" << F(nm + "_len") << "] + chain);\n";
+    };
+    if (t.k == Type::R) { add_scalar(fn, false, id); v.expr = id; }
+    else if (t.integral()) { add_scalar(fn, true, id); v.expr = id; }
+    else if (t.k == Type::Vec) { add_vec(fn, t.sub[0].k != Type::R, id); v.expr = id; }
+    else if (t.k == Type::Union) {
+      std::string st = g.union_struct(t);
+      const UnionLayout& L = g.unions[t.str()];
+      load << "  " << st << " " << id << ";\n";
+      fields.push_back({fn + "_tag", true, "1"});
+      load << "  " << id << ".tag = ((const int*)a.field[F_" << fn << "_tag])[chain];\n";
+      store << "  ((int*)a.field[F_" << fn << "_tag])[chain] = " << id << ".tag;\n";
+      rec << " " << fn << "_tag";
+      for (const Slot& s : L.slots) {
+        std::string nm = fn + "_" + s.name.substr(2);
+        if (s.type.k == Type::Vec) {
+          bool i32 = s.type.sub[0].k != Type::R;
+          fields.push_back({nm, i32, "0"}); fields.push_back({nm + "_len", true, "1"});
+          load << "  " << id << "." << s.name << " = " << (i32 ? "VecI" : "VecD") << "((" << (i32 ? "int" : "double") << "*)a.field[F_" << nm << "] + chain, a.n_chains, ((const int*)a.field[F_" << nm << "_len])[chain]);\n";
+          store << "  store_vec(" << id << "." << s.name << ", (" << (i32 ? "int" : "double") << "*)a.field[F_" << nm << "] + chain, a.n_chains, (int)a.flen[F_" << nm << "], (int*)a.field[F_" << nm << "_len] + chain);\n";
+        } else {
+          bool i32 = s.type.k != Type::R;
+          fields.push_back({nm, i32, "1"});
+          load << "  " << id << "." << s.name << " = ((const " << (i32 ? "int" : "double") << "*)a.field[F_" << nm << "])[chain];\n";
+          store << "  ((" << (i32 ? "int" : "double") << "*)a.field[F_" << nm << "])[chain] = " << id << "." << s.name << ";\n";
+          rec << " " << nm;
+        }
+      }
+      v.expr = id;
+    } else die("kernel input of type " + t.str() + " is not supported by the CUDA lowering");
+    g.bind(id, v); in_names.push_back(id);
+  }
+  // ---- the transition body ----
+  g.ind = 4;
+  g.body(prog);
+  if (kernel && prog.rets.size() != its.size()) die("a transition kernel must return as many values as it takes (t -> P t): " + std::to_string(its.size()) + " inputs, " + std::to_string(prog.rets.size()) + " returns");
+  std::ostringstream feed;
+  std::vector<Field> out_fields; std::ostringstream out_store;
+  for (size_t k = 0; k < prog.rets.size(); ++k) {
+    Type rt = g.type_of(prog.rets[k]);
+    if (kernel) {
+      if (!(rt == its[k]) && !(rt.integral() && its[k].integral())) die("return " + std::to_string(k) + " has type " + rt.str() + ", input has " + its[k].str());
+      std::string e = g.rv(prog.rets[k], its[k].k == Type::R);
+      std::string nx = "nx" + std::to_string(k);
+      g.line((its[k].k == Type::Union ? g.union_struct(its[k]) : Gen::ctype(its[k])) + " " + nx + " = " + e + ";");
+      if (its[k].k == Type::Vec) feed << "    assign_vec(" << in_names[k] << ", " << nx << ", (int)a.flen[F_in" << k << "]);\n";
+      else if (its[k].k == Type::Union) {
+        const UnionLayout& L = g.unions[its[k].str()];
+        feed << "    " << in_names[k] << ".tag = " << nx << ".tag;\n";
+        for (const Slot& s : L.slots) {
+          if (s.type.k == Type::Vec) feed << "    assign_vec(" << in_names[k] << "." << s.name << ", " << nx << "." << s.name << ", (int)a.flen[F_in" << k << "_" << s.name.substr(2) << "]);\n";
+          else feed << "    " << in_names[k] << "." << s.name << " = " << nx << "." << s.name << ";\n";
+        }
+      } else feed << "    " << in_names[k] << " = " << nx << ";\n";
+    } else {
+      std::string nm = "out" + std::to_string(k);
+      if (!rt.scalar()) die("simulate: return of type " + rt.str() + " is not supported");
+      out_fields.push_back({nm, rt.k != Type::R, "1"});
+      g.line("((" + std::string(rt.k != Type::R ? "int" : "double") + "*)a.field[F_" + nm + "])[chain] = " + g.rv(prog.rets[k], rt.k == Type::R) + ";");
+      rec << " " << nm;
+    }
+  }
+  for (auto& f : out_fields) fields.push_back(f);
+  if ((int)fields.size() > 24) die("too many state fields");
+
+  std::ostringstream o;
+  o << "// generated by stkc (libstk_cuda, Language.CUDA lowering) — do not edit\n";
+  o << "#define STK_VECCAP " << veccap << "\n";
+  o << "#include \"stk_device.cuh\"\nusing namespace stk;\n";
+  o << "enum {";
+  for (size_t i = 0; i < fields.size(); ++i) o << (i ? ", " : " ") << "F_" << fields[i].name << " = " << i;
+  o << " };\n";
+  for (auto& kv : g.union_cname) {
+    const UnionLayout& L = g.unions[kv.first];
+    o << "struct " << kv.second << " { int tag;";
+    for (const Slot& s : L.slots) o << " " << Gen::ctype(s.type) << " " << s.name << ";";
+    o << " };   // " << kv.first << "\n";
+  }
+  const char* sym = kernel ? "stk_ir_step" : "stk_ir_simulate";
+  o << "extern \"C\" __global__ void __launch_bounds__(" << block << ") " << sym << "(const __grid_constant__ StkArgs a) {\n";
+  o << "  const long long chain = (long long)blockIdx.x * blockDim.x + threadIdx.x;\n  if (chain >= a.n_chains) return;\n";
+  o << load.str() << g.decls.str();
+  if (kernel) {
+    o << "  for (long long t_ = 0; t_ < a.n_steps; ++t_) {\n";
+    o << "    Rng rng; rng.init(a.seed, (u64)(a.chain0 + chain), a.step0 + (u64)t_);\n";
+    o << g.out.str() << feed.str();
+    o << "  }\n" << store.str() << "}\n";
+  } else {
+    o << "  {\n    Rng rng; rng.init(a.seed, (u64)(a.chain0 + chain), ~0ULL);\n" << g.out.str() << "  }\n}\n";
+  }
+  o << "extern \"C\" __device__ const char stk_desc[] =\n  \"stk-module 1\\n\"\n  \"name " << name << "\\n\"\n  \"nparam 0\\n\"\n";
+  for (auto& f : fields) o << "  \"field " << f.name << " state " << (f.i32 ? "i32" : "f64") << " " << f.len << "\\n\"\n";
+  if (!rec.str().empty()) o << "  \"record" << rec.str() << "\\n\"\n";
+  if (kernel) o << "  \"kernel step " << sym << " " << block << " " << block << " 0 - 0\\n\";\n";
+  else o << "  \"entry simulate " << sym << " " << block << " " << block << " 0 - 0\\n\";\n";
+  return o.str();
+}
+
+}  // namespace stkc
+
+extern "C" int stk_set_error_(int code, const char* msg);   // stk_runtime.cpp
+
+extern "C" int stk_ir_to_cuda(const char* ir_text, const char* input_types, const char* options,
+                              char* out, size_t cap, size_t* needed) {
+  if (!ir_text) return stk_set_error_(STK_ERR_ARG, "null IR text");
+  try {
+    std::string s = stkc::generate(ir_text, input_types ? input_types : "", options);
+    if (needed) *needed = s.size() + 1;
+    if (!out || cap == 0) return STK_OK;
+    if (s.size() + 1 > cap) return stk_set_error_(STK_ERR_ARG, "output buffer too small");
+    memcpy(out, s.c_str(), s.size() + 1);
+    return STK_OK;
+  } catch (const stkc::Error& e) {
+    return stk_set_error_(STK_ERR_UNSUPPORTED, e.what());
+  } catch (const std::exception& e) {
+    return stk_set_error_(STK_ERR_ARG, e.what());
+  }
+}

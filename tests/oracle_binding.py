@@ -167,6 +167,16 @@ class Oracle:
         assert q.flags.c_contiguous and q.dtype == np.float64 and q.shape[0] == d + 2
         return self.l.orc_linreg_hmc_run(_p(X), _p(y), n, d, _p(q), q.shape[1], T, eps, L, seed, chain0, step0, nthreads)
 
+    def u01x2(self, seed, chain, step, slot):
+        a = D(); b = D()
+        self.l.orc_u01x2(seed, chain, step, slot, C.byref(a), C.byref(b))
+        return a.value, b.value
+
+    def normal2(self, seed, chain, step, slot):
+        a = D(); b = D()
+        self.l.orc_normal2(seed, chain, step, slot, C.byref(a), C.byref(b))
+        return a.value, b.value
+
     def philox(self, ctr, key):
         c = np.asarray(ctr, dtype=np.uint32); k = np.asarray(key, dtype=np.uint32); o = np.empty(4, dtype=np.uint32)
         self.l.orc_philox4x32_10(_p(c), _p(k), _p(o))

@@ -301,6 +301,433 @@ __device__ __forceinline__ void rj_body(const StkArgs& a) {
 
 }  // namespace
 
+// ---------------------------------------------------------------------------------------------------------
+// v2: `coal_rj1` — ONE lane per chain, built for the LATENCY of a transition (profiles/r01_coal_rj.md: with 4096
+// chains the kernel is bound by the dependent chain of one transition, throughput = chains / latency).
+//   * per-segment caches in shared memory, [row][lane]: s (upper boundary), F = s/t, cnt = #events below s,
+//     g, lg = log g, lw = log(F_i - F_{i-1}).  The joint density is head[n] + sum_i term_i with
+//       term_i = lw_i + (alb + am1 lg_i - b g_i) + ((cnt_i - cnt_{i-1}) lg_i - (s_i - s_{i-1}) g_i),
+//     and a move touches at most two segments: f(y) - f(x) is evaluated from the <= 2 new and <= 2 old terms (the
+//     reference re-evaluates all n+1 segments and 191 events twice per transition).  lp is re-summed in full when the
+//     state is stored, so the carried value cannot drift across launches.
+//   * one branch-free instruction stream for the four move types (32 different chains share a warp);
+//   * log g of a proposed rate is known in closed form (u + log g_j, z + log g_j), so the proposal needs ONE exp,
+//     at most two logs (segment widths) and one event-count lookup (bucket table + short scan), all independent;
+//   * accept test as log(uB) < log r — the final exp leaves the critical path — with log(uB), the Box-Muller normal
+//     and all Philox blocks of transition t+1 computed while transition t waits on its exp/log chains.
+// Same Philox layout and the same draws -> proposals as v1 and the oracle; results differ from the full
+// re-evaluation only by rounding (~1e-15 relative on log r).
+// ---------------------------------------------------------------------------------------------------------
+namespace {
+
+constexpr int NB = 256;               // buckets of the event-count table
+constexpr int R1 = 34;                // rows per chain: 0 .. 33
+constexpr int V2_SMEM_DOUBLES = 196 + TAB_DOUBLES + 5 * R1 * 32;   // y(+pad) | Tabs | s F g lg lw
+constexpr int V2_SMEM_BYTES = V2_SMEM_DOUBLES * 8 + R1 * 32 * 4 + (NB + 1) * 4;
+
+struct Draws { double uA, luB, uC, uD, z; };
+
+__device__ __forceinline__ Draws draw5(u64 seed, u64 gchain, u64 step) {
+  Rng rng; rng.init(seed, gchain, step);
+  Draws d; double uB, u1, u2;
+  rng.u01x2(d.uA, uB);
+  rng.u01x2(d.uC, d.uD);
+  rng.u01x2(u1, u2);                                  // block 2: Box-Muller, cosine branch (Rng::normal)
+  d.luB = log(uB);
+  double sn, cs; sincospi(2.0 * u2, &sn, &cs);
+  d.z = sqrt(-2.0 * log(u1)) * cs;
+  return d;
+}
+
+// #events strictly below v: bucket table start, then a short scan (y padded with +inf)
+__device__ __forceinline__ int count_below_tab(const double* __restrict__ y, const int* __restrict__ tab, int ny,
+                                               double v, double nb_over_t) {
+  int b = (int)(v * nb_over_t);
+  b = max(0, min(b, NB - 1));
+  int c = tab[b];
+  while (c > 0 && !(y[c - 1] < v)) --c;               // rounding of the bucket index (practically never taken)
+  int k = (int)(y[c] < v) + (int)(y[c + 1] < v) + (int)(y[c + 2] < v) + (int)(y[c + 3] < v);
+  c += k;
+  if (k == 4) while (c < ny && y[c] < v) ++c;
+  return c;
+}
+
+__device__ __forceinline__ double seg_term(double lw, double lg, double g, int dc, double ds, const Consts& k) {
+  return lw + ((k.alb + k.am1 * lg) - k.b * g) + ((double)dc * lg - ds * g);
+}
+
+}  // namespace
+
+extern "C" __global__ void __launch_bounds__(32) coal_rj1(const __grid_constant__ StkArgs a) {
+  extern __shared__ __align__(16) double smem[];
+  const int lane = threadIdx.x;
+  const int ny = (int)a.flen[F_Y];
+  double* ysm = smem;                                   // [ny + 4]
+  Tabs* T = reinterpret_cast<Tabs*>(smem + 196);
+  double* S = smem + 196 + TAB_DOUBLES;                 // [R1][32] each
+  double* Fc = S + R1 * 32; double* Gv = Fc + R1 * 32; double* LG = Gv + R1 * 32; double* LW = LG + R1 * 32;
+  int* CN = reinterpret_cast<int*>(LW + R1 * 32);       // [R1][32]
+  int* btab = CN + R1 * 32;                             // [NB + 1]
+  Consts k;
+  k.t = a.par[PAR_T]; k.a = a.par[PAR_A]; k.b = a.par[PAR_B]; k.ny = ny;
+  k.alb = k.a * log(k.b) - lgamma(k.a); k.am1 = k.a - 1.0;
+  const int lam = (int)a.par[PAR_LAM], nmax = min((int)a.par[PAR_NMAX], SMAX);
+  const double* Y = (const double*)a.field[F_Y];
+  for (int i = lane; i < ny + 4; i += 32) ysm[i] = i < ny ? Y[i] : pos_inf();
+  build_tabs(T, k.t, lam, nmax);
+  __syncwarp();
+  const double nb_over_t = (double)NB / k.t;
+  for (int b = lane; b <= NB; b += 32) btab[b] = count_below(ysm, ny, (double)b * (k.t / (double)NB));
+  __syncwarp();
+
+  const long long chain = (long long)blockIdx.x * 32 + lane;
+  const bool active = chain < a.n_chains;
+  const long long cidx = active ? chain : a.n_chains - 1;
+#define AT(A, i) A[(i) * 32 + lane]
+  int n = ((const int*)a.field[F_N])[cidx];
+  n = max(0, min(n, SMAX));
+  {
+    const double* Sg = (const double*)a.field[F_S];
+    const double* Gg = (const double*)a.field[F_G];
+    AT(S, 0) = 0.0; AT(Fc, 0) = 0.0; AT(CN, 0) = 0; AT(Gv, 0) = 0.0; AT(LG, 0) = 0.0; AT(LW, 0) = 0.0;
+    for (int i = 1; i < R1; ++i) {
+      const double si = i <= n ? Sg[(long long)(i - 1) * a.n_chains + cidx] : k.t;
+      const double gi = i <= n + 1 ? Gg[(long long)(i - 1) * a.n_chains + cidx] : 1.0;
+      const double Fi = si < 0.0 ? 0.0 : (si > k.t ? 1.0 : si / k.t);
+      AT(S, i) = si; AT(Fc, i) = Fi; AT(Gv, i) = gi; AT(LG, i) = log(gi);
+      AT(CN, i) = i <= n ? count_below(ysm, ny, si) : ny;
+      AT(LW, i) = log(Fi - AT(Fc, i - 1));
+    }
+  }
+  // full evaluation (same left-to-right order as the oracle's fold); also used when the state is stored
+  auto full_lp = [&](int nn) {
+    double acc = 0.0; bool bad = false;
+    for (int i = 1; i <= nn + 1; ++i) {
+      acc += seg_term(AT(LW, i), AT(LG, i), AT(Gv, i), AT(CN, i) - AT(CN, i - 1), AT(S, i) - AT(S, i - 1), k);
+      if (i <= nn && (AT(S, i) < 0.0 || k.t < AT(S, i))) bad = true;
+    }
+    return bad ? neg_inf() : acc + T->head[nn];
+  };
+  double lp = full_lp(n);
+  const double log_inv_t = log(1.0 / (k.t - 0.0));
+  const u64 gchain = (u64)(a.chain0 + cidx);
+  unsigned long long n_acc = 0;
+  Draws nx = draw5(a.seed, gchain, a.step0);
+
+  for (long long tr = 0; tr < a.n_steps; ++tr) {
+    const Draws d = nx;
+    nx = draw5(a.seed, gchain, a.step0 + (u64)tr + 1);   // independent of everything below: fills the stall slots
+    // ---- move type (pmf draw), index, birth position -------------------------------------------------
+    const double* pr = T->pr[n];
+    const double p0 = pr[0], p1 = pr[1], p2 = pr[2], p3 = pr[3];
+    const double ua = d.uA * (((p0 + p1) + p2) + p3);
+    const double c1 = p0, c2 = c1 + p1, c3 = c2 + p2;
+    const int move = ua < c1 ? 1 : (ua < c2 ? 2 : (ua < c3 ? 3 : 4));
+    const int m = max((move == 1) ? n + 1 : n, 1);
+    int j = (int)floor(d.uC * (double)m); if (j >= m) j = m - 1; j += 1;
+    const double x = 0.0 + (k.t - 0.0) * d.uD;
+    if (move == 3) {                                     // findSortedInsertIndex x s: first rank with x < s_i
+      int lo = 1, hi = n + 1;
+      while (lo < hi) { const int mid = (lo + hi) >> 1; if (x < AT(S, mid)) hi = mid; else lo = mid + 1; }
+      j = lo;
+    }
+    // ---- neighbourhood of rank j -----------------------------------------------------------------------
+    const double sm1 = AT(S, j - 1), s0 = AT(S, j), sp1 = AT(S, j + 1);
+    const double Fm1 = AT(Fc, j - 1), F0 = AT(Fc, j), Fp1 = AT(Fc, j + 1);
+    const int cm1 = AT(CN, j - 1), c0 = AT(CN, j), cp1 = AT(CN, j + 1);
+    const double g0 = AT(Gv, j), lg0 = AT(LG, j), lw0 = AT(LW, j);
+    const double g1 = AT(Gv, j + 1), lg1 = AT(LG, j + 1), lw1 = AT(LW, j + 1);
+    // ---- the proposal: one exp, one count, two logs, all independent -----------------------------------
+    const double u = -0.5 + (0.5 - (-0.5)) * d.uD;                        // coalMoveH
+    const double lgn = (move == 1 ? u : d.z) + lg0;                       // log of the proposed rate, closed form
+    const double E = exp(move == 1 ? lgn : d.z);
+    const double gn = move == 1 ? E : E * g0;                             // exp(u + log g_j)  |  exp(z) g_j
+    const double snew = move == 2 ? sm1 + (sp1 - sm1) * (0.0 + (1.0 - 0.0) * d.uD) : x;   // coalMoveP | birth point
+    const int cn = count_below_tab(ysm, btab, ny, snew, nb_over_t);
+    const double Fn = snew < 0.0 ? 0.0 : (snew > k.t ? 1.0 : snew / k.t);
+    const double hiA = move == 4 ? Fp1 : Fn;                              // segment A = (s_{j-1}, snew | s_{j+1})
+    const double hiB = move == 2 ? Fp1 : F0;                              // segment B = (snew, s_{j+1} | s_j)
+    const double wA = log(hiA - Fm1);
+    const double wB = log(hiB - Fn);
+    // ---- f(y) - f(x) from the touched segments ------------------------------------------------------------
+    const double old0 = seg_term(lw0, lg0, g0, c0 - cm1, s0 - sm1, k);
+    const double old1 = seg_term(lw1, lg1, g1, cp1 - c0, sp1 - s0, k);
+    double df, lq; int np = n;
+    if (move == 1) {
+      df = seg_term(lw0, lgn, gn, c0 - cm1, s0 - sm1, k) - old0;
+      lq = u;                                                             // log(g_j'/g_j)
+    } else if (move == 2) {
+      df = (seg_term(wA, lg0, g0, cn - cm1, snew - sm1, k) + seg_term(wB, lg1, g1, cp1 - cn, sp1 - snew, k)) - (old0 + old1);
+      lq = 0.0;
+    } else if (move == 3) {
+      np = n + 1;
+      df = ((seg_term(wA, lg0, g0, cn - cm1, snew - sm1, k) + seg_term(wB, lgn, gn, c0 - cn, s0 - snew, k)) - old0)
+           + (T->head[np] - T->head[n]);
+      const double lu_rev = T->lpr[np][3] + T->logdinv[np];
+      const double lu_fwd = (T->lpr[n][2] + log_inv_t) + (-kHalfLog2Pi - 0.5 * d.z * d.z);
+      lq = (lu_rev - lu_fwd) + lgn;                                       // + log g'_{j+1}
+    } else {
+      np = n - 1;
+      df = (seg_term(wA, lg0, g0, cp1 - cm1, sp1 - sm1, k) - (old0 + old1)) + (T->head[np] - T->head[n]);
+      const double zr = lg1 - lg0;                                        // log(g_{j+1}/g_j)
+      const double lu_rev = (T->lpr[np][2] + log_inv_t) + (-kHalfLog2Pi - 0.5 * zr * zr);
+      const double lu_fwd = T->lpr[n][3] + T->logdinv[n];
+      lq = (lu_rev - lu_fwd) - lg1;                                       // - log g_{j+1}
+    }
+    const double logr = df + lq;
+    const bool accept = d.luB < logr;                                     // uB < min(1, exp(log r))
+    // ---- commit ------------------------------------------------------------------------------------------
+    if (accept) {
+      if (move == 1) { AT(Gv, j) = gn; AT(LG, j) = lgn; }
+      else if (move == 2) { AT(S, j) = snew; AT(Fc, j) = Fn; AT(CN, j) = cn; AT(LW, j) = wA; AT(LW, j + 1) = wB; }
+      else if (move == 3) {
+        for (int i = n + 1; i >= j; --i) { AT(S, i + 1) = AT(S, i); AT(Fc, i + 1) = AT(Fc, i); AT(CN, i + 1) = AT(CN, i); }
+        for (int i = n + 1; i > j; --i) { AT(Gv, i + 1) = AT(Gv, i); AT(LG, i + 1) = AT(LG, i); AT(LW, i + 1) = AT(LW, i); }
+        AT(S, j) = snew; AT(Fc, j) = Fn; AT(CN, j) = cn; AT(LW, j) = wA;
+        AT(Gv, j + 1) = gn; AT(LG, j + 1) = lgn; AT(LW, j + 1) = wB;
+      } else {
+        for (int i = j; i <= n; ++i) { AT(S, i) = AT(S, i + 1); AT(Fc, i) = AT(Fc, i + 1); AT(CN, i) = AT(CN, i + 1); }
+        for (int i = j + 1; i <= n; ++i) { AT(Gv, i) = AT(Gv, i + 1); AT(LG, i) = AT(LG, i + 1); AT(LW, i) = AT(LW, i + 1); }
+        AT(LW, j) = wA;
+      }
+      n = np; lp += df; ++n_acc;
+    }
+    long long slot;
+    if (active && record_slot(a, tr, &slot)) {
+      record_value(a, slot, 0, chain, (double)n);
+      for (int i = 1; i <= SMAX + 1; ++i) {
+        if (i <= SMAX) record_value(a, slot, i, chain, i <= n ? AT(S, i) : 0.0);
+        record_value(a, slot, SMAX + i, chain, i <= n + 1 ? AT(Gv, i) : 0.0);
+      }
+    }
+  }
+  if (active) {
+    double* Sg = (double*)a.field[F_S];
+    double* Gg = (double*)a.field[F_G];
+    for (int i = 1; i <= SMAX + 1; ++i) {
+      if (i <= SMAX) Sg[(long long)(i - 1) * a.n_chains + chain] = i <= n ? AT(S, i) : 0.0;
+      Gg[(long long)(i - 1) * a.n_chains + chain] = i <= n + 1 ? AT(Gv, i) : 0.0;
+    }
+    ((int*)a.field[F_N])[chain] = n;
+    ((double*)a.field[F_LP])[chain] = full_lp(n);
+    if (a.accept) a.accept[chain] += n_acc;
+  }
+#undef AT
+}
+static_assert(V2_SMEM_BYTES == 53044, "V2_SMEM_BYTES");
+
+// ---------------------------------------------------------------------------------------------------------
+// v3: `coal_draws` + `coal_rj2<LPW>` — the state-independent half of a transition (3 Philox blocks, log uB, the
+// Box-Muller normal: ~600 of v2's ~1150 instructions) moves into a PRE-PASS kernel that runs one thread per
+// (chain, transition) at full occupancy and leaves [transition][5][chain] doubles in HBM; the sequential kernel
+// streams them back (coalesced, prefetched two transitions ahead) and keeps only the dependent chain:
+// select move -> neighbourhood (packed 16-byte rows) -> one exp | one count | two logs -> compare -> commit.
+// LPW = chains per warp: with 4096 chains the kernel is latency-bound whatever the packing, and fewer chains per
+// warp means fewer lanes to wait for in the divergent parts (rank search of a birth, row shifts of an accepted
+// birth/death).  Same draws -> proposals as v1/v2 and the oracle.
+// ---------------------------------------------------------------------------------------------------------
+extern "C" __global__ void __launch_bounds__(256) coal_draws(const __grid_constant__ StkArgs a) {
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= a.n_chains * a.n_steps) return;
+  const long long tr = idx / a.n_chains, c = idx - tr * a.n_chains;
+  const Draws d = draw5(a.seed, (u64)(a.chain0 + c), a.step0 + (u64)tr);
+  double* o = a.scratch + (tr * 5) * a.n_chains + c;
+  o[0] = d.uA; o[a.n_chains] = d.luB; o[2 * a.n_chains] = d.uC; o[3 * a.n_chains] = d.uD; o[4 * a.n_chains] = d.z;
+}
+
+namespace {
+
+struct Tabs2 { double birthC[32]; double deathC[32]; };   // per-n constants of log q ratios + head differences
+
+template <int LPW>
+__device__ __forceinline__ void rj2_body(const StkArgs& a) {
+  extern __shared__ __align__(16) double smem[];
+  const int lane = threadIdx.x;
+  const int ny = (int)a.flen[F_Y];
+  double* ysm = smem;                                   // [ny + 4]
+  Tabs* T = reinterpret_cast<Tabs*>(smem + 196);
+  Tabs2* T2 = reinterpret_cast<Tabs2*>(smem + 196 + TAB_DOUBLES);
+  double2* P = reinterpret_cast<double2*>(smem + 196 + TAB_DOUBLES + 64);   // [R1][LPW] (s, F)
+  double2* Q = P + R1 * LPW;                                                 // (g, log g)
+  double2* W = Q + R1 * LPW;                                                 // (log width, #events below s)
+  double* ring = reinterpret_cast<double*>(W + R1 * LPW);                    // [4][5][LPW] draws in flight
+  int* btab = reinterpret_cast<int*>(ring + 4 * 5 * LPW);                    // [NB + 1]
+  Consts k;
+  k.t = a.par[PAR_T]; k.a = a.par[PAR_A]; k.b = a.par[PAR_B]; k.ny = ny;
+  k.alb = k.a * log(k.b) - lgamma(k.a); k.am1 = k.a - 1.0;
+  const int lam = (int)a.par[PAR_LAM], nmax = min((int)a.par[PAR_NMAX], SMAX);
+  const double* Y = (const double*)a.field[F_Y];
+  for (int i = lane; i < ny + 4; i += 32) ysm[i] = i < ny ? Y[i] : pos_inf();
+  build_tabs(T, k.t, lam, nmax);
+  __syncwarp();
+  const double log_inv_t = log(1.0 / (k.t - 0.0));
+  {
+    const int n = lane;                                  // one n per lane
+    const int nu = min(n + 1, 31), nd = max(n - 1, 0);
+    T2->birthC[n] = ((T->lpr[nu][3] + T->logdinv[nu]) - ((T->lpr[n][2] + log_inv_t) - kHalfLog2Pi)) + (T->head[nu] - T->head[n]);
+    T2->deathC[n] = (((T->lpr[nd][2] + log_inv_t) - kHalfLog2Pi) - (T->lpr[n][3] + T->logdinv[n])) + (T->head[nd] - T->head[n]);
+  }
+  const double nb_over_t = (double)NB / k.t;
+  for (int b = lane; b <= NB; b += 32) btab[b] = count_below(ysm, ny, (double)b * (k.t / (double)NB));
+  __syncwarp();
+  if (lane >= LPW) return;
+
+  const long long chain = (long long)blockIdx.x * LPW + lane;
+  const bool active = chain < a.n_chains;
+  const long long cidx = active ? chain : a.n_chains - 1;
+#define ROW(A, i) A[(i) * LPW + lane]
+  int n = ((const int*)a.field[F_N])[cidx];
+  n = max(0, min(n, SMAX));
+  {
+    const double* Sg = (const double*)a.field[F_S];
+    const double* Gg = (const double*)a.field[F_G];
+    ROW(P, 0) = make_double2(0.0, 0.0); ROW(Q, 0) = make_double2(0.0, 0.0); ROW(W, 0) = make_double2(0.0, 0.0);
+    double Fprev = 0.0;
+    for (int i = 1; i < R1; ++i) {
+      const double si = i <= n ? Sg[(long long)(i - 1) * a.n_chains + cidx] : k.t;
+      const double gi = i <= n + 1 ? Gg[(long long)(i - 1) * a.n_chains + cidx] : 1.0;
+      const double Fi = si < 0.0 ? 0.0 : (si > k.t ? 1.0 : si / k.t);
+      ROW(P, i) = make_double2(si, Fi); ROW(Q, i) = make_double2(gi, log(gi));
+      ROW(W, i) = make_double2(log(Fi - Fprev), (double)(i <= n ? count_below(ysm, ny, si) : ny));
+      Fprev = Fi;
+    }
+  }
+  auto full_lp = [&](int nn) {
+    double acc = 0.0; bool bad = false;
+    for (int i = 1; i <= nn + 1; ++i) {
+      const double2 p1 = ROW(P, i), p0 = ROW(P, i - 1), q = ROW(Q, i), w1 = ROW(W, i), w0 = ROW(W, i - 1);
+      acc += w1.x + ((k.alb + k.am1 * q.y) - k.b * q.x) + ((w1.y - w0.y) * q.y - (p1.x - p0.x) * q.x);
+      if (i <= nn && (p1.x < 0.0 || k.t < p1.x)) bad = true;
+    }
+    return bad ? neg_inf() : acc + T->head[nn];
+  };
+  double lp = full_lp(n);
+  unsigned long long n_acc = 0;
+  // draws of this chain: [tr][5][n_chains] in HBM -> a 4-deep cp.async ring in shared memory (three transitions in
+  // flight; a register FIFO would be rotated by the compiler right behind the loads and wait for them)
+  const double* D = a.scratch + cidx;
+  const long long NC = a.n_chains;
+  const unsigned ring_base = (unsigned)__cvta_generic_to_shared(ring + lane);
+  auto fetch = [&](long long tr) {
+    if (tr < a.n_steps) {
+      const double* p = D + tr * 5 * NC;
+      const unsigned dst = ring_base + (unsigned)((tr & 3) * 5 * LPW * 8);
+#pragma unroll
+      for (int q = 0; q < 5; ++q)
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst + q * LPW * 8), "l"(p + q * NC) : "memory");
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  fetch(0); fetch(1); fetch(2);
+
+  for (long long tr = 0; tr < a.n_steps; ++tr) {
+    fetch(tr + 3);
+    asm volatile("cp.async.wait_group 3;" ::: "memory");
+    const double* dr = ring + (tr & 3) * 5 * LPW + lane;
+    const double uA = dr[0], luB = dr[LPW], uC = dr[2 * LPW], uD = dr[3 * LPW], z = dr[4 * LPW];
+    // ---- move type (pmf draw), index, birth position -------------------------------------------------
+    const double2 pa = *reinterpret_cast<const double2*>(&T->pr[n][0]), pb = *reinterpret_cast<const double2*>(&T->pr[n][2]);
+    const double ua = uA * (((pa.x + pa.y) + pb.x) + pb.y);
+    const double c1 = pa.x, c2 = c1 + pa.y, c3 = c2 + pb.x;
+    const int move = ua < c1 ? 1 : (ua < c2 ? 2 : (ua < c3 ? 3 : 4));
+    const int m = max((move == 1) ? n + 1 : n, 1);
+    int j = (int)(uC * (double)m); if (j >= m) j = m - 1; j += 1;
+    const double x = 0.0 + (k.t - 0.0) * uD;
+    if (move == 3) {                                     // findSortedInsertIndex x s: first rank with x < s_i
+      int lo = 1, hi = n + 1;
+      while (lo < hi) { const int mid = (lo + hi) >> 1; if (x < ROW(P, mid).x) hi = mid; else lo = mid + 1; }
+      j = lo;
+    }
+    // ---- neighbourhood of rank j -----------------------------------------------------------------------
+    const double2 Pm1 = ROW(P, j - 1), P0 = ROW(P, j), Pp1 = ROW(P, j + 1);
+    const double2 Q0 = ROW(Q, j), Q1 = ROW(Q, j + 1);
+    const double2 Wm1 = ROW(W, j - 1), W0 = ROW(W, j), W1 = ROW(W, j + 1);
+    const double bC = T2->birthC[n], dC = T2->deathC[n];
+    const double sm1 = Pm1.x, s0 = P0.x, sp1 = Pp1.x, Fm1 = Pm1.y, F0 = P0.y, Fp1 = Pp1.y;
+    const double g0 = Q0.x, lg0 = Q0.y, g1 = Q1.x, lg1 = Q1.y;
+    const double cm1 = Wm1.y, c0 = W0.y, cp1 = W1.y, lw0 = W0.x, lw1 = W1.x;
+    // ---- the proposal: one exp, one count, two logs, all independent -----------------------------------
+    const bool m1 = move == 1, m2 = move == 2, m3 = move == 3, m4 = move == 4;
+    const double u = -0.5 + (0.5 - (-0.5)) * uD;                          // coalMoveH
+    const double lgn = (m1 ? u : z) + lg0;                                // log of the proposed rate, closed form
+    const double E = exp(m1 ? lgn : z);
+    const double gn = m1 ? E : E * g0;                                    // exp(u + log g_j)  |  exp(z) g_j
+    const double snew = m2 ? sm1 + (sp1 - sm1) * (0.0 + (1.0 - 0.0) * uD) : x;   // coalMoveP | birth point
+    const double cn = (double)count_below_tab(ysm, btab, ny, snew, nb_over_t);
+    const double Fn = snew < 0.0 ? 0.0 : (snew > k.t ? 1.0 : snew / k.t);
+    const double wA = log((m4 ? Fp1 : Fn) - Fm1);                         // segment A = (s_{j-1}, snew | s_{j+1})
+    const double wB = log((m2 ? Fp1 : F0) - Fn);                          // segment B = (snew, s_{j+1} | s_j)
+    // ---- f(y) - f(x) from the touched segments (selects, no branches) ----------------------------------
+    const double old0 = seg_term(lw0, lg0, g0, 0, 0.0, k) + ((c0 - cm1) * lg0 - (s0 - sm1) * g0);
+    const double old1 = seg_term(lw1, lg1, g1, 0, 0.0, k) + ((cp1 - c0) * lg1 - (sp1 - s0) * g1);
+    const double hiA = m1 ? s0 : (m4 ? sp1 : snew), chA = m1 ? c0 : (m4 ? cp1 : cn);
+    const double lgA = m1 ? lgn : lg0, gA = m1 ? gn : g0, lwA = m1 ? lw0 : wA;
+    const double tA = seg_term(lwA, lgA, gA, 0, 0.0, k) + ((chA - cm1) * lgA - (hiA - sm1) * gA);
+    const double hiB = m2 ? sp1 : s0, chB = m2 ? cp1 : c0, lgB = m2 ? lg1 : lgn, gB = m2 ? g1 : gn;
+    const double tB = (m2 || m3) ? seg_term(wB, lgB, gB, 0, 0.0, k) + ((chB - cn) * lgB - (hiB - snew) * gB) : 0.0;
+    const double told = (m2 || m4) ? old0 + old1 : old0;
+    const double zr = lg1 - lg0;                                          // log(g_{j+1}/g_j), death
+    const double extra = m1 ? u : (m2 ? 0.0 : (m3 ? (bC + 0.5 * z * z) + lgn : (dC - 0.5 * zr * zr) - lg1));
+    const double df = (tA + tB) - told;                                   // without the head difference (in bC/dC)
+    const double logr = df + extra;
+    const bool accept = luB < logr;                                       // uB < min(1, exp(log r))
+    // ---- commit ------------------------------------------------------------------------------------------
+    if (accept) {
+      if (m1) ROW(Q, j) = make_double2(gn, lgn);
+      else if (m2) { ROW(P, j) = make_double2(snew, Fn); ROW(W, j) = make_double2(wA, cn); ROW(W, j + 1) = make_double2(wB, cp1); }
+      else if (m3) {
+        for (int i = n + 1; i >= j; --i) {               // rows j.. move up; row j is then re-written
+          const double2 p = ROW(P, i), q = ROW(Q, i), w = ROW(W, i);
+          ROW(P, i + 1) = p; ROW(Q, i + 1) = q; ROW(W, i + 1) = w;
+        }
+        ROW(P, j) = make_double2(snew, Fn); ROW(W, j) = make_double2(wA, cn);
+        ROW(Q, j + 1) = make_double2(gn, lgn); ROW(W, j + 1) = make_double2(wB, c0);
+        ++n;
+      } else {
+        for (int i = j; i <= n; ++i) {                   // rows j+1.. move down; row j keeps its rate, new width
+          const double2 p = ROW(P, i + 1), q = ROW(Q, i + 1), w = ROW(W, i + 1);
+          ROW(P, i) = p; ROW(Q, i) = q; ROW(W, i) = w;
+        }
+        ROW(Q, j) = make_double2(g0, lg0); ROW(W, j) = make_double2(wA, cp1);
+        --n;
+      }
+      lp += df + (m3 ? T->head[n] - T->head[n - 1] : (m4 ? T->head[n] - T->head[n + 1] : 0.0));
+      ++n_acc;
+    }
+    long long slot;
+    if (active && record_slot(a, tr, &slot)) {
+      record_value(a, slot, 0, chain, (double)n);
+      for (int i = 1; i <= SMAX + 1; ++i) {
+        if (i <= SMAX) record_value(a, slot, i, chain, i <= n ? ROW(P, i).x : 0.0);
+        record_value(a, slot, SMAX + i, chain, i <= n + 1 ? ROW(Q, i).x : 0.0);
+      }
+    }
+  }
+  if (active) {
+    double* Sg = (double*)a.field[F_S];
+    double* Gg = (double*)a.field[F_G];
+    for (int i = 1; i <= SMAX + 1; ++i) {
+      if (i <= SMAX) Sg[(long long)(i - 1) * a.n_chains + chain] = i <= n ? ROW(P, i).x : 0.0;
+      Gg[(long long)(i - 1) * a.n_chains + chain] = i <= n + 1 ? ROW(Q, i).x : 0.0;
+    }
+    ((int*)a.field[F_N])[chain] = n;
+    ((double*)a.field[F_LP])[chain] = full_lp(n);
+    if (a.accept) a.accept[chain] += n_acc;
+  }
+#undef ROW
+}
+
+// smem: (196 + TAB_DOUBLES + 64) doubles + 3 arrays of R1*LPW double2 + (NB+1) ints
+constexpr int rj2_smem(int lpw) { return (196 + TAB_DOUBLES + 64) * 8 + 3 * R1 * lpw * 16 + 20 * lpw * 8 + (NB + 1) * 4; }
+static_assert(rj2_smem(8) == 20020 && rj2_smem(4) == 12852 && rj2_smem(16) == 34356 && rj2_smem(32) == 63028, "rj2 smem");
+
+}  // namespace
+
+extern "C" __global__ void __launch_bounds__(32) coal_rj2_8(const __grid_constant__ StkArgs a) { rj2_body<8>(a); }
+extern "C" __global__ void __launch_bounds__(32) coal_rj2_4(const __grid_constant__ StkArgs a) { rj2_body<4>(a); }
+extern "C" __global__ void __launch_bounds__(32) coal_rj2_16(const __grid_constant__ StkArgs a) { rj2_body<16>(a); }
+extern "C" __global__ void __launch_bounds__(32) coal_rj2_32(const __grid_constant__ StkArgs a) { rj2_body<32>(a); }
+
 // G = 8 lanes per chain is the default (`rj`): at 4096 chains per GPU it is the best trade between lanes that idle
 // when n+1 < G and warps per scheduler (B200: G=32 874 M, G=16 1168 M, G=8 1285 M, G=4 1000 M transitions/s;
 // profiles/r01_coal_rj.md).
@@ -373,6 +800,11 @@ extern "C" __device__ const char stk_desc[] =
     "param b 200\n"
     "record n s g\n"
     "kernel rj coal_rj8 128 16 10784 y 8\n"
+    "kernel rj1 coal_rj1 32 32 53044 - 0\n"
+    "kernel rj2 coal_rj2_8 32 8 20020 - 0 pre coal_draws 256 5\n"
+    "kernel rj2x4 coal_rj2_4 32 4 12852 - 0 pre coal_draws 256 5\n"
+    "kernel rj2x16 coal_rj2_16 32 16 34356 - 0 pre coal_draws 256 5\n"
+    "kernel rj2x32 coal_rj2_32 32 32 63028 - 0 pre coal_draws 256 5\n"
     "kernel rj32 coal_rj32 128 4 4640 y 8\n"
     "kernel rj16 coal_rj16 128 8 6688 y 8\n"
     "kernel rj4 coal_rj4 128 32 18976 y 8\n"

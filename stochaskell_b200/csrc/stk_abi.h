@@ -17,7 +17,11 @@
  *   param  <name> <default>          scalar tunable -> StkArgs.par[i]
  *   record <field> ...               fields (as doubles) that make up a draw
  *   kernel <name> <symbol> <block> <chains_per_block> <smem_fixed> <smem_field|-> <smem_bytes_per_elem>
- *          transition kernels, kernel_id = order of appearance
+ *          [pre <symbol> <block> <doubles_per_chain_transition>]
+ *          transition kernels, kernel_id = order of appearance.  `pre` names a pre-pass kernel that the runtime
+ *          launches first, one thread per (chain, transition) of the launch, to fill StkArgs.scratch
+ *          [transition][k][chain] (k < doubles_per_chain_transition) — the state-independent part of a transition
+ *          (its random draws) computed at full occupancy instead of inside the sequential chain loop.
  *   entry  <logp|logp_grad|simulate> <symbol> <block> <chains_per_block> <smem_fixed> <smem_field|-> <smem_bytes_per_elem>
  * Launch geometry: grid = ceil(n_chains / chains_per_block) CTAs of <block>
  * threads, dynamic smem = smem_fixed + flen[smem_field] * bytes_per_elem.
@@ -48,6 +52,7 @@ struct StkArgs {
   double* out_lp;              /* [n_chains]   (logp / logp_grad entries)     */
   double* out_grad;            /* [P][n_chains]                               */
   unsigned long long* accept;  /* [n_chains] accepted-transition counters     */
+  double* scratch;             /* pre-pass output [n_steps][k][n_chains], or NULL */
 };
 
 #endif /* STK_ABI_H */

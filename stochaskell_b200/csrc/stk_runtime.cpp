@@ -131,6 +131,7 @@ struct KernelDesc {
   std::string name, symbol;
   int block = 0, cpb = 1; long long smem_fixed = 0; std::string smem_field; long long smem_per = 0;
   cudaKernel_t k = nullptr;
+  std::string pre_symbol; int pre_block = 0; long long pre_per = 0; cudaKernel_t pre_k = nullptr;
 };
 
 }  // namespace
@@ -163,6 +164,7 @@ struct stk_chains {
   double* draws = nullptr; long long slots = 0, thin = 1, recorded = 0, nrec = 0;
   double* out_lp = nullptr; double* out_grad = nullptr;
   unsigned long long* accept = nullptr;
+  double* scratch = nullptr; size_t scratch_bytes = 0;
 };
 
 namespace {
@@ -176,6 +178,11 @@ int parse_kernel_line(std::istringstream& ls, KernelDesc* k) {
   std::string sf;
   if (!(ls >> k->name >> k->symbol >> k->block >> k->cpb >> k->smem_fixed >> sf >> k->smem_per)) return -1;
   k->smem_field = (sf == "-") ? "" : sf;
+  std::string opt;
+  while (ls >> opt) {
+    if (opt == "pre") { if (!(ls >> k->pre_symbol >> k->pre_block >> k->pre_per) || k->pre_block <= 0 || k->pre_per <= 0) return -1; }
+    else return -1;
+  }
   return 0;
 }
 
@@ -254,7 +261,15 @@ int launch(stk_chains* c, KernelDesc& k, long long n_steps, cudaStream_t st) {
   for (size_t f = 0; f < m->fields.size(); ++f) { a.field[f] = c->dptr[f]; a.flen[f] = c->flen[f]; }
   for (size_t p = 0; p < c->par.size(); ++p) a.par[p] = c->par[p];
   a.draws = c->draws; a.draw_slots = c->slots; a.draw_thin = c->thin; a.draw_base = c->recorded; a.n_rec = c->nrec;
-  a.out_lp = c->out_lp; a.out_grad = c->out_grad; a.accept = c->accept;
+  a.out_lp = c->out_lp; a.out_grad = c->out_grad; a.accept = c->accept; a.scratch = c->scratch;
+  if (k.pre_k) {   // pre-pass: one thread per (chain, transition) of this launch
+    long long items = c->n * n_steps;
+    long long pgrid = (items + k.pre_block - 1) / k.pre_block;
+    void* pparams[1] = {&a};
+    TRACE("launch pre %s grid=%lld block=%d", k.pre_symbol.c_str(), pgrid, k.pre_block);
+    CU(cudaLaunchKernel((const void*)k.pre_k, dim3((unsigned)pgrid), dim3((unsigned)k.pre_block), pparams, 0, st));
+    g_launches.fetch_add(1);
+  }
   long long smem = k.smem_fixed;
   if (!k.smem_field.empty()) {
     int f = field_index(m, k.smem_field);
@@ -407,6 +422,10 @@ int stk_module_load(stk_ctx* ctx, const char* spec, const char* cache_dir, stk_m
     TRACE("resolve %s", k.symbol.c_str());
     cudaError_t e3 = cudaLibraryGetKernel(&k.k, m->lib, k.symbol.c_str());
     if (e3 != cudaSuccess) return fail(STK_ERR_ARG, "module %s: kernel symbol %s: %s", m->name.c_str(), k.symbol.c_str(), cudaGetErrorString(e3));
+    if (!k.pre_symbol.empty()) {
+      e3 = cudaLibraryGetKernel(&k.pre_k, m->lib, k.pre_symbol.c_str());
+      if (e3 != cudaSuccess) return fail(STK_ERR_ARG, "module %s: pre-pass symbol %s: %s", m->name.c_str(), k.pre_symbol.c_str(), cudaGetErrorString(e3));
+    }
     return STK_OK;
   };
   for (auto& k : m->kernels) if ((rc = resolve(k))) { cudaLibraryUnload(m->lib); delete m; return rc; }
@@ -474,6 +493,7 @@ int stk_chains_destroy(stk_chains* c) {
   if (c->out_lp) cudaFree(c->out_lp);
   if (c->out_grad) cudaFree(c->out_grad);
   if (c->accept) cudaFree(c->accept);
+  if (c->scratch) cudaFree(c->scratch);
   delete c;
   return STK_OK;
 }
@@ -618,14 +638,33 @@ int stk_step(stk_chains* c, int kernel_id, int64_t n_transitions, stk_stream str
   int rc = need_device(c->mod->ctx);
   if (rc) return rc;
   cudaStream_t st = stream ? (cudaStream_t)stream : c->mod->ctx->stream;
-  rc = launch(c, c->mod->kernels[kernel_id], n_transitions, st);
-  if (rc) return rc;
-  if (c->draws && c->slots > 0) {
-    unsigned long long a = c->step, b = c->step + (unsigned long long)n_transitions;
-    long long add = (long long)(b / (unsigned long long)c->thin - a / (unsigned long long)c->thin);
-    c->recorded = std::min(c->slots, c->recorded + add);
+  KernelDesc& kd = c->mod->kernels[kernel_id];
+  // a kernel with a pre-pass runs in chunks whose scratch ([transitions][k][chains] doubles) fits the budget
+  long long chunk = n_transitions;
+  if (kd.pre_k) {
+    size_t per_tr = sizeof(double) * (size_t)kd.pre_per * (size_t)c->n;
+    size_t budget = (size_t)512 << 20;
+    if (const char* mb = getenv("STK_SCRATCH_MB")) budget = (size_t)std::max(1, atoi(mb)) << 20;
+    chunk = std::max<long long>(1, std::min<long long>(n_transitions, (long long)(budget / per_tr)));
+    size_t need = per_tr * (size_t)chunk;
+    if (need > c->scratch_bytes) {
+      CU(cudaStreamSynchronize(st));
+      if (c->scratch) { CU(cudaFree(c->scratch)); c->scratch = nullptr; c->scratch_bytes = 0; }
+      CU(cudaMalloc((void**)&c->scratch, need));
+      c->scratch_bytes = need;
+    }
   }
-  c->step += (unsigned long long)n_transitions;
+  for (long long done = 0; done < n_transitions; done += chunk) {
+    long long nt = std::min(chunk, n_transitions - done);
+    rc = launch(c, kd, nt, st);
+    if (rc) return rc;
+    if (c->draws && c->slots > 0) {
+      unsigned long long a = c->step, b = c->step + (unsigned long long)nt;
+      long long add = (long long)(b / (unsigned long long)c->thin - a / (unsigned long long)c->thin);
+      c->recorded = std::min(c->slots, c->recorded + add);
+    }
+    c->step += (unsigned long long)nt;
+  }
   return STK_OK;
 }
 

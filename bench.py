@@ -54,7 +54,7 @@ class ClockSampler(threading.Thread):
     def run(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             for line in self.proc.stdout:
                 self.rows.append([t.strip() for t in line.split(",")])
@@ -123,7 +123,7 @@ class CoalRJ:
     name = "coal_rj"
     module = "builtin:coal"
     kernel = "rj"
-    symbol = "coal_rj8"
+    symbol = "coal_rj2_4"
     dtype = "f64"
     transitions_per_step = 2000
     burnin = 4000
@@ -132,8 +132,13 @@ class CoalRJ:
     state_fields = ("n", "s", "g")
     # state read+write 2*492 B + one pass over y (191*8 B) per transition
     bytes_per_transition = 2 * 492 + 1528
-    roofline_note = ("latency/issue-bound kernel: chain state and y live in shared memory for the whole launch, "
-                     "so the algorithmic bytes (2,512 B/transition, SURVEY 8d) are not DRAM traffic")
+    # ncu (profiles/r01_coal_rj.md): dram read+write of coal_rj2_4 per launch of 4096 chains x 2000 transitions
+    ncu_traffic_bytes = 525034496 + 4091904
+    roofline_note = ("latency-bound kernel (one warp per scheduler, 4.95 cycles per issued instruction): the chain state "
+                     "lives in shared memory for the whole launch and a move re-evaluates only the <= 2 segments it "
+                     "touches, so the SURVEY 8d accounting unit (2,512 algorithmic B/transition = full state r/w + a pass "
+                     "over y) over-counts what the kernel does and `frac` can exceed 1; physical DRAM traffic (`traffic`) is "
+                     "64 B/transition of pre-generated draws = 3.5% of the HBM peak")
 
     def __init__(self):
         from stochaskell_b200.fixtures import COAL_T, coal_days
@@ -184,6 +189,16 @@ def cpu_arm(wl, orc, C, T, steps, warmup, nthreads):
     return C * T * steps / dt, dt
 
 
+def calibrate(wl, orc, st, nt):
+    """seconds per transition (of the whole chain batch) from pilots that last at least 0.3 s"""
+    T = 4
+    while True:
+        t0 = time.perf_counter(); wl.cpu_run(orc, st, T, 1, 0, 0, nt); dt = time.perf_counter() - t0
+        if dt >= 0.3 or T >= (1 << 24):
+            return dt / T
+        T *= 8
+
+
 def host_threads():
     try:
         return max(1, len(os.sched_getaffinity(0)))
@@ -200,10 +215,9 @@ def reference_arm(args, wl):
     C = 2 * nt
     # calibrate so that the whole run (steps + warmup) stays within ~2 minutes
     st = wl.init_state(C, 0)
-    t0 = time.perf_counter(); wl.cpu_run(orc, st, 4, 1, 0, 0, nt); dt = time.perf_counter() - t0
-    per_tr = dt / 4
+    per_tr = calibrate(wl, orc, st, nt)
     budget = 90.0 / max(1, args.steps + args.warmup)
-    T = int(max(1, min(args.transitions, budget / max(per_tr, 1e-9))))
+    T = int(max(1, min(50000000, budget / max(per_tr, 1e-12))))   # a bounded sample: ~90 s for the whole run
     for w in range(args.warmup):
         wl.cpu_run(orc, st, T, 1, 0, 10 + w * T, nt)
     t0 = time.perf_counter()
@@ -355,8 +369,8 @@ def run_native(args, wl, rank, world, local, torch, dist):
         nt = host_threads()
         Cs = 2 * nt
         stc = wl.init_state(Cs, 0)
-        t0 = time.perf_counter(); wl.cpu_run(orc, stc, 4, 1, 0, 0, nt); per_tr = (time.perf_counter() - t0) / 4
-        Ts = int(max(1, min(1000000, 12.0 / max(per_tr, 1e-9))))
+        per_tr = calibrate(wl, orc, stc, nt)
+        Ts = int(max(1, min(50000000, 12.0 / max(per_tr, 1e-12))))
         v, dt = cpu_arm(wl, orc, Cs, Ts, 1, 0, nt)
         cpu = dict(value=v, unit=UNIT, cores=nt, kind=wl_kind(wl),
                    sample=f"{Cs} chains x {Ts} transitions of the same workload on {nt} host threads ({dt:.1f} s)")

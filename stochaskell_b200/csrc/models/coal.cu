@@ -31,6 +31,7 @@
 //   block 1 -> (uC, uD): index j (discreteUniform), continuous uniform (u / x)
 //   block 2 -> z ~ normal(0,1) for the birth move
 #include "../stk_device.cuh"
+#include "../stk_fastmath.cuh"
 
 using namespace stk;
 
@@ -531,8 +532,14 @@ extern "C" __global__ void __launch_bounds__(256) coal_draws(const __grid_consta
   if (idx >= a.n_chains * a.n_steps) return;
   const long long tr = idx / a.n_chains, c = idx - tr * a.n_chains;
   const Draws d = draw5(a.seed, (u64)(a.chain0 + c), a.step0 + (u64)tr);
-  double* o = a.scratch + (tr * 5) * a.n_chains + c;
-  o[0] = d.uA; o[a.n_chains] = d.luB; o[2 * a.n_chains] = d.uC; o[3 * a.n_chains] = d.uD; o[4 * a.n_chains] = d.z;
+  // [transition][chain][8]: everything about the transition that does not depend on the chain's state, including
+  // the two exps of the rate proposals (g' = exp(u) g_j for the rate move, exp(z) g_j for a birth)
+  double2* o = reinterpret_cast<double2*>(a.scratch) + (tr * a.n_chains + c) * 4;
+  const double u = -0.5 + (0.5 - (-0.5)) * d.uD;
+  o[0] = make_double2(d.uA, d.luB);
+  o[1] = make_double2(d.uC, d.uD);
+  o[2] = make_double2(d.z, 0.5 * d.z * d.z);
+  o[3] = make_double2(exp(u), exp(d.z));
 }
 
 namespace {
@@ -547,11 +554,12 @@ __device__ __forceinline__ void rj2_body(const StkArgs& a) {
   double* ysm = smem;                                   // [ny + 4]
   Tabs* T = reinterpret_cast<Tabs*>(smem + 196);
   Tabs2* T2 = reinterpret_cast<Tabs2*>(smem + 196 + TAB_DOUBLES);
-  double2* P = reinterpret_cast<double2*>(smem + 196 + TAB_DOUBLES + 64);   // [R1][LPW] (s, F)
+  double* fm = smem + 196 + TAB_DOUBLES + 64;           // fast exp/log tables (stk_fastmath.cuh)
+  double2* P = reinterpret_cast<double2*>(fm + kFmTableDoubles);             // [R1][LPW] (s, #events below s)
   double2* Q = P + R1 * LPW;                                                 // (g, log g)
-  double2* W = Q + R1 * LPW;                                                 // (log width, #events below s)
-  double* ring = reinterpret_cast<double*>(W + R1 * LPW);                    // [4][5][LPW] draws in flight
-  int* btab = reinterpret_cast<int*>(ring + 4 * 5 * LPW);                    // [NB + 1]
+  double* LW = reinterpret_cast<double*>(Q + R1 * LPW);                      // log((s_i - s_{i-1}) / t)
+  double2* ring = reinterpret_cast<double2*>(LW + R1 * LPW + ((R1 * LPW) & 1));   // [4][LPW][4] double2: draws in flight
+  int* btab = reinterpret_cast<int*>(ring + 4 * LPW * 4);                    // [NB + 1]
   Consts k;
   k.t = a.par[PAR_T]; k.a = a.par[PAR_A]; k.b = a.par[PAR_B]; k.ny = ny;
   k.alb = k.a * log(k.b) - lgamma(k.a); k.am1 = k.a - 1.0;
@@ -559,8 +567,10 @@ __device__ __forceinline__ void rj2_body(const StkArgs& a) {
   const double* Y = (const double*)a.field[F_Y];
   for (int i = lane; i < ny + 4; i += 32) ysm[i] = i < ny ? Y[i] : pos_inf();
   build_tabs(T, k.t, lam, nmax);
+  fm_build_tables(fm, lane, 32);
   __syncwarp();
   const double log_inv_t = log(1.0 / (k.t - 0.0));
+  const double inv_t = 1.0 / k.t;
   {
     const int n = lane;                                  // one n per lane
     const int nu = min(n + 1, 31), nd = max(n - 1, 0);
@@ -581,50 +591,52 @@ __device__ __forceinline__ void rj2_body(const StkArgs& a) {
   {
     const double* Sg = (const double*)a.field[F_S];
     const double* Gg = (const double*)a.field[F_G];
-    ROW(P, 0) = make_double2(0.0, 0.0); ROW(Q, 0) = make_double2(0.0, 0.0); ROW(W, 0) = make_double2(0.0, 0.0);
-    double Fprev = 0.0;
+    ROW(P, 0) = make_double2(0.0, 0.0); ROW(Q, 0) = make_double2(0.0, 0.0); ROW(LW, 0) = 0.0;
+    double sprev = 0.0;
     for (int i = 1; i < R1; ++i) {
       const double si = i <= n ? Sg[(long long)(i - 1) * a.n_chains + cidx] : k.t;
       const double gi = i <= n + 1 ? Gg[(long long)(i - 1) * a.n_chains + cidx] : 1.0;
-      const double Fi = si < 0.0 ? 0.0 : (si > k.t ? 1.0 : si / k.t);
-      ROW(P, i) = make_double2(si, Fi); ROW(Q, i) = make_double2(gi, log(gi));
-      ROW(W, i) = make_double2(log(Fi - Fprev), (double)(i <= n ? count_below(ysm, ny, si) : ny));
-      Fprev = Fi;
+      ROW(P, i) = make_double2(si, (double)(i <= n ? count_below(ysm, ny, si) : ny));
+      ROW(Q, i) = make_double2(gi, log(gi));
+      ROW(LW, i) = log((si - sprev) * inv_t);
+      sprev = si;
     }
   }
   auto full_lp = [&](int nn) {
     double acc = 0.0; bool bad = false;
     for (int i = 1; i <= nn + 1; ++i) {
-      const double2 p1 = ROW(P, i), p0 = ROW(P, i - 1), q = ROW(Q, i), w1 = ROW(W, i), w0 = ROW(W, i - 1);
-      acc += w1.x + ((k.alb + k.am1 * q.y) - k.b * q.x) + ((w1.y - w0.y) * q.y - (p1.x - p0.x) * q.x);
+      const double2 p1 = ROW(P, i), p0 = ROW(P, i - 1), q = ROW(Q, i);
+      acc += ROW(LW, i) + ((k.alb + k.am1 * q.y) - k.b * q.x) + ((p1.y - p0.y) * q.y - (p1.x - p0.x) * q.x);
       if (i <= nn && (p1.x < 0.0 || k.t < p1.x)) bad = true;
     }
     return bad ? neg_inf() : acc + T->head[nn];
   };
   double lp = full_lp(n);
   unsigned long long n_acc = 0;
-  // draws of this chain: [tr][5][n_chains] in HBM -> a 4-deep cp.async ring in shared memory (three transitions in
+  // draws of this chain: [tr][chain][8] in HBM -> a 4-deep cp.async ring in shared memory (three transitions in
   // flight; a register FIFO would be rotated by the compiler right behind the loads and wait for them)
-  const double* D = a.scratch + cidx;
-  const long long NC = a.n_chains;
-  const unsigned ring_base = (unsigned)__cvta_generic_to_shared(ring + lane);
+  const double2* D = reinterpret_cast<const double2*>(a.scratch) + cidx * 4;
+  const long long NC4 = a.n_chains * 4;
+  const unsigned ring_base = (unsigned)__cvta_generic_to_shared(ring + lane * 4);
   auto fetch = [&](long long tr) {
     if (tr < a.n_steps) {
-      const double* p = D + tr * 5 * NC;
-      const unsigned dst = ring_base + (unsigned)((tr & 3) * 5 * LPW * 8);
+      const double2* p = D + tr * NC4;
+      const unsigned dst = ring_base + (unsigned)((tr & 3) * LPW * 64);
 #pragma unroll
-      for (int q = 0; q < 5; ++q)
-        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst + q * LPW * 8), "l"(p + q * NC) : "memory");
+      for (int q = 0; q < 4; ++q)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + q * 16), "l"(p + q) : "memory");
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
   };
   fetch(0); fetch(1); fetch(2);
+  const bool rec = active && a.draws && a.draw_slots > 0;
 
   for (long long tr = 0; tr < a.n_steps; ++tr) {
     fetch(tr + 3);
     asm volatile("cp.async.wait_group 3;" ::: "memory");
-    const double* dr = ring + (tr & 3) * 5 * LPW + lane;
-    const double uA = dr[0], luB = dr[LPW], uC = dr[2 * LPW], uD = dr[3 * LPW], z = dr[4 * LPW];
+    const double2* dr = ring + ((tr & 3) * LPW + lane) * 4;
+    const double2 dA = dr[0], dC = dr[1], dZ = dr[2], dE = dr[3];
+    const double uA = dA.x, luB = dA.y, uC = dC.x, uD = dC.y, z = dZ.x, hz2 = dZ.y;
     // ---- move type (pmf draw), index, birth position -------------------------------------------------
     const double2 pa = *reinterpret_cast<const double2*>(&T->pr[n][0]), pb = *reinterpret_cast<const double2*>(&T->pr[n][2]);
     const double ua = uA * (((pa.x + pa.y) + pb.x) + pb.y);
@@ -641,61 +653,60 @@ __device__ __forceinline__ void rj2_body(const StkArgs& a) {
     // ---- neighbourhood of rank j -----------------------------------------------------------------------
     const double2 Pm1 = ROW(P, j - 1), P0 = ROW(P, j), Pp1 = ROW(P, j + 1);
     const double2 Q0 = ROW(Q, j), Q1 = ROW(Q, j + 1);
-    const double2 Wm1 = ROW(W, j - 1), W0 = ROW(W, j), W1 = ROW(W, j + 1);
-    const double bC = T2->birthC[n], dC = T2->deathC[n];
-    const double sm1 = Pm1.x, s0 = P0.x, sp1 = Pp1.x, Fm1 = Pm1.y, F0 = P0.y, Fp1 = Pp1.y;
+    const double lw0 = ROW(LW, j), lw1 = ROW(LW, j + 1);
+    const double bC = T2->birthC[n], dCn = T2->deathC[n];
+    const double sm1 = Pm1.x, s0 = P0.x, sp1 = Pp1.x, cm1 = Pm1.y, c0 = P0.y, cp1 = Pp1.y;
     const double g0 = Q0.x, lg0 = Q0.y, g1 = Q1.x, lg1 = Q1.y;
-    const double cm1 = Wm1.y, c0 = W0.y, cp1 = W1.y, lw0 = W0.x, lw1 = W1.x;
     // ---- the proposal: one exp, one count, two logs, all independent -----------------------------------
     const bool m1 = move == 1, m2 = move == 2, m3 = move == 3, m4 = move == 4;
     const double u = -0.5 + (0.5 - (-0.5)) * uD;                          // coalMoveH
     const double lgn = (m1 ? u : z) + lg0;                                // log of the proposed rate, closed form
-    const double E = exp(m1 ? lgn : z);
-    const double gn = m1 ? E : E * g0;                                    // exp(u + log g_j)  |  exp(z) g_j
+    const double gn = (m1 ? dE.x : dE.y) * g0;                            // exp(u) g_j  |  exp(z) g_j (exps from the pre-pass)
     const double snew = m2 ? sm1 + (sp1 - sm1) * (0.0 + (1.0 - 0.0) * uD) : x;   // coalMoveP | birth point
     const double cn = (double)count_below_tab(ysm, btab, ny, snew, nb_over_t);
-    const double Fn = snew < 0.0 ? 0.0 : (snew > k.t ? 1.0 : snew / k.t);
-    const double wA = log((m4 ? Fp1 : Fn) - Fm1);                         // segment A = (s_{j-1}, snew | s_{j+1})
-    const double wB = log((m2 ? Fp1 : F0) - Fn);                          // segment B = (snew, s_{j+1} | s_j)
+    const double hiA = m1 ? s0 : (m4 ? sp1 : snew), hiB = m2 ? sp1 : s0;
+    const double dsA = hiA - sm1, dsB = hiB - snew;                       // widths of segment A = (s_{j-1}, .), B = (snew, .)
+    const double wA = fast_log(dsA * inv_t, fm);
+    const double wB = fast_log(dsB * inv_t, fm);
     // ---- f(y) - f(x) from the touched segments (selects, no branches) ----------------------------------
     const double old0 = seg_term(lw0, lg0, g0, 0, 0.0, k) + ((c0 - cm1) * lg0 - (s0 - sm1) * g0);
     const double old1 = seg_term(lw1, lg1, g1, 0, 0.0, k) + ((cp1 - c0) * lg1 - (sp1 - s0) * g1);
-    const double hiA = m1 ? s0 : (m4 ? sp1 : snew), chA = m1 ? c0 : (m4 ? cp1 : cn);
+    const double chA = m1 ? c0 : (m4 ? cp1 : cn);
     const double lgA = m1 ? lgn : lg0, gA = m1 ? gn : g0, lwA = m1 ? lw0 : wA;
-    const double tA = seg_term(lwA, lgA, gA, 0, 0.0, k) + ((chA - cm1) * lgA - (hiA - sm1) * gA);
-    const double hiB = m2 ? sp1 : s0, chB = m2 ? cp1 : c0, lgB = m2 ? lg1 : lgn, gB = m2 ? g1 : gn;
-    const double tB = (m2 || m3) ? seg_term(wB, lgB, gB, 0, 0.0, k) + ((chB - cn) * lgB - (hiB - snew) * gB) : 0.0;
+    const double tA = seg_term(lwA, lgA, gA, 0, 0.0, k) + ((chA - cm1) * lgA - dsA * gA);
+    const double chB = m2 ? cp1 : c0, lgB = m2 ? lg1 : lgn, gB = m2 ? g1 : gn;
+    const double tB = (m2 || m3) ? seg_term(wB, lgB, gB, 0, 0.0, k) + ((chB - cn) * lgB - dsB * gB) : 0.0;
     const double told = (m2 || m4) ? old0 + old1 : old0;
     const double zr = lg1 - lg0;                                          // log(g_{j+1}/g_j), death
-    const double extra = m1 ? u : (m2 ? 0.0 : (m3 ? (bC + 0.5 * z * z) + lgn : (dC - 0.5 * zr * zr) - lg1));
+    const double extra = m1 ? u : (m2 ? 0.0 : (m3 ? (bC + hz2) + lgn : (dCn - 0.5 * zr * zr) - lg1));
     const double df = (tA + tB) - told;                                   // without the head difference (in bC/dC)
     const double logr = df + extra;
     const bool accept = luB < logr;                                       // uB < min(1, exp(log r))
     // ---- commit ------------------------------------------------------------------------------------------
     if (accept) {
       if (m1) ROW(Q, j) = make_double2(gn, lgn);
-      else if (m2) { ROW(P, j) = make_double2(snew, Fn); ROW(W, j) = make_double2(wA, cn); ROW(W, j + 1) = make_double2(wB, cp1); }
+      else if (m2) { ROW(P, j) = make_double2(snew, cn); ROW(LW, j) = wA; ROW(LW, j + 1) = wB; }
       else if (m3) {
         for (int i = n + 1; i >= j; --i) {               // rows j.. move up; row j is then re-written
-          const double2 p = ROW(P, i), q = ROW(Q, i), w = ROW(W, i);
-          ROW(P, i + 1) = p; ROW(Q, i + 1) = q; ROW(W, i + 1) = w;
+          const double2 p = ROW(P, i), q = ROW(Q, i); const double w = ROW(LW, i);
+          ROW(P, i + 1) = p; ROW(Q, i + 1) = q; ROW(LW, i + 1) = w;
         }
-        ROW(P, j) = make_double2(snew, Fn); ROW(W, j) = make_double2(wA, cn);
-        ROW(Q, j + 1) = make_double2(gn, lgn); ROW(W, j + 1) = make_double2(wB, c0);
+        ROW(P, j) = make_double2(snew, cn); ROW(LW, j) = wA;
+        ROW(Q, j + 1) = make_double2(gn, lgn); ROW(LW, j + 1) = wB;
         ++n;
       } else {
         for (int i = j; i <= n; ++i) {                   // rows j+1.. move down; row j keeps its rate, new width
-          const double2 p = ROW(P, i + 1), q = ROW(Q, i + 1), w = ROW(W, i + 1);
-          ROW(P, i) = p; ROW(Q, i) = q; ROW(W, i) = w;
+          const double2 p = ROW(P, i + 1), q = ROW(Q, i + 1); const double w = ROW(LW, i + 1);
+          ROW(P, i) = p; ROW(Q, i) = q; ROW(LW, i) = w;
         }
-        ROW(Q, j) = make_double2(g0, lg0); ROW(W, j) = make_double2(wA, cp1);
+        ROW(Q, j) = make_double2(g0, lg0); ROW(LW, j) = wA;
         --n;
       }
       lp += df + (m3 ? T->head[n] - T->head[n - 1] : (m4 ? T->head[n] - T->head[n + 1] : 0.0));
       ++n_acc;
     }
     long long slot;
-    if (active && record_slot(a, tr, &slot)) {
+    if (rec && record_slot(a, tr, &slot)) {
       record_value(a, slot, 0, chain, (double)n);
       for (int i = 1; i <= SMAX + 1; ++i) {
         if (i <= SMAX) record_value(a, slot, i, chain, i <= n ? ROW(P, i).x : 0.0);
@@ -717,14 +728,16 @@ __device__ __forceinline__ void rj2_body(const StkArgs& a) {
 #undef ROW
 }
 
-// smem: (196 + TAB_DOUBLES + 64) doubles + 3 arrays of R1*LPW double2 + (NB+1) ints
-constexpr int rj2_smem(int lpw) { return (196 + TAB_DOUBLES + 64) * 8 + 3 * R1 * lpw * 16 + 20 * lpw * 8 + (NB + 1) * 4; }
-static_assert(rj2_smem(8) == 20020 && rj2_smem(4) == 12852 && rj2_smem(16) == 34356 && rj2_smem(32) == 63028, "rj2 smem");
+// smem: (196 + TAB_DOUBLES + 64 + fast-math tables) doubles + rows (40 B per row and chain) + ring + (NB+1) ints
+constexpr int rj2_smem(int lpw) { return (196 + TAB_DOUBLES + 64 + kFmTableDoubles) * 8 + R1 * lpw * 40 + 8 + 4 * lpw * 64 + (NB + 1) * 4; }
+static_assert(rj2_smem(8) == 23740 && rj2_smem(4) == 17276 && rj2_smem(16) == 36668 && rj2_smem(32) == 62524, "rj2 smem");
 
 }  // namespace
 
 extern "C" __global__ void __launch_bounds__(32) coal_rj2_8(const __grid_constant__ StkArgs a) { rj2_body<8>(a); }
 extern "C" __global__ void __launch_bounds__(32) coal_rj2_4(const __grid_constant__ StkArgs a) { rj2_body<4>(a); }
+extern "C" __global__ void __launch_bounds__(32) coal_rj2_2(const __grid_constant__ StkArgs a) { rj2_body<2>(a); }
+extern "C" __global__ void __launch_bounds__(32) coal_rj2_1(const __grid_constant__ StkArgs a) { rj2_body<1>(a); }
 extern "C" __global__ void __launch_bounds__(32) coal_rj2_16(const __grid_constant__ StkArgs a) { rj2_body<16>(a); }
 extern "C" __global__ void __launch_bounds__(32) coal_rj2_32(const __grid_constant__ StkArgs a) { rj2_body<32>(a); }
 
@@ -799,12 +812,14 @@ extern "C" __device__ const char stk_desc[] =
     "param a 1\n"
     "param b 200\n"
     "record n s g\n"
-    "kernel rj coal_rj8 128 16 10784 y 8\n"
+    "kernel rj coal_rj2_4 32 4 17276 - 0 pre coal_draws 256 8\n"
+    "kernel rj8 coal_rj8 128 16 10784 y 8\n"
     "kernel rj1 coal_rj1 32 32 53044 - 0\n"
-    "kernel rj2 coal_rj2_8 32 8 20020 - 0 pre coal_draws 256 5\n"
-    "kernel rj2x4 coal_rj2_4 32 4 12852 - 0 pre coal_draws 256 5\n"
-    "kernel rj2x16 coal_rj2_16 32 16 34356 - 0 pre coal_draws 256 5\n"
-    "kernel rj2x32 coal_rj2_32 32 32 63028 - 0 pre coal_draws 256 5\n"
+    "kernel rj2 coal_rj2_8 32 8 23740 - 0 pre coal_draws 256 8\n"
+    "kernel rj2x2 coal_rj2_2 32 2 14044 - 0 pre coal_draws 256 8\n"
+    "kernel rj2x1 coal_rj2_1 32 1 12428 - 0 pre coal_draws 256 8\n"
+    "kernel rj2x16 coal_rj2_16 32 16 36668 - 0 pre coal_draws 256 8\n"
+    "kernel rj2x32 coal_rj2_32 32 32 62524 - 0 pre coal_draws 256 8\n"
     "kernel rj32 coal_rj32 128 4 4640 y 8\n"
     "kernel rj16 coal_rj16 128 8 6688 y 8\n"
     "kernel rj4 coal_rj4 128 32 18976 y 8\n"

@@ -643,7 +643,7 @@ int stk_step(stk_chains* c, int kernel_id, int64_t n_transitions, stk_stream str
   long long chunk = n_transitions;
   if (kd.pre_k) {
     size_t per_tr = sizeof(double) * (size_t)kd.pre_per * (size_t)c->n;
-    size_t budget = (size_t)512 << 20;
+    size_t budget = (size_t)2048 << 20;
     if (const char* mb = getenv("STK_SCRATCH_MB")) budget = (size_t)std::max(1, atoi(mb)) << 20;
     chunk = std::max<long long>(1, std::min<long long>(n_transitions, (long long)(budget / per_tr)));
     size_t need = per_tr * (size_t)chunk;

@@ -112,7 +112,106 @@ def linreg():
     print("linreg: lp", gold["small_lp"][:3], "post mean", gold["small_post_mean"][:3])
 
 
-MODELS = {"linreg": linreg}
+def notebook_stan(nb, cell):
+    """the Stan program text that Language.Stan generated, as preserved in a notebook's output
+    (between '--- Generating Stan code ---' and the 'make -C' line; never copied into the repository)"""
+    import json
+    c = json.load(open(os.path.join(os.environ.get("REF", "/root/reference"), nb)))["cells"][cell]
+    txt = "".join("".join(o.get("text", [])) + "".join(o.get("data", {}).get("text/plain", [])) for o in c.get("outputs", []))
+    a = txt.index("--- Generating Stan code ---") + len("--- Generating Stan code ---")
+    return txt[a:txt.index("\nmake -C", a)].strip() + "\n"
+
+
+def lp_driver(model):
+    """full-precision log_prob_grad of a compiled model (oracle/stan/lp_driver.cpp on stanc's C++)"""
+    exe = os.path.join(WORK, model + "_lp")
+    hpp = os.path.join(WORK, model + ".hpp")
+    if not os.path.exists(exe) or os.path.getmtime(exe) < os.path.getmtime(hpp):
+        sm = os.path.join(CMDSTAN, "stan", "lib", "stan_math")
+        inc = ["-I", os.path.join(CMDSTAN, "src"), "-I", os.path.join(CMDSTAN, "stan", "src"), "-isystem", sm,
+               "-isystem", os.path.join(sm, "lib", "eigen_3.3.3"), "-isystem", os.path.join(sm, "lib", "boost_1.69.0"),
+               "-isystem", os.path.join(sm, "lib", "sundials_4.1.0", "include")]
+        import glob
+        for pat, key in (("eigen_*", 7), ("boost_*", 9), ("sundials_*", 11)):
+            hits = sorted(glob.glob(os.path.join(sm, "lib", pat)))
+            if hits:
+                inc[key] = hits[-1] if key != 11 else os.path.join(hits[-1], "include")
+        cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+        subprocess.run([cxx, "-O2", "-std=c++1y", "-w", "-DBOOST_DISABLE_ASSERTS", f'-DMODEL_HPP="{hpp}"'] + inc +
+                       [os.path.join(HERE, "lp_driver.cpp"), "-o", exe], check=True)
+    return exe
+
+
+def lp_grad(exe, data, points, propto=0):
+    inp = "\n".join(" ".join(repr(float(v)) for v in q) for q in points) + "\n"
+    out = subprocess.run([exe, data, str(propto)], input=inp, capture_output=True, text=True, check=True).stdout
+    rows = np.array([[float(v) for v in l.split()] for l in out.splitlines() if l.strip()])
+    return rows[:, 0], rows[:, 1:]
+
+
+BIRATS_X = [8.0, 15.0, 22.0, 29.0, 36.0]
+
+
+def birats_y():
+    """OpenBUGS BiRats data (public data set, http://www.openbugs.net/Examples/BiRatsdata.html) as in birats.ipynb cell 5"""
+    import json, re as _re
+    c = json.load(open(os.path.join(os.environ.get("REF", "/root/reference"), "birats.ipynb")))["cells"][5]
+    nums = [float(v) for v in _re.findall(r"\d+", "".join(c["source"]).split("biratsY")[1])]
+    return np.array(nums).reshape(30, 5)
+
+
+def birats():
+    os.makedirs(WORK, exist_ok=True)
+    open(os.path.join(WORK, "birats.stan"), "w").write(notebook_stan("birats.ipynb", 8))
+    exe = os.path.join(WORK, "birats")
+    if not os.path.exists(exe):
+        subprocess.run(["make", "-C", CMDSTAN, exe], check=True, capture_output=True)
+    drv = lp_driver("birats")
+    Y = birats_y(); X = np.array(BIRATS_X)
+    data = os.path.join(WORK, "birats.data")
+    rdump(data, x_stan_0_0=X, x_stan_0_6=Y)
+    rng = np.random.default_rng(20261104)
+    N = 30
+    K = 12
+    Q = np.empty((K, 2 * N + 6))
+    for k in range(K):
+        mu = np.array([106.0, 6.2]) + rng.standard_normal(2) * (0 if k == 0 else 3.0)
+        tau = np.abs(np.array([10.0, 0.5]) * (1 + 0.3 * rng.standard_normal(2)))
+        yo = 0.0 if k == 0 else 0.8 * rng.standard_normal()
+        b1 = 106 + 10 * rng.standard_normal(N); b2 = 6.2 + 0.5 * rng.standard_normal(N)
+        ls = np.log(6.0) + (0 if k == 0 else 0.3 * rng.standard_normal())
+        Q[k] = np.r_[mu, tau, yo, b1, b2, ls]
+    Q[1, :] = np.r_[0, 0, 1, 1, 0, np.ones(2 * N), 0.0]          # the notebook's `initial` (cell 7)
+    lp, g = lp_grad(drv, data, Q, 0)
+    gold = dict(x=X, y=Y, q=Q, lp=lp, grad=g)
+    # posterior moments by the reference sampler: 4 chains x 3000 static-HMC draws (eps 0.04, L 50: int_time 2, the
+    # benchmark's eps 0.02 / L 10 mixes too slowly in betaMu to pin moments) after 1000 warm-up transitions
+    init = os.path.join(WORK, "birats.init")
+    q0 = Q[0]
+    z = np.tanh(q0[4])
+    rdump(init, x_stan_0_1=q0[0:2], x_stan_0_2=q0[2:4], x_stan_0_3=np.array([[1, z], [z, 1.0]]),
+          x_stan_0_4=np.stack([q0[5:5 + N], q0[5 + N:5 + 2 * N]], axis=1), x_stan_0_5=np.exp(q0[-1]))
+    draws = []
+    for c in range(4):
+        out = os.path.join(WORK, f"birats_s{c}.csv")
+        subprocess.run([exe, "method=sample", "num_samples=3000", "num_warmup=1000", "adapt", "engaged=0", "algorithm=hmc",
+                        "engine=static", f"int_time={0.04 * 50}", "metric=unit_e", "stepsize=0.04", "data", f"file={data}",
+                        f"init={init}", "random", "seed=777", f"id={c + 1}", "output", f"file={out}"], check=True, capture_output=True)
+        rows = [l for l in open(out).read().splitlines() if l and not l.startswith("#")]
+        hdr = rows[0].split(",")
+        arr = np.array([[float(v) for v in r.split(",")] for r in rows[1:]])
+        col = {h: i for i, h in enumerate(hdr)}
+        sel = ["x_stan_0_1.1", "x_stan_0_1.2", "x_stan_0_2.1", "x_stan_0_2.2", "x_stan_0_3.1.2", "x_stan_0_5"]
+        draws.append(arr[:, [col[h] for h in sel]])
+    dr = np.stack(draws)                                       # [chain][draw][betaMu1, betaMu2, tau1, tau2, rho, sigma]
+    gold["post_names"] = np.array(["betaMu1", "betaMu2", "tau1", "tau2", "rho", "sigma"])
+    gold["post_mean"] = dr.mean(axis=(0, 1)); gold["post_sd"] = dr.std(axis=(0, 1), ddof=1)
+    gold["post_chain_means"] = dr.mean(axis=1); gold["post_eps_L"] = np.array([0.04, 50])
+    np.savez_compressed(os.path.join(GOLD, "birats_stan.npz"), **gold)
+    print("birats: lp", lp[:3], "post mean", gold["post_mean"], "sd", gold["post_sd"])
+
+
+MODELS = {"linreg": linreg, "birats": birats}
 
 if __name__ == "__main__":
     for m in (sys.argv[1:] or list(MODELS)):

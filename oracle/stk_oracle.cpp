@@ -51,6 +51,7 @@ static void rng_normal2(orc_rng* g, double* a, double* b) {
   *a = r * std::cos(2.0 * kPi * u2); *b = r * std::sin(2.0 * kPi * u2);
 }
 extern "C" double orc_u01(orc_rng* g) { double a, b; rng_u01x2(g, &a, &b); return a; }
+extern "C" void orc_rng_normal2(orc_rng* g, double* a, double* b) { rng_normal2(g, a, b); }
 extern "C" double orc_normal(orc_rng* g) { double a, b; rng_normal2(g, &a, &b); return a; }
 extern "C" void orc_u01x2(uint64_t seed, uint64_t chain, uint64_t step, uint32_t slot, double* a, double* b) {
   orc_rng g; orc_rng_init(&g, seed, chain, step); g.slot = slot; rng_u01x2(&g, a, b);

@@ -34,6 +34,7 @@ typedef struct { uint32_t k0, k1, c0, c1, c2, slot; } orc_rng;
 void orc_rng_init(orc_rng* g, uint64_t seed, uint64_t chain, uint64_t step);
 double orc_u01(orc_rng* g);
 double orc_normal(orc_rng* g);
+void orc_rng_normal2(orc_rng* g, double* a, double* b);  /* one block -> two normals */
 int orc_draw_discrete_uniform(orc_rng* g, int a, int b);
 int orc_draw_bernoulli(orc_rng* g, double p);
 int orc_draw_pmf(orc_rng* g, const double* ps, int n);
@@ -82,6 +83,13 @@ void orc_coal_simulate(uint64_t seed, uint64_t chain, double t, int lam, int nma
 long long orc_coal_rj_run(int* n, double* s, double* g, long long C, long long T, const double* y, int ny,
                           double t, int lam, int nmax, double a, double b, uint64_t seed, uint64_t chain0,
                           uint64_t step0, int nthreads);
+
+// ---- C4 birats (birats.ipynb; q = betaMu[2], tau[2], y_omega, beta[.,1], beta[.,2], log sigma) ----
+double orc_birats_logp(const double* x, const double* y, int N, int Tn, const double* q, double* grad);
+int orc_birats_hmc_step(const double* x, const double* y, int N, int Tn, double* q, double eps, int L,
+                        uint64_t seed, uint64_t chain, uint64_t step, double* lp_out);
+long long orc_birats_hmc_run(const double* x, const double* y, int N, int Tn, double* q, long long C, long long T,
+                             double eps, int L, uint64_t seed, uint64_t chain0, uint64_t step0, int nthreads);
 
 // ---- soccer RJ (rj.ipynb; pinned against the reference's generated C++ in oracle/_ref) -----
 double orc_soccer_accept_prob(int tag, double lam, double kappa, const int* y, int ny, double x, double* kappa_prop);

@@ -70,6 +70,35 @@ class Oracle:
         l.orc_soccer_rj_step.restype = I
         l.orc_soccer_rj_step.argtypes = [I, D, P, P, I, U, U, U, P]
 
+        l.orc_birats_logp.restype = D
+        l.orc_birats_logp.argtypes = [P, P, I, I, P, P]
+        l.orc_birats_hmc_step.restype = I
+        l.orc_birats_hmc_step.argtypes = [P, P, I, I, P, D, I, U, U, U, P]
+        l.orc_birats_hmc_run.restype = C.c_longlong
+        l.orc_birats_hmc_run.argtypes = [P, P, I, I, P, C.c_longlong, C.c_longlong, D, I, U, U, U, I]
+
+    # -- C4 birats ------------------------------------------------------------------
+    def birats_logp(self, x, y, q, grad=True):
+        x = np.ascontiguousarray(x, dtype=np.float64); y = np.ascontiguousarray(y, dtype=np.float64)
+        q = np.ascontiguousarray(q, dtype=np.float64)
+        N, Tn = y.shape
+        g = np.empty(2 * N + 6)
+        lp = self.l.orc_birats_logp(_p(x), _p(y), N, Tn, _p(q), _p(g) if grad else None)
+        return (lp, g) if grad else lp
+
+    def birats_hmc_step(self, x, y, q, eps, L, seed, chain, step):
+        x = np.ascontiguousarray(x, dtype=np.float64); y = np.ascontiguousarray(y, dtype=np.float64)
+        N, Tn = y.shape
+        lp = D()
+        acc = self.l.orc_birats_hmc_step(_p(x), _p(y), N, Tn, _p(q), eps, L, seed, chain, step, C.byref(lp))
+        return acc, lp.value
+
+    def birats_hmc_run(self, x, y, q, T, eps, L, seed, chain0=0, step0=0, nthreads=1):
+        x = np.ascontiguousarray(x, dtype=np.float64); y = np.ascontiguousarray(y, dtype=np.float64)
+        N, Tn = y.shape
+        assert q.flags.c_contiguous and q.dtype == np.float64 and q.shape[0] == 2 * N + 6
+        return self.l.orc_birats_hmc_run(_p(x), _p(y), N, Tn, _p(q), q.shape[1], T, eps, L, seed, chain0, step0, nthreads)
+
     # -- soccer RJ (rj.ipynb) ---------------------------------------------------------
     def soccer_accept_prob(self, tag, lam, kappa, y, x):
         y = np.ascontiguousarray(y, dtype=np.int32)

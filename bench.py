@@ -210,7 +210,48 @@ class BiratsHMC:
         return orc.birats_hmc_run(self.x, self.y, state["q"], T, self.eps, self.L, seed, chain0, step0, nthreads)
 
 
-WORKLOADS = {"linreg_hmc": LinregHMC, "coal_rj": CoalRJ, "birats_hmc": BiratsHMC}
+class DPGibbs:
+    """C5: Dirichlet-process mixture (dp.ipynb), N = 100,000 observations of a planted 5-component mixture, truncated
+    stick-breaking K = 32, alpha = 5, 1024 chains; one transition = one blocked Gibbs sweep (assignments, sticks, atoms)."""
+    name = "dp_gibbs"
+    module = "builtin:dp"
+    kernel = "sweep"
+    symbol = "dp_assign"
+    dtype = "f64"
+    chains = 1024
+    transitions_per_step = 4
+    N, K = 100000, 32
+    state_fields = ("v", "mu")
+    diag_thin = 1
+    diag_warmup = 8
+    roofline_note = ("SURVEY 8d unit: 8N (y) + 2*4N (z read+write) B per sweep and chain; the kernel never reads z back "
+                     "(blocked Gibbs) and y is shared by all chains (L2), so physical HBM traffic is the 4N-byte z write; "
+                     "the assignment step is bound by fp64 issue (32 clusters x ~12 fp64 instructions per observation)")
+
+    def __init__(self):
+        rng = np.random.default_rng(20261104)
+        centers = rng.uniform(0, 100, 5)
+        self.y = centers[rng.integers(0, 5, self.N)] + rng.standard_normal(self.N)
+        self.bytes_per_transition = 8 * self.N + 2 * 4 * self.N
+        self.describe = (f"C5 DP mixture N={self.N} (5 planted components), truncated stick-breaking K={self.K}, alpha=5, "
+                         f"blocked Gibbs sweep (configs[4], 1024 chains/GPU)")
+
+    def data(self):
+        return dict(y=self.y)
+
+    def params(self):
+        return dict(K=self.K)
+
+    def init_state(self, C, chain0):
+        rng = np.random.default_rng(7 + chain0)
+        v = rng.beta(1.0, 5.0, (self.K, C)); v[-1] = 1.0
+        return dict(v=np.ascontiguousarray(v), mu=np.ascontiguousarray(rng.uniform(0, 100, (self.K, C))))
+
+    def cpu_run(self, orc, state, T, seed, chain0, step0, nthreads):
+        return orc.dp_run(self.y, state["v"], state["mu"], T, seed, chain0, step0, nthreads)
+
+
+WORKLOADS = {"linreg_hmc": LinregHMC, "coal_rj": CoalRJ, "birats_hmc": BiratsHMC, "dp_gibbs": DPGibbs}
 DEFAULT_WORKLOAD = "coal_rj"
 
 
@@ -452,10 +493,13 @@ def main():
             reference_arm(args, wl)
         return 0
 
+    # the driver parses ONE JSON line from stdout: libraries that print there (NCCL's version banner) go to stderr
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     import torch
     import torch.distributed as dist
     if not torch.cuda.is_available():
-        print(json.dumps(dict(error="no CUDA device; libstk_cuda has no CPU fallback")), flush=True)
+        print(json.dumps(dict(error="no CUDA device; libstk_cuda has no CPU fallback")), file=real_stdout, flush=True)
         return 2
     torch.cuda.set_device(local)
     if world > 1:
@@ -475,7 +519,7 @@ def main():
         if extra:
             out["gpu_launches"] += sum(v["gpu_launches"] for v in extra.values())
             out["also"] = extra
-        print(json.dumps(out), flush=True)
+        print(json.dumps(out), file=real_stdout, flush=True)
     if world > 1:
         dist.destroy_process_group()
     return 0

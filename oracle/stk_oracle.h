@@ -91,6 +91,14 @@ int orc_birats_hmc_step(const double* x, const double* y, int N, int Tn, double*
 long long orc_birats_hmc_run(const double* x, const double* y, int N, int Tn, double* q, long long C, long long T,
                              double eps, int L, uint64_t seed, uint64_t chain0, uint64_t step0, int nthreads);
 
+// ---- C5 DP mixture (dp.ipynb; truncated stick-breaking, blocked Gibbs; PARITY UNPINNED) -------
+void orc_dp_sweep(const double* y, int N, int K, double alpha, double lo, double hi, double* v, double* mu, int* z,
+                  uint64_t seed, uint64_t chain, uint64_t sweep);
+void orc_dp_simulate(int N, int K, double alpha, double lo, double hi, uint64_t seed, uint64_t chain,
+                     double* v, double* mu, int* z, double* ysim);
+long long orc_dp_run(const double* y, int N, int K, double alpha, double lo, double hi, double* v, double* mu,
+                     long long C, long long T, uint64_t seed, uint64_t chain0, uint64_t step0, int nthreads);
+
 // ---- soccer RJ (rj.ipynb; pinned against the reference's generated C++ in oracle/_ref) -----
 double orc_soccer_accept_prob(int tag, double lam, double kappa, const int* y, int ny, double x, double* kappa_prop);
 int orc_soccer_rj_step(int tag, double lam, double* kappa, const int* y, int ny,

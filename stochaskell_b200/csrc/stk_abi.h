@@ -18,10 +18,15 @@
  *   record <field> ...               fields (as doubles) that make up a draw
  *   kernel <name> <symbol> <block> <chains_per_block> <smem_fixed> <smem_field|-> <smem_bytes_per_elem>
  *          [pre <symbol> <block> <doubles_per_chain_transition>]
+ *          [phase <symbol> <block> <chains_per_block> <items_field> <items_per_block> <smem_bytes>]
  *          transition kernels, kernel_id = order of appearance.  `pre` names a pre-pass kernel that the runtime
  *          launches first, one thread per (chain, transition) of the launch, to fill StkArgs.scratch
  *          [transition][k][chain] (k < doubles_per_chain_transition) — the state-independent part of a transition
  *          (its random draws) computed at full occupancy instead of inside the sequential chain loop.
+ *          `phase` names a kernel that runs before the main kernel in EVERY transition (the launch is then split
+ *          into single transitions) on a 2-D grid: x = ceil(n_chains / chains_per_block) chain groups,
+ *          y = ceil(flen[items_field] / items_per_block) tiles of the per-item work of one transition (e.g. the
+ *          assignment step of a Gibbs sweep over the observations); the main kernel then finishes the transition.
  *   entry  <logp|logp_grad|simulate> <symbol> <block> <chains_per_block> <smem_fixed> <smem_field|-> <smem_bytes_per_elem>
  * Launch geometry: grid = ceil(n_chains / chains_per_block) CTAs of <block>
  * threads, dynamic smem = smem_fixed + flen[smem_field] * bytes_per_elem.

@@ -132,6 +132,7 @@ struct KernelDesc {
   int block = 0, cpb = 1; long long smem_fixed = 0; std::string smem_field; long long smem_per = 0;
   cudaKernel_t k = nullptr;
   std::string pre_symbol; int pre_block = 0; long long pre_per = 0; cudaKernel_t pre_k = nullptr;
+  std::string ph_symbol, ph_field; int ph_block = 0, ph_cpb = 1; long long ph_items = 1, ph_smem = 0; cudaKernel_t ph_k = nullptr;
 };
 
 }  // namespace
@@ -181,6 +182,9 @@ int parse_kernel_line(std::istringstream& ls, KernelDesc* k) {
   std::string opt;
   while (ls >> opt) {
     if (opt == "pre") { if (!(ls >> k->pre_symbol >> k->pre_block >> k->pre_per) || k->pre_block <= 0 || k->pre_per <= 0) return -1; }
+    else if (opt == "phase") {
+      if (!(ls >> k->ph_symbol >> k->ph_block >> k->ph_cpb >> k->ph_field >> k->ph_items >> k->ph_smem) || k->ph_block <= 0 || k->ph_cpb <= 0 || k->ph_items <= 0) return -1;
+    }
     else return -1;
   }
   return 0;
@@ -268,6 +272,18 @@ int launch(stk_chains* c, KernelDesc& k, long long n_steps, cudaStream_t st) {
     void* pparams[1] = {&a};
     TRACE("launch pre %s grid=%lld block=%d", k.pre_symbol.c_str(), pgrid, k.pre_block);
     CU(cudaLaunchKernel((const void*)k.pre_k, dim3((unsigned)pgrid), dim3((unsigned)k.pre_block), pparams, 0, st));
+    g_launches.fetch_add(1);
+  }
+  if (k.ph_k) {    // per-transition phase kernel on a (chain groups) x (item tiles) grid
+    int f = field_index(m, k.ph_field);
+    long long items = c->flen[f];
+    if (items <= 0) return fail(STK_ERR_ARG, "kernel %s: field %s not set", k.name.c_str(), k.ph_field.c_str());
+    dim3 pg((unsigned)((c->n + k.ph_cpb - 1) / k.ph_cpb), (unsigned)((items + k.ph_items - 1) / k.ph_items));
+    if (k.ph_smem > 48 * 1024)
+      CU(cudaFuncSetAttribute((const void*)k.ph_k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k.ph_smem));
+    void* pparams[1] = {&a};
+    TRACE("launch phase %s grid=%u x %u block=%d", k.ph_symbol.c_str(), pg.x, pg.y, k.ph_block);
+    CU(cudaLaunchKernel((const void*)k.ph_k, pg, dim3((unsigned)k.ph_block), pparams, (size_t)k.ph_smem, st));
     g_launches.fetch_add(1);
   }
   long long smem = k.smem_fixed;
@@ -425,6 +441,11 @@ int stk_module_load(stk_ctx* ctx, const char* spec, const char* cache_dir, stk_m
     if (!k.pre_symbol.empty()) {
       e3 = cudaLibraryGetKernel(&k.pre_k, m->lib, k.pre_symbol.c_str());
       if (e3 != cudaSuccess) return fail(STK_ERR_ARG, "module %s: pre-pass symbol %s: %s", m->name.c_str(), k.pre_symbol.c_str(), cudaGetErrorString(e3));
+    }
+    if (!k.ph_symbol.empty()) {
+      e3 = cudaLibraryGetKernel(&k.ph_k, m->lib, k.ph_symbol.c_str());
+      if (e3 != cudaSuccess) return fail(STK_ERR_ARG, "module %s: phase symbol %s: %s", m->name.c_str(), k.ph_symbol.c_str(), cudaGetErrorString(e3));
+      if (field_index(m, k.ph_field) < 0) return fail(STK_ERR_ARG, "module %s: phase items field %s unknown", m->name.c_str(), k.ph_field.c_str());
     }
     return STK_OK;
   };
@@ -641,6 +662,7 @@ int stk_step(stk_chains* c, int kernel_id, int64_t n_transitions, stk_stream str
   KernelDesc& kd = c->mod->kernels[kernel_id];
   // a kernel with a pre-pass runs in chunks whose scratch ([transitions][k][chains] doubles) fits the budget
   long long chunk = n_transitions;
+  if (kd.ph_k) chunk = 1;
   if (kd.pre_k) {
     size_t per_tr = sizeof(double) * (size_t)kd.pre_per * (size_t)c->n;
     size_t budget = (size_t)2048 << 20;

@@ -77,6 +77,31 @@ class Oracle:
         l.orc_birats_hmc_run.restype = C.c_longlong
         l.orc_birats_hmc_run.argtypes = [P, P, I, I, P, C.c_longlong, C.c_longlong, D, I, U, U, U, I]
 
+        l.orc_dp_sweep.restype = None
+        l.orc_dp_sweep.argtypes = [P, I, I, D, D, D, P, P, P, U, U, U]
+        l.orc_dp_simulate.restype = None
+        l.orc_dp_simulate.argtypes = [I, I, D, D, D, U, U, P, P, P, P]
+        l.orc_dp_run.restype = C.c_longlong
+        l.orc_dp_run.argtypes = [P, I, I, D, D, D, P, P, C.c_longlong, C.c_longlong, U, U, U, I]
+
+    # -- C5 DP mixture ------------------------------------------------------------------
+    def dp_sweep(self, y, v, mu, seed, chain, sweep, alpha=5.0, lo=0.0, hi=100.0):
+        """v[K], mu[K] float64 updated in place; returns z[N] (1-based int32)"""
+        y = np.ascontiguousarray(y, dtype=np.float64)
+        z = np.empty(len(y), dtype=np.int32)
+        self.l.orc_dp_sweep(_p(y), len(y), len(v), alpha, lo, hi, _p(v), _p(mu), _p(z), seed, chain, sweep)
+        return z
+
+    def dp_simulate(self, N, K, seed, chain, alpha=5.0, lo=0.0, hi=100.0):
+        v = np.empty(K); mu = np.empty(K); z = np.empty(N, dtype=np.int32); ys = np.empty(N)
+        self.l.orc_dp_simulate(N, K, alpha, lo, hi, seed, chain, _p(v), _p(mu), _p(z), _p(ys))
+        return v, mu, z, ys
+
+    def dp_run(self, y, v, mu, T, seed, chain0=0, step0=0, nthreads=1, alpha=5.0, lo=0.0, hi=100.0):
+        y = np.ascontiguousarray(y, dtype=np.float64)
+        assert v.flags.c_contiguous and mu.flags.c_contiguous and v.shape == mu.shape
+        return self.l.orc_dp_run(_p(y), len(y), v.shape[0], alpha, lo, hi, _p(v), _p(mu), v.shape[1], T, seed, chain0, step0, nthreads)
+
     # -- C4 birats ------------------------------------------------------------------
     def birats_logp(self, x, y, q, grad=True):
         x = np.ascontiguousarray(x, dtype=np.float64); y = np.ascontiguousarray(y, dtype=np.float64)

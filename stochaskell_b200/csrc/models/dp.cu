@@ -16,6 +16,7 @@
 //     draws of the stick's beta posterior, the atom's truncated-normal posterior; resets the accumulators.
 // Philox: counter (chain, sweep, slot): slot i/2 component i%2 -> u_i;  2^30 + 64k (+32) -> stick k;  2^30 + 2^16 + 64k -> atom k.
 #include "../stk_device.cuh"
+#include "../stk_fastmath.cuh"
 
 using namespace stk;
 
@@ -29,9 +30,14 @@ constexpr double FIX = 68719476736.0; // 2^36
 enum { F_V = 0, F_MU = 1, F_Z = 2, F_ACCN = 3, F_ACCS = 4, F_YSIM = 5, F_Y = 6 };
 enum { PAR_ALPHA = 0, PAR_K = 1, PAR_LO = 2, PAR_HI = 3 };
 
-// categorical draw over K <= 32 clusters with log-weights lpi_k - (y - mu_k)^2 / 2; tables are [k][32 lanes]
+// categorical draw over K <= 32 clusters with log-weights lpi_k - (y - mu_k)^2 / 2; tables are [k][32 lanes].
+// Weights more than e^-50 below the largest are exactly zero (the oracle's rule), so only a few clusters per
+// observation need an exp — but WHICH ones differs from lane to lane (a lane is a chain).  Looping over k with a
+// branch around the exp makes the warp run all 32 exps (ncu r01dp: 2,120 instructions per warp-observation);
+// instead each lane walks ITS OWN candidate bitmask, so the warp runs max-over-lanes(#candidates) ~ 3 iterations of
+// one exp.  Sums run over the candidates in increasing k: identical to the full loop, which only adds zeros.
 __device__ __forceinline__ int assign(double y, const double* __restrict__ lpi, const double* __restrict__ mu,
-                                      int lane, int K, double u) {
+                                      const double* __restrict__ fm, double* __restrict__ wbuf, int lane, int K, double u) {
   double lw[KMAX];
   double m = neg_inf();
 #pragma unroll
@@ -40,20 +46,26 @@ __device__ __forceinline__ int assign(double y, const double* __restrict__ lpi, 
     lw[k] = fma(-0.5 * d, d, lpi[k * 32 + lane]);      // clusters >= K carry lpi = -inf
     m = lw[k] > m ? lw[k] : m;
   }
-  double S = 0.0;
+  u32 mask = 0u;
 #pragma unroll
-  for (int k = 0; k < KMAX; ++k) {
-    const double t = lw[k] - m;
-    lw[k] = (t < -50.0) ? 0.0 : exp(t);                // NaN (all -inf) compares false -> exp(NaN): never with K >= 1 finite
-    S += lw[k];
+  for (int k = 0; k < KMAX; ++k) mask |= (lw[k] - m < -50.0) ? 0u : (1u << k);
+  // candidate weights go through a per-thread column of shared memory ([slot][thread]): a dynamic index costs one
+  // STS/LDS there, where a register array would cost a select chain per slot
+  double S = 0.0;
+  int nc = 0;
+  for (u32 mm = mask; mm; mm &= mm - 1u) {
+    const int k = __ffs((int)mm) - 1;
+    const double d = y - mu[k * 32 + lane];
+    const double w = fast_exp(fma(-0.5 * d, d, lpi[k * 32 + lane]) - m, fm);   // table exp: 15 instructions, <= 1 ulp
+    S += w;
+    wbuf[nc * 256] = w;
+    ++nc;
   }
   const double target = u * S;
-  double cum = 0.0; int z = K;
-  bool found = false;
-#pragma unroll
-  for (int k = 0; k < KMAX; ++k) {
-    cum += lw[k];
-    if (!found && target < cum) { z = k + 1; found = true; }
+  double cum = 0.0; int z = K, j = 0;
+  for (u32 mm = mask; mm; mm &= mm - 1u, ++j) {
+    cum += wbuf[j * 256];
+    if (target < cum) { z = __ffs((int)mm); break; }
   }
   return min(z, K);
 }
@@ -79,9 +91,11 @@ __device__ __forceinline__ void stage_tables(const StkArgs& a, long long cidx, i
 // assignment step: grid.x = 32-chain groups, grid.y = tiles of TP observations; block 256
 // ---------------------------------------------------------------------------------------------------------
 extern "C" __global__ void __launch_bounds__(256) dp_assign(const __grid_constant__ StkArgs a) {
+  extern __shared__ __align__(16) double wcols[];      // [KMAX][256]: candidate weights of every thread
   __shared__ double lpi[KMAX * 32], mus[KMAX * 32];
   __shared__ unsigned cnt[KMAX * 32];
   __shared__ unsigned long long sum[KMAX * 32];
+  __shared__ __align__(16) double fm[kFmTableDoubles];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int K = min((int)a.par[PAR_K], KMAX);
   const long long chain = (long long)blockIdx.x * 32 + lane;
@@ -89,6 +103,7 @@ extern "C" __global__ void __launch_bounds__(256) dp_assign(const __grid_constan
   const long long cidx = active ? chain : a.n_chains - 1;
   const long long N = a.flen[F_Y];
   for (int i = threadIdx.x; i < KMAX * 32; i += blockDim.x) { cnt[i] = 0u; sum[i] = 0ull; }
+  fm_build_tables(fm, threadIdx.x, blockDim.x);
   if (w == 0) stage_tables(a, cidx, lane, K, lpi, mus);
   __syncthreads();
   const double* Y = (const double*)a.field[F_Y];
@@ -102,7 +117,7 @@ extern "C" __global__ void __launch_bounds__(256) dp_assign(const __grid_constan
     for (int e = 0; e < 2; ++e) {
       if (i + e < i1) {
         const double y = __ldg(Y + i + e);
-        const int z = assign(y, lpi, mus, lane, K, e ? u1 : u0);
+        const int z = assign(y, lpi, mus, fm, wcols + threadIdx.x, lane, K, e ? u1 : u0);
         if (active) {
           Z[(i + e) * a.n_chains + chain] = z;
           atomicAdd(&cnt[(z - 1) * 32 + lane], 1u);
@@ -254,5 +269,5 @@ extern "C" __device__ const char stk_desc[] =
     "param lo 0\n"
     "param hi 100\n"
     "record v mu\n"
-    "kernel sweep dp_params 128 4 0 - 0 phase dp_assign 256 32 y 2048 0\n"
+    "kernel sweep dp_params 128 4 0 - 0 phase dp_assign 256 32 y 2048 65536\n"
     "entry simulate dp_sim_params 128 4 0 - 0 phase dp_sim_points 256 32 y 2048 0\n";

@@ -211,7 +211,31 @@ def birats():
     print("birats: lp", lp[:3], "post mean", gold["post_mean"], "sd", gold["post_sd"])
 
 
-MODELS = {"linreg": linreg, "birats": birats}
+def gp():
+    """gp.ipynb cell 15: GP classifier, fixed SE kernel, whitened latent; lp/grad at n = 48 and n = 160"""
+    os.makedirs(WORK, exist_ok=True)
+    open(os.path.join(WORK, "gp.stan"), "w").write(notebook_stan("gp.ipynb", 15))
+    exe = os.path.join(WORK, "gp")
+    if not os.path.exists(exe):
+        subprocess.run(["make", "-C", CMDSTAN, exe], check=True, capture_output=True)
+    drv = lp_driver("gp")
+    gold = {}
+    for tag, n in (("small", 48), ("mid", 160)):
+        rng = np.random.default_rng(20261104 + n)
+        x = np.sort(rng.uniform(0, 10, n))
+        f = np.sin(x) * 1.5
+        z = (rng.uniform(size=n) < 1 / (1 + np.exp(-f))).astype(np.int64)
+        data = os.path.join(WORK, f"gp_{tag}.data")
+        rdump(data, x_stan_0_0=n, x_stan_0_1=x, x_stan_0_3=z)
+        K = 6
+        W = rng.standard_normal((K, n)) * np.array([0.0, 0.3, 1.0, 1.0, 2.0, 1.0])[:, None]
+        lp, g = lp_grad(drv, data, W, 0)
+        gold.update({f"{tag}_x": x, f"{tag}_z": z, f"{tag}_w": W, f"{tag}_lp": lp, f"{tag}_grad": g})
+    np.savez_compressed(os.path.join(GOLD, "gp_stan.npz"), **gold)
+    print("gp: lp", gold["small_lp"], gold["mid_lp"][:2])
+
+
+MODELS = {"linreg": linreg, "birats": birats, "gp": gp}
 
 if __name__ == "__main__":
     for m in (sys.argv[1:] or list(MODELS)):

@@ -99,6 +99,14 @@ void orc_dp_simulate(int N, int K, double alpha, double lo, double hi, uint64_t 
 long long orc_dp_run(const double* y, int N, int K, double alpha, double lo, double hi, double* v, double* mu,
                      long long C, long long T, uint64_t seed, uint64_t chain0, uint64_t step0, int nthreads);
 
+// ---- C3 GP classifier, gp.ipynb form (fixed SE kernel, whitened latent w; pinned by tests/golden/gp_stan.npz) ----
+int orc_gp_chol(const double* x, int n, double* L);
+double orc_gp_logp(const double* L, const int* z, int n, const double* w, double* grad);
+int orc_gp_hmc_step(const double* L, const int* z, int n, double* w, double eps, int Lf,
+                    uint64_t seed, uint64_t chain, uint64_t step, double* lp_out);
+long long orc_gp_hmc_run(const double* L, const int* z, int n, double* W, long long C, long long T, double eps, int Lf,
+                         uint64_t seed, uint64_t chain0, uint64_t step0, int nthreads);
+
 // ---- soccer RJ (rj.ipynb; pinned against the reference's generated C++ in oracle/_ref) -----
 double orc_soccer_accept_prob(int tag, double lam, double kappa, const int* y, int ny, double x, double* kappa_prop);
 int orc_soccer_rj_step(int tag, double lam, double* kappa, const int* y, int ny,

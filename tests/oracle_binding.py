@@ -84,6 +84,15 @@ class Oracle:
         l.orc_dp_run.restype = C.c_longlong
         l.orc_dp_run.argtypes = [P, I, I, D, D, D, P, P, C.c_longlong, C.c_longlong, U, U, U, I]
 
+        l.orc_gp_chol.restype = I
+        l.orc_gp_chol.argtypes = [P, I, P]
+        l.orc_gp_logp.restype = D
+        l.orc_gp_logp.argtypes = [P, P, I, P, P]
+        l.orc_gp_hmc_step.restype = I
+        l.orc_gp_hmc_step.argtypes = [P, P, I, P, D, I, U, U, U, P]
+        l.orc_gp_hmc_run.restype = C.c_longlong
+        l.orc_gp_hmc_run.argtypes = [P, P, I, P, C.c_longlong, C.c_longlong, D, I, U, U, U, I]
+
     # -- C5 DP mixture ------------------------------------------------------------------
     def dp_sweep(self, y, v, mu, seed, chain, sweep, alpha=5.0, lo=0.0, hi=100.0):
         """v[K], mu[K] float64 updated in place; returns z[N] (1-based int32)"""
@@ -101,6 +110,31 @@ class Oracle:
         y = np.ascontiguousarray(y, dtype=np.float64)
         assert v.flags.c_contiguous and mu.flags.c_contiguous and v.shape == mu.shape
         return self.l.orc_dp_run(_p(y), len(y), v.shape[0], alpha, lo, hi, _p(v), _p(mu), v.shape[1], T, seed, chain0, step0, nthreads)
+
+    # -- C3 GP classifier (gp.ipynb form) ------------------------------------------------
+    def gp_chol(self, x):
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        L = np.zeros((len(x), len(x)))
+        if self.l.orc_gp_chol(_p(x), len(x), _p(L)) != 0:
+            raise ValueError("covariance not positive definite")
+        return L
+
+    def gp_logp(self, L, z, w, grad=True):
+        z = np.ascontiguousarray(z, dtype=np.int32); w = np.ascontiguousarray(w, dtype=np.float64)
+        g = np.empty(len(w))
+        lp = self.l.orc_gp_logp(_p(L), _p(z), len(w), _p(w), _p(g) if grad else None)
+        return (lp, g) if grad else lp
+
+    def gp_hmc_step(self, L, z, w, eps, Lf, seed, chain, step):
+        z = np.ascontiguousarray(z, dtype=np.int32)
+        lp = D()
+        acc = self.l.orc_gp_hmc_step(_p(L), _p(z), len(w), _p(w), eps, Lf, seed, chain, step, C.byref(lp))
+        return acc, lp.value
+
+    def gp_hmc_run(self, L, z, W, T, eps, Lf, seed, chain0=0, step0=0, nthreads=1):
+        z = np.ascontiguousarray(z, dtype=np.int32)
+        assert W.flags.c_contiguous and W.dtype == np.float64
+        return self.l.orc_gp_hmc_run(_p(L), _p(z), W.shape[0], _p(W), W.shape[1], T, eps, Lf, seed, chain0, step0, nthreads)
 
     # -- C4 birats ------------------------------------------------------------------
     def birats_logp(self, x, y, q, grad=True):

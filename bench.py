@@ -35,7 +35,8 @@ def measured_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
         d = json.load(open(p))
-        return dict(hbm_gbs=float(d["hbm_gbs"]), bf16_tflops=float(d.get("bf16_tflops", 1585.2)), source="measured")
+        return dict(hbm_gbs=float(d["hbm_gbs"]), bf16_tflops=float(d.get("bf16_tflops", 1585.2)),
+                    bf16_tflops_sustained=float(d.get("bf16_tflops_sustained", d.get("bf16_tflops", 1585.2))), source="measured")
     return dict(hbm_gbs=6650.0, bf16_tflops=1590.0, source="fallback")
 
 
@@ -251,7 +252,67 @@ class DPGibbs:
         return orc.dp_run(self.y, state["v"], state["mu"], T, seed, chain0, step0, nthreads)
 
 
-WORKLOADS = {"linreg_hmc": LinregHMC, "coal_rj": CoalRJ, "birats_hmc": BiratsHMC, "dp_gibbs": DPGibbs}
+class GPHMC:
+    """C3: GP classifier of gp.ipynb (fixed squared-exponential kernel, whitened latent), n = 2048 inputs, static HMC over
+    w in R^2048; the Cholesky factor is computed once per data set (`prepare`), one gradient evaluation of all chains is
+    two triangular matrix products L W and L^T R (n x n by n x chains)."""
+    name = "gp_hmc"
+    module = "builtin:gp"
+    kernel = "hmc"
+    symbol = "gp_gemm1"
+    dtype = "f64"
+    chains = 4096
+    transitions_per_step = 2
+    n, L, eps = 2048, 10, 0.1
+    state_fields = ("w",)
+    e2e_fields = ("w", "lp")
+    diag_thin = 1
+    diag_warmup = 10
+    diag_draws = 8
+    cpu_chains_per_thread = 1
+
+    def __init__(self):
+        rng = np.random.default_rng(20261104)
+        self.x = np.sort(rng.uniform(0, 10, self.n))
+        self.z = (rng.uniform(size=self.n) < 1 / (1 + np.exp(-2 * np.sin(self.x)))).astype(np.int32)
+        self._L = None
+        # per gradient evaluation and chain: two triangular products = 2 * (2 * n^2 / 2) flops; L evaluations per
+        # transition (the gradient at the start of a transition is carried over from the previous one)
+        self.flops_per_eval = 2.0 * self.n * self.n
+        self.flops_per_transition = self.L * self.flops_per_eval
+        # HBM bytes the products must move per evaluation and chain: read w, write r, read r, w, p, write gr, p, w
+        self.bytes_per_transition = self.L * 8 * 8 * self.n
+        self.describe = (f"C3 GP classifier (gp.ipynb) n={self.n}, SE kernel + 1e-6 jitter, whitened latent, static HMC "
+                         f"eps={self.eps} L={self.L} unit_e (configs[2] at 4096 chains/GPU; one Cholesky per data set)")
+
+    def data(self):
+        return dict(x=self.x, z=self.z)
+
+    def params(self):
+        return dict(eps=self.eps, L=self.L)
+
+    def init_state(self, C, chain0):
+        rng = np.random.default_rng(5 + chain0)
+        return dict(w=np.ascontiguousarray(0.1 * rng.standard_normal((self.n, C))))
+
+    def cpu_run(self, orc, state, T, seed, chain0, step0, nthreads):
+        if self._L is None:
+            self._L = orc.gp_chol(self.x)
+        return orc.gp_hmc_run(self._L, self.z, state["w"], T, self.eps, self.L, seed, chain0, step0, nthreads)
+
+    def roofline(self, C, T, ms_per_launch, peaks):
+        tf = C * T * self.flops_per_transition / (ms_per_launch * 1e-3) / 1e12
+        peak = peaks.get("bf16_tflops_sustained") or peaks.get("bf16_tflops") or 1365.0
+        return dict(bound="tensor", achieved=tf, peak=peak, unit="TFLOP/s", frac=tf / peak, traffic=None,
+                    kernel="gp_gemm1 + gp_gemm2_leap", peak_source=peaks["source"],
+                    useful_flops_per_transition_per_chain=self.flops_per_transition,
+                    note="useful flops = L x 2 n^2 per chain and transition (two triangular n x n products per gradient); "
+                         "this arm is the fp64 tier (1e-10 parity): the products run on the fp64 pipe (DFMA), which tcgen05 "
+                         "does not serve, so the fraction of the dense bf16 tensor peak is small by construction; "
+                         "fp64 DFMA peak of a B200 is ~37 TFLOP/s")
+
+
+WORKLOADS = {"linreg_hmc": LinregHMC, "coal_rj": CoalRJ, "birats_hmc": BiratsHMC, "dp_gibbs": DPGibbs, "gp_hmc": GPHMC}
 DEFAULT_WORKLOAD = "coal_rj"
 
 
@@ -290,7 +351,7 @@ def reference_arm(args, wl):
     from tests.oracle_binding import oracle
     orc = oracle()
     nt = host_threads()
-    C = 2 * nt
+    C = getattr(wl, "cpu_chains_per_thread", 2) * nt
     # calibrate so that the whole run (steps + warmup) stays within ~2 minutes
     st = wl.init_state(C, 0)
     per_tr = calibrate(wl, orc, st, nt)
@@ -379,7 +440,8 @@ def run_native(args, wl, rank, world, local, torch, dist):
     # ---- e2e: public API, HOST (pinned) buffers, H2D + kernel + D2H inside the timed region -----
     e2e = None
     if not args.no_e2e:
-        fields = [f for f, d in s.module.fields.items() if d["state"] and not str(d["len"]).startswith("@")]
+        fields = list(getattr(wl, "e2e_fields", None) or
+                      [f for f, d in s.module.fields.items() if d["state"] and not str(d["len"]).startswith("@")])
         cur = {k: ch.get_state(k) for k in st0}   # continue from the (burnt-in) device state
         host_in = {k: torch.from_numpy(np.ascontiguousarray(v)).pin_memory().numpy() for k, v in cur.items()}
         host_out = {}
@@ -414,22 +476,23 @@ def run_native(args, wl, rank, world, local, torch, dist):
     try:
         thin = getattr(wl, "diag_thin", 4)
         ch.step(kernel, getattr(wl, "diag_warmup", 300))  # move off the synthetic init before judging mixing
-        ch.record(32, thin)
+        nd = getattr(wl, "diag_draws", 32)
+        ch.record(nd, thin)
         t0 = time.perf_counter()
-        ch.step(kernel, 32 * thin)
+        ch.step(kernel, nd * thin)
         ch.sync()
         dt_draws = time.perf_counter() - t0
-        max_lag = 31
+        max_lag = nd - 1
         buf = torch.from_numpy(ch.diag_partial(max_lag)).to(dev)
         if world > 1:
             dist.all_reduce(buf, op=dist.ReduceOp.SUM)  # NCCL over NVLink
         P = lib().stk_num_recorded_values(ch._h)
-        r = diag_finish(buf.cpu().numpy(), P, 32, max_lag)
+        r = diag_finish(buf.cpu().numpy(), P, nd, max_lag)
         ok = np.isfinite(r["rhat"]) & np.isfinite(r["ess"])
         diag = dict(rhat_max=float(np.max(r["rhat"][ok])) if ok.any() else None,
                     ess_min=float(np.min(r["ess"][ok])) if ok.any() else None,
                     ess_per_sec_min=float(np.min(r["ess"][ok]) / dt_draws) if ok.any() else None,
-                    params_finite=int(ok.sum()), params=int(P), draws=32, thin=thin, chains=world * C,
+                    params_finite=int(ok.sum()), params=int(P), draws=nd, thin=thin, chains=world * C,
                     collective="nccl all_reduce(sum) of [P*(4+max_lag+1)] f64" if world > 1 else "none (1 GPU)")
     except Exception as e:  # diagnostics are not part of the timed path
         diag = dict(error=str(e)[:200])
@@ -440,7 +503,7 @@ def run_native(args, wl, rank, world, local, torch, dist):
     ms_per_launch = dev_ms / K
     alg_bytes = C * T * wl.bytes_per_transition
     achieved = alg_bytes / (ms_per_launch * 1e-3) / 1e9
-    roofline = dict(bound="hbm", achieved=achieved, peak=peaks["hbm_gbs"], unit="GB/s", frac=achieved / peaks["hbm_gbs"],
+    roofline = wl.roofline(C, T, ms_per_launch, peaks) if hasattr(wl, "roofline") else dict(bound="hbm", achieved=achieved, peak=peaks["hbm_gbs"], unit="GB/s", frac=achieved / peaks["hbm_gbs"],
                     traffic=getattr(wl, "ncu_traffic_bytes", None), kernel=wl.symbol if not args.kernel else f"{wl.module[8:]}_{kernel}",
                     peak_source=peaks["source"],
                     algorithmic_bytes_per_transition=wl.bytes_per_transition,
@@ -451,7 +514,7 @@ def run_native(args, wl, rank, world, local, torch, dist):
         from tests.oracle_binding import oracle
         orc = oracle()
         nt = host_threads()
-        Cs = 2 * nt
+        Cs = getattr(wl, "cpu_chains_per_thread", 2) * nt
         stc = wl.init_state(Cs, 0)
         per_tr = calibrate(wl, orc, stc, nt)
         Ts = int(max(1, min(50000000, 12.0 / max(per_tr, 1e-12))))

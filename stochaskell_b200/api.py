@@ -98,14 +98,14 @@ class Module:
             if not t:
                 continue
             if t[0] == "field":
-                self.fields[t[1]] = dict(index=len(self.fields), state=(t[2] == "state"),
-                                         dtype=np.int32 if t[3] == "i32" else np.float64, len=t[4])
-            elif t[0] == "kernel":
+                dt = {"i32": np.int32, "f32": np.float32, "bf16": np.uint16}.get(t[3], np.float64)
+                self.fields[t[1]] = dict(index=len(self.fields), state=(t[2] == "state"), kind=t[2], dtype=dt, len=t[4])
+            elif t[0] == "kernel" or (t[0] == "plan" and t[2] == "kernel"):
                 self.kernels.append(t[1])
             elif t[0] == "param":
                 self.params[t[1]] = float(t[2])
             elif t[0] == "nparam":
-                self.nparam = int(t[1])
+                self.nparam = int(t[1]) if t[1].isdigit() else 0   # an expression: ask stk_num_params(chains)
             elif t[0] == "name":
                 self.name = t[1]
 
@@ -175,7 +175,7 @@ class Chains:
 
     def logp_grad(self):
         lp = np.empty(self.n)
-        g = np.empty((self.module.nparam, self.n))
+        g = np.empty((lib().stk_num_params(self._h), self.n))
         check(lib().stk_logp_grad(self._h, _ptr(lp), _ptr(g)))
         return lp, g
 

@@ -28,6 +28,22 @@
  *          y = ceil(flen[items_field] / items_per_block) tiles of the per-item work of one transition (e.g. the
  *          assignment step of a Gibbs sweep over the observations); the main kernel then finishes the transition.
  *   entry  <logp|logp_grad|simulate> <symbol> <block> <chains_per_block> <smem_fixed> <smem_field|-> <smem_bytes_per_elem>
+ *   plan   <name> <kernel|logp|logp_grad|simulate|prepare> <loop-param|->
+ *   stage  <plan> <init|pre|body|post> <symbol> <block> <gx> <gy> <smem> [coop]
+ *          A plan is a transition kernel (or an entry) made of several launches — what a model needs when one
+ *          transition is a sequence of grid-wide steps (a matrix product over all chains, then an elementwise
+ *          update, ...).  Per stk_step call the runtime runs the `init` stages once if the chains are dirty
+ *          (data or state uploaded since the last launch); then per transition: the `pre` stages, par[loop-param]
+ *          times the `body` stages (StkArgs.iter = 0.., StkArgs.n_iter = the count), the `post` stages.  An entry
+ *          plan runs its stages once, in order.  A `prepare` plan runs before any other launch whenever a data
+ *          field changed (per-data-set precomputation into `work` fields); if the module has an i32 work field
+ *          named `info`, a non-zero info[0] after prepare is reported as an error.
+ *          gx / gy: <int> | sms | chains/<k> | @<field>/<k> (ceiling division; `sms` = SM count of the device);
+ *          `coop` launches cooperatively (grid-wide sync allowed, grid must be co-resident).
+ * Field kinds: `state` (per chain, [len][n_chains]), `data` (uploaded, shared by all chains), `work` (runtime-
+ * allocated scratch shared by all chains, len = total elements).  Types f64 | i32 | f32 | bf16.  <len> is a product
+ * of terms <int> | @<field> | @<field>^<k> (length of the field rounded up to a multiple of k) | chains | chains^<k>.
+ * `nparam` accepts the same expressions (models whose parameter count follows the data).
  * Launch geometry: grid = ceil(n_chains / chains_per_block) CTAs of <block>
  * threads, dynamic smem = smem_fixed + flen[smem_field] * bytes_per_elem.
  *
@@ -58,6 +74,10 @@ struct StkArgs {
   double* out_grad;            /* [P][n_chains]                               */
   unsigned long long* accept;  /* [n_chains] accepted-transition counters     */
   double* scratch;             /* pre-pass output [n_steps][k][n_chains], or NULL */
+  long long iter;              /* plan stages: index of the body iteration    */
+  long long n_iter;            /* plan stages: body iterations per transition (0 outside a transition plan) */
+  int sm_count;                /* SMs of the device                           */
+  int stage_kind;              /* 0 init, 1 pre, 2 body, 3 post, 4 entry/prepare */
 };
 
 #endif /* STK_ABI_H */

@@ -126,19 +126,25 @@ std::string lib_dir() {
   return ".";
 }
 
-struct FieldDesc { std::string name; bool is_state; bool is_i32; long long len; std::string len_ref; bool sorted = false; };
+struct FieldDesc {
+  std::string name; bool is_state; bool is_i32; long long len; std::string len_ref; bool sorted = false;
+  bool is_work = false; int esize = 8; std::string len_expr;   // len_expr: set when <len> is not a plain integer
+};
+struct StageDesc { int kind = 0; std::string symbol; int block = 0; std::string gx, gy; long long smem = 0; bool coop = false; cudaKernel_t k = nullptr; };
+struct PlanDesc { std::string name, role, loop_param; std::vector<StageDesc> stages; };
 struct KernelDesc {
   std::string name, symbol;
   int block = 0, cpb = 1; long long smem_fixed = 0; std::string smem_field; long long smem_per = 0;
   cudaKernel_t k = nullptr;
   std::string pre_symbol; int pre_block = 0; long long pre_per = 0; cudaKernel_t pre_k = nullptr;
   std::string ph_symbol, ph_field; int ph_block = 0, ph_cpb = 1; long long ph_items = 1, ph_smem = 0; cudaKernel_t ph_k = nullptr;
+  int plan = -1;   // index into stk_module::plans when this transition kernel / entry is a plan
 };
 
 }  // namespace
 
 struct stk_ctx {
-  int device; cudaStream_t stream;
+  int device; cudaStream_t stream; int sm_count = 0;
   cudaLibrary_t diag_lib = nullptr; cudaKernel_t k_moments = nullptr, k_acov = nullptr;
 };
 
@@ -153,6 +159,9 @@ struct stk_module {
   std::vector<KernelDesc> kernels;
   KernelDesc entry[3];  // logp, logp_grad, simulate
   bool has_entry[3] = {false, false, false};
+  std::vector<PlanDesc> plans;
+  int prepare_plan = -1;
+  std::string nparam_expr;
 };
 
 struct stk_chains {
@@ -166,6 +175,8 @@ struct stk_chains {
   double* out_lp = nullptr; double* out_grad = nullptr;
   unsigned long long* accept = nullptr;
   double* scratch = nullptr; size_t scratch_bytes = 0;
+  bool dirty_data = true, dirty_state = true;   // plans: run `prepare` / `init` stages before the next launch
+  long long grad_cap = 0;
 };
 
 namespace {
@@ -201,13 +212,20 @@ int parse_desc(stk_module* m) {
     if (!(ls >> kw)) continue;
     if (kw == "stk-module") { int v; ls >> v; if (v != 1) return fail(STK_ERR_ARG, "descriptor version %d unsupported", v); header = true; }
     else if (kw == "name") ls >> m->name;
-    else if (kw == "nparam") ls >> m->nparam;
+    else if (kw == "nparam") {
+      std::string v; ls >> v;
+      if (v.find_first_not_of("0123456789") == std::string::npos) m->nparam = atoi(v.c_str()); else m->nparam_expr = v;
+    }
     else if (kw == "field") {
       FieldDesc f; std::string kind, ty, len;
       if (!(ls >> f.name >> kind >> ty >> len)) return fail(STK_ERR_ARG, "bad field line: %s", line.c_str());
-      f.is_state = (kind == "state"); f.is_i32 = (ty == "i32");
-      if (!len.empty() && len[0] == '@') { f.len = 0; f.len_ref = len.substr(1); }
-      else f.len = atoll(len.c_str());
+      f.is_state = (kind == "state"); f.is_work = (kind == "work"); f.is_i32 = (ty == "i32");
+      f.esize = (ty == "i32" || ty == "f32") ? 4 : ty == "bf16" ? 2 : 8;
+      if (len.find_first_not_of("0123456789") == std::string::npos) f.len = atoll(len.c_str());
+      else {
+        f.len = 0; f.len_expr = len;
+        if (len[0] == '@' && len.find_first_of("*^") == std::string::npos) f.len_ref = len.substr(1);
+      }
       { std::string attr; while (ls >> attr) if (attr == "sorted") f.sorted = true; }
       if ((int)m->fields.size() >= STK_MAX_FIELDS) return fail(STK_ERR_ARG, "too many fields");
       m->fields.push_back(f);
@@ -221,6 +239,30 @@ int parse_desc(stk_module* m) {
     } else if (kw == "kernel") {
       KernelDesc k; if (parse_kernel_line(ls, &k)) return fail(STK_ERR_ARG, "bad kernel line: %s", line.c_str());
       m->kernels.push_back(k);
+    } else if (kw == "plan") {
+      PlanDesc p;
+      if (!(ls >> p.name >> p.role >> p.loop_param)) return fail(STK_ERR_ARG, "bad plan line: %s", line.c_str());
+      if (p.loop_param == "-") p.loop_param.clear();
+      int pi = (int)m->plans.size();
+      KernelDesc k; k.name = p.name; k.plan = pi;
+      if (p.role == "kernel") m->kernels.push_back(k);
+      else if (p.role == "prepare") m->prepare_plan = pi;
+      else {
+        int e = p.role == "logp" ? 0 : p.role == "logp_grad" ? 1 : p.role == "simulate" ? 2 : -1;
+        if (e < 0) return fail(STK_ERR_ARG, "plan %s: unknown role %s", p.name.c_str(), p.role.c_str());
+        m->entry[e] = k; m->has_entry[e] = true;
+      }
+      m->plans.push_back(p);
+    } else if (kw == "stage") {
+      std::string pn, kind, opt; StageDesc sd;
+      if (!(ls >> pn >> kind >> sd.symbol >> sd.block >> sd.gx >> sd.gy >> sd.smem) || sd.block <= 0) return fail(STK_ERR_ARG, "bad stage line: %s", line.c_str());
+      sd.kind = kind == "init" ? 0 : kind == "pre" ? 1 : kind == "body" ? 2 : kind == "post" ? 3 : -1;
+      if (sd.kind < 0) return fail(STK_ERR_ARG, "stage: unknown kind %s", kind.c_str());
+      while (ls >> opt) { if (opt == "coop") sd.coop = true; else return fail(STK_ERR_ARG, "stage: unknown option %s", opt.c_str()); }
+      PlanDesc* pl = nullptr;
+      for (auto& p : m->plans) if (p.name == pn) pl = &p;
+      if (!pl) return fail(STK_ERR_ARG, "stage names unknown plan %s", pn.c_str());
+      pl->stages.push_back(sd);
     } else if (kw == "entry") {
       KernelDesc k; if (parse_kernel_line(ls, &k)) return fail(STK_ERR_ARG, "bad entry line: %s", line.c_str());
       int e = k.name == "logp" ? 0 : k.name == "logp_grad" ? 1 : k.name == "simulate" ? 2 : -1;
@@ -232,22 +274,59 @@ int parse_desc(stk_module* m) {
   return STK_OK;
 }
 
+// <len> / <gx> expressions: product (or one ceiling quotient) of terms <int> | sms | chains[^k] | @field[^k];
+// 0 when a referenced field has no size yet, -1 on a syntax error
+long long eval_term(const stk_chains* c, const std::string& t) {
+  std::string base = t; long long round = 0;
+  size_t h = t.find('^');
+  if (h != std::string::npos) { base = t.substr(0, h); round = atoll(t.c_str() + h + 1); if (round <= 0) return -1; }
+  long long v;
+  if (base == "chains") v = c->n;
+  else if (base == "sms") v = c->mod->ctx->sm_count;
+  else if (!base.empty() && base[0] == '@') { int r = field_index(c->mod, base.substr(1)); if (r < 0) return -1; v = c->flen[r]; }
+  else if (!base.empty() && base.find_first_not_of("0123456789") == std::string::npos) v = atoll(base.c_str());
+  else return -1;
+  if (round > 0 && v > 0) v = (v + round - 1) / round * round;
+  return v;
+}
+long long eval_expr(const stk_chains* c, const std::string& e) {
+  size_t sl = e.find('/');
+  if (sl != std::string::npos) {
+    long long a = eval_expr(c, e.substr(0, sl)), b = atoll(e.c_str() + sl + 1);
+    if (a < 0 || b <= 0) return -1;
+    return (a + b - 1) / b;
+  }
+  long long v = 1; size_t i = 0;
+  while (i <= e.size()) {
+    size_t j = e.find('*', i);
+    if (j == std::string::npos) j = e.size();
+    long long t = eval_term(c, e.substr(i, j - i));
+    if (t < 0) return -1;
+    v *= t; i = j + 1;
+  }
+  return v;
+}
 long long state_len(const stk_chains* c, int f) {
   const FieldDesc& fd = c->mod->fields[f];
   if (fd.len > 0) return fd.len;
-  if (!fd.len_ref.empty()) { int r = field_index(c->mod, fd.len_ref); if (r >= 0) return c->flen[r]; }
+  if (!fd.len_expr.empty()) { long long v = eval_expr(c, fd.len_expr); return v > 0 ? v : 0; }
   return c->flen[f];
 }
-size_t elem_size(const FieldDesc& f) { return f.is_i32 ? 4 : 8; }
+size_t elem_size(const FieldDesc& f) { return (size_t)f.esize; }
+long long num_params(const stk_chains* c) {
+  if (c->mod->nparam_expr.empty()) return c->mod->nparam;
+  long long v = eval_expr(c, c->mod->nparam_expr);
+  return v > 0 ? v : 0;
+}
 
 // allocate deferred-size state fields whose size is now known
 int ensure_fields(stk_chains* c) {
   for (size_t f = 0; f < c->mod->fields.size(); ++f) {
     const FieldDesc& fd = c->mod->fields[f];
-    if (!fd.is_state || c->dptr[f]) continue;
+    if (!(fd.is_state || fd.is_work) || c->dptr[f]) continue;
     long long L = state_len(c, (int)f);
     if (L <= 0) continue;
-    size_t bytes = (size_t)L * (size_t)c->n * elem_size(fd);
+    size_t bytes = (size_t)L * (fd.is_state ? (size_t)c->n : 1) * elem_size(fd);
     CU(cudaMalloc(&c->dptr[f], bytes));
     CU(cudaMemsetAsync(c->dptr[f], 0, bytes, c->mod->ctx->stream));
     c->flen[f] = L;
@@ -255,17 +334,131 @@ int ensure_fields(stk_chains* c) {
   return STK_OK;
 }
 
-int launch(stk_chains* c, KernelDesc& k, long long n_steps, cudaStream_t st) {
+void fill_args(stk_chains* c, long long n_steps, StkArgs* ap) {
   stk_module* m = c->mod;
-  int rc = ensure_fields(c);
-  if (rc) return rc;
-  StkArgs a;
+  StkArgs& a = *ap;
   memset(&a, 0, sizeof a);
   a.n_chains = c->n; a.chain0 = c->chain0; a.seed = c->seed; a.step0 = c->step; a.n_steps = n_steps;
   for (size_t f = 0; f < m->fields.size(); ++f) { a.field[f] = c->dptr[f]; a.flen[f] = c->flen[f]; }
   for (size_t p = 0; p < c->par.size(); ++p) a.par[p] = c->par[p];
   a.draws = c->draws; a.draw_slots = c->slots; a.draw_thin = c->thin; a.draw_base = c->recorded; a.n_rec = c->nrec;
   a.out_lp = c->out_lp; a.out_grad = c->out_grad; a.accept = c->accept; a.scratch = c->scratch;
+  a.sm_count = m->ctx->sm_count; a.stage_kind = 4;
+}
+
+// one stage of a plan
+int launch_stage(stk_chains* c, StageDesc& sd, StkArgs& a, cudaStream_t st, int kind = -1) {
+  long long gx = eval_expr(c, sd.gx), gy = eval_expr(c, sd.gy);
+  if (gx <= 0 || gy <= 0 || gy > 65535) return fail(STK_ERR_ARG, "stage %s: grid %s x %s evaluates to %lld x %lld", sd.symbol.c_str(), sd.gx.c_str(), sd.gy.c_str(), gx, gy);
+  if (sd.smem > 227 * 1024) return fail(STK_ERR_UNSUPPORTED, "stage %s needs %lld B shared memory (> 227 KB)", sd.symbol.c_str(), sd.smem);
+  if (sd.smem > 48 * 1024)
+    CU(cudaFuncSetAttribute((const void*)sd.k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sd.smem));
+  a.stage_kind = kind >= 0 ? kind : sd.kind;
+  void* params[1] = {&a};
+  TRACE("stage %s grid=%lld x %lld block=%d smem=%lld coop=%d iter=%lld/%lld", sd.symbol.c_str(), gx, gy, sd.block, sd.smem, (int)sd.coop, a.iter, a.n_iter);
+  if (sd.coop) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)gx, (unsigned)gy); cfg.blockDim = dim3((unsigned)sd.block);
+    cfg.dynamicSmemBytes = (size_t)sd.smem; cfg.stream = st;
+    cudaLaunchAttribute at[1]; at[0].id = cudaLaunchAttributeCooperative; at[0].val.cooperative = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    CU(cudaLaunchKernelExC(&cfg, (const void*)sd.k, params));
+  } else {
+    CU(cudaLaunchKernel((const void*)sd.k, dim3((unsigned)gx, (unsigned)gy), dim3((unsigned)sd.block), params, (size_t)sd.smem, st));
+  }
+  g_launches.fetch_add(1);
+  return STK_OK;
+}
+
+// per-data-set precomputation: runs when a data field changed since the last launch
+int run_prepare(stk_chains* c, cudaStream_t st) {
+  stk_module* m = c->mod;
+  if (!c->dirty_data) return STK_OK;
+  int rc = ensure_fields(c);
+  if (rc) return rc;
+  if (m->prepare_plan >= 0) {
+    StkArgs a; fill_args(c, 0, &a);
+    for (auto& sd : m->plans[m->prepare_plan].stages) if ((rc = launch_stage(c, sd, a, st, 4))) return rc;
+    int fi = field_index(m, "info");
+    if (fi >= 0 && m->fields[fi].is_work && c->dptr[fi]) {
+      int info = 0;
+      CU(cudaMemcpyAsync(&info, c->dptr[fi], sizeof info, cudaMemcpyDeviceToHost, st));
+      CU(cudaStreamSynchronize(st));
+      if (info != 0) return fail(STK_ERR_ARG, "module %s: prepare failed, info = %d (e.g. covariance not positive definite at pivot %d)", m->name.c_str(), info, info);
+    }
+  }
+  c->dirty_data = false;
+  return STK_OK;
+}
+
+int ensure_grad(stk_chains* c) {
+  long long P = num_params(c);
+  if (P > 0 && P * c->n > c->grad_cap) {
+    CU(cudaStreamSynchronize(c->mod->ctx->stream));
+    if (c->out_grad) { CU(cudaFree(c->out_grad)); c->out_grad = nullptr; c->grad_cap = 0; }
+    CU(cudaMalloc((void**)&c->out_grad, sizeof(double) * (size_t)P * (size_t)c->n));
+    c->grad_cap = P * c->n;
+  }
+  return STK_OK;
+}
+
+// a plan used as an entry (logp / logp_grad / simulate): its stages once, in order
+int run_entry_plan(stk_chains* c, int pi, cudaStream_t st) {
+  int rc = run_prepare(c, st);
+  if (rc) return rc;
+  if ((rc = ensure_fields(c))) return rc;
+  StkArgs a; fill_args(c, 0, &a);
+  for (auto& sd : c->mod->plans[pi].stages) if ((rc = launch_stage(c, sd, a, st, 4))) return rc;
+  return STK_OK;
+}
+
+// a plan used as a transition kernel: n_steps transitions, host-sequenced
+int run_kernel_plan(stk_chains* c, int pi, long long n_steps, cudaStream_t st) {
+  stk_module* m = c->mod;
+  PlanDesc& pl = m->plans[pi];
+  int rc = run_prepare(c, st);
+  if (rc) return rc;
+  if ((rc = ensure_fields(c))) return rc;
+  long long n_iter = 1;
+  if (!pl.loop_param.empty()) {
+    int pidx = -1;
+    for (size_t i = 0; i < m->params.size(); ++i) if (m->params[i].first == pl.loop_param) pidx = (int)i;
+    if (pidx < 0) return fail(STK_ERR_ARG, "plan %s: unknown loop parameter %s", pl.name.c_str(), pl.loop_param.c_str());
+    n_iter = (long long)c->par[pidx];
+    if (n_iter < 1) return fail(STK_ERR_ARG, "plan %s: %s must be >= 1", pl.name.c_str(), pl.loop_param.c_str());
+  }
+  StkArgs a; fill_args(c, 1, &a);
+  a.n_iter = n_iter;
+  if (c->dirty_state) {
+    for (auto& sd : pl.stages) if (sd.kind == 0 && (rc = launch_stage(c, sd, a, st))) return rc;
+    c->dirty_state = false;
+  }
+  for (long long t = 0; t < n_steps; ++t) {
+    a.step0 = c->step; a.draw_base = c->recorded; a.iter = 0;
+    for (auto& sd : pl.stages) if (sd.kind == 1 && (rc = launch_stage(c, sd, a, st))) return rc;
+    for (long long it = 0; it < n_iter; ++it) {
+      a.iter = it;
+      for (auto& sd : pl.stages) if (sd.kind == 2 && (rc = launch_stage(c, sd, a, st))) return rc;
+    }
+    a.iter = n_iter;
+    for (auto& sd : pl.stages) if (sd.kind == 3 && (rc = launch_stage(c, sd, a, st))) return rc;
+    if (c->draws && c->slots > 0) {
+      unsigned long long s0 = c->step, s1 = c->step + 1;
+      long long add = (long long)(s1 / (unsigned long long)c->thin - s0 / (unsigned long long)c->thin);
+      c->recorded = std::min(c->slots, c->recorded + add);
+    }
+    c->step += 1;
+  }
+  return STK_OK;
+}
+
+int launch(stk_chains* c, KernelDesc& k, long long n_steps, cudaStream_t st) {
+  stk_module* m = c->mod;
+  int rc = run_prepare(c, st);
+  if (rc) return rc;
+  if ((rc = ensure_fields(c))) return rc;
+  StkArgs a;
+  fill_args(c, n_steps, &a);
   if (k.pre_k) {   // pre-pass: one thread per (chain, transition) of this launch
     long long items = c->n * n_steps;
     long long pgrid = (items + k.pre_block - 1) / k.pre_block;
@@ -333,6 +526,7 @@ int stk_ctx_create(int device, stk_ctx** out) {
   if (device < 0 || device >= n) return fail(STK_ERR_ARG, "device %d out of range (0..%d)", device, n - 1);
   CU(cudaSetDevice(device));
   stk_ctx* c = new stk_ctx; c->device = device; c->stream = nullptr;
+  cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device);
   cudaError_t e2 = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
   if (e2 != cudaSuccess) { delete c; return fail(STK_ERR_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(e2)); }
   *out = c;
@@ -435,6 +629,7 @@ int stk_module_load(stk_ctx* ctx, const char* spec, const char* cache_dir, stk_m
   if (rc) { cudaLibraryUnload(m->lib); delete m; return rc; }
   TRACE("descriptor parsed: %zu fields, %zu kernels", m->fields.size(), m->kernels.size());
   auto resolve = [&](KernelDesc& k) -> int {
+    if (k.plan >= 0) return STK_OK;
     TRACE("resolve %s", k.symbol.c_str());
     cudaError_t e3 = cudaLibraryGetKernel(&k.k, m->lib, k.symbol.c_str());
     if (e3 != cudaSuccess) return fail(STK_ERR_ARG, "module %s: kernel symbol %s: %s", m->name.c_str(), k.symbol.c_str(), cudaGetErrorString(e3));
@@ -451,6 +646,14 @@ int stk_module_load(stk_ctx* ctx, const char* spec, const char* cache_dir, stk_m
   };
   for (auto& k : m->kernels) if ((rc = resolve(k))) { cudaLibraryUnload(m->lib); delete m; return rc; }
   for (int i = 0; i < 3; ++i) if (m->has_entry[i] && (rc = resolve(m->entry[i]))) { cudaLibraryUnload(m->lib); delete m; return rc; }
+  for (auto& pl : m->plans)
+    for (auto& sd : pl.stages) {
+      cudaError_t e3 = cudaLibraryGetKernel(&sd.k, m->lib, sd.symbol.c_str());
+      if (e3 != cudaSuccess) {
+        rc = fail(STK_ERR_ARG, "module %s: stage symbol %s: %s", m->name.c_str(), sd.symbol.c_str(), cudaGetErrorString(e3));
+        cudaLibraryUnload(m->lib); delete m; return rc;
+      }
+    }
   *out = m;
   return STK_OK;
 }
@@ -498,7 +701,10 @@ int stk_chains_create(stk_module* m, int64_t n_chains, uint64_t seed, stk_chains
   cudaError_t e = cudaMalloc((void**)&c->accept, sizeof(unsigned long long) * (size_t)n_chains);
   if (e == cudaSuccess) e = cudaMemset(c->accept, 0, sizeof(unsigned long long) * (size_t)n_chains);
   if (e == cudaSuccess) e = cudaMalloc((void**)&c->out_lp, sizeof(double) * (size_t)n_chains);
-  if (e == cudaSuccess && m->nparam > 0) e = cudaMalloc((void**)&c->out_grad, sizeof(double) * (size_t)n_chains * (size_t)m->nparam);
+  if (e == cudaSuccess && m->nparam > 0) {
+    e = cudaMalloc((void**)&c->out_grad, sizeof(double) * (size_t)n_chains * (size_t)m->nparam);
+    if (e == cudaSuccess) c->grad_cap = (long long)n_chains * m->nparam;
+  }
   if (e != cudaSuccess) { stk_chains_destroy(c); return fail(STK_ERR_CUDA, "cudaMalloc: %s", cudaGetErrorString(e)); }
   for (int f : m->record) c->nrec += 0 * f;  // sized at stk_record time (capacities may be deferred)
   *out = c;
@@ -536,9 +742,15 @@ int stk_set_data(stk_chains* c, int field, const void* host, size_t bytes) {
   if (bytes % es) return fail(STK_ERR_ARG, "data field %s: %zu bytes is not a multiple of %zu", fd.name.c_str(), bytes, es);
   long long len = (long long)(bytes / es);
   if (fd.len > 0 && len != fd.len) return fail(STK_ERR_ARG, "data field %s expects %lld elements, got %lld", fd.name.c_str(), fd.len, len);
-  if (c->dptr[field] && c->flen[field] != len) { CU(cudaStreamSynchronize(m->ctx->stream)); CU(cudaFree(c->dptr[field])); c->dptr[field] = nullptr; }
+  if (c->dptr[field] && c->flen[field] != len) {
+    CU(cudaStreamSynchronize(m->ctx->stream)); CU(cudaFree(c->dptr[field])); c->dptr[field] = nullptr;
+    // fields sized by an expression follow the data: drop them, ensure_fields re-creates them (zeroed)
+    for (size_t f = 0; f < m->fields.size(); ++f)
+      if (!m->fields[f].len_expr.empty() && c->dptr[f]) { CU(cudaFree(c->dptr[f])); c->dptr[f] = nullptr; c->flen[f] = 0; }
+  }
   if (!c->dptr[field]) CU(cudaMalloc(&c->dptr[field], bytes ? bytes : 8));
   c->flen[field] = len;
+  c->dirty_data = true; c->dirty_state = true;
   // `sorted` data fields (kernels that binary-search them; a sum over the observations does not depend on
   // their order): upload an ascending copy.
   std::vector<double> tmp;
@@ -561,7 +773,7 @@ int stk_set_state(stk_chains* c, int field, const void* host, size_t bytes, int 
   if ((rc = ensure_fields(c))) return rc;
   const FieldDesc& fd = m->fields[field];
   size_t es = elem_size(fd);
-  if (c->flen[field] <= 0 && fd.len == 0 && fd.len_ref.empty()) {
+  if (c->flen[field] <= 0 && fd.len == 0 && fd.len_expr.empty()) {
     // a state field declared with length 0 (vectors of stkc-generated modules) takes its capacity from the first upload
     size_t per = broadcast ? es : es * (size_t)c->n;
     if (bytes == 0 || bytes % per) return fail(STK_ERR_ARG, "state field %s: %zu bytes is not a whole number of %s", fd.name.c_str(), bytes, broadcast ? "elements" : "[.][n_chains] rows");
@@ -570,6 +782,7 @@ int stk_set_state(stk_chains* c, int field, const void* host, size_t bytes, int 
   }
   long long L = c->flen[field];
   if (L <= 0 || !c->dptr[field]) return fail(STK_ERR_ARG, "state field %s has no size yet", fd.name.c_str());
+  c->dirty_state = true;
   if (broadcast) {
     if (bytes != (size_t)L * es) return fail(STK_ERR_ARG, "state field %s (broadcast) expects %zu bytes, got %zu", fd.name.c_str(), (size_t)L * es, bytes);
     std::vector<char> tmp((size_t)L * (size_t)c->n * es);
@@ -630,6 +843,11 @@ static int run_entry(stk_chains* c, int e, const char* what) {
   if (!c->mod->has_entry[e]) return fail(STK_ERR_UNSUPPORTED, "module %s has no %s entry", c->mod->name.c_str(), what);
   int rc = need_device(c->mod->ctx);
   if (rc) return rc;
+  if (e == 1 && (rc = ensure_grad(c))) return rc;
+  if (c->mod->entry[e].plan >= 0) {
+    if (e == 2) c->dirty_state = true;
+    return run_entry_plan(c, c->mod->entry[e].plan, c->mod->ctx->stream);
+  }
   return launch(c, c->mod->entry[e], 0, c->mod->ctx->stream);
 }
 
@@ -646,7 +864,7 @@ int stk_logp_grad(stk_chains* c, double* lp_host, double* grad_host) {
   if (rc) return rc;
   cudaStream_t st = c->mod->ctx->stream;
   if (lp_host) CU(cudaMemcpyAsync(lp_host, c->out_lp, sizeof(double) * (size_t)c->n, cudaMemcpyDeviceToHost, st));
-  if (grad_host) CU(cudaMemcpyAsync(grad_host, c->out_grad, sizeof(double) * (size_t)c->n * (size_t)c->mod->nparam, cudaMemcpyDeviceToHost, st));
+  if (grad_host) CU(cudaMemcpyAsync(grad_host, c->out_grad, sizeof(double) * (size_t)c->n * (size_t)num_params(c), cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
   return STK_OK;
 }
@@ -660,6 +878,7 @@ int stk_step(stk_chains* c, int kernel_id, int64_t n_transitions, stk_stream str
   if (rc) return rc;
   cudaStream_t st = stream ? (cudaStream_t)stream : c->mod->ctx->stream;
   KernelDesc& kd = c->mod->kernels[kernel_id];
+  if (kd.plan >= 0) return run_kernel_plan(c, kd.plan, n_transitions, st);
   // a kernel with a pre-pass runs in chunks whose scratch ([transitions][k][chains] doubles) fits the budget
   long long chunk = n_transitions;
   if (kd.ph_k) chunk = 1;
@@ -696,6 +915,8 @@ int stk_simulate(stk_chains* c, stk_stream stream) {
   int rc = need_device(c->mod->ctx);
   if (rc) return rc;
   cudaStream_t st = stream ? (cudaStream_t)stream : c->mod->ctx->stream;
+  c->dirty_state = true;
+  if (c->mod->entry[2].plan >= 0) return run_entry_plan(c, c->mod->entry[2].plan, st);
   return launch(c, c->mod->entry[2], 0, st);
 }
 
@@ -738,7 +959,7 @@ int stk_sync(stk_chains* c) {
   return STK_OK;
 }
 
-int stk_num_params(stk_chains* c) { return c ? c->mod->nparam : fail(STK_ERR_ARG, "null chains"); }
+int stk_num_params(stk_chains* c) { return c ? (int)num_params(c) : fail(STK_ERR_ARG, "null chains"); }
 int64_t stk_num_chains(stk_chains* c) { return c ? c->n : (int64_t)fail(STK_ERR_ARG, "null chains"); }
 
 }  // extern "C"

@@ -312,7 +312,27 @@ class GPHMC:
                          "fp64 DFMA peak of a B200 is ~37 TFLOP/s")
 
 
-WORKLOADS = {"linreg_hmc": LinregHMC, "coal_rj": CoalRJ, "birats_hmc": BiratsHMC, "dp_gibbs": DPGibbs, "gp_hmc": GPHMC}
+class GPHMCTC(GPHMC):
+    """C3 on the tensor cores (fp32 tier, 1e-5): the two products as split-bf16 tcgen05.mma (3 x 3 bf16 terms, 6 MMAs
+    per useful product, fp32 accumulation in TMEM); everything else as gp_hmc."""
+    name = "gp_hmc_tc"
+    module = "builtin:gp_tc"
+    symbol = "gp_tc_gemm1"
+    dtype = "bf16x3 (fp32-equivalent operands, fp32 accumulate); state f64"
+    transitions_per_step = 8
+
+    def roofline(self, C, T, ms_per_launch, peaks):
+        r = super().roofline(C, T, ms_per_launch, peaks)
+        r["kernel"] = "gp_tc_gemm1 + gp_tc_gemm2_leap"
+        r["tensor_flops_issued_tflops"] = 6 * r["achieved"]
+        r["frac_issued"] = 6 * r["achieved"] / r["peak"]
+        r["note"] = ("useful flops = L x 2 n^2 per chain and transition; each useful product is issued as 6 bf16 tcgen05.mma "
+                     "terms (hi/mid/lo splits of both operands), so the tensor pipe executes 6x the useful flops: `frac` is "
+                     "useful/peak, `frac_issued` is issued/peak")
+        return r
+
+
+WORKLOADS = {"gp_hmc_tc": GPHMCTC, "linreg_hmc": LinregHMC, "coal_rj": CoalRJ, "birats_hmc": BiratsHMC, "dp_gibbs": DPGibbs, "gp_hmc": GPHMC}
 DEFAULT_WORKLOAD = "coal_rj"
 
 

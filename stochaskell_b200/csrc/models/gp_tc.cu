@@ -7,17 +7,19 @@
 //   * L and L^T are split once per data set (gp_tc_split_L); W and R are written as split-bf16 by the epilogue of
 //     the product (or the begin / finish stage) that produces them, so no separate conversion pass runs per step;
 //   * one CTA = one 128 x 128 output tile; warps 0-3 stage the operand tiles with cp.async into the canonical
-//     128-byte-swizzled layouts (A = L rows: K-major; B = W/R rows [k][chain]: MN-major), warp 4 lane 0 issues the
-//     MMAs, two 96 KB stages hand over through mbarriers (full: 128 producer arrivals, empty: tcgen05.commit);
+//     128-byte-swizzled MN-major layouts (both operands are stored [k][m] / [k][chain], contraction index major),
+//     warp 4 lane 0 issues the MMAs, four 48 KB stages (32 k each) hand over through mbarriers (full: 128 producer
+//     arrivals after cp.async.wait_group + fence.proxy.async, empty: tcgen05.commit);
 //   * the same four warps then read the accumulator with tcgen05.ld (thread = output row) and run the fused epilogue
 //     of gp.cu (r = z - sigmoid(g) / the leapfrog update), writing fp64 state and the split-bf16 operand of the next
 //     product.  Row tiles are issued longest-first (the k range of a tile is triangular).
 #define GP_TC 1
 #include "gp.cu"
 
-#define TC_BK 64
-#define TC_STAGE_BYTES 98304          // 3 x (128 x 64) bf16 A + 3 x (64 x 128) bf16 B
-#define TC_SPLIT_BYTES 16384
+#define TC_BK 32
+#define TC_STAGES 4
+#define TC_STAGE_BYTES 49152          // 3 x (32 k x 128 m) bf16 A + 3 x (32 k x 128 chains) bf16 B
+#define TC_SPLIT_BYTES 8192
 
 // ---- PTX wrappers -----------------------------------------------------------------------------------------------
 __device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
@@ -68,37 +70,35 @@ __device__ __forceinline__ unsigned long long smem_desc(unsigned addr, unsigned 
   return (unsigned long long)((addr >> 4) & 0x3fff) | ((unsigned long long)((lbo_bytes >> 4) & 0x3fff) << 16) |
          ((unsigned long long)((sbo_bytes >> 4) & 0x3fff) << 32) | (1ULL << 46) | (2ULL << 61);
 }
-// instruction descriptor (InstrDescriptor): D = f32, A = B = bf16, A K-major, B MN-major, N = 128, M = 128
-#define TC_IDESC ((1u << 4) | (1u << 7) | (1u << 10) | (0u << 15) | (1u << 16) | ((128u >> 3) << 17) | ((128u >> 4) << 24))
+// instruction descriptor (InstrDescriptor): D = f32, A = B = bf16, A and B MN-major, N = 128, M = 128
+#define TC_IDESC ((1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((128u >> 3) << 17) | ((128u >> 4) << 24))
 
 // ---- operand staging (warps 0-3) ---------------------------------------------------------------------------------
-// A tile, K-major, 128 rows x 64 k, SWIZZLE_128B: byte (r, k) = (r/8) 1024 + (r%8) 128 + ((k/8) ^ (r%8)) 16 + (k%8) 2
-// B tile, MN-major, 64 k x 128 columns, SWIZZLE_128B, two 64-column atoms 8192 B apart:
-//   byte (k, c) = (c/64) 8192 + (k/8) 1024 + (k%8) 128 + (((c%64)/8) ^ (k%8)) 16 + (c%8) 2
-__device__ __forceinline__ void tc_load_stage(unsigned char* st, const __nv_bfloat16* Aop, const __nv_bfloat16* Bop, long long ld,
-                                              long long C, long long m0, long long c0, long long k0, int tid, bool vec) {
-  const long long planeA = ld * ld, planeB = ld * C;
+// A and B tiles are both MN-major, 32 k x 128 (m | chains), SWIZZLE_128B, two 64-wide atoms 4096 B apart:
+//   byte (k, c) = (c/64) 4096 + (k/8) 1024 + (k%8) 128 + (((c%64)/8) ^ (k%8)) 16 + (c%8) 2
+// Thread t of the 128 producers owns 16-byte chunk (t & 15) of rows (t >> 4) + 8u, u = 0..3, of every tile: its
+// shared-memory offset and global pointers are computed once, the loop only adds strides.
+struct TcLoader {
+  const __nv_bfloat16* pa; const __nv_bfloat16* pb;   // chunk of row k = kbeg + (t >> 4), split 0
+  long long planeA, planeB, rowA8, rowB8;             // elements: split stride, 8-row stride
+  unsigned soff;                                      // byte offset of the chunk inside a split tile (u = 0)
+  int bvalid;                                         // chains of the B chunk inside [0, C): 8 = whole, 0 = none
+  bool vec;
+};
+__device__ __forceinline__ void tc_load_stage(unsigned char* st, const TcLoader& L) {
 #pragma unroll
   for (int s = 0; s < 3; ++s) {
-    unsigned char* as = st + s * TC_SPLIT_BYTES;
-    unsigned char* bs = st + 3 * TC_SPLIT_BYTES + s * TC_SPLIT_BYTES;
+    unsigned char* as = st + s * TC_SPLIT_BYTES + L.soff;
+    unsigned char* bs = st + (3 + s) * TC_SPLIT_BYTES + L.soff;
+    const __nv_bfloat16* ga = L.pa + s * L.planeA;
+    const __nv_bfloat16* gb = L.pb + s * L.planeB;
 #pragma unroll
-    for (int u = 0; u < 8; ++u) {
-      const int q = tid + 128 * u;
-      {  // A: 128 rows x 8 chunks
-        const int r = q >> 3, j = q & 7;
-        cp_async16(as + (r >> 3) * 1024 + (r & 7) * 128 + ((j ^ (r & 7)) << 4), Aop + s * planeA + (m0 + r) * ld + k0 + j * 8, 16);
-      }
-      {  // B: 64 k x 16 chunks
-        const int k = q >> 4, jj = q & 15, j = jj & 7;
-        unsigned char* dst = bs + (jj >> 3) * 8192 + (k >> 3) * 1024 + (k & 7) * 128 + ((j ^ (k & 7)) << 4);
-        const long long c = c0 + jj * 8;
-        const __nv_bfloat16* src = Bop + s * planeB + (k0 + k) * C + c;
-        if (vec) cp_async16(dst, c < C ? src : Bop, c < C ? 16 : 0);
-        else {   // chain count not a multiple of 8: rows are not 16-byte aligned
-          __nv_bfloat16* d = reinterpret_cast<__nv_bfloat16*>(dst);
-          for (int e = 0; e < 8; ++e) d[e] = c + e < C ? src[e] : __float2bfloat16(0.f);
-        }
+    for (int u = 0; u < 4; ++u) {
+      cp_async16(as + u * 1024, ga + u * L.rowA8, 16);
+      if (L.vec) cp_async16(bs + u * 1024, L.bvalid ? gb + u * L.rowB8 : gb, L.bvalid ? 16 : 0);
+      else {   // chain count not a multiple of 8: rows are not 16-byte aligned
+        __nv_bfloat16* d = reinterpret_cast<__nv_bfloat16*>(bs + u * 1024);
+        for (int e = 0; e < 8; ++e) d[e] = e < L.bvalid ? gb[u * L.rowB8 + e] : __float2bfloat16(0.f);
       }
     }
   }
@@ -112,24 +112,24 @@ template <int MODE>
 __device__ __forceinline__ void gp_tc_gemm(const StkArgs& a) {
   extern __shared__ unsigned char smraw[];
   unsigned char* smem = (unsigned char*)(((unsigned long long)smraw + 1023) & ~1023ULL);
-  unsigned long long* bars = (unsigned long long*)(smem + 2 * TC_STAGE_BYTES);   // full[2], empty[2], accum
-  unsigned* tmem_slot = (unsigned*)(bars + 8);
+  unsigned long long* bars = (unsigned long long*)(smem + TC_STAGES * TC_STAGE_BYTES);   // full[4], empty[4], accum
+  unsigned* tmem_slot = (unsigned*)(bars + 16);
   const long long n = a.flen[F_X], ld = ld_of(n), C = a.n_chains;
   const int tid = threadIdx.x, warp = tid >> 5;
   const int nt = gridDim.y;
   const int I = MODE == 1 ? nt - 1 - (int)blockIdx.y : (int)blockIdx.y;
   const long long m0 = (long long)I * 128, c0 = (long long)blockIdx.x * 128;
-  const __nv_bfloat16* Aop = (const __nv_bfloat16*)a.field[MODE == 1 ? F_LA : F_LTA];
+  // A operand stored [k][m]: product 1 (A = L) reads the split of L^T's rows, product 2 (A = L^T) the split of L's
+  const __nv_bfloat16* Aop = (const __nv_bfloat16*)a.field[MODE == 1 ? F_LTA : F_LA];
   const __nv_bfloat16* Bop = (const __nv_bfloat16*)a.field[MODE == 1 ? F_WB : F_RB];
   const long long kbeg = MODE == 1 ? 0 : m0, kend = MODE == 1 ? m0 + 128 : ld;
   const int ktiles = (int)((kend - kbeg) / TC_BK);
   const bool vec = (C & 7) == 0;
   int* info = (int*)a.field[F_INFO];
-  const unsigned full0 = smem_u32(bars), empty0 = smem_u32(bars + 2), accum = smem_u32(bars + 4);
+  const unsigned full0 = smem_u32(bars), empty0 = smem_u32(bars + TC_STAGES), accum = smem_u32(bars + 2 * TC_STAGES);
 
   if (tid == 0) {
-    mbar_init(full0, 128); mbar_init(full0 + 8, 128);
-    mbar_init(empty0, 1); mbar_init(empty0 + 8, 1);
+    for (int i = 0; i < TC_STAGES; ++i) { mbar_init(full0 + 8 * i, 128); mbar_init(empty0 + 8 * i, 1); }
     mbar_init(accum, 1);
     asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
   }
@@ -144,119 +144,159 @@ __device__ __forceinline__ void gp_tc_gemm(const StkArgs& a) {
 
   if (warp < 4) {
     // ===== producers =====
-    for (int t = 0; t < ktiles; ++t) {
-      const int st = t & 1;
-      if (t >= 2 && !mbar_wait(empty0 + 8 * st, ((t >> 1) & 1) ^ 1)) info[1] = 1;
-      tc_load_stage(smem + st * TC_STAGE_BYTES, Aop, Bop, ld, C, m0, c0, kbeg + (long long)t * TC_BK, tid, vec);
-      if (t >= 1) { cp_async_wait<1>(); fence_proxy_async(); mbar_arrive(full0 + 8 * ((t - 1) & 1)); }
+    TcLoader Ld;
+    {
+      const int kr = tid >> 4, jj = tid & 15;
+      Ld.planeA = ld * ld; Ld.planeB = ld * C; Ld.rowA8 = 8 * ld; Ld.rowB8 = 8 * C; Ld.vec = vec;
+      Ld.soff = (unsigned)((jj >> 3) * 4096 + kr * 128 + (((jj & 7) ^ kr) << 4));
+      const long long c = c0 + jj * 8;
+      Ld.bvalid = c >= C ? 0 : (C - c >= 8 ? 8 : (int)(C - c));
+      Ld.pa = Aop + (kbeg + kr) * ld + m0 + jj * 8;
+      Ld.pb = Bop + (kbeg + kr) * C + (Ld.bvalid ? c : 0);
     }
-    cp_async_wait<0>(); fence_proxy_async(); mbar_arrive(full0 + 8 * ((ktiles - 1) & 1));
+    for (int t = 0; t < ktiles; ++t) {
+      const int st = t & (TC_STAGES - 1);
+      if (t >= TC_STAGES && !mbar_wait(empty0 + 8 * st, ((t / TC_STAGES) & 1) ^ 1)) info[1] = 1;
+      tc_load_stage(smem + st * TC_STAGE_BYTES, Ld);
+      Ld.pa += TC_BK * ld; Ld.pb += TC_BK * C;
+      if (t >= 2) { cp_async_wait<2>(); fence_proxy_async(); mbar_arrive(full0 + 8 * ((t - 2) & (TC_STAGES - 1))); }
+    }
+    cp_async_wait<1>(); fence_proxy_async(); mbar_arrive(full0 + 8 * ((ktiles - 2) & (TC_STAGES - 1)));
+    cp_async_wait<0>(); fence_proxy_async(); mbar_arrive(full0 + 8 * ((ktiles - 1) & (TC_STAGES - 1)));
   } else if (tid == 128) {
     // ===== MMA issuer (one thread) =====
     for (int t = 0; t < ktiles; ++t) {
-      const int st = t & 1;
-      if (!mbar_wait(full0 + 8 * st, (t >> 1) & 1)) info[1] = 2;
+      const int st = t & (TC_STAGES - 1);
+      if (!mbar_wait(full0 + 8 * st, (t / TC_STAGES) & 1)) info[1] = 2;
       tc_fence_after();
       const unsigned sa = smem_u32(smem + st * TC_STAGE_BYTES), sb = sa + 3 * TC_SPLIT_BYTES;
       // (A split, B split): smallest terms first, hi*hi last
       const int pa[6] = {2, 0, 1, 1, 0, 0}, pb[6] = {0, 2, 1, 0, 1, 0};
 #pragma unroll
       for (int q = 0; q < 6; ++q) {
-        const unsigned long long da = smem_desc(sa + pa[q] * TC_SPLIT_BYTES, 16, 1024);
-        const unsigned long long db = smem_desc(sb + pb[q] * TC_SPLIT_BYTES, 8192, 1024);
+        const unsigned long long da = smem_desc(sa + pa[q] * TC_SPLIT_BYTES, 4096, 1024);
+        const unsigned long long db = smem_desc(sb + pb[q] * TC_SPLIT_BYTES, 4096, 1024);
 #pragma unroll
-        for (int k4 = 0; k4 < 4; ++k4)   // UMMA_K = 16: A advances 32 B inside the swizzle row, B two 8-k groups
-          tc_mma(tmem, da + (unsigned long long)(k4 * 2), db + (unsigned long long)(k4 * 128), TC_IDESC, (t | q | k4) != 0);
+        for (int k2 = 0; k2 < TC_BK / 16; ++k2)   // UMMA_K = 16 = two 8-k groups (2048 B) of either operand
+          tc_mma(tmem, da + (unsigned long long)(k2 * 128), db + (unsigned long long)(k2 * 128), TC_IDESC, (t | q | k2) != 0);
       }
       tc_commit(empty0 + 8 * st);
     }
     tc_commit(accum);
   }
 
-  // ===== epilogue (warps 0-3; thread = output row, TMEM lane) =====
+  // ===== epilogue (warps 0-3) =====
+  // phase A: thread = accumulator row (TMEM lane): tcgen05.ld -> shared tile T[128][132] (the operand stages are free);
+  // phase B: warp = 32 rows, lane = 4 consecutive chains: every global access of a warp is one contiguous run
   if (warp < 4) {
     if (!mbar_wait(accum, 0)) info[1] = 3;
     tc_fence_after();
-    const long long m = m0 + tid;
-    const unsigned trow = tmem + ((unsigned)(warp * 32) << 16);
-    double* sc0 = (double*)smem;                 // [128][33] column-sum scratch (operand stages are free now)
-    double* sc1 = sc0 + 128 * 33;
-    double* red = (double*)a.field[F_RED];
+    float* T = (float*)smem;
+    double* sc = (double*)(smem + 69632);         // [2][4][128] column sums of the four warps
+    {
+      const unsigned trow = tmem + ((unsigned)(warp * 32) << 16);
+      for (int j = 0; j < 4; ++j) {
+        float v[32];
+        tc_ld32(trow + 32 * j, v);
+#pragma unroll
+        for (int q = 0; q < 8; ++q)
+          *reinterpret_cast<float4*>(T + tid * 132 + 32 * j + 4 * q) = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+      }
+    }
+    tc_fence_before();
+    asm volatile("bar.sync 1, 128;\n" ::: "memory");
+    const int lane = tid & 31;
+    const long long cc = c0 + 4 * lane;
     const long long planeB = ld * C;
     const bool last = a.iter == a.n_iter - 1;
     const bool sums = MODE == 1 ? (a.stage_kind != 2 || last) : (MODE == 3 && last);
-    const int zi = (MODE == 1 && m < n) ? ((const int*)a.field[F_Z])[m] : 0;
+    const bool full4 = (C & 3) == 0 && cc + 4 <= C;
     const double eps = a.par[P_EPS];
-    for (int j = 0; j < 4; ++j) {
-      float v[32];
-      tc_ld32(trow + 32 * j, v);
-      const long long cb = c0 + 32 * j;
-      double s0[32], s1[32];
+    double* red = (double*)a.field[F_RED];
+    double cs0[4] = {0.0, 0.0, 0.0, 0.0}, cs1[4] = {0.0, 0.0, 0.0, 0.0};
+    for (int rr = 0; rr < 32; ++rr) {
+      const int row = warp * 32 + rr;
+      const long long m = m0 + row;
+      if (m >= n) break;
+      const float4 g4 = *reinterpret_cast<const float4*>(T + row * 132 + 4 * lane);
+      const float g[4] = {g4.x, g4.y, g4.z, g4.w};
+      const long long o = m * C + cc;
       if (MODE == 1) {
         __nv_bfloat16* RB = (__nv_bfloat16*)a.field[F_RB];
-        __align__(16) __nv_bfloat16 h[32], md[32], lo[32];
+        const int zi = ((const int*)a.field[F_Z])[m];
+        __align__(8) __nv_bfloat16 h[4], md[4], lo[4];
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          const float g = v[i];
-          const double rv = (double)((float)zi - sigmoidf_(g));
-          split3(rv, h[i], md[i], lo[i]);
-          if (sums) s0[i] = (m < n && cb + i < C) ? (double)(zi ? -log1p_expf_(-g) : -log1p_expf_(g)) : 0.0;
+        for (int e = 0; e < 4; ++e) {
+          split3((double)((float)zi - sigmoidf_(g[e])), h[e], md[e], lo[e]);
+          if (sums && cc + e < C) cs0[e] += (double)(zi ? -log1p_expf_(-g[e]) : -log1p_expf_(g[e]));
         }
-        if (m < n) {
-          const long long o = m * C + cb;
-          if (vec && cb + 32 <= C) {
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-              *reinterpret_cast<uint4*>(RB + o + 8 * q) = *reinterpret_cast<const uint4*>(h + 8 * q);
-              *reinterpret_cast<uint4*>(RB + planeB + o + 8 * q) = *reinterpret_cast<const uint4*>(md + 8 * q);
-              *reinterpret_cast<uint4*>(RB + 2 * planeB + o + 8 * q) = *reinterpret_cast<const uint4*>(lo + 8 * q);
-            }
-          } else {
-            for (int i = 0; i < 32; ++i)
-              if (cb + i < C) { RB[o + i] = h[i]; RB[planeB + o + i] = md[i]; RB[2 * planeB + o + i] = lo[i]; }
-          }
+        if (full4) {
+          *reinterpret_cast<uint2*>(RB + o) = *reinterpret_cast<const uint2*>(h);
+          *reinterpret_cast<uint2*>(RB + planeB + o) = *reinterpret_cast<const uint2*>(md);
+          *reinterpret_cast<uint2*>(RB + 2 * planeB + o) = *reinterpret_cast<const uint2*>(lo);
+        } else {
+          for (int e = 0; e < 4; ++e)
+            if (cc + e < C) { RB[o + e] = h[e]; RB[planeB + o + e] = md[e]; RB[2 * planeB + o + e] = lo[e]; }
         }
       } else {
         double* Wm = (double*)a.field[F_W];
         double* Pm = (double*)a.field[F_P];
         double* GR = (double*)a.field[F_GR];
         __nv_bfloat16* WB = (__nv_bfloat16*)a.field[F_WB];
+        double wv[4], pv[4], d[4];
+        if (full4) {
+          const double2 w0 = *reinterpret_cast<const double2*>(Wm + o), w1 = *reinterpret_cast<const double2*>(Wm + o + 2);
+          wv[0] = w0.x; wv[1] = w0.y; wv[2] = w1.x; wv[3] = w1.y;
+          if (MODE == 3) {
+            const double2 p0 = *reinterpret_cast<const double2*>(Pm + o), p1 = *reinterpret_cast<const double2*>(Pm + o + 2);
+            pv[0] = p0.x; pv[1] = p0.y; pv[2] = p1.x; pv[3] = p1.y;
+          }
+        } else {
+          for (int e = 0; e < 4; ++e) { wv[e] = cc + e < C ? Wm[o + e] : 0.0; pv[e] = (MODE == 3 && cc + e < C) ? Pm[o + e] : 0.0; }
+        }
+        __align__(8) __nv_bfloat16 h[4], md[4], lo[4];
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          s0[i] = 0.0; s1[i] = 0.0;
-          if (m < n && cb + i < C) {
-            const long long o = m * C + cb + i;
-            const double wv = Wm[o];
-            const double d = (double)v[i] - wv;
-            if (MODE == 2) { GR[o] = d; if (a.out_grad) a.out_grad[o] = d; }
-            else {
-              double pv = Pm[o];
-              pv += 0.5 * eps * d;
-              if (!last) {
-                pv += 0.5 * eps * d;
-                const double wn = wv + eps * pv;
-                Wm[o] = wn;
-                split3_store(WB, planeB, o, wn);
-              } else { GR[o] = d; s0[i] = pv * pv; s1[i] = wv * wv; }
-              Pm[o] = pv;
-            }
+        for (int e = 0; e < 4; ++e) {
+          d[e] = (double)g[e] - wv[e];
+          if (MODE == 3) {
+            pv[e] += 0.5 * eps * d[e];
+            if (!last) { pv[e] += 0.5 * eps * d[e]; wv[e] += eps * pv[e]; split3(wv[e], h[e], md[e], lo[e]); }
+            else if (cc + e < C) { cs0[e] += pv[e] * pv[e]; cs1[e] += wv[e] * wv[e]; }
           }
         }
-      }
-      if (sums) {   // column sums over the 128 rows of the tile, fixed order
-        asm volatile("bar.sync 1, 128;\n" ::: "memory");
-#pragma unroll
-        for (int i = 0; i < 32; ++i) { sc0[tid * 33 + i] = s0[i]; if (MODE == 3) sc1[tid * 33 + i] = s1[i]; }
-        asm volatile("bar.sync 1, 128;\n" ::: "memory");
-        if (tid < 32 && cb + tid < C) {
-          double t0 = 0.0, t1 = 0.0;
-          for (int r = 0; r < 128; ++r) { t0 += sc0[r * 33 + tid]; if (MODE == 3) t1 += sc1[r * 33 + tid]; }
-          if (MODE == 1) red[((long long)RED_LIK * RED_TILES + I) * C + cb + tid] = t0;
-          else { red[((long long)RED_KE * RED_TILES + I) * C + cb + tid] = t0; red[((long long)RED_WW * RED_TILES + I) * C + cb + tid] = t1; }
+        const bool wr_gr = MODE == 2 || last, wr_w = MODE == 3 && !last;
+        if (full4) {
+          if (wr_gr) { *reinterpret_cast<double2*>(GR + o) = make_double2(d[0], d[1]); *reinterpret_cast<double2*>(GR + o + 2) = make_double2(d[2], d[3]); }
+          if (MODE == 2 && a.out_grad) { *reinterpret_cast<double2*>(a.out_grad + o) = make_double2(d[0], d[1]); *reinterpret_cast<double2*>(a.out_grad + o + 2) = make_double2(d[2], d[3]); }
+          if (MODE == 3) { *reinterpret_cast<double2*>(Pm + o) = make_double2(pv[0], pv[1]); *reinterpret_cast<double2*>(Pm + o + 2) = make_double2(pv[2], pv[3]); }
+          if (wr_w) {
+            *reinterpret_cast<double2*>(Wm + o) = make_double2(wv[0], wv[1]); *reinterpret_cast<double2*>(Wm + o + 2) = make_double2(wv[2], wv[3]);
+            *reinterpret_cast<uint2*>(WB + o) = *reinterpret_cast<const uint2*>(h);
+            *reinterpret_cast<uint2*>(WB + planeB + o) = *reinterpret_cast<const uint2*>(md);
+            *reinterpret_cast<uint2*>(WB + 2 * planeB + o) = *reinterpret_cast<const uint2*>(lo);
+          }
+        } else {
+          for (int e = 0; e < 4; ++e)
+            if (cc + e < C) {
+              if (wr_gr) GR[o + e] = d[e];
+              if (MODE == 2 && a.out_grad) a.out_grad[o + e] = d[e];
+              if (MODE == 3) Pm[o + e] = pv[e];
+              if (wr_w) { Wm[o + e] = wv[e]; WB[o + e] = h[e]; WB[planeB + o + e] = md[e]; WB[2 * planeB + o + e] = lo[e]; }
+            }
         }
       }
     }
-    tc_fence_before();
+    if (sums) {   // column sums: rows in order inside a warp, then the four warps in order
+#pragma unroll
+      for (int e = 0; e < 4; ++e) { sc[warp * 128 + 4 * lane + e] = cs0[e]; sc[512 + warp * 128 + 4 * lane + e] = cs1[e]; }
+      asm volatile("bar.sync 1, 128;\n" ::: "memory");
+      if (c0 + tid < C) {
+        const double t0 = ((sc[tid] + sc[128 + tid]) + sc[256 + tid]) + sc[384 + tid];
+        const double t1 = ((sc[512 + tid] + sc[640 + tid]) + sc[768 + tid]) + sc[896 + tid];
+        if (MODE == 1) red[((long long)RED_LIK * RED_TILES + I) * C + c0 + tid] = t0;
+        else { red[((long long)RED_KE * RED_TILES + I) * C + c0 + tid] = t0; red[((long long)RED_WW * RED_TILES + I) * C + c0 + tid] = t1; }
+      }
+    }
   }
   __syncthreads();
   if (warp == 4) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tmem), "n"(128));

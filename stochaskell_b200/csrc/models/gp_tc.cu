@@ -6,10 +6,11 @@
 //     six tcgen05.mma terms hi*hi + hi*mid + mid*hi + mid*mid + hi*lo + lo*hi accumulated in fp32 in TMEM;
 //   * L and L^T are split once per data set (gp_tc_split_L); W and R are written as split-bf16 by the epilogue of
 //     the product (or the begin / finish stage) that produces them, so no separate conversion pass runs per step;
-//   * one CTA = one 128 x 128 output tile; warps 0-3 stage the operand tiles with cp.async into the canonical
-//     128-byte-swizzled MN-major layouts (both operands are stored [k][m] / [k][chain], contraction index major),
-//     warp 4 lane 0 issues the MMAs, four 48 KB stages (32 k each) hand over through mbarriers (full: 128 producer
-//     arrivals after cp.async.wait_group + fence.proxy.async, empty: tcgen05.commit);
+//   * the split operands live in HBM as the shared-memory images of their 32 k x 128 tiles (canonical MN-major
+//     SWIZZLE_128B layout of tcgen05, see tc_tile_off in gp.cu), so staging a k step is two linear 24 KB bulk
+//     copies (cp.async.bulk + mbarrier complete_tx) issued by ONE thread: TMA-class staging without a tensor map;
+//   * one CTA = one 128 x 128 output tile; warp 5 lane 0 issues the bulk copies, warp 4 lane 0 the MMAs, four 48 KB
+//     stages hand over through mbarriers (full: expect_tx bytes, empty: tcgen05.commit);
 //   * the same four warps then read the accumulator with tcgen05.ld (thread = output row) and run the fused epilogue
 //     of gp.cu (r = z - sigmoid(g) / the leapfrog update), writing fp64 state and the split-bf16 operand of the next
 //     product.  Row tiles are issued longest-first (the k range of a tile is triangular).
@@ -73,36 +74,14 @@ __device__ __forceinline__ unsigned long long smem_desc(unsigned addr, unsigned 
 // instruction descriptor (InstrDescriptor): D = f32, A = B = bf16, A and B MN-major, N = 128, M = 128
 #define TC_IDESC ((1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((128u >> 3) << 17) | ((128u >> 4) << 24))
 
-// ---- operand staging (warps 0-3) ---------------------------------------------------------------------------------
-// A and B tiles are both MN-major, 32 k x 128 (m | chains), SWIZZLE_128B, two 64-wide atoms 4096 B apart:
-//   byte (k, c) = (c/64) 4096 + (k/8) 1024 + (k%8) 128 + (((c%64)/8) ^ (k%8)) 16 + (c%8) 2
-// Thread t of the 128 producers owns 16-byte chunk (t & 15) of rows (t >> 4) + 8u, u = 0..3, of every tile: its
-// shared-memory offset and global pointers are computed once, the loop only adds strides.
-struct TcLoader {
-  const __nv_bfloat16* pa; const __nv_bfloat16* pb;   // chunk of row k = kbeg + (t >> 4), split 0
-  long long planeA, planeB, rowA8, rowB8;             // elements: split stride, 8-row stride
-  unsigned soff;                                      // byte offset of the chunk inside a split tile (u = 0)
-  int bvalid;                                         // chains of the B chunk inside [0, C): 8 = whole, 0 = none
-  bool vec;
-};
-__device__ __forceinline__ void tc_load_stage(unsigned char* st, const TcLoader& L) {
-#pragma unroll
-  for (int s = 0; s < 3; ++s) {
-    unsigned char* as = st + s * TC_SPLIT_BYTES + L.soff;
-    unsigned char* bs = st + (3 + s) * TC_SPLIT_BYTES + L.soff;
-    const __nv_bfloat16* ga = L.pa + s * L.planeA;
-    const __nv_bfloat16* gb = L.pb + s * L.planeB;
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      cp_async16(as + u * 1024, ga + u * L.rowA8, 16);
-      if (L.vec) cp_async16(bs + u * 1024, L.bvalid ? gb + u * L.rowB8 : gb, L.bvalid ? 16 : 0);
-      else {   // chain count not a multiple of 8: rows are not 16-byte aligned
-        __nv_bfloat16* d = reinterpret_cast<__nv_bfloat16*>(bs + u * 1024);
-        for (int e = 0; e < 8; ++e) d[e] = e < L.bvalid ? gb[u * L.rowB8 + e] : __float2bfloat16(0.f);
-      }
-    }
-  }
-  cp_async_commit();
+// ---- operand staging: linear bulk copies of tile images --------------------------------------------------------------
+__device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
+  asm volatile("{\n.reg .b64 st;\nmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n}\n" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(unsigned dst, const void* src, unsigned bytes, unsigned bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(dst), "l"(src),
+               "r"(bytes), "r"(bar)
+               : "memory");
 }
 
 __device__ __forceinline__ float sigmoidf_(float g) { return 1.f / (1.f + __expf(-g)); }
@@ -124,12 +103,12 @@ __device__ __forceinline__ void gp_tc_gemm(const StkArgs& a) {
   const __nv_bfloat16* Bop = (const __nv_bfloat16*)a.field[MODE == 1 ? F_WB : F_RB];
   const long long kbeg = MODE == 1 ? 0 : m0, kend = MODE == 1 ? m0 + 128 : ld;
   const int ktiles = (int)((kend - kbeg) / TC_BK);
-  const bool vec = (C & 7) == 0;
+  const long long ncbA = ld >> 7, ncbB = (C + 127) >> 7;
   int* info = (int*)a.field[F_INFO];
   const unsigned full0 = smem_u32(bars), empty0 = smem_u32(bars + TC_STAGES), accum = smem_u32(bars + 2 * TC_STAGES);
 
   if (tid == 0) {
-    for (int i = 0; i < TC_STAGES; ++i) { mbar_init(full0 + 8 * i, 128); mbar_init(empty0 + 8 * i, 1); }
+    for (int i = 0; i < TC_STAGES; ++i) { mbar_init(full0 + 8 * i, 1); mbar_init(empty0 + 8 * i, 1); }
     mbar_init(accum, 1);
     asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
   }
@@ -142,27 +121,19 @@ __device__ __forceinline__ void gp_tc_gemm(const StkArgs& a) {
   tc_fence_after();
   const unsigned tmem = *tmem_slot;
 
-  if (warp < 4) {
-    // ===== producers =====
-    TcLoader Ld;
-    {
-      const int kr = tid >> 4, jj = tid & 15;
-      Ld.planeA = ld * ld; Ld.planeB = ld * C; Ld.rowA8 = 8 * ld; Ld.rowB8 = 8 * C; Ld.vec = vec;
-      Ld.soff = (unsigned)((jj >> 3) * 4096 + kr * 128 + (((jj & 7) ^ kr) << 4));
-      const long long c = c0 + jj * 8;
-      Ld.bvalid = c >= C ? 0 : (C - c >= 8 ? 8 : (int)(C - c));
-      Ld.pa = Aop + (kbeg + kr) * ld + m0 + jj * 8;
-      Ld.pb = Bop + (kbeg + kr) * C + (Ld.bvalid ? c : 0);
-    }
+  if (tid == 160) {
+    // ===== producer (one thread): two 24 KB bulk copies per stage =====
+    const __nv_bfloat16* ga = Aop + ((kbeg >> 5) * ncbA + I) * (3 * 4096);
+    const __nv_bfloat16* gb = Bop + ((kbeg >> 5) * ncbB + blockIdx.x) * (3 * 4096);
     for (int t = 0; t < ktiles; ++t) {
       const int st = t & (TC_STAGES - 1);
       if (t >= TC_STAGES && !mbar_wait(empty0 + 8 * st, ((t / TC_STAGES) & 1) ^ 1)) info[1] = 1;
-      tc_load_stage(smem + st * TC_STAGE_BYTES, Ld);
-      Ld.pa += TC_BK * ld; Ld.pb += TC_BK * C;
-      if (t >= 2) { cp_async_wait<2>(); fence_proxy_async(); mbar_arrive(full0 + 8 * ((t - 2) & (TC_STAGES - 1))); }
+      const unsigned dst = smem_u32(smem + st * TC_STAGE_BYTES), bar = full0 + 8 * st;
+      mbar_expect_tx(bar, TC_STAGE_BYTES);
+      bulk_g2s(dst, ga, 3 * TC_SPLIT_BYTES, bar);
+      bulk_g2s(dst + 3 * TC_SPLIT_BYTES, gb, 3 * TC_SPLIT_BYTES, bar);
+      ga += ncbA * (3 * 4096); gb += ncbB * (3 * 4096);
     }
-    cp_async_wait<1>(); fence_proxy_async(); mbar_arrive(full0 + 8 * ((ktiles - 2) & (TC_STAGES - 1)));
-    cp_async_wait<0>(); fence_proxy_async(); mbar_arrive(full0 + 8 * ((ktiles - 1) & (TC_STAGES - 1)));
   } else if (tid == 128) {
     // ===== MMA issuer (one thread) =====
     for (int t = 0; t < ktiles; ++t) {
@@ -207,7 +178,6 @@ __device__ __forceinline__ void gp_tc_gemm(const StkArgs& a) {
     asm volatile("bar.sync 1, 128;\n" ::: "memory");
     const int lane = tid & 31;
     const long long cc = c0 + 4 * lane;
-    const long long planeB = ld * C;
     const bool last = a.iter == a.n_iter - 1;
     const bool sums = MODE == 1 ? (a.stage_kind != 2 || last) : (MODE == 3 && last);
     const bool full4 = (C & 3) == 0 && cc + 4 <= C;
@@ -230,13 +200,12 @@ __device__ __forceinline__ void gp_tc_gemm(const StkArgs& a) {
           split3((double)((float)zi - sigmoidf_(g[e])), h[e], md[e], lo[e]);
           if (sums && cc + e < C) cs0[e] += (double)(zi ? -log1p_expf_(-g[e]) : -log1p_expf_(g[e]));
         }
-        if (full4) {
-          *reinterpret_cast<uint2*>(RB + o) = *reinterpret_cast<const uint2*>(h);
-          *reinterpret_cast<uint2*>(RB + planeB + o) = *reinterpret_cast<const uint2*>(md);
-          *reinterpret_cast<uint2*>(RB + 2 * planeB + o) = *reinterpret_cast<const uint2*>(lo);
-        } else {
-          for (int e = 0; e < 4; ++e)
-            if (cc + e < C) { RB[o + e] = h[e]; RB[planeB + o + e] = md[e]; RB[2 * planeB + o + e] = lo[e]; }
+        if (cc < C) {   // 4 chains = half a 16-byte chunk of the tile image; chains >= C of the last tile are kept zero
+          const long long ot = tc_tile_off(m, cc, ncbB);
+          if (!full4) for (int e = 0; e < 4; ++e) if (cc + e >= C) { h[e] = md[e] = lo[e] = __float2bfloat16(0.f); }
+          *reinterpret_cast<uint2*>(RB + ot) = *reinterpret_cast<const uint2*>(h);
+          *reinterpret_cast<uint2*>(RB + ot + TC_SPLIT_ELEMS) = *reinterpret_cast<const uint2*>(md);
+          *reinterpret_cast<uint2*>(RB + ot + 2 * TC_SPLIT_ELEMS) = *reinterpret_cast<const uint2*>(lo);
         }
       } else {
         double* Wm = (double*)a.field[F_W];
@@ -271,9 +240,10 @@ __device__ __forceinline__ void gp_tc_gemm(const StkArgs& a) {
           if (MODE == 3) { *reinterpret_cast<double2*>(Pm + o) = make_double2(pv[0], pv[1]); *reinterpret_cast<double2*>(Pm + o + 2) = make_double2(pv[2], pv[3]); }
           if (wr_w) {
             *reinterpret_cast<double2*>(Wm + o) = make_double2(wv[0], wv[1]); *reinterpret_cast<double2*>(Wm + o + 2) = make_double2(wv[2], wv[3]);
-            *reinterpret_cast<uint2*>(WB + o) = *reinterpret_cast<const uint2*>(h);
-            *reinterpret_cast<uint2*>(WB + planeB + o) = *reinterpret_cast<const uint2*>(md);
-            *reinterpret_cast<uint2*>(WB + 2 * planeB + o) = *reinterpret_cast<const uint2*>(lo);
+            const long long ot = tc_tile_off(m, cc, ncbB);
+            *reinterpret_cast<uint2*>(WB + ot) = *reinterpret_cast<const uint2*>(h);
+            *reinterpret_cast<uint2*>(WB + ot + TC_SPLIT_ELEMS) = *reinterpret_cast<const uint2*>(md);
+            *reinterpret_cast<uint2*>(WB + ot + 2 * TC_SPLIT_ELEMS) = *reinterpret_cast<const uint2*>(lo);
           }
         } else {
           for (int e = 0; e < 4; ++e)
@@ -281,7 +251,11 @@ __device__ __forceinline__ void gp_tc_gemm(const StkArgs& a) {
               if (wr_gr) GR[o + e] = d[e];
               if (MODE == 2 && a.out_grad) a.out_grad[o + e] = d[e];
               if (MODE == 3) Pm[o + e] = pv[e];
-              if (wr_w) { Wm[o + e] = wv[e]; WB[o + e] = h[e]; WB[planeB + o + e] = md[e]; WB[2 * planeB + o + e] = lo[e]; }
+              if (wr_w) {
+                Wm[o + e] = wv[e];
+                const long long ot = tc_tile_off(m, cc + e, ncbB);
+                WB[ot] = h[e]; WB[ot + TC_SPLIT_ELEMS] = md[e]; WB[ot + 2 * TC_SPLIT_ELEMS] = lo[e];
+              }
             }
         }
       }
@@ -302,12 +276,14 @@ __device__ __forceinline__ void gp_tc_gemm(const StkArgs& a) {
   if (warp == 4) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tmem), "n"(128));
 }
 
-extern "C" __global__ void __launch_bounds__(160, 1) gp_tc_gemm1(const __grid_constant__ StkArgs a) { gp_tc_gemm<1>(a); }
-extern "C" __global__ void __launch_bounds__(160, 1) gp_tc_gemm2_grad(const __grid_constant__ StkArgs a) { gp_tc_gemm<2>(a); }
-extern "C" __global__ void __launch_bounds__(160, 1) gp_tc_gemm2_leap(const __grid_constant__ StkArgs a) { gp_tc_gemm<3>(a); }
+extern "C" __global__ void __launch_bounds__(192, 1) gp_tc_gemm1(const __grid_constant__ StkArgs a) { gp_tc_gemm<1>(a); }
+extern "C" __global__ void __launch_bounds__(192, 1) gp_tc_gemm2_grad(const __grid_constant__ StkArgs a) { gp_tc_gemm<2>(a); }
+extern "C" __global__ void __launch_bounds__(192, 1) gp_tc_gemm2_leap(const __grid_constant__ StkArgs a) { gp_tc_gemm<3>(a); }
 
 // ---- split stages -------------------------------------------------------------------------------------------------
-// once per data set: La[s][m][k] = split(L[m][k]), Lta[s][m][k] = split(L^T[m][k])  (both K-major A operands)
+// once per data set, both A operands as tile images of [k][m] matrices:
+//   Lta (product 1, A = L):   element (k, m) = L[m][k] = Lt[k][m];    La (product 2, A = L^T): element (k, m) = L[k][m]
+// the identity padding of Lk / Lt (rows >= n) is dropped: padded rows and columns of the operands are zero
 extern "C" __global__ void __launch_bounds__(256) gp_tc_split_L(const __grid_constant__ StkArgs a) {
   const long long n = a.flen[F_X], ld = ld_of(n), tot = ld * ld;
   const double* Lk = (const double*)a.field[F_LK];
@@ -316,11 +292,10 @@ extern "C" __global__ void __launch_bounds__(256) gp_tc_split_L(const __grid_con
   __nv_bfloat16* Lta = (__nv_bfloat16*)a.field[F_LTA];
   const long long stride = (long long)gridDim.x * gridDim.y * 256;
   for (long long i = ((long long)blockIdx.y * gridDim.x + blockIdx.x) * 256 + threadIdx.x; i < tot; i += stride) {
-    // the identity padding of Lk / Lt (rows >= n) is dropped: padded rows and columns of the operands are zero
-    const long long r = i / ld, c = i % ld;
-    const bool in = r < n && c < n;
-    split3_store(La, tot, i, in ? Lk[i] : 0.0);
-    split3_store(Lta, tot, i, in ? Lt[i] : 0.0);
+    const long long k = i / ld, m = i % ld;
+    const bool in = k < n && m < n;
+    split3_store_t(La, k, m, ld >> 7, in ? Lk[i] : 0.0);
+    split3_store_t(Lta, k, m, ld >> 7, in ? Lt[i] : 0.0);
   }
 }
 
@@ -331,5 +306,5 @@ extern "C" __global__ void __launch_bounds__(128) gp_tc_split_w(const __grid_con
   const long long n = a.flen[F_X], C = a.n_chains;
   const double* W = (const double*)a.field[F_W];
   const long long j0 = (long long)blockIdx.y * 128, j1 = j0 + 128 < n ? j0 + 128 : n;
-  for (long long j = j0; j < j1; ++j) split3_store((__nv_bfloat16*)a.field[F_WB], ld_of(n) * C, j * C + c, W[j * C + c]);
+  for (long long j = j0; j < j1; ++j) split3_store_t((__nv_bfloat16*)a.field[F_WB], j, c, (C + 127) >> 7, W[j * C + c]);
 }

@@ -313,22 +313,22 @@ class GPHMC:
 
 
 class GPHMCTC(GPHMC):
-    """C3 on the tensor cores (fp32 tier, 1e-5): the two products as split-bf16 tcgen05.mma (3 x 3 bf16 terms, 6 MMAs
-    per useful product, fp32 accumulation in TMEM); everything else as gp_hmc."""
+    """C3 on the tensor cores (fp32 tier, 1e-5): the two products as split-fp16 tcgen05.mma (x = hi + lo/2^11, 3 MMA terms
+    per useful product, two fp32 accumulators in TMEM); everything else as gp_hmc."""
     name = "gp_hmc_tc"
     module = "builtin:gp_tc"
     symbol = "gp_tc_gemm1"
-    dtype = "bf16x3 (fp32-equivalent operands, fp32 accumulate); state f64"
+    dtype = "f16x2 (22-bit split operands, fp32 accumulate in TMEM); state f64"
     transitions_per_step = 8
 
     def roofline(self, C, T, ms_per_launch, peaks):
         r = super().roofline(C, T, ms_per_launch, peaks)
         r["kernel"] = "gp_tc_gemm1 + gp_tc_gemm2_leap"
-        r["tensor_flops_issued_tflops"] = 6 * r["achieved"]
-        r["frac_issued"] = 6 * r["achieved"] / r["peak"]
-        r["note"] = ("useful flops = L x 2 n^2 per chain and transition; each useful product is issued as 6 bf16 tcgen05.mma "
-                     "terms (hi/mid/lo splits of both operands), so the tensor pipe executes 6x the useful flops: `frac` is "
-                     "useful/peak, `frac_issued` is issued/peak")
+        r["tensor_flops_issued_tflops"] = 3 * r["achieved"]
+        r["frac_issued"] = 3 * r["achieved"] / r["peak"]
+        r["note"] = ("useful flops = L x 2 n^2 per chain and transition; each useful product is issued as 3 fp16 tcgen05.mma "
+                     "terms (hi*hi, hi*lo, lo*hi of the two-way split operands), so the tensor pipe executes 3x the useful "
+                     "flops: `frac` is useful/peak, `frac_issued` is issued/peak")
         return r
 
 

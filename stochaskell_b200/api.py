@@ -98,7 +98,7 @@ class Module:
             if not t:
                 continue
             if t[0] == "field":
-                dt = {"i32": np.int32, "f32": np.float32, "bf16": np.uint16}.get(t[3], np.float64)
+                dt = {"i32": np.int32, "f32": np.float32, "bf16": np.uint16, "f16": np.float16}.get(t[3], np.float64)
                 self.fields[t[1]] = dict(index=len(self.fields), state=(t[2] == "state"), kind=t[2], dtype=dt, len=t[4])
             elif t[0] == "kernel" or (t[0] == "plan" and t[2] == "kernel"):
                 self.kernels.append(t[1])

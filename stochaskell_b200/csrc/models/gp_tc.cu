@@ -2,25 +2,27 @@
 //
 // Same model, plan, prepare (fp64 Cholesky), begin / finish stages as gp.cu (included below with GP_TC defined); the
 // two triangular products of a gradient evaluation,  G = L W  and  D = L^T R,  run on the 5th-generation tensor cores:
-//   * every operand is split into three bf16 terms, x = hi + mid + lo (24 significand bits), and a product is the
-//     six tcgen05.mma terms hi*hi + hi*mid + mid*hi + mid*mid + hi*lo + lo*hi accumulated in fp32 in TMEM;
-//   * L and L^T are split once per data set (gp_tc_split_L); W and R are written as split-bf16 by the epilogue of
+//   * every operand is split into two fp16 terms, x = hi + lo / 2^11 (22 significand bits, the residual scaled so
+//     that it keeps 11 bits of its own), and a product is three tcgen05.mma terms: hi*hi into one fp32 accumulator
+//     in TMEM, hi*lo + lo*hi into a second one that the epilogue adds scaled by 2^-11 (lo*lo, 2^-22, is dropped);
+//   * L and L^T are split once per data set (gp_tc_split_L); W and R are written as split-fp16 by the epilogue of
 //     the product (or the begin / finish stage) that produces them, so no separate conversion pass runs per step;
 //   * the split operands live in HBM as the shared-memory images of their 32 k x 128 tiles (canonical MN-major
-//     SWIZZLE_128B layout of tcgen05, see tc_tile_off in gp.cu), so staging a k step is two linear 24 KB bulk
+//     SWIZZLE_128B layout of tcgen05, see tc_tile_off in gp.cu), so staging a k step is two linear 16 KB bulk
 //     copies (cp.async.bulk + mbarrier complete_tx) issued by ONE thread: TMA-class staging without a tensor map;
-//   * one CTA = one 128 x 128 output tile; warp 5 lane 0 issues the bulk copies, warp 4 lane 0 the MMAs, four 48 KB
+//   * one CTA = one 128 x 128 output tile; warp 5 lane 0 issues the bulk copies, warp 4 lane 0 the MMAs, six 32 KB
 //     stages hand over through mbarriers (full: expect_tx bytes, empty: tcgen05.commit);
 //   * the same four warps then read the accumulator with tcgen05.ld (thread = output row) and run the fused epilogue
-//     of gp.cu (r = z - sigmoid(g) / the leapfrog update), writing fp64 state and the split-bf16 operand of the next
+//     of gp.cu (r = z - sigmoid(g) / the leapfrog update), writing fp64 state and the split-fp16 operand of the next
 //     product.  Row tiles are issued longest-first (the k range of a tile is triangular).
 #define GP_TC 1
 #include "gp.cu"
 
 #define TC_BK 32
-#define TC_STAGES 4
-#define TC_STAGE_BYTES 49152          // 3 x (32 k x 128 m) bf16 A + 3 x (32 k x 128 chains) bf16 B
+#define TC_STAGES 6
+#define TC_STAGE_BYTES 32768          // 2 x (32 k x 128 m) fp16 A + 2 x (32 k x 128 chains) fp16 B
 #define TC_SPLIT_BYTES 8192
+#define TC_TMEM_COLS 256              // two 128 x 128 fp32 accumulators
 
 // ---- PTX wrappers -----------------------------------------------------------------------------------------------
 __device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
@@ -71,8 +73,8 @@ __device__ __forceinline__ unsigned long long smem_desc(unsigned addr, unsigned 
   return (unsigned long long)((addr >> 4) & 0x3fff) | ((unsigned long long)((lbo_bytes >> 4) & 0x3fff) << 16) |
          ((unsigned long long)((sbo_bytes >> 4) & 0x3fff) << 32) | (1ULL << 46) | (2ULL << 61);
 }
-// instruction descriptor (InstrDescriptor): D = f32, A = B = bf16, A and B MN-major, N = 128, M = 128
-#define TC_IDESC ((1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((128u >> 3) << 17) | ((128u >> 4) << 24))
+// instruction descriptor (InstrDescriptor): D = f32, A = B = f16 (format 0), A and B MN-major, N = 128, M = 128
+#define TC_IDESC ((1u << 4) | (0u << 7) | (0u << 10) | (1u << 15) | (1u << 16) | ((128u >> 3) << 17) | ((128u >> 4) << 24))
 
 // ---- operand staging: linear bulk copies of tile images --------------------------------------------------------------
 __device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
@@ -99,8 +101,8 @@ __device__ __forceinline__ void gp_tc_gemm(const StkArgs& a) {
   const int I = MODE == 1 ? nt - 1 - (int)blockIdx.y : (int)blockIdx.y;
   const long long m0 = (long long)I * 128, c0 = (long long)blockIdx.x * 128;
   // A operand stored [k][m]: product 1 (A = L) reads the split of L^T's rows, product 2 (A = L^T) the split of L's
-  const __nv_bfloat16* Aop = (const __nv_bfloat16*)a.field[MODE == 1 ? F_LTA : F_LA];
-  const __nv_bfloat16* Bop = (const __nv_bfloat16*)a.field[MODE == 1 ? F_WB : F_RB];
+  const tc_t* Aop = (const tc_t*)a.field[MODE == 1 ? F_LTA : F_LA];
+  const tc_t* Bop = (const tc_t*)a.field[MODE == 1 ? F_WB : F_RB];
   const long long kbeg = MODE == 1 ? 0 : m0, kend = MODE == 1 ? m0 + 128 : ld;
   const int ktiles = (int)((kend - kbeg) / TC_BK);
   const long long ncbA = ld >> 7, ncbB = (C + 127) >> 7;
@@ -113,7 +115,7 @@ __device__ __forceinline__ void gp_tc_gemm(const StkArgs& a) {
     asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
   }
   if (warp == 4) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(smem_u32(tmem_slot)), "n"(128));
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(smem_u32(tmem_slot)), "n"(TC_TMEM_COLS));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::);
   }
   tc_fence_before();
@@ -122,34 +124,34 @@ __device__ __forceinline__ void gp_tc_gemm(const StkArgs& a) {
   const unsigned tmem = *tmem_slot;
 
   if (tid == 160) {
-    // ===== producer (one thread): two 24 KB bulk copies per stage =====
-    const __nv_bfloat16* ga = Aop + ((kbeg >> 5) * ncbA + I) * (3 * 4096);
-    const __nv_bfloat16* gb = Bop + ((kbeg >> 5) * ncbB + blockIdx.x) * (3 * 4096);
+    // ===== producer (one thread): two 16 KB bulk copies per stage =====
+    const tc_t* ga = Aop + ((kbeg >> 5) * ncbA + I) * (TC_NS * 4096);
+    const tc_t* gb = Bop + ((kbeg >> 5) * ncbB + blockIdx.x) * (TC_NS * 4096);
     for (int t = 0; t < ktiles; ++t) {
-      const int st = t & (TC_STAGES - 1);
+      const int st = t % TC_STAGES;
       if (t >= TC_STAGES && !mbar_wait(empty0 + 8 * st, ((t / TC_STAGES) & 1) ^ 1)) info[1] = 1;
       const unsigned dst = smem_u32(smem + st * TC_STAGE_BYTES), bar = full0 + 8 * st;
       mbar_expect_tx(bar, TC_STAGE_BYTES);
-      bulk_g2s(dst, ga, 3 * TC_SPLIT_BYTES, bar);
-      bulk_g2s(dst + 3 * TC_SPLIT_BYTES, gb, 3 * TC_SPLIT_BYTES, bar);
-      ga += ncbA * (3 * 4096); gb += ncbB * (3 * 4096);
+      bulk_g2s(dst, ga, TC_NS * TC_SPLIT_BYTES, bar);
+      bulk_g2s(dst + TC_NS * TC_SPLIT_BYTES, gb, TC_NS * TC_SPLIT_BYTES, bar);
+      ga += ncbA * (TC_NS * 4096); gb += ncbB * (TC_NS * 4096);
     }
   } else if (tid == 128) {
     // ===== MMA issuer (one thread) =====
     for (int t = 0; t < ktiles; ++t) {
-      const int st = t & (TC_STAGES - 1);
+      const int st = t % TC_STAGES;
       if (!mbar_wait(full0 + 8 * st, (t / TC_STAGES) & 1)) info[1] = 2;
       tc_fence_after();
-      const unsigned sa = smem_u32(smem + st * TC_STAGE_BYTES), sb = sa + 3 * TC_SPLIT_BYTES;
-      // (A split, B split): smallest terms first, hi*hi last
-      const int pa[6] = {2, 0, 1, 1, 0, 0}, pb[6] = {0, 2, 1, 0, 1, 0};
+      const unsigned sa = smem_u32(smem + st * TC_STAGE_BYTES), sb = sa + TC_NS * TC_SPLIT_BYTES;
+      const unsigned long long a_hi = smem_desc(sa, 4096, 1024), a_lo = smem_desc(sa + TC_SPLIT_BYTES, 4096, 1024);
+      const unsigned long long b_hi = smem_desc(sb, 4096, 1024), b_lo = smem_desc(sb + TC_SPLIT_BYTES, 4096, 1024);
 #pragma unroll
-      for (int q = 0; q < 6; ++q) {
-        const unsigned long long da = smem_desc(sa + pa[q] * TC_SPLIT_BYTES, 4096, 1024);
-        const unsigned long long db = smem_desc(sb + pb[q] * TC_SPLIT_BYTES, 4096, 1024);
-#pragma unroll
-        for (int k2 = 0; k2 < TC_BK / 16; ++k2)   // UMMA_K = 16 = two 8-k groups (2048 B) of either operand
-          tc_mma(tmem, da + (unsigned long long)(k2 * 128), db + (unsigned long long)(k2 * 128), TC_IDESC, (t | q | k2) != 0);
+      for (int k2 = 0; k2 < TC_BK / 16; ++k2) {   // UMMA_K = 16 = two 8-k groups (2048 B) of either operand
+        const unsigned long long adv = (unsigned long long)(k2 * 128);
+        const unsigned acc = (t | k2) != 0;
+        tc_mma(tmem, a_hi + adv, b_hi + adv, TC_IDESC, acc);              // accumulator 0: hi * hi
+        tc_mma(tmem + 128, a_hi + adv, b_lo + adv, TC_IDESC, acc);        // accumulator 1: hi * lo + lo * hi
+        tc_mma(tmem + 128, a_lo + adv, b_hi + adv, TC_IDESC, 1u);
       }
       tc_commit(empty0 + 8 * st);
     }
@@ -167,8 +169,11 @@ __device__ __forceinline__ void gp_tc_gemm(const StkArgs& a) {
     {
       const unsigned trow = tmem + ((unsigned)(warp * 32) << 16);
       for (int j = 0; j < 4; ++j) {
-        float v[32];
+        float v[32], x[32];
         tc_ld32(trow + 32 * j, v);
+        tc_ld32(trow + 128 + 32 * j, x);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = fmaf(x[i], (float)(1.0 / TC_LO_SCALE), v[i]);
 #pragma unroll
         for (int q = 0; q < 8; ++q)
           *reinterpret_cast<float4*>(T + tid * 132 + 32 * j + 4 * q) = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
@@ -192,26 +197,25 @@ __device__ __forceinline__ void gp_tc_gemm(const StkArgs& a) {
       const float g[4] = {g4.x, g4.y, g4.z, g4.w};
       const long long o = m * C + cc;
       if (MODE == 1) {
-        __nv_bfloat16* RB = (__nv_bfloat16*)a.field[F_RB];
+        tc_t* RB = (tc_t*)a.field[F_RB];
         const int zi = ((const int*)a.field[F_Z])[m];
-        __align__(8) __nv_bfloat16 h[4], md[4], lo[4];
+        __align__(8) tc_t h[4], lo[4];
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
-          split3((double)((float)zi - sigmoidf_(g[e])), h[e], md[e], lo[e]);
+          split2((double)((float)zi - sigmoidf_(g[e])), h[e], lo[e]);
           if (sums && cc + e < C) cs0[e] += (double)(zi ? -log1p_expf_(-g[e]) : -log1p_expf_(g[e]));
         }
         if (cc < C) {   // 4 chains = half a 16-byte chunk of the tile image; chains >= C of the last tile are kept zero
           const long long ot = tc_tile_off(m, cc, ncbB);
-          if (!full4) for (int e = 0; e < 4; ++e) if (cc + e >= C) { h[e] = md[e] = lo[e] = __float2bfloat16(0.f); }
+          if (!full4) for (int e = 0; e < 4; ++e) if (cc + e >= C) { h[e] = lo[e] = __float2half(0.f); }
           *reinterpret_cast<uint2*>(RB + ot) = *reinterpret_cast<const uint2*>(h);
-          *reinterpret_cast<uint2*>(RB + ot + TC_SPLIT_ELEMS) = *reinterpret_cast<const uint2*>(md);
-          *reinterpret_cast<uint2*>(RB + ot + 2 * TC_SPLIT_ELEMS) = *reinterpret_cast<const uint2*>(lo);
+          *reinterpret_cast<uint2*>(RB + ot + TC_SPLIT_ELEMS) = *reinterpret_cast<const uint2*>(lo);
         }
       } else {
         double* Wm = (double*)a.field[F_W];
         double* Pm = (double*)a.field[F_P];
         double* GR = (double*)a.field[F_GR];
-        __nv_bfloat16* WB = (__nv_bfloat16*)a.field[F_WB];
+        tc_t* WB = (tc_t*)a.field[F_WB];
         double wv[4], pv[4], d[4];
         if (full4) {
           const double2 w0 = *reinterpret_cast<const double2*>(Wm + o), w1 = *reinterpret_cast<const double2*>(Wm + o + 2);
@@ -223,13 +227,13 @@ __device__ __forceinline__ void gp_tc_gemm(const StkArgs& a) {
         } else {
           for (int e = 0; e < 4; ++e) { wv[e] = cc + e < C ? Wm[o + e] : 0.0; pv[e] = (MODE == 3 && cc + e < C) ? Pm[o + e] : 0.0; }
         }
-        __align__(8) __nv_bfloat16 h[4], md[4], lo[4];
+        __align__(8) tc_t h[4], lo[4];
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
           d[e] = (double)g[e] - wv[e];
           if (MODE == 3) {
             pv[e] += 0.5 * eps * d[e];
-            if (!last) { pv[e] += 0.5 * eps * d[e]; wv[e] += eps * pv[e]; split3(wv[e], h[e], md[e], lo[e]); }
+            if (!last) { pv[e] += 0.5 * eps * d[e]; wv[e] += eps * pv[e]; split2(wv[e], h[e], lo[e]); }
             else if (cc + e < C) { cs0[e] += pv[e] * pv[e]; cs1[e] += wv[e] * wv[e]; }
           }
         }
@@ -242,8 +246,7 @@ __device__ __forceinline__ void gp_tc_gemm(const StkArgs& a) {
             *reinterpret_cast<double2*>(Wm + o) = make_double2(wv[0], wv[1]); *reinterpret_cast<double2*>(Wm + o + 2) = make_double2(wv[2], wv[3]);
             const long long ot = tc_tile_off(m, cc, ncbB);
             *reinterpret_cast<uint2*>(WB + ot) = *reinterpret_cast<const uint2*>(h);
-            *reinterpret_cast<uint2*>(WB + ot + TC_SPLIT_ELEMS) = *reinterpret_cast<const uint2*>(md);
-            *reinterpret_cast<uint2*>(WB + ot + 2 * TC_SPLIT_ELEMS) = *reinterpret_cast<const uint2*>(lo);
+            *reinterpret_cast<uint2*>(WB + ot + TC_SPLIT_ELEMS) = *reinterpret_cast<const uint2*>(lo);
           }
         } else {
           for (int e = 0; e < 4; ++e)
@@ -254,7 +257,7 @@ __device__ __forceinline__ void gp_tc_gemm(const StkArgs& a) {
               if (wr_w) {
                 Wm[o + e] = wv[e];
                 const long long ot = tc_tile_off(m, cc + e, ncbB);
-                WB[ot] = h[e]; WB[ot + TC_SPLIT_ELEMS] = md[e]; WB[ot + 2 * TC_SPLIT_ELEMS] = lo[e];
+                WB[ot] = h[e]; WB[ot + TC_SPLIT_ELEMS] = lo[e];
               }
             }
         }
@@ -273,7 +276,7 @@ __device__ __forceinline__ void gp_tc_gemm(const StkArgs& a) {
     }
   }
   __syncthreads();
-  if (warp == 4) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tmem), "n"(128));
+  if (warp == 4) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tmem), "n"(TC_TMEM_COLS));
 }
 
 extern "C" __global__ void __launch_bounds__(192, 1) gp_tc_gemm1(const __grid_constant__ StkArgs a) { gp_tc_gemm<1>(a); }
@@ -288,14 +291,14 @@ extern "C" __global__ void __launch_bounds__(256) gp_tc_split_L(const __grid_con
   const long long n = a.flen[F_X], ld = ld_of(n), tot = ld * ld;
   const double* Lk = (const double*)a.field[F_LK];
   const double* Lt = (const double*)a.field[F_LT];
-  __nv_bfloat16* La = (__nv_bfloat16*)a.field[F_LA];
-  __nv_bfloat16* Lta = (__nv_bfloat16*)a.field[F_LTA];
+  tc_t* La = (tc_t*)a.field[F_LA];
+  tc_t* Lta = (tc_t*)a.field[F_LTA];
   const long long stride = (long long)gridDim.x * gridDim.y * 256;
   for (long long i = ((long long)blockIdx.y * gridDim.x + blockIdx.x) * 256 + threadIdx.x; i < tot; i += stride) {
     const long long k = i / ld, m = i % ld;
     const bool in = k < n && m < n;
-    split3_store_t(La, k, m, ld >> 7, in ? Lk[i] : 0.0);
-    split3_store_t(Lta, k, m, ld >> 7, in ? Lt[i] : 0.0);
+    split_store_t(La, k, m, ld >> 7, in ? Lk[i] : 0.0);
+    split_store_t(Lta, k, m, ld >> 7, in ? Lt[i] : 0.0);
   }
 }
 
@@ -306,5 +309,5 @@ extern "C" __global__ void __launch_bounds__(128) gp_tc_split_w(const __grid_con
   const long long n = a.flen[F_X], C = a.n_chains;
   const double* W = (const double*)a.field[F_W];
   const long long j0 = (long long)blockIdx.y * 128, j1 = j0 + 128 < n ? j0 + 128 : n;
-  for (long long j = j0; j < j1; ++j) split3_store_t((__nv_bfloat16*)a.field[F_WB], j, c, (C + 127) >> 7, W[j * C + c]);
+  for (long long j = j0; j < j1; ++j) split_store_t((tc_t*)a.field[F_WB], j, c, (C + 127) >> 7, W[j * C + c]);
 }

@@ -41,7 +41,7 @@
  *          gx / gy: <int> | sms | chains/<k> | @<field>/<k> (ceiling division; `sms` = SM count of the device);
  *          `coop` launches cooperatively (grid-wide sync allowed, grid must be co-resident).
  * Field kinds: `state` (per chain, [len][n_chains]), `data` (uploaded, shared by all chains), `work` (runtime-
- * allocated scratch shared by all chains, len = total elements).  Types f64 | i32 | f32 | bf16.  <len> is a product
+ * allocated scratch shared by all chains, len = total elements).  Types f64 | i32 | f32 | bf16 | f16.  <len> is a product
  * of terms <int> | @<field> | @<field>^<k> (length of the field rounded up to a multiple of k) | chains | chains^<k>.
  * `nparam` accepts the same expressions (models whose parameter count follows the data).
  * Launch geometry: grid = ceil(n_chains / chains_per_block) CTAs of <block>

@@ -220,7 +220,7 @@ int parse_desc(stk_module* m) {
       FieldDesc f; std::string kind, ty, len;
       if (!(ls >> f.name >> kind >> ty >> len)) return fail(STK_ERR_ARG, "bad field line: %s", line.c_str());
       f.is_state = (kind == "state"); f.is_work = (kind == "work"); f.is_i32 = (ty == "i32");
-      f.esize = (ty == "i32" || ty == "f32") ? 4 : ty == "bf16" ? 2 : 8;
+      f.esize = (ty == "i32" || ty == "f32") ? 4 : (ty == "bf16" || ty == "f16") ? 2 : 8;
       if (len.find_first_not_of("0123456789") == std::string::npos) f.len = atoll(len.c_str());
       else {
         f.len = 0; f.len_expr = len;

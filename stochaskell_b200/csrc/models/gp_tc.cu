@@ -10,8 +10,8 @@
 //   * the split operands live in HBM as the shared-memory images of their 32 k x 128 tiles (canonical MN-major
 //     SWIZZLE_128B layout of tcgen05, see tc_tile_off in gp.cu), so staging a k step is two linear 16 KB bulk
 //     copies (cp.async.bulk + mbarrier complete_tx) issued by ONE thread: TMA-class staging without a tensor map;
-//   * one CTA = one 128 x 128 output tile; warp 5 lane 0 issues the bulk copies, warp 4 lane 0 the MMAs, six 32 KB
-//     stages hand over through mbarriers (full: expect_tx bytes, empty: tcgen05.commit);
+//   * one CTA = one 128 x 128 output tile; warp 5 lane 0 issues the bulk copies, warp 4 lane 0 the MMAs, three 32 KB
+//     stages (two CTAs per SM: one's epilogue overlaps the other's main loop) hand over through mbarriers (full: expect_tx bytes, empty: tcgen05.commit);
 //   * the same four warps then read the accumulator with tcgen05.ld (thread = output row) and run the fused epilogue
 //     of gp.cu (r = z - sigmoid(g) / the leapfrog update), writing fp64 state and the split-fp16 operand of the next
 //     product.  Row tiles are issued longest-first (the k range of a tile is triangular).
@@ -19,7 +19,7 @@
 #include "gp.cu"
 
 #define TC_BK 32
-#define TC_STAGES 6
+#define TC_STAGES 3
 #define TC_STAGE_BYTES 32768          // 2 x (32 k x 128 m) fp16 A + 2 x (32 k x 128 chains) fp16 B
 #define TC_SPLIT_BYTES 8192
 #define TC_TMEM_COLS 256              // two 128 x 128 fp32 accumulators
@@ -189,77 +189,79 @@ __device__ __forceinline__ void gp_tc_gemm(const StkArgs& a) {
     const double eps = a.par[P_EPS];
     double* red = (double*)a.field[F_RED];
     double cs0[4] = {0.0, 0.0, 0.0, 0.0}, cs1[4] = {0.0, 0.0, 0.0, 0.0};
-    for (int rr = 0; rr < 32; ++rr) {
-      const int row = warp * 32 + rr;
-      const long long m = m0 + row;
-      if (m >= n) break;
-      const float4 g4 = *reinterpret_cast<const float4*>(T + row * 132 + 4 * lane);
-      const float g[4] = {g4.x, g4.y, g4.z, g4.w};
-      const long long o = m * C + cc;
-      if (MODE == 1) {
-        tc_t* RB = (tc_t*)a.field[F_RB];
-        const int zi = ((const int*)a.field[F_Z])[m];
+    const long long mw = m0 + warp * 32;                         // first row of this warp
+    const int nrows = n - mw >= 32 ? 32 : (n > mw ? (int)(n - mw) : 0);
+    const int zlane = (MODE == 1 && lane < nrows) ? ((const int*)a.field[F_Z])[mw + lane] : 0;
+    double* Wm = (double*)a.field[F_W];
+    double* Pm = (double*)a.field[F_P];
+    double* GR = (double*)a.field[F_GR];
+    tc_t* OB = (tc_t*)a.field[MODE == 1 ? F_RB : F_WB];       // split operand this epilogue produces
+    const bool wr_gr = MODE == 2 || (MODE == 3 && last), wr_w = MODE == 3 && !last;
+    for (int rb = 0; rb < nrows; rb += 4) {                      // 4 rows per batch: all global loads first
+      double wv[4][4], pv[4][4];
+      if (MODE != 1) {
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const long long o = (mw + rb + u) * C + cc;
+          if (rb + u < nrows) {
+            if (full4) {
+              const double2 w0 = *reinterpret_cast<const double2*>(Wm + o), w1 = *reinterpret_cast<const double2*>(Wm + o + 2);
+              wv[u][0] = w0.x; wv[u][1] = w0.y; wv[u][2] = w1.x; wv[u][3] = w1.y;
+              if (MODE == 3) {
+                const double2 p0 = *reinterpret_cast<const double2*>(Pm + o), p1 = *reinterpret_cast<const double2*>(Pm + o + 2);
+                pv[u][0] = p0.x; pv[u][1] = p0.y; pv[u][2] = p1.x; pv[u][3] = p1.y;
+              }
+            } else {
+              for (int e = 0; e < 4; ++e) { wv[u][e] = cc + e < C ? Wm[o + e] : 0.0; pv[u][e] = (MODE == 3 && cc + e < C) ? Pm[o + e] : 0.0; }
+            }
+          }
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int zi = __shfl_sync(0xffffffffu, zlane, (rb + u) & 31);
+        if (rb + u >= nrows) continue;
+        const long long m = mw + rb + u;
+        const float4 g4 = *reinterpret_cast<const float4*>(T + (warp * 32 + rb + u) * 132 + 4 * lane);
+        const float g[4] = {g4.x, g4.y, g4.z, g4.w};
+        const long long o = m * C + cc;
         __align__(8) tc_t h[4], lo[4];
+        double d[4];
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
-          split2((double)((float)zi - sigmoidf_(g[e])), h[e], lo[e]);
-          if (sums && cc + e < C) cs0[e] += (double)(zi ? -log1p_expf_(-g[e]) : -log1p_expf_(g[e]));
+          if (MODE == 1) {
+            split2((double)((float)zi - sigmoidf_(g[e])), h[e], lo[e]);
+            if (sums && cc + e < C) cs0[e] += (double)(zi ? -log1p_expf_(-g[e]) : -log1p_expf_(g[e]));
+          } else {
+            d[e] = (double)g[e] - wv[u][e];
+            if (MODE == 3) {
+              pv[u][e] += 0.5 * eps * d[e];
+              if (!last) { pv[u][e] += 0.5 * eps * d[e]; wv[u][e] += eps * pv[u][e]; split2(wv[u][e], h[e], lo[e]); }
+              else if (cc + e < C) { cs0[e] += pv[u][e] * pv[u][e]; cs1[e] += wv[u][e] * wv[u][e]; }
+            }
+          }
         }
-        if (cc < C) {   // 4 chains = half a 16-byte chunk of the tile image; chains >= C of the last tile are kept zero
+        if ((MODE == 1 || wr_w) && cc < C) {   // 4 chains = half a 16-byte chunk of the tile image; chains >= C stay zero
           const long long ot = tc_tile_off(m, cc, ncbB);
           if (!full4) for (int e = 0; e < 4; ++e) if (cc + e >= C) { h[e] = lo[e] = __float2half(0.f); }
-          *reinterpret_cast<uint2*>(RB + ot) = *reinterpret_cast<const uint2*>(h);
-          *reinterpret_cast<uint2*>(RB + ot + TC_SPLIT_ELEMS) = *reinterpret_cast<const uint2*>(lo);
+          *reinterpret_cast<uint2*>(OB + ot) = *reinterpret_cast<const uint2*>(h);
+          *reinterpret_cast<uint2*>(OB + ot + TC_SPLIT_ELEMS) = *reinterpret_cast<const uint2*>(lo);
         }
-      } else {
-        double* Wm = (double*)a.field[F_W];
-        double* Pm = (double*)a.field[F_P];
-        double* GR = (double*)a.field[F_GR];
-        tc_t* WB = (tc_t*)a.field[F_WB];
-        double wv[4], pv[4], d[4];
-        if (full4) {
-          const double2 w0 = *reinterpret_cast<const double2*>(Wm + o), w1 = *reinterpret_cast<const double2*>(Wm + o + 2);
-          wv[0] = w0.x; wv[1] = w0.y; wv[2] = w1.x; wv[3] = w1.y;
-          if (MODE == 3) {
-            const double2 p0 = *reinterpret_cast<const double2*>(Pm + o), p1 = *reinterpret_cast<const double2*>(Pm + o + 2);
-            pv[0] = p0.x; pv[1] = p0.y; pv[2] = p1.x; pv[3] = p1.y;
-          }
-        } else {
-          for (int e = 0; e < 4; ++e) { wv[e] = cc + e < C ? Wm[o + e] : 0.0; pv[e] = (MODE == 3 && cc + e < C) ? Pm[o + e] : 0.0; }
-        }
-        __align__(8) tc_t h[4], lo[4];
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          d[e] = (double)g[e] - wv[e];
-          if (MODE == 3) {
-            pv[e] += 0.5 * eps * d[e];
-            if (!last) { pv[e] += 0.5 * eps * d[e]; wv[e] += eps * pv[e]; split2(wv[e], h[e], lo[e]); }
-            else if (cc + e < C) { cs0[e] += pv[e] * pv[e]; cs1[e] += wv[e] * wv[e]; }
-          }
-        }
-        const bool wr_gr = MODE == 2 || last, wr_w = MODE == 3 && !last;
-        if (full4) {
-          if (wr_gr) { *reinterpret_cast<double2*>(GR + o) = make_double2(d[0], d[1]); *reinterpret_cast<double2*>(GR + o + 2) = make_double2(d[2], d[3]); }
-          if (MODE == 2 && a.out_grad) { *reinterpret_cast<double2*>(a.out_grad + o) = make_double2(d[0], d[1]); *reinterpret_cast<double2*>(a.out_grad + o + 2) = make_double2(d[2], d[3]); }
-          if (MODE == 3) { *reinterpret_cast<double2*>(Pm + o) = make_double2(pv[0], pv[1]); *reinterpret_cast<double2*>(Pm + o + 2) = make_double2(pv[2], pv[3]); }
-          if (wr_w) {
-            *reinterpret_cast<double2*>(Wm + o) = make_double2(wv[0], wv[1]); *reinterpret_cast<double2*>(Wm + o + 2) = make_double2(wv[2], wv[3]);
-            const long long ot = tc_tile_off(m, cc, ncbB);
-            *reinterpret_cast<uint2*>(WB + ot) = *reinterpret_cast<const uint2*>(h);
-            *reinterpret_cast<uint2*>(WB + ot + TC_SPLIT_ELEMS) = *reinterpret_cast<const uint2*>(lo);
-          }
-        } else {
-          for (int e = 0; e < 4; ++e)
-            if (cc + e < C) {
-              if (wr_gr) GR[o + e] = d[e];
-              if (MODE == 2 && a.out_grad) a.out_grad[o + e] = d[e];
-              if (MODE == 3) Pm[o + e] = pv[e];
-              if (wr_w) {
-                Wm[o + e] = wv[e];
-                const long long ot = tc_tile_off(m, cc + e, ncbB);
-                WB[ot] = h[e]; WB[ot + TC_SPLIT_ELEMS] = lo[e];
+        if (MODE != 1) {
+          if (full4) {
+            if (wr_gr) { *reinterpret_cast<double2*>(GR + o) = make_double2(d[0], d[1]); *reinterpret_cast<double2*>(GR + o + 2) = make_double2(d[2], d[3]); }
+            if (MODE == 2 && a.out_grad) { *reinterpret_cast<double2*>(a.out_grad + o) = make_double2(d[0], d[1]); *reinterpret_cast<double2*>(a.out_grad + o + 2) = make_double2(d[2], d[3]); }
+            if (MODE == 3) { *reinterpret_cast<double2*>(Pm + o) = make_double2(pv[u][0], pv[u][1]); *reinterpret_cast<double2*>(Pm + o + 2) = make_double2(pv[u][2], pv[u][3]); }
+            if (wr_w) { *reinterpret_cast<double2*>(Wm + o) = make_double2(wv[u][0], wv[u][1]); *reinterpret_cast<double2*>(Wm + o + 2) = make_double2(wv[u][2], wv[u][3]); }
+          } else {
+            for (int e = 0; e < 4; ++e)
+              if (cc + e < C) {
+                if (wr_gr) GR[o + e] = d[e];
+                if (MODE == 2 && a.out_grad) a.out_grad[o + e] = d[e];
+                if (MODE == 3) Pm[o + e] = pv[u][e];
+                if (wr_w) Wm[o + e] = wv[u][e];
               }
-            }
+          }
         }
       }
     }
@@ -279,9 +281,9 @@ __device__ __forceinline__ void gp_tc_gemm(const StkArgs& a) {
   if (warp == 4) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tmem), "n"(TC_TMEM_COLS));
 }
 
-extern "C" __global__ void __launch_bounds__(192, 1) gp_tc_gemm1(const __grid_constant__ StkArgs a) { gp_tc_gemm<1>(a); }
-extern "C" __global__ void __launch_bounds__(192, 1) gp_tc_gemm2_grad(const __grid_constant__ StkArgs a) { gp_tc_gemm<2>(a); }
-extern "C" __global__ void __launch_bounds__(192, 1) gp_tc_gemm2_leap(const __grid_constant__ StkArgs a) { gp_tc_gemm<3>(a); }
+extern "C" __global__ void __launch_bounds__(192, 2) gp_tc_gemm1(const __grid_constant__ StkArgs a) { gp_tc_gemm<1>(a); }
+extern "C" __global__ void __launch_bounds__(192, 2) gp_tc_gemm2_grad(const __grid_constant__ StkArgs a) { gp_tc_gemm<2>(a); }
+extern "C" __global__ void __launch_bounds__(192, 2) gp_tc_gemm2_leap(const __grid_constant__ StkArgs a) { gp_tc_gemm<3>(a); }
 
 // ---- split stages -------------------------------------------------------------------------------------------------
 // once per data set, both A operands as tile images of [k][m] matrices:

@@ -112,6 +112,16 @@ double orc_soccer_accept_prob(int tag, double lam, double kappa, const int* y, i
 int orc_soccer_rj_step(int tag, double lam, double* kappa, const int* y, int ny,
                        uint64_t seed, uint64_t chain, uint64_t step, double* p_out);
 
+// ---- adaptive static HMC with a diagonal metric (Stan's adapt_diag_e_static_hmc; stk_oracle_adapt.cpp) ----
+#define ORC_AD_LEN 10
+#define ORC_CFG_LEN 10
+int orc_linreg_hmc_adapt_step(const double* X, const double* y, int n, int d, double* q, double* ad, double* minv,
+                              double* wm, double* wm2, const double* cfg, uint64_t seed, uint64_t chain, uint64_t step,
+                              double* lp_out, double* out3);
+int orc_birats_hmc_adapt_step(const double* x, const double* y, int N, int Tn, double* q, double* ad, double* minv,
+                              double* wm, double* wm2, const double* cfg, uint64_t seed, uint64_t chain, uint64_t step,
+                              double* lp_out, double* out3);
+
 #ifdef __cplusplus
 }
 #endif

@@ -244,6 +244,19 @@ class CudaMethod:
     seed: int = 1
     device: int = 0
     kernel: str = "hmc"
+    # adapt=True: Stan's `adapt engaged=1` for the static engine with a diagonal metric (adapt_diag_e_static_hmc):
+    # every chain tunes its own step size (dual averaging towards `delta`) and metric over num_warmup transitions,
+    # the trajectory length is int_time; kernel `hmc_adapt` of the module (csrc/stk_adapt.cuh).  Defaults are
+    # CmdStan's (Stan.hs:428-440 leaves them untouched): delta 0.8, gamma 0.05, kappa 0.75, t0 10, windows 75/50/25.
+    adapt: bool = False
+    int_time: float = 0.0            # 0 = num_leapfrog * step_size
+    delta: float = 0.8
+    gamma: float = 0.05
+    kappa: float = 0.75
+    t0: float = 10.0
+    init_buffer: int = 75
+    term_buffer: int = 50
+    window: int = 25
 
 
 class Sampler:
@@ -292,6 +305,17 @@ def hmcCUDA(method: CudaMethod, module_spec: str, data: dict, init: Optional[Seq
     if "eps" in s.module.params:
         ch.set_param("eps", method.step_size)
         ch.set_param("L", method.num_leapfrog)
+    kernel = method.kernel
+    if method.adapt:
+        if "stepsize" not in s.module.params:
+            raise StkError(-1, f"module {module_spec} has no adaptive HMC kernel")
+        kernel = "hmc_adapt"
+        for k, v in dict(stepsize=method.step_size, int_time=method.int_time or method.num_leapfrog * method.step_size,
+                         num_warmup=method.num_warmup, delta=method.delta, gamma=method.gamma, kappa=method.kappa,
+                         t0=method.t0, init_buffer=method.init_buffer, term_buffer=method.term_buffer,
+                         window=method.window).items():
+            ch.set_param(k, float(v))
+    method = dataclasses.replace(method, kernel=kernel)
     if init is not None:
         ch.set_state("q", np.asarray(init, dtype=np.float64), broadcast=True)
     if method.num_warmup:

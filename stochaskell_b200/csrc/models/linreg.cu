@@ -20,6 +20,7 @@
 //
 // Unconstrained parameters q = (b, w[0..D-1], log sigma), P = D+2.
 #include "../stk_device.cuh"
+#include "../stk_adapt.cuh"
 
 using namespace stk;
 
@@ -35,8 +36,8 @@ constexpr int RS = (D + 2) & ~1;  // smem row stride in doubles (x[D], y, pad) -
 static_assert(RS >= D + 1, "row stride");
 constexpr int NACC = D + 2;     // sum r, sum x_j r (D), sum r^2
 
-enum { F_Q = 0, F_LP = 1, F_X = 2, F_Y = 3, F_YSIM = 4 };
-enum { PAR_EPS = 0, PAR_L = 1, PAR_RW = 2 };
+enum { F_Q = 0, F_LP = 1, F_X = 2, F_Y = 3, F_YSIM = 4, F_AD = 5, F_MINV = 6, F_WM = 7, F_WM2 = 8 };
+enum { PAR_EPS = 0, PAR_L = 1, PAR_RW = 2, PAR_ADAPT = 3 /* stepsize .. window, stk_adapt.cuh */ };
 
 // stage [n][D] X and [n] y from HBM into smem rows
 __device__ __forceinline__ void stage_data(const StkArgs& a, double* xy, int n) {
@@ -239,6 +240,182 @@ linreg_hmc(const __grid_constant__ StkArgs a) {
 }
 
 // ---------------------------------------------------------------------------
+// adaptive static HMC with a diagonal metric: Stan's adapt_diag_e_static_hmc, every chain adapting its own step
+// size (dual averaging) and metric (windowed Welford variances) during the first num_warmup transitions
+// (stk_adapt.cuh; oracle/stk_oracle_adapt.cpp is the step-by-step restatement).  The K observation slices of a
+// chain hold replicas of the whole per-chain state and take every decision redundantly; anything that contains a
+// data pass runs in CTA-uniform control flow (the loops run to the CTA's maximum trip count, lanes that are done
+// keep evaluating at their final point and ignore the result).
+// ---------------------------------------------------------------------------
+extern "C" __global__ void __launch_bounds__(256, 1)
+linreg_hmc_adapt(const __grid_constant__ StkArgs a) {
+  extern __shared__ __align__(16) double smem[];
+  const int n = (int)a.flen[F_Y];
+  const int K = blockDim.x >> 5;
+  const int lane = threadIdx.x & 31, slice = threadIdx.x >> 5;
+  Smem sm(smem, n, K);
+  stage_data(a, sm.xy, n);
+  __syncthreads();
+
+  const long long chain = (long long)blockIdx.x * 32 + lane;
+  const bool active = chain < a.n_chains;
+  const long long cidx = active ? chain : a.n_chains - 1;
+  const long long nc = a.n_chains;
+  const bool writer = slice == 0 && active;
+  double* Q = (double*)a.field[F_Q];
+  double* AD = (double*)a.field[F_AD];
+  double* MINV = (double*)a.field[F_MINV];
+  double* WM = (double*)a.field[F_WM];
+  double* WM2 = (double*)a.field[F_WM2];
+  AdaptCfg cfg; cfg.init(&a.par[PAR_ADAPT]);
+  double q[P], g[P], p[P], minv[P], acc[NACC], ad[STK_AD_LEN];
+#pragma unroll
+  for (int j = 0; j < P; ++j) { q[j] = Q[j * nc + cidx]; minv[j] = MINV[j * nc + cidx]; }
+#pragma unroll
+  for (int j = 0; j < STK_AD_LEN; ++j) ad[j] = AD[j * nc + cidx];
+  unsigned long long n_acc = 0;
+  double lp = 0.0;
+
+  auto sample_p = [&](Rng& rng) {
+#pragma unroll
+    for (int j = 0; j < P; j += 2) {
+      double z0, z1; rng.normal2(z0, z1);
+      p[j] = z0 / sqrt(minv[j]); if (j + 1 < P) p[j + 1] = z1 / sqrt(minv[j + 1]);
+    }
+  };
+  auto kinetic = [&]() {
+    double ke = 0.0;
+#pragma unroll
+    for (int j = 0; j < P; ++j) ke = fma(minv[j] * p[j], p[j], ke);
+    return 0.5 * ke;
+  };
+  // base_hmc::init_stepsize for the lanes with `want`; lp / g hold the density and gradient at q on entry and on exit
+  auto init_stepsize = [&](Rng& rng, bool want) {
+    double eps = ad[0];
+    int dir = 0;
+    bool done = !want || eps == 0.0 || eps > 1e7;
+    const double lp0 = lp;
+    double g0[P];
+#pragma unroll
+    for (int j = 0; j < P; ++j) g0[j] = g[j];
+    while (__syncthreads_or(!done)) {
+      double qt[P], gt[P];
+      if (!done) sample_p(rng);
+      const double H0 = -lp0 + kinetic();
+#pragma unroll
+      for (int j = 0; j < P; ++j) { p[j] = fma(0.5 * eps, g0[j], p[j]); qt[j] = fma(eps * minv[j], p[j], q[j]); }
+      data_pass<true>(sm.xy, n, slice, K, lane, sm.red, sm.tot, qt, acc);
+      const double lpt = finish_eval<true>(n, qt, acc, gt);
+#pragma unroll
+      for (int j = 0; j < P; ++j) p[j] = fma(0.5 * eps, gt[j], p[j]);
+      double h = -lpt + kinetic();
+      if (isnan(h)) h = pos_inf();
+      if (!done) done = init_stepsize_update(eps, dir, H0 - h);
+    }
+    if (want) ad[0] = eps;
+  };
+
+  for (long long t = 0; t < a.n_steps; ++t) {
+    const unsigned long long step = a.step0 + (u64)t;
+    Rng rng; rng.init(a.seed, (u64)(a.chain0 + cidx), step);
+    const bool fresh = ad[9] == 0.0;
+    if (fresh) {
+#pragma unroll
+      for (int j = 0; j < P; ++j) minv[j] = 1.0;
+      adapt_reset(ad, cfg);
+    }
+    // hamiltonian_.init: density and gradient at the current point (shared by init_stepsize and the transition)
+    data_pass<true>(sm.xy, n, slice, K, lane, sm.red, sm.tot, q, acc);
+    lp = finish_eval<true>(n, q, acc, g);
+    if (__syncthreads_or(fresh)) init_stepsize(rng, fresh);
+    if (ad[9] == 1.0 && (double)step >= cfg.num_warmup) { ad[0] = exp(ad[3]); ad[9] = 2.0; }  // complete_adaptation
+    const double eps = ad[0];
+    const int L = adapt_leaps(cfg.int_time, eps);
+    sample_p(rng);
+    const double H0 = -lp + kinetic();
+    double q0[P]; const double lp0 = lp;
+#pragma unroll
+    for (int j = 0; j < P; ++j) q0[j] = q[j];
+    for (int l = 0; __syncthreads_or(l < L); ++l) {
+      const bool on = l < L;
+      if (on) {
+#pragma unroll
+        for (int j = 0; j < P; ++j) { p[j] = fma(0.5 * eps, g[j], p[j]); q[j] = fma(eps * minv[j], p[j], q[j]); }
+      }
+      data_pass<true>(sm.xy, n, slice, K, lane, sm.red, sm.tot, q, acc);
+      lp = finish_eval<true>(n, q, acc, g);
+      if (on) {
+#pragma unroll
+        for (int j = 0; j < P; ++j) p[j] = fma(0.5 * eps, g[j], p[j]);
+      }
+    }
+    double H = -lp + kinetic();
+    if (isnan(H)) H = pos_inf();
+    double accept_prob = exp(H0 - H);
+    const double u = rng.u01();
+    if (accept_prob < 1.0 && u > accept_prob) {
+#pragma unroll
+      for (int j = 0; j < P; ++j) q[j] = q0[j];
+      lp = lp0;
+    } else {
+      ++n_acc;
+    }
+    if (accept_prob > 1.0) accept_prob = 1.0;
+    bool update = false, store = false;
+    if (ad[9] == 1.0) {
+      adapt_learn_stepsize(ad, cfg, accept_prob);
+      const bool in_w = adapt_in_window(ad, cfg), ends = adapt_window_ends(ad, cfg);
+      if (in_w || ends) {
+        double wm[P], wm2[P];
+#pragma unroll
+        for (int j = 0; j < P; ++j) { wm[j] = WM[j * nc + cidx]; wm2[j] = WM2[j * nc + cidx]; }
+        if (in_w) {
+          ad[8] += 1.0;
+#pragma unroll
+          for (int j = 0; j < P; ++j) welford_add(ad[8], q[j], wm[j], wm2[j]);
+        }
+        if (ends) {
+          adapt_next_window(ad, cfg);
+#pragma unroll
+          for (int j = 0; j < P; ++j) { minv[j] = adapt_window_var(ad[8], wm2[j], minv[j]); wm[j] = 0.0; wm2[j] = 0.0; }
+          ad[8] = 0.0;
+          update = true;
+        }
+        // every slice reads the estimator before slice 0 writes it back (after the barrier below)
+#pragma unroll
+        for (int j = 0; j < P; ++j) { g[j] = wm[j]; p[j] = wm2[j]; }  // park in dead registers until the barrier
+      }
+      ad[5] += 1.0;
+      store = in_w || ends;
+    }
+    __syncthreads();
+    if (store && writer) {
+#pragma unroll
+      for (int j = 0; j < P; ++j) { WM[j * nc + chain] = g[j]; WM2[j * nc + chain] = p[j]; }
+    }
+    if (__syncthreads_or(update)) {
+      data_pass<true>(sm.xy, n, slice, K, lane, sm.red, sm.tot, q, acc);
+      lp = finish_eval<true>(n, q, acc, g);
+      init_stepsize(rng, update);
+      if (update) { ad[1] = log(10.0 * ad[0]); ad[2] = 0.0; ad[3] = 0.0; ad[4] = 0.0; }
+    }
+    long long slot;
+    if (writer && record_slot(a, t, &slot)) {
+#pragma unroll
+      for (int j = 0; j < P; ++j) record_value(a, slot, j, chain, q[j]);
+    }
+  }
+  if (writer) {
+#pragma unroll
+    for (int j = 0; j < P; ++j) { Q[j * nc + chain] = q[j]; MINV[j * nc + chain] = minv[j]; }
+#pragma unroll
+    for (int j = 0; j < STK_AD_LEN; ++j) AD[j * nc + chain] = ad[j];
+    ((double*)a.field[F_LP])[chain] = lp;
+    if (a.accept) a.accept[chain] += n_acc;
+  }
+}
+
+// ---------------------------------------------------------------------------
 // random-walk Metropolis (the `mh`-style kernel of mh.ipynb cell 1, proposal
 // q' = q + rw * N(0, I) on the unconstrained scale), n_steps per launch
 // ---------------------------------------------------------------------------
@@ -401,12 +578,18 @@ extern "C" __device__ const char stk_desc[] =
     "field X data f64 0\n"
     "field y data f64 0\n"
     "field ysim state f64 @y\n"
+    "field ad state f64 10\n"
+    "field minv state f64 " STR(LINREG_P) "\n"
+    "field wm state f64 " STR(LINREG_P) "\n"
+    "field wm2 state f64 " STR(LINREG_P) "\n"
     "param eps 0.01\n"
     "param L 10\n"
     "param rw 0.05\n"
+    STK_ADAPT_PARAMS
     "record q\n"
     "kernel hmc linreg_hmc" GEOM
     "kernel mh linreg_mh" GEOM
+    "kernel hmc_adapt linreg_hmc_adapt" GEOM
     "entry logp linreg_logp" GEOM
     "entry logp_grad linreg_logp_grad" GEOM
     "entry simulate linreg_simulate" GEOM;

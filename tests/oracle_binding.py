@@ -255,6 +255,41 @@ class Oracle:
         assert q.flags.c_contiguous and q.dtype == np.float64 and q.shape[0] == d + 2
         return self.l.orc_linreg_hmc_run(_p(X), _p(y), n, d, _p(q), q.shape[1], T, eps, L, seed, chain0, step0, nthreads)
 
+    # ---- adaptive static HMC, diagonal metric (oracle/stk_oracle_adapt.cpp) ----
+    ADAPT_CFG = dict(stepsize=1.0, int_time=6.283185307179586, num_warmup=1000, delta=0.8, gamma=0.05, kappa=0.75, t0=10.0,
+                     init_buffer=75, term_buffer=50, window=25)
+
+    @staticmethod
+    def adapt_cfg(**kw):
+        c = dict(Oracle.ADAPT_CFG); c.update(kw)
+        return np.array([c[k] for k in ("stepsize", "int_time", "num_warmup", "delta", "gamma", "kappa", "t0",
+                                        "init_buffer", "term_buffer", "window")], dtype=np.float64)
+
+    @staticmethod
+    def adapt_state(P):
+        """(ad[10], minv[P], wm[P], wm2[P]) of a chain that has not been initialised"""
+        return np.zeros(10), np.ones(P), np.zeros(P), np.zeros(P)
+
+    def _adapt_step(self, fn, a, b, i0, i1, q, st, cfg, seed, chain, step):
+        ad, minv, wm, wm2 = st
+        lp = D(); out3 = np.zeros(3)
+        fn.restype = C.c_int
+        fn.argtypes = [P, P, C.c_int, C.c_int, P, P, P, P, P, P, C.c_uint64, C.c_uint64, C.c_uint64, P, P]
+        acc = fn(_p(a), _p(b), i0, i1, _p(q), _p(ad), _p(minv), _p(wm), _p(wm2), _p(cfg), seed, chain, step,
+                 C.cast(C.byref(lp), P), _p(out3))
+        return acc, lp.value, out3
+
+    def linreg_hmc_adapt_step(self, X, y, q, st, cfg, seed, chain, step):
+        """q and the adaptation state st = (ad, minv, wm, wm2) updated in place; returns (accepted, lp, [accept_stat, eps, L])"""
+        X = np.ascontiguousarray(X, dtype=np.float64); y = np.ascontiguousarray(y, dtype=np.float64)
+        n, d = X.shape
+        return self._adapt_step(self.l.orc_linreg_hmc_adapt_step, X, y, n, d, q, st, cfg, seed, chain, step)
+
+    def birats_hmc_adapt_step(self, x, y, q, st, cfg, seed, chain, step):
+        x = np.ascontiguousarray(x, dtype=np.float64); y = np.ascontiguousarray(y, dtype=np.float64)
+        N, Tn = y.shape
+        return self._adapt_step(self.l.orc_birats_hmc_adapt_step, x, y, N, Tn, q, st, cfg, seed, chain, step)
+
     def u01x2(self, seed, chain, step, slot):
         a = D(); b = D()
         self.l.orc_u01x2(seed, chain, step, slot, C.byref(a), C.byref(b))

@@ -113,3 +113,26 @@ def test_adapt_quirks(ctx, orc):
         assert np.array_equal(ad[4:10, 3], st[0][4:10])
         assert np.allclose(ad[0:4, 3], st[0][0:4], rtol=1e-2, atol=1e-3)
         assert np.allclose(s.chains.get_state("q")[:, 3], q, rtol=1e-2, atol=1e-2)
+
+
+def test_linreg_adapt_vs_cmdstan(ctx):
+    """adapted step sizes and metrics of 1024 device chains against 48 chains of the reference's adaptive static
+    sampler (tests/golden/linreg_adapt_stan.json: vendored CmdStan, same data, same configuration)"""
+    from stochaskell_b200 import CudaMethod, hmcCUDA
+    from tests.test_adapt_cpu import gold_problem
+    g, X, y = gold_problem()
+    c = g["config"]
+    m = CudaMethod(num_chains=1024, num_samples=c["num_samples"], num_warmup=c["num_warmup"], step_size=c["stepsize"],
+                   int_time=c["int_time"], adapt=True, seed=21)
+    draws = hmcCUDA(m, "builtin:linreg", dict(X=X, y=y), init=np.zeros(g["d"] + 2))
+    ch = hmcCUDA.last_sampler.chains
+    eps = ch.get_state("ad")[0]; minv = ch.get_state("minv")
+    ge, gm = np.array(g["stepsize"]), np.array(g["inv_metric"])
+    se = np.hypot(eps.std() / np.sqrt(eps.size), ge.std() / np.sqrt(ge.size))
+    assert abs(eps.mean() - ge.mean()) < 4 * se, (eps.mean(), ge.mean(), se)
+    sm = np.hypot(minv.std(axis=1) / np.sqrt(eps.size), gm.std(axis=0) / np.sqrt(ge.size))
+    assert np.all(np.abs(minv.mean(axis=1) - gm.mean(axis=0)) < 4 * sm), (minv.mean(axis=1), gm.mean(axis=0), sm)
+    # posterior means on the constrained scale (sigma = exp(q[-1])) against the reference sampler's
+    mu = draws.mean(axis=(0, 2)); mu[-1] = np.exp(draws[:, -1, :]).mean()
+    sd = draws.std(axis=(0, 2))
+    assert np.all(np.abs(mu - np.array(g["post_mean"])) < 0.1 * np.maximum(sd, 0.02)), (mu, g["post_mean"])

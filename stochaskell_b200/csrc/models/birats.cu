@@ -16,14 +16,15 @@
 //     assignment of normals to parameters as the oracle's sequential loop;
 //   * x and y are staged in shared memory once per launch and then held in registers.
 #include "../stk_device.cuh"
+#include "../stk_adapt.cuh"
 
 using namespace stk;
 
 namespace {
 
 constexpr int TMAX = 8;                 // observations per rat held in registers
-enum { F_Q = 0, F_LP = 1, F_X = 2, F_Y = 3 };
-enum { PAR_EPS = 0, PAR_L = 1 };
+enum { F_Q = 0, F_LP = 1, F_X = 2, F_Y = 3, F_AD = 4, F_MINV = 5, F_WM = 6, F_WM2 = 7 };
+enum { PAR_EPS = 0, PAR_L = 1, PAR_ADAPT = 2 /* stepsize .. window, stk_adapt.cuh */ };
 
 struct Hyper { double mu1, mu2, t1, t2, yo, ls; };
 
@@ -210,6 +211,195 @@ extern "C" __global__ void __launch_bounds__(128) birats_hmc(const __grid_consta
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// adaptive static HMC with a diagonal metric (Stan's adapt_diag_e_static_hmc per chain; stk_adapt.cuh,
+// oracle/stk_oracle_adapt.cpp).  One warp = one chain, so every loop of the adaptation is warp-uniform; the metric
+// and the Welford estimator are distributed like q (lane i: its rat's two coefficients; the six hyper-parameter
+// entries replicated).  Philox blocks are consumed in the oracle's order: a momentum draw takes (P+1)/2 blocks from
+// the running block counter, a uniform one.
+// ---------------------------------------------------------------------------------------------------------
+extern "C" __global__ void __launch_bounds__(128) birats_hmc_adapt(const __grid_constant__ StkArgs a) {
+  extern __shared__ __align__(16) double smem[];
+  Ctx c; double y[TMAX];
+  setup(a, smem, c, y);
+  Hyper h; double b1, b2;
+  load_q(a, c, h, b1, b2);
+  const long long nc = a.n_chains;
+  const int r = c.has_rat ? c.lane : 0;
+  const int j1 = 5 + r, j2 = 5 + c.N + r;
+  // parameter index of hyper slot k
+  auto hidx = [&](int k) { return k < 5 ? k : c.P - 1; };
+  double* AD = (double*)a.field[F_AD];
+  double* MINV = (double*)a.field[F_MINV];
+  double* WM = (double*)a.field[F_WM];
+  double* WM2 = (double*)a.field[F_WM2];
+  AdaptCfg cfg; cfg.init(&a.par[PAR_ADAPT]);
+  double ad[STK_AD_LEN], mh[6], m1, m2;
+#pragma unroll
+  for (int j = 0; j < STK_AD_LEN; ++j) ad[j] = AD[j * nc + c.cidx];
+#pragma unroll
+  for (int k = 0; k < 6; ++k) mh[k] = MINV[(long long)hidx(k) * nc + c.cidx];
+  m1 = MINV[(long long)j1 * nc + c.cidx]; m2 = MINV[(long long)j2 * nc + c.cidx];
+  const u32 blocks_p = (u32)((c.P + 1) / 2);
+  unsigned long long n_acc = 0;
+  double lp = 0.0, ph[6], p1, p2, gh[6], g1, g2;
+
+  auto sample_p = [&](const Rng& rng, u32& base) {
+    double za, zb, za32 = 0.0, zb32 = 0.0;
+    { Rng q = rng; q.slot = base + (u32)c.lane; q.normal2(za, zb); }
+    if (c.P > 64) { Rng q = rng; q.slot = base + 32u; q.normal2(za32, zb32); }
+    base += blocks_p;
+#pragma unroll
+    for (int k = 0; k < 5; ++k) ph[k] = momentum(k, za, zb, za32, zb32) / sqrt(mh[k]);
+    ph[5] = momentum(c.P - 1, za, zb, za32, zb32) / sqrt(mh[5]);
+    p1 = momentum(j1, za, zb, za32, zb32) / sqrt(m1);
+    p2 = momentum(j2, za, zb, za32, zb32) / sqrt(m2);
+  };
+  auto kinetic = [&]() {
+    double ke = warp_sum(c.has_rat ? fma(m2 * p2, p2, m1 * p1 * p1) : 0.0);
+#pragma unroll
+    for (int k = 0; k < 6; ++k) ke = fma(mh[k] * ph[k], ph[k], ke);
+    return 0.5 * ke;
+  };
+  // one leapfrog step of (h, b1, b2, p) with the gradient in (gh, g1, g2); returns lp at the new point
+  auto evolve = [&](Hyper& hh, double& bb1, double& bb2, double eps) {
+    double* hv = &hh.mu1;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) { ph[k] = fma(0.5 * eps, gh[k], ph[k]); hv[k] = fma(eps * mh[k], ph[k], hv[k]); }
+    p1 = fma(0.5 * eps, g1, p1); bb1 = fma(eps * m1, p1, bb1);
+    p2 = fma(0.5 * eps, g2, p2); bb2 = fma(eps * m2, p2, bb2);
+    const double l = eval<true>(hh, bb1, bb2, y, c.xs, c.N, c.Tn, c.has_rat, gh, g1, g2);
+#pragma unroll
+    for (int k = 0; k < 6; ++k) ph[k] = fma(0.5 * eps, gh[k], ph[k]);
+    p1 = fma(0.5 * eps, g1, p1); p2 = fma(0.5 * eps, g2, p2);
+    return l;
+  };
+  // base_hmc::init_stepsize at (h, b1, b2); lp and the gradient at that point are valid on entry and on exit
+  auto init_stepsize = [&](const Rng& rng, u32& base) {
+    double eps = ad[0];
+    if (eps == 0.0 || eps > 1e7) return;
+    const double lp0 = lp, g10 = g1, g20 = g2;
+    double gh0[6];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) gh0[k] = gh[k];
+    int dir = 0;
+    for (;;) {
+      Hyper ht = h; double bt1 = b1, bt2 = b2;
+      sample_p(rng, base);
+#pragma unroll
+      for (int k = 0; k < 6; ++k) gh[k] = gh0[k];
+      g1 = g10; g2 = g20;
+      const double H0 = -lp0 + kinetic();
+      const double lpt = evolve(ht, bt1, bt2, eps);
+      double hh = -lpt + kinetic();
+      if (isnan(hh)) hh = pos_inf();
+      if (init_stepsize_update(eps, dir, H0 - hh)) break;
+    }
+#pragma unroll
+    for (int k = 0; k < 6; ++k) gh[k] = gh0[k];
+    g1 = g10; g2 = g20;
+    ad[0] = eps;
+  };
+
+  for (long long t = 0; t < a.n_steps; ++t) {
+    const unsigned long long step = a.step0 + (u64)t;
+    Rng rng; rng.init(a.seed, (u64)(a.chain0 + c.cidx), step);
+    u32 base = 0;
+    lp = eval<true>(h, b1, b2, y, c.xs, c.N, c.Tn, c.has_rat, gh, g1, g2);
+    if (ad[9] == 0.0) {
+#pragma unroll
+      for (int k = 0; k < 6; ++k) mh[k] = 1.0;
+      m1 = 1.0; m2 = 1.0;
+      adapt_reset(ad, cfg);
+      init_stepsize(rng, base);
+    }
+    if (ad[9] == 1.0 && (double)step >= cfg.num_warmup) { ad[0] = exp(ad[3]); ad[9] = 2.0; }
+    const double eps = ad[0];
+    const int L = adapt_leaps(cfg.int_time, eps);
+    sample_p(rng, base);
+    const double H0 = -lp + kinetic();
+    const Hyper h0 = h; const double b10 = b1, b20 = b2, lp0 = lp;
+    for (int l = 0; l < L; ++l) lp = evolve(h, b1, b2, eps);
+    double H = -lp + kinetic();
+    if (isnan(H)) H = pos_inf();
+    double accept_prob = exp(H0 - H);
+    Rng ru = rng; ru.slot = base; base += 1;
+    const double u = ru.u01();
+    if (accept_prob < 1.0 && u > accept_prob) { h = h0; b1 = b10; b2 = b20; lp = lp0; }
+    else ++n_acc;
+    if (accept_prob > 1.0) accept_prob = 1.0;
+    if (ad[9] == 1.0) {
+      adapt_learn_stepsize(ad, cfg, accept_prob);
+      const bool in_w = adapt_in_window(ad, cfg), ends = adapt_window_ends(ad, cfg);
+      bool update = false;
+      if (in_w || ends) {
+        const double* hv = &h.mu1;
+        double wh[6], wh2[6];
+#pragma unroll
+        for (int k = 0; k < 6; ++k) { wh[k] = WM[(long long)hidx(k) * nc + c.cidx]; wh2[k] = WM2[(long long)hidx(k) * nc + c.cidx]; }
+        double w1 = WM[(long long)j1 * nc + c.cidx], w12 = WM2[(long long)j1 * nc + c.cidx];
+        double w2 = WM[(long long)j2 * nc + c.cidx], w22 = WM2[(long long)j2 * nc + c.cidx];
+        if (in_w) {
+          ad[8] += 1.0;
+#pragma unroll
+          for (int k = 0; k < 6; ++k) welford_add(ad[8], hv[k], wh[k], wh2[k]);
+          welford_add(ad[8], b1, w1, w12); welford_add(ad[8], b2, w2, w22);
+        }
+        if (ends) {
+          adapt_next_window(ad, cfg);
+#pragma unroll
+          for (int k = 0; k < 6; ++k) { mh[k] = adapt_window_var(ad[8], wh2[k], mh[k]); wh[k] = 0.0; wh2[k] = 0.0; }
+          m1 = adapt_window_var(ad[8], w12, m1); m2 = adapt_window_var(ad[8], w22, m2);
+          w1 = w12 = w2 = w22 = 0.0;
+          ad[8] = 0.0;
+          update = true;
+        }
+        __syncwarp();   // all lanes have read the replicated hyper entries before lane 0 rewrites them
+        if (c.active) {
+          if (c.lane == 0) {
+#pragma unroll
+            for (int k = 0; k < 6; ++k) { WM[(long long)hidx(k) * nc + c.chain] = wh[k]; WM2[(long long)hidx(k) * nc + c.chain] = wh2[k]; }
+          }
+          if (c.has_rat) {
+            WM[(long long)j1 * nc + c.chain] = w1; WM2[(long long)j1 * nc + c.chain] = w12;
+            WM[(long long)j2 * nc + c.chain] = w2; WM2[(long long)j2 * nc + c.chain] = w22;
+          }
+        }
+        __syncwarp();
+      }
+      ad[5] += 1.0;
+      if (update) {
+        lp = eval<true>(h, b1, b2, y, c.xs, c.N, c.Tn, c.has_rat, gh, g1, g2);
+        init_stepsize(rng, base);
+        ad[1] = log(10.0 * ad[0]); ad[2] = 0.0; ad[3] = 0.0; ad[4] = 0.0;
+      }
+    }
+    long long slot;
+    if (c.active && record_slot(a, t, &slot)) {
+      if (c.lane == 0) {
+        const double* hv = &h.mu1;
+        for (int k = 0; k < 5; ++k) record_value(a, slot, k, c.chain, hv[k]);
+        record_value(a, slot, c.P - 1, c.chain, h.ls);
+      }
+      if (c.has_rat) { record_value(a, slot, 5 + c.lane, c.chain, b1); record_value(a, slot, 5 + c.N + c.lane, c.chain, b2); }
+    }
+  }
+  if (c.active) {
+    double* Q = (double*)a.field[F_Q];
+    if (c.lane == 0) {
+      const double* hv = &h.mu1;
+      for (int k = 0; k < 6; ++k) { Q[(long long)hidx(k) * nc + c.chain] = hv[k]; MINV[(long long)hidx(k) * nc + c.chain] = mh[k]; }
+      for (int j = 0; j < STK_AD_LEN; ++j) AD[j * nc + c.chain] = ad[j];
+      ((double*)a.field[F_LP])[c.chain] = lp;
+      if (a.accept) a.accept[c.chain] += n_acc;
+    }
+    if (c.has_rat) {
+      Q[(long long)j1 * nc + c.chain] = b1; Q[(long long)j2 * nc + c.chain] = b2;
+      MINV[(long long)j1 * nc + c.chain] = m1; MINV[(long long)j2 * nc + c.chain] = m2;
+    }
+  }
+}
+
 template <bool GRAD>
 __device__ __forceinline__ void logp_entry(const StkArgs& a) {
   extern __shared__ __align__(16) double smem[];
@@ -247,8 +437,14 @@ extern "C" __device__ const char stk_desc[] =
     "field x data f64 0\n"
     "field y data f64 0\n"
     "param eps 0.02\n"
+    "field ad state f64 10\n"
+    "field minv state f64 66\n"
+    "field wm state f64 66\n"
+    "field wm2 state f64 66\n"
     "param L 10\n"
+    STK_ADAPT_PARAMS
     "record q\n"
     "kernel hmc birats_hmc 128 4 64 y 8\n"
+    "kernel hmc_adapt birats_hmc_adapt 128 4 64 y 8\n"
     "entry logp birats_logp 128 4 64 y 8\n"
     "entry logp_grad birats_logp_grad 128 4 64 y 8\n";

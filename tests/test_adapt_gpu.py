@@ -136,3 +136,45 @@ def test_linreg_adapt_vs_cmdstan(ctx):
     mu = draws.mean(axis=(0, 2)); mu[-1] = np.exp(draws[:, -1, :]).mean()
     sd = draws.std(axis=(0, 2))
     assert np.all(np.abs(mu - np.array(g["post_mean"])) < 0.1 * np.maximum(sd, 0.02)), (mu, g["post_mean"])
+
+
+def test_birats_adapt_trajectory_parity(ctx, orc):
+    """birats (warp per chain): the same adaptation, Philox blocks consumed in the oracle's order"""
+    import os
+    from stochaskell_b200 import Sampler
+    gold = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "birats_stan.npz"))
+    x, y = gold["x"], gold["y"]
+    C, seed = 9, 13
+    cfgd = dict(CFG, int_time=0.2, stepsize=0.1)
+    s = Sampler("builtin:birats", C, dict(x=x, y=y), seed=seed, ctx=ctx, first_global_chain=100)
+    ch = s.chains
+    set_cfg(ch, cfgd)
+    rng = np.random.default_rng(8)
+    q0 = np.repeat(gold["q"][0].reshape(-1, 1), C, axis=1) * (1 + 0.01 * rng.standard_normal((66, C)))
+    ch.set_state("q", q0)
+    cfg = orc.adapt_cfg(**cfgd)
+    chains = [0, 4, 8]
+    qs = {c: np.ascontiguousarray(q0[:, c]) for c in chains}
+    sts = {c: orc.adapt_state(66) for c in chains}
+    t = 0
+    for cp in [1, 2, 3, 60, 61, 62, 99, 100, 101, 102, 149, 150, 151, 199, 200, 201, 202, 210]:
+        span = cp - t
+        ch.step("hmc_adapt", span)
+        for c in chains:
+            for step in range(t, cp):
+                orc.birats_hmc_adapt_step(x, y, qs[c], sts[c], cfg, seed, 100 + c, step)
+        t = cp
+        q = ch.get_state("q"); ad = ch.get_state("ad"); minv = ch.get_state("minv")
+        wm = ch.get_state("wm"); wm2 = ch.get_state("wm2")
+        tol = 1e-9 if span == 1 else 1e-3
+        for c in chains:
+            ado = sts[c][0]
+            assert np.array_equal(ad[4:10, c], ado[4:10]), (cp, c, ad[:, c], ado)
+            if span == 1:   # longer spans: a 66-dimensional trajectory amplifies rounding until an accept decision flips
+                assert np.allclose(ad[0:4, c], ado[0:4], rtol=tol, atol=tol), (cp, c, ad[:, c], ado)
+                assert np.allclose(minv[:, c], sts[c][1], rtol=tol), (cp, c)
+                assert np.allclose(wm[:, c], sts[c][2], rtol=tol, atol=tol) and np.allclose(wm2[:, c], sts[c][3], rtol=tol, atol=tol)
+                scale = np.maximum(1.0, np.abs(qs[c]))
+                assert np.all(np.abs(q[:, c] - qs[c]) <= tol * scale), (cp, c, np.max(np.abs(q[:, c] - qs[c])))
+            qs[c][:] = q[:, c]; ado[:] = ad[:, c]; sts[c][1][:] = minv[:, c]; sts[c][2][:] = wm[:, c]; sts[c][3][:] = wm2[:, c]
+    assert np.all(ad[9] == 2.0)

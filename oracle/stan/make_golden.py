@@ -112,7 +112,7 @@ def linreg():
     print("linreg: lp", gold["small_lp"][:3], "post mean", gold["small_post_mean"][:3])
 
 
-def linreg_adapt():
+def linreg_adapt(engine="static"):
     """Adapted step sizes and diagonal inverse metrics of the reference's adaptive static sampler
     (`adapt engaged=1`, metric=diag_e) over 48 independent CmdStan chains of the full-size linreg problem:
     the statistical pin of csrc/stk_adapt.cuh / oracle/stk_oracle_adapt.cpp (tests/golden/linreg_adapt_stan.json)."""
@@ -127,11 +127,11 @@ def linreg_adapt():
     init = os.path.join(WORK, "linreg_adapt.init")
     rdump(init, x_stan_0_1=0.0, x_stan_0_2=np.zeros(d), x_stan_0_3=1.0)
     cfg = dict(num_warmup=300, num_samples=200, int_time=1.5, stepsize=1.0)
-    eps, minv, acc, means = [], [], [], []
+    eps, minv, acc, means, depth, nleap = [], [], [], [], [], []
     for c in range(48):
         out = os.path.join(WORK, f"adapt_{c}.csv")
         subprocess.run([exe, "method=sample", f"num_samples={cfg['num_samples']}", f"num_warmup={cfg['num_warmup']}",
-                        "adapt", "engaged=1", "algorithm=hmc", "engine=static", f"int_time={cfg['int_time']}",
+                        "adapt", "engaged=1", "algorithm=hmc"] + (["engine=static", f"int_time={cfg['int_time']}"] if engine == "static" else ["engine=nuts", "max_depth=10"]) + [
                         "metric=diag_e", f"stepsize={cfg['stepsize']}", "data", f"file={data}", f"init={init}",
                         "random", "seed=777", f"id={c + 1}", "output", f"file={out}"], check=True, capture_output=True)
         lines = open(out).read().splitlines()
@@ -142,12 +142,16 @@ def linreg_adapt():
         hdr = rows[0].split(",")
         arr = np.array([[float(v) for v in r.split(",")] for r in rows[1:]])
         acc.append(arr[:, hdr.index("accept_stat__")].mean())
+        if engine == "nuts":
+            depth.append(arr[:, hdr.index("treedepth__")].mean()); nleap.append(arr[:, hdr.index("n_leapfrog__")].mean())
         cols = [k for k, h in enumerate(hdr) if h.startswith("x_stan")]
         means.append(arr[:, cols].mean(axis=0))
     gold = dict(config=cfg, n=n, d=d, data_seed=20261104 + n, chains=48,
                 stepsize=eps, inv_metric=minv, accept_stat_mean=acc, post_mean=np.mean(means, axis=0).tolist(),
                 note="CmdStan 2.20 adapt_diag_e_static_hmc; inv_metric rows are on the unconstrained scale (b, w[10], log sigma)")
-    json.dump(gold, open(os.path.join(GOLD, "linreg_adapt_stan.json"), "w"), indent=1)
+    if engine == "nuts":
+        gold.update(treedepth_mean=depth, n_leapfrog_mean=nleap, note="CmdStan 2.20 adapt_diag_e_nuts (the hmcStan default), max_depth 10")
+    json.dump(gold, open(os.path.join(GOLD, "linreg_adapt_stan.json" if engine == "static" else "linreg_nuts_stan.json"), "w"), indent=1)
     print("linreg_adapt: eps", np.mean(eps), np.std(eps), "accept", np.mean(acc), "minv", np.mean(minv, axis=0)[:3])
 
 
@@ -274,7 +278,7 @@ def gp():
     print("gp: lp", gold["small_lp"], gold["mid_lp"][:2])
 
 
-MODELS = {"linreg": linreg, "linreg_adapt": linreg_adapt, "birats": birats, "gp": gp}
+MODELS = {"linreg": linreg, "linreg_adapt": linreg_adapt, "linreg_nuts": lambda: linreg_adapt("nuts"), "birats": birats, "gp": gp}
 
 if __name__ == "__main__":
     for m in (sys.argv[1:] or list(MODELS)):

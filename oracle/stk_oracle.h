@@ -122,6 +122,14 @@ int orc_birats_hmc_adapt_step(const double* x, const double* y, int N, int Tn, d
                               double* wm, double* wm2, const double* cfg, uint64_t seed, uint64_t chain, uint64_t step,
                               double* lp_out, double* out3);
 
+// NUTS with a diagonal metric + the same adaptation (hmcStan's default sampler); out5: accept_stat, eps, treedepth, n_leapfrog, divergent
+void orc_linreg_nuts_step(const double* X, const double* y, int n, int d, double* q, double* ad, double* minv, double* wm,
+                          double* wm2, const double* cfg, int max_depth, uint64_t seed, uint64_t chain, uint64_t step,
+                          double* lp_out, double* out5);
+void orc_birats_nuts_step(const double* x, const double* y, int N, int Tn, double* q, double* ad, double* minv, double* wm,
+                          double* wm2, const double* cfg, int max_depth, uint64_t seed, uint64_t chain, uint64_t step,
+                          double* lp_out, double* out5);
+
 #ifdef __cplusplus
 }
 #endif

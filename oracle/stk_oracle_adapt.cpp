@@ -95,46 +95,11 @@ struct Hmc {
 };
 }  // namespace
 
-#define ORC_MAX_LEAPS 1000000
-
-// One adaptive transition of one chain; returns 1 if the proposal was accepted.  out3 (optional): accept_stat, eps used, L used.
-static int hmc_adapt_step(int P, const LogpGrad& f, double* q, double* ad, double* minv, double* wm, double* wm2,
-                          const double* cfg, uint64_t seed, uint64_t chain, uint64_t step, double* lp_out, double* out3) {
-  orc_rng g; orc_rng_init(&g, seed, chain, step);
-  Hmc h(P, f, &g);
-  const Windows w = windows_of(cfg);
-  const double num_warmup = std::floor(cfg[2]);
+// learn_stepsize + learn_variance + (on a window end) init_stepsize and the dual-averaging restart:
+// adapt_diag_e_static_hmc.hpp:33-47 == adapt_diag_e_nuts.hpp:31-44 (the static engine adds update_L_, derived from eps)
+static void adapt_after_transition(Hmc& h, const LogpGrad& f, int P, double* q, double* ad, double* minv, double* wm,
+                                   double* wm2, const double* cfg, const Windows& w, double accept_prob) {
   std::vector<double> g0(P);
-  if (ad[9] == 0) {  // hmc_static_diag_e_adapt.hpp:62-74 + run_adaptive_sampler.hpp:55-57
-    for (int j = 0; j < P; ++j) { minv[j] = 1.0; wm[j] = 0; wm2[j] = 0; }
-    ad[0] = cfg[0]; ad[1] = std::log(10 * cfg[0]); ad[2] = ad[3] = ad[4] = 0;
-    ad[5] = 0; ad[7] = w.windows_on ? w.base : 0; ad[6] = w.windows_on ? w.init_buffer + w.base - 1 : -1; ad[8] = 0;
-    const double lp0 = f(q, g0.data());
-    h.init_stepsize(q, minv, &ad[0], lp0, g0);
-    ad[9] = 1;
-  }
-  if (ad[9] == 1 && (double)step >= num_warmup) { ad[0] = std::exp(ad[3]); ad[9] = 2; }  // complete_adaptation
-  // ---- transition (base_static_hmc.hpp:42-72) ----
-  const double eps = ad[0];
-  double Ld = std::floor(cfg[1] / eps);  // update_L_
-  if (!(Ld >= 1)) Ld = 1;
-  if (Ld > ORC_MAX_LEAPS) Ld = ORC_MAX_LEAPS;
-  const int L = (int)Ld;
-  h.sample_p(minv);
-  double lp = f(q, h.gr.data());
-  const double lp0 = lp;
-  const std::vector<double> q0(q, q + P);
-  const double H0 = -lp + h.kinetic(minv);
-  for (int l = 0; l < L; ++l) lp = h.evolve(q, minv, eps);
-  double H = -lp + h.kinetic(minv);
-  if (std::isnan(H)) H = std::numeric_limits<double>::infinity();
-  double accept_prob = std::exp(H0 - H);
-  const double u = orc_u01(&g);
-  int acc = 1;
-  if (accept_prob < 1 && u > accept_prob) { std::memcpy(q, q0.data(), sizeof(double) * P); lp = lp0; acc = 0; }
-  if (accept_prob > 1) accept_prob = 1;
-  if (out3) { out3[0] = accept_prob; out3[1] = eps; out3[2] = L; }
-  // ---- adaptation (adapt_diag_e_static_hmc.hpp:33-47) ----
   if (ad[9] == 1) {
     // learn_stepsize
     ad[4] += 1;
@@ -180,6 +145,48 @@ static int hmc_adapt_step(int P, const LogpGrad& f, double* q, double* ad, doubl
       ad[2] = ad[3] = ad[4] = 0;
     }
   }
+}
+
+#define ORC_MAX_LEAPS 1000000
+
+// One adaptive transition of one chain; returns 1 if the proposal was accepted.  out3 (optional): accept_stat, eps used, L used.
+static int hmc_adapt_step(int P, const LogpGrad& f, double* q, double* ad, double* minv, double* wm, double* wm2,
+                          const double* cfg, uint64_t seed, uint64_t chain, uint64_t step, double* lp_out, double* out3) {
+  orc_rng g; orc_rng_init(&g, seed, chain, step);
+  Hmc h(P, f, &g);
+  const Windows w = windows_of(cfg);
+  const double num_warmup = std::floor(cfg[2]);
+  std::vector<double> g0(P);
+  if (ad[9] == 0) {  // hmc_static_diag_e_adapt.hpp:62-74 + run_adaptive_sampler.hpp:55-57
+    for (int j = 0; j < P; ++j) { minv[j] = 1.0; wm[j] = 0; wm2[j] = 0; }
+    ad[0] = cfg[0]; ad[1] = std::log(10 * cfg[0]); ad[2] = ad[3] = ad[4] = 0;
+    ad[5] = 0; ad[7] = w.windows_on ? w.base : 0; ad[6] = w.windows_on ? w.init_buffer + w.base - 1 : -1; ad[8] = 0;
+    const double lp0 = f(q, g0.data());
+    h.init_stepsize(q, minv, &ad[0], lp0, g0);
+    ad[9] = 1;
+  }
+  if (ad[9] == 1 && (double)step >= num_warmup) { ad[0] = std::exp(ad[3]); ad[9] = 2; }  // complete_adaptation
+  // ---- transition (base_static_hmc.hpp:42-72) ----
+  const double eps = ad[0];
+  double Ld = std::floor(cfg[1] / eps);  // update_L_
+  if (!(Ld >= 1)) Ld = 1;
+  if (Ld > ORC_MAX_LEAPS) Ld = ORC_MAX_LEAPS;
+  const int L = (int)Ld;
+  h.sample_p(minv);
+  double lp = f(q, h.gr.data());
+  const double lp0 = lp;
+  const std::vector<double> q0(q, q + P);
+  const double H0 = -lp + h.kinetic(minv);
+  for (int l = 0; l < L; ++l) lp = h.evolve(q, minv, eps);
+  double H = -lp + h.kinetic(minv);
+  if (std::isnan(H)) H = std::numeric_limits<double>::infinity();
+  double accept_prob = std::exp(H0 - H);
+  const double u = orc_u01(&g);
+  int acc = 1;
+  if (accept_prob < 1 && u > accept_prob) { std::memcpy(q, q0.data(), sizeof(double) * P); lp = lp0; acc = 0; }
+  if (accept_prob > 1) accept_prob = 1;
+  if (out3) { out3[0] = accept_prob; out3[1] = eps; out3[2] = L; }
+  adapt_after_transition(h, f, P, q, ad, minv, wm, wm2, cfg, w, accept_prob);
   if (lp_out) *lp_out = lp;
   return acc;
 }
@@ -196,4 +203,141 @@ extern "C" int orc_birats_hmc_adapt_step(const double* x, const double* y, int N
                                          uint64_t chain, uint64_t step, double* lp_out, double* out3) {
   LogpGrad f = [&](const double* qq, double* gr) { return orc_birats_logp(x, y, N, Tn, qq, gr); };
   return hmc_adapt_step(2 * N + 6, f, q, ad, minv, wm, wm2, cfg, seed, chain, step, lp_out, out3);
+}
+
+// =====================================================================================================================
+// NUTS with a diagonal metric and adaptation — `hmcStan`'s DEFAULT sampler (Stan.hs:428-440: algorithm=hmc engine=nuts,
+// max_depth 10, metric diag_e, adapt engaged): cmdstan/stan/src/stan/mcmc/hmc/nuts/base_nuts.hpp:71-244 (transition,
+// build_tree, compute_criterion — the 2.20 form: multinomial sampling, generalised U-turn criterion on rho, no extra
+// sub-tree checks), adapt_diag_e_nuts.hpp:27-48.  Recursive exactly as the reference; the CUDA kernel builds the same
+// tree iteratively and must reproduce it leaf for leaf (same uniforms in the same post-order).
+// =====================================================================================================================
+namespace {
+double log_sum_exp2(double a, double b) {  // stan/math/prim/scal/fun/log_sum_exp.hpp
+  if (a == -std::numeric_limits<double>::infinity()) return b;
+  if (a == std::numeric_limits<double>::infinity() && b == std::numeric_limits<double>::infinity()) return a;
+  if (a > b) return a + std::log1p(std::exp(b - a));
+  return b + std::log1p(std::exp(a - b));
+}
+
+struct PsPoint { std::vector<double> q, p, g; double lp; };
+
+struct Nuts {
+  int P; const LogpGrad& f; orc_rng* rng; const double* minv; double eps; double max_deltaH;
+  PsPoint z;
+  int n_leapfrog; bool divergent; double sum_metro_prob;
+  double H() const { double k = 0; for (int j = 0; j < P; ++j) k += minv[j] * z.p[j] * z.p[j]; return -z.lp + 0.5 * k; }
+  void evolve(double e) {
+    for (int j = 0; j < P; ++j) { z.p[j] += 0.5 * e * z.g[j]; z.q[j] += e * minv[j] * z.p[j]; }
+    z.lp = f(z.q.data(), z.g.data());
+    for (int j = 0; j < P; ++j) z.p[j] += 0.5 * e * z.g[j];
+  }
+  std::vector<double> p_sharp() const { std::vector<double> s(P); for (int j = 0; j < P; ++j) s[j] = minv[j] * z.p[j]; return s; }
+  static bool criterion(const std::vector<double>& sm, const std::vector<double>& sp, const std::vector<double>& rho) {
+    double a = 0, b = 0;
+    for (size_t j = 0; j < rho.size(); ++j) { a += sp[j] * rho[j]; b += sm[j] * rho[j]; }
+    return a > 0 && b > 0;
+  }
+  bool build_tree(int depth, PsPoint& z_propose, std::vector<double>& ps_left, std::vector<double>& ps_right,
+                  std::vector<double>& rho, double H0, double sign, double& log_sum_weight) {
+    if (depth == 0) {
+      evolve(sign * eps);
+      ++n_leapfrog;
+      double h = H();
+      if (std::isnan(h)) h = std::numeric_limits<double>::infinity();
+      if ((h - H0) > max_deltaH) divergent = true;
+      log_sum_weight = log_sum_exp2(log_sum_weight, H0 - h);
+      if (H0 - h > 0) sum_metro_prob += 1; else sum_metro_prob += std::exp(H0 - h);
+      z_propose = z;
+      for (int j = 0; j < P; ++j) rho[j] += z.p[j];
+      ps_left = p_sharp(); ps_right = ps_left;
+      return !divergent;
+    }
+    std::vector<double> dummy(P);
+    double lsw_left = -std::numeric_limits<double>::infinity();
+    std::vector<double> rho_left(P, 0.0);
+    if (!build_tree(depth - 1, z_propose, ps_left, dummy, rho_left, H0, sign, lsw_left)) return false;
+    PsPoint z_propose_right = z;
+    double lsw_right = -std::numeric_limits<double>::infinity();
+    std::vector<double> rho_right(P, 0.0);
+    if (!build_tree(depth - 1, z_propose_right, dummy, ps_right, rho_right, H0, sign, lsw_right)) return false;
+    const double lsw_subtree = log_sum_exp2(lsw_left, lsw_right);
+    log_sum_weight = log_sum_exp2(log_sum_weight, lsw_subtree);
+    if (lsw_right > lsw_subtree) z_propose = z_propose_right;
+    else if (orc_u01(rng) < std::exp(lsw_right - lsw_subtree)) z_propose = z_propose_right;
+    std::vector<double> rho_subtree(P);
+    for (int j = 0; j < P; ++j) { rho_subtree[j] = rho_left[j] + rho_right[j]; rho[j] += rho_subtree[j]; }
+    return criterion(ps_left, ps_right, rho_subtree);
+  }
+};
+}  // namespace
+
+// One adaptive NUTS transition of one chain.  out5 (optional): accept_stat, eps, treedepth, n_leapfrog, divergent.
+static void nuts_adapt_step(int P, const LogpGrad& f, double* q, double* ad, double* minv, double* wm, double* wm2,
+                            const double* cfg, int max_depth, uint64_t seed, uint64_t chain, uint64_t step,
+                            double* lp_out, double* out5) {
+  orc_rng g; orc_rng_init(&g, seed, chain, step);
+  Hmc h(P, f, &g);
+  const Windows w = windows_of(cfg);
+  const double num_warmup = std::floor(cfg[2]);
+  std::vector<double> g0(P);
+  if (ad[9] == 0) {  // services/sample/hmc_nuts_diag_e_adapt.hpp + run_adaptive_sampler.hpp:55-57
+    for (int j = 0; j < P; ++j) { minv[j] = 1.0; wm[j] = 0; wm2[j] = 0; }
+    ad[0] = cfg[0]; ad[1] = std::log(10 * cfg[0]); ad[2] = ad[3] = ad[4] = 0;
+    ad[5] = 0; ad[7] = w.windows_on ? w.base : 0; ad[6] = w.windows_on ? w.init_buffer + w.base - 1 : -1; ad[8] = 0;
+    const double lp0 = f(q, g0.data());
+    h.init_stepsize(q, minv, &ad[0], lp0, g0);
+    ad[9] = 1;
+  }
+  if (ad[9] == 1 && (double)step >= num_warmup) { ad[0] = std::exp(ad[3]); ad[9] = 2; }
+  const double inf = std::numeric_limits<double>::infinity();
+  Nuts nt{P, f, &g, minv, ad[0], 1000.0, PsPoint(), 0, false, 0.0};
+  h.sample_p(minv);
+  nt.z.q.assign(q, q + P); nt.z.p.assign(h.p.begin(), h.p.begin() + P); nt.z.g.resize(P);
+  nt.z.lp = f(nt.z.q.data(), nt.z.g.data());
+  PsPoint z_plus = nt.z, z_minus = nt.z, z_sample = nt.z, z_propose = nt.z;
+  std::vector<double> ps_plus = nt.p_sharp(), ps_dummy = ps_plus, ps_minus = ps_plus, rho = nt.z.p;
+  double log_sum_weight = 0;
+  const double H0 = nt.H();
+  int depth = 0;
+  while (depth < max_depth) {
+    std::vector<double> rho_subtree(P, 0.0);
+    bool valid;
+    double lsw_subtree = -inf;
+    if (orc_u01(&g) > 0.5) {
+      nt.z = z_plus;
+      valid = nt.build_tree(depth, z_propose, ps_dummy, ps_plus, rho_subtree, H0, 1, lsw_subtree);
+      z_plus = nt.z;
+    } else {
+      nt.z = z_minus;
+      valid = nt.build_tree(depth, z_propose, ps_dummy, ps_minus, rho_subtree, H0, -1, lsw_subtree);
+      z_minus = nt.z;
+    }
+    if (!valid) break;
+    ++depth;
+    if (lsw_subtree > log_sum_weight) z_sample = z_propose;
+    else if (orc_u01(&g) < std::exp(lsw_subtree - log_sum_weight)) z_sample = z_propose;
+    log_sum_weight = log_sum_exp2(log_sum_weight, lsw_subtree);
+    for (int j = 0; j < P; ++j) rho[j] += rho_subtree[j];
+    if (!Nuts::criterion(ps_minus, ps_plus, rho)) break;
+  }
+  const double accept_prob = nt.sum_metro_prob / (double)nt.n_leapfrog;
+  std::memcpy(q, z_sample.q.data(), sizeof(double) * P);
+  if (out5) { out5[0] = accept_prob; out5[1] = ad[0]; out5[2] = depth; out5[3] = nt.n_leapfrog; out5[4] = nt.divergent; }
+  if (lp_out) *lp_out = z_sample.lp;
+  adapt_after_transition(h, f, P, q, ad, minv, wm, wm2, cfg, w, accept_prob);
+}
+
+extern "C" void orc_linreg_nuts_step(const double* X, const double* y, int n, int d, double* q, double* ad, double* minv,
+                                     double* wm, double* wm2, const double* cfg, int max_depth, uint64_t seed,
+                                     uint64_t chain, uint64_t step, double* lp_out, double* out5) {
+  LogpGrad f = [&](const double* qq, double* gr) { return orc_linreg_logp(X, y, n, d, qq, gr); };
+  nuts_adapt_step(d + 2, f, q, ad, minv, wm, wm2, cfg, max_depth, seed, chain, step, lp_out, out5);
+}
+
+extern "C" void orc_birats_nuts_step(const double* x, const double* y, int N, int Tn, double* q, double* ad, double* minv,
+                                     double* wm, double* wm2, const double* cfg, int max_depth, uint64_t seed,
+                                     uint64_t chain, uint64_t step, double* lp_out, double* out5) {
+  LogpGrad f = [&](const double* qq, double* gr) { return orc_birats_logp(x, y, N, Tn, qq, gr); };
+  nuts_adapt_step(2 * N + 6, f, q, ad, minv, wm, wm2, cfg, max_depth, seed, chain, step, lp_out, out5);
 }

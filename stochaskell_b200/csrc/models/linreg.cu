@@ -36,8 +36,8 @@ constexpr int RS = (D + 2) & ~1;  // smem row stride in doubles (x[D], y, pad) -
 static_assert(RS >= D + 1, "row stride");
 constexpr int NACC = D + 2;     // sum r, sum x_j r (D), sum r^2
 
-enum { F_Q = 0, F_LP = 1, F_X = 2, F_Y = 3, F_YSIM = 4, F_AD = 5, F_MINV = 6, F_WM = 7, F_WM2 = 8 };
-enum { PAR_EPS = 0, PAR_L = 1, PAR_RW = 2, PAR_ADAPT = 3 /* stepsize .. window, stk_adapt.cuh */ };
+enum { F_Q = 0, F_LP = 1, F_X = 2, F_Y = 3, F_YSIM = 4, F_AD = 5, F_MINV = 6, F_WM = 7, F_WM2 = 8, F_NUTS = 9 };
+enum { PAR_EPS = 0, PAR_L = 1, PAR_RW = 2, PAR_ADAPT = 3 /* stepsize .. window, stk_adapt.cuh */, PAR_MAXDEPTH = 13 };
 
 // stage [n][D] X and [n] y from HBM into smem rows
 __device__ __forceinline__ void stage_data(const StkArgs& a, double* xy, int n) {
@@ -416,6 +416,292 @@ linreg_hmc_adapt(const __grid_constant__ StkArgs a) {
 }
 
 // ---------------------------------------------------------------------------
+// NUTS with a diagonal metric + the same warm-up adaptation: `hmcStan`'s DEFAULT sampler (Stan.hs:428-440;
+// linreg.ipynb cell 7 runs it), cmdstan/stan/src/stan/mcmc/hmc/nuts/base_nuts.hpp:71-244 (2.20 form: multinomial
+// sampling, generalised U-turn criterion on rho) + adapt_diag_e_nuts.hpp:27-48.
+//
+// GPU form: the reference's recursive build_tree becomes an iterative one (leaf i of a subtree is followed by one
+// merge per trailing 1 bit of i, against a stack of pending left siblings — the same pairings and the same uniforms
+// in the same post-order), and every chain runs its own STATE MACHINE whose tick is one gradient evaluation: the CTA
+// ticks in lockstep (the data pass is cooperative across the K observation slices), but a chain that finishes a
+// transition starts its next one at once instead of waiting for the deepest tree of the CTA, so the cost of a launch
+// is max over the CTA's chains of the SUM of their leapfrogs, not the sum of the per-transition maxima.
+// oracle/stk_oracle_adapt.cpp (recursive, as the reference) must agree leaf for leaf.
+// ---------------------------------------------------------------------------
+constexpr int NUTS_MAXD = 10;
+enum { PH_START = 0, PH_TRIAL = 1, PH_LEAF = 2, PH_UPD = 3, PH_DONE = 4 };
+
+__device__ __forceinline__ double log_sum_exp2(double x, double y) {  // stan/math/prim/scal/fun/log_sum_exp.hpp
+  if (x == neg_inf()) return y;
+  if (x == pos_inf() && y == pos_inf()) return x;
+  if (x > y) return x + log1p(exp(y - x));
+  return y + log1p(exp(x - y));
+}
+
+extern "C" __global__ void __launch_bounds__(256, 1)
+linreg_nuts(const __grid_constant__ StkArgs a) {
+  extern __shared__ __align__(16) double smem[];
+  const int n = (int)a.flen[F_Y];
+  const int K = blockDim.x >> 5;
+  const int lane = threadIdx.x & 31, slice = threadIdx.x >> 5;
+  Smem sm(smem, n, K);
+  stage_data(a, sm.xy, n);
+  __syncthreads();
+
+  const long long chain = (long long)blockIdx.x * 32 + lane;
+  const bool active = chain < a.n_chains;
+  const long long cidx = active ? chain : a.n_chains - 1;
+  const long long nc = a.n_chains;
+  const bool writer = slice == 0 && active;
+  double* Q = (double*)a.field[F_Q];
+  double* AD = (double*)a.field[F_AD];
+  double* MINV = (double*)a.field[F_MINV];
+  double* WM = (double*)a.field[F_WM];
+  double* WM2 = (double*)a.field[F_WM2];
+  double* NS = (double*)a.field[F_NUTS];
+  AdaptCfg cfg; cfg.init(&a.par[PAR_ADAPT]);
+  int max_depth = (int)a.par[PAR_MAXDEPTH];
+  max_depth = max_depth < 1 ? 1 : (max_depth > NUTS_MAXD ? NUTS_MAXD : max_depth);
+
+  // ---- per-chain state (replicated in the K slices; every decision is taken redundantly and identically) ----
+  double q[P], minv[P], wm[P], wm2[P], ad[STK_AD_LEN];
+  double qe[P], ge[P], acc[NACC];               // evaluation point of the next tick / its gradient
+  double g0[P], lp0 = 0.0;                      // density and gradient at q (start of a transition, step-size trials)
+  double zq[P], zp[P], zg[P];                   // the end of the trajectory that is being extended
+  double eq[2][P], ep[2][P], eg[2][P];          // z_minus (0) and z_plus (1)
+  double qs[P], lps = 0.0, rho[P];              // z_sample, rho of the whole tree
+  double st_rho[NUTS_MAXD][P], st_psl[NUTS_MAXD][P], st_q[NUTS_MAXD][P], st_lsw[NUTS_MAXD], st_lp[NUTS_MAXD];
+  double lp = 0.0, lsw = 0.0, H0 = 0.0, sum_metro = 0.0, eps = 0.0, H0t = 0.0, teps = 0.0;
+  double stat_depth = 0.0, stat_leaps = 0.0, stat_div = 0.0, stat_acc = 0.0;
+  int phase = a.n_steps > 0 ? PH_START : PH_DONE, depth = 0, leaf = 0, sgn = 1, n_leap = 0, tdir = 0;
+  bool divergent = false, from_update = false;
+  long long t = 0;
+  unsigned long long n_acc = 0;
+  Rng rng; rng.init(a.seed, (u64)(a.chain0 + cidx), a.step0);
+#pragma unroll
+  for (int j = 0; j < P; ++j) {
+    q[j] = Q[j * nc + cidx]; minv[j] = MINV[j * nc + cidx]; wm[j] = WM[j * nc + cidx]; wm2[j] = WM2[j * nc + cidx];
+    qe[j] = q[j];
+  }
+#pragma unroll
+  for (int j = 0; j < STK_AD_LEN; ++j) ad[j] = AD[j * nc + cidx];
+
+  auto kinetic = [&](const double* p) {
+    double ke = 0.0;
+#pragma unroll
+    for (int j = 0; j < P; ++j) ke = fma(minv[j] * p[j], p[j], ke);
+    return 0.5 * ke;
+  };
+  auto sample_p = [&](double* p) {
+#pragma unroll
+    for (int j = 0; j < P; j += 2) {
+      double z0, z1; rng.normal2(z0, z1);
+      p[j] = z0 / sqrt(minv[j]); if (j + 1 < P) p[j + 1] = z1 / sqrt(minv[j + 1]);
+    }
+  };
+  // first half of a leapfrog step from (zq, zp, zg) with step e: zp <- half-kicked momentum, qe <- new position
+  auto half_step = [&](const double* q_from, const double* g_from, double e) {
+#pragma unroll
+    for (int j = 0; j < P; ++j) { zp[j] = fma(0.5 * e, g_from[j], zp[j]); qe[j] = fma(e * minv[j], zp[j], q_from[j]); }
+  };
+  auto prepare_leaf = [&]() { half_step(zq, zg, sgn * eps); phase = PH_LEAF; };
+  auto start_subtree = [&]() {
+    sgn = rng.u01() > 0.5 ? 1 : -1;
+    const int e = sgn > 0 ? 1 : 0;
+#pragma unroll
+    for (int j = 0; j < P; ++j) { zq[j] = eq[e][j]; zp[j] = ep[e][j]; zg[j] = eg[e][j]; }
+    leaf = 0;
+    prepare_leaf();
+  };
+  auto prepare_trial = [&]() {
+    sample_p(zp);
+    H0t = -lp0 + kinetic(zp);
+    half_step(q, g0, teps);
+    phase = PH_TRIAL;
+  };
+  auto begin_transition = [&]() {
+    const unsigned long long step = a.step0 + (u64)t;
+    if (ad[9] == 1.0 && (double)step >= cfg.num_warmup) { ad[0] = exp(ad[3]); ad[9] = 2.0; }  // complete_adaptation
+    eps = ad[0];
+    sample_p(zp);
+#pragma unroll
+    for (int j = 0; j < P; ++j) {
+      eq[0][j] = eq[1][j] = q[j]; ep[0][j] = ep[1][j] = zp[j]; eg[0][j] = eg[1][j] = g0[j];
+      qs[j] = q[j]; rho[j] = zp[j];
+    }
+    lps = lp0; lsw = 0.0; H0 = -lp0 + kinetic(zp);
+    depth = 0; n_leap = 0; sum_metro = 0.0; divergent = false;
+    start_subtree();
+  };
+  auto begin_init_stepsize = [&](bool upd) {
+    from_update = upd; teps = ad[0]; tdir = 0;
+    if (teps == 0.0 || teps > 1e7) return false;
+    prepare_trial();
+    return true;
+  };
+  auto next_transition = [&]() {
+    ++t;
+    if (t >= a.n_steps) { phase = PH_DONE; return; }
+    rng.init(a.seed, (u64)(a.chain0 + cidx), a.step0 + (u64)t);
+#pragma unroll
+    for (int j = 0; j < P; ++j) qe[j] = q[j];
+    phase = PH_START;
+  };
+  auto end_transition = [&]() {
+    double accept_prob = sum_metro / (double)n_leap;
+#pragma unroll
+    for (int j = 0; j < P; ++j) q[j] = qs[j];
+    lp = lps;
+    ++n_acc;
+    stat_depth = depth; stat_leaps += n_leap; stat_div += divergent ? 1.0 : 0.0; stat_acc = accept_prob;
+    long long slot;
+    if (writer && record_slot(a, t, &slot)) {
+#pragma unroll
+      for (int j = 0; j < P; ++j) record_value(a, slot, j, chain, q[j]);
+    }
+    bool update = false;
+    if (ad[9] == 1.0) {
+      adapt_learn_stepsize(ad, cfg, accept_prob > 1.0 ? 1.0 : accept_prob);
+      const bool in_w = adapt_in_window(ad, cfg), ends = adapt_window_ends(ad, cfg);
+      if (in_w) {
+        ad[8] += 1.0;
+#pragma unroll
+        for (int j = 0; j < P; ++j) welford_add(ad[8], q[j], wm[j], wm2[j]);
+      }
+      if (ends) {
+        adapt_next_window(ad, cfg);
+#pragma unroll
+        for (int j = 0; j < P; ++j) { minv[j] = adapt_window_var(ad[8], wm2[j], minv[j]); wm[j] = 0.0; wm2[j] = 0.0; }
+        ad[8] = 0.0;
+        update = true;
+      }
+      ad[5] += 1.0;
+    }
+    if (update) {
+#pragma unroll
+      for (int j = 0; j < P; ++j) qe[j] = q[j];
+      phase = PH_UPD;
+    } else {
+      next_transition();
+    }
+  };
+
+  for (;;) {
+    const bool busy = phase != PH_DONE;
+    if (!__syncthreads_or(busy)) break;
+    data_pass<true>(sm.xy, n, slice, K, lane, sm.red, sm.tot, qe, acc);
+    const double lpe = finish_eval<true>(n, qe, acc, ge);
+    if (!busy) continue;
+    if (phase == PH_START || phase == PH_UPD) {
+      lp0 = lpe; lp = lpe;
+#pragma unroll
+      for (int j = 0; j < P; ++j) g0[j] = ge[j];
+      if (phase == PH_START) {
+        bool trials = false;
+        if (ad[9] == 0.0) {
+#pragma unroll
+          for (int j = 0; j < P; ++j) { minv[j] = 1.0; wm[j] = 0.0; wm2[j] = 0.0; }
+          adapt_reset(ad, cfg);
+          trials = begin_init_stepsize(false);
+        }
+        if (!trials) begin_transition();
+      } else if (!begin_init_stepsize(true)) {
+        ad[1] = log(10.0 * ad[0]); ad[2] = 0.0; ad[3] = 0.0; ad[4] = 0.0;
+        next_transition();
+      }
+    } else if (phase == PH_TRIAL) {
+#pragma unroll
+      for (int j = 0; j < P; ++j) zp[j] = fma(0.5 * teps, ge[j], zp[j]);
+      double h = -lpe + kinetic(zp);
+      if (isnan(h)) h = pos_inf();
+      if (!init_stepsize_update(teps, tdir, H0t - h)) {
+        prepare_trial();
+      } else {
+        ad[0] = teps;
+        if (from_update) {
+          ad[1] = log(10.0 * ad[0]); ad[2] = 0.0; ad[3] = 0.0; ad[4] = 0.0;
+          next_transition();
+        } else {
+          begin_transition();
+        }
+      }
+    } else {  // PH_LEAF: build_tree(depth == 0), then the merges that complete with this leaf
+      const double e = sgn * eps;
+#pragma unroll
+      for (int j = 0; j < P; ++j) { zq[j] = qe[j]; zg[j] = ge[j]; zp[j] = fma(0.5 * e, ge[j], zp[j]); }
+      ++n_leap;
+      double h = -lpe + kinetic(zp);
+      if (isnan(h)) h = pos_inf();
+      if (h - H0 > 1000.0) divergent = true;
+      double c_lsw = H0 - h, c_lp = lpe;
+      sum_metro += (H0 - h > 0.0) ? 1.0 : exp(H0 - h);
+      double c_rho[P], c_psl[P], c_q[P];
+#pragma unroll
+      for (int j = 0; j < P; ++j) { c_rho[j] = zp[j]; c_psl[j] = minv[j] * zp[j]; c_q[j] = zq[j]; }
+      bool valid = !divergent;
+      int k = 0;
+      while (valid && ((leaf >> k) & 1)) {
+        const double l_lsw = st_lsw[k];
+        const double sub = log_sum_exp2(l_lsw, c_lsw);
+        bool take_right = c_lsw > sub;
+        if (!take_right) take_right = rng.u01() < exp(c_lsw - sub);
+        double dl = 0.0, dr = 0.0;
+#pragma unroll
+        for (int j = 0; j < P; ++j) {
+          const double r = st_rho[k][j] + c_rho[j];
+          c_rho[j] = r;
+          c_psl[j] = st_psl[k][j];
+          if (!take_right) c_q[j] = st_q[k][j];
+          dr = fma(minv[j] * zp[j], r, dr); dl = fma(c_psl[j], r, dl);
+        }
+        if (!take_right) c_lp = st_lp[k];
+        c_lsw = sub;
+        valid = dr > 0.0 && dl > 0.0;
+        ++k;
+      }
+      if (!valid) {
+        end_transition();
+      } else if (leaf + 1 == (1 << depth)) {
+        const int en = sgn > 0 ? 1 : 0;
+#pragma unroll
+        for (int j = 0; j < P; ++j) { eq[en][j] = zq[j]; ep[en][j] = zp[j]; eg[en][j] = zg[j]; }
+        ++depth;
+        bool take = c_lsw > lsw;
+        if (!take) take = rng.u01() < exp(c_lsw - lsw);
+        lsw = log_sum_exp2(lsw, c_lsw);
+        double dp = 0.0, dm = 0.0;
+#pragma unroll
+        for (int j = 0; j < P; ++j) {
+          if (take) qs[j] = c_q[j];
+          rho[j] += c_rho[j];
+          dp = fma(minv[j] * ep[1][j], rho[j], dp); dm = fma(minv[j] * ep[0][j], rho[j], dm);
+        }
+        if (take) lps = c_lp;
+        if (!(dp > 0.0 && dm > 0.0) || depth >= max_depth) end_transition();
+        else start_subtree();
+      } else {
+#pragma unroll
+        for (int j = 0; j < P; ++j) { st_rho[k][j] = c_rho[j]; st_psl[k][j] = c_psl[j]; st_q[k][j] = c_q[j]; }
+        st_lsw[k] = c_lsw; st_lp[k] = c_lp;
+        ++leaf;
+        prepare_leaf();
+      }
+    }
+  }
+  if (writer) {
+#pragma unroll
+    for (int j = 0; j < P; ++j) {
+      Q[j * nc + chain] = q[j]; MINV[j * nc + chain] = minv[j]; WM[j * nc + chain] = wm[j]; WM2[j * nc + chain] = wm2[j];
+    }
+#pragma unroll
+    for (int j = 0; j < STK_AD_LEN; ++j) AD[j * nc + chain] = ad[j];
+    NS[0 * nc + chain] = stat_depth; NS[1 * nc + chain] += stat_leaps; NS[2 * nc + chain] += stat_div; NS[3 * nc + chain] = stat_acc;
+    ((double*)a.field[F_LP])[chain] = lp;
+    if (a.accept) a.accept[chain] += n_acc;
+  }
+}
+
+// ---------------------------------------------------------------------------
 // random-walk Metropolis (the `mh`-style kernel of mh.ipynb cell 1, proposal
 // q' = q + rw * N(0, I) on the unconstrained scale), n_steps per launch
 // ---------------------------------------------------------------------------
@@ -582,14 +868,17 @@ extern "C" __device__ const char stk_desc[] =
     "field minv state f64 " STR(LINREG_P) "\n"
     "field wm state f64 " STR(LINREG_P) "\n"
     "field wm2 state f64 " STR(LINREG_P) "\n"
+    "field nuts state f64 4\n"
     "param eps 0.01\n"
     "param L 10\n"
     "param rw 0.05\n"
     STK_ADAPT_PARAMS
+    "param max_depth 10\n"
     "record q\n"
     "kernel hmc linreg_hmc" GEOM
     "kernel mh linreg_mh" GEOM
     "kernel hmc_adapt linreg_hmc_adapt" GEOM
+    "kernel nuts linreg_nuts" GEOM
     "entry logp linreg_logp" GEOM
     "entry logp_grad linreg_logp_grad" GEOM
     "entry simulate linreg_simulate" GEOM;

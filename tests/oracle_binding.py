@@ -290,6 +290,26 @@ class Oracle:
         N, Tn = y.shape
         return self._adapt_step(self.l.orc_birats_hmc_adapt_step, x, y, N, Tn, q, st, cfg, seed, chain, step)
 
+    def _nuts_step(self, fn, a, b, i0, i1, q, st, cfg, max_depth, seed, chain, step):
+        ad, minv, wm, wm2 = st
+        lp = D(); out5 = np.zeros(5)
+        fn.restype = None
+        fn.argtypes = [P, P, C.c_int, C.c_int, P, P, P, P, P, P, C.c_int, C.c_uint64, C.c_uint64, C.c_uint64, P, P]
+        fn(_p(a), _p(b), i0, i1, _p(q), _p(ad), _p(minv), _p(wm), _p(wm2), _p(cfg), max_depth, seed, chain, step,
+           C.cast(C.byref(lp), P), _p(out5))
+        return lp.value, out5
+
+    def linreg_nuts_step(self, X, y, q, st, cfg, seed, chain, step, max_depth=10):
+        """one adaptive NUTS transition; q, st updated in place; returns (lp, [accept_stat, eps, treedepth, n_leapfrog, divergent])"""
+        X = np.ascontiguousarray(X, dtype=np.float64); y = np.ascontiguousarray(y, dtype=np.float64)
+        n, d = X.shape
+        return self._nuts_step(self.l.orc_linreg_nuts_step, X, y, n, d, q, st, cfg, max_depth, seed, chain, step)
+
+    def birats_nuts_step(self, x, y, q, st, cfg, seed, chain, step, max_depth=10):
+        x = np.ascontiguousarray(x, dtype=np.float64); y = np.ascontiguousarray(y, dtype=np.float64)
+        N, Tn = y.shape
+        return self._nuts_step(self.l.orc_birats_nuts_step, x, y, N, Tn, q, st, cfg, max_depth, seed, chain, step)
+
     def u01x2(self, seed, chain, step, slot):
         a = D(); b = D()
         self.l.orc_u01x2(seed, chain, step, slot, C.byref(a), C.byref(b))

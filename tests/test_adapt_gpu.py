@@ -178,3 +178,78 @@ def test_birats_adapt_trajectory_parity(ctx, orc):
                 assert np.all(np.abs(q[:, c] - qs[c]) <= tol * scale), (cp, c, np.max(np.abs(q[:, c] - qs[c])))
             qs[c][:] = q[:, c]; ado[:] = ad[:, c]; sts[c][1][:] = minv[:, c]; sts[c][2][:] = wm[:, c]; sts[c][3][:] = wm2[:, c]
     assert np.all(ad[9] == 2.0)
+
+
+def test_linreg_nuts_trajectory_parity(ctx, orc):
+    """the iterative per-chain state machine against the recursive restatement: tree depth and leapfrog counts exact,
+    states and adaptation transition by transition"""
+    from stochaskell_b200 import Sampler
+    n, d, C = 100, 10, 40
+    X, y = make_data(n, d)
+    cfgd = dict(CFG, num_warmup=200)
+    s = Sampler("builtin:linreg", C, dict(X=X, y=y), seed=19, ctx=ctx)
+    ch = s.chains
+    set_cfg(ch, cfgd)
+    rng = np.random.default_rng(6)
+    q0 = 0.1 * rng.standard_normal((d + 2, C))
+    ch.set_state("q", q0)
+    cfg = orc.adapt_cfg(**cfgd)
+    chains = [0, 7, 31, 32, 39]
+    qs = {c: np.ascontiguousarray(q0[:, c]) for c in chains}
+    sts = {c: orc.adapt_state(d + 2) for c in chains}
+    leaps = {c: 0.0 for c in chains}
+    singles = list(range(1, 13)) + [99, 100, 101, 102, 149, 150, 151, 152, 199, 200, 201, 202, 203, 204, 205, 230]
+    t = 0
+    for cp in singles:
+        span = cp - t
+        ch.step("nuts", span)
+        last = {}
+        for c in chains:
+            for step in range(t, cp):
+                _, o5 = orc.linreg_nuts_step(X, y, qs[c], sts[c], cfg, 19, c, step)
+                leaps[c] += o5[3]; last[c] = o5
+        t = cp
+        q = ch.get_state("q"); ad = ch.get_state("ad"); minv = ch.get_state("minv"); ns = ch.get_state("nuts")
+        wm = ch.get_state("wm"); wm2 = ch.get_state("wm2")
+        for c in chains:
+            ado = sts[c][0]
+            assert np.array_equal(ad[4:10, c], ado[4:10]), (cp, c, ad[:, c], ado)
+            if span == 1:
+                assert ns[0, c] == last[c][2] and ns[1, c] == leaps[c], (cp, c, ns[:, c], last[c], leaps[c])
+                assert np.allclose(ad[0:4, c], ado[0:4], rtol=1e-9, atol=1e-9), (cp, c, ad[:, c], ado)
+                assert np.allclose(minv[:, c], sts[c][1], rtol=1e-9), (cp, c)
+                assert np.allclose(q[:, c], qs[c], rtol=1e-9, atol=1e-9), (cp, c, q[:, c], qs[c])
+            qs[c][:] = q[:, c]; ado[:] = ad[:, c]; sts[c][1][:] = minv[:, c]; sts[c][2][:] = wm[:, c]; sts[c][3][:] = wm2[:, c]
+            leaps[c] = ns[1, c]
+    assert np.all(ad[9] == 2.0)
+
+
+def test_linreg_nuts_vs_cmdstan(ctx):
+    """1024 device chains against 48 chains of the reference's default sampler (tests/golden/linreg_nuts_stan.json)"""
+    import json, os
+    from stochaskell_b200 import Sampler
+    from tests.test_adapt_cpu import gold_problem
+    g = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "linreg_nuts_stan.json")))
+    _, X, y = gold_problem()
+    c = g["config"]
+    C = 1024
+    s = Sampler("builtin:linreg", C, dict(X=X, y=y), seed=23, ctx=ctx)
+    ch = s.chains
+    set_cfg(ch, dict(CFG, stepsize=c["stepsize"], num_warmup=c["num_warmup"]))
+    ch.set_state("q", np.zeros((g["d"] + 2, C)))
+    ch.step("nuts", c["num_warmup"])
+    l0 = ch.get_state("nuts")[1].copy()
+    ch.record(c["num_samples"])
+    ch.step("nuts", c["num_samples"])
+    draws = ch.draws()
+    ns = ch.get_state("nuts"); eps = ch.get_state("ad")[0]
+    leaps = (ns[1] - l0) / c["num_samples"]
+
+    def close(mine, ref, k=4.0):
+        se = np.hypot(np.std(mine) / np.sqrt(len(mine)), np.std(ref) / np.sqrt(len(ref)))
+        return abs(np.mean(mine) - np.mean(ref)) < k * se
+    assert close(eps, g["stepsize"]), (eps.mean(), np.mean(g["stepsize"]))
+    assert close(leaps, g["n_leapfrog_mean"]), (leaps.mean(), np.mean(g["n_leapfrog_mean"]))
+    mu = draws.mean(axis=(0, 2)); mu[-1] = np.exp(draws[:, -1, :]).mean()
+    assert np.allclose(mu, g["post_mean"], atol=0.005), (mu, g["post_mean"])
+    assert ns[2].sum() <= 0.02 * C * (c["num_warmup"] + c["num_samples"])     # divergences are rare (early warm-up only)

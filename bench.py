@@ -118,6 +118,53 @@ class LinregHMC:
         return orc.linreg_hmc_run(self.X, self.y, state["q"], T, self.eps, self.L, seed, chain0, step0, nthreads)
 
 
+class LinregNUTS(LinregHMC):
+    """C1 under hmcStan's DEFAULT sampler (linreg.ipynb cell 7): NUTS, diag_e metric, max_depth 10, after warm-up.
+    Chains start from an adapted state (step size and metric = the means over 48 chains of the vendored CmdStan's own
+    adaptation on this data, tests/golden/linreg_nuts_stan.json) so that the device arm and the CPU arm time the same
+    post-warm-up transitions."""
+    name = "linreg_nuts"
+    kernel = "nuts"
+    symbol = "linreg_nuts"
+    state_fields = ("q", "ad", "minv", "wm", "wm2")
+    e2e_fields = ("q",)
+    transitions_per_step = 50
+    diag_warmup = 50
+
+    def __init__(self):
+        super().__init__()
+        g = json.load(open(os.path.join(ROOT, "tests", "golden", "linreg_nuts_stan.json")))
+        rng = np.random.default_rng(g["data_seed"])
+        self.X = rng.standard_normal((self.n, self.d)); w = rng.standard_normal(self.d)
+        self.y = self.X @ w + 0.5 + rng.standard_normal(self.n)
+        self.gold = g
+        self.eps0 = float(np.mean(g["stepsize"])); self.minv0 = np.mean(g["inv_metric"], axis=0)
+        self.post = np.array(g["post_mean"]); self.post[-1] = np.log(self.post[-1])
+        self.evals = float(np.mean(g["n_leapfrog_mean"])) + 1.0   # leapfrogs + the evaluation that opens a transition
+        self.bytes_per_transition = self.evals * self.bytes_per_eval
+        self.describe = (f"C1 linreg n={self.n} d={self.d}, NUTS diag_e max_depth 10 after warm-up (hmcStan default; adapted "
+                         f"eps={self.eps0:.3f}, {self.evals - 1:.2f} leapfrogs/transition in the reference's own runs)")
+        self.roofline_note = ("algorithmic bytes = (mean leapfrogs per transition of the reference's sampler + 1) x 88,192 B; "
+                              "data is staged in shared memory, physical DRAM traffic is ~0; bound: fp64 pipe + the CTA ticking "
+                              "at the pace of its slowest chain")
+        self.cfg = np.array([1.0, 1.0, 0.0, 0.8, 0.05, 0.75, 10.0, 75, 50, 25], dtype=np.float64)
+
+    def params(self):
+        return dict(stepsize=1.0, num_warmup=0.0, max_depth=10.0)
+
+    def init_state(self, C, chain0):
+        rng = np.random.default_rng(4321 + chain0)
+        P = self.d + 2
+        ad = np.zeros((10, C)); ad[0] = self.eps0; ad[9] = 2.0
+        return dict(q=np.ascontiguousarray(self.post[:, None] + np.sqrt(self.minv0)[:, None] * rng.standard_normal((P, C))),
+                    ad=ad, minv=np.ascontiguousarray(np.repeat(self.minv0[:, None], C, axis=1)),
+                    wm=np.zeros((P, C)), wm2=np.zeros((P, C)))
+
+    def cpu_run(self, orc, state, T, seed, chain0, step0, nthreads):
+        return orc.linreg_nuts_run(self.X, self.y, state["q"], state["ad"], state["minv"], state["wm"], state["wm2"], T,
+                                   self.cfg, seed, chain0, step0, nthreads)
+
+
 class CoalRJ:
     """C2: coal-mining reversible-jump change-point sampler, 4096 chains (BASELINE.json configs[1]);
     coal t `rjmc` coalMove' t of app/rj/Main.hs:115-238 on the 191 disaster dates."""
@@ -332,7 +379,7 @@ class GPHMCTC(GPHMC):
         return r
 
 
-WORKLOADS = {"gp_hmc_tc": GPHMCTC, "linreg_hmc": LinregHMC, "coal_rj": CoalRJ, "birats_hmc": BiratsHMC, "dp_gibbs": DPGibbs, "gp_hmc": GPHMC}
+WORKLOADS = {"gp_hmc_tc": GPHMCTC, "linreg_hmc": LinregHMC, "linreg_nuts": LinregNUTS, "coal_rj": CoalRJ, "birats_hmc": BiratsHMC, "dp_gibbs": DPGibbs, "gp_hmc": GPHMC}
 DEFAULT_WORKLOAD = "coal_rj"
 
 
@@ -478,7 +525,8 @@ def run_native(args, wl, rank, world, local, torch, dist):
             for f in fields:
                 ch.get_state(f, out=host_out[f])
             for k in host_in:  # next step starts from the downloaded state, like a runCC loop
-                host_in[k][...] = host_out[k].reshape(host_in[k].shape)
+                if k in host_out:
+                    host_in[k][...] = host_out[k].reshape(host_in[k].shape)
         for _ in range(2):
             e2e_step()
         barrier()

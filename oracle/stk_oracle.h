@@ -130,6 +130,10 @@ void orc_birats_nuts_step(const double* x, const double* y, int N, int Tn, doubl
                           double* wm2, const double* cfg, int max_depth, uint64_t seed, uint64_t chain, uint64_t step,
                           double* lp_out, double* out5);
 
+long long orc_linreg_nuts_run(const double* X, const double* y, int n, int d, double* q, double* ad, double* minv, double* wm,
+                              double* wm2, long long C, long long T, const double* cfg, int max_depth, uint64_t seed,
+                              uint64_t chain0, uint64_t step0, int nthreads);
+
 #ifdef __cplusplus
 }
 #endif

@@ -341,3 +341,38 @@ extern "C" void orc_birats_nuts_step(const double* x, const double* y, int N, in
   LogpGrad f = [&](const double* qq, double* gr) { return orc_birats_logp(x, y, N, Tn, qq, gr); };
   nuts_adapt_step(2 * N + 6, f, q, ad, minv, wm, wm2, cfg, max_depth, seed, chain, step, lp_out, out5);
 }
+
+// CPU-baseline driver (bench.py cpu_baseline / --impl reference): C chains x T NUTS transitions, one sequential chain at
+// a time per host thread.  q, minv, wm, wm2 are [P][C], ad is [ORC_AD_LEN][C]; returns the total number of leapfrogs.
+#include <atomic>
+#include <thread>
+extern "C" long long orc_linreg_nuts_run(const double* X, const double* y, int n, int d, double* q, double* ad, double* minv,
+                                         double* wm, double* wm2, long long C, long long T, const double* cfg,
+                                         int max_depth, uint64_t seed, uint64_t chain0, uint64_t step0, int nthreads) {
+  const int P = d + 2;
+  std::atomic<long long> next{0}, leaps{0};
+  auto work = [&]() {
+    std::vector<double> qc(P), mc(P), w1(P), w2(P), ac(ORC_AD_LEN);
+    double o5[5];
+    for (;;) {
+      const long long c = next.fetch_add(1);
+      if (c >= C) break;
+      for (int j = 0; j < P; ++j) { qc[j] = q[(size_t)j * C + c]; mc[j] = minv[(size_t)j * C + c]; w1[j] = wm[(size_t)j * C + c]; w2[j] = wm2[(size_t)j * C + c]; }
+      for (int j = 0; j < ORC_AD_LEN; ++j) ac[j] = ad[(size_t)j * C + c];
+      long long nl = 0;
+      for (long long t = 0; t < T; ++t) {
+        orc_linreg_nuts_step(X, y, n, d, qc.data(), ac.data(), mc.data(), w1.data(), w2.data(), cfg, max_depth, seed,
+                             chain0 + c, step0 + t, nullptr, o5);
+        nl += (long long)o5[3];
+      }
+      for (int j = 0; j < P; ++j) { q[(size_t)j * C + c] = qc[j]; minv[(size_t)j * C + c] = mc[j]; wm[(size_t)j * C + c] = w1[j]; wm2[(size_t)j * C + c] = w2[j]; }
+      for (int j = 0; j < ORC_AD_LEN; ++j) ad[(size_t)j * C + c] = ac[j];
+      leaps.fetch_add(nl);
+    }
+  };
+  if (nthreads <= 1) { work(); return leaps.load(); }
+  std::vector<std::thread> th;
+  for (int i = 0; i < nthreads; ++i) th.emplace_back(work);
+  for (auto& t : th) t.join();
+  return leaps.load();
+}

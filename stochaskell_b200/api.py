@@ -249,6 +249,9 @@ class CudaMethod:
     # the trajectory length is int_time; kernel `hmc_adapt` of the module (csrc/stk_adapt.cuh).  Defaults are
     # CmdStan's (Stan.hs:428-440 leaves them untouched): delta 0.8, gamma 0.05, kappa 0.75, t0 10, windows 75/50/25.
     adapt: bool = False
+    # engine="nuts" (+ adapt=True, num_warmup=1000, step_size=1): hmcStan's default, kernel `nuts` (max_depth as below)
+    engine: str = "static"
+    max_depth: int = 10
     int_time: float = 0.0            # 0 = num_leapfrog * step_size
     delta: float = 0.8
     gamma: float = 0.05
@@ -309,12 +312,18 @@ def hmcCUDA(method: CudaMethod, module_spec: str, data: dict, init: Optional[Seq
     if method.adapt:
         if "stepsize" not in s.module.params:
             raise StkError(-1, f"module {module_spec} has no adaptive HMC kernel")
-        kernel = "hmc_adapt"
+        kernel = "nuts" if method.engine == "nuts" else "hmc_adapt"
+        if method.engine == "nuts":
+            ch.set_param("max_depth", float(method.max_depth))
         for k, v in dict(stepsize=method.step_size, int_time=method.int_time or method.num_leapfrog * method.step_size,
                          num_warmup=method.num_warmup, delta=method.delta, gamma=method.gamma, kappa=method.kappa,
                          t0=method.t0, init_buffer=method.init_buffer, term_buffer=method.term_buffer,
                          window=method.window).items():
             ch.set_param(k, float(v))
+    elif method.engine == "nuts":
+        # no adaptation: the nuts kernel with num_warmup = 0 would re-tune the step size (init_stepsize) and then use
+        # exp(x_bar) = 1 like the reference's `adapt engaged=0 ... engine=nuts` does NOT; keep the caller's step size
+        raise StkError(-1, "engine='nuts' needs adapt=True (the reference's default); fixed-step NUTS is not exposed")
     method = dataclasses.replace(method, kernel=kernel)
     if init is not None:
         ch.set_state("q", np.asarray(init, dtype=np.float64), broadcast=True)

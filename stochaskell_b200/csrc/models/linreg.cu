@@ -422,8 +422,8 @@ linreg_hmc_adapt(const __grid_constant__ StkArgs a) {
 //
 // GPU form: the reference's recursive build_tree becomes an iterative one (leaf i of a subtree is followed by one
 // merge per trailing 1 bit of i, against a stack of pending left siblings — the same pairings and the same uniforms
-// in the same post-order), and every chain runs its own STATE MACHINE whose tick is one gradient evaluation: the CTA
-// ticks in lockstep (the data pass is cooperative across the K observation slices), but a chain that finishes a
+// in the same post-order), and every chain runs its own STATE MACHINE (in its slice-0 thread) whose tick is one gradient
+// evaluation: the CTA ticks in lockstep (the data pass is cooperative across the K observation slices), but a chain that finishes a
 // transition starts its next one at once instead of waiting for the deepest tree of the CTA, so the cost of a launch
 // is max over the CTA's chains of the SUM of their leapfrogs, not the sum of the per-transition maxima.
 // oracle/stk_oracle_adapt.cpp (recursive, as the reference) must agree leaf for leaf.
@@ -463,7 +463,7 @@ linreg_nuts(const __grid_constant__ StkArgs a) {
   int max_depth = (int)a.par[PAR_MAXDEPTH];
   max_depth = max_depth < 1 ? 1 : (max_depth > NUTS_MAXD ? NUTS_MAXD : max_depth);
 
-  // ---- per-chain state (replicated in the K slices; every decision is taken redundantly and identically) ----
+  // ---- per-chain state (used by the chain's slice-0 thread) ----
   double q[P], minv[P], wm[P], wm2[P], ad[STK_AD_LEN];
   double qe[P], ge[P], acc[NACC];               // evaluation point of the next tick / its gradient
   double g0[P], lp0 = 0.0;                      // density and gradient at q (start of a transition, step-size trials)
@@ -586,12 +586,23 @@ linreg_nuts(const __grid_constant__ StkArgs a) {
     }
   };
 
+  // Only slice 0 runs the state machine (its K-1 replicas would only multiply the local-memory traffic of the tree
+  // stack by K); it publishes the next evaluation point through the — at that moment idle — reduction buffer.
   for (;;) {
-    const bool busy = phase != PH_DONE;
+    const bool busy = slice == 0 && phase != PH_DONE;
+    if (slice == 0) {
+#pragma unroll
+      for (int j = 0; j < P; ++j) sm.red[j * 32 + lane] = qe[j];
+    }
     if (!__syncthreads_or(busy)) break;
+    if (slice != 0) {
+#pragma unroll
+      for (int j = 0; j < P; ++j) qe[j] = sm.red[j * 32 + lane];
+    }
+    __syncthreads();
     data_pass<true>(sm.xy, n, slice, K, lane, sm.red, sm.tot, qe, acc);
-    const double lpe = finish_eval<true>(n, qe, acc, ge);
     if (!busy) continue;
+    const double lpe = finish_eval<true>(n, qe, acc, ge);
     if (phase == PH_START || phase == PH_UPD) {
       lp0 = lpe; lp = lpe;
 #pragma unroll

@@ -310,6 +310,19 @@ class Oracle:
         N, Tn = y.shape
         return self._nuts_step(self.l.orc_birats_nuts_step, x, y, N, Tn, q, st, cfg, max_depth, seed, chain, step)
 
+    def linreg_nuts_run(self, X, y, q, ad, minv, wm, wm2, T, cfg, seed, chain0=0, step0=0, nthreads=1, max_depth=10):
+        """q/minv/wm/wm2 [P][C], ad [10][C] float64 contiguous, updated in place; returns the total number of leapfrogs"""
+        X = np.ascontiguousarray(X, dtype=np.float64); y = np.ascontiguousarray(y, dtype=np.float64)
+        n, d = X.shape
+        fn = self.l.orc_linreg_nuts_run
+        fn.restype = C.c_longlong
+        fn.argtypes = [P, P, C.c_int, C.c_int, P, P, P, P, P, C.c_longlong, C.c_longlong, P, C.c_int, C.c_uint64,
+                       C.c_uint64, C.c_uint64, C.c_int]
+        for a in (q, ad, minv, wm, wm2):
+            assert a.flags.c_contiguous and a.dtype == np.float64
+        return fn(_p(X), _p(y), n, d, _p(q), _p(ad), _p(minv), _p(wm), _p(wm2), q.shape[1], T, _p(cfg), max_depth, seed,
+                  chain0, step0, nthreads)
+
     def u01x2(self, seed, chain, step, slot):
         a = D(); b = D()
         self.l.orc_u01x2(seed, chain, step, slot, C.byref(a), C.byref(b))

@@ -168,6 +168,36 @@ int stk_num_recorded_values(stk_chains* ch);
 int stk_num_params(stk_chains* ch);
 int64_t stk_num_chains(stk_chains* ch);
 
+/* ---- wire formats either side of the HMC path (csrc/stk_io.cpp) ------------------------------------------
+ * R dump: the text `stanDump` writes for data and initial values (Stan.hs:346-363) and CmdStan reads (`data file=`,
+ * `init=`).  stk_rdump_parse replaces the reference's reliance on CmdStan's own reader: values come back column-major
+ * as in the file, dims = {} for a scalar.  stk_rdump_format writes one `name <- value` line in stanDump's shape.
+ * Stan CSV: what `runStan` reads back through `stanRead` (Stan.hs:365-371, 466-484): `#` comments, a header of column
+ * names (`lp__`, `name.i.j`), one row per draw.  Errors: STK_ERR_ARG with stk_last_error(), e.g. "CSV file contains no
+ * data" (the message of Stan.hs:371). */
+typedef struct stk_rdump stk_rdump;
+typedef struct stk_csv stk_csv;
+int stk_rdump_parse(const char* text, stk_rdump** out);
+int stk_rdump_count(const stk_rdump* d);
+const char* stk_rdump_name(const stk_rdump* d, int i);
+int stk_rdump_ndim(const stk_rdump* d, int i);
+const long long* stk_rdump_dims(const stk_rdump* d, int i);
+int stk_rdump_is_int(const stk_rdump* d, int i);
+long long stk_rdump_size(const stk_rdump* d, int i);
+const double* stk_rdump_values(const stk_rdump* d, int i);
+void stk_rdump_free(stk_rdump* d);
+int stk_rdump_format(const char* name, const double* values, int is_int, int ndim, const long long* dims,
+                     char* buf, size_t cap, size_t* need);
+int stk_stan_csv_write(const char* path, int n_cols, const char* const* col_names, const double* draws,
+                       long long n_draws, long long stride_draw, long long stride_col, const char* comment);
+int stk_stan_csv_read(const char* path, stk_csv** out);
+int stk_csv_cols(const stk_csv* c);
+long long stk_csv_rows(const stk_csv* c);
+const char* stk_csv_col_name(const stk_csv* c, int i);
+const double* stk_csv_values(const stk_csv* c);      /* row-major [rows][cols] */
+const char* stk_csv_comments(const stk_csv* c);
+void stk_csv_free(stk_csv* c);
+
 #ifdef __cplusplus
 }
 #endif

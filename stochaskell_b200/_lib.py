@@ -60,6 +60,27 @@ SIGNATURES = {
     "stk_num_params": (C.c_int, [C.c_void_p]),
     "stk_num_chains": (C.c_int64, [C.c_void_p]),
     "stk_num_recorded_values": (C.c_int, [C.c_void_p]),
+    # wire formats (csrc/stk_io.cpp)
+    "stk_rdump_parse": (C.c_int, [C.c_char_p, C.POINTER(C.c_void_p)]),
+    "stk_rdump_count": (C.c_int, [C.c_void_p]),
+    "stk_rdump_name": (C.c_char_p, [C.c_void_p, C.c_int]),
+    "stk_rdump_ndim": (C.c_int, [C.c_void_p, C.c_int]),
+    "stk_rdump_dims": (C.POINTER(C.c_longlong), [C.c_void_p, C.c_int]),
+    "stk_rdump_is_int": (C.c_int, [C.c_void_p, C.c_int]),
+    "stk_rdump_size": (C.c_longlong, [C.c_void_p, C.c_int]),
+    "stk_rdump_values": (C.POINTER(C.c_double), [C.c_void_p, C.c_int]),
+    "stk_rdump_free": (None, [C.c_void_p]),
+    "stk_rdump_format": (C.c_int, [C.c_char_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_size_t,
+                                   C.POINTER(C.c_size_t)]),
+    "stk_stan_csv_write": (C.c_int, [C.c_char_p, C.c_int, C.POINTER(C.c_char_p), C.c_void_p, C.c_longlong, C.c_longlong,
+                                     C.c_longlong, C.c_char_p]),
+    "stk_stan_csv_read": (C.c_int, [C.c_char_p, C.POINTER(C.c_void_p)]),
+    "stk_csv_cols": (C.c_int, [C.c_void_p]),
+    "stk_csv_rows": (C.c_longlong, [C.c_void_p]),
+    "stk_csv_col_name": (C.c_char_p, [C.c_void_p, C.c_int]),
+    "stk_csv_values": (C.POINTER(C.c_double), [C.c_void_p]),
+    "stk_csv_comments": (C.c_char_p, [C.c_void_p]),
+    "stk_csv_free": (None, [C.c_void_p]),
 }
 
 

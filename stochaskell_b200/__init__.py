@@ -6,6 +6,6 @@ the IR -> CUDA code generator in stkc.py, and the diagnostics plumbing.
 """
 from ._lib import LIB_PATH, StkError, lib  # noqa: F401
 from .api import (Chains, Context, CudaMethod, Module, Sampler, compile_source,  # noqa: F401
-                  compileCUDA, diag_finish, hmcCUDA, ir_to_cuda, runCUDA)
+                  compileCUDA, diag_finish, hmcCUDA, ir_to_cuda, runCUDA, runStanCUDA)
 from .io import (rdump_dumps, rdump_load, rdump_loads, read_stan_csv, stan_columns,  # noqa: F401
                  write_stan_csv)

@@ -335,3 +335,72 @@ def hmcCUDA(method: CudaMethod, module_spec: str, data: dict, init: Optional[Seq
     s.last_chains = ch
     hmcCUDA.last_sampler = s
     return out
+
+
+# ---------------------------------------------------------------------------
+# runStan-shaped entry point: R-dump files in, Stan CSV files out (Stan.hs:443-490)
+# ---------------------------------------------------------------------------
+# How a builtin module's fields map onto the identifiers of the Stan program Language.Stan generates for the same
+# model (data block / parameters block), and the constraining transform of its unconstrained `q`.
+STAN_BINDINGS = {
+    # linreg.ipynb cell 7 (vector w): data x_stan_0_0 (X), x_stan_0_4 (y); parameters x_stan_0_1 (b), x_stan_0_2 (w),
+    # x_stan_0_3 (sigma, <lower=0>: q holds log sigma)
+    "builtin:linreg": dict(
+        data={"X": "x_stan_0_0", "y": "x_stan_0_4"},
+        params=lambda d: [("x_stan_0_1", (), slice(0, 1)), ("x_stan_0_2", (d["X"].shape[1],), slice(1, 1 + d["X"].shape[1])),
+                          ("x_stan_0_3", (), slice(1 + d["X"].shape[1], 2 + d["X"].shape[1]))],
+        constrain=lambda q: np.concatenate([q[:-1], np.exp(q[-1:])], axis=0),
+        unconstrain=lambda v: np.concatenate([v[:-1], np.log(v[-1:])], axis=0),
+    ),
+}
+
+
+def runStanCUDA(method: CudaMethod, module_spec: str, data_file: str, init_file: Optional[str] = None,
+                output_file: Optional[str] = None, csv_chains: int = 4) -> np.ndarray:
+    """`runStan` with the process boundary of the reference kept (Stan.hs:443-490): data and initial values come from the
+    R-dump files `stanDump` writes, the draws of the first `csv_chains` chains go to Stan CSV files
+    (`<output_file stem>_<chain>.csv`, CmdStan's per-chain layout: lp__, the constrained parameters) that `stanRead`
+    and stansummary read; returns the constrained draws [num_samples][P][num_chains]."""
+    from .io import rdump_load, stan_columns, write_stan_csv
+    b = STAN_BINDINGS.get(module_spec)
+    if b is None:
+        raise StkError(-1, f"no Stan identifier binding for {module_spec}")
+    env = rdump_load(data_file)
+    data = {}
+    for field, ident in b["data"].items():
+        if ident not in env:
+            raise StkError(-1, f"{data_file}: variable {ident} (field {field}) is missing")
+        data[field] = np.ascontiguousarray(env[ident], dtype=np.float64)
+    layout = b["params"](data)
+    init = None
+    if init_file:
+        ienv = rdump_load(init_file)
+        P = layout[-1][2].stop
+        v = np.zeros(P)
+        for ident, shape, sl in layout:
+            if ident not in ienv:
+                raise StkError(-1, f"{init_file}: parameter {ident} is missing")
+            v[sl] = np.asarray(ienv[ident], dtype=np.float64).flatten(order="F")
+        init = b["unconstrain"](v)
+    draws = hmcCUDA(method, module_spec, data, init=init)
+    ch = hmcCUDA.last_sampler.chains
+    cons = np.stack([b["constrain"](draws[t]) for t in range(draws.shape[0])]) if draws.size else draws
+    if output_file:
+        names = ["lp__"] + [c for ident, shape, _ in layout for c in stan_columns(ident, shape)]
+        stem = output_file[:-4] if output_file.endswith(".csv") else output_file
+        eps = ch.get_state("ad")[0] if method.adapt else None
+        minv = ch.get_state("minv") if method.adapt else None
+        # lp__ per draw: the module's logp entry on the recorded draws (joint log-density on the unconstrained scale with
+        # all constants kept, as Program.hs `lpdf`; Stan's own lp__ drops the constants of `~` statements)
+        q_last = ch.get_state("q")
+        lps = np.stack([(ch.set_state("q", np.ascontiguousarray(draws[t])), ch.logp())[1] for t in range(draws.shape[0])]) \
+            if draws.shape[0] else np.zeros((0, draws.shape[2]))
+        ch.set_state("q", q_last)
+        for c in range(min(csv_chains, draws.shape[2])):
+            lp = lps[:, c:c + 1]
+            comment = f"model = {module_spec}\nalgorithm = hmc, engine = {method.engine}, chains = {method.num_chains}, chain = {c + 1}"
+            if eps is not None:
+                comment += (f"\nAdaptation terminated\nStep size = {eps[c]:.6g}\nDiagonal elements of inverse mass matrix:\n"
+                            + ", ".join(f"{x:.6g}" for x in minv[:, c]))
+            write_stan_csv(f"{stem}_{c + 1}.csv", names, np.concatenate([lp, cons[:, :, c]], axis=1), comment=comment)
+    return cons

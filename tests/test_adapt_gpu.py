@@ -253,3 +253,23 @@ def test_linreg_nuts_vs_cmdstan(ctx):
     mu = draws.mean(axis=(0, 2)); mu[-1] = np.exp(draws[:, -1, :]).mean()
     assert np.allclose(mu, g["post_mean"], atol=0.005), (mu, g["post_mean"])
     assert ns[2].sum() <= 0.02 * C * (c["num_warmup"] + c["num_samples"])     # divergences are rare (early warm-up only)
+
+
+def test_runstan_shaped_entry_point(ctx, tmp_path):
+    """R-dump data + init files in (the ones the vendored CmdStan consumed), Stan CSV out, read back by the C-ABI reader;
+    the posterior agrees with the CSV CmdStan itself produced from the same files (tests/golden/wire/)"""
+    import os
+    from stochaskell_b200 import CudaMethod, read_stan_csv, runStanCUDA
+    W = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "wire")
+    m = CudaMethod(num_chains=256, num_samples=100, num_warmup=150, step_size=1.0, adapt=True, engine="nuts", seed=5)
+    out = str(tmp_path / "out.csv")
+    cons = runStanCUDA(m, "builtin:linreg", os.path.join(W, "linreg_tiny.data.R"), os.path.join(W, "linreg_tiny.init.R"), out, csv_chains=2)
+    assert cons.shape == (100, 12, 256) and np.all(cons[:, -1, :] > 0)
+    names, v, comments = read_stan_csv(str(tmp_path / "out_2.csv"))
+    ref_names, ref, _ = read_stan_csv(os.path.join(W, "linreg_tiny_stan.csv"))
+    assert names == ["lp__"] + [n for n in ref_names if n.startswith("x_stan")]
+    assert v.shape == (100, 13) and np.array_equal(v[:, 1:], cons[:, :, 1]) and "Step size" in comments and np.all(np.isfinite(v[:, 0]))
+    # n = 6 observations, d = 10: a prior-dominated posterior (sd ~ 10); CmdStan's 12 draws vs our 25,600
+    cols = [ref_names.index(n) for n in names[1:]]
+    mu, sd = cons.mean(axis=(0, 2)), cons.std(axis=(0, 2))
+    assert np.all(np.abs(ref[:, cols].mean(axis=0) - mu) < 4 * sd / np.sqrt(3) + 1e-9)

@@ -15,7 +15,7 @@
 -- sources (Data.Program, Data.Expression, Data.Expression.Const) but has NOT been compiled; the same calls are
 -- exercised from Python (stochaskell_b200/api.py) by the test suite.  INTEGRATION.md lists what a maintainer adds.
 module Language.CUDA
-  ( compileCUDA, runCUDA, hmcCUDA, CudaMethod(..), defaultCudaMethod
+  ( compileCUDA, runCUDA, hmcCUDA, CudaMethod(..), CudaEngine(..), defaultCudaMethod, stanDefaultMethod
   , StkCtx, StkModule, StkChains, withCtx
   ) where
 
@@ -164,8 +164,12 @@ runCUDA prog x = do
 -- HMC (hmcStan's counterpart)                                              --
 ------------------------------------------------------------------------------
 
--- | mirrors StanMethod / StanHMCEngine (Language/Stan.hs:378-440) for the engine the kernels implement:
--- static HMC, unit_e metric, no adaptation (= benchStanHMC, app/benchmark/Main.hs:248-262)
+-- | mirrors StanMethod / StanHMCEngine (Language/Stan.hs:378-440).  Engines the kernels implement:
+--   CudaStatic  static HMC, unit_e metric, no adaptation (= benchStanHMC, app/benchmark/Main.hs:248-262): kernel "hmc"
+--   CudaStaticAdapt  Stan's adapt_diag_e_static_hmc per chain (dual averaging + windowed diagonal metric): "hmc_adapt"
+--   CudaNuts    hmcStan's DEFAULT (Stan.hs:428-440: NUTS, diag_e, adaptation, max_depth 10, stepsize 1): kernel "nuts"
+data CudaEngine = CudaStatic | CudaStaticAdapt | CudaNuts deriving (Eq, Show)
+
 data CudaMethod = CudaSample
   { numChains  :: Int
   , numSamples :: Int
@@ -174,12 +178,20 @@ data CudaMethod = CudaSample
   , hmcStepSize :: Double
   , hmcNumLeapfrog :: Int   -- int_time = hmcNumLeapfrog * hmcStepSize
   , seed       :: Word64
+  , engine     :: CudaEngine
+  , adaptDelta :: Double    -- 0.8; gamma 0.05, kappa 0.75, t0 10, windows 75/50/25 are the module's defaults (= CmdStan's)
+  , maxDepth   :: Int
   }
 
 defaultCudaMethod :: CudaMethod
 defaultCudaMethod = CudaSample
   { numChains = 4096, numSamples = 1000, numWarmup = 1000, thin = 1
-  , hmcStepSize = 0.01, hmcNumLeapfrog = 10, seed = 1 }
+  , hmcStepSize = 0.01, hmcNumLeapfrog = 10, seed = 1
+  , engine = CudaStatic, adaptDelta = 0.8, maxDepth = 10 }
+
+-- | what `hmcStan n` runs (Stan.hs:493-496): NUTS with adaptation, n warm-up + n sampling transitions
+stanDefaultMethod :: Int -> CudaMethod
+stanDefaultMethod n = defaultCudaMethod { numSamples = n, numWarmup = n, hmcStepSize = 1, engine = CudaNuts }
 
 -- | static HMC on a builtin module ("builtin:linreg", ...): draws[sample][param][chain] on the unconstrained scale.
 -- hmcStan / hmcStanInit (Stan.hs:493-500) return [t]; here every chain's draws come back, chains x draws.
@@ -200,7 +212,14 @@ hmcCUDA CudaSample{..} spec dat initq = withCtx 0 $ \ctx ->
       i <- c_module_field m cn
       withArrayLen (realToFrac <$> q :: [CDouble]) $ \len p ->
         check "stk_set_state q" $ c_set_state ch i (castPtr p) (fromIntegral $ 8 * len) 1
-    kid <- withCString "hmc" $ c_module_kernel m
+    let setp name v = withCString name $ \cn -> check name $ c_set_param ch cn (realToFrac (v :: Double))
+    when (engine /= CudaStatic) $ do     -- the ten adaptation params of csrc/stk_adapt.cuh; the rest keep CmdStan's defaults
+      setp "stepsize" hmcStepSize
+      setp "int_time" (fromIntegral hmcNumLeapfrog * hmcStepSize)
+      setp "num_warmup" (fromIntegral numWarmup)
+      setp "delta" adaptDelta
+      when (engine == CudaNuts) $ setp "max_depth" (fromIntegral maxDepth)
+    kid <- withCString (case engine of { CudaStatic -> "hmc"; CudaStaticAdapt -> "hmc_adapt"; CudaNuts -> "nuts" }) $ c_module_kernel m
     when (numWarmup > 0) $ check "warmup" $ c_step ch kid (fromIntegral numWarmup) nullPtr
     check "stk_record" $ c_record ch (fromIntegral numSamples) (fromIntegral thin)
     check "stk_step" $ c_step ch kid (fromIntegral $ numSamples * thin) nullPtr

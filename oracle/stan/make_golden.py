@@ -254,6 +254,47 @@ def birats():
     print("birats: lp", lp[:3], "post mean", gold["post_mean"], "sd", gold["post_sd"])
 
 
+def birats_nuts():
+    """hmcStan's default sampler on birats (birats.ipynb cell 8 runs exactly this): 24 CmdStan chains of adapt_diag_e_nuts,
+    300 warm-up + 300 draws, from the golden point q[0]: adapted step size, tree depth, leapfrogs, posterior means."""
+    import json
+    os.makedirs(WORK, exist_ok=True)
+    open(os.path.join(WORK, "birats.stan"), "w").write(notebook_stan("birats.ipynb", 8))
+    exe = os.path.join(WORK, "birats")
+    if not os.path.exists(exe):
+        subprocess.run(["make", "-C", CMDSTAN, exe], check=True, capture_output=True)
+    g = np.load(os.path.join(GOLD, "birats_stan.npz"))
+    X, Y, q0 = g["x"], g["y"], g["q"][0]
+    N = 30
+    data = os.path.join(WORK, "birats.data"); rdump(data, x_stan_0_0=X, x_stan_0_6=Y)
+    init = os.path.join(WORK, "birats.init")
+    z = np.tanh(q0[4])
+    rdump(init, x_stan_0_1=q0[0:2], x_stan_0_2=q0[2:4], x_stan_0_3=np.array([[1, z], [z, 1.0]]),
+          x_stan_0_4=np.stack([q0[5:5 + N], q0[5 + N:5 + 2 * N]], axis=1), x_stan_0_5=np.exp(q0[-1]))
+    cfg = dict(num_warmup=300, num_samples=300, stepsize=1.0)
+    eps, acc, depth, nleap, means = [], [], [], [], []
+    sel = ["x_stan_0_1.1", "x_stan_0_1.2", "x_stan_0_2.1", "x_stan_0_2.2", "x_stan_0_3.1.2", "x_stan_0_5"]
+    for c in range(24):
+        out = os.path.join(WORK, f"birats_nuts_{c}.csv")
+        subprocess.run([exe, "method=sample", f"num_samples={cfg['num_samples']}", f"num_warmup={cfg['num_warmup']}",
+                        "data", f"file={data}", f"init={init}", "random", "seed=4321", f"id={c + 1}", "output", f"file={out}"],
+                       check=True, capture_output=True)
+        lines = open(out).read().splitlines()
+        i = next(k for k, l in enumerate(lines) if l.startswith("# Step size"))
+        eps.append(float(lines[i].split("=")[1]))
+        rows = [l for l in lines if l and not l.startswith("#")]
+        hdr = rows[0].split(","); arr = np.array([[float(v) for v in r.split(",")] for r in rows[1:]])
+        col = {h: k for k, h in enumerate(hdr)}
+        acc.append(arr[:, col["accept_stat__"]].mean()); depth.append(arr[:, col["treedepth__"]].mean())
+        nleap.append(arr[:, col["n_leapfrog__"]].mean()); means.append(arr[:, [col[h] for h in sel]].mean(axis=0))
+    gold = dict(config=cfg, chains=24, stepsize=eps, accept_stat_mean=acc, treedepth_mean=depth, n_leapfrog_mean=nleap,
+                post_names=["betaMu1", "betaMu2", "tau1", "tau2", "rho", "sigma"], post_mean=np.mean(means, axis=0).tolist(),
+                post_chain_means=np.array(means).tolist(),
+                note="CmdStan 2.20 defaults (NUTS, diag_e, adapt engaged, max_depth 10) on the Stan program of birats.ipynb cell 8")
+    json.dump(gold, open(os.path.join(GOLD, "birats_nuts_stan.json"), "w"), indent=1)
+    print("birats_nuts: eps", np.mean(eps), np.std(eps), "depth", np.mean(depth), "leaps", np.mean(nleap), "acc", np.mean(acc), gold["post_mean"])
+
+
 def gp():
     """gp.ipynb cell 15: GP classifier, fixed SE kernel, whitened latent; lp/grad at n = 48 and n = 160"""
     os.makedirs(WORK, exist_ok=True)
@@ -278,7 +319,7 @@ def gp():
     print("gp: lp", gold["small_lp"], gold["mid_lp"][:2])
 
 
-MODELS = {"linreg": linreg, "linreg_adapt": linreg_adapt, "linreg_nuts": lambda: linreg_adapt("nuts"), "birats": birats, "gp": gp}
+MODELS = {"linreg": linreg, "linreg_adapt": linreg_adapt, "linreg_nuts": lambda: linreg_adapt("nuts"), "birats": birats, "birats_nuts": birats_nuts, "gp": gp}
 
 if __name__ == "__main__":
     for m in (sys.argv[1:] or list(MODELS)):

@@ -23,8 +23,8 @@ using namespace stk;
 namespace {
 
 constexpr int TMAX = 8;                 // observations per rat held in registers
-enum { F_Q = 0, F_LP = 1, F_X = 2, F_Y = 3, F_AD = 4, F_MINV = 5, F_WM = 6, F_WM2 = 7 };
-enum { PAR_EPS = 0, PAR_L = 1, PAR_ADAPT = 2 /* stepsize .. window, stk_adapt.cuh */ };
+enum { F_Q = 0, F_LP = 1, F_X = 2, F_Y = 3, F_AD = 4, F_MINV = 5, F_WM = 6, F_WM2 = 7, F_NUTS = 8 };
+enum { PAR_EPS = 0, PAR_L = 1, PAR_ADAPT = 2 /* stepsize .. window, stk_adapt.cuh */, PAR_MAXDEPTH = 12 };
 
 struct Hyper { double mu1, mu2, t1, t2, yo, ls; };
 
@@ -218,7 +218,21 @@ extern "C" __global__ void __launch_bounds__(128) birats_hmc(const __grid_consta
 // entries replicated).  Philox blocks are consumed in the oracle's order: a momentum draw takes (P+1)/2 blocks from
 // the running block counter, a uniform one.
 // ---------------------------------------------------------------------------------------------------------
-extern "C" __global__ void __launch_bounds__(128) birats_hmc_adapt(const __grid_constant__ StkArgs a) {
+struct TreeNode { double rh[6], r1, r2, sh[6], s1, s2, qh[6], q1, q2, lsw, lp; };   // a pending left sibling (NUTS)
+struct TreeEnd { double hv[6], b1, b2, ph[6], p1, p2, gh[6], g1, g2; };               // z_minus / z_plus
+
+__device__ __forceinline__ double log_sum_exp2(double x, double y) {  // stan/math/prim/scal/fun/log_sum_exp.hpp
+  if (x == neg_inf()) return y;
+  if (x == pos_inf() && y == pos_inf()) return x;
+  if (x > y) return x + log1p(exp(y - x));
+  return y + log1p(exp(x - y));
+}
+
+// NUTS = false: adapt_diag_e_static_hmc;  NUTS = true: adapt_diag_e_nuts (base_nuts.hpp:71-244, the default of hmcStan —
+// birats.ipynb cell 8 runs it), the tree built iteratively as in linreg_nuts; one warp = one chain, so the tree loops are
+// warp-uniform and no state machine is needed.
+template <bool NUTS>
+__device__ __forceinline__ void birats_adaptive(const StkArgs& a) {
   extern __shared__ __align__(16) double smem[];
   Ctx c; double y[TMAX];
   setup(a, smem, c, y);
@@ -241,6 +255,9 @@ extern "C" __global__ void __launch_bounds__(128) birats_hmc_adapt(const __grid_
   for (int k = 0; k < 6; ++k) mh[k] = MINV[(long long)hidx(k) * nc + c.cidx];
   m1 = MINV[(long long)j1 * nc + c.cidx]; m2 = MINV[(long long)j2 * nc + c.cidx];
   const u32 blocks_p = (u32)((c.P + 1) / 2);
+  int max_depth = (int)a.par[PAR_MAXDEPTH];
+  max_depth = max_depth < 1 ? 1 : (max_depth > 10 ? 10 : max_depth);
+  double st_depth = 0.0, st_leaps = 0.0, st_div = 0.0, st_acc = 0.0;
   unsigned long long n_acc = 0;
   double lp = 0.0, ph[6], p1, p2, gh[6], g1, g2;
 
@@ -314,19 +331,125 @@ extern "C" __global__ void __launch_bounds__(128) birats_hmc_adapt(const __grid_
       init_stepsize(rng, base);
     }
     if (ad[9] == 1.0 && (double)step >= cfg.num_warmup) { ad[0] = exp(ad[3]); ad[9] = 2.0; }
-    const double eps = ad[0];
-    const int L = adapt_leaps(cfg.int_time, eps);
-    sample_p(rng, base);
-    const double H0 = -lp + kinetic();
-    const Hyper h0 = h; const double b10 = b1, b20 = b2, lp0 = lp;
-    for (int l = 0; l < L; ++l) lp = evolve(h, b1, b2, eps);
-    double H = -lp + kinetic();
-    if (isnan(H)) H = pos_inf();
-    double accept_prob = exp(H0 - H);
-    Rng ru = rng; ru.slot = base; base += 1;
-    const double u = ru.u01();
-    if (accept_prob < 1.0 && u > accept_prob) { h = h0; b1 = b10; b2 = b20; lp = lp0; }
-    else ++n_acc;
+    double accept_prob;
+    if constexpr (!NUTS) {
+      const double eps = ad[0];
+      const int L = adapt_leaps(cfg.int_time, eps);
+      sample_p(rng, base);
+      const double H0 = -lp + kinetic();
+      const Hyper h0 = h; const double b10 = b1, b20 = b2, lp0 = lp;
+      for (int l = 0; l < L; ++l) lp = evolve(h, b1, b2, eps);
+      double H = -lp + kinetic();
+      if (isnan(H)) H = pos_inf();
+      accept_prob = exp(H0 - H);
+      Rng ru = rng; ru.slot = base; base += 1;
+      const double u = ru.u01();
+      if (accept_prob < 1.0 && u > accept_prob) { h = h0; b1 = b10; b2 = b20; lp = lp0; }
+      else ++n_acc;
+    } else {
+      const double eps = ad[0];
+      sample_p(rng, base);
+      auto save_end = [&](TreeEnd& e, const Hyper& zh, double zb1, double zb2) {
+        const double* hv = &zh.mu1;
+#pragma unroll
+        for (int k = 0; k < 6; ++k) { e.hv[k] = hv[k]; e.ph[k] = ph[k]; e.gh[k] = gh[k]; }
+        e.b1 = zb1; e.b2 = zb2; e.p1 = p1; e.p2 = p2; e.g1 = g1; e.g2 = g2;
+      };
+      auto dot = [&](const double* ah, double a1, double a2, const double* bh, double bb1, double bb2) {
+        double d = warp_sum(c.has_rat ? fma(a2, bb2, a1 * bb1) : 0.0);
+#pragma unroll
+        for (int k = 0; k < 6; ++k) d = fma(ah[k], bh[k], d);
+        return d;
+      };
+      TreeEnd ends2[2];
+      save_end(ends2[0], h, b1, b2); ends2[1] = ends2[0];
+      Hyper hs = h; double bs1 = b1, bs2 = b2, lps = lp;            // z_sample
+      double rh[6], r1 = p1, r2 = p2;                                // rho
+#pragma unroll
+      for (int k = 0; k < 6; ++k) rh[k] = ph[k];
+      double lsw = 0.0, sum_metro = 0.0;
+      const double H0 = -lp + kinetic();
+      int depth = 0, n_leap = 0;
+      bool divergent = false;
+      TreeNode st[10];
+      while (depth < max_depth) {
+        double ud; { Rng ru = rng; ru.slot = base; base += 1; ud = ru.u01(); }
+        const int en = ud > 0.5 ? 1 : 0;
+        const double e = en ? eps : -eps;
+        Hyper zh; double zb1, zb2;
+        {
+          const TreeEnd& te = ends2[en];
+          double* hv = &zh.mu1;
+#pragma unroll
+          for (int k = 0; k < 6; ++k) { hv[k] = te.hv[k]; ph[k] = te.ph[k]; gh[k] = te.gh[k]; }
+          zb1 = te.b1; zb2 = te.b2; p1 = te.p1; p2 = te.p2; g1 = te.g1; g2 = te.g2;
+        }
+        TreeNode cur;
+        bool valid = true;
+        const int leaves = 1 << depth;
+        for (int leaf = 0; leaf < leaves; ++leaf) {
+          const double lpz = evolve(zh, zb1, zb2, e);
+          ++n_leap;
+          double hh = -lpz + kinetic();
+          if (isnan(hh)) hh = pos_inf();
+          if (hh - H0 > 1000.0) divergent = true;
+          cur.lsw = H0 - hh; cur.lp = lpz;
+          sum_metro += (H0 - hh > 0.0) ? 1.0 : exp(H0 - hh);
+          const double* hv = &zh.mu1;
+#pragma unroll
+          for (int k = 0; k < 6; ++k) { cur.rh[k] = ph[k]; cur.sh[k] = mh[k] * ph[k]; cur.qh[k] = hv[k]; }
+          cur.r1 = p1; cur.r2 = p2; cur.s1 = m1 * p1; cur.s2 = m2 * p2; cur.q1 = zb1; cur.q2 = zb2;
+          valid = !divergent;
+          int k = 0;
+          while (valid && ((leaf >> k) & 1)) {
+            const TreeNode& l = st[k];
+            const double sub = log_sum_exp2(l.lsw, cur.lsw);
+            bool take_right = cur.lsw > sub;
+            if (!take_right) { Rng ru = rng; ru.slot = base; base += 1; take_right = ru.u01() < exp(cur.lsw - sub); }
+            double psr[6];
+#pragma unroll
+            for (int j = 0; j < 6; ++j) {
+              cur.rh[j] = l.rh[j] + cur.rh[j]; cur.sh[j] = l.sh[j]; psr[j] = mh[j] * ph[j];
+              if (!take_right) cur.qh[j] = l.qh[j];
+            }
+            cur.r1 = l.r1 + cur.r1; cur.r2 = l.r2 + cur.r2; cur.s1 = l.s1; cur.s2 = l.s2;
+            if (!take_right) { cur.q1 = l.q1; cur.q2 = l.q2; cur.lp = l.lp; }
+            cur.lsw = sub;
+            const double dr = dot(psr, m1 * p1, m2 * p2, cur.rh, cur.r1, cur.r2);
+            const double dl = dot(cur.sh, cur.s1, cur.s2, cur.rh, cur.r1, cur.r2);
+            valid = dr > 0.0 && dl > 0.0;
+            ++k;
+          }
+          if (!valid) break;
+          if (leaf + 1 < leaves) st[k] = cur;
+        }
+        if (!valid) break;
+        save_end(ends2[en], zh, zb1, zb2);
+        ++depth;
+        bool take = cur.lsw > lsw;
+        if (!take) { Rng ru = rng; ru.slot = base; base += 1; take = ru.u01() < exp(cur.lsw - lsw); }
+        if (take) {
+          double* hv = &hs.mu1;
+#pragma unroll
+          for (int k = 0; k < 6; ++k) hv[k] = cur.qh[k];
+          bs1 = cur.q1; bs2 = cur.q2; lps = cur.lp;
+        }
+        lsw = log_sum_exp2(lsw, cur.lsw);
+#pragma unroll
+        for (int k = 0; k < 6; ++k) rh[k] += cur.rh[k];
+        r1 += cur.r1; r2 += cur.r2;
+        double sp[6], sm6[6];
+#pragma unroll
+        for (int k = 0; k < 6; ++k) { sp[k] = mh[k] * ends2[1].ph[k]; sm6[k] = mh[k] * ends2[0].ph[k]; }
+        const double dp = dot(sp, m1 * ends2[1].p1, m2 * ends2[1].p2, rh, r1, r2);
+        const double dm = dot(sm6, m1 * ends2[0].p1, m2 * ends2[0].p2, rh, r1, r2);
+        if (!(dp > 0.0 && dm > 0.0)) break;
+      }
+      accept_prob = sum_metro / (double)n_leap;
+      h = hs; b1 = bs1; b2 = bs2; lp = lps;
+      ++n_acc;
+      st_depth = depth; st_leaps += n_leap; st_div += divergent ? 1.0 : 0.0; st_acc = accept_prob;
+    }
     if (accept_prob > 1.0) accept_prob = 1.0;
     if (ad[9] == 1.0) {
       adapt_learn_stepsize(ad, cfg, accept_prob);
@@ -392,6 +515,10 @@ extern "C" __global__ void __launch_bounds__(128) birats_hmc_adapt(const __grid_
       for (int j = 0; j < STK_AD_LEN; ++j) AD[j * nc + c.chain] = ad[j];
       ((double*)a.field[F_LP])[c.chain] = lp;
       if (a.accept) a.accept[c.chain] += n_acc;
+      if (NUTS) {
+        double* NS = (double*)a.field[F_NUTS];
+        NS[0 * nc + c.chain] = st_depth; NS[1 * nc + c.chain] += st_leaps; NS[2 * nc + c.chain] += st_div; NS[3 * nc + c.chain] = st_acc;
+      }
     }
     if (c.has_rat) {
       Q[(long long)j1 * nc + c.chain] = b1; Q[(long long)j2 * nc + c.chain] = b2;
@@ -399,6 +526,8 @@ extern "C" __global__ void __launch_bounds__(128) birats_hmc_adapt(const __grid_
     }
   }
 }
+extern "C" __global__ void __launch_bounds__(128) birats_hmc_adapt(const __grid_constant__ StkArgs a) { birats_adaptive<false>(a); }
+extern "C" __global__ void __launch_bounds__(128) birats_nuts(const __grid_constant__ StkArgs a) { birats_adaptive<true>(a); }
 
 template <bool GRAD>
 __device__ __forceinline__ void logp_entry(const StkArgs& a) {
@@ -441,10 +570,13 @@ extern "C" __device__ const char stk_desc[] =
     "field minv state f64 66\n"
     "field wm state f64 66\n"
     "field wm2 state f64 66\n"
+    "field nuts state f64 4\n"
     "param L 10\n"
     STK_ADAPT_PARAMS
+    "param max_depth 10\n"
     "record q\n"
     "kernel hmc birats_hmc 128 4 64 y 8\n"
     "kernel hmc_adapt birats_hmc_adapt 128 4 64 y 8\n"
+    "kernel nuts birats_nuts 128 4 64 y 8\n"
     "entry logp birats_logp 128 4 64 y 8\n"
     "entry logp_grad birats_logp_grad 128 4 64 y 8\n";

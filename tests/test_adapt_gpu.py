@@ -273,3 +273,48 @@ def test_runstan_shaped_entry_point(ctx, tmp_path):
     cols = [ref_names.index(n) for n in names[1:]]
     mu, sd = cons.mean(axis=(0, 2)), cons.std(axis=(0, 2))
     assert np.all(np.abs(ref[:, cols].mean(axis=0) - mu) < 4 * sd / np.sqrt(3) + 1e-9)
+
+
+def test_birats_nuts_trajectory_parity(ctx, orc):
+    """birats under hmcStan's default sampler: warp-per-chain iterative tree vs the recursive restatement"""
+    import os
+    from stochaskell_b200 import Sampler
+    gold = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "birats_stan.npz"))
+    x, y = gold["x"], gold["y"]
+    C, seed = 9, 29
+    cfgd = dict(CFG, stepsize=0.1)
+    s = Sampler("builtin:birats", C, dict(x=x, y=y), seed=seed, ctx=ctx, first_global_chain=50)
+    ch = s.chains
+    set_cfg(ch, cfgd)
+    rng = np.random.default_rng(9)
+    q0 = np.repeat(gold["q"][0].reshape(-1, 1), C, axis=1) * (1 + 0.01 * rng.standard_normal((66, C)))
+    ch.set_state("q", q0)
+    cfg = orc.adapt_cfg(**cfgd)
+    chains = [0, 4, 8]
+    qs = {c: np.ascontiguousarray(q0[:, c]) for c in chains}
+    sts = {c: orc.adapt_state(66) for c in chains}
+    leaps = {c: 0.0 for c in chains}
+    t = 0
+    for cp in list(range(1, 9)) + [60, 61, 62, 99, 100, 101, 102, 149, 150, 151, 199, 200, 201, 202, 203, 204, 220]:
+        span = cp - t
+        ch.step("nuts", span)
+        last = {}
+        for c in chains:
+            for step in range(t, cp):
+                _, o5 = orc.birats_nuts_step(x, y, qs[c], sts[c], cfg, seed, 50 + c, step)
+                leaps[c] += o5[3]; last[c] = o5
+        t = cp
+        q = ch.get_state("q"); ad = ch.get_state("ad"); minv = ch.get_state("minv"); ns = ch.get_state("nuts")
+        wm = ch.get_state("wm"); wm2 = ch.get_state("wm2")
+        for c in chains:
+            ado = sts[c][0]
+            assert np.array_equal(ad[4:10, c], ado[4:10]), (cp, c, ad[:, c], ado)
+            if span == 1:
+                assert ns[0, c] == last[c][2] and ns[1, c] == leaps[c], (cp, c, ns[:, c], last[c], leaps[c])
+                assert np.allclose(ad[0:4, c], ado[0:4], rtol=1e-8, atol=1e-8), (cp, c, ad[:, c], ado)
+                assert np.allclose(minv[:, c], sts[c][1], rtol=1e-8), (cp, c)
+                scale = np.maximum(1.0, np.abs(qs[c]))
+                assert np.all(np.abs(q[:, c] - qs[c]) <= 1e-8 * scale), (cp, c, np.max(np.abs(q[:, c] - qs[c])))
+            qs[c][:] = q[:, c]; ado[:] = ad[:, c]; sts[c][1][:] = minv[:, c]; sts[c][2][:] = wm[:, c]; sts[c][3][:] = wm2[:, c]
+            leaps[c] = ns[1, c]
+    assert np.all(ad[9] == 2.0)

@@ -55,8 +55,10 @@ __device__ __forceinline__ double eval(const Hyper& h, double b1, double b2, con
   const double a = (b1 - h.mu1) * it1, c = (b2 - h.mu2) * it2;
   const double da = (a - z * c) * iD, dc = (c - z * a) * iD;
   const double Q = (a * a - 2.0 * z * a * c + c * c) * iD;
-  g1 = -da * it1 + sr * is2;
-  g2 = -dc * it2 + srx * is2;
+  // lanes without a rat (N < 32) carry a phantom copy of rat 0 with no data: it must stay put, or a long adaptive launch
+  // lets it run away under a metric estimated from its own wanderings until 0 * inf poisons the warp sums
+  g1 = has_rat ? -da * it1 + sr * is2 : 0.0;
+  g2 = has_rat ? -dc * it2 + srx * is2 : 0.0;
   const double w = has_rat ? 1.0 : 0.0;
   double s_mu1 = w * da * it1, s_mu2 = w * dc * it2;
   double s_t1 = w * (-it1 + a * da * it1), s_t2 = w * (-it2 + c * dc * it2);
@@ -271,6 +273,7 @@ __device__ __forceinline__ void birats_adaptive(const StkArgs& a) {
     ph[5] = momentum(c.P - 1, za, zb, za32, zb32) / sqrt(mh[5]);
     p1 = momentum(j1, za, zb, za32, zb32) / sqrt(m1);
     p2 = momentum(j2, za, zb, za32, zb32) / sqrt(m2);
+    if (!c.has_rat) { p1 = 0.0; p2 = 0.0; }
   };
   auto kinetic = [&]() {
     double ke = warp_sum(c.has_rat ? fma(m2 * p2, p2, m1 * p1 * p1) : 0.0);

@@ -318,3 +318,53 @@ def test_birats_nuts_trajectory_parity(ctx, orc):
             qs[c][:] = q[:, c]; ado[:] = ad[:, c]; sts[c][1][:] = minv[:, c]; sts[c][2][:] = wm[:, c]; sts[c][3][:] = wm2[:, c]
             leaps[c] = ns[1, c]
     assert np.all(ad[9] == 2.0)
+
+
+def test_birats_nuts_vs_cmdstan(ctx):
+    """512 device chains against 24 chains of the reference's default sampler on birats (tests/golden/birats_nuts_stan.json)"""
+    from stochaskell_b200 import Sampler
+    from tests.test_adapt_cpu import _close, birats_gold, birats_summaries
+    g, d = birats_gold()
+    c = g["config"]
+    C = 512
+    s = Sampler("builtin:birats", C, dict(x=d["x"], y=d["y"]), seed=37, ctx=ctx)
+    ch = s.chains
+    set_cfg(ch, dict(CFG, stepsize=c["stepsize"], num_warmup=c["num_warmup"]))
+    ch.set_state("q", np.repeat(d["q"][0].reshape(-1, 1), C, axis=1))
+    ch.step("nuts", c["num_warmup"])
+    l0 = ch.get_state("nuts")[1].copy()
+    ch.record(c["num_samples"])
+    ch.step("nuts", c["num_samples"])
+    draws = ch.draws()                                  # [draw][66][chain]
+    ns = ch.get_state("nuts"); eps = ch.get_state("ad")[0]
+    leaps = (ns[1] - l0) / c["num_samples"]
+    assert _close(eps, g["stepsize"]), (eps.mean(), np.mean(g["stepsize"]))
+    assert _close(leaps, g["n_leapfrog_mean"]), (leaps.mean(), np.mean(g["n_leapfrog_mean"]))
+    mine = birats_summaries(draws.transpose(0, 2, 1)).mean(axis=0)      # [chain][6]
+    ref = np.array(g["post_chain_means"])
+    for j in range(6):
+        assert _close(mine[:, j], ref[:, j], 5.0), (g["post_names"][j], mine[:, j].mean(), ref[:, j].mean())
+
+
+@pytest.mark.parametrize("module,kernel", [("birats", "nuts"), ("birats", "hmc_adapt"), ("linreg", "nuts"), ("linreg", "hmc_adapt")])
+def test_adaptive_launch_split_invariance(ctx, module, kernel):
+    """window ends in the middle of a launch: one launch of 260 transitions == 100 + 60 + 100, bit for bit
+    (regression: the idle lanes of a birats warp used to drift in long launches and poison the warp sums)"""
+    import os
+    from stochaskell_b200 import Sampler
+    if module == "birats":
+        gold = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "birats_stan.npz"))
+        data = dict(x=gold["x"], y=gold["y"]); q0 = np.repeat(gold["q"][0].reshape(-1, 1), 6, axis=1); C = 6
+    else:
+        X, y = make_data(200, 10); data = dict(X=X, y=y); C = 37; q0 = np.zeros((12, C))
+    out = []
+    for spans in ([260], [100, 60, 100]):
+        s = Sampler(f"builtin:{module}", C, data, seed=41, ctx=ctx)
+        set_cfg(s.chains, dict(CFG, stepsize=0.5, int_time=0.2, num_warmup=250))
+        s.chains.set_state("q", q0)
+        for sp in spans:
+            s.chains.step(kernel, sp)
+        out.append([s.chains.get_state(f) for f in ("q", "ad", "minv", "wm", "wm2")])
+    for a, b in zip(*out):
+        assert np.array_equal(a, b)
+    assert np.all(out[0][1][9] == 2.0) and np.all(out[0][1][0] > 1e-4)

@@ -258,6 +258,58 @@ class BiratsHMC:
         return orc.birats_hmc_run(self.x, self.y, state["q"], T, self.eps, self.L, seed, chain0, step0, nthreads)
 
 
+class BiratsNUTS(BiratsHMC):
+    """C4 under hmcStan's DEFAULT sampler (birats.ipynb cell 8): NUTS, diag_e, max_depth 10, after warm-up.  Chains start from an
+    adapted state: step size = the mean over 24 chains of the vendored CmdStan's adaptation (tests/golden/birats_nuts_stan.json),
+    metric = the one a 300-transition warm-up of the CPU restatement reaches (computed once at start-up, untimed)."""
+    name = "birats_nuts"
+    kernel = "nuts"
+    symbol = "birats_nuts"
+    state_fields = ("q", "ad", "minv", "wm", "wm2")
+    e2e_fields = ("q",)
+    transitions_per_step = 20
+    diag_thin = 2
+    diag_warmup = 40
+
+    def __init__(self):
+        super().__init__()
+        g = json.load(open(os.path.join(ROOT, "tests", "golden", "birats_nuts_stan.json")))
+        self.eps0 = float(np.mean(g["stepsize"]))
+        self.evals = float(np.mean(g["n_leapfrog_mean"])) + 1.0
+        self.bytes_per_transition = self.evals * self.bytes_per_eval
+        self.cfg = np.array([1.0, 1.0, 0.0, 0.8, 0.05, 0.75, 10.0, 75, 50, 25], dtype=np.float64)
+        self.describe = (f"C4 birats 30 rats x 5 points, P=66, NUTS diag_e max_depth 10 after warm-up (hmcStan default; adapted "
+                         f"eps={self.eps0:.3f}, {self.evals - 1:.1f} leapfrogs/transition in the reference's own runs; 1024 chains per GPU)")
+        self.roofline_note = ("algorithmic bytes = (mean leapfrogs per transition of the reference's sampler + 1) x 2,296 B; data in "
+                              "shared memory / registers, physical DRAM traffic ~0; bound: latency of one warp per chain")
+        self._adapted = None
+
+    def _warm(self):
+        if self._adapted is None:
+            from tests.oracle_binding import oracle
+            orc = oracle()
+            cfg = orc.adapt_cfg(stepsize=1.0, num_warmup=300)
+            q = np.ascontiguousarray(self.q0.copy()); st = orc.adapt_state(66)
+            for step in range(301):
+                orc.birats_nuts_step(self.x, self.y, q, st, cfg, 12345, 0, step)
+            self._adapted = (q, st[1].copy())
+        return self._adapted
+
+    def params(self):
+        return dict(stepsize=1.0, num_warmup=0.0, max_depth=10.0)
+
+    def init_state(self, C, chain0):
+        qa, minv = self._warm()
+        rng = np.random.default_rng(77 + chain0)
+        ad = np.zeros((10, C)); ad[0] = self.eps0; ad[9] = 2.0
+        return dict(q=np.ascontiguousarray(qa[:, None] + 0.1 * np.sqrt(minv)[:, None] * rng.standard_normal((66, C))),
+                    ad=ad, minv=np.ascontiguousarray(np.repeat(minv[:, None], C, axis=1)), wm=np.zeros((66, C)), wm2=np.zeros((66, C)))
+
+    def cpu_run(self, orc, state, T, seed, chain0, step0, nthreads):
+        return orc.birats_nuts_run(self.x, self.y, state["q"], state["ad"], state["minv"], state["wm"], state["wm2"], T,
+                                   self.cfg, seed, chain0, step0, nthreads)
+
+
 class DPGibbs:
     """C5: Dirichlet-process mixture (dp.ipynb), N = 100,000 observations of a planted 5-component mixture, truncated
     stick-breaking K = 32, alpha = 5, 1024 chains; one transition = one blocked Gibbs sweep (assignments, sticks, atoms)."""
@@ -379,7 +431,7 @@ class GPHMCTC(GPHMC):
         return r
 
 
-WORKLOADS = {"gp_hmc_tc": GPHMCTC, "linreg_hmc": LinregHMC, "linreg_nuts": LinregNUTS, "coal_rj": CoalRJ, "birats_hmc": BiratsHMC, "dp_gibbs": DPGibbs, "gp_hmc": GPHMC}
+WORKLOADS = {"gp_hmc_tc": GPHMCTC, "linreg_hmc": LinregHMC, "linreg_nuts": LinregNUTS, "coal_rj": CoalRJ, "birats_hmc": BiratsHMC, "birats_nuts": BiratsNUTS, "dp_gibbs": DPGibbs, "gp_hmc": GPHMC}
 DEFAULT_WORKLOAD = "coal_rj"
 
 

@@ -133,6 +133,9 @@ void orc_birats_nuts_step(const double* x, const double* y, int N, int Tn, doubl
 long long orc_linreg_nuts_run(const double* X, const double* y, int n, int d, double* q, double* ad, double* minv, double* wm,
                               double* wm2, long long C, long long T, const double* cfg, int max_depth, uint64_t seed,
                               uint64_t chain0, uint64_t step0, int nthreads);
+long long orc_birats_nuts_run(const double* x, const double* y, int N, int Tn, double* q, double* ad, double* minv, double* wm,
+                              double* wm2, long long C, long long T, const double* cfg, int max_depth, uint64_t seed,
+                              uint64_t chain0, uint64_t step0, int nthreads);
 
 #ifdef __cplusplus
 }

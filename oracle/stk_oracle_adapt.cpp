@@ -346,10 +346,9 @@ extern "C" void orc_birats_nuts_step(const double* x, const double* y, int N, in
 // a time per host thread.  q, minv, wm, wm2 are [P][C], ad is [ORC_AD_LEN][C]; returns the total number of leapfrogs.
 #include <atomic>
 #include <thread>
-extern "C" long long orc_linreg_nuts_run(const double* X, const double* y, int n, int d, double* q, double* ad, double* minv,
-                                         double* wm, double* wm2, long long C, long long T, const double* cfg,
-                                         int max_depth, uint64_t seed, uint64_t chain0, uint64_t step0, int nthreads) {
-  const int P = d + 2;
+template <class StepFn>
+static long long nuts_run(int P, StepFn step_fn, double* q, double* ad, double* minv, double* wm, double* wm2, long long C,
+                          long long T, uint64_t chain0, uint64_t step0, int nthreads) {
   std::atomic<long long> next{0}, leaps{0};
   auto work = [&]() {
     std::vector<double> qc(P), mc(P), w1(P), w2(P), ac(ORC_AD_LEN);
@@ -361,8 +360,7 @@ extern "C" long long orc_linreg_nuts_run(const double* X, const double* y, int n
       for (int j = 0; j < ORC_AD_LEN; ++j) ac[j] = ad[(size_t)j * C + c];
       long long nl = 0;
       for (long long t = 0; t < T; ++t) {
-        orc_linreg_nuts_step(X, y, n, d, qc.data(), ac.data(), mc.data(), w1.data(), w2.data(), cfg, max_depth, seed,
-                             chain0 + c, step0 + t, nullptr, o5);
+        step_fn(qc.data(), ac.data(), mc.data(), w1.data(), w2.data(), chain0 + c, step0 + t, o5);
         nl += (long long)o5[3];
       }
       for (int j = 0; j < P; ++j) { q[(size_t)j * C + c] = qc[j]; minv[(size_t)j * C + c] = mc[j]; wm[(size_t)j * C + c] = w1[j]; wm2[(size_t)j * C + c] = w2[j]; }
@@ -375,4 +373,22 @@ extern "C" long long orc_linreg_nuts_run(const double* X, const double* y, int n
   for (int i = 0; i < nthreads; ++i) th.emplace_back(work);
   for (auto& t : th) t.join();
   return leaps.load();
+}
+
+extern "C" long long orc_linreg_nuts_run(const double* X, const double* y, int n, int d, double* q, double* ad, double* minv,
+                                         double* wm, double* wm2, long long C, long long T, const double* cfg,
+                                         int max_depth, uint64_t seed, uint64_t chain0, uint64_t step0, int nthreads) {
+  auto f = [&](double* qc, double* ac, double* mc, double* w1, double* w2, uint64_t chain, uint64_t step, double* o5) {
+    orc_linreg_nuts_step(X, y, n, d, qc, ac, mc, w1, w2, cfg, max_depth, seed, chain, step, nullptr, o5);
+  };
+  return nuts_run(d + 2, f, q, ad, minv, wm, wm2, C, T, chain0, step0, nthreads);
+}
+
+extern "C" long long orc_birats_nuts_run(const double* x, const double* y, int N, int Tn, double* q, double* ad, double* minv,
+                                         double* wm, double* wm2, long long C, long long T, const double* cfg,
+                                         int max_depth, uint64_t seed, uint64_t chain0, uint64_t step0, int nthreads) {
+  auto f = [&](double* qc, double* ac, double* mc, double* w1, double* w2, uint64_t chain, uint64_t step, double* o5) {
+    orc_birats_nuts_step(x, y, N, Tn, qc, ac, mc, w1, w2, cfg, max_depth, seed, chain, step, nullptr, o5);
+  };
+  return nuts_run(2 * N + 6, f, q, ad, minv, wm, wm2, C, T, chain0, step0, nthreads);
 }

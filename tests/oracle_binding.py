@@ -323,6 +323,16 @@ class Oracle:
         return fn(_p(X), _p(y), n, d, _p(q), _p(ad), _p(minv), _p(wm), _p(wm2), q.shape[1], T, _p(cfg), max_depth, seed,
                   chain0, step0, nthreads)
 
+    def birats_nuts_run(self, x, y, q, ad, minv, wm, wm2, T, cfg, seed, chain0=0, step0=0, nthreads=1, max_depth=10):
+        x = np.ascontiguousarray(x, dtype=np.float64); y = np.ascontiguousarray(y, dtype=np.float64)
+        N, Tn = y.shape
+        fn = self.l.orc_birats_nuts_run
+        fn.restype = C.c_longlong
+        fn.argtypes = [P, P, C.c_int, C.c_int, P, P, P, P, P, C.c_longlong, C.c_longlong, P, C.c_int, C.c_uint64,
+                       C.c_uint64, C.c_uint64, C.c_int]
+        return fn(_p(x), _p(y), N, Tn, _p(q), _p(ad), _p(minv), _p(wm), _p(wm2), q.shape[1], T, _p(cfg), max_depth, seed,
+                  chain0, step0, nthreads)
+
     def u01x2(self, seed, chain, step, slot):
         a = D(); b = D()
         self.l.orc_u01x2(seed, chain, step, slot, C.byref(a), C.byref(b))

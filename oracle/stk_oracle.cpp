@@ -104,6 +104,21 @@ extern "C" double orc_draw_cauchy(orc_rng* g, double m, double s) {
   double x, y; rng_normal2(g, &x, &y); return m + s * (x / y);
 }
 
+extern "C" double orc_draw_inv_gamma(orc_rng* g, double a, double b) { return 1.0 / orc_draw_gamma(g, a, b); }  // Abstract.hs:72-75
+extern "C" int orc_draw_geometric(orc_rng* g, double p) {  // Abstract.hs:80-85 (the law; one uniform by inversion)
+  const double u = orc_u01(g);
+  if (p >= 1.0) return 0;
+  const double k = std::floor(std::log(u) / std::log1p(-p));
+  return k < 2147483647.0 ? (int)k : 2147483647;
+}
+extern "C" double orc_draw_logistic(orc_rng* g, double m, double s) { const double u = orc_u01(g); return m + s * std::log(u / (1.0 - u)); }
+extern "C" int orc_draw_neg_binomial(orc_rng* g, double a, double b) { const double l = orc_draw_gamma(g, a, b); return orc_draw_poisson(g, l); }
+extern "C" double orc_draw_beta(orc_rng* g, double a, double b) {
+  const double X = orc_draw_gamma(g, a, 1.0), Y = orc_draw_gamma(g, b, 1.0);
+  return X / (X + Y);
+}
+extern "C" double orc_draw_lkj_corr2(orc_rng* g, double v) { return 2.0 * orc_draw_beta(g, v, v) - 1.0; }
+
 // ---------------------------------------------------------------------------
 // log densities
 // ---------------------------------------------------------------------------

@@ -41,6 +41,12 @@ int orc_draw_pmf(orc_rng* g, const double* ps, int n);
 int orc_draw_poisson(orc_rng* g, double l);
 double orc_draw_gamma(orc_rng* g, double a, double b);
 double orc_draw_cauchy(orc_rng* g, double m, double s);
+double orc_draw_inv_gamma(orc_rng* g, double a, double b);
+int orc_draw_geometric(orc_rng* g, double p);
+double orc_draw_logistic(orc_rng* g, double m, double s);
+int orc_draw_neg_binomial(orc_rng* g, double a, double b);
+double orc_draw_beta(orc_rng* g, double a, double b);
+double orc_draw_lkj_corr2(orc_rng* g, double v);
 
 // ---- log densities (Abstract.hs:68-167, Const.hs:90-106) ---------------------
 double orc_normal_lpdf(double x, double m, double s);

@@ -162,6 +162,28 @@ STK_DEV double draw_cauchy(Rng& g, double m, double s) {
   double x, y; g.normal2(x, y); return m + s * (x / y);
 }
 
+// inv_gamma(a, b) = 1 / gamma(a, b).  Abstract.hs:72-75
+STK_DEV double draw_inv_gamma(Rng& g, double a, double b) { return 1.0 / draw_gamma(g, a, b); }
+// geometric(p): failures before the first success.  The reference flips bernoulli(p) coins one by one
+// (Abstract.hs:80-85); the same law by inversion of one uniform, k = floor(log u / log(1 - p)): 1 block.
+STK_DEV int draw_geometric(Rng& g, double p) {
+  const double u = g.u01();
+  if (p >= 1.0) return 0;
+  const double k = floor(log(u) / log1p(-p));
+  return k < 2147483647.0 ? (int)k : 2147483647;
+}
+// logistic(m, s) = m + s log(u / (1 - u)).  Abstract.hs:101-104.  1 block.
+STK_DEV double draw_logistic(Rng& g, double m, double s) { const double u = g.u01(); return m + s * log(u / (1.0 - u)); }
+// neg_binomial(a, b): l ~ gamma(a, b), then poisson(l).  Abstract.hs:108-111
+STK_DEV int draw_neg_binomial(Rng& g, double a, double b) { const double l = draw_gamma(g, a, b); return draw_poisson(g, l); }
+// beta(a, b) = X / (X + Y), X ~ gamma(a, 1), Y ~ gamma(b, 1) (the construction random-fu's Beta uses, Abstract.hs:40-41)
+STK_DEV double draw_beta(Rng& g, double a, double b) {
+  const double X = draw_gamma(g, a, 1.0), Y = draw_gamma(g, b, 1.0);
+  return X / (X + Y);
+}
+// lkj_corr(v) for a 2 x 2 correlation matrix: the off-diagonal r = 2 beta(v, v) - 1.  Abstract.hs:93-97
+STK_DEV double draw_lkj_corr2(Rng& g, double v) { return 2.0 * draw_beta(g, v, v) - 1.0; }
+
 // ---- log densities ---------------------------------------------------------
 STK_DEV double log_factorial(int k) { return lgamma(1.0 + (double)k); }  // CC.hs:167-168
 

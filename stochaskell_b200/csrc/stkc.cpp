@@ -807,6 +807,12 @@ struct Gen {
     else if (f == "poisson") e = "stk::draw_poisson(" + g + ", " + arg(0) + ")";                          // :279
     else if (f == "discreteUniform") e = "stk::draw_discrete_uniform(" + g + ", " + arg(0, false) + ", " + arg(1, false) + ")";   // :277
     else if (f == "cauchy") e = "stk::draw_cauchy(" + g + ", " + arg(0) + ", " + arg(1) + ")";
+    // distributions only the interpreter samples in the reference (samplePNode, Program.hs:1093-1170)
+    else if (f == "inv_gamma") e = "stk::draw_inv_gamma(" + g + ", " + arg(0) + ", " + arg(1) + ")";
+    else if (f == "geometric") e = "stk::draw_geometric(" + g + ", " + arg(0) + ")";
+    else if (f == "logistic") e = "stk::draw_logistic(" + g + ", " + arg(0) + ", " + arg(1) + ")";
+    else if (f == "neg_binomial") e = "stk::draw_neg_binomial(" + g + ", " + arg(0) + ", " + arg(1) + ")";
+    else if (f == "beta") e = "stk::draw_beta(" + g + ", " + arg(0) + ", " + arg(1) + ")";
     else if (f == "pmf" || f == "categorical") {                                                          // :292-293
       const RefP& ps = q.args.at(0);
       if (ps->k != Ref::List) die("pmf needs a literal probability list");

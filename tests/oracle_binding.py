@@ -333,6 +333,25 @@ class Oracle:
         return fn(_p(x), _p(y), N, Tn, _p(q), _p(ad), _p(minv), _p(wm), _p(wm2), q.shape[1], T, _p(cfg), max_depth, seed,
                   chain0, step0, nthreads)
 
+    class _Rng(C.Structure):
+        _fields_ = [(n, C.c_uint32) for n in ("k0", "k1", "c0", "c1", "c2", "slot")]
+
+    _DRAWS = dict(inv_gamma=(D, 2), geometric=(C.c_int, 1), logistic=(D, 2), neg_binomial=(C.c_int, 2), beta=(D, 2),
+                  lkj_corr2=(D, 1), gamma=(D, 2), cauchy=(D, 2), poisson=(C.c_int, 1), bernoulli=(C.c_int, 1))
+
+    def draw(self, name, seed, chain, step, slot, *args):
+        """one draw of `name` from the Philox stream (seed, chain, step) starting at block `slot` (orc_draw_<name>)"""
+        res, n = self._DRAWS[name]
+        assert len(args) == n
+        g = self._Rng()
+        self.l.orc_rng_init.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64]
+        self.l.orc_rng_init(C.byref(g), seed, chain, step)
+        g.slot = slot
+        fn = getattr(self.l, "orc_draw_" + name)
+        fn.restype = res
+        fn.argtypes = [C.c_void_p] + [D] * n
+        return fn(C.byref(g), *[float(a) for a in args])
+
     def u01x2(self, seed, chain, step, slot):
         a = D(); b = D()
         self.l.orc_u01x2(seed, chain, step, slot, C.byref(a), C.byref(b))

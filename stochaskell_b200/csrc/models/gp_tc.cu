@@ -23,6 +23,9 @@
 #define TC_STAGE_BYTES 32768          // 2 x (32 k x 128 m) fp16 A + 2 x (32 k x 128 chains) fp16 B
 #define TC_SPLIT_BYTES 8192
 #define TC_TMEM_COLS 256              // two 128 x 128 fp32 accumulators
+#define TC_EPI_WARPS 8                // epilogue warps (4 or 8); + 1 MMA warp + 1 producer warp
+#define TC_EPI_ROWS (128 / TC_EPI_WARPS)
+#define TC_THREADS (32 * (TC_EPI_WARPS + 2))
 
 // ---- PTX wrappers -----------------------------------------------------------------------------------------------
 __device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
@@ -104,7 +107,11 @@ __device__ __forceinline__ void gp_tc_gemm(const StkArgs& a) {
   const tc_t* Aop = (const tc_t*)a.field[MODE == 1 ? F_LTA : F_LA];
   const tc_t* Bop = (const tc_t*)a.field[MODE == 1 ? F_WB : F_RB];
   const long long kbeg = MODE == 1 ? 0 : m0, kend = MODE == 1 ? m0 + 128 : ld;
+#ifdef TC_DIAG_K1         /* diagnostic build: one k step per tile = the fixed cost of a tile (set-up + epilogue) */
+  const int ktiles = 1;
+#else
   const int ktiles = (int)((kend - kbeg) / TC_BK);
+#endif
   const long long ncbA = ld >> 7, ncbB = (C + 127) >> 7;
   int* info = (int*)a.field[F_INFO];
   const unsigned full0 = smem_u32(bars), empty0 = smem_u32(bars + TC_STAGES), accum = smem_u32(bars + 2 * TC_STAGES);
@@ -114,7 +121,7 @@ __device__ __forceinline__ void gp_tc_gemm(const StkArgs& a) {
     mbar_init(accum, 1);
     asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
   }
-  if (warp == 4) {
+  if (warp == TC_EPI_WARPS) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(smem_u32(tmem_slot)), "n"(TC_TMEM_COLS));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::);
   }
@@ -123,7 +130,7 @@ __device__ __forceinline__ void gp_tc_gemm(const StkArgs& a) {
   tc_fence_after();
   const unsigned tmem = *tmem_slot;
 
-  if (tid == 160) {
+  if (tid == 32 * (TC_EPI_WARPS + 1)) {
     // ===== producer (one thread): two 16 KB bulk copies per stage =====
     const tc_t* ga = Aop + ((kbeg >> 5) * ncbA + I) * (TC_NS * 4096);
     const tc_t* gb = Bop + ((kbeg >> 5) * ncbB + blockIdx.x) * (TC_NS * 4096);
@@ -136,7 +143,7 @@ __device__ __forceinline__ void gp_tc_gemm(const StkArgs& a) {
       bulk_g2s(dst + TC_NS * TC_SPLIT_BYTES, gb, TC_NS * TC_SPLIT_BYTES, bar);
       ga += ncbA * (TC_NS * 4096); gb += ncbB * (TC_NS * 4096);
     }
-  } else if (tid == 128) {
+  } else if (tid == 32 * TC_EPI_WARPS) {
     // ===== MMA issuer (one thread) =====
     for (int t = 0; t < ktiles; ++t) {
       const int st = t % TC_STAGES;
@@ -150,25 +157,30 @@ __device__ __forceinline__ void gp_tc_gemm(const StkArgs& a) {
         const unsigned long long adv = (unsigned long long)(k2 * 128);
         const unsigned acc = (t | k2) != 0;
         tc_mma(tmem, a_hi + adv, b_hi + adv, TC_IDESC, acc);              // accumulator 0: hi * hi
+#ifndef TC_DIAG_ONE_MMA   /* diagnostic build: only the hi * hi term (is the main loop bound by operand delivery or by MMA issue?) */
         tc_mma(tmem + 128, a_hi + adv, b_lo + adv, TC_IDESC, acc);        // accumulator 1: hi * lo + lo * hi
         tc_mma(tmem + 128, a_lo + adv, b_hi + adv, TC_IDESC, 1u);
+#endif
       }
       tc_commit(empty0 + 8 * st);
     }
     tc_commit(accum);
   }
 
-  // ===== epilogue (warps 0-3) =====
+  // ===== epilogue (warps 0 .. TC_EPI_WARPS-1; the tile epilogue is a latency-bound instruction stream: measured with a one-k-step
+  // build, 4 warps spent 49-58 us of a 91 us launch here, so it runs on 8 warps of 16 rows) =====
   // phase A: thread = accumulator row (TMEM lane): tcgen05.ld -> shared tile T[128][132] (the operand stages are free);
   // phase B: warp = 32 rows, lane = 4 consecutive chains: every global access of a warp is one contiguous run
-  if (warp < 4) {
+  if (warp < TC_EPI_WARPS) {
     if (!mbar_wait(accum, 0)) info[1] = 3;
     tc_fence_after();
     float* T = (float*)smem;
-    double* sc = (double*)(smem + 69632);         // [2][4][128] column sums of the four warps
+    double* sc = (double*)(smem + 69632);         // [2][TC_EPI_WARPS][128] column sums of the epilogue warps
     {
-      const unsigned trow = tmem + ((unsigned)(warp * 32) << 16);
-      for (int j = 0; j < 4; ++j) {
+      // a warp reaches the TMEM lanes 32 (warp % 4) ..: warps w and w + 4 share a lane quarter and split its columns
+      const unsigned trow = tmem + ((unsigned)((warp & 3) * 32) << 16);
+      const int trw = (warp & 3) * 32 + (tid & 31);              // accumulator row of this thread
+      for (int j = (warp >> 2) * (16 / TC_EPI_WARPS); j < ((warp >> 2) + 1) * (16 / TC_EPI_WARPS); ++j) {
         float v[32], x[32];
         tc_ld32(trow + 32 * j, v);
         tc_ld32(trow + 128 + 32 * j, x);
@@ -176,11 +188,11 @@ __device__ __forceinline__ void gp_tc_gemm(const StkArgs& a) {
         for (int i = 0; i < 32; ++i) v[i] = fmaf(x[i], (float)(1.0 / TC_LO_SCALE), v[i]);
 #pragma unroll
         for (int q = 0; q < 8; ++q)
-          *reinterpret_cast<float4*>(T + tid * 132 + 32 * j + 4 * q) = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+          *reinterpret_cast<float4*>(T + trw * 132 + 32 * j + 4 * q) = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
       }
     }
     tc_fence_before();
-    asm volatile("bar.sync 1, 128;\n" ::: "memory");
+    asm volatile("bar.sync 1, %0;\n" ::"n"(32 * TC_EPI_WARPS) : "memory");
     const int lane = tid & 31;
     const long long cc = c0 + 4 * lane;
     const bool last = a.iter == a.n_iter - 1;
@@ -189,19 +201,20 @@ __device__ __forceinline__ void gp_tc_gemm(const StkArgs& a) {
     const double eps = a.par[P_EPS];
     double* red = (double*)a.field[F_RED];
     double cs0[4] = {0.0, 0.0, 0.0, 0.0}, cs1[4] = {0.0, 0.0, 0.0, 0.0};
-    const long long mw = m0 + warp * 32;                         // first row of this warp
-    const int nrows = n - mw >= 32 ? 32 : (n > mw ? (int)(n - mw) : 0);
+    const long long mw = m0 + warp * TC_EPI_ROWS;                // first row of this warp
+    const int nrows = n - mw >= TC_EPI_ROWS ? TC_EPI_ROWS : (n > mw ? (int)(n - mw) : 0);
     const int zlane = (MODE == 1 && lane < nrows) ? ((const int*)a.field[F_Z])[mw + lane] : 0;
     double* Wm = (double*)a.field[F_W];
     double* Pm = (double*)a.field[F_P];
     double* GR = (double*)a.field[F_GR];
     tc_t* OB = (tc_t*)a.field[MODE == 1 ? F_RB : F_WB];       // split operand this epilogue produces
     const bool wr_gr = MODE == 2 || (MODE == 3 && last), wr_w = MODE == 3 && !last;
-    for (int rb = 0; rb < nrows; rb += 4) {                      // 4 rows per batch: all global loads first
-      double wv[4][4], pv[4][4];
+    constexpr int RBATCH = MODE == 3 ? 2 : 4;                    // the leapfrog epilogue holds w and p rows in registers: 102 per thread
+    for (int rb = 0; rb < nrows; rb += RBATCH) {                 // RBATCH rows per batch: all global loads first
+      double wv[RBATCH][4], pv[RBATCH][4];
       if (MODE != 1) {
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
+        for (int u = 0; u < RBATCH; ++u) {
           const long long o = (mw + rb + u) * C + cc;
           if (rb + u < nrows) {
             if (full4) {
@@ -218,11 +231,11 @@ __device__ __forceinline__ void gp_tc_gemm(const StkArgs& a) {
         }
       }
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < RBATCH; ++u) {
         const int zi = __shfl_sync(0xffffffffu, zlane, (rb + u) & 31);
         if (rb + u >= nrows) continue;
         const long long m = mw + rb + u;
-        const float4 g4 = *reinterpret_cast<const float4*>(T + (warp * 32 + rb + u) * 132 + 4 * lane);
+        const float4 g4 = *reinterpret_cast<const float4*>(T + (warp * TC_EPI_ROWS + rb + u) * 132 + 4 * lane);
         const float g[4] = {g4.x, g4.y, g4.z, g4.w};
         const long long o = m * C + cc;
         __align__(8) tc_t h[4], lo[4];
@@ -230,7 +243,7 @@ __device__ __forceinline__ void gp_tc_gemm(const StkArgs& a) {
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
           if (MODE == 1) {
-            split2((double)((float)zi - sigmoidf_(g[e])), h[e], lo[e]);
+            split2f((float)zi - sigmoidf_(g[e]), h[e], lo[e]);
             if (sums && cc + e < C) cs0[e] += (double)(zi ? -log1p_expf_(-g[e]) : -log1p_expf_(g[e]));
           } else {
             d[e] = (double)g[e] - wv[u][e];
@@ -267,23 +280,24 @@ __device__ __forceinline__ void gp_tc_gemm(const StkArgs& a) {
     }
     if (sums) {   // column sums: rows in order inside a warp, then the four warps in order
 #pragma unroll
-      for (int e = 0; e < 4; ++e) { sc[warp * 128 + 4 * lane + e] = cs0[e]; sc[512 + warp * 128 + 4 * lane + e] = cs1[e]; }
-      asm volatile("bar.sync 1, 128;\n" ::: "memory");
-      if (c0 + tid < C) {
-        const double t0 = ((sc[tid] + sc[128 + tid]) + sc[256 + tid]) + sc[384 + tid];
-        const double t1 = ((sc[512 + tid] + sc[640 + tid]) + sc[768 + tid]) + sc[896 + tid];
+      for (int e = 0; e < 4; ++e) { sc[warp * 128 + 4 * lane + e] = cs0[e]; sc[TC_EPI_WARPS * 128 + warp * 128 + 4 * lane + e] = cs1[e]; }
+      asm volatile("bar.sync 1, %0;\n" ::"n"(32 * TC_EPI_WARPS) : "memory");
+      if (tid < 128 && c0 + tid < C) {
+        double t0 = 0.0, t1 = 0.0;
+#pragma unroll
+        for (int w8 = 0; w8 < TC_EPI_WARPS; ++w8) { t0 += sc[w8 * 128 + tid]; t1 += sc[TC_EPI_WARPS * 128 + w8 * 128 + tid]; }
         if (MODE == 1) red[((long long)RED_LIK * RED_TILES + I) * C + c0 + tid] = t0;
         else { red[((long long)RED_KE * RED_TILES + I) * C + c0 + tid] = t0; red[((long long)RED_WW * RED_TILES + I) * C + c0 + tid] = t1; }
       }
     }
   }
   __syncthreads();
-  if (warp == 4) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tmem), "n"(TC_TMEM_COLS));
+  if (warp == TC_EPI_WARPS) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tmem), "n"(TC_TMEM_COLS));
 }
 
-extern "C" __global__ void __launch_bounds__(192, 2) gp_tc_gemm1(const __grid_constant__ StkArgs a) { gp_tc_gemm<1>(a); }
-extern "C" __global__ void __launch_bounds__(192, 2) gp_tc_gemm2_grad(const __grid_constant__ StkArgs a) { gp_tc_gemm<2>(a); }
-extern "C" __global__ void __launch_bounds__(192, 2) gp_tc_gemm2_leap(const __grid_constant__ StkArgs a) { gp_tc_gemm<3>(a); }
+extern "C" __global__ void __launch_bounds__(TC_THREADS, 2) gp_tc_gemm1(const __grid_constant__ StkArgs a) { gp_tc_gemm<1>(a); }
+extern "C" __global__ void __launch_bounds__(TC_THREADS, 2) gp_tc_gemm2_grad(const __grid_constant__ StkArgs a) { gp_tc_gemm<2>(a); }
+extern "C" __global__ void __launch_bounds__(TC_THREADS, 2) gp_tc_gemm2_leap(const __grid_constant__ StkArgs a) { gp_tc_gemm<3>(a); }
 
 // ---- split stages -------------------------------------------------------------------------------------------------
 // once per data set, both A operands as tile images of [k][m] matrices:

@@ -83,6 +83,47 @@ class ClockSampler(threading.Thread):
 # ---------------------------------------------------------------------------
 # workloads (BASELINE.json configs; synthetic inputs of SURVEY 8d)
 # ---------------------------------------------------------------------------
+def _rdump(path, **kv):
+    """R dump in stanDump's shape (Stan.hs:346-363) for the reference sampler's data / init files"""
+    with open(path, "w") as f:
+        for k, v in kv.items():
+            a = np.asarray(v)
+            fmt = (lambda x: repr(int(x))) if a.dtype.kind in "iu" else (lambda x: repr(float(x)))
+            if a.ndim == 0:
+                f.write(f"{k} <- {fmt(a)}\n")
+            elif a.ndim == 1:
+                f.write(f"{k} <- c({', '.join(fmt(x) for x in a)})\n")
+            else:
+                f.write(f"{k} <- structure(c({', '.join(fmt(x) for x in a.flatten(order='F'))}), .Dim = c({', '.join(str(d) for d in a.shape)}))\n")
+
+
+def stan_reference_run(exe, data, init, args, n_samples, nthreads, workdir):
+    """The reference's own HMC backend (vendored CmdStan, oracle/_ref/stan_*), one chain per host core (SURVEY 8d ii):
+    nthreads processes side by side; every process reports its own sampling time in the CSV footer.  Returns
+    (transitions/s summed over the processes, mean leapfrogs per transition or None)."""
+    import re
+    procs = []
+    for c in range(nthreads):
+        out = os.path.join(workdir, f"ref_{c}.csv")
+        procs.append((out, subprocess.Popen([exe, "method=sample", f"num_samples={n_samples}"] + args +
+                                            ["data", f"file={data}", f"init={init}", "random", "seed=20261104", f"id={c + 1}",
+                                             "output", f"file={out}", "refresh=1000000"],
+                                            stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)))
+    rate, leaps = 0.0, []
+    for out, pr in procs:
+        pr.wait()
+        txt = open(out).read()
+        m = re.search(r"([0-9.eE+-]+) seconds \(Sampling\)", txt)
+        t = max(float(m.group(1)), 1e-6)
+        rate += n_samples / t
+        rows = [l for l in txt.splitlines() if l and not l.startswith("#")]
+        hdr = rows[0].split(",")
+        if "n_leapfrog__" in hdr and len(rows) > 1:
+            j = hdr.index("n_leapfrog__")
+            leaps.append(np.mean([float(r.split(",")[j]) for r in rows[1:]]))
+    return rate, (float(np.mean(leaps)) if leaps else None)
+
+
 class LinregHMC:
     """C1: Bayesian linear regression n=1000, d=10, static HMC eps=0.01 L=10 (benchStanHMC shape)."""
     name = "linreg_hmc"
@@ -116,6 +157,19 @@ class LinregHMC:
 
     def cpu_run(self, orc, state, T, seed, chain0, step0, nthreads):
         return orc.linreg_hmc_run(self.X, self.y, state["q"], T, self.eps, self.L, seed, chain0, step0, nthreads)
+
+    stan_exe = os.path.join(ROOT, "oracle", "_ref", "stan_linreg")
+
+    def stan_files(self, workdir):
+        data = os.path.join(workdir, "linreg.data.R"); init = os.path.join(workdir, "linreg.init.R")
+        _rdump(data, n=self.n, d=self.d, x_stan_0_0=self.X, x_stan_0_4=self.y)
+        _rdump(init, x_stan_0_1=0.5, x_stan_0_2=np.linalg.lstsq(self.X, self.y - 0.5, rcond=None)[0], x_stan_0_3=1.0)
+        return data, init
+
+    def stan_args(self):
+        """benchStanHMC (app/benchmark/Main.hs:250-258): static engine, unit metric, no adaptation"""
+        return (["num_warmup=0", "adapt", "engaged=0", "algorithm=hmc", "engine=static", f"int_time={self.eps * self.L}",
+                 "metric=unit_e", f"stepsize={self.eps}"], 2000)
 
 
 class LinregNUTS(LinregHMC):
@@ -159,6 +213,10 @@ class LinregNUTS(LinregHMC):
         return dict(q=np.ascontiguousarray(self.post[:, None] + np.sqrt(self.minv0)[:, None] * rng.standard_normal((P, C))),
                     ad=ad, minv=np.ascontiguousarray(np.repeat(self.minv0[:, None], C, axis=1)),
                     wm=np.zeros((P, C)), wm2=np.zeros((P, C)))
+
+    def stan_args(self):
+        """hmcStan's defaults (Stan.hs:428-440): NUTS, diag_e, adaptation; only the sampling phase is timed"""
+        return (["num_warmup=300"], 3000)
 
     def cpu_run(self, orc, state, T, seed, chain0, step0, nthreads):
         return orc.linreg_nuts_run(self.X, self.y, state["q"], state["ad"], state["minv"], state["wm"], state["wm2"], T,
@@ -257,6 +315,21 @@ class BiratsHMC:
     def cpu_run(self, orc, state, T, seed, chain0, step0, nthreads):
         return orc.birats_hmc_run(self.x, self.y, state["q"], T, self.eps, self.L, seed, chain0, step0, nthreads)
 
+    stan_exe = os.path.join(ROOT, "oracle", "_ref", "stan_birats")
+
+    def stan_files(self, workdir):
+        data = os.path.join(workdir, "birats.data.R"); init = os.path.join(workdir, "birats.init.R")
+        q0, N = self.q0, self.N
+        z = np.tanh(q0[4])
+        _rdump(data, x_stan_0_0=self.x, x_stan_0_6=self.y)
+        _rdump(init, x_stan_0_1=q0[0:2], x_stan_0_2=q0[2:4], x_stan_0_3=np.array([[1, z], [z, 1.0]]),
+               x_stan_0_4=np.stack([q0[5:5 + N], q0[5 + N:5 + 2 * N]], axis=1), x_stan_0_5=np.exp(q0[-1]))
+        return data, init
+
+    def stan_args(self):
+        return (["num_warmup=0", "adapt", "engaged=0", "algorithm=hmc", "engine=static", f"int_time={self.eps * self.L}",
+                 "metric=unit_e", f"stepsize={self.eps}"], 20000)
+
 
 class BiratsNUTS(BiratsHMC):
     """C4 under hmcStan's DEFAULT sampler (birats.ipynb cell 8): NUTS, diag_e, max_depth 10, after warm-up.  Chains start from an
@@ -304,6 +377,9 @@ class BiratsNUTS(BiratsHMC):
         ad = np.zeros((10, C)); ad[0] = self.eps0; ad[9] = 2.0
         return dict(q=np.ascontiguousarray(qa[:, None] + 0.1 * np.sqrt(minv)[:, None] * rng.standard_normal((66, C))),
                     ad=ad, minv=np.ascontiguousarray(np.repeat(minv[:, None], C, axis=1)), wm=np.zeros((66, C)), wm2=np.zeros((66, C)))
+
+    def stan_args(self):
+        return (["num_warmup=300"], 3000)
 
     def cpu_run(self, orc, state, T, seed, chain0, step0, nthreads):
         return orc.birats_nuts_run(self.x, self.y, state["q"], state["ad"], state["minv"], state["wm"], state["wm2"], T,
@@ -467,9 +543,19 @@ def host_threads():
 def reference_arm(args, wl):
     """--impl reference: the reference's CPU implementation of the path on the host cores
     (oracle port; `kind` says which), same metric/config, bounded sample per step."""
+    nt = host_threads()
+    if getattr(wl, "stan_exe", None) and os.path.exists(wl.stan_exe):
+        vals = [stan_baseline(wl, nt) for _ in range(args.warmup + args.steps)][args.warmup:]
+        val = float(np.mean([v["value"] for v in vals]))
+        out = dict(metric=METRIC, value=val, unit=UNIT, impl="reference", n_gpus=args.gpus, steps=args.steps,
+                   warmup=args.warmup, ms_per_step=None, higher_is_better=True, scaling="weak", vs_baseline=None, dtype=wl.dtype,
+                   data="synthetic", config=dict(workload=wl.describe),
+                   cpu_baseline=dict(vals[-1], value=val),
+                   e2e=dict(value=val, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0), gpu_launches=0)
+        print(json.dumps(out), flush=True)
+        return
     from tests.oracle_binding import oracle
     orc = oracle()
-    nt = host_threads()
     C = getattr(wl, "cpu_chains_per_thread", 2) * nt
     # calibrate so that the whole run (steps + warmup) stays within ~2 minutes
     st = wl.init_state(C, 0)
@@ -491,6 +577,24 @@ def reference_arm(args, wl):
                cpu_baseline=dict(value=val, unit=UNIT, cores=nt, kind=wl_kind(wl), sample=sample),
                e2e=dict(value=val, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0), gpu_launches=0)
     print(json.dumps(out), flush=True)
+
+
+def stan_baseline(wl, nt):
+    """cpu_baseline through the reference's own sampler when its binary travelled with the repo (oracle/_ref/stan_*)"""
+    exe = getattr(wl, "stan_exe", None)
+    if not exe or not os.path.exists(exe):
+        return None
+    import tempfile
+    with tempfile.TemporaryDirectory() as wd:
+        data, init = wl.stan_files(wd)
+        args, n = wl.stan_args()
+        t0 = time.perf_counter()
+        rate, leaps = stan_reference_run(exe, data, init, args, n, nt, wd)
+        dt = time.perf_counter() - t0
+    return dict(value=rate, unit=UNIT, cores=nt, kind="reference",
+                sample=(f"vendored CmdStan 2.20 ({os.path.basename(exe)}), {nt} processes x {n} transitions, one chain per host core, "
+                        f"args: {' '.join(args)}; sampling time as each process reports it ({dt:.1f} s wall)"
+                        + (f"; {leaps:.1f} leapfrogs per transition" if leaps else "")))
 
 
 def wl_kind(wl):
@@ -634,13 +738,15 @@ def run_native(args, wl, rank, world, local, torch, dist):
         from tests.oracle_binding import oracle
         orc = oracle()
         nt = host_threads()
-        Cs = getattr(wl, "cpu_chains_per_thread", 2) * nt
-        stc = wl.init_state(Cs, 0)
-        per_tr = calibrate(wl, orc, stc, nt)
-        Ts = int(max(1, min(50000000, 12.0 / max(per_tr, 1e-12))))
-        v, dt = cpu_arm(wl, orc, Cs, Ts, 1, 0, nt)
-        cpu = dict(value=v, unit=UNIT, cores=nt, kind=wl_kind(wl),
-                   sample=f"{Cs} chains x {Ts} transitions of the same workload on {nt} host threads ({dt:.1f} s)")
+        cpu = stan_baseline(wl, nt)
+        if cpu is None:
+            Cs = getattr(wl, "cpu_chains_per_thread", 2) * nt
+            stc = wl.init_state(Cs, 0)
+            per_tr = calibrate(wl, orc, stc, nt)
+            Ts = int(max(1, min(50000000, 12.0 / max(per_tr, 1e-12))))
+            v, dt = cpu_arm(wl, orc, Cs, Ts, 1, 0, nt)
+            cpu = dict(value=v, unit=UNIT, cores=nt, kind=wl_kind(wl),
+                       sample=f"{Cs} chains x {Ts} transitions of the same workload on {nt} host threads ({dt:.1f} s)")
     return dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=K, warmup=W, ms_per_step=ms_per_launch,
                 higher_is_better=True, scaling="weak", vs_baseline=None, dtype=wl.dtype, data="synthetic",
                 config=dict(workload=wl.describe, chains_per_gpu=C, transitions_per_step=T, parallelism=f"chains-sharded x{world}",

@@ -133,6 +133,7 @@ class LinregHMC:
     dtype = "f64"
     n, d, L, eps = 1000, 10, 10, 0.01
     state_fields = ("q",)
+    logpdf_populations = (4096, 131072)
 
     def __init__(self):
         rng = np.random.default_rng(20261104)
@@ -179,6 +180,7 @@ class LinregNUTS(LinregHMC):
     post-warm-up transitions."""
     name = "linreg_nuts"
     kernel = "nuts"
+    logpdf_populations = None
     symbol = "linreg_nuts"
     state_fields = ("q", "ad", "minv", "wm", "wm2")
     e2e_fields = ("q",)
@@ -291,6 +293,7 @@ class BiratsHMC:
     transitions_per_step = 200
     N, Tn, L, eps = 30, 5, 10, 0.02
     state_fields = ("q",)
+    logpdf_populations = (1024, 131072)
     diag_thin = 20
 
     def __init__(self):
@@ -337,6 +340,7 @@ class BiratsNUTS(BiratsHMC):
     metric = the one a 300-transition warm-up of the CPU restatement reaches (computed once at start-up, untimed)."""
     name = "birats_nuts"
     kernel = "nuts"
+    logpdf_populations = None
     symbol = "birats_nuts"
     state_fields = ("q", "ad", "minv", "wm", "wm2")
     e2e_fields = ("q",)
@@ -601,6 +605,68 @@ def wl_kind(wl):
     return getattr(wl, "cpu_kind", "port")
 
 
+def logpdf_arm(args, wl, rank, world, local, torch, dist):
+    """The third leg of BASELINE.json's metric, "logpdf GB/s": joint log-density + gradient evaluations (stk_logp_grad, the
+    entry that replaces one runCC call of an `lpdf` program / one Stan log_prob_grad) over all resident chains, at the
+    metric's 4096 chains and at a particle-filter-sized population.  GB/s = evaluations/s x SURVEY 8d's algorithmic bytes
+    per evaluation.  Device-timed with CUDA events on the library's stream (L2 flushed before every call); `e2e` uploads
+    the points from pinned host memory and reads lp + gradient back into pinned host memory inside the timed region."""
+    from stochaskell_b200 import Sampler
+    dev = torch.device("cuda", local)
+    K, W = max(args.steps, 10), max(args.warmup, 3)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    out = {}
+    for C in wl.logpdf_populations:
+        s = Sampler(wl.module, C, wl.data(), seed=20261104, device=local, first_global_chain=rank * C)
+        ch = s.chains
+        st0 = wl.init_state(C, rank * C)
+        ch.set_state("q", st0["q"])
+        stream = torch.cuda.ExternalStream(s.ctx.stream, device=dev)
+        with torch.cuda.stream(stream):
+            for _ in range(W):
+                flush.zero_(); ch.logp_grad(host=False)
+            ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+            torch.cuda.synchronize(dev)
+            if world > 1:
+                dist.barrier()
+            for k in range(K):
+                flush.zero_()
+                ev[k][0].record(stream)
+                ch.logp_grad(host=False)
+                ev[k][1].record(stream)
+            torch.cuda.synchronize(dev)
+            dev_ms = sum(a.elapsed_time(b) for a, b in ev)
+            q_host = torch.from_numpy(np.ascontiguousarray(st0["q"])).pin_memory().numpy()
+            P = q_host.shape[0]
+            lp_host = torch.empty(C, dtype=torch.float64).pin_memory().numpy()
+            g_host = torch.empty((P, C), dtype=torch.float64).pin_memory().numpy()
+            for _ in range(2):
+                ch.set_state("q", q_host); ch.logp_grad(lp_host, g_host)
+            torch.cuda.synchronize(dev)
+            if world > 1:
+                dist.barrier()
+            t0 = time.perf_counter()
+            for _ in range(K):
+                ch.set_state("q", q_host); ch.logp_grad(lp_host, g_host)
+            torch.cuda.synchronize(dev)
+            te = time.perf_counter() - t0
+        tm = torch.tensor([dev_ms, te], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+        evals = world * C * K / (float(tm[0]) * 1e-3)
+        out[str(C)] = dict(evals_per_sec=evals, logpdf_gbs=evals * wl.bytes_per_eval / 1e9, us_per_launch=float(tm[0]) * 1e3 / K,
+                           chains_per_gpu=C, finite=bool(np.isfinite(lp_host).all() and np.isfinite(g_host).all()),
+                           e2e=dict(evals_per_sec=world * C * K / float(tm[1]), logpdf_gbs=world * C * K / float(tm[1]) * wl.bytes_per_eval / 1e9,
+                                    h2d_bytes_per_step=int(q_host.nbytes), d2h_bytes_per_step=int(lp_host.nbytes + g_host.nbytes)))
+        del s, ch
+    peaks = measured_peaks()
+    best = max(v["logpdf_gbs"] for v in out.values()) / world
+    return dict(unit="GB/s", kernel=wl.module[8:] + "_logp_grad", algorithmic_bytes_per_eval=wl.bytes_per_eval, steps=K, warmup=W,
+                populations=out, frac_of_hbm_peak_best=best / peaks["hbm_gbs"], peak=peaks["hbm_gbs"],
+                note="algorithmic bytes (SURVEY 8d: the data a one-chain evaluation streams + its state); the observed data is "
+                     "shared by the chains of a CTA and staged in shared memory, so the figure exceeds physical DRAM traffic")
+
+
 def run_native(args, wl, rank, world, local, torch, dist):
     """One workload on this rank's GPU; returns the result dict on rank 0 (None elsewhere)."""
     from stochaskell_b200 import Sampler, diag_finish, lib
@@ -721,6 +787,12 @@ def run_native(args, wl, rank, world, local, torch, dist):
     except Exception as e:  # diagnostics are not part of the timed path
         diag = dict(error=str(e)[:200])
 
+    logpdf = None
+    if getattr(wl, "logpdf_populations", None) and not args.no_e2e:
+        try:
+            logpdf = logpdf_arm(args, wl, rank, world, local, torch, dist)
+        except Exception as e:
+            logpdf = dict(error=str(e)[:200])
     if rank != 0:
         return None
     peaks = measured_peaks()
@@ -752,7 +824,8 @@ def run_native(args, wl, rank, world, local, torch, dist):
                 config=dict(workload=wl.describe, chains_per_gpu=C, transitions_per_step=T, parallelism=f"chains-sharded x{world}",
                             l2="flushed (256 MiB memset) before every step, outside the per-step CUDA events",
                             wall_ms_per_step_incl_flush=wall_ms / K),
-                roofline=roofline, cpu_baseline=cpu, e2e=e2e, gpu_launches=int(launches), clocks=clk, diagnostics=diag)
+                roofline=roofline, cpu_baseline=cpu, e2e=e2e, gpu_launches=int(launches), clocks=clk, diagnostics=diag,
+                **(dict(logpdf=logpdf) if logpdf else {}))
 
 
 def main():

@@ -197,6 +197,11 @@ const char* stk_csv_col_name(const stk_csv* c, int i);
 const double* stk_csv_values(const stk_csv* c);      /* row-major [rows][cols] */
 const char* stk_csv_comments(const stk_csv* c);
 void stk_csv_free(stk_csv* c);
+/* writeNPy (Data/Expression/Const/IO.hs:28-45): NumPy 1.0 file, '<f8', C order, the reference's header padding byte for
+ * byte; `values` row-major, dims = {} for a scalar.  readRealMatrix (IO.hs:22-26): headerless CSV of doubles into an
+ * stk_csv (column names empty); ragged rows or non-numeric fields are STK_ERR_ARG. */
+int stk_npy_write(const char* path, const double* values, int ndim, const long long* dims);
+int stk_real_matrix_read(const char* path, stk_csv** out);
 
 #ifdef __cplusplus
 }

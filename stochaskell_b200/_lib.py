@@ -81,6 +81,8 @@ SIGNATURES = {
     "stk_csv_values": (C.POINTER(C.c_double), [C.c_void_p]),
     "stk_csv_comments": (C.c_char_p, [C.c_void_p]),
     "stk_csv_free": (None, [C.c_void_p]),
+    "stk_npy_write": (C.c_int, [C.c_char_p, C.c_void_p, C.c_int, C.POINTER(C.c_longlong)]),
+    "stk_real_matrix_read": (C.c_int, [C.c_char_p, C.POINTER(C.c_void_p)]),
 }
 
 

@@ -173,9 +173,14 @@ class Chains:
         check(lib().stk_logp(self._h, _ptr(out)))
         return out
 
-    def logp_grad(self):
-        lp = np.empty(self.n)
-        g = np.empty((lib().stk_num_params(self._h), self.n))
+    def logp_grad(self, out_lp: Optional[np.ndarray] = None, out_grad: Optional[np.ndarray] = None, host: bool = True):
+        """lp [chains] and gradient [P][chains] at the resident state.  `out_*`: caller-owned (e.g. pinned) host buffers;
+        `host=False` evaluates on the device only (results stay in the library's buffers, nothing is copied back)."""
+        if not host:
+            check(lib().stk_logp_grad(self._h, None, None))
+            return None, None
+        lp = np.empty(self.n) if out_lp is None else out_lp
+        g = np.empty((lib().stk_num_params(self._h), self.n)) if out_grad is None else out_grad
         check(lib().stk_logp_grad(self._h, _ptr(lp), _ptr(g)))
         return lp, g
 

@@ -228,3 +228,69 @@ extern "C" const char* stk_csv_col_name(const stk_csv* c, int i) { return c->c.c
 extern "C" const double* stk_csv_values(const stk_csv* c) { return c->c.v.data(); }   // row-major [rows][cols]
 extern "C" const char* stk_csv_comments(const stk_csv* c) { return c->c.comments.c_str(); }
 extern "C" void stk_csv_free(stk_csv* c) { delete c; }
+
+// ---- .npy and headerless CSV matrices (Data/Expression/Const/IO.hs) -----------------------------------------------------
+// writeNPy (IO.hs:28-45): NumPy format 1.0, '<f8', C order; the dictionary is padded with spaces so that
+// 10 + len(header) is a multiple of 16, exactly as the reference computes it (pad = (10 + len(dic) + 1) mod 16).
+extern "C" int stk_npy_write(const char* path, const double* values, int ndim, const long long* dims) {
+  if (!path || ndim < 0 || (ndim > 0 && !dims)) return stk_set_error_(STK_ERR_ARG, "stk_npy_write: bad argument");
+  long long n = 1;
+  std::string sh;
+  for (int i = 0; i < ndim; ++i) {
+    if (dims[i] < 0) return stk_set_error_(STK_ERR_ARG, "stk_npy_write: negative dimension");
+    n *= dims[i];
+    if (i) sh += ",";
+    sh += std::to_string(dims[i]);
+  }
+  if (ndim == 1) sh += ",";
+  if (n > 0 && !values) return stk_set_error_(STK_ERR_ARG, "stk_npy_write: null values");
+  std::string dic = "{'descr': '<f8', 'fortran_order': False, 'shape': (" + sh + "), }";
+  const size_t pad = (10 + dic.size() + 1) % 16;
+  std::string header = dic + (pad ? std::string(16 - pad, ' ') : std::string()) + "\n";
+  FILE* f = fopen(path, "wb");
+  if (!f) return stk_set_error_(STK_ERR_ARG, (std::string("cannot open ") + path + ": " + strerror(errno)).c_str());
+  const unsigned char magic[10] = {0x93, 'N', 'U', 'M', 'P', 'Y', 1, 0, (unsigned char)(header.size() & 0xff), (unsigned char)(header.size() >> 8)};
+  bool ok = fwrite(magic, 1, 10, f) == 10 && fwrite(header.data(), 1, header.size(), f) == header.size();
+  // putFloat64le: the image's hosts are little-endian, so the in-memory doubles are the file's bytes
+  if (ok && n > 0) ok = fwrite(values, sizeof(double), (size_t)n, f) == (size_t)n;
+  if (fclose(f) != 0 || !ok) return stk_set_error_(STK_ERR_ARG, "stk_npy_write: write failed");
+  return STK_OK;
+}
+
+// readRealMatrix (IO.hs:22-26): CSV.decode NoHeader into rows of doubles.  Returned as an stk_csv without column names
+// (stk_csv_col_name gives ""); every row must have the first row's length.
+extern "C" int stk_real_matrix_read(const char* path, stk_csv** out) {
+  if (!path || !out) return stk_set_error_(STK_ERR_ARG, "stk_real_matrix_read: null argument");
+  FILE* f = fopen(path, "r");
+  if (!f) return stk_set_error_(STK_ERR_ARG, (std::string("cannot open ") + path + ": " + strerror(errno)).c_str());
+  stk_csv* r = new stk_csv(); r->c.rows = 0;
+  std::string line; char buf[1 << 16];
+  bool bad = false;
+  auto handle = [&](const std::string& ln) {
+    if (ln.empty()) return;
+    const char* p = ln.c_str(); size_t n0 = r->c.v.size();
+    for (;;) {
+      while (*p == ' ' || *p == '"') ++p;
+      char* end; double x = strtod(p, &end);
+      if (end == p) { bad = true; break; }
+      r->c.v.push_back(x); p = end;
+      while (*p == ' ' || *p == '"') ++p;
+      if (*p == ',') { ++p; continue; }
+      if (*p) bad = true;
+      break;
+    }
+    const size_t w = r->c.v.size() - n0;
+    if (r->c.rows == 0) r->c.cols.assign(w, std::string());
+    else if (w != r->c.cols.size()) bad = true;
+    ++r->c.rows;
+  };
+  while (fgets(buf, sizeof buf, f)) {
+    line += buf;
+    if (!line.empty() && line.back() == '\n') { line.pop_back(); if (!line.empty() && line.back() == '\r') line.pop_back(); handle(line); line.clear(); }
+  }
+  if (!line.empty()) handle(line);
+  fclose(f);
+  if (bad) { delete r; return stk_set_error_(STK_ERR_ARG, "readRealMatrix: a field is not a number or the rows are ragged"); }
+  *out = r;
+  return STK_OK;
+}

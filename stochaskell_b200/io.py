@@ -89,3 +89,23 @@ def stan_columns(name: str, shape: Sequence[int]) -> list:
         return [name]
     idx = np.indices(shape).reshape(len(shape), -1, order="F").T + 1
     return [name + "." + ".".join(str(i) for i in row) for row in idx]
+
+
+def write_npy(path: str, value) -> None:
+    """writeNPy (Data/Expression/Const/IO.hs:28-45): a real array as a NumPy 1.0 '<f8' C-order file"""
+    l = _sig()
+    a = np.ascontiguousarray(value, dtype=np.float64)
+    dims = (C.c_longlong * max(a.ndim, 1))(*a.shape)
+    check(l.stk_npy_write(path.encode(), a.ctypes.data_as(C.c_void_p), a.ndim, dims))
+
+
+def read_real_matrix(path: str) -> np.ndarray:
+    """readRealMatrix (IO.hs:22-26): headerless CSV -> matrix [rows][cols]"""
+    l = _sig()
+    h = C.c_void_p()
+    check(l.stk_real_matrix_read(path.encode(), C.byref(h)))
+    try:
+        nc, nr = l.stk_csv_cols(h), l.stk_csv_rows(h)
+        return np.ctypeslib.as_array(l.stk_csv_values(h), shape=(nr * nc,)).copy().reshape(nr, nc) if nr * nc else np.zeros((nr, nc))
+    finally:
+        l.stk_csv_free(h)

@@ -59,3 +59,45 @@ def test_stan_csv_reads_cmdstan_output_and_round_trips(tmp_path):
     open(p, "w").write("# only comments\n")
     with pytest.raises(StkError, match="CSV file contains no data"):      # stanRead's own message (Stan.hs:371)
         read_stan_csv(p)
+
+
+def _ref_npy_bytes(a):
+    """writeNPy restated byte for byte (Data/Expression/Const/IO.hs:28-45)"""
+    import struct
+    sh = list(a.shape)
+    dic = "{'descr': '<f8', 'fortran_order': False, 'shape': (" + ",".join(str(d) for d in sh) + ("," if len(sh) == 1 else "") + "), }"
+    pad = (10 + len(dic) + 1) % 16
+    header = dic + ("" if pad == 0 else " " * (16 - pad)) + "\n"
+    return b"\x93NUMPY\x01\x00" + struct.pack("<H", len(header)) + header.encode() + a.astype("<f8").tobytes(order="C")
+
+
+@pytest.mark.parametrize("shape", [(7,), (3, 5), (2, 3, 4), (1,), (0,), (16, 1), (123456,)])
+def test_npy_matches_writeNPy_and_numpy_loads_it(tmp_path, shape):
+    from stochaskell_b200.io import write_npy
+    a = np.random.default_rng(5).standard_normal(shape)
+    p = str(tmp_path / "a.npy")
+    write_npy(p, a)
+    raw = open(p, "rb").read()
+    assert raw == _ref_npy_bytes(a)
+    assert (len(raw) - a.size * 8) % 16 == 0
+    b = np.load(p)
+    assert b.dtype == np.float64 and b.shape == a.shape and np.array_equal(a, b)
+
+
+def test_real_matrix_read(tmp_path):
+    from stochaskell_b200.io import read_real_matrix
+    from stochaskell_b200._lib import StkError
+    a = np.random.default_rng(6).standard_normal((9, 4))
+    p = str(tmp_path / "m.csv")
+    with open(p, "w") as f:
+        for r in a:
+            f.write(",".join(repr(float(x)) for x in r) + "\r\n")
+    assert np.array_equal(read_real_matrix(p), a)
+    with open(p, "w") as f:
+        f.write("1,2,3\n4,5\n")
+    with pytest.raises(StkError):
+        read_real_matrix(p)
+    with open(p, "w") as f:
+        f.write("1,x,3\n")
+    with pytest.raises(StkError):
+        read_real_matrix(p)

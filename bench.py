@@ -876,7 +876,7 @@ def main():
         r = run_native(args, WORKLOADS[name](), rank, world, local, torch, dist)
         if r is not None:
             extra[name] = {k: r[k] for k in ("value", "unit", "ms_per_step", "dtype", "config", "roofline", "cpu_baseline",
-                                             "e2e", "gpu_launches", "diagnostics")}
+                                             "e2e", "gpu_launches", "diagnostics", "logpdf") if k in r}
     if rank == 0:
         if extra:
             out["gpu_launches"] += sum(v["gpu_launches"] for v in extra.values())

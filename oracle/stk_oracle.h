@@ -113,6 +113,14 @@ int orc_gp_hmc_step(const double* L, const int* z, int n, double* w, double eps,
 long long orc_gp_hmc_run(const double* L, const int* z, int n, double* W, long long C, long long T, double eps, int Lf,
                          uint64_t seed, uint64_t chain0, uint64_t step0, int nthreads);
 
+// ---- C3 with per-chain hyper-parameters: GP marginal likelihood, one Cholesky per evaluation (stk_oracle_gpr.cpp;
+//      pinned by tests/golden/gpr_cc.json = the CC templates on the vendored Eigen) ----
+double orc_gpr_logp(const double* x, const double* y, int n, const double* q);
+int orc_gpr_mh_step(const double* x, const double* y, int n, double* q, double rw, uint64_t seed, uint64_t chain,
+                    uint64_t step, double* lp_io);
+long long orc_gpr_mh_run(const double* x, const double* y, int n, double* Q, double* LP, long long C, long long T, double rw,
+                         uint64_t seed, uint64_t chain0, uint64_t step0, int nthreads);
+
 // ---- soccer RJ (rj.ipynb; pinned against the reference's generated C++ in oracle/_ref) -----
 double orc_soccer_accept_prob(int tag, double lam, double kappa, const int* y, int ny, double x, double* kappa_prop);
 int orc_soccer_rj_step(int tag, double lam, double* kappa, const int* y, int ny,

@@ -1,0 +1,318 @@
+// gpr.cu — config C3 with PER-CHAIN hyper-parameters (BASELINE configs[2] "batched Cholesky per chain").
+//
+// Model (reference: `gpclas` priors and `kernelSE'`, stochaskell/app/benchmark/Main.hs:65-91; `multi_normal_lpdf`,
+// the statement template of ccNode, stochaskell/src/Language/CC.hs:221-225, with LOG_DET of the prelude :420-421 and
+// Eigen's `llt().matrixL()` :161-162):
+//   lsv ~ normal 0 1;   lls2 ~ normal (log 100) 2
+//   C = exp(lsv - distEucSq x x / (2 exp lls2)) + diag 0.01,  distEucSq a b = a_i^2 + b_j^2 - 2 a_i b_j  (kept expanded)
+//   y ~ multi_normal 0 C:   lp = -0.5 (|L^-1 y|^2 + n log 2pi + 2 sum log L_ii) + priors,   L = chol C
+// so EVERY evaluation of EVERY chain is a covariance build + an n x n Cholesky + a triangular solve.
+// Transition: random-walk Metropolis on (lsv, lls2) (the `mh` shape of mh.ipynb cell 1): slot 0 = two proposal normals,
+// slot 1 = the accept uniform; bernoulli(min 1 a) of Program.hs:1278-1283.
+//
+// B200 design: tcgen05 has no fp64 path and cond(C) ~ n e^lsv / 0.01 ~ 1e6 rules fp32 out at the 1e-10 tier, so the
+// factorisation runs on the fp64 pipe — one PERSISTENT CTA per SM, each factoring one chain's matrix at a time
+// (148 matrices in flight, the chains of a launch strided over the CTAs):
+//   * left-looking blocked Cholesky, 128 x 128 tiles: tile (I,J) = C(I,J) - sum_{k < 128 J} L[I,k] L[J,k]^T is a
+//     register-tiled DFMA product (8 x 8 per thread, cp.async double-buffered k-slabs of 16, both operands are unit-stride
+//     columns of the column-major factor) — the accumulator never leaves registers, so HBM/L2 sees only the operand
+//     stream (16 flop per byte) and ONE write of each finished tile;
+//   * the covariance is never materialised: the epilogue of a tile evaluates C(I,J) from x and the chain's
+//     hyper-parameters and subtracts the accumulator;
+//   * the diagonal tile is factored in shared memory (right-looking, two barriers per column) with the forward
+//     substitution z = L^-1 y of its 128 rows folded into the same loop (the y-row's dot products with the finished
+//     columns ride on the diagonal tile's operand stream); off-diagonal tiles are solved against the packed factor in
+//     shared memory, a row per thread, four columns at a time;
+//   * per-CTA scratch (work fields): the factor [ld][ld] column-major (ld = n rounded up to 128) and z [ld].
+// Padding rows/columns are the identity (log 1 = 0, y = 0), so n need not be a multiple of 128.
+//
+// Oracle: oracle/stk_oracle_gpr.cpp, pinned by tests/golden/gpr_cc.json (the CC templates on the vendored Eigen).
+#include "../stk_device.cuh"
+
+using namespace stk;
+
+#define F_X 0
+#define F_Y 1
+#define F_Q 2
+#define F_LP 3
+#define F_Q0 4
+#define F_LPN 5
+#define F_A 6
+#define F_ZW 7
+#define P_RW 0
+
+#define TB 128                 // tile edge
+#define BK 16                  // k-slab
+#define CP 129                 // pitch of the shared C tile (column-major [c][r])
+#define SM_TILE (TB * CP)      // doubles; aliases the operand buffers (2 * 2 * BK * TB = 8192 doubles)
+#define SM_LS (TB * (TB + 1) / 2)
+#define GPR_SMEM 202496         // (SM_TILE + SM_LS + 2 BK + 4 TB) doubles
+static_assert(GPR_SMEM == (SM_TILE + SM_LS + 2 * BK + 4 * TB) * 8, "descriptor smem size");
+#define STRINGIFY(x) #x
+#define STR(x) STRINGIFY(x)
+
+extern "C" __device__ const char stk_desc[] =
+    "stk-module 1\n"
+    "name gpr\n"
+    "nparam 2\n"
+    "field x data f64 0\n"
+    "field y data f64 0\n"
+    "field q state f64 2\n"
+    "field lp state f64 1\n"
+    "field q0 state f64 2\n"
+    "field lpn state f64 1\n"
+    "field A work f64 sms*@x^128*@x^128\n"
+    "field zw work f64 sms*@x^128\n"
+    "param rw 0.1\n"
+    "record q\n"
+    "plan logp logp -\n"
+    "stage logp body gpr_chol 256 sms 1 " STR(GPR_SMEM) "\n"
+    "plan mh kernel -\n"
+    "stage mh init gpr_chol 256 sms 1 " STR(GPR_SMEM) "\n"
+    "stage mh pre gpr_propose 128 chains/128 1 0\n"
+    "stage mh body gpr_chol 256 sms 1 " STR(GPR_SMEM) "\n"
+    "stage mh post gpr_accept 128 chains/128 1 0\n";
+
+__device__ __forceinline__ long long ld_of(long long n) { return (n + TB - 1) / TB * TB; }
+
+__device__ __forceinline__ void cp_async16(void* dst, const void* src) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(src));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N)); }
+
+// covariance entry (kernelSE' with the expanded squared distance; no contraction, as the reference's Eigen expression)
+__device__ __forceinline__ double cov_entry(double xi, double xj, double lsv, double den, bool diag) {
+  const double d2 = __dsub_rn(__dadd_rn(__dmul_rn(xi, xi), __dmul_rn(xj, xj)), __dmul_rn(2.0, __dmul_rn(xi, xj)));
+  const double v = exp(__dsub_rn(lsv, __ddiv_rn(d2, den)));
+  return diag ? __dadd_rn(v, 0.01) : v;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// gpr_chol: lp of every chain at its current q.  Persistent: CTA b takes chains b, b + grid, ...
+// Output: stage_kind 4 (logp entry) -> out_lp; 0 (init: lp of the current state) -> lp; 2 (body: proposal) -> lpn.
+// ---------------------------------------------------------------------------------------------------------------
+extern "C" __global__ void __launch_bounds__(256, 1) gpr_chol(const __grid_constant__ StkArgs a) {
+  extern __shared__ __align__(16) double sm[];
+  double* Cs = sm;                          // [TB][CP] finished tile, column-major; during the product: operand buffers
+  double* As = sm;                          // [2][BK][TB]
+  double* Bs = sm + 2 * BK * TB;            // [2][BK][TB]
+  double* Ls = sm + SM_TILE;                // packed factor of the current diagonal tile: L[c][k] at c(c+1)/2 + k
+  double* zs = Ls + SM_LS;                  // [2][BK] slab of z
+  double* lcol = zs + 2 * BK;               // [TB] scaled pivot column
+  double* ss = lcol + TB;                   // [TB] running right-hand side of the y row
+  double* zout = ss + TB;                   // [TB] solved z of this block
+  double* yacc_s = zout + TB;               // [TB] dot products of the y row with the finished columns
+
+  const long long n = a.flen[F_X], ld = ld_of(n), C = a.n_chains;
+  const int T = (int)(ld / TB);
+  const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
+  const double* x = (const double*)a.field[F_X];
+  const double* y = (const double*)a.field[F_Y];
+  const double* Q = (const double*)a.field[F_Q];
+  double* A = (double*)a.field[F_A] + (long long)blockIdx.x * ld * ld;
+  double* zw = (double*)a.field[F_ZW] + (long long)blockIdx.x * ld;
+  double* out = a.stage_kind == 4 ? a.out_lp : (double*)a.field[a.stage_kind == 0 ? F_LP : F_LPN];
+
+  for (long long chain = blockIdx.x; chain < C; chain += gridDim.x) {
+    const double lsv = Q[chain], lls2 = Q[C + chain];
+    const double den = __dmul_rn(2.0, exp(lls2));
+    double logdet = 0.0, quad = 0.0;
+    bool bad = false;
+
+    for (int J = 0; J < T; ++J) {
+      for (int I = J; I < T; ++I) {
+        const bool diag_tile = I == J;
+        const int ktiles = J * (TB / BK);
+        // ---- product: acc[r][c] = sum_{k < 128 J} L[128 I + r, k] L[128 J + c, k] ----
+        double acc[8][8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[i][j] = 0.0;
+        double yacc = 0.0;
+        auto load_slab = [&](int t, int buf) {
+          const long long k0 = (long long)t * BK;
+          double* as = As + buf * BK * TB;
+          double* bs = Bs + buf * BK * TB;
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const int ch = tid + 256 * u, kk = ch >> 6, col = (ch & 63) * 2;
+            cp_async16(as + kk * TB + col, A + (k0 + kk) * ld + (long long)I * TB + col);
+            cp_async16(bs + kk * TB + col, A + (k0 + kk) * ld + (long long)J * TB + col);
+          }
+          if (diag_tile && tid < BK / 2) cp_async16(zs + buf * BK + 2 * tid, zw + k0 + 2 * tid);
+          cp_async_commit();
+        };
+        if (ktiles > 0) load_slab(0, 0);
+        for (int t = 0; t < ktiles; ++t) {
+          const int buf = t & 1;
+          if (t + 1 < ktiles) { load_slab(t + 1, buf ^ 1); cp_async_wait<1>(); } else cp_async_wait<0>();
+          __syncthreads();
+          const double* as = As + buf * BK * TB;
+          const double* bs = Bs + buf * BK * TB;
+#pragma unroll
+          for (int kk = 0; kk < BK; ++kk) {
+            double av[8], bv[8];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const double2 x2 = *reinterpret_cast<const double2*>(as + kk * TB + ty * 2 + 32 * j);
+              const double2 y2 = *reinterpret_cast<const double2*>(bs + kk * TB + tx * 2 + 32 * j);
+              av[2 * j] = x2.x; av[2 * j + 1] = x2.y; bv[2 * j] = y2.x; bv[2 * j + 1] = y2.y;
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+              for (int j = 0; j < 8; ++j) acc[i][j] = fma(av[i], bv[j], acc[i][j]);
+          }
+          if (diag_tile && tid < TB) {
+            const double* zb = zs + buf * BK;
+#pragma unroll
+            for (int kk = 0; kk < BK; ++kk) yacc = fma(zb[kk], bs[kk * TB + tid], yacc);
+          }
+          __syncthreads();
+        }
+        if (diag_tile && tid < TB) yacc_s[tid] = yacc;   // parked outside the region the tile is about to overwrite
+
+        // ---- epilogue: tile = C(I,J) - acc, into shared memory (column-major, pitch CP) ----
+        {
+          double xr[8], xc[8];
+          int gr[8], gc[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            gr[i] = I * TB + ty * 2 + 32 * (i >> 1) + (i & 1);
+            gc[i] = J * TB + tx * 2 + 32 * (i >> 1) + (i & 1);
+            xr[i] = gr[i] < n ? x[gr[i]] : 0.0;
+            xc[i] = gc[i] < n ? x[gc[i]] : 0.0;
+          }
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int r = ty * 2 + 32 * (i >> 1) + (i & 1);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const int c = tx * 2 + 32 * (j >> 1) + (j & 1);
+              double kv;
+              if (gr[i] < n && gc[j] < n) {
+                // the upper half of a diagonal tile is never read
+                kv = (!diag_tile || r >= c) ? cov_entry(xr[i], xc[j], lsv, den, gr[i] == gc[j]) : 0.0;
+              } else kv = gr[i] == gc[j] ? 1.0 : 0.0;
+              Cs[c * CP + r] = kv - acc[i][j];
+            }
+          }
+        }
+        __syncthreads();
+
+        if (diag_tile) {
+          // ---- factor the tile in place; the y row rides along: ss = y_J - (dot products), z_j = ss_j / L_jj ----
+          const int r = tid & (TB - 1), h = tid >> 7;
+          if (tid < TB) {
+            const long long g = (long long)J * TB + tid;
+            ss[tid] = (g < n ? y[g] : 0.0) - yacc_s[tid];
+          }
+          for (int j = 0; j < TB; ++j) {
+            __syncthreads();
+            const double piv = Cs[j * CP + j];
+            if (!(piv > 0.0)) bad = true;
+            const double dj = sqrt(piv);
+            const double zj = ss[j] / dj;
+            logdet += log(dj);
+            quad = fma(zj, zj, quad);
+            if (h == 0) {
+              if (r > j) { const double l = Cs[j * CP + r] / dj; Cs[j * CP + r] = l; lcol[r] = l; }
+              else if (r == j) zout[j] = zj;
+            }
+            __syncthreads();
+            if (tid == j) Cs[j * CP + j] = dj;    // after the barrier: every thread has read the pivot
+            if (r > j) {
+              const double lr = lcol[r];
+              if (h == 1) ss[r] = fma(-lr, zj, ss[r]);
+              for (int c = j + 1 + h; c <= r; c += 2) Cs[c * CP + r] = fma(-lr, lcol[c], Cs[c * CP + r]);
+            }
+          }
+          __syncthreads();
+          // packed copy of the factor for the solves of this block column; z of this block to the CTA's z vector
+          for (int e = tid; e < TB * TB; e += 256) {
+            const int c = e >> 7, k = e & (TB - 1);
+            if (k <= c) Ls[c * (c + 1) / 2 + k] = Cs[k * CP + c];
+          }
+          if (tid < TB) zw[(long long)J * TB + tid] = zout[tid];
+          __syncthreads();
+        } else {
+          // ---- X L_JJ^T = tile: a row per thread, four columns at a time; the solved tile goes to the factor ----
+          if (tid < TB) {
+            const int r = tid;
+            for (int cb = 0; cb < TB; cb += 4) {
+              double s0 = Cs[(cb + 0) * CP + r], s1 = Cs[(cb + 1) * CP + r], s2 = Cs[(cb + 2) * CP + r], s3 = Cs[(cb + 3) * CP + r];
+              const double* l0 = Ls + (cb + 0) * (cb + 1) / 2;
+              const double* l1 = Ls + (cb + 1) * (cb + 2) / 2;
+              const double* l2 = Ls + (cb + 2) * (cb + 3) / 2;
+              const double* l3 = Ls + (cb + 3) * (cb + 4) / 2;
+              for (int k = 0; k < cb; ++k) {
+                const double v = Cs[k * CP + r];
+                s0 = fma(-v, l0[k], s0); s1 = fma(-v, l1[k], s1); s2 = fma(-v, l2[k], s2); s3 = fma(-v, l3[k], s3);
+              }
+              s0 = s0 / l0[cb];
+              s1 = fma(-s0, l1[cb], s1) / l1[cb + 1];
+              s2 = fma(-s1, l2[cb + 1], fma(-s0, l2[cb], s2)) / l2[cb + 2];
+              s3 = fma(-s2, l3[cb + 2], fma(-s1, l3[cb + 1], fma(-s0, l3[cb], s3))) / l3[cb + 3];
+              Cs[(cb + 0) * CP + r] = s0; Cs[(cb + 1) * CP + r] = s1; Cs[(cb + 2) * CP + r] = s2; Cs[(cb + 3) * CP + r] = s3;
+            }
+          }
+          __syncthreads();
+          for (int e = tid; e < TB * TB; e += 256) {
+            const int c = e >> 7, r = e & (TB - 1);
+            A[((long long)J * TB + c) * ld + (long long)I * TB + r] = Cs[c * CP + r];
+          }
+          __syncthreads();   // the tile (= the operand buffers) is free again, the factor is visible to the CTA
+        }
+      }
+    }
+    if (tid == 0) {
+      double lp = -0.5 * (quad + kLog2Pi * (double)n + 2.0 * logdet);
+      lp += normal_lpdf(lsv, 0.0, 1.0);
+      lp += normal_lpdf(lls2, log(100.0), 2.0);
+      out[chain] = bad ? __longlong_as_double(0x7ff8000000000000ULL) : lp;
+    }
+  }
+}
+
+// proposal: q0 = q;  q = q + rw * N(0, I)   (slot 0 of the transition's Philox stream)
+extern "C" __global__ void __launch_bounds__(128) gpr_propose(const __grid_constant__ StkArgs a) {
+  const long long c = (long long)blockIdx.x * 128 + threadIdx.x;
+  if (c >= a.n_chains) return;
+  const long long C = a.n_chains;
+  double* Q = (double*)a.field[F_Q];
+  double* Q0 = (double*)a.field[F_Q0];
+  Rng g; g.init(a.seed, (u64)(a.chain0 + c), a.step0);
+  double z0, z1; g.normal2(z0, z1);
+  const double rw = a.par[P_RW];
+  const double q0 = Q[c], q1 = Q[C + c];
+  Q0[c] = q0; Q0[C + c] = q1;
+  Q[c] = __dadd_rn(q0, __dmul_rn(rw, z0));
+  Q[C + c] = __dadd_rn(q1, __dmul_rn(rw, z1));
+}
+
+// accept / reject (slot 1), record
+extern "C" __global__ void __launch_bounds__(128) gpr_accept(const __grid_constant__ StkArgs a) {
+  const long long c = (long long)blockIdx.x * 128 + threadIdx.x;
+  if (c >= a.n_chains) return;
+  const long long C = a.n_chains;
+  double* Q = (double*)a.field[F_Q];
+  const double* Q0 = (const double*)a.field[F_Q0];
+  double* LP = (double*)a.field[F_LP];
+  const double lpn = ((const double*)a.field[F_LPN])[c];
+  const double lp = LP[c];
+  Rng g; g.init(a.seed, (u64)(a.chain0 + c), a.step0); g.slot = 1;
+  const double u = g.u01();
+  // a proposal whose covariance does not factor (lp = NaN) is rejected
+  if (lpn == lpn && u < fmin(1.0, exp(lpn - lp))) {
+    LP[c] = lpn;
+    if (a.accept) a.accept[c] += 1;
+  } else {
+    Q[c] = Q0[c]; Q[C + c] = Q0[C + c];
+  }
+  long long slot;
+  if (record_slot(a, 0, &slot)) { record_value(a, slot, 0, c, Q[c]); record_value(a, slot, 1, c, Q[C + c]); }
+}

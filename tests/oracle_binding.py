@@ -90,6 +90,12 @@ class Oracle:
         l.orc_gp_logp.argtypes = [P, P, I, P, P]
         l.orc_gp_hmc_step.restype = I
         l.orc_gp_hmc_step.argtypes = [P, P, I, P, D, I, U, U, U, P]
+        l.orc_gpr_logp.restype = D
+        l.orc_gpr_logp.argtypes = [P, P, I, P]
+        l.orc_gpr_mh_step.restype = I
+        l.orc_gpr_mh_step.argtypes = [P, P, I, P, D, U, U, U, P]
+        l.orc_gpr_mh_run.restype = C.c_longlong
+        l.orc_gpr_mh_run.argtypes = [P, P, I, P, P, C.c_longlong, C.c_longlong, D, U, U, U, I]
         l.orc_gp_hmc_run.restype = C.c_longlong
         l.orc_gp_hmc_run.argtypes = [P, P, I, P, C.c_longlong, C.c_longlong, D, I, U, U, U, I]
 
@@ -135,6 +141,19 @@ class Oracle:
         z = np.ascontiguousarray(z, dtype=np.int32)
         assert W.flags.c_contiguous and W.dtype == np.float64
         return self.l.orc_gp_hmc_run(_p(L), _p(z), W.shape[0], _p(W), W.shape[1], T, eps, Lf, seed, chain0, step0, nthreads)
+
+    # -- C3 with per-chain hyper-parameters (GP marginal likelihood, Cholesky per evaluation) ------
+    def gpr_logp(self, x, y, q):
+        x = np.ascontiguousarray(x, dtype=np.float64); y = np.ascontiguousarray(y, dtype=np.float64)
+        q = np.ascontiguousarray(q, dtype=np.float64)
+        return self.l.orc_gpr_logp(_p(x), _p(y), len(x), _p(q))
+
+    def gpr_mh_run(self, x, y, Q, T, rw, seed, chain0=0, step0=0, nthreads=1, LP=None):
+        """Q [2][C] updated in place; LP [C] (optional) carries lp; returns the number of accepted proposals"""
+        x = np.ascontiguousarray(x, dtype=np.float64); y = np.ascontiguousarray(y, dtype=np.float64)
+        assert Q.flags.c_contiguous and Q.dtype == np.float64 and Q.shape[0] == 2
+        return self.l.orc_gpr_mh_run(_p(x), _p(y), len(x), _p(Q), _p(LP) if LP is not None else None, Q.shape[1], T, rw,
+                                     seed, chain0, step0, nthreads)
 
     # -- C4 birats ------------------------------------------------------------------
     def birats_logp(self, x, y, q, grad=True):

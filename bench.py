@@ -511,7 +511,85 @@ class GPHMCTC(GPHMC):
         return r
 
 
-WORKLOADS = {"gp_hmc_tc": GPHMCTC, "linreg_hmc": LinregHMC, "linreg_nuts": LinregNUTS, "coal_rj": CoalRJ, "birats_hmc": BiratsHMC, "birats_nuts": BiratsNUTS, "dp_gibbs": DPGibbs, "gp_hmc": GPHMC}
+class GPRMH:
+    """C3 with PER-CHAIN hyper-parameters (BASELINE configs[2] "batched Cholesky per chain"): GP marginal likelihood
+    y ~ multi_normal(0, kernelSE' lsv lls2 x x) with gpclas' priors on (lsv, lls2), n = 2048; random-walk Metropolis on the two
+    hyper-parameters, so every transition of every chain is a covariance build + a 2048 x 2048 Cholesky + a triangular solve."""
+    name = "gpr_mh"
+    module = "builtin:gpr"
+    kernel = "mh"
+    symbol = "gpr_chol"
+    dtype = "f64"
+    chains = 4096
+    transitions_per_step = 2
+    n, rw = 2048, 0.1
+    state_fields = ("q",)
+    e2e_fields = ("q", "lp")
+    diag_thin = 1
+    diag_warmup = 2
+    diag_draws = 4
+    cpu_kind = "reference"
+    stan_exe = os.path.join(ROOT, "oracle", "_ref", "cc_mvn")
+
+    def __init__(self):
+        rng = np.random.default_rng(20261104)
+        self.x = np.sort(rng.uniform(0, 50, self.n))
+        self.y = np.sin(self.x / 5) + 0.1 * rng.standard_normal(self.n)
+        self.flops_per_transition = self.n ** 3 / 3.0        # SURVEY 8d: logp eval = n^3/3
+        self.bytes_per_transition = 8.0 * self.n * self.n     # the factor written once (SURVEY 8d: 8 n^2 per chain matrix)
+        self.describe = (f"C3 GP marginal likelihood with per-chain hyper-parameters (gpclas priors, kernelSE' + 0.01 I, "
+                         f"multi_normal_lpdf) n={self.n}, random-walk MH rw={self.rw}: one covariance build + Cholesky + solve "
+                         f"per chain and transition (configs[2] at 4096 chains/GPU)")
+
+    def data(self):
+        return dict(x=self.x, y=self.y)
+
+    def params(self):
+        return dict(rw=self.rw)
+
+    def init_state(self, C, chain0):
+        rng = np.random.default_rng(77 + chain0)
+        return dict(q=np.ascontiguousarray(np.stack([rng.normal(0.0, 0.5, C), rng.normal(np.log(100.0), 0.5, C)])))
+
+    def cpu_run(self, orc, state, T, seed, chain0, step0, nthreads):
+        return orc.gpr_mh_run(self.x, self.y, state["q"], T, self.rw, seed, chain0, step0, nthreads)
+
+    def reference_baseline(self, nt):
+        """the reference's own statement templates (CC.hs:221-225, :420-421, :161-162) on its vendored Eigen, one process per
+        host core, each evaluating the density `evals` times = that many MH transitions of one chain"""
+        if not os.path.exists(self.stan_exe):
+            return None
+        evals = 3
+        inp = (f"{self.n}\n" + " ".join(repr(float(v)) for v in self.x) + "\n" + " ".join(repr(float(v)) for v in self.y)
+               + f"\n0.0 {float(np.log(100.0))!r}\n")
+        t0 = time.perf_counter()
+        procs = [subprocess.Popen([self.stan_exe, "bench", str(evals)], stdin=subprocess.PIPE, stdout=subprocess.PIPE, text=True)
+                 for _ in range(nt)]
+        for pr in procs:
+            pr.stdin.write(inp); pr.stdin.close()
+        rate = 0.0
+        for pr in procs:
+            tok = pr.stdout.read().split(); pr.wait()
+            rate += int(tok[0]) / max(float(tok[1]), 1e-9)
+        dt = time.perf_counter() - t0
+        return dict(value=rate, unit=UNIT, cores=nt, kind="reference",
+                    sample=(f"oracle/_ref/cc_mvn (the CC backend's covariance / multi_normal_lpdf / LOG_DET templates on the vendored "
+                            f"Eigen, -O2 as compileCC builds), {nt} processes x {evals} evaluations = transitions of one chain each, "
+                            f"in-process time as each reports it ({dt:.1f} s wall)"))
+
+    def roofline(self, C, T, ms_per_launch, peaks):
+        tf = C * T * self.flops_per_transition / (ms_per_launch * 1e-3) / 1e12
+        peak = peaks.get("bf16_tflops_sustained") or peaks.get("bf16_tflops") or 1365.0
+        return dict(bound="tensor", achieved=tf, peak=peak, unit="TFLOP/s", frac=tf / peak, traffic=None,
+                    kernel="gpr_chol", peak_source=peaks["source"], useful_flops_per_transition_per_chain=self.flops_per_transition,
+                    fp64_pipe_peak_tflops=37.0, frac_of_fp64_pipe=tf / 37.0,
+                    note="useful flops = n^3/3 per chain and transition (SURVEY 8d, the Cholesky; covariance exps and the solve not "
+                         "counted); the factorisation needs fp64 (cond(C) ~ 1e6, parity tier 1e-10) and tcgen05 has no fp64 path, so "
+                         "it runs on the DFMA pipe (~37 TFLOP/s on a B200): `frac` against the dense bf16 tensor peak is small by "
+                         "construction, `frac_of_fp64_pipe` is the meaningful one")
+
+
+WORKLOADS = {"gp_hmc_tc": GPHMCTC, "linreg_hmc": LinregHMC, "linreg_nuts": LinregNUTS, "coal_rj": CoalRJ, "birats_hmc": BiratsHMC, "birats_nuts": BiratsNUTS, "dp_gibbs": DPGibbs, "gp_hmc": GPHMC, "gpr_mh": GPRMH}
 DEFAULT_WORKLOAD = "coal_rj"
 
 
@@ -588,6 +666,8 @@ def stan_baseline(wl, nt):
     exe = getattr(wl, "stan_exe", None)
     if not exe or not os.path.exists(exe):
         return None
+    if hasattr(wl, "reference_baseline"):
+        return wl.reference_baseline(nt)
     import tempfile
     with tempfile.TemporaryDirectory() as wd:
         data, init = wl.stan_files(wd)

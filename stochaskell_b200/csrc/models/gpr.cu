@@ -44,10 +44,15 @@ using namespace stk;
 #define TB 128                 // tile edge
 #define BK 16                  // k-slab
 #define CP 129                 // pitch of the shared C tile (column-major [c][r])
-#define SM_TILE (TB * CP)      // doubles; aliases the operand buffers (2 * 2 * BK * TB = 8192 doubles)
+#define SP 136                 // pitch of an operand slab row: = 8 mod 16 doubles, so that the 32 lanes of a DMMA fragment
+                               // load (4 k x 8 rows) spread over all banks (two wavefronts, the minimum for 256 B)
+#define NBUF 3                 // slab buffers per operand
+#define SLAB (BK * SP)
+#define SM_TILE (TB * CP)      // doubles; aliases the operand buffers (2 * NBUF * SLAB = 13056 doubles)
+static_assert(2 * NBUF * SLAB <= SM_TILE, "operand buffers must fit in the tile region");
 #define SM_LS (TB * (TB + 1) / 2)
-#define GPR_SMEM 202496         // (SM_TILE + SM_LS + 2 BK + 4 TB) doubles
-static_assert(GPR_SMEM == (SM_TILE + SM_LS + 2 * BK + 4 * TB) * 8, "descriptor smem size");
+#define GPR_SMEM 202624         // (SM_TILE + SM_LS + NBUF BK + 4 TB) doubles
+static_assert(GPR_SMEM == (SM_TILE + SM_LS + NBUF * BK + 4 * TB) * 8, "descriptor smem size");
 #define STRINGIFY(x) #x
 #define STR(x) STRINGIFY(x)
 
@@ -97,18 +102,19 @@ __device__ __forceinline__ double cov_entry(double xi, double xj, double lsv, do
 extern "C" __global__ void __launch_bounds__(256, 1) gpr_chol(const __grid_constant__ StkArgs a) {
   extern __shared__ __align__(16) double sm[];
   double* Cs = sm;                          // [TB][CP] finished tile, column-major; during the product: operand buffers
-  double* As = sm;                          // [2][BK][TB]
-  double* Bs = sm + 2 * BK * TB;            // [2][BK][TB]
+  double* As = sm;                          // [NBUF][BK][SP]
+  double* Bs = sm + NBUF * SLAB;            // [NBUF][BK][SP]
   double* Ls = sm + SM_TILE;                // packed factor of the current diagonal tile: L[c][k] at c(c+1)/2 + k
-  double* zs = Ls + SM_LS;                  // [2][BK] slab of z
-  double* lcol = zs + 2 * BK;               // [TB] scaled pivot column
+  double* zs = Ls + SM_LS;                  // [NBUF][BK] slab of z
+  double* lcol = zs + NBUF * BK;            // [TB] scaled pivot column
   double* ss = lcol + TB;                   // [TB] running right-hand side of the y row
   double* zout = ss + TB;                   // [TB] solved z of this block
   double* yacc_s = zout + TB;               // [TB] dot products of the y row with the finished columns
 
   const long long n = a.flen[F_X], ld = ld_of(n), C = a.n_chains;
   const int T = (int)(ld / TB);
-  const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int wr = warp >> 2, wc = warp & 3, lg = lane >> 2, lk = lane & 3;   // warp grid 2 x 4; DMMA group / index in group
   const double* x = (const double*)a.field[F_X];
   const double* y = (const double*)a.field[F_Y];
   const double* Q = (const double*)a.field[F_Q];
@@ -126,55 +132,61 @@ extern "C" __global__ void __launch_bounds__(256, 1) gpr_chol(const __grid_const
       for (int I = J; I < T; ++I) {
         const bool diag_tile = I == J;
         const int ktiles = J * (TB / BK);
-        // ---- product: acc[r][c] = sum_{k < 128 J} L[128 I + r, k] L[128 J + c, k] ----
-        double acc[8][8];
+        // ---- product: acc[r][c] = sum_{k < 128 J} L[128 I + r, k] L[128 J + c, k]  on the fp64 tensor pipe ----
+        // mma.sync.m8n8k4.f64 (DMMA): a warp owns 64 rows x 32 columns = 8 x 4 fragments (64 accumulators per lane);
+        // lane l holds A[l/4][l%4], B[l%4][l/4], C[l/4][2 (l%4) + {0,1}].  Three slab buffers, ONE barrier per slab.
+        double acc[8][4][2];
 #pragma unroll
         for (int i = 0; i < 8; ++i)
 #pragma unroll
-          for (int j = 0; j < 8; ++j) acc[i][j] = 0.0;
+          for (int j = 0; j < 4; ++j) { acc[i][j][0] = 0.0; acc[i][j][1] = 0.0; }
         double yacc = 0.0;
-        auto load_slab = [&](int t, int buf) {
+        auto load_slab = [&](int t) {
+          const int buf = t % NBUF;
           const long long k0 = (long long)t * BK;
-          double* as = As + buf * BK * TB;
-          double* bs = Bs + buf * BK * TB;
+          double* as = As + buf * SLAB;
+          double* bs = Bs + buf * SLAB;
 #pragma unroll
           for (int u = 0; u < 4; ++u) {
             const int ch = tid + 256 * u, kk = ch >> 6, col = (ch & 63) * 2;
-            cp_async16(as + kk * TB + col, A + (k0 + kk) * ld + (long long)I * TB + col);
-            cp_async16(bs + kk * TB + col, A + (k0 + kk) * ld + (long long)J * TB + col);
+            cp_async16(as + kk * SP + col, A + (k0 + kk) * ld + (long long)I * TB + col);
+            cp_async16(bs + kk * SP + col, A + (k0 + kk) * ld + (long long)J * TB + col);
           }
           if (diag_tile && tid < BK / 2) cp_async16(zs + buf * BK + 2 * tid, zw + k0 + 2 * tid);
           cp_async_commit();
         };
-        if (ktiles > 0) load_slab(0, 0);
+        if (ktiles > 0) load_slab(0);
+        if (ktiles > 1) load_slab(1);
         for (int t = 0; t < ktiles; ++t) {
-          const int buf = t & 1;
-          if (t + 1 < ktiles) { load_slab(t + 1, buf ^ 1); cp_async_wait<1>(); } else cp_async_wait<0>();
-          __syncthreads();
-          const double* as = As + buf * BK * TB;
-          const double* bs = Bs + buf * BK * TB;
+          const int buf = t % NBUF;
+          if (t + 1 < ktiles) cp_async_wait<1>(); else cp_async_wait<0>();
+          __syncthreads();                       // slab t has landed for everyone; buffer (t + 2) % 3 is no longer read
+          if (t + 2 < ktiles) load_slab(t + 2);
+          const double* as = As + buf * SLAB + wr * 64 + lg;
+          const double* bs = Bs + buf * SLAB + wc * 32 + lg;
 #pragma unroll
-          for (int kk = 0; kk < BK; ++kk) {
-            double av[8], bv[8];
+          for (int k4 = 0; k4 < BK; k4 += 4) {
+            double av[8], bv[4];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const double2 x2 = *reinterpret_cast<const double2*>(as + kk * TB + ty * 2 + 32 * j);
-              const double2 y2 = *reinterpret_cast<const double2*>(bs + kk * TB + tx * 2 + 32 * j);
-              av[2 * j] = x2.x; av[2 * j + 1] = x2.y; bv[2 * j] = y2.x; bv[2 * j + 1] = y2.y;
-            }
+            for (int i = 0; i < 8; ++i) av[i] = as[(k4 + lk) * SP + i * 8];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) bv[j] = bs[(k4 + lk) * SP + j * 8];
 #pragma unroll
             for (int i = 0; i < 8; ++i)
 #pragma unroll
-              for (int j = 0; j < 8; ++j) acc[i][j] = fma(av[i], bv[j], acc[i][j]);
+              for (int j = 0; j < 4; ++j)
+                asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+                             : "+d"(acc[i][j][0]), "+d"(acc[i][j][1]) : "d"(av[i]), "d"(bv[j]));
           }
           if (diag_tile && tid < TB) {
             const double* zb = zs + buf * BK;
+            const double* bcol = Bs + buf * SLAB + tid;
 #pragma unroll
-            for (int kk = 0; kk < BK; ++kk) yacc = fma(zb[kk], bs[kk * TB + tid], yacc);
+            for (int kk = 0; kk < BK; ++kk) yacc = fma(zb[kk], bcol[kk * SP], yacc);
           }
-          __syncthreads();
         }
         if (diag_tile && tid < TB) yacc_s[tid] = yacc;   // parked outside the region the tile is about to overwrite
+        __syncthreads();                                  // the operand buffers become the tile
 
         // ---- epilogue: tile = C(I,J) - acc, into shared memory (column-major, pitch CP) ----
         {
@@ -182,23 +194,23 @@ extern "C" __global__ void __launch_bounds__(256, 1) gpr_chol(const __grid_const
           int gr[8], gc[8];
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
-            gr[i] = I * TB + ty * 2 + 32 * (i >> 1) + (i & 1);
-            gc[i] = J * TB + tx * 2 + 32 * (i >> 1) + (i & 1);
+            gr[i] = I * TB + wr * 64 + i * 8 + lg;
+            gc[i] = J * TB + wc * 32 + (i >> 1) * 8 + 2 * lk + (i & 1);
             xr[i] = gr[i] < n ? x[gr[i]] : 0.0;
             xc[i] = gc[i] < n ? x[gc[i]] : 0.0;
           }
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
-            const int r = ty * 2 + 32 * (i >> 1) + (i & 1);
+            const int r = wr * 64 + i * 8 + lg;
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
-              const int c = tx * 2 + 32 * (j >> 1) + (j & 1);
+              const int c = wc * 32 + (j >> 1) * 8 + 2 * lk + (j & 1);
               double kv;
               if (gr[i] < n && gc[j] < n) {
                 // the upper half of a diagonal tile is never read
                 kv = (!diag_tile || r >= c) ? cov_entry(xr[i], xc[j], lsv, den, gr[i] == gc[j]) : 0.0;
               } else kv = gr[i] == gc[j] ? 1.0 : 0.0;
-              Cs[c * CP + r] = kv - acc[i][j];
+              Cs[c * CP + r] = kv - acc[i][j >> 1][j & 1];
             }
           }
         }

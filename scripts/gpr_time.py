@@ -13,3 +13,7 @@ for C in [int(v) for v in (sys.argv[2:] or [148, 592])]:
     t0 = time.perf_counter(); lp = s.chains.logp(); dt = time.perf_counter() - t0
     fl = C * n ** 3 / 3
     print(f"n={n} chains={C}: {dt * 1e3:.1f} ms per evaluation of all chains, {C / dt:.0f} Cholesky/s, {fl / dt / 1e12:.2f} TFLOP/s fp64 (n^3/3), finite={np.isfinite(lp).all()}", flush=True)
+    pr = s.chains.get_state("prof").reshape(-1, 8)[:min(C, 148), :5]
+    tot = pr.sum(axis=1).mean()
+    print("   phase shares (thread 0 clocks, mean over CTAs): " + ", ".join(f"{nm} {100 * pr[:, k].mean() / tot:.1f}%" for k, nm in
+          enumerate(("product", "epilogue (covariance)", "diagonal factor", "solve", "store"))) + f"; {tot / 1.965e6 / max(1, C // 148):.2f} ms per matrix at 1965 MHz", flush=True)

@@ -39,6 +39,7 @@ using namespace stk;
 #define F_LPN 5
 #define F_A 6
 #define F_ZW 7
+#define F_PROF 8
 #define P_RW 0
 
 #define TB 128                 // tile edge
@@ -50,9 +51,9 @@ using namespace stk;
 #define SLAB (BK * SP)
 #define SM_TILE (TB * CP)      // doubles; aliases the operand buffers (2 * NBUF * SLAB = 13056 doubles)
 static_assert(2 * NBUF * SLAB <= SM_TILE, "operand buffers must fit in the tile region");
-#define SM_LS (TB * (TB + 1) / 2)
-#define GPR_SMEM 202624         // (SM_TILE + SM_LS + NBUF BK + 4 TB) doubles
-static_assert(GPR_SMEM == (SM_TILE + SM_LS + NBUF * BK + 4 * TB) * 8, "descriptor smem size");
+#define SM_LS 8320             // k-major factor of the diagonal tile, rows padded to an even start: lt_off(128)
+#define GPR_SMEM 204160         // (SM_TILE + SM_LS + NBUF BK + 5 TB) doubles
+static_assert(GPR_SMEM == (SM_TILE + SM_LS + NBUF * BK + 5 * TB) * 8, "descriptor smem size");
 #define STRINGIFY(x) #x
 #define STR(x) STRINGIFY(x)
 
@@ -68,6 +69,7 @@ extern "C" __device__ const char stk_desc[] =
     "field lpn state f64 1\n"
     "field A work f64 sms*@x^128*@x^128\n"
     "field zw work f64 sms*@x^128\n"
+    "field prof work f64 sms*8\n"
     "param rw 0.1\n"
     "record q\n"
     "plan logp logp -\n"
@@ -79,6 +81,8 @@ extern "C" __device__ const char stk_desc[] =
     "stage mh post gpr_accept 128 chains/128 1 0\n";
 
 __device__ __forceinline__ long long ld_of(long long n) { return (n + TB - 1) / TB * TB; }
+// offset of row k of the k-major factor copy: rows 2m and 2m + 1 both start at column 2m (128 - 2m entries each)
+__device__ __forceinline__ int lt_off(int k) { const int m = k >> 1; return 258 * m - 2 * m * m + (k & 1) * (TB - 2 * m); }
 
 __device__ __forceinline__ void cp_async16(void* dst, const void* src) {
   const unsigned d = (unsigned)__cvta_generic_to_shared(dst);
@@ -88,9 +92,10 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N)); }
 
-// covariance entry (kernelSE' with the expanded squared distance; no contraction, as the reference's Eigen expression)
-__device__ __forceinline__ double cov_entry(double xi, double xj, double lsv, double den, bool diag) {
-  const double d2 = __dsub_rn(__dadd_rn(__dmul_rn(xi, xi), __dmul_rn(xj, xj)), __dmul_rn(2.0, __dmul_rn(xi, xj)));
+// covariance entry (kernelSE' with the expanded squared distance; no contraction, as the reference's Eigen expression);
+// sq = x^2 precomputed per row / column; d2 / den stays a division, as the reference's expression has it
+__device__ __forceinline__ double cov_entry(double xi, double xj, double sqi, double sqj, double lsv, double den, bool diag) {
+  const double d2 = __dsub_rn(__dadd_rn(sqi, sqj), __dmul_rn(2.0, __dmul_rn(xi, xj)));
   const double v = exp(__dsub_rn(lsv, __ddiv_rn(d2, den)));
   return diag ? __dadd_rn(v, 0.01) : v;
 }
@@ -104,12 +109,13 @@ extern "C" __global__ void __launch_bounds__(256, 1) gpr_chol(const __grid_const
   double* Cs = sm;                          // [TB][CP] finished tile, column-major; during the product: operand buffers
   double* As = sm;                          // [NBUF][BK][SP]
   double* Bs = sm + NBUF * SLAB;            // [NBUF][BK][SP]
-  double* Ls = sm + SM_TILE;                // packed factor of the current diagonal tile: L[c][k] at c(c+1)/2 + k
+  double* Ls = sm + SM_TILE;                // factor of the current diagonal tile, k-major: L[c][k] at lt_off(k) + c - (k & ~1)
   double* zs = Ls + SM_LS;                  // [NBUF][BK] slab of z
   double* lcol = zs + NBUF * BK;            // [TB] scaled pivot column
   double* ss = lcol + TB;                   // [TB] running right-hand side of the y row
   double* zout = ss + TB;                   // [TB] solved z of this block
   double* yacc_s = zout + TB;               // [TB] dot products of the y row with the finished columns
+  double* rdiag = yacc_s + TB;              // [TB] reciprocal diagonal of the current diagonal tile's factor
 
   const long long n = a.flen[F_X], ld = ld_of(n), C = a.n_chains;
   const int T = (int)(ld / TB);
@@ -122,6 +128,8 @@ extern "C" __global__ void __launch_bounds__(256, 1) gpr_chol(const __grid_const
   double* zw = (double*)a.field[F_ZW] + (long long)blockIdx.x * ld;
   double* out = a.stage_kind == 4 ? a.out_lp : (double*)a.field[a.stage_kind == 0 ? F_LP : F_LPN];
 
+  // phase clocks of thread 0 (cycles, summed over the launch): product, epilogue, diagonal factor, solve, store
+  long long tk[5] = {0, 0, 0, 0, 0};
   for (long long chain = blockIdx.x; chain < C; chain += gridDim.x) {
     const double lsv = Q[chain], lls2 = Q[C + chain];
     const double den = __dmul_rn(2.0, exp(lls2));
@@ -136,6 +144,7 @@ extern "C" __global__ void __launch_bounds__(256, 1) gpr_chol(const __grid_const
         // mma.sync.m8n8k4.f64 (DMMA): a warp owns 64 rows x 32 columns = 8 x 4 fragments (64 accumulators per lane);
         // lane l holds A[l/4][l%4], B[l%4][l/4], C[l/4][2 (l%4) + {0,1}].  Three slab buffers, ONE barrier per slab.
         double acc[8][4][2];
+        const long long t_a = clock64();
 #pragma unroll
         for (int i = 0; i < 8; ++i)
 #pragma unroll
@@ -187,10 +196,11 @@ extern "C" __global__ void __launch_bounds__(256, 1) gpr_chol(const __grid_const
         }
         if (diag_tile && tid < TB) yacc_s[tid] = yacc;   // parked outside the region the tile is about to overwrite
         __syncthreads();                                  // the operand buffers become the tile
+        const long long t_b = clock64();
 
         // ---- epilogue: tile = C(I,J) - acc, into shared memory (column-major, pitch CP) ----
         {
-          double xr[8], xc[8];
+          double xr[8], xc[8], sr[8], sc[8];
           int gr[8], gc[8];
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
@@ -198,6 +208,8 @@ extern "C" __global__ void __launch_bounds__(256, 1) gpr_chol(const __grid_const
             gc[i] = J * TB + wc * 32 + (i >> 1) * 8 + 2 * lk + (i & 1);
             xr[i] = gr[i] < n ? x[gr[i]] : 0.0;
             xc[i] = gc[i] < n ? x[gc[i]] : 0.0;
+            sr[i] = __dmul_rn(xr[i], xr[i]);
+            sc[i] = __dmul_rn(xc[i], xc[i]);
           }
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
@@ -208,13 +220,14 @@ extern "C" __global__ void __launch_bounds__(256, 1) gpr_chol(const __grid_const
               double kv;
               if (gr[i] < n && gc[j] < n) {
                 // the upper half of a diagonal tile is never read
-                kv = (!diag_tile || r >= c) ? cov_entry(xr[i], xc[j], lsv, den, gr[i] == gc[j]) : 0.0;
+                kv = (!diag_tile || r >= c) ? cov_entry(xr[i], xc[j], sr[i], sc[j], lsv, den, gr[i] == gc[j]) : 0.0;
               } else kv = gr[i] == gc[j] ? 1.0 : 0.0;
               Cs[c * CP + r] = kv - acc[i][j >> 1][j & 1];
             }
           }
         }
         __syncthreads();
+        const long long t_c = clock64();
 
         if (diag_tile) {
           // ---- factor the tile in place; the y row rides along: ss = y_J - (dot products), z_j = ss_j / L_jj ----
@@ -228,11 +241,10 @@ extern "C" __global__ void __launch_bounds__(256, 1) gpr_chol(const __grid_const
             const double piv = Cs[j * CP + j];
             if (!(piv > 0.0)) bad = true;
             const double dj = sqrt(piv);
-            const double zj = ss[j] / dj;
-            logdet += log(dj);
-            quad = fma(zj, zj, quad);
+            const double rd = 1.0 / dj;           // one reciprocal on the critical path of a column instead of two divisions
+            const double zj = ss[j] * rd;
             if (h == 0) {
-              if (r > j) { const double l = Cs[j * CP + r] / dj; Cs[j * CP + r] = l; lcol[r] = l; }
+              if (r > j) { const double l = Cs[j * CP + r] * rd; Cs[j * CP + r] = l; lcol[r] = l; }
               else if (r == j) zout[j] = zj;
             }
             __syncthreads();
@@ -240,45 +252,73 @@ extern "C" __global__ void __launch_bounds__(256, 1) gpr_chol(const __grid_const
             if (r > j) {
               const double lr = lcol[r];
               if (h == 1) ss[r] = fma(-lr, zj, ss[r]);
-              for (int c = j + 1 + h; c <= r; c += 2) Cs[c * CP + r] = fma(-lr, lcol[c], Cs[c * CP + r]);
+              // rank-1 update of this thread's row, every second column; four columns in flight (loads, then stores)
+              int c = j + 1 + h;
+              for (; c + 6 <= r; c += 8) {
+                const double l0 = lcol[c], l1 = lcol[c + 2], l2 = lcol[c + 4], l3 = lcol[c + 6];
+                const double v0 = Cs[c * CP + r], v1 = Cs[(c + 2) * CP + r], v2 = Cs[(c + 4) * CP + r], v3 = Cs[(c + 6) * CP + r];
+                Cs[c * CP + r] = fma(-lr, l0, v0); Cs[(c + 2) * CP + r] = fma(-lr, l1, v1);
+                Cs[(c + 4) * CP + r] = fma(-lr, l2, v2); Cs[(c + 6) * CP + r] = fma(-lr, l3, v3);
+              }
+              for (; c <= r; c += 2) Cs[c * CP + r] = fma(-lr, lcol[c], Cs[c * CP + r]);
             }
           }
           __syncthreads();
-          // packed copy of the factor for the solves of this block column; z of this block to the CTA's z vector
+          // k-major copy of the factor for the solves of this block column (row k holds L[c][k] for c >= k & ~1, so that
+          // an aligned 16-byte broadcast load gives two columns), reciprocal diagonal, log of the diagonal; z of this
+          // block to the CTA's z vector
           for (int e = tid; e < TB * TB; e += 256) {
-            const int c = e >> 7, k = e & (TB - 1);
-            if (k <= c) Ls[c * (c + 1) / 2 + k] = Cs[k * CP + c];
+            const int k = e >> 7, c = e & (TB - 1);
+            if (c >= k) Ls[lt_off(k) + c - (k & ~1)] = Cs[k * CP + c];
           }
-          if (tid < TB) zw[(long long)J * TB + tid] = zout[tid];
+          if (tid < TB) {
+            const double d = Cs[tid * CP + tid];
+            rdiag[tid] = 1.0 / d;
+            lcol[tid] = log(d);
+            zw[(long long)J * TB + tid] = zout[tid];
+          }
           __syncthreads();
+          if (tid == 0)
+            for (int j = 0; j < TB; ++j) { logdet += lcol[j]; quad = fma(zout[j], zout[j], quad); }
+          tk[2] += clock64() - t_c;
         } else {
-          // ---- X L_JJ^T = tile: a row per thread, four columns at a time; the solved tile goes to the factor ----
+          // ---- X L_JJ^T = tile: a row per thread, eight columns at a time; the solved tile goes to the factor ----
           if (tid < TB) {
             const int r = tid;
-            for (int cb = 0; cb < TB; cb += 4) {
-              double s0 = Cs[(cb + 0) * CP + r], s1 = Cs[(cb + 1) * CP + r], s2 = Cs[(cb + 2) * CP + r], s3 = Cs[(cb + 3) * CP + r];
-              const double* l0 = Ls + (cb + 0) * (cb + 1) / 2;
-              const double* l1 = Ls + (cb + 1) * (cb + 2) / 2;
-              const double* l2 = Ls + (cb + 2) * (cb + 3) / 2;
-              const double* l3 = Ls + (cb + 3) * (cb + 4) / 2;
+            for (int cb = 0; cb < TB; cb += 8) {
+              double sv[8];
+#pragma unroll
+              for (int e = 0; e < 8; ++e) sv[e] = Cs[(cb + e) * CP + r];
+              const double* lrow = Ls + cb;        // row k of the k-major factor, indexed by column: lrow[c - cb]
+#pragma unroll 4
               for (int k = 0; k < cb; ++k) {
                 const double v = Cs[k * CP + r];
-                s0 = fma(-v, l0[k], s0); s1 = fma(-v, l1[k], s1); s2 = fma(-v, l2[k], s2); s3 = fma(-v, l3[k], s3);
+                const double2 l01 = *reinterpret_cast<const double2*>(lrow), l23 = *reinterpret_cast<const double2*>(lrow + 2);
+                const double2 l45 = *reinterpret_cast<const double2*>(lrow + 4), l67 = *reinterpret_cast<const double2*>(lrow + 6);
+                sv[0] = fma(-v, l01.x, sv[0]); sv[1] = fma(-v, l01.y, sv[1]); sv[2] = fma(-v, l23.x, sv[2]); sv[3] = fma(-v, l23.y, sv[3]);
+                sv[4] = fma(-v, l45.x, sv[4]); sv[5] = fma(-v, l45.y, sv[5]); sv[6] = fma(-v, l67.x, sv[6]); sv[7] = fma(-v, l67.y, sv[7]);
+                lrow += TB - ((k + 1) & ~1);
               }
-              s0 = s0 / l0[cb];
-              s1 = fma(-s0, l1[cb], s1) / l1[cb + 1];
-              s2 = fma(-s1, l2[cb + 1], fma(-s0, l2[cb], s2)) / l2[cb + 2];
-              s3 = fma(-s2, l3[cb + 2], fma(-s1, l3[cb + 1], fma(-s0, l3[cb], s3))) / l3[cb + 3];
-              Cs[(cb + 0) * CP + r] = s0; Cs[(cb + 1) * CP + r] = s1; Cs[(cb + 2) * CP + r] = s2; Cs[(cb + 3) * CP + r] = s3;
+#pragma unroll
+              for (int e = 0; e < 8; ++e) {
+#pragma unroll
+                for (int f = 0; f < e; ++f) sv[e] = fma(-sv[f], Ls[lt_off(cb + f) + e - (f & ~1)], sv[e]);
+                sv[e] *= rdiag[cb + e];
+              }
+#pragma unroll
+              for (int e = 0; e < 8; ++e) Cs[(cb + e) * CP + r] = sv[e];
             }
           }
           __syncthreads();
+          const long long t_d = clock64();
           for (int e = tid; e < TB * TB; e += 256) {
             const int c = e >> 7, r = e & (TB - 1);
             A[((long long)J * TB + c) * ld + (long long)I * TB + r] = Cs[c * CP + r];
           }
           __syncthreads();   // the tile (= the operand buffers) is free again, the factor is visible to the CTA
+          tk[3] += t_d - t_c; tk[4] += clock64() - t_d;
         }
+        tk[0] += t_b - t_a; tk[1] += t_c - t_b;
       }
     }
     if (tid == 0) {
@@ -287,6 +327,10 @@ extern "C" __global__ void __launch_bounds__(256, 1) gpr_chol(const __grid_const
       lp += normal_lpdf(lls2, log(100.0), 2.0);
       out[chain] = bad ? __longlong_as_double(0x7ff8000000000000ULL) : lp;
     }
+  }
+  if (tid == 0) {
+    double* prof = (double*)a.field[F_PROF] + (long long)blockIdx.x * 8;
+    for (int k = 0; k < 5; ++k) prof[k] = (double)tk[k];
   }
 }
 

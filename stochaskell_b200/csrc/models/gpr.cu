@@ -52,8 +52,8 @@ using namespace stk;
 #define SM_TILE (TB * CP)      // doubles; aliases the operand buffers (2 * NBUF * SLAB = 13056 doubles)
 static_assert(2 * NBUF * SLAB <= SM_TILE, "operand buffers must fit in the tile region");
 #define SM_LS 8320             // k-major factor of the diagonal tile, rows padded to an even start: lt_off(128)
-#define GPR_SMEM 204160         // (SM_TILE + SM_LS + NBUF BK + 5 TB) doubles
-static_assert(GPR_SMEM == (SM_TILE + SM_LS + NBUF * BK + 5 * TB) * 8, "descriptor smem size");
+#define GPR_SMEM 212352         // (SM_TILE + SM_LS + NBUF BK + 13 TB) doubles
+static_assert(GPR_SMEM == (SM_TILE + SM_LS + NBUF * BK + 13 * TB) * 8, "descriptor smem size");
 #define STRINGIFY(x) #x
 #define STR(x) STRINGIFY(x)
 
@@ -116,6 +116,7 @@ extern "C" __global__ void __launch_bounds__(256, 1) gpr_chol(const __grid_const
   double* zout = ss + TB;                   // [TB] solved z of this block
   double* yacc_s = zout + TB;               // [TB] dot products of the y row with the finished columns
   double* rdiag = yacc_s + TB;              // [TB] reciprocal diagonal of the current diagonal tile's factor
+  double* part = rdiag + TB;                // [8][TB] partial sums of the odd-k half of a solve
 
   const long long n = a.flen[F_X], ld = ld_of(n), C = a.n_chains;
   const int T = (int)(ld / TB);
@@ -283,30 +284,40 @@ extern "C" __global__ void __launch_bounds__(256, 1) gpr_chol(const __grid_const
           tk[2] += clock64() - t_c;
         } else {
           // ---- X L_JJ^T = tile: a row per thread, eight columns at a time; the solved tile goes to the factor ----
-          if (tid < TB) {
-            const int r = tid;
+          // all eight warps: threads (r, 0) and (r, 1) share row r, taking the even / the odd k of the running sums
+          {
+            const int r = tid & (TB - 1), h = tid >> 7;
             for (int cb = 0; cb < TB; cb += 8) {
               double sv[8];
 #pragma unroll
-              for (int e = 0; e < 8; ++e) sv[e] = Cs[(cb + e) * CP + r];
-              const double* lrow = Ls + cb;        // row k of the k-major factor, indexed by column: lrow[c - cb]
+              for (int e = 0; e < 8; ++e) sv[e] = h == 0 ? Cs[(cb + e) * CP + r] : 0.0;
+              const double* lrow = Ls + cb + h * TB;   // row k = h of the k-major factor, indexed by column
 #pragma unroll 4
-              for (int k = 0; k < cb; ++k) {
+              for (int k = h; k < cb; k += 2) {
                 const double v = Cs[k * CP + r];
                 const double2 l01 = *reinterpret_cast<const double2*>(lrow), l23 = *reinterpret_cast<const double2*>(lrow + 2);
                 const double2 l45 = *reinterpret_cast<const double2*>(lrow + 4), l67 = *reinterpret_cast<const double2*>(lrow + 6);
                 sv[0] = fma(-v, l01.x, sv[0]); sv[1] = fma(-v, l01.y, sv[1]); sv[2] = fma(-v, l23.x, sv[2]); sv[3] = fma(-v, l23.y, sv[3]);
                 sv[4] = fma(-v, l45.x, sv[4]); sv[5] = fma(-v, l45.y, sv[5]); sv[6] = fma(-v, l67.x, sv[6]); sv[7] = fma(-v, l67.y, sv[7]);
-                lrow += TB - ((k + 1) & ~1);
+                lrow += 2 * TB - 2 - 2 * k;            // rows k and k + 1 of the padded k-major layout
               }
+              if (h == 1) {
 #pragma unroll
-              for (int e = 0; e < 8; ++e) {
-#pragma unroll
-                for (int f = 0; f < e; ++f) sv[e] = fma(-sv[f], Ls[lt_off(cb + f) + e - (f & ~1)], sv[e]);
-                sv[e] *= rdiag[cb + e];
+                for (int e = 0; e < 8; ++e) part[e * TB + r] = sv[e];
               }
+              __syncthreads();
+              if (h == 0) {
 #pragma unroll
-              for (int e = 0; e < 8; ++e) Cs[(cb + e) * CP + r] = sv[e];
+                for (int e = 0; e < 8; ++e) {
+                  sv[e] += part[e * TB + r];
+#pragma unroll
+                  for (int f = 0; f < e; ++f) sv[e] = fma(-sv[f], Ls[lt_off(cb + f) + e - (f & ~1)], sv[e]);
+                  sv[e] *= rdiag[cb + e];
+                }
+#pragma unroll
+                for (int e = 0; e < 8; ++e) Cs[(cb + e) * CP + r] = sv[e];
+              }
+              __syncthreads();
             }
           }
           __syncthreads();

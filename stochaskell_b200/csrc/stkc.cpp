@@ -788,15 +788,9 @@ struct Gen {
     for (auto& r : b.rets) need(r);
   }
 
-  void pnode(const PNode& q) {
-    int level, ptr; id_level_ptr(q.id, &level, &ptr);
-    std::string slot = std::to_string(256 * level + 16 * ptr) + "u";
-    if (q.k == PNode::Switch) { switch_node(q); return; }
-    if (q.k == PNode::Loop) die("joint (Loop) PNodes are not supported by the CUDA lowering yet");
-    for (auto& a : q.args) need(a);
+  // the sampler call of a Dist PNode on the generator variable `g` (ccPNode, CC.hs:276-297)
+  std::string draw_expr(const PNode& q, const std::string& g) {
     auto arg = [&](size_t i, bool real = true) { return rv(q.args.at(i), real); };
-    std::string g = fresh("g");
-    line("stk::Rng " + g + " = rng; " + g + ".slot = " + slot + ";");
     const std::string& f = q.dist;
     std::string e;
     if (f == "normal") e = "stk::draw_normal(" + g + ", " + arg(0) + ", " + arg(1) + ")";                 // CC.hs:278
@@ -821,6 +815,48 @@ struct Gen {
       line("const double " + tab + "[] = {" + init + "};");
       e = "stk::draw_pmf(" + g + ", " + tab + ", " + std::to_string(ps->args.size()) + ")";
     } else die("distribution `" + f + "` is not supported by the CUDA lowering");
+    return e;
+  }
+
+  // joint (Loop) PNode (ccPNode (Loop ..), CC.hs:299-302: for-loops around the element's DAG and draw; samplePNode,
+  // Program.hs:1171-1181): the elements are drawn in index order into per-thread storage; element k (0-based) of the
+  // PNode with slot s uses Philox slot s + (k + 1) * 2^16, so every element has its own counter range and the stream
+  // does not depend on the order of evaluation.
+  void loop_node(const PNode& q, const std::string& slot) {
+    if (q.params.size() != 1) die("multi-dimensional joint (Loop) PNodes are not supported by the CUDA lowering");
+    const PNode& in = *q.inner;
+    if (in.k != PNode::Dist || !in.type.scalar()) die("joint (Loop) over a non-scalar distribution is not supported");
+    need(q.shape[0].first); need(q.shape[0].second);
+    need_body(*q.lam);
+    for (auto& a : in.args) need(a);
+    bool real = in.type.k == Type::R;
+    std::string buf = fresh(q.id + "_buf"), lo = fresh("lo"), hi = fresh("hi");
+    decls << "  " << (real ? "double" : "int") << " " << buf << "[STK_VECCAP];\n";
+    line("const int " + lo + " = " + rv(q.shape[0].first) + ";");
+    line("const int " + hi + " = min(" + rv(q.shape[0].second) + ", " + lo + " + STK_VECCAP - 1);");
+    const std::string& iv = q.params[0];
+    line("for (int " + iv + " = " + lo + "; " + iv + " <= " + hi + "; ++" + iv + ") {");
+    ind += 2; push();
+    Val v; v.type = scalarT(Type::Z); v.expr = iv; bind(iv, v);
+    for (const Def& d : q.lam->defs) def(d);
+    std::string g = fresh("g");
+    line("stk::Rng " + g + " = rng; " + g + ".slot = " + slot + " + ((unsigned)(" + iv + " - " + lo + " + 1) << 16);");
+    line(buf + "[" + iv + " - " + lo + "] = " + draw_expr(in, g) + ";");
+    pop(); ind -= 2; line("}");
+    Type vt = vecT(in.type);
+    line("const " + ctype(vt) + " " + q.id + "(" + buf + ", 1, " + hi + " < " + lo + " ? 0 : " + hi + " - " + lo + " + 1);");
+    Val r; r.type = vt; r.expr = q.id; bind(q.id, r);
+  }
+
+  void pnode(const PNode& q) {
+    int level, ptr; id_level_ptr(q.id, &level, &ptr);
+    std::string slot = std::to_string(256 * level + 16 * ptr) + "u";
+    if (q.k == PNode::Switch) { switch_node(q); return; }
+    if (q.k == PNode::Loop) { loop_node(q, slot); return; }
+    for (auto& a : q.args) need(a);
+    std::string g = fresh("g");
+    line("stk::Rng " + g + " = rng; " + g + ".slot = " + slot + ";");
+    std::string e = draw_expr(q, g);
     if (!q.type.scalar()) die("draw of type " + q.type.str() + " is not supported");
     line("const " + ctype(q.type) + " " + q.id + " = " + e + ";");
     Val v; v.type = q.type; v.expr = q.id; bind(q.id, v);
@@ -992,6 +1028,13 @@ static std::string generate(const std::string& ir, const std::string& input_type
       } else feed << "    " << in_names[k] << " = " << nx << ";\n";
     } else {
       std::string nm = "out" + std::to_string(k);
+      if (rt.k == Type::Vec && rt.sub[0].scalar()) {   // a joint's draws: [veccap][chains] + the length
+        bool i32 = rt.sub[0].k != Type::R;
+        out_fields.push_back({nm, i32, std::to_string(veccap)}); out_fields.push_back({nm + "_len", true, "1"});
+        g.line("store_vec(" + g.rv(prog.rets[k]) + ", (" + (i32 ? "int" : "double") + "*)a.field[F_" + nm + "] + chain, a.n_chains, " + std::to_string(veccap) +
+               ", (int*)a.field[F_" + nm + "_len] + chain);");
+        continue;
+      }
       if (!rt.scalar()) die("simulate: return of type " + rt.str() + " is not supported");
       out_fields.push_back({nm, rt.k != Type::R, "1"});
       g.line("((" + std::string(rt.k != Type::R ? "int" : "double") + "*)a.field[F_" + nm + "])[chain] = " + g.rv(prog.rets[k], rt.k == Type::R) + ";");

@@ -10,7 +10,9 @@ from stochaskell_b200 import StkError, compile_source, ir_to_cuda
 
 IR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ir")
 SOCCER_T = "Union[(R, ZVec), (R, R, ZVec)]"
-CASES = {"soccer_rj": [SOCCER_T], "mh_sym": ["R"], "mh_asym": ["R"], "solve_case": [], "tom": []}
+CASES = {"soccer_rj": [SOCCER_T], "mh_sym": ["R"], "mh_asym": ["R"], "solve_case": [], "tom": [],
+         # joint (Loop) PNodes: hand-written in the shape `Show PNode` prints (Program.hs:142-145) — no notebook preserves one
+         "joint_sim": [], "joint_rw": ["RVec"]}
 
 
 def ir(name):
@@ -25,6 +27,19 @@ def test_notebook_ir_lowers_and_compiles(name, tmp_path):
     assert ("entry simulate stk_ir_simulate" in src) == (not CASES[name])
     cubin = compile_source(src, str(tmp_path))
     assert os.path.getsize(cubin) > 2000
+
+
+def test_joint_lowers_to_a_loop_with_its_own_philox_slots():
+    """ccPNode (Loop ..) (CC.hs:299-302): a for-loop around the element's DAG and draw; element k uses slot s + (k+1) 2^16"""
+    src = ir_to_cuda(ir("joint_sim"), [], veccap=8)
+    assert "for (int i_1_0 = lo_" in src and "<< 16)" in src
+    assert "x_sim_0_2_buf" in src and "= stk::draw_normal(g_" in src and "= stk::draw_poisson(g_" in src
+    assert "field out1 state f64 8" in src and "field out1_len state i32 1" in src and "field out2 state i32 8" in src
+    k = ir_to_cuda(ir("joint_rw"), ["RVec"])
+    assert "assign_vec(i_0_0, nx0" in k and "stk::draw_normal(g_" in k
+    with pytest.raises(StkError) as e:
+        ir_to_cuda(ir("joint_sim").replace("| i_1_0 <- 1...6 ]", "| i_1_0 <- 1...6, i_1_1 <- 1...2 ]"), [])
+    assert e.value.code == -5
 
 
 def test_soccer_lowering_follows_the_reference_templates():

@@ -151,10 +151,10 @@ struct Node {
 };
 struct Def { std::string id; Node node; };
 struct PNode {
-  enum K { Dist, Switch, Loop } k = Dist;
+  enum K { Dist, Switch, Loop, Chain } k = Dist;
   std::string id, dist;
-  std::vector<RefP> args;     // Dist args; Switch: head
-  std::vector<Alt> alts;      // Switch
+  std::vector<RefP> args;     // Dist args; Switch: head; Chain: lo, hi, initial state
+  std::vector<Alt> alts;      // Switch; Chain: one alternative, inputs = index and carried state
   std::vector<std::string> params; std::vector<std::pair<RefP, RefP>> shape; std::shared_ptr<PNode> inner; std::shared_ptr<Body> lam;  // Loop
   Type type;
 };
@@ -275,8 +275,8 @@ struct Parser {
     if (accept("do")) {
       while (!is("return")) b.pnodes.push_back(pnode());
       expect("return");
-      expect("[");
-      if (!accept("]")) { do b.rets.push_back(ref()); while (accept(",")); expect("]"); }
+      if (accept("[")) { if (!accept("]")) { do b.rets.push_back(ref()); while (accept(",")); expect("]"); } }
+      else b.rets.push_back(ref());                  // a Chain body returns one NodeRef, printed bare
     } else if (list_rets && is("[")) {
       next();
       if (!accept("]")) { do b.rets.push_back(ref()); while (accept(",")); expect("]"); }
@@ -375,8 +375,17 @@ struct Parser {
       dist(q.inner.get());
       expect("|"); array_params(&q.params, &q.shape); expect("]");
       expect("::"); q.type = type();
-    } else if (is("chain") || is("unfoldP") || is("foldP") || is("AnamorphismP") || is("CatamorphismP")) {
-      fail("Chain / RecursionScheme PNodes are not supported by the CUDA lowering");
+    } else if (accept("chain")) {                      // chain (lo,hi) x0 $ \i j -> [let .. in] do .. return r   (Program.hs:154-157)
+      q.k = PNode::Chain;
+      expect("("); q.args.push_back(ref()); expect(","); q.args.push_back(ref()); expect(")");
+      q.args.push_back(ref());
+      expect("$"); expect("\\");
+      Alt a; a.inputs.push_back(next().s); a.inputs.push_back(next().s);
+      expect("->");
+      a.body = body(false);
+      q.alts.push_back(std::move(a));
+    } else if (is("unfoldP") || is("foldP") || is("AnamorphismP") || is("CatamorphismP")) {
+      fail("RecursionScheme PNodes are not supported by the CUDA lowering");
     } else {
       dist(&q);
     }
@@ -840,7 +849,7 @@ struct Gen {
     Val v; v.type = scalarT(Type::Z); v.expr = iv; bind(iv, v);
     for (const Def& d : q.lam->defs) def(d);
     std::string g = fresh("g");
-    line("stk::Rng " + g + " = rng; " + g + ".slot = " + slot + " + ((unsigned)(" + iv + " - " + lo + " + 1) << 16);");
+    line("stk::Rng " + g + " = " + rng_name + "; " + g + ".slot = " + slot + " + ((unsigned)(" + iv + " - " + lo + " + 1) << 16);");
     line(buf + "[" + iv + " - " + lo + "] = " + draw_expr(in, g) + ";");
     pop(); ind -= 2; line("}");
     Type vt = vecT(in.type);
@@ -848,14 +857,49 @@ struct Gen {
     Val r; r.type = vt; r.expr = q.id; bind(q.id, r);
   }
 
+  // Chain PNode (ccPNode (Chain ..), CC.hs:314-320: `name = x; for i in lo..hi { j = name; <body>; name = ret; }`;
+  // chainRange', Program.hs:304-316).  The body's PNodes keep their own slots; iteration k (1-based) of the chain PNode
+  // with slot s draws from a generator whose third counter word is XOR-ed with (k << 12) ^ s, i.e. from the streams of
+  // "transition step ^ (((k << 12) ^ s) << 32)": two chains of one program, and two iterations of one chain, never share
+  // a Philox block.
+  std::string rng_name = "rng";
+  void chain_node(const PNode& q) {
+    if (rng_name != "rng") die("nested chain PNodes are not supported by the CUDA lowering");
+    for (auto& a : q.args) need(a);
+    const Alt& a = q.alts.at(0);
+    Type st = type_of(q.args[2]);
+    if (!st.scalar()) die("chain carrying a state of type " + st.str() + " is not supported by the CUDA lowering");
+    bool real = st.k == Type::R;
+    need_body(a.body);
+    std::string lo = fresh("lo"), hi = fresh("hi"), rc = fresh("rngc");
+    line(ctype(st) + " " + q.id + " = " + rv(q.args[2], real) + ";");
+    line("const int " + lo + " = " + rv(q.args[0]) + ", " + hi + " = " + rv(q.args[1]) + ";");
+    const std::string &iv = a.inputs[0], &jv = a.inputs[1];
+    line("for (int " + iv + " = " + lo + "; " + iv + " <= " + hi + "; ++" + iv + ") {");
+    ind += 2; push();
+    Val v; v.type = scalarT(Type::Z); v.expr = iv; bind(iv, v);
+    line("const " + ctype(st) + " " + jv + " = " + q.id + ";");
+    Val j; j.type = st; j.expr = jv; bind(jv, j);
+    int level, ptr; id_level_ptr(q.id, &level, &ptr);
+    line("stk::Rng " + rc + " = rng; " + rc + ".c2 ^= ((unsigned)(" + iv + " - " + lo + " + 1) << 12) ^ " + std::to_string(256 * level + 16 * ptr) + "u;");
+    rng_name = rc;
+    body(a.body);
+    if (a.body.rets.size() != 1) die("chain body must return one value");
+    line(q.id + " = " + rv(a.body.rets[0], real) + ";");
+    rng_name = "rng";
+    pop(); ind -= 2; line("}");
+    Val r; r.type = st; r.expr = q.id; bind(q.id, r);
+  }
+
   void pnode(const PNode& q) {
     int level, ptr; id_level_ptr(q.id, &level, &ptr);
     std::string slot = std::to_string(256 * level + 16 * ptr) + "u";
     if (q.k == PNode::Switch) { switch_node(q); return; }
     if (q.k == PNode::Loop) { loop_node(q, slot); return; }
+    if (q.k == PNode::Chain) { chain_node(q); return; }
     for (auto& a : q.args) need(a);
     std::string g = fresh("g");
-    line("stk::Rng " + g + " = rng; " + g + ".slot = " + slot + ";");
+    line("stk::Rng " + g + " = " + rng_name + "; " + g + ".slot = " + slot + ";");
     std::string e = draw_expr(q, g);
     if (!q.type.scalar()) die("draw of type " + q.type.str() + " is not supported");
     line("const " + ctype(q.type) + " " + q.id + " = " + e + ";");

@@ -12,7 +12,7 @@ IR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ir")
 SOCCER_T = "Union[(R, ZVec), (R, R, ZVec)]"
 CASES = {"soccer_rj": [SOCCER_T], "mh_sym": ["R"], "mh_asym": ["R"], "solve_case": [], "tom": [],
          # joint (Loop) PNodes: hand-written in the shape `Show PNode` prints (Program.hs:142-145) — no notebook preserves one
-         "joint_sim": [], "joint_rw": ["RVec"]}
+         "joint_sim": [], "joint_rw": ["RVec"], "chain_rw": []}
 
 
 def ir(name):
@@ -40,6 +40,18 @@ def test_joint_lowers_to_a_loop_with_its_own_philox_slots():
     with pytest.raises(StkError) as e:
         ir_to_cuda(ir("joint_sim").replace("| i_1_0 <- 1...6 ]", "| i_1_0 <- 1...6, i_1_1 <- 1...2 ]"), [])
     assert e.value.code == -5
+
+
+def test_chain_lowers_to_a_state_carrying_loop():
+    """ccPNode (Chain ..) (CC.hs:314-320): name = x; for i in lo..hi { j = name; body; name = ret; }"""
+    src = ir_to_cuda(ir("chain_rw"), [])
+    assert "double x_sim_0_0 = 0.0;" in src and "for (int i_99_0 = lo_" in src and "const double i_99_1 = x_sim_0_0;" in src
+    assert ".c2 ^= ((unsigned)(i_99_0 - lo_" in src and "x_sim_0_0 = x_sim_1_0;" in src
+    nested = ir("chain_rw").replace("in do x_sim_1_0 <- normal i_99_1 1.0 :: P R",
+                                    "in do x_sim_1_0 <- chain (1,2) i_99_1 $ \\i_98_0 i_98_1 ->\n                  do x_sim_2_0 <- normal i_98_1 1.0 :: P R\n                     return x_sim_2_0", 1)
+    with pytest.raises(StkError) as e:
+        ir_to_cuda(nested, [])
+    assert e.value.code == -5 and "nested chain" in str(e.value)
 
 
 def test_soccer_lowering_follows_the_reference_templates():

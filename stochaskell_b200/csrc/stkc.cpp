@@ -693,23 +693,45 @@ struct Gen {
     Val v; v.type = n.type; v.expr = d.id; bind(d.id, v);
   }
 
-  // FoldScan (CC.hs:236-262): sequential loop, left/right; the list is a vector view or an inlined Array
+  // FoldScan (CC.hs:236-262): sequential loop, left/right; the list is a vector view or an inlined Array.
+  // Scans keep every partial result (interpreter semantics, Eval.hs:213-221 = Haskell's scanl / scanr: n + 1 elements,
+  // the seed first for scanl, last for scanr) in per-thread storage.  The CC template indexes `name[idx-1-1]` for a left
+  // scan (CC.hs:256-259 builds "loc-1" from the string "idx-1"), i.e. reads one element before the seed: the interpreter
+  // is the reference here.
   void fold(const Def& d) {
     const Node& n = d.node;
-    if (n.f != "foldl" && n.f != "foldr") die("scans are not supported by the CUDA lowering");
-    if (!n.type.scalar() && n.type.k != Type::Unknown) die("fold producing " + n.type.str() + " is not supported");
-    Type at = n.type.k == Type::Unknown ? type_of(n.args[0]) : n.type;
+    const bool scan = n.f == "scanl" || n.f == "scanr";
+    const bool left = n.f == "foldl" || n.f == "scanl";
+    if (n.f != "foldl" && n.f != "foldr" && !scan) die("`" + n.f + "` is not supported by the CUDA lowering");
+    Type at;
+    if (scan) {
+      if (n.type.k == Type::Vec && n.type.sub[0].scalar()) at = n.type.sub[0];
+      else if (n.type.k == Type::Unknown) at = type_of(n.args[0]);
+      else die("scan producing " + n.type.str() + " is not supported");
+    } else {
+      if (!n.type.scalar() && n.type.k != Type::Unknown) die("fold producing " + n.type.str() + " is not supported");
+      at = n.type.k == Type::Unknown ? type_of(n.args[0]) : n.type;
+    }
     bool rt = at.k == Type::R;
-    line(ctype(at) + " " + d.id + " = " + rv(n.args[0], rt) + ";");
+    const std::string cur = scan ? fresh(d.id + "_acc") : d.id;
+    line(ctype(at) + " " + cur + " = " + rv(n.args[0], rt) + ";");
     const RefP& ls = n.args[1];
     std::string it = fresh("k");
     const Node* arr = (ls->k == Ref::Var && lookup(ls->name).array) ? lookup(ls->name).array : nullptr;
-    // showNode prints the lambda inputs reversed for foldl: \acc elem
-    std::string acc = n.f == "foldl" ? n.params[0] : n.params[1], elem = n.f == "foldl" ? n.params[1] : n.params[0];
+    // showNode prints the lambda inputs reversed for a left fold / scan: \acc elem
+    std::string acc = left ? n.params[0] : n.params[1], elem = left ? n.params[1] : n.params[0];
     std::string lo, hi;
     if (arr) { if (arr->params.size() != 1) die("fold over a multi-dimensional array"); lo = rv(arr->shape[0].first); hi = rv(arr->shape[0].second); }
     else { lo = "1"; hi = rv(ls) + ".len"; }
-    if (n.f == "foldl") line("for (int " + it + " = " + lo + "; " + it + " <= " + hi + "; ++" + it + ") {");
+    std::string buf, len;
+    if (scan) {
+      buf = fresh(d.id + "_buf"); len = fresh("n");
+      decls << "  " << (rt ? "double" : "int") << " " << buf << "[STK_VECCAP];\n";
+      line("const int " + len + " = min(max((" + hi + ") - (" + lo + ") + 1, 0), STK_VECCAP - 1);");
+      hi = "(" + lo + ") + " + len + " - 1";
+      line(buf + "[" + (left ? "0" : len) + "] = " + cur + ";");
+    }
+    if (left) line("for (int " + it + " = " + lo + "; " + it + " <= " + hi + "; ++" + it + ") {");
     else line("for (int " + it + " = " + hi + "; " + it + " >= " + lo + "; --" + it + ") {");
     ind += 2; push();
     Val ev;
@@ -725,12 +747,18 @@ struct Gen {
     }
     ev.expr = elem; bind(elem, ev);
     Val av; av.type = at; av.expr = acc;
-    line("const " + ctype(at) + " " + acc + " = " + d.id + ";");
+    line("const " + ctype(at) + " " + acc + " = " + cur + ";");
     bind(acc, av);
     for (const Def& bd : n.lam->defs) def(bd);
-    line(d.id + " = " + rv(n.lam->rets[0], rt) + ";");
+    line(cur + " = " + rv(n.lam->rets[0], rt) + ";");
+    if (scan) line(buf + "[" + it + " - (" + lo + ")" + (left ? " + 1" : "") + "] = " + cur + ";");
     pop(); ind -= 2; line("}");
-    Val v; v.type = at; v.expr = d.id; bind(d.id, v);
+    Val v;
+    if (scan) {
+      v.type = vecT(at);
+      line("const " + ctype(v.type) + " " + d.id + "(" + buf + ", 1, " + len + " + 1);");
+    } else v.type = at;
+    v.expr = d.id; bind(d.id, v);
   }
 
   // Case on an integer head, alternatives 1..n (CC.hs:263-273)

@@ -12,7 +12,7 @@ IR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ir")
 SOCCER_T = "Union[(R, ZVec), (R, R, ZVec)]"
 CASES = {"soccer_rj": [SOCCER_T], "mh_sym": ["R"], "mh_asym": ["R"], "solve_case": [], "tom": [],
          # joint (Loop) PNodes: hand-written in the shape `Show PNode` prints (Program.hs:142-145) — no notebook preserves one
-         "joint_sim": [], "joint_rw": ["RVec"], "chain_rw": []}
+         "joint_sim": [], "joint_rw": ["RVec"], "chain_rw": [], "scan_sim": []}
 
 
 def ir(name):
@@ -52,6 +52,14 @@ def test_chain_lowers_to_a_state_carrying_loop():
     with pytest.raises(StkError) as e:
         ir_to_cuda(nested, [])
     assert e.value.code == -5 and "nested chain" in str(e.value)
+
+
+def test_scans_keep_every_partial_result():
+    """scanl / scanr with the interpreter's semantics (Eval.hs:213-221): n + 1 elements, seed first / last"""
+    src = ir_to_cuda(ir("scan_sim"), [], veccap=8)
+    assert "v_0_1_buf" in src and "[0] = v_0_1_acc" in src          # scanl: seed at index 0
+    assert "] = v_0_2_acc" in src and "; --k_" in src                # scanr: backwards, seed at index n
+    assert "const VecI v_0_4(" in src and "field out2 state i32 8" in src
 
 
 def test_soccer_lowering_follows_the_reference_templates():

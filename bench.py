@@ -580,7 +580,9 @@ class GPRMH:
     def roofline(self, C, T, ms_per_launch, peaks):
         tf = C * T * self.flops_per_transition / (ms_per_launch * 1e-3) / 1e12
         peak = peaks.get("bf16_tflops_sustained") or peaks.get("bf16_tflops") or 1365.0
-        return dict(bound="tensor", achieved=tf, peak=peak, unit="TFLOP/s", frac=tf / peak, traffic=None,
+        # dram__bytes_read + dram__bytes_write of one gpr_chol launch: 159 MB + 15.8 MB per matrix in the ncu capture of
+        # profiles/r01_gpr.md (592 chains), scaled to this launch's chains (the kernel is persistent: per-matrix traffic is flat)
+        return dict(bound="tensor", achieved=tf, peak=peak, unit="TFLOP/s", frac=tf / peak, traffic=int(C * (158.7e6 + 15.8e6)),
                     kernel="gpr_chol", peak_source=peaks["source"], useful_flops_per_transition_per_chain=self.flops_per_transition,
                     fp64_pipe_peak_tflops=37.0, frac_of_fp64_pipe=tf / 37.0,
                     note="useful flops = n^3/3 per chain and transition (SURVEY 8d, the Cholesky; covariance exps and the solve not "

@@ -10,20 +10,23 @@
 // Transition: random-walk Metropolis on (lsv, lls2) (the `mh` shape of mh.ipynb cell 1): slot 0 = two proposal normals,
 // slot 1 = the accept uniform; bernoulli(min 1 a) of Program.hs:1278-1283.
 //
-// B200 design: tcgen05 has no fp64 path and cond(C) ~ n e^lsv / 0.01 ~ 1e6 rules fp32 out at the 1e-10 tier, so the
-// factorisation runs on the fp64 pipe — one PERSISTENT CTA per SM, each factoring one chain's matrix at a time
-// (148 matrices in flight, the chains of a launch strided over the CTAs):
-//   * left-looking blocked Cholesky, 128 x 128 tiles: tile (I,J) = C(I,J) - sum_{k < 128 J} L[I,k] L[J,k]^T is a
-//     register-tiled DFMA product (8 x 8 per thread, cp.async double-buffered k-slabs of 16, both operands are unit-stride
-//     columns of the column-major factor) — the accumulator never leaves registers, so HBM/L2 sees only the operand
-//     stream (16 flop per byte) and ONE write of each finished tile;
+// B200 design: cond(C) ~ n e^lsv / 0.01 ~ 1e6 rules fp32 out at the 1e-10 tier and tcgen05 has no fp64 kind, so the
+// factorisation runs on the fp64 tensor pipe (mma.sync.m8n8k4.f64, DMMA: 36.9 TFLOP/s measured with 8 warps per SM,
+// scripts/micro/dmma_bench.cu) — one PERSISTENT CTA per SM, each factoring one chain's matrix at a time (148 matrices in
+// flight, the chains of a launch strided over the CTAs):
+//   * left-looking blocked Cholesky, 128 x 128 tiles: tile (I,J) = C(I,J) - sum_{k < 128 J} L[I,k] L[J,k]^T is a DMMA
+//     product (a warp owns 64 x 32 of the tile = 8 x 4 fragments; cp.async k-slabs of 16 in three buffers with one
+//     barrier per slab; slab row pitch 136 doubles so that fragment loads are conflict-free; both operands are
+//     unit-stride column segments of the column-major factor) — the accumulator never leaves registers, so HBM/L2 sees
+//     only the operand stream (16 flop per byte) and ONE write of each finished tile;
 //   * the covariance is never materialised: the epilogue of a tile evaluates C(I,J) from x and the chain's
 //     hyper-parameters and subtracts the accumulator;
 //   * the diagonal tile is factored in shared memory (right-looking, two barriers per column) with the forward
 //     substitution z = L^-1 y of its 128 rows folded into the same loop (the y-row's dot products with the finished
-//     columns ride on the diagonal tile's operand stream); off-diagonal tiles are solved against the packed factor in
-//     shared memory, a row per thread, four columns at a time;
-//   * per-CTA scratch (work fields): the factor [ld][ld] column-major (ld = n rounded up to 128) and z [ld].
+//     columns ride on the diagonal tile's operand stream); off-diagonal tiles are solved against a k-major copy of the
+//     factor in shared memory, eight columns at a time, all eight warps (even / odd k halves of a row's running sums);
+//   * per-CTA scratch (work fields): the factor [ld][ld] column-major (ld = n rounded up to 128), z [ld], and `prof`
+//     (clock64 totals of the phases: product, covariance epilogue, diagonal factor, solve, store).
 // Padding rows/columns are the identity (log 1 = 0, y = 0), so n need not be a multiple of 128.
 //
 // Oracle: oracle/stk_oracle_gpr.cpp, pinned by tests/golden/gpr_cc.json (the CC templates on the vendored Eigen).

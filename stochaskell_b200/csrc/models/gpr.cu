@@ -47,7 +47,11 @@ using namespace stk;
 
 #define TB 128                 // tile edge
 #define BK 16                  // k-slab
-#define CP 129                 // pitch of the shared C tile (column-major [c][r])
+#ifndef GPR_SOLVE_DMMA
+#define GPR_SOLVE_DMMA 1       // off-diagonal solves on the DMMA pipe (0: the DFMA version on even / odd k halves)
+#endif
+#define CP 136                 // pitch of the shared C tile (column-major [c][r]); = 8 mod 16: DMMA A-fragment loads of
+                               // four columns x eight rows hit every bank twice
 #define SP 136                 // pitch of an operand slab row: = 8 mod 16 doubles, so that the 32 lanes of a DMMA fragment
                                // load (4 k x 8 rows) spread over all banks (two wavefronts, the minimum for 256 B)
 #define NBUF 3                 // slab buffers per operand
@@ -55,7 +59,7 @@ using namespace stk;
 #define SM_TILE (TB * CP)      // doubles; aliases the operand buffers (2 * NBUF * SLAB = 13056 doubles)
 static_assert(2 * NBUF * SLAB <= SM_TILE, "operand buffers must fit in the tile region");
 #define SM_LS 8320             // k-major factor of the diagonal tile, rows padded to an even start: lt_off(128)
-#define GPR_SMEM 212352         // (SM_TILE + SM_LS + NBUF BK + 13 TB) doubles
+#define GPR_SMEM 219520         // (SM_TILE + SM_LS + NBUF BK + 13 TB) doubles
 static_assert(GPR_SMEM == (SM_TILE + SM_LS + NBUF * BK + 13 * TB) * 8, "descriptor smem size");
 #define STRINGIFY(x) #x
 #define STR(x) STRINGIFY(x)
@@ -287,6 +291,48 @@ extern "C" __global__ void __launch_bounds__(256, 1) gpr_chol(const __grid_const
           tk[2] += clock64() - t_c;
         } else {
           // ---- X L_JJ^T = tile: a row per thread, eight columns at a time; the solved tile goes to the factor ----
+#if GPR_SOLVE_DMMA
+          // warp w owns rows 16 w .. 16 w + 15 of the tile through all sixteen 8-column blocks, so the solve needs no CTA
+          // barrier: per block the update S = X[rows, 0:cb] L[cb:cb+8, 0:cb]^T is two DMMA fragment rows (k-steps of 4,
+          // A = the solved columns of the tile, conflict-free at pitch 136; B = rows of the k-major factor copy), then 16
+          // lanes finish their row against the 8 x 8 diagonal block of the factor
+          {
+            const int rbase = warp * 16;
+            for (int cb = 0; cb < TB; cb += 8) {
+              double s0[2] = {0.0, 0.0}, s1[2] = {0.0, 0.0};
+#pragma unroll 2
+              for (int k4 = 0; k4 < cb; k4 += 4) {
+                const int k = k4 + lk, m = k >> 1;
+                const double a0 = Cs[k * CP + rbase + lg], a1 = Cs[k * CP + rbase + 8 + lg];
+                const double b = Ls[256 * m - 2 * m * m + (k & 1) * (TB - 2 * m) + cb + lg];   // lt_off(k) - (k & ~1) + column
+                asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+                             : "+d"(s0[0]), "+d"(s0[1]) : "d"(a0), "d"(b));
+                asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+                             : "+d"(s1[0]), "+d"(s1[1]) : "d"(a1), "d"(b));
+              }
+              if (cb > 0) {
+                double* c0 = Cs + (cb + 2 * lk) * CP + rbase + lg;
+                c0[0] -= s0[0]; c0[CP] -= s0[1]; c0[8] -= s1[0]; c0[CP + 8] -= s1[1];
+              }
+              __syncwarp();
+              if (lane < 16) {
+                const int r = rbase + lane;
+                double sv[8];
+#pragma unroll
+                for (int e = 0; e < 8; ++e) sv[e] = Cs[(cb + e) * CP + r];
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+#pragma unroll
+                  for (int f = 0; f < e; ++f) sv[e] = fma(-sv[f], Ls[lt_off(cb + f) + e - (f & ~1)], sv[e]);
+                  sv[e] *= rdiag[cb + e];
+                }
+#pragma unroll
+                for (int e = 0; e < 8; ++e) Cs[(cb + e) * CP + r] = sv[e];
+              }
+              __syncwarp();
+            }
+          }
+#else
           // all eight warps: threads (r, 0) and (r, 1) share row r, taking the even / the odd k of the running sums
           {
             const int r = tid & (TB - 1), h = tid >> 7;
@@ -323,6 +369,7 @@ extern "C" __global__ void __launch_bounds__(256, 1) gpr_chol(const __grid_const
               __syncthreads();
             }
           }
+#endif
           __syncthreads();
           const long long t_d = clock64();
           for (int e = tid; e < TB * TB; e += 256) {

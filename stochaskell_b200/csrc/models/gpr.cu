@@ -299,17 +299,27 @@ extern "C" __global__ void __launch_bounds__(256, 1) gpr_chol(const __grid_const
           {
             const int rbase = warp * 16;
             for (int cb = 0; cb < TB; cb += 8) {
-              double s0[2] = {0.0, 0.0}, s1[2] = {0.0, 0.0};
-#pragma unroll 2
-              for (int k4 = 0; k4 < cb; k4 += 4) {
-                const int k = k4 + lk, m = k >> 1;
-                const double a0 = Cs[k * CP + rbase + lg], a1 = Cs[k * CP + rbase + 8 + lg];
-                const double b = Ls[256 * m - 2 * m * m + (k & 1) * (TB - 2 * m) + cb + lg];   // lt_off(k) - (k & ~1) + column
+              // four independent accumulator chains per warp (two fragment rows x even / odd k-steps): a DMMA's latency is
+              // longer than its issue interval
+              double s0[2] = {0.0, 0.0}, s1[2] = {0.0, 0.0}, t0[2] = {0.0, 0.0}, t1[2] = {0.0, 0.0};
+#pragma unroll 4
+              for (int k8 = 0; k8 < cb; k8 += 8) {
+                const int ka = k8 + lk, ma = ka >> 1, kb = ka + 4, mb = kb >> 1;
+                const double a0 = Cs[ka * CP + rbase + lg], a1 = Cs[ka * CP + rbase + 8 + lg];
+                const double b0 = Cs[kb * CP + rbase + lg], b1 = Cs[kb * CP + rbase + 8 + lg];
+                // lt_off(k) - (k & ~1) + column
+                const double la = Ls[256 * ma - 2 * ma * ma + (ka & 1) * (TB - 2 * ma) + cb + lg];
+                const double lb = Ls[256 * mb - 2 * mb * mb + (kb & 1) * (TB - 2 * mb) + cb + lg];
                 asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
-                             : "+d"(s0[0]), "+d"(s0[1]) : "d"(a0), "d"(b));
+                             : "+d"(s0[0]), "+d"(s0[1]) : "d"(a0), "d"(la));
                 asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
-                             : "+d"(s1[0]), "+d"(s1[1]) : "d"(a1), "d"(b));
+                             : "+d"(s1[0]), "+d"(s1[1]) : "d"(a1), "d"(la));
+                asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+                             : "+d"(t0[0]), "+d"(t0[1]) : "d"(b0), "d"(lb));
+                asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+                             : "+d"(t1[0]), "+d"(t1[1]) : "d"(b1), "d"(lb));
               }
+              s0[0] += t0[0]; s0[1] += t0[1]; s1[0] += t1[0]; s1[1] += t1[1];
               if (cb > 0) {
                 double* c0 = Cs + (cb + 2 * lk) * CP + rbase + lg;
                 c0[0] -= s0[0]; c0[CP] -= s0[1]; c0[8] -= s1[0]; c0[CP + 8] -= s1[1];

@@ -151,12 +151,13 @@ struct Node {
 };
 struct Def { std::string id; Node node; };
 struct PNode {
-  enum K { Dist, Switch, Loop, Chain } k = Dist;
+  enum K { Dist, Switch, Loop, Chain, Ordered } k = Dist;
   std::string id, dist;
   std::vector<RefP> args;     // Dist args; Switch: head; Chain: lo, hi, initial state
   std::vector<Alt> alts;      // Switch; Chain: one alternative, inputs = index and carried state
   std::vector<std::string> params; std::vector<std::pair<RefP, RefP>> shape; std::shared_ptr<PNode> inner; std::shared_ptr<Body> lam;  // Loop
   Type type;
+  RefP sub_lo, sub_hi;        // SubrangeT bounds of the PNode's type (`truncated`): the draw is a rejection loop
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -201,7 +202,12 @@ struct Parser {
       if (accept(",")) fail("multi-dimensional Array types are not supported by the CUDA lowering");
       return vecT(type());
     }
-    if (x.s == "Subrange") { Type b = type(); ref(); ref(); return b; }
+    if (x.s == "Subrange") {       // Subrange T lo hi (showType, Expression.hs:442-443); `Nothing` = unbounded
+      Type b = type(); RefP lo = ref(), hi = ref();
+      auto some = [](const RefP& r) { return !(r->k == Ref::Var && r->name == "Nothing"); };
+      last_sub_lo = some(lo) ? lo : nullptr; last_sub_hi = some(hi) ? hi : nullptr;
+      return b;
+    }
     if (x.s == "Union") {
       expect("[");
       Type u; u.k = Type::Union;
@@ -359,6 +365,8 @@ struct Parser {
     return d;
   }
 
+  RefP last_sub_lo, last_sub_hi;   // bounds of the most recently parsed Subrange type
+
   PNode pnode() {
     PNode q; Tok id = next();
     if (id.k != Tok::Id) { --p; fail("expected `x <- ...`"); }
@@ -394,12 +402,22 @@ struct Parser {
   void dist(PNode* q) {
     Tok f = next(); if (f.k != Tok::Id) { --p; fail("expected a distribution name"); }
     q->k = PNode::Dist; q->dist = f.s;
-    if (is("(") && peek(1).k == Tok::Id && !ctor_name(peek(1).s, nullptr) && peek(1).s.find('_') == std::string::npos)
-      fail("higher-order distributions (" + f.s + ") are not supported by the CUDA lowering");
+    if (is("(") && peek(1).k == Tok::Id && !ctor_name(peek(1).s, nullptr) && peek(1).s.find('_') == std::string::npos) {
+      // HODist: `d (inner dist args :: P T) args :: P T'` (Show PNode, Program.hs:146)
+      if (f.s != "orderedSample") fail("higher-order distributions (" + f.s + ") are not supported by the CUDA lowering");
+      next();
+      q->k = PNode::Ordered;
+      q->inner = std::make_shared<PNode>();
+      dist(q->inner.get());
+      expect(")");
+    }
     while (!is("::")) q->args.push_back(ref());
     expect("::");
     if (!(peek().k == Tok::Id && peek().s == "P")) fail("expected `P <type>`");
-    next(); q->type = type();
+    next();
+    last_sub_lo = last_sub_hi = nullptr;
+    q->type = type();
+    q->sub_lo = last_sub_lo; q->sub_hi = last_sub_hi;
   }
 
   Body program() {
@@ -737,10 +755,20 @@ struct Gen {
     Val ev;
     if (arr) {
       Val iv; iv.type = scalarT(Type::Z); iv.expr = it; bind(arr->params[0], iv);
-      for (const Def& ad : arr->lam->defs) def(ad);
       ev.type = lookup(ls->name).type.sub[0];
-      if (ev.type.k == Type::Unknown) ev.type = type_of(arr->lam->rets[0]);
-      line("const " + ctype(ev.type) + " " + elem + " = " + rv(arr->lam->rets[0], ev.type.k == Type::R) + ";");
+      if (ev.type.k != Type::Unknown && !arr->lam->defs.empty()) {
+        // the comprehension's definitions live at the same DAG level as the fold body's (both are lambdas of this
+        // block: v_<L+1>_k in either), so they get a C scope of their own
+        line(ctype(ev.type) + " " + elem + ";");
+        line("{"); ind += 2; push();
+        for (const Def& ad : arr->lam->defs) def(ad);
+        line(elem + " = " + rv(arr->lam->rets[0], ev.type.k == Type::R) + ";");
+        pop(); ind -= 2; line("}");
+      } else {
+        for (const Def& ad : arr->lam->defs) def(ad);
+        if (ev.type.k == Type::Unknown) ev.type = type_of(arr->lam->rets[0]);
+        line("const " + ctype(ev.type) + " " + elem + " = " + rv(arr->lam->rets[0], ev.type.k == Type::R) + ";");
+      }
     } else {
       ev.type = type_of(ls).sub[0];
       line("const " + ctype(ev.type) + " " + elem + " = " + rv(ls) + ".at(" + it + ");");
@@ -919,17 +947,58 @@ struct Gen {
     Val r; r.type = st; r.expr = q.id; bind(q.id, r);
   }
 
+  // orderedSample n d (HODist, samplePNode Program.hs:1174-1176: `sort <$> sequence [sample d | _ <- [1..n]]`): n draws
+  // of the scalar distribution d, element k from Philox slot s + (k + 1) 2^16 like a joint, insertion-sorted ascending
+  // into per-thread storage.
+  void ordered_node(const PNode& q, const std::string& slot) {
+    const PNode& in = *q.inner;
+    if (in.k != PNode::Dist || !in.type.scalar() || in.sub_lo || in.sub_hi) die("orderedSample over `" + in.dist + "` is not supported by the CUDA lowering");
+    if (q.args.size() != 1) die("orderedSample takes one count");
+    need(q.args[0]);
+    for (auto& a : in.args) need(a);
+    bool real = in.type.k == Type::R;
+    std::string ct = real ? "double" : "int", buf = fresh(q.id + "_buf"), n = fresh("n"), i = fresh("i"), j = fresh("j"), v = fresh("v"), g = fresh("g");
+    decls << "  " << ct << " " << buf << "[STK_VECCAP];\n";
+    line("const int " + n + " = min(max(" + rv(q.args[0]) + ", 0), STK_VECCAP);");
+    line("for (int " + i + " = 0; " + i + " < " + n + "; ++" + i + ") {");
+    ind += 2;
+    line("stk::Rng " + g + " = " + rng_name + "; " + g + ".slot = " + slot + " + ((unsigned)(" + i + " + 1) << 16);");
+    line("const " + ct + " " + v + " = " + draw_expr(in, g) + ";");
+    line("int " + j + " = " + i + ";");
+    line("while (" + j + " > 0 && " + buf + "[" + j + " - 1] > " + v + ") { " + buf + "[" + j + "] = " + buf + "[" + j + " - 1]; --" + j + "; }");
+    line(buf + "[" + j + "] = " + v + ";");
+    ind -= 2; line("}");
+    Type vt = vecT(in.type);
+    line("const " + ctype(vt) + " " + q.id + "(" + buf + ", 1, " + n + ");");
+    Val r; r.type = vt; r.expr = q.id; bind(q.id, r);
+  }
+
   void pnode(const PNode& q) {
     int level, ptr; id_level_ptr(q.id, &level, &ptr);
     std::string slot = std::to_string(256 * level + 16 * ptr) + "u";
     if (q.k == PNode::Switch) { switch_node(q); return; }
     if (q.k == PNode::Loop) { loop_node(q, slot); return; }
     if (q.k == PNode::Chain) { chain_node(q); return; }
+    if (q.k == PNode::Ordered) { ordered_node(q, slot); return; }
     for (auto& a : q.args) need(a);
     std::string g = fresh("g");
     line("stk::Rng " + g + " = " + rng_name + "; " + g + ".slot = " + slot + ";");
     std::string e = draw_expr(q, g);
     if (!q.type.scalar()) die("draw of type " + q.type.str() + " is not supported");
+    if (q.sub_lo || q.sub_hi) {
+      // ccPNode' on a SubrangeT (`truncated`, CC.hs:283-287): do { draw } while (out of range); the generator keeps
+      // counting blocks across the retries.  The reference loops for ever on an impossible range; here the loop gives
+      // up after 2^16 tries and keeps the last draw, so that a kernel cannot hang the device.
+      need(q.sub_lo); need(q.sub_hi);
+      bool real = q.type.k == Type::R;
+      std::string cond, tries = fresh("tries");
+      if (q.sub_lo) cond = q.id + " < " + rv(q.sub_lo, real);
+      if (q.sub_hi) cond += (cond.empty() ? "" : " || ") + q.id + " > " + rv(q.sub_hi, real);
+      line(ctype(q.type) + " " + q.id + "; int " + tries + " = 0;");
+      line("do { " + q.id + " = " + e + "; } while ((" + cond + ") && ++" + tries + " < 65536);");
+      Val v; v.type = q.type; v.expr = q.id; bind(q.id, v);
+      return;
+    }
     line("const " + ctype(q.type) + " " + q.id + " = " + e + ";");
     Val v; v.type = q.type; v.expr = q.id; bind(q.id, v);
   }

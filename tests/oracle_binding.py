@@ -371,6 +371,23 @@ class Oracle:
         fn.argtypes = [C.c_void_p] + [D] * n
         return fn(C.byref(g), *[float(a) for a in args])
 
+    def draw_until(self, name, seed, chain, step, slot, accept, *args, max_tries=65536):
+        """`do { draw } while (!accept)` on ONE generator (the retries keep counting Philox blocks from `slot`)"""
+        res, n = self._DRAWS[name]
+        assert len(args) == n
+        g = self._Rng()
+        self.l.orc_rng_init.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64]
+        self.l.orc_rng_init(C.byref(g), seed, chain, step)
+        g.slot = slot
+        fn = getattr(self.l, "orc_draw_" + name)
+        fn.restype = res
+        fn.argtypes = [C.c_void_p] + [D] * n
+        for _ in range(max_tries):
+            v = fn(C.byref(g), *[float(a) for a in args])
+            if accept(v):
+                break
+        return v
+
     def u01x2(self, seed, chain, step, slot):
         a = D(); b = D()
         self.l.orc_u01x2(seed, chain, step, slot, C.byref(a), C.byref(b))

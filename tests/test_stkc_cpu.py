@@ -12,7 +12,9 @@ IR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ir")
 SOCCER_T = "Union[(R, ZVec), (R, R, ZVec)]"
 CASES = {"soccer_rj": [SOCCER_T], "mh_sym": ["R"], "mh_asym": ["R"], "solve_case": [], "tom": [],
          # joint (Loop) PNodes: hand-written in the shape `Show PNode` prints (Program.hs:142-145) — no notebook preserves one
-         "joint_sim": [], "joint_rw": ["RVec"], "chain_rw": [], "scan_sim": []}
+         "joint_sim": [], "joint_rw": ["RVec"], "chain_rw": [], "scan_sim": [],
+         # coalPrior (app/rj/Main.hs:115-122): truncated Poisson, orderedSample of uniforms, joint of gammas
+         "coal_prior": []}
 
 
 def ir(name):
@@ -60,6 +62,18 @@ def test_scans_keep_every_partial_result():
     assert "v_0_1_buf" in src and "[0] = v_0_1_acc" in src          # scanl: seed at index 0
     assert "] = v_0_2_acc" in src and "; --k_" in src                # scanr: backwards, seed at index n
     assert "const VecI v_0_4(" in src and "field out2 state i32 8" in src
+
+
+def test_truncated_draws_are_rejection_loops_and_ordered_sample_sorts():
+    """ccPNode' on a SubrangeT (CC.hs:283-287): do { draw } while (out of range); orderedSample (Program.hs:1174-1176)"""
+    src = ir_to_cuda(ir("coal_prior"), [])
+    assert "do { x_sim_0_0 = stk::draw_poisson(g_0, 3.0); } while ((x_sim_0_0 < 1 || x_sim_0_0 > 30)" in src
+    assert "stk::draw_uniform(g_" in src and "x_sim_0_1_buf" in src and "--j_" in src
+    half = ir_to_cuda("let v_0_0 = getExternal x_a_0_0 :: Subrange R 0.0 Nothing\n in do x_a_0_0 <- cauchy 0.0 2.5 :: P Subrange R 0.0 Nothing\n       return [v_0_0]\n", [])
+    assert "while ((x_a_0_0 < 0.0) &&" in half
+    with pytest.raises(StkError) as e:
+        ir_to_cuda(ir("coal_prior").replace("orderedSample (uniform", "wishartOf (uniform"), [])
+    assert e.value.code == -5 and "higher-order" in str(e.value)
 
 
 def test_soccer_lowering_follows_the_reference_templates():

@@ -102,3 +102,21 @@ def test_recorded_draws_and_posterior_concentrates(ctx):
     assert np.array_equal(d[-1].reshape(2, C), q)
     # data drawn from sin(x/5) + 0.1 noise: signal variance below prior mean, length scale^2 of a few tens to hundreds
     assert -3.0 < q[0].mean() < 1.5 and 2.0 < q[1].mean() < 8.0
+
+
+def test_full_size_n2048_against_oracle_and_across_ctas(ctx):
+    """BASELINE configs[2] size: n = 2048 (16 x 16 tiles), more chains than SMs so that the persistent CTAs wrap around;
+    two chains checked against the oracle (1e-10), equal points on different CTAs / rounds give bit-identical lp"""
+    from tests.oracle_binding import oracle
+    o = oracle()
+    n, C = 2048, 150
+    x, y, rng = synth(n, 2048)
+    Q = np.ascontiguousarray(np.stack([rng.normal(0, 0.7, C), rng.normal(np.log(100.0), 0.7, C)]))
+    Q[:, 149] = Q[:, 0]; Q[:, 77] = Q[:, 0]
+    s = sampler(ctx, x, y, C)
+    s.chains.set_state("q", Q)
+    lp = s.chains.logp()
+    assert np.isfinite(lp).all()
+    assert lp[149] == lp[0] and lp[77] == lp[0]
+    for c in (0, 101):
+        assert lp[c] == pytest.approx(o.gpr_logp(x, y, Q[:, c]), rel=1e-10), c

@@ -973,6 +973,43 @@ struct Gen {
     Val r; r.type = vt; r.expr = q.id; bind(q.id, r);
   }
 
+  // vectorised Dist PNodes `normals m s`, `uniforms a b`, `cauchys m s`, `bernoulliLogits l`, `bernoullis p`, `poissons l`
+  // (samplePNode, Program.hs:1093-1170; normalChol / gpclas / gpClassifier use them): element k ~ the scalar distribution
+  // at the k-th elements of the argument vectors (views, or comprehensions with a bare body such as `[ 0.0 | _ <- 1...n ]`),
+  // drawn like a joint: Philox slot s + (k + 1) 2^16, per-thread storage.
+  bool vectorised_node(const PNode& q, const std::string& slot) {
+    static const std::map<std::string, std::string> scalar_of = {{"normals", "normal"}, {"uniforms", "uniform"}, {"cauchys", "cauchy"},
+      {"bernoulliLogits", "bernoulliLogit"}, {"bernoullis", "bernoulli"}, {"poissons", "poisson"}};
+    auto it = scalar_of.find(q.dist);
+    if (it == scalar_of.end()) return false;
+    if (q.type.k != Type::Vec || !q.type.sub[0].scalar()) die("`" + q.dist + "` of type " + q.type.str() + " is not supported by the CUDA lowering (vectors only)");
+    for (auto& a : q.args) need(a);
+    bool real = q.type.sub[0].k == Type::R;
+    std::string buf = fresh(q.id + "_buf"), n = fresh("n"), k = fresh("k"), g = fresh("g");
+    decls << "  " << (real ? "double" : "int") << " " << buf << "[STK_VECCAP];\n";
+    auto length = [&](const RefP& a) -> std::string {
+      if (a->k == Ref::Var && lookup(a->name).array) { const Node& an = *lookup(a->name).array; return "(" + rv(an.shape[0].second) + " - " + rv(an.shape[0].first) + " + 1)"; }
+      return rv(a) + ".len";
+    };
+    line("const int " + n + " = min(max(" + length(q.args.at(0)) + ", 0), STK_VECCAP);");
+    line("for (int " + k + " = 1; " + k + " <= " + n + "; ++" + k + ") {");
+    ind += 2;
+    // the scalar PNode of one element: arguments are the vectors indexed at k
+    PNode el; el.k = PNode::Dist; el.dist = it->second; el.type = q.type.sub[0]; el.id = q.id;
+    push(); Val kv; kv.type = scalarT(Type::Z); kv.expr = k; bind(k, kv);
+    for (auto& a : q.args) {
+      auto ix = std::make_shared<Ref>(); ix->k = Ref::Index; ix->base = a;
+      auto kr = std::make_shared<Ref>(); kr->k = Ref::Var; kr->name = k; ix->args.push_back(kr);
+      el.args.push_back(ix);
+    }
+    line("stk::Rng " + g + " = " + rng_name + "; " + g + ".slot = " + slot + " + ((unsigned)" + k + " << 16);");
+    line(buf + "[" + k + " - 1] = " + draw_expr(el, g) + ";");
+    pop(); ind -= 2; line("}");
+    line("const " + ctype(q.type) + " " + q.id + "(" + buf + ", 1, " + n + ");");
+    Val r; r.type = q.type; r.expr = q.id; bind(q.id, r);
+    return true;
+  }
+
   void pnode(const PNode& q) {
     int level, ptr; id_level_ptr(q.id, &level, &ptr);
     std::string slot = std::to_string(256 * level + 16 * ptr) + "u";
@@ -980,6 +1017,7 @@ struct Gen {
     if (q.k == PNode::Loop) { loop_node(q, slot); return; }
     if (q.k == PNode::Chain) { chain_node(q); return; }
     if (q.k == PNode::Ordered) { ordered_node(q, slot); return; }
+    if (vectorised_node(q, slot)) return;
     for (auto& a : q.args) need(a);
     std::string g = fresh("g");
     line("stk::Rng " + g + " = " + rng_name + "; " + g + ".slot = " + slot + ";");

@@ -14,7 +14,9 @@ CASES = {"soccer_rj": [SOCCER_T], "mh_sym": ["R"], "mh_asym": ["R"], "solve_case
          # joint (Loop) PNodes: hand-written in the shape `Show PNode` prints (Program.hs:142-145) — no notebook preserves one
          "joint_sim": [], "joint_rw": ["RVec"], "chain_rw": [], "scan_sim": [],
          # coalPrior (app/rj/Main.hs:115-122): truncated Poisson, orderedSample of uniforms, joint of gammas
-         "coal_prior": []}
+         "coal_prior": [],
+         # the vectorised Dist PNodes of normalChol / gpclas / gpClassifier (Program.hs:668-673, app/benchmark/Main.hs:76-91)
+         "gpc_prior": []}
 
 
 def ir(name):
@@ -74,6 +76,15 @@ def test_truncated_draws_are_rejection_loops_and_ordered_sample_sorts():
     with pytest.raises(StkError) as e:
         ir_to_cuda(ir("coal_prior").replace("orderedSample (uniform", "wishartOf (uniform"), [])
     assert e.value.code == -5 and "higher-order" in str(e.value)
+
+
+def test_vectorised_distributions_lower_elementwise():
+    src = ir_to_cuda(ir("gpc_prior"), [], veccap=8)
+    assert "stk::draw_uniform(g_3, 0.0, 50.0)" in src                       # comprehension arguments inlined at the index
+    assert "stk::draw_normal(g_7, x_sim_0_0.at(k_6), 1.0)" in src and "const VecI x_sim_0_2(" in src
+    with pytest.raises(StkError) as e:
+        ir_to_cuda(ir("gpc_prior").replace("uniforms v_0_0 v_0_1 :: P RVec", "uniforms v_0_0 v_0_1 :: P RMat"), [])
+    assert e.value.code == -5
 
 
 def test_soccer_lowering_follows_the_reference_templates():

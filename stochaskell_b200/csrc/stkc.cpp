@@ -597,6 +597,19 @@ struct Gen {
     return nullptr;
   }
 
+  // scalar log-densities: the log-space forms of stk_device.cuh behind the names of CC.hs:198-228
+  std::string lpdf_call(const std::string& f, const std::vector<RefP>& args) {
+    static const std::set<std::string> intx = {"poisson_lpdf", "neg_binomial_lpdf", "geometric_lpdf", "bernoulli_lpdf", "bernoulliLogit_lpdf", "discreteUniform_lpdf"};
+    static const std::map<std::string, std::string> rename = {{"bernoulliLogit_lpdf", "bernoulli_logit_lpdf"}, {"discreteUniform_lpdf", "discrete_uniform_lpdf"}};
+    static const std::set<std::string> known = {"normal_lpdf", "gamma_lpdf", "inv_gamma_lpdf", "geometric_lpdf", "neg_binomial_lpdf", "poisson_lpdf", "uniform_lpdf",
+      "discreteUniform_lpdf", "bernoulli_lpdf", "bernoulliLogit_lpdf", "cauchy_lpdf", "logistic_lpdf", "beta_lpdf"};
+    if (!known.count(f)) die("log-density `" + f + "` is not in the device library");
+    auto it = rename.find(f);
+    std::string e = "stk::" + (it == rename.end() ? f : it->second) + "(" + rv(args.at(0), !intx.count(f));
+    for (size_t i = 1; i < args.size(); ++i) e += ", " + rv(args[i], f != "discreteUniform_lpdf");
+    return e + ")";
+  }
+
   void def(const Def& d) {
     const Node& n = d.node;
     Val v; v.type = n.type;
@@ -664,17 +677,27 @@ struct Gen {
       line("const double " + tab + "[] = {" + init + "};");
       e = "stk::pmf_lpdf(" + arg(0) + ", " + tab + ")";
     }
-    else if (f.size() > 5 && f.compare(f.size() - 5, 5, "_lpdf") == 0) {                    // CC.hs:198-228, log-space forms of stk_device.cuh
-      static const std::set<std::string> intx = {"poisson_lpdf", "neg_binomial_lpdf", "geometric_lpdf", "bernoulli_lpdf", "bernoulliLogit_lpdf", "discreteUniform_lpdf"};
-      static const std::map<std::string, std::string> rename = {{"bernoulliLogit_lpdf", "bernoulli_logit_lpdf"}, {"discreteUniform_lpdf", "discrete_uniform_lpdf"}};
-      static const std::set<std::string> known = {"normal_lpdf", "gamma_lpdf", "inv_gamma_lpdf", "geometric_lpdf", "neg_binomial_lpdf", "poisson_lpdf", "uniform_lpdf",
-        "discreteUniform_lpdf", "bernoulli_lpdf", "bernoulliLogit_lpdf", "cauchy_lpdf", "logistic_lpdf", "beta_lpdf"};
-      if (!known.count(f)) die("log-density `" + f + "` is not in the device library");
-      auto it = rename.find(f);
-      e = "stk::" + (it == rename.end() ? f : it->second) + "(" + arg(0, !intx.count(f));
-      for (size_t i = 1; i < n.args.size(); ++i) e += ", " + arg(i, f != "discreteUniform_lpdf");
-      e += ")";
+    else if (f == "normals_lpdf" || f == "uniforms_lpdf" || f == "cauchys_lpdf" || f == "bernoulliLogits_lpdf" || f == "poissons_lpdf" || f == "bernoullis_lpdf") {
+      // vectorised log-densities: the loop of CC.hs:214-220 (`normals_lpdf`; 1-D only, as there), summed in index order
+      std::string sf = f.substr(0, f.size() - 6) + "_lpdf", k = fresh("k"), len;
+      const RefP& x0 = n.args.at(0);
+      if (x0->k == Ref::Var && lookup(x0->name).array) { const Node& an = *lookup(x0->name).array; len = "(" + rv(an.shape[0].second) + " - " + rv(an.shape[0].first) + " + 1)"; }
+      else len = rv(x0) + ".len";
+      line("double " + d.id + " = 0.0;");
+      line("for (int " + k + " = 1; " + k + " <= " + len + "; ++" + k + ") {");
+      ind += 2; push();
+      Val kv; kv.type = scalarT(Type::Z); kv.expr = k; bind(k, kv);
+      std::vector<RefP> el;
+      for (auto& a : n.args) {
+        auto ix = std::make_shared<Ref>(); ix->k = Ref::Index; ix->base = a;
+        auto kr = std::make_shared<Ref>(); kr->k = Ref::Var; kr->name = k; ix->args.push_back(kr);
+        el.push_back(ix);
+      }
+      line(d.id + " += " + lpdf_call(sf, el) + ";");
+      pop(); ind -= 2; line("}");
+      v.expr = d.id; bind(d.id, v); return;
     }
+    else if (f.size() > 5 && f.compare(f.size() - 5, 5, "_lpdf") == 0) e = lpdf_call(f, n.args);   // CC.hs:198-228
     else if (f == "uniform_cdf") e = "stk::uniform_cdf(" + arg(0, true) + ", " + arg(1, true) + ", " + arg(2, true) + ")";
     else {
       static const std::set<std::string> math1 = {"exp", "log", "sqrt", "abs", "sin", "cos", "tan", "tanh", "sinh", "cosh", "floor", "ceil", "lgamma", "log1p", "expm1", "asin", "acos", "atan"};

@@ -16,7 +16,9 @@ CASES = {"soccer_rj": [SOCCER_T], "mh_sym": ["R"], "mh_asym": ["R"], "solve_case
          # coalPrior (app/rj/Main.hs:115-122): truncated Poisson, orderedSample of uniforms, joint of gammas
          "coal_prior": [],
          # the vectorised Dist PNodes of normalChol / gpclas / gpClassifier (Program.hs:668-673, app/benchmark/Main.hs:76-91)
-         "gpc_prior": []}
+         "gpc_prior": [],
+         # an MH kernel on the mean of iid normals written with the vectorised log-density (CC.hs:214-220)
+         "normals_mh": ["R", "RVec"]}
 
 
 def ir(name):
@@ -85,6 +87,12 @@ def test_vectorised_distributions_lower_elementwise():
     with pytest.raises(StkError) as e:
         ir_to_cuda(ir("gpc_prior").replace("uniforms v_0_0 v_0_1 :: P RVec", "uniforms v_0_0 v_0_1 :: P RMat"), [])
     assert e.value.code == -5
+
+
+def test_vectorised_lpdf_is_the_cc_loop():
+    src = ir_to_cuda(ir("normals_mh"), ["R", "RVec"])
+    assert "for (int k_1 = 1; k_1 <= i_0_1.len; ++k_1) {" in src
+    assert "v_0_5 += stk::normal_lpdf(i_0_1.at(k_1), v_0_1, 2.0);" in src
 
 
 def test_soccer_lowering_follows_the_reference_templates():

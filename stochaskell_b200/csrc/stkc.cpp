@@ -533,19 +533,59 @@ struct Gen {
   }
 
   // scalar / view expression for a reference (ccNodeRef, CC.hs:47-60)
+  // An Array comprehension used as a value (returned, stored, passed to a vector operation) is materialised once, where
+  // it is first needed, into per-thread storage — the resize + loops of CC.hs:231-235; its other uses stay inlined.
+  std::string materialise(const std::string& name) {
+    Val* vp = nullptr;
+    for (size_t i = scopes.size(); i-- > 0 && !vp;) { auto it = scopes[i].find(name); if (it != scopes[i].end()) vp = &it->second; }
+    const Node& an = *vp->array;
+    if (an.params.size() != 1) die("array " + name + " has " + std::to_string(an.params.size()) + " dimensions; only vectors can be materialised");
+    Type et = vp->type.k == Type::Vec ? vp->type.sub[0] : scalarT(Type::R);
+    if (!et.scalar()) die("array " + name + " of " + et.str() + " cannot be materialised");
+    bool real = et.k == Type::R;
+    std::string buf = fresh(name + "_buf"), lo = fresh("lo"), n = fresh("n"), vec = fresh(name + "_m");
+    const std::string& iv = an.params[0];
+    decls << "  " << (real ? "double" : "int") << " " << buf << "[STK_VECCAP];\n";
+    line("const int " + lo + " = " + rv(an.shape[0].first) + ";");
+    line("const int " + n + " = min(max(" + rv(an.shape[0].second) + " - " + lo + " + 1, 0), STK_VECCAP);");
+    line("for (int " + iv + " = " + lo + "; " + iv + " < " + lo + " + " + n + "; ++" + iv + ") {");
+    ind += 2; push();
+    Val kv; kv.type = scalarT(Type::Z); kv.expr = iv; bind(iv, kv);
+    for (const Def& ad : an.lam->defs) def(ad);
+    line(buf + "[" + iv + " - " + lo + "] = " + rv(an.lam->rets.at(0), real) + ";");
+    pop(); ind -= 2; line("}");
+    Type vt = vecT(et);
+    line("const " + ctype(vt) + " " + vec + "(" + buf + ", 1, " + n + ");");
+    // remember the storage only when it was filled in the C scope the array was defined in (storage filled inside a loop
+    // or branch body is out of scope afterwards: the array stays symbolic for later uses)
+    for (size_t i = scopes.size(); i-- > 0;) {
+      auto it = scopes[i].find(name);
+      if (it == scopes[i].end()) continue;
+      if (i + 1 == scopes.size()) { it->second.array = nullptr; it->second.type = vt; it->second.expr = vec; }
+      break;
+    }
+    return vec;
+  }
+
   std::string rv(const RefP& r, bool want_real = false) {
     switch (r->k) {
       case Ref::Num: return num(r->name, want_real);
       case Ref::Var: {
         const Val& v = lookup(r->name);
-        if (v.array) die("array " + r->name + " is used where it would have to be materialised; not supported");
+        if (v.array) return materialise(r->name);
         if (want_real && v.type.integral()) return "(double)" + v.expr;
         return v.expr;
       }
       case Ref::Index: {
         if (r->args.size() != 1) die("only 1-D indexing is supported");
         RefP b = r->base;
-        if (b->k == Ref::Var && lookup(b->name).array) return inline_array_at(*lookup(b->name).array, rv(r->args[0]));
+        if (b->k == Ref::Var && lookup(b->name).array) {
+          const Node& an = *lookup(b->name).array;
+          if (an.lam->defs.empty() && an.params.size() == 1) return inline_array_at(an, rv(r->args[0]));
+          std::string e = materialise(b->name) + ".at(" + rv(r->args[0]) + ")";     // a computed array: indexed through its storage
+          if (want_real && type_of(r).integral()) return "(double)" + e;
+          return e;
+        }
         std::string e = rv(b) + ".at(" + rv(r->args[0]) + ")";
         if (want_real && type_of(r).integral()) return "(double)" + e;
         return e;

@@ -73,6 +73,7 @@ def test_truncated_draws_are_rejection_loops_and_ordered_sample_sorts():
     src = ir_to_cuda(ir("coal_prior"), [])
     assert "do { x_sim_0_0 = stk::draw_poisson(g_0, 3.0); } while ((x_sim_0_0 < 1 || x_sim_0_0 > 30)" in src
     assert "stk::draw_uniform(g_" in src and "x_sim_0_1_buf" in src and "--j_" in src
+    assert "v_0_4_buf" in src and "field out4 state f64 64" in src       # the thinned vector is materialised for the return
     half = ir_to_cuda("let v_0_0 = getExternal x_a_0_0 :: Subrange R 0.0 Nothing\n in do x_a_0_0 <- cauchy 0.0 2.5 :: P Subrange R 0.0 Nothing\n       return [v_0_0]\n", [])
     assert "while ((x_a_0_0 < 0.0) &&" in half
     with pytest.raises(StkError) as e:

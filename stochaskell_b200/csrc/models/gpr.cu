@@ -47,6 +47,9 @@ using namespace stk;
 
 #define TB 128                 // tile edge
 #define BK 16                  // k-slab
+#ifndef GPR_COV_RECIP
+#define GPR_COV_RECIP 1        // covariance epilogue: multiply by the reciprocal of 2 exp lls2 instead of dividing 64 times per thread
+#endif
 #ifndef GPR_SOLVE_DMMA
 #define GPR_SOLVE_DMMA 1       // off-diagonal solves on the DMMA pipe (0: the DFMA version on even / odd k halves)
 #endif
@@ -103,7 +106,11 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 // sq = x^2 precomputed per row / column; d2 / den stays a division, as the reference's expression has it
 __device__ __forceinline__ double cov_entry(double xi, double xj, double sqi, double sqj, double lsv, double den, bool diag) {
   const double d2 = __dsub_rn(__dadd_rn(sqi, sqj), __dmul_rn(2.0, __dmul_rn(xi, xj)));
+#if GPR_COV_RECIP
+  const double v = exp(__dsub_rn(lsv, __dmul_rn(d2, den)));     // den holds 1 / (2 exp lls2): one ulp off the reference's quotient
+#else
   const double v = exp(__dsub_rn(lsv, __ddiv_rn(d2, den)));
+#endif
   return diag ? __dadd_rn(v, 0.01) : v;
 }
 
@@ -140,7 +147,11 @@ extern "C" __global__ void __launch_bounds__(256, 1) gpr_chol(const __grid_const
   long long tk[5] = {0, 0, 0, 0, 0};
   for (long long chain = blockIdx.x; chain < C; chain += gridDim.x) {
     const double lsv = Q[chain], lls2 = Q[C + chain];
+#if GPR_COV_RECIP
+    const double den = 1.0 / __dmul_rn(2.0, exp(lls2));
+#else
     const double den = __dmul_rn(2.0, exp(lls2));
+#endif
     double logdet = 0.0, quad = 0.0;
     bool bad = false;
 

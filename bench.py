@@ -337,7 +337,7 @@ class BiratsHMC:
 class BiratsNUTS(BiratsHMC):
     """C4 under hmcStan's DEFAULT sampler (birats.ipynb cell 8): NUTS, diag_e, max_depth 10, after warm-up.  Chains start from an
     adapted state: step size = the mean over 24 chains of the vendored CmdStan's adaptation (tests/golden/birats_nuts_stan.json),
-    metric = the one a 300-transition warm-up of the CPU restatement reaches (computed once at start-up, untimed)."""
+    metric = the one a 300-transition adaptive warm-up of the device kernel reaches (computed once at start-up, untimed)."""
     name = "birats_nuts"
     kernel = "nuts"
     logpdf_populations = None
@@ -361,8 +361,21 @@ class BiratsNUTS(BiratsHMC):
                               "shared memory / registers, physical DRAM traffic ~0; bound: latency of one warp per chain")
         self._adapted = None
 
-    def _warm(self):
+    def prepare_device(self, device):
+        """the GPU arm's start state comes from the DEVICE's own warm-up (300 adaptive NUTS transitions of one chain through the
+        library, untimed) — nothing of oracle/ feeds the measured path"""
         if self._adapted is None:
+            from stochaskell_b200 import Sampler
+            s = Sampler(self.module, 32, self.data(), seed=12345, device=device)
+            for k, v in dict(stepsize=1.0, num_warmup=300.0, max_depth=10.0).items():
+                s.chains.set_param(k, v)
+            s.chains.set_state("q", np.ascontiguousarray(np.repeat(self.q0.reshape(-1, 1), 32, axis=1)))
+            s.chains.step("nuts", 301)
+            q = s.chains.get_state("q"); minv = s.chains.get_state("minv")
+            self._adapted = (np.ascontiguousarray(q[:, 0]), np.ascontiguousarray(np.median(minv, axis=1)))
+
+    def _warm(self):
+        if self._adapted is None:          # CPU arm only (no device): the restatement's warm-up
             from tests.oracle_binding import oracle
             orc = oracle()
             cfg = orc.adapt_cfg(stepsize=1.0, num_warmup=300)
@@ -761,6 +774,8 @@ def run_native(args, wl, rank, world, local, torch, dist):
     ch = s.chains
     for k, v in wl.params().items():
         ch.set_param(k, v)
+    if hasattr(wl, "prepare_device"):
+        wl.prepare_device(local)
     st0 = wl.init_state(C, chain0)
     for k, v in st0.items():
         ch.set_state(k, v)

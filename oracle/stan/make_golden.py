@@ -73,6 +73,7 @@ def sample(exe, data, init, eps, L, n, seed, chain_id):
 
 def linreg():
     exe = build("linreg")
+    drv = lp_driver("linreg")       # full-precision log_prob_grad (17 digits), not `diagnose`'s 6 significant digits
     gold = {}
     # (a) lp/grad points at n=40 and n=1000 (d=10)
     for tag, n in (("small", 40), ("full", 1000)):
@@ -83,15 +84,16 @@ def linreg():
         data = os.path.join(WORK, f"linreg_{tag}.data")
         rdump(data, n=n, d=d, x_stan_0_0=X, x_stan_0_4=y)
         K = 8 if tag == "small" else 4
-        Q = np.empty((K, d + 2)); LP = np.empty(K); G = np.empty((K, d + 2))
+        Q = np.empty((K, d + 2))
         for k in range(K):
             q = np.r_[0.5 + 0.3 * rng.standard_normal(), w + 0.3 * rng.standard_normal(d), 0.4 * rng.standard_normal()]
             if k == 0:
                 q[:] = 0.0
-            init = os.path.join(WORK, "linreg.init")
-            rdump(init, x_stan_0_1=q[0], x_stan_0_2=q[1:1 + d], x_stan_0_3=np.exp(q[d + 1]))
-            LP[k], G[k] = diagnose(exe, data, init)
             Q[k] = q
+        # unconstrained order of the Stan program: x_stan_0_1 (b), x_stan_0_2[d] (w), log x_stan_0_3 (sigma)
+        LP, G = lp_grad(drv, data, Q, 0)        # propto = 0: jacobian on, every constant kept (log_prob_grad<false, true>)
+        LPp, _ = lp_grad(drv, data, Q, 1)       # propto = 1: what `~` statements keep under autodiff (= the sampler's lp__)
+        gold[f"{tag}_lp_propto"] = LPp
         gold.update({f"{tag}_X": X, f"{tag}_y": y, f"{tag}_q": Q, f"{tag}_lp": LP, f"{tag}_grad": G})
         if tag == "small":
             # (b) posterior moments by the reference sampler: 4 chains x 2500 static-HMC draws
@@ -304,15 +306,15 @@ def gp():
         subprocess.run(["make", "-C", CMDSTAN, exe], check=True, capture_output=True)
     drv = lp_driver("gp")
     gold = {}
-    for tag, n in (("small", 48), ("mid", 160)):
+    for tag, n in (("small", 48), ("mid", 160), ("big", 512)):
         rng = np.random.default_rng(20261104 + n)
         x = np.sort(rng.uniform(0, 10, n))
         f = np.sin(x) * 1.5
         z = (rng.uniform(size=n) < 1 / (1 + np.exp(-f))).astype(np.int64)
         data = os.path.join(WORK, f"gp_{tag}.data")
         rdump(data, x_stan_0_0=n, x_stan_0_1=x, x_stan_0_3=z)
-        K = 6
-        W = rng.standard_normal((K, n)) * np.array([0.0, 0.3, 1.0, 1.0, 2.0, 1.0])[:, None]
+        K = 6 if n < 500 else 3
+        W = rng.standard_normal((K, n)) * np.array([0.0, 0.3, 1.0, 1.0, 2.0, 1.0])[:K, None]
         lp, g = lp_grad(drv, data, W, 0)
         gold.update({f"{tag}_x": x, f"{tag}_z": z, f"{tag}_w": W, f"{tag}_lp": lp, f"{tag}_grad": g})
     np.savez_compressed(os.path.join(GOLD, "gp_stan.npz"), **gold)

@@ -63,17 +63,20 @@ double orc_soccer_accept_prob(int tag, double lam, double kappa, const int* y, i
   return std::fmin(1.0, std::exp(v16));
 }
 
-// one transition with the Philox layout of stkc-generated kernels (csrc/stkc.cpp): the PNode x_<ns>_<L>_<P> draws
-// from slot 256*L + 16*P.  Model1 alternative: x_cc_1_0 ~ normal (slot 256), x_cc_1_1 ~ bernoulli (slot 272);
-// Model2 alternative: x_cc_1_0 ~ bernoulli (slot 256).  Returns the new tag; *kappa updated on a 0 -> 1 jump.
+// one transition with the Philox layout of stkc-generated kernels (csrc/stkc.cpp): the PNode x_<ns>_<L>_<P> draws with
+// counter word c2 ^ (L << 24 | P << 12), blocks counted from 0.  Model1 alternative: x_cc_1_0 ~ normal (L 1, P 0),
+// x_cc_1_1 ~ bernoulli (L 1, P 1); Model2 alternative: x_cc_1_0 ~ bernoulli (L 1, P 0).  Returns the new tag; *kappa
+// updated on a 0 -> 1 jump.
 int orc_soccer_rj_step(int tag, double lam, double* kappa, const int* y, int ny,
                        uint64_t seed, uint64_t chain, uint64_t step, double* p_out) {
-  orc_rng g; orc_rng_init(&g, seed, chain, step);
+  orc_rng g0; orc_rng_init(&g0, seed, chain, step);
+  const uint32_t t10 = (1u << 24) | (0u << 12), t11 = (1u << 24) | (1u << 12);
+  orc_rng g = g0;
   double x = 0.0;
-  if (tag == 0) { g.slot = 256; x = 0.0 + 1.5 * orc_normal(&g); }
+  if (tag == 0) { g.c2 ^= t10; g.slot = 0; x = 0.0 + 1.5 * orc_normal(&g); }
   double kp = *kappa;
   const double p = orc_soccer_accept_prob(tag, lam, *kappa, y, ny, x, &kp);
-  g.slot = tag == 0 ? 272 : 256;
+  g = g0; g.c2 ^= tag == 0 ? t11 : t10; g.slot = 0;
   const int acc = orc_draw_bernoulli(&g, p);
   if (p_out) *p_out = p;
   if (!acc) return tag;

@@ -103,7 +103,8 @@ template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N)); }
 
 // covariance entry (kernelSE' with the expanded squared distance; no contraction, as the reference's Eigen expression);
-// sq = x^2 precomputed per row / column; d2 / den stays a division, as the reference's expression has it
+// sq = x^2 precomputed per row / column; with GPR_COV_RECIP (default) d2 / den is a multiplication by the reciprocal of den
+// (one ulp off the reference's quotient, parity unchanged at 1e-10); GPR_COV_RECIP=0 keeps the division of the reference's expression
 __device__ __forceinline__ double cov_entry(double xi, double xj, double sqi, double sqj, double lsv, double den, bool diag) {
   const double d2 = __dsub_rn(__dadd_rn(sqi, sqj), __dmul_rn(2.0, __dmul_rn(xi, xj)));
 #if GPR_COV_RECIP

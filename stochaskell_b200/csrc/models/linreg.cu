@@ -334,6 +334,9 @@ linreg_hmc_adapt(const __grid_constant__ StkArgs a) {
     if (__syncthreads_or(fresh)) init_stepsize(rng, fresh);
     if (ad[9] == 1.0 && (double)step >= cfg.num_warmup) { ad[0] = exp(ad[3]); ad[9] = 2.0; }  // complete_adaptation
     const double eps = ad[0];
+    // L = floor(int_time / eps) at the step size in force.  Deliberate divergence from CmdStan 2.20 after warm-up:
+    // adapt_diag_e_static_hmc::disengage_adaptation calls complete_adaptation but not update_L_, so Stan keeps the L of the
+    // last warm-up step size while sampling; here L follows the final (averaged) step size ("divergences").
     const int L = adapt_leaps(cfg.int_time, eps);
     sample_p(rng);
     const double H0 = -lp + kinetic();
@@ -879,7 +882,7 @@ extern "C" __device__ const char stk_desc[] =
     "nparam " STR(LINREG_P) "\n"
     "field q state f64 " STR(LINREG_P) "\n"
     "field lp state f64 1\n"
-    "field X data f64 0\n"
+    "field X data f64 @y*" STR(LINREG_D) "\n"     /* row-major [n][d]: the runtime rejects any other size (d is compiled in) */
     "field y data f64 0\n"
     "field ysim state f64 @y\n"
     "field ad state f64 10\n"

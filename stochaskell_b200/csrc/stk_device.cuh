@@ -255,16 +255,22 @@ struct Vec {
 };
 typedef Vec<double> VecD;
 typedef Vec<int> VecI;
+// length of a vector about to be written into storage of `cap` elements: an overflow is clamped AND reported through the
+// module's `err` work field (the runtime turns it into STK_ERR_ARG at the next synchronising call), never silent
+STK_DEV int cap_len(int n, int cap, int* err, int code = 1) {
+  if (n > cap) { if (err) *err = code; return cap; }
+  return n < 0 ? 0 : n;
+}
 // next-transition feed: make the state vector `dst` hold `src` (no copy when it already does)
 template <class T>
-STK_DEV void assign_vec(Vec<T>& dst, const Vec<T>& src, int cap) {
-  const int n = src.len < cap ? src.len : cap;
+STK_DEV void assign_vec(Vec<T>& dst, const Vec<T>& src, int cap, int* err = nullptr) {
+  const int n = cap_len(src.len, cap, err, 2);
   if (src.p != dst.p) for (int i = 0; i < n; ++i) dst.p[(long long)i * dst.stride] = src.p[(long long)i * src.stride];
   dst.len = n;
 }
 template <class T>
-STK_DEV void store_vec(const Vec<T>& v, T* dst, long long stride, int cap, int* len_out) {
-  const int n = v.len < cap ? v.len : cap;
+STK_DEV void store_vec(const Vec<T>& v, T* dst, long long stride, int cap, int* len_out, int* err = nullptr) {
+  const int n = cap_len(v.len, cap, err, 2);
   if (v.p != dst) for (int i = 0; i < n; ++i) dst[(long long)i * stride] = v.p[(long long)i * v.stride];
   *len_out = n;
 }

@@ -177,6 +177,7 @@ struct stk_chains {
   double* scratch = nullptr; size_t scratch_bytes = 0;
   bool dirty_data = true, dirty_state = true;   // plans: run `prepare` / `init` stages before the next launch
   long long grad_cap = 0;
+  cudaStream_t last = nullptr;                  // caller stream of the most recent stk_step / stk_simulate (nullptr = the ctx stream)
 };
 
 namespace {
@@ -329,7 +330,44 @@ int ensure_fields(stk_chains* c) {
     size_t bytes = (size_t)L * (fd.is_state ? (size_t)c->n : 1) * elem_size(fd);
     CU(cudaMalloc(&c->dptr[f], bytes));
     CU(cudaMemsetAsync(c->dptr[f], 0, bytes, c->mod->ctx->stream));
+    // allocation is rare (once per field): finish the zero-fill here, so that a launch on a caller's stream cannot race it
+    CU(cudaStreamSynchronize(c->mod->ctx->stream));
     c->flen[f] = L;
+  }
+  return STK_OK;
+}
+
+// every stream that may still be running this chain set's kernels: the context's own and the caller stream of the last launch
+int sync_chains(stk_chains* c) {
+  CU(cudaStreamSynchronize(c->mod->ctx->stream));
+  if (c->last && c->last != c->mod->ctx->stream) CU(cudaStreamSynchronize(c->last));
+  return STK_OK;
+}
+
+// generated (stkc) modules carry an i32 work field `err` that a kernel sets when a per-thread vector would overflow its
+// storage (STK_VECCAP) or a state field's capacity: reported, after the launch has finished, by every call that synchronises
+int check_err(stk_chains* c) {
+  int fi = field_index(c->mod, "err");
+  if (fi < 0 || !c->mod->fields[fi].is_work || !c->mod->fields[fi].is_i32 || !c->dptr[fi]) return STK_OK;
+  int code = 0;
+  CU(cudaMemcpy(&code, c->dptr[fi], sizeof code, cudaMemcpyDeviceToHost));
+  if (code == 0) return STK_OK;
+  CU(cudaMemset(c->dptr[fi], 0, sizeof code));
+  return fail(STK_ERR_ARG, "module %s: a kernel reported error %d (%s); the chain state is not valid — rebuild the module with a larger "
+              "veccap / upload the state field with more rows", c->mod->name.c_str(), code,
+              code == 1 ? "a vector outgrew the per-thread storage STK_VECCAP" : code == 2 ? "a vector outgrew the capacity of its state field" :
+              code == 3 ? "a matrix outgrew the per-thread storage STK_MATCAP" : "unknown");
+}
+
+// data fields declared with a length expression (e.g. `field X data f64 @y*10`) must have exactly that many elements
+int check_data_shapes(stk_chains* c) {
+  for (size_t f = 0; f < c->mod->fields.size(); ++f) {
+    const FieldDesc& fd = c->mod->fields[f];
+    if (fd.is_state || fd.is_work || fd.len_expr.empty() || !c->dptr[f]) continue;
+    long long want = eval_expr(c, fd.len_expr);
+    if (want > 0 && want != c->flen[f])
+      return fail(STK_ERR_ARG, "module %s: data field %s holds %lld elements, the descriptor requires %s = %lld", c->mod->name.c_str(),
+                  fd.name.c_str(), c->flen[f], fd.len_expr.c_str(), want);
   }
   return STK_OK;
 }
@@ -376,6 +414,7 @@ int run_prepare(stk_chains* c, cudaStream_t st) {
   if (!c->dirty_data) return STK_OK;
   int rc = ensure_fields(c);
   if (rc) return rc;
+  if ((rc = check_data_shapes(c))) return rc;
   if (m->prepare_plan >= 0) {
     StkArgs a; fill_args(c, 0, &a);
     for (auto& sd : m->plans[m->prepare_plan].stages) if ((rc = launch_stage(c, sd, a, st, 4))) return rc;
@@ -488,9 +527,6 @@ int launch(stk_chains* c, KernelDesc& k, long long n_steps, cudaStream_t st) {
   }
   if (smem > 227 * 1024) return fail(STK_ERR_UNSUPPORTED, "kernel %s needs %lld B shared memory (> 227 KB)", k.name.c_str(), smem);
   int block = k.block;
-  if (const char* ob = getenv("STK_BLOCK_OVERRIDE")) {  // tuning knob for kernels that size smem by block
-    (void)ob;
-  }
   if (smem > 48 * 1024)
     CU(cudaFuncSetAttribute((const void*)k.k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   long long grid = (c->n + k.cpb - 1) / k.cpb;
@@ -715,6 +751,7 @@ int stk_chains_destroy(stk_chains* c) {
   if (!c) return STK_OK;
   cudaSetDevice(c->mod->ctx->device);
   cudaStreamSynchronize(c->mod->ctx->stream);
+  if (c->last && c->last != c->mod->ctx->stream) cudaStreamSynchronize(c->last);
   for (void* p : c->dptr) if (p) cudaFree(p);
   if (c->draws) cudaFree(c->draws);
   if (c->out_lp) cudaFree(c->out_lp);
@@ -742,11 +779,12 @@ int stk_set_data(stk_chains* c, int field, const void* host, size_t bytes) {
   if (bytes % es) return fail(STK_ERR_ARG, "data field %s: %zu bytes is not a multiple of %zu", fd.name.c_str(), bytes, es);
   long long len = (long long)(bytes / es);
   if (fd.len > 0 && len != fd.len) return fail(STK_ERR_ARG, "data field %s expects %lld elements, got %lld", fd.name.c_str(), fd.len, len);
+  if ((rc = sync_chains(c))) return rc;            // no kernel of these chains may still be reading the old buffer
   if (c->dptr[field] && c->flen[field] != len) {
-    CU(cudaStreamSynchronize(m->ctx->stream)); CU(cudaFree(c->dptr[field])); c->dptr[field] = nullptr;
+    CU(cudaFree(c->dptr[field])); c->dptr[field] = nullptr;
     // fields sized by an expression follow the data: drop them, ensure_fields re-creates them (zeroed)
     for (size_t f = 0; f < m->fields.size(); ++f)
-      if (!m->fields[f].len_expr.empty() && c->dptr[f]) { CU(cudaFree(c->dptr[f])); c->dptr[f] = nullptr; c->flen[f] = 0; }
+      if (!m->fields[f].len_expr.empty() && (m->fields[f].is_state || m->fields[f].is_work) && c->dptr[f]) { CU(cudaFree(c->dptr[f])); c->dptr[f] = nullptr; c->flen[f] = 0; }
   }
   if (!c->dptr[field]) CU(cudaMalloc(&c->dptr[field], bytes ? bytes : 8));
   c->flen[field] = len;
@@ -771,6 +809,7 @@ int stk_set_state(stk_chains* c, int field, const void* host, size_t bytes, int 
   int rc = need_device(m->ctx);
   if (rc) return rc;
   if ((rc = ensure_fields(c))) return rc;
+  if (c->last && c->last != m->ctx->stream) CU(cudaStreamSynchronize(c->last));   // a launch on a caller stream may still use the field
   const FieldDesc& fd = m->fields[field];
   size_t es = elem_size(fd);
   if (c->flen[field] <= 0 && fd.len == 0 && fd.len_expr.empty()) {
@@ -809,9 +848,10 @@ int stk_get_state(stk_chains* c, int field, void* host, size_t bytes) {
   size_t want = (size_t)c->flen[field] * elem_size(fd) * (fd.is_state ? (size_t)c->n : 1);
   if (!c->dptr[field] || want == 0) return fail(STK_ERR_ARG, "field %s is empty", fd.name.c_str());
   if (bytes != want) return fail(STK_ERR_ARG, "field %s holds %zu bytes, buffer is %zu", fd.name.c_str(), want, bytes);
+  if (c->last && c->last != m->ctx->stream) CU(cudaStreamSynchronize(c->last));
   CU(cudaMemcpyAsync(host, c->dptr[field], bytes, cudaMemcpyDeviceToHost, m->ctx->stream));
   CU(cudaStreamSynchronize(m->ctx->stream));
-  return STK_OK;
+  return check_err(c);
 }
 
 int stk_device_ptr(stk_chains* c, int field, void** dptr, size_t* bytes) {
@@ -844,6 +884,7 @@ static int run_entry(stk_chains* c, int e, const char* what) {
   int rc = need_device(c->mod->ctx);
   if (rc) return rc;
   if (e == 1 && (rc = ensure_grad(c))) return rc;
+  if (c->last && c->last != c->mod->ctx->stream) { CU(cudaStreamSynchronize(c->last)); c->last = nullptr; }
   if (c->mod->entry[e].plan >= 0) {
     if (e == 2) c->dirty_state = true;
     return run_entry_plan(c, c->mod->entry[e].plan, c->mod->ctx->stream);
@@ -856,7 +897,7 @@ int stk_logp(stk_chains* c, double* lp_host) {
   if (rc) return rc;
   if (lp_host) CU(cudaMemcpyAsync(lp_host, c->out_lp, sizeof(double) * (size_t)c->n, cudaMemcpyDeviceToHost, c->mod->ctx->stream));
   CU(cudaStreamSynchronize(c->mod->ctx->stream));
-  return STK_OK;
+  return check_err(c);
 }
 
 int stk_logp_grad(stk_chains* c, double* lp_host, double* grad_host) {
@@ -866,7 +907,7 @@ int stk_logp_grad(stk_chains* c, double* lp_host, double* grad_host) {
   if (lp_host) CU(cudaMemcpyAsync(lp_host, c->out_lp, sizeof(double) * (size_t)c->n, cudaMemcpyDeviceToHost, st));
   if (grad_host) CU(cudaMemcpyAsync(grad_host, c->out_grad, sizeof(double) * (size_t)c->n * (size_t)num_params(c), cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
-  return STK_OK;
+  return check_err(c);
 }
 
 int stk_step(stk_chains* c, int kernel_id, int64_t n_transitions, stk_stream stream) {
@@ -877,6 +918,8 @@ int stk_step(stk_chains* c, int kernel_id, int64_t n_transitions, stk_stream str
   int rc = need_device(c->mod->ctx);
   if (rc) return rc;
   cudaStream_t st = stream ? (cudaStream_t)stream : c->mod->ctx->stream;
+  if (c->last && c->last != st) CU(cudaStreamSynchronize(c->last));   // launches of one chain set are ordered, whatever the stream
+  c->last = st;
   KernelDesc& kd = c->mod->kernels[kernel_id];
   if (kd.plan >= 0) return run_kernel_plan(c, kd.plan, n_transitions, st);
   // a kernel with a pre-pass runs in chunks whose scratch ([transitions][k][chains] doubles) fits the budget
@@ -915,6 +958,8 @@ int stk_simulate(stk_chains* c, stk_stream stream) {
   int rc = need_device(c->mod->ctx);
   if (rc) return rc;
   cudaStream_t st = stream ? (cudaStream_t)stream : c->mod->ctx->stream;
+  if (c->last && c->last != st) CU(cudaStreamSynchronize(c->last));
+  c->last = st;
   c->dirty_state = true;
   if (c->mod->entry[2].plan >= 0) return run_entry_plan(c, c->mod->entry[2].plan, st);
   return launch(c, c->mod->entry[2], 0, st);
@@ -924,7 +969,7 @@ int stk_record(stk_chains* c, int64_t n_slots, int64_t thin) {
   if (!c || n_slots < 0 || thin < 1) return fail(STK_ERR_ARG, "bad argument");
   int rc = need_device(c->mod->ctx);
   if (rc) return rc;
-  CU(cudaStreamSynchronize(c->mod->ctx->stream));
+  if ((rc = sync_chains(c))) return rc;
   if (c->draws) { CU(cudaFree(c->draws)); c->draws = nullptr; }
   c->slots = 0; c->recorded = 0; c->thin = thin;
   if (n_slots == 0) return STK_OK;
@@ -946,6 +991,7 @@ int stk_get_draws(stk_chains* c, double* host, size_t bytes, int64_t* n_recorded
   if (rc) return rc;
   size_t want = sizeof(double) * (size_t)c->recorded * (size_t)c->nrec * (size_t)c->n;
   if (bytes < want) return fail(STK_ERR_ARG, "draws need %zu bytes, buffer is %zu", want, bytes);
+  if (c->last && c->last != c->mod->ctx->stream) CU(cudaStreamSynchronize(c->last));
   if (want) CU(cudaMemcpyAsync(host, c->draws, want, cudaMemcpyDeviceToHost, c->mod->ctx->stream));
   CU(cudaStreamSynchronize(c->mod->ctx->stream));
   return STK_OK;
@@ -955,8 +1001,8 @@ int stk_sync(stk_chains* c) {
   if (!c) return fail(STK_ERR_ARG, "null chains");
   int rc = need_device(c->mod->ctx);
   if (rc) return rc;
-  CU(cudaStreamSynchronize(c->mod->ctx->stream));
-  return STK_OK;
+  if ((rc = sync_chains(c))) return rc;
+  return check_err(c);
 }
 
 int stk_num_params(stk_chains* c) { return c ? (int)num_params(c) : fail(STK_ERR_ARG, "null chains"); }
@@ -988,6 +1034,7 @@ int stk_diag_partial(stk_chains* c, int64_t max_lag, double* buf, size_t bytes) 
   if (rc) return rc;
   stk_ctx* ctx = c->mod->ctx;
   if ((rc = load_diag(ctx))) return rc;
+  if (c->last && c->last != ctx->stream) CU(cudaStreamSynchronize(c->last));
   long long N = c->recorded, C = c->n; int P = (int)c->nrec;
   if (max_lag < 0 || max_lag > N - 1) max_lag = N - 1;
   size_t want = sizeof(double) * (size_t)P * (size_t)(4 + max_lag + 1);

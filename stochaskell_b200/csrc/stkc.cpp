@@ -15,9 +15,11 @@
 // compileCC, 9 for runStep); their types are not part of the printed IR and are passed beside it.
 //
 // Execution shape of the generated module: ONE THREAD PER CHAIN, the whole transition loop inside
-// the kernel, state in registers/local memory between transitions, Philox counter =
-// (global chain, transition, slot) with slot = 256*level + 16*pointer of the drawing PNode — a draw
-// is a pure function of (seed, chain, transition, PNode), whatever the sharding.
+// the kernel, state in registers/local memory between transitions.  Philox counter of a draw of PNode x_<ns>_<L>_<P>:
+//   c0 = global chain, c1 = transition (low word), c2 = transition (high word) ^ (L << 24 | P << 12 | enclosing chain PNode + 1),
+//   c3 = element index of a joint << 16 | block inside the draw;   key = seed, its high word ^ iteration of the enclosing chain
+// so every PNode (and every element, and every iteration of a `chain`) owns a counter range of 2^16 blocks that no other
+// draw can reach — a draw is a pure function of (seed, chain, transition, PNode), whatever the sharding.
 // Hand-tuned builtins (models/*.cu) exist for the benchmark configs; this is the generic path.
 #include "../../include/stk_cuda.h"
 
@@ -547,7 +549,7 @@ struct Gen {
     const std::string& iv = an.params[0];
     decls << "  " << (real ? "double" : "int") << " " << buf << "[STK_VECCAP];\n";
     line("const int " + lo + " = " + rv(an.shape[0].first) + ";");
-    line("const int " + n + " = min(max(" + rv(an.shape[0].second) + " - " + lo + " + 1, 0), STK_VECCAP);");
+    line("const int " + n + " = stk::cap_len(" + rv(an.shape[0].second) + " - " + lo + " + 1, STK_VECCAP, err_);");
     line("for (int " + iv + " = " + lo + "; " + iv + " < " + lo + " + " + n + "; ++" + iv + ") {");
     ind += 2; push();
     Val kv; kv.type = scalarT(Type::Z); kv.expr = iv; bind(iv, kv);
@@ -755,19 +757,25 @@ struct Gen {
     bool real = n.type.sub[0].k == Type::R;
     std::string ct = real ? "double" : "int", buf = fresh(d.id + "_buf");
     decls << "  " << ct << " " << buf << "[STK_VECCAP];\n";
-    std::string src = rv(n.args.at(0)), i = fresh("i");
+    std::string src = rv(n.args.at(0)), i = fresh("i"), ln = fresh("n");
+    // every copy into per-thread storage is bounded by STK_VECCAP; an overflow sets the module's err flag
     if (f == "replaceIndex") {
-      line("for (int " + i + " = 1; " + i + " <= " + src + ".len; ++" + i + ") " + buf + "[" + i + " - 1] = " + src + ".at(" + i + ");");
-      line(buf + "[" + rv(n.args.at(1)) + " - 1] = " + rv(n.args.at(2), real) + ";");
-      line("const " + ctype(n.type) + " " + d.id + "(" + buf + ", 1, " + src + ".len);");
+      std::string j = fresh("j");
+      line("const int " + ln + " = stk::cap_len(" + src + ".len, STK_VECCAP, err_);");
+      line("for (int " + i + " = 1; " + i + " <= " + ln + "; ++" + i + ") " + buf + "[" + i + " - 1] = " + src + ".at(" + i + ");");
+      line("const int " + j + " = " + rv(n.args.at(1)) + ";");
+      line("if (" + j + " >= 1 && " + j + " <= " + ln + ") " + buf + "[" + j + " - 1] = " + rv(n.args.at(2), real) + ";");
+      line("const " + ctype(n.type) + " " + d.id + "(" + buf + ", 1, " + ln + ");");
     } else if (f == "insertIndex") {
       std::string j = rv(n.args.at(1)), e = rv(n.args.at(2), real);
-      line("for (int " + i + " = 1; " + i + " <= " + src + ".len + 1; ++" + i + ") " + buf + "[" + i + " - 1] = " + i + " < " + j + " ? " + src + ".at(" + i + ") : (" + i + " == " + j + " ? " + e + " : " + src + ".at(" + i + " - 1));");
-      line("const " + ctype(n.type) + " " + d.id + "(" + buf + ", 1, " + src + ".len + 1);");
+      line("const int " + ln + " = stk::cap_len(" + src + ".len + 1, STK_VECCAP, err_);");
+      line("for (int " + i + " = 1; " + i + " <= " + ln + "; ++" + i + ") " + buf + "[" + i + " - 1] = " + i + " < " + j + " ? " + src + ".at(" + i + ") : (" + i + " == " + j + " ? " + e + " : " + src + ".at(" + i + " - 1));");
+      line("const " + ctype(n.type) + " " + d.id + "(" + buf + ", 1, " + ln + ");");
     } else if (f == "deleteIndex") {
       std::string j = rv(n.args.at(1));
-      line("for (int " + i + " = 1; " + i + " <= " + src + ".len - 1; ++" + i + ") " + buf + "[" + i + " - 1] = " + i + " < " + j + " ? " + src + ".at(" + i + ") : " + src + ".at(" + i + " + 1);");
-      line("const " + ctype(n.type) + " " + d.id + "(" + buf + ", 1, " + src + ".len - 1);");
+      line("const int " + ln + " = stk::cap_len(" + src + ".len - 1, STK_VECCAP, err_);");
+      line("for (int " + i + " = 1; " + i + " <= " + ln + "; ++" + i + ") " + buf + "[" + i + " - 1] = " + i + " < " + j + " ? " + src + ".at(" + i + ") : " + src + ".at(" + i + " + 1);");
+      line("const " + ctype(n.type) + " " + d.id + "(" + buf + ", 1, " + ln + ");");
     } else if (f == "id") {
       line("const " + ctype(n.type) + " " + d.id + " = " + src + ";");
     } else die("vector node `" + f + "` is not supported by the CUDA lowering");
@@ -808,7 +816,7 @@ struct Gen {
     if (scan) {
       buf = fresh(d.id + "_buf"); len = fresh("n");
       decls << "  " << (rt ? "double" : "int") << " " << buf << "[STK_VECCAP];\n";
-      line("const int " + len + " = min(max((" + hi + ") - (" + lo + ") + 1, 0), STK_VECCAP - 1);");
+      line("const int " + len + " = stk::cap_len((" + hi + ") - (" + lo + ") + 1, STK_VECCAP - 1, err_);");
       hi = "(" + lo + ") + " + len + " - 1";
       line(buf + "[" + (left ? "0" : len) + "] = " + cur + ";");
     }
@@ -961,14 +969,14 @@ struct Gen {
     std::string buf = fresh(q.id + "_buf"), lo = fresh("lo"), hi = fresh("hi");
     decls << "  " << (real ? "double" : "int") << " " << buf << "[STK_VECCAP];\n";
     line("const int " + lo + " = " + rv(q.shape[0].first) + ";");
-    line("const int " + hi + " = min(" + rv(q.shape[0].second) + ", " + lo + " + STK_VECCAP - 1);");
+    line("const int " + hi + " = " + lo + " + stk::cap_len(" + rv(q.shape[0].second) + " - " + lo + " + 1, STK_VECCAP, err_) - 1;");
     const std::string& iv = q.params[0];
     line("for (int " + iv + " = " + lo + "; " + iv + " <= " + hi + "; ++" + iv + ") {");
     ind += 2; push();
     Val v; v.type = scalarT(Type::Z); v.expr = iv; bind(iv, v);
     for (const Def& d : q.lam->defs) def(d);
     std::string g = fresh("g");
-    line("stk::Rng " + g + " = " + rng_name + "; " + g + ".slot = " + slot + " + ((unsigned)(" + iv + " - " + lo + " + 1) << 16);");
+    line(gen_decl(g, slot, "(" + iv + " - " + lo + " + 1)"));
     line(buf + "[" + iv + " - " + lo + "] = " + draw_expr(in, g) + ";");
     pop(); ind -= 2; line("}");
     Type vt = vecT(in.type);
@@ -1000,7 +1008,8 @@ struct Gen {
     line("const " + ctype(st) + " " + jv + " = " + q.id + ";");
     Val j; j.type = st; j.expr = jv; bind(jv, j);
     int level, ptr; id_level_ptr(q.id, &level, &ptr);
-    line("stk::Rng " + rc + " = rng; " + rc + ".c2 ^= ((unsigned)(" + iv + " - " + lo + " + 1) << 12) ^ " + std::to_string(256 * level + 16 * ptr) + "u;");
+    if (ptr >= 4095) die("PNode pointer " + std::to_string(ptr) + " of a chain exceeds the 4094 the Philox layout reserves");
+    line("stk::Rng " + rc + " = rng; " + rc + ".k1 ^= (unsigned)(" + iv + " - " + lo + " + 1); " + rc + ".c2 ^= " + std::to_string(ptr + 1) + "u;");
     rng_name = rc;
     body(a.body);
     if (a.body.rets.size() != 1) die("chain body must return one value");
@@ -1022,10 +1031,10 @@ struct Gen {
     bool real = in.type.k == Type::R;
     std::string ct = real ? "double" : "int", buf = fresh(q.id + "_buf"), n = fresh("n"), i = fresh("i"), j = fresh("j"), v = fresh("v"), g = fresh("g");
     decls << "  " << ct << " " << buf << "[STK_VECCAP];\n";
-    line("const int " + n + " = min(max(" + rv(q.args[0]) + ", 0), STK_VECCAP);");
+    line("const int " + n + " = stk::cap_len(" + rv(q.args[0]) + ", STK_VECCAP, err_);");
     line("for (int " + i + " = 0; " + i + " < " + n + "; ++" + i + ") {");
     ind += 2;
-    line("stk::Rng " + g + " = " + rng_name + "; " + g + ".slot = " + slot + " + ((unsigned)(" + i + " + 1) << 16);");
+    line(gen_decl(g, slot, "(" + i + " + 1)"));
     line("const " + ct + " " + v + " = " + draw_expr(in, g) + ";");
     line("int " + j + " = " + i + ";");
     line("while (" + j + " > 0 && " + buf + "[" + j + " - 1] > " + v + ") { " + buf + "[" + j + "] = " + buf + "[" + j + " - 1]; --" + j + "; }");
@@ -1054,7 +1063,7 @@ struct Gen {
       if (a->k == Ref::Var && lookup(a->name).array) { const Node& an = *lookup(a->name).array; return "(" + rv(an.shape[0].second) + " - " + rv(an.shape[0].first) + " + 1)"; }
       return rv(a) + ".len";
     };
-    line("const int " + n + " = min(max(" + length(q.args.at(0)) + ", 0), STK_VECCAP);");
+    line("const int " + n + " = stk::cap_len(" + length(q.args.at(0)) + ", STK_VECCAP, err_);");
     line("for (int " + k + " = 1; " + k + " <= " + n + "; ++" + k + ") {");
     ind += 2;
     // the scalar PNode of one element: arguments are the vectors indexed at k
@@ -1065,7 +1074,7 @@ struct Gen {
       auto kr = std::make_shared<Ref>(); kr->k = Ref::Var; kr->name = k; ix->args.push_back(kr);
       el.args.push_back(ix);
     }
-    line("stk::Rng " + g + " = " + rng_name + "; " + g + ".slot = " + slot + " + ((unsigned)" + k + " << 16);");
+    line(gen_decl(g, slot, k));
     line(buf + "[" + k + " - 1] = " + draw_expr(el, g) + ";");
     pop(); ind -= 2; line("}");
     line("const " + ctype(q.type) + " " + q.id + "(" + buf + ", 1, " + n + ");");
@@ -1073,9 +1082,19 @@ struct Gen {
     return true;
   }
 
+  // generator of one draw: the PNode's tag goes into counter word c2, the element index of a joint into the high half of
+  // the block counter; the low 16 bits count the blocks the draw itself consumes (rejection loops included)
+  std::string gen_decl(const std::string& g, const std::string& tag, const std::string& elem) {
+    return "stk::Rng " + g + " = " + rng_name + "; " + g + ".c2 ^= " + tag + "; " + g + ".slot = " +
+           (elem.empty() ? std::string("0u") : "(unsigned)" + elem + " << 16") + ";";
+  }
+
   void pnode(const PNode& q) {
     int level, ptr; id_level_ptr(q.id, &level, &ptr);
-    std::string slot = std::to_string(256 * level + 16 * ptr) + "u";
+    // the PNode's own word of the Philox counter (slots of different PNodes must not be reachable from one another)
+    if (level < 0 || level >= 256 || ptr < 0 || ptr >= 4096)
+      die("PNode " + q.id + ": level/pointer outside the 256 x 4096 ids the Philox counter layout reserves");
+    std::string slot = std::to_string(((unsigned)level << 24) | ((unsigned)ptr << 12)) + "u";
     if (q.k == PNode::Switch) { switch_node(q); return; }
     if (q.k == PNode::Loop) { loop_node(q, slot); return; }
     if (q.k == PNode::Chain) { chain_node(q); return; }
@@ -1083,7 +1102,7 @@ struct Gen {
     if (vectorised_node(q, slot)) return;
     for (auto& a : q.args) need(a);
     std::string g = fresh("g");
-    line("stk::Rng " + g + " = " + rng_name + "; " + g + ".slot = " + slot + ";");
+    line(gen_decl(g, slot, ""));
     std::string e = draw_expr(q, g);
     if (!q.type.scalar()) die("draw of type " + q.type.str() + " is not supported");
     if (q.sub_lo || q.sub_hi) {
@@ -1164,7 +1183,7 @@ struct Gen {
 // ---------------------------------------------------------------------------------------------
 // whole module (ccProgram, CC.hs:398-432)
 // ---------------------------------------------------------------------------------------------
-struct Field { std::string name; bool i32; std::string len; };
+struct Field { std::string name; bool i32; std::string len; const char* kind = "state"; };
 
 static std::vector<Type> parse_types(const std::string& s) {
   std::vector<Type> ts;
@@ -1214,7 +1233,7 @@ static std::string generate(const std::string& ir, const std::string& input_type
     auto add_vec = [&](const std::string& nm, bool i32, const std::string& cvar) {
       fields.push_back({nm, i32, "0"}); fields.push_back({nm + "_len", true, "1"});
       load << "  " << (i32 ? "VecI " : "VecD ") << cvar << "((" << (i32 ? "int" : "double") << "*)a.field[" << F(nm) << "] + chain, a.n_chains, ((const int*)a.field[" << F(nm + "_len") << "])[chain]);\n";
-      store << "  store_vec(" << cvar << ", (" << (i32 ? "int" : "double") << "*)a.field[" << F(nm) << "] + chain, a.n_chains, (int)a.flen[" << F(nm) << "], (int*)a.field[" << F(nm + "_len") << "] + chain);\n";
+      store << "  store_vec(" << cvar << ", (" << (i32 ? "int" : "double") << "*)a.field[" << F(nm) << "] + chain, a.n_chains, (int)a.flen[" << F(nm) << "], (int*)a.field[" << F(nm + "_len") << "] + chain, err_);\n";
     };
     if (t.k == Type::R) { add_scalar(fn, false, id); v.expr = id; }
     else if (t.integral()) { add_scalar(fn, true, id); v.expr = id; }
@@ -1233,7 +1252,7 @@ static std::string generate(const std::string& ir, const std::string& input_type
           bool i32 = s.type.sub[0].k != Type::R;
           fields.push_back({nm, i32, "0"}); fields.push_back({nm + "_len", true, "1"});
           load << "  " << id << "." << s.name << " = " << (i32 ? "VecI" : "VecD") << "((" << (i32 ? "int" : "double") << "*)a.field[F_" << nm << "] + chain, a.n_chains, ((const int*)a.field[F_" << nm << "_len])[chain]);\n";
-          store << "  store_vec(" << id << "." << s.name << ", (" << (i32 ? "int" : "double") << "*)a.field[F_" << nm << "] + chain, a.n_chains, (int)a.flen[F_" << nm << "], (int*)a.field[F_" << nm << "_len] + chain);\n";
+          store << "  store_vec(" << id << "." << s.name << ", (" << (i32 ? "int" : "double") << "*)a.field[F_" << nm << "] + chain, a.n_chains, (int)a.flen[F_" << nm << "], (int*)a.field[F_" << nm << "_len] + chain, err_);\n";
         } else {
           bool i32 = s.type.k != Type::R;
           fields.push_back({nm, i32, "1"});
@@ -1259,12 +1278,12 @@ static std::string generate(const std::string& ir, const std::string& input_type
       std::string e = g.rv(prog.rets[k], its[k].k == Type::R);
       std::string nx = "nx" + std::to_string(k);
       g.line((its[k].k == Type::Union ? g.union_struct(its[k]) : Gen::ctype(its[k])) + " " + nx + " = " + e + ";");
-      if (its[k].k == Type::Vec) feed << "    assign_vec(" << in_names[k] << ", " << nx << ", (int)a.flen[F_in" << k << "]);\n";
+      if (its[k].k == Type::Vec) feed << "    assign_vec(" << in_names[k] << ", " << nx << ", (int)a.flen[F_in" << k << "], err_);\n";
       else if (its[k].k == Type::Union) {
         const UnionLayout& L = g.unions[its[k].str()];
         feed << "    " << in_names[k] << ".tag = " << nx << ".tag;\n";
         for (const Slot& s : L.slots) {
-          if (s.type.k == Type::Vec) feed << "    assign_vec(" << in_names[k] << "." << s.name << ", " << nx << "." << s.name << ", (int)a.flen[F_in" << k << "_" << s.name.substr(2) << "]);\n";
+          if (s.type.k == Type::Vec) feed << "    assign_vec(" << in_names[k] << "." << s.name << ", " << nx << "." << s.name << ", (int)a.flen[F_in" << k << "_" << s.name.substr(2) << "], err_);\n";
           else feed << "    " << in_names[k] << "." << s.name << " = " << nx << "." << s.name << ";\n";
         }
       } else feed << "    " << in_names[k] << " = " << nx << ";\n";
@@ -1274,7 +1293,7 @@ static std::string generate(const std::string& ir, const std::string& input_type
         bool i32 = rt.sub[0].k != Type::R;
         out_fields.push_back({nm, i32, std::to_string(veccap)}); out_fields.push_back({nm + "_len", true, "1"});
         g.line("store_vec(" + g.rv(prog.rets[k]) + ", (" + (i32 ? "int" : "double") + "*)a.field[F_" + nm + "] + chain, a.n_chains, " + std::to_string(veccap) +
-               ", (int*)a.field[F_" + nm + "_len] + chain);");
+               ", (int*)a.field[F_" + nm + "_len] + chain, err_);");
         continue;
       }
       if (!rt.scalar()) die("simulate: return of type " + rt.str() + " is not supported");
@@ -1284,6 +1303,7 @@ static std::string generate(const std::string& ir, const std::string& input_type
     }
   }
   for (auto& f : out_fields) fields.push_back(f);
+  { Field ef{"err", true, "1"}; ef.kind = "work"; fields.push_back(ef); }   // overflow flag, checked by the runtime after the launch
   if ((int)fields.size() > 24) die("too many state fields");
 
   std::ostringstream o;
@@ -1302,6 +1322,7 @@ static std::string generate(const std::string& ir, const std::string& input_type
   const char* sym = kernel ? "stk_ir_step" : "stk_ir_simulate";
   o << "extern \"C\" __global__ void __launch_bounds__(" << block << ") " << sym << "(const __grid_constant__ StkArgs a) {\n";
   o << "  const long long chain = (long long)blockIdx.x * blockDim.x + threadIdx.x;\n  if (chain >= a.n_chains) return;\n";
+  o << "  int* const err_ = (int*)a.field[F_err];\n";
   o << load.str() << g.decls.str();
   if (kernel) {
     o << "  for (long long t_ = 0; t_ < a.n_steps; ++t_) {\n";
@@ -1312,7 +1333,7 @@ static std::string generate(const std::string& ir, const std::string& input_type
     o << "  {\n    Rng rng; rng.init(a.seed, (u64)(a.chain0 + chain), ~0ULL);\n" << g.out.str() << "  }\n}\n";
   }
   o << "extern \"C\" __device__ const char stk_desc[] =\n  \"stk-module 1\\n\"\n  \"name " << name << "\\n\"\n  \"nparam 0\\n\"\n";
-  for (auto& f : fields) o << "  \"field " << f.name << " state " << (f.i32 ? "i32" : "f64") << " " << f.len << "\\n\"\n";
+  for (auto& f : fields) o << "  \"field " << f.name << " " << f.kind << " " << (f.i32 ? "i32" : "f64") << " " << f.len << "\\n\"\n";
   if (!rec.str().empty()) o << "  \"record" << rec.str() << "\\n\"\n";
   if (kernel) o << "  \"kernel step " << sym << " " << block << " " << block << " 0 - 0\\n\";\n";
   else o << "  \"entry simulate " << sym << " " << block << " " << block << " 0 - 0\\n\";\n";

@@ -49,6 +49,29 @@ def test_sweeps_match_oracle(ctx, orc, N, C, K):
     assert np.all(s.chains.get_state("acc_n") == 0)     # accumulators are reset for the next sweep
 
 
+def test_sweeps_match_oracle_at_baseline_size(ctx, orc):
+    """BASELINE configs[4] / the bench shape: 100,000 points, 1024 chains, K = 32 (49 observation tiles per chain group, the
+    multi-tile accumulators, 400 MB of z): cluster indices of chains spread over the launch bit-exact after two sweeps"""
+    N, C, K, seed, T = 100_000, 1024, 32, 5, 2
+    rng = np.random.default_rng(17)
+    mu_true = rng.uniform(0, 100, 5)
+    y = mu_true[rng.integers(0, 5, N)] + rng.standard_normal(N)        # dp.ipynb cell 3's planted mixture
+    s = sampler(ctx, y, C, seed, K=K)
+    st = s.simulate()
+    v0 = st["v"].copy(); mu0 = st["mu"].copy()
+    s.chains.step("sweep", T)
+    v = s.chains.get_state("v"); mu = s.chains.get_state("mu"); z = s.chains.get_state("z")
+    assert z.shape == (N, C) and z.min() >= 1 and z.max() <= K
+    for c in (0, 31, 32, 517, 1023):
+        vo = v0[:K, c].copy(); mo = mu0[:K, c].copy()
+        for t in range(T):
+            zo = orc.dp_sweep(y, vo, mo, seed, c, t)
+        assert np.array_equal(z[:, c], zo), (c, np.flatnonzero(z[:, c] != zo)[:5])
+        np.testing.assert_allclose(v[:K, c], vo, rtol=1e-9)
+        np.testing.assert_allclose(mu[:K, c], mo, rtol=1e-9)
+    assert np.all(s.chains.get_state("acc_n") == 0)
+
+
 def test_simulate_matches_oracle(ctx, orc):
     N, C, K, seed = 1001, 33, 32, 4
     s = sampler(ctx, np.zeros(N), C, seed, K=K)

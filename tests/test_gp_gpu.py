@@ -45,7 +45,7 @@ def synth(n, seed):
     return x, z, rng
 
 
-@pytest.mark.parametrize("tag", ["small", "mid"])
+@pytest.mark.parametrize("tag", ["small", "mid", "big"])
 def test_lp_grad_match_stan(ctx, gold, tag):
     x, z, W = gold[f"{tag}_x"], gold[f"{tag}_z"], gold[f"{tag}_w"]
     K = W.shape[0]
@@ -59,7 +59,7 @@ def test_lp_grad_match_stan(ctx, gold, tag):
         np.testing.assert_allclose(g[:, k], gold[f"{tag}_grad"][k], rtol=1e-7, atol=1e-8)
 
 
-@pytest.mark.parametrize("n", [5, 64, 200, 700])
+@pytest.mark.parametrize("n", [5, 64, 200, 700, 2048])
 def test_cholesky(ctx, orc, n):
     x, z, _ = synth(n, n)
     s = sampler(ctx, x, z, 2)
@@ -81,7 +81,7 @@ def test_not_positive_definite_is_reported(ctx):
         s.chains.logp()
 
 
-@pytest.mark.parametrize("n,C", [(5, 1), (64, 7), (130, 129), (300, 256), (513, 33)])
+@pytest.mark.parametrize("n,C", [(5, 1), (64, 7), (130, 129), (300, 256), (513, 33), (2048, 4096)])      # last: the BASELINE / bench shape
 def test_lp_grad_match_oracle(ctx, orc, n, C):
     x, z, rng = synth(n, 100 + n)
     W = rng.standard_normal((n, C))

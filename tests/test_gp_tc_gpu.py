@@ -30,7 +30,7 @@ def synth(n, seed):
     return x, z, rng
 
 
-@pytest.mark.parametrize("tag", ["small", "mid"])
+@pytest.mark.parametrize("tag", ["small", "mid", "big"])
 def test_lp_grad_match_stan(ctx, tag):
     gold = np.load(GOLD)
     x, z, W = gold[f"{tag}_x"], gold[f"{tag}_z"], gold[f"{tag}_w"]
@@ -44,7 +44,7 @@ def test_lp_grad_match_stan(ctx, tag):
         np.testing.assert_allclose(g[:, k], gg, rtol=0, atol=TOL * np.max(np.abs(gg)))
 
 
-@pytest.mark.parametrize("n,C", [(64, 8), (130, 136), (300, 256), (513, 33), (1024, 512)])
+@pytest.mark.parametrize("n,C", [(64, 8), (130, 136), (300, 256), (513, 33), (1024, 512), (2048, 4096)])   # last: the BASELINE / bench shape
 def test_lp_grad_match_fp64_module(ctx, n, C):
     x, z, rng = synth(n, 100 + n)
     W = rng.standard_normal((n, C))

@@ -48,6 +48,31 @@ def test_logp_grad_parity(ctx, orc, n, C):
         assert np.allclose(g[:, c], go, rtol=1e-10, atol=1e-9), (c, g[:, c], go)
 
 
+@pytest.mark.parametrize("tag", ["small", "full"])
+def test_lp_grad_match_stan(ctx, tag):
+    """builtin:linreg against the reference's own HMC backend (no oracle in between): log_prob_grad of the Stan program of
+    linreg.ipynb cell 7 (stanProgram, Stan.hs:325-344) on the vendored CmdStan 2.20 at 17 digits
+    (tests/golden/linreg_stan.npz; `full` = the BASELINE shape n = 1000, d = 10).  1e-10 relative on lp, on lp differences
+    against the constants-dropped (`~`) values, and on the gradient."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "linreg_stan.npz"))
+    X, y, Q, LP, G, LPp = (g[f"{tag}_{k}"] for k in ("X", "y", "q", "lp", "grad", "lp_propto"))
+    K = len(Q)
+    C = 64                                            # every golden point on several chains of one launch
+    s = sampler(ctx, C, X, y)
+    q0 = np.ascontiguousarray(np.stack([Q[c % K] for c in range(C)], axis=1))
+    s.chains.set_state("q", q0)
+    lp, gr = s.chains.logp_grad()
+    lp_only = s.chains.logp()
+    for c in range(C):
+        k = c % K
+        assert abs(lp[c] - LP[k]) <= 1e-10 * abs(LP[k]), (c, lp[c], LP[k])
+        assert abs(lp_only[c] - LP[k]) <= 1e-10 * abs(LP[k])
+        assert np.max(np.abs(gr[:, c] - G[k])) <= 1e-10 * max(1.0, np.max(np.abs(G[k]))), (c, gr[:, c], G[k])
+    dl, ds = lp[1:K] - lp[0], LPp[1:] - LPp[0]
+    assert np.all(np.abs(dl - ds) <= 1e-10 * np.maximum(1.0, np.abs(ds))), (dl, ds)
+
+
 def test_logp_extreme_points(ctx, orc):
     """far tails: log-space formulas stay finite where log(boost::math::pdf()) (CC.hs:226-228) underflows"""
     X, y = make_data(50, 10)
@@ -169,6 +194,9 @@ def test_errors_are_loud(ctx):
         s.chains.step("nosuchkernel", 1)
     with pytest.raises(StkError):
         s.chains.set_param("nosuchparam", 1.0)
+    Xw, yw = make_data(16, 9)                         # the module is compiled for d = 10 (used to read out of bounds)
+    with pytest.raises(StkError, match="data field X"):
+        sampler(ctx, 8, Xw, yw).chains.logp()
     big = sampler(ctx, 8, *make_data(4000, 10))
     with pytest.raises(StkError):  # 4000 rows do not fit the 227 KB staging budget
         big.chains.logp()

@@ -67,6 +67,29 @@ def test_linreg_logp_and_grad(orc):
             assert g[j] == pytest.approx(fd, rel=2e-6, abs=1e-5)
 
 
+@pytest.mark.parametrize("tag", ["small", "full"])
+def test_linreg_lp_grad_match_stan(orc, tag):
+    """C1 pin to the reference's own HMC backend: stan::model::log_prob_grad<false, true> of the Stan program Language.Stan
+    generates for linreg (linreg.ipynb cell 7; stanProgram, Stan.hs:325-344) on the vendored CmdStan 2.20, printed with 17
+    digits by oracle/stan/lp_driver.cpp (tests/golden/linreg_stan.npz, written by oracle/stan/make_golden.py linreg).
+    `full` is the BASELINE shape (n = 1000, d = 10).  Tolerance 1e-10 relative (north_star, fp64 tier) on the value, the
+    differences between points (what a sampler sees; `~` statements drop constants) and the whole gradient."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "linreg_stan.npz"))
+    X, y, Q, LP, G, LPp = (g[f"{tag}_{k}"] for k in ("X", "y", "q", "lp", "grad", "lp_propto"))
+    lps = []
+    for k in range(len(Q)):
+        lp, gr = orc.linreg_logp(X, y, Q[k])
+        lps.append(lp)
+        assert abs(lp - LP[k]) <= 1e-10 * abs(LP[k]), (k, lp, LP[k])
+        assert np.max(np.abs(gr - G[k])) <= 1e-10 * max(1.0, np.max(np.abs(G[k]))), (k, gr, G[k])
+    lps = np.array(lps)
+    # differences against the propto (constants dropped) values: the constant cancels
+    dl, ds = lps[1:] - lps[0], LPp[1:] - LPp[0]
+    assert np.all(np.abs(dl - ds) <= 1e-10 * np.maximum(1.0, np.abs(ds))), (dl, ds)
+    assert np.ptp(LP - LPp) < 1e-9 * abs(LP[0])      # Stan's two variants differ by a constant only
+
+
 def test_linreg_hmc_reversible_energy(orc):
     """leapfrog sanity: tiny eps => acceptance ~1 and |dH| small"""
     rng = np.random.default_rng(5)

@@ -36,9 +36,10 @@ def test_notebook_ir_lowers_and_compiles(name, tmp_path):
 
 
 def test_joint_lowers_to_a_loop_with_its_own_philox_slots():
-    """ccPNode (Loop ..) (CC.hs:299-302): a for-loop around the element's DAG and draw; element k uses slot s + (k+1) 2^16"""
+    """ccPNode (Loop ..) (CC.hs:299-302): a for-loop around the element's DAG and draw; element k counts its blocks from (k+1) 2^16 under the
+    PNode's own counter word (c2 ^ tag)"""
     src = ir_to_cuda(ir("joint_sim"), [], veccap=8)
-    assert "for (int i_1_0 = lo_" in src and "<< 16)" in src
+    assert "for (int i_1_0 = lo_" in src and "+ 1) << 16;" in src and ".c2 ^= 8192u;" in src
     assert "x_sim_0_2_buf" in src and "= stk::draw_normal(g_" in src and "= stk::draw_poisson(g_" in src
     assert "field out1 state f64 8" in src and "field out1_len state i32 1" in src and "field out2 state i32 8" in src
     k = ir_to_cuda(ir("joint_rw"), ["RVec"])
@@ -52,7 +53,7 @@ def test_chain_lowers_to_a_state_carrying_loop():
     """ccPNode (Chain ..) (CC.hs:314-320): name = x; for i in lo..hi { j = name; body; name = ret; }"""
     src = ir_to_cuda(ir("chain_rw"), [])
     assert "double x_sim_0_0 = 0.0;" in src and "for (int i_99_0 = lo_" in src and "const double i_99_1 = x_sim_0_0;" in src
-    assert ".c2 ^= ((unsigned)(i_99_0 - lo_" in src and "x_sim_0_0 = x_sim_1_0;" in src
+    assert ".k1 ^= (unsigned)(i_99_0 - lo_" in src and ".c2 ^= 1u;" in src and "x_sim_0_0 = x_sim_1_0;" in src
     nested = ir("chain_rw").replace("in do x_sim_1_0 <- normal i_99_1 1.0 :: P R",
                                     "in do x_sim_1_0 <- chain (1,2) i_99_1 $ \\i_98_0 i_98_1 ->\n                  do x_sim_2_0 <- normal i_98_1 1.0 :: P R\n                     return x_sim_2_0", 1)
     with pytest.raises(StkError) as e:
@@ -109,8 +110,8 @@ def test_soccer_lowering_follows_the_reference_templates():
     for f in ("field in0_tag state i32 1", "field in0_r0 state f64 1", "field in0_r1 state f64 1",
               "field in0_zv0 state i32 0", "field in0_zv0_len state i32 1"):
         assert f in src
-    # draws: slot = 256*level + 16*pointer
-    assert "g_0.slot = 256u" in src and ".slot = 272u" in src
+    # draws: the PNode's tag level << 24 | pointer << 12 in counter word c2, blocks counted from 0
+    assert f"g_0.c2 ^= {1 << 24}u; g_0.slot = 0u" in src and f".c2 ^= {(1 << 24) | (1 << 12)}u" in src
 
 
 def test_mh_kernel_shape():

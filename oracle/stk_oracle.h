@@ -84,6 +84,9 @@ int orc_coal_trans_ratio(int n, const double* s, const double* g, int n2, const 
                          double t, int lam, int nmax, double* out3);
 int orc_coal_rj_step(int* n_io, double* s, double* g, const double* y, int ny, double t, int lam, int nmax,
                      double a, double b, uint64_t seed, uint64_t chain, uint64_t step, double* info8);
+/* the same transition under the Philox layout of the stkc-generated kernel (9 PNodes of the printed IR) */
+int orc_coal_rj_step_ir(int* n_io, double* s, double* g, const double* y, int ny, double t, int lam, int nmax,
+                     double a, double b, uint64_t seed, uint64_t chain, uint64_t step, double* info8);
 void orc_coal_simulate(uint64_t seed, uint64_t chain, double t, int lam, int nmax, double a, double b,
                        int* n_out, double* s, double* g);
 long long orc_coal_rj_run(int* n, double* s, double* g, long long C, long long T, const double* y, int ny,

@@ -8,13 +8,15 @@
 //     poissonProcess_lpdf                     Data/Expression/Eval.hs:185-190
 //     lpdfs                                   Random/Distribution/Abstract.hs
 //
-// Parity status: PARITY UNPINNED against an executable reference — the
-// reference can only run this kernel through the Haskell interpreter (CC and
-// Stan lack pmf_lpdf / poissonProcess_lpdf / uniform_cdf, SURVEY 8a'), and
-// GHC is absent.  Pins that do exist: the lpdf formulas (pinned vs scipy /
-// Boost elsewhere), the closed-form log|det J| per move (checked against a
-// finite-difference Jacobian of the move maps in tests/test_coal_cpu.py), and
-// the statistical pins of rj-coal.ipynb (posterior mode of n in {2,3}).
+// Parity status: pinned to the reference's own PRINTED PROGRAM, not to an executable reference — the reference can only run
+// this kernel through the Haskell interpreter (CC and Stan lack pmf_lpdf / poissonProcess_lpdf / uniform_cdf, SURVEY 8a'),
+// and GHC is absent.  The pin: the kernel IR that `runStep` printed (rj-coal.ipynb cell 8, tests/golden/ir/coal_rj.txt)
+// is lowered node by node by the code generator (csrc/stkc.cpp) and run on B200; this restatement must agree with that
+// generated kernel transition by transition under the generated kernel's own draws (orc_coal_rj_step_ir): dimension
+// trajectory exactly, states 1e-9, log acceptance ratio / both densities / proposal ratio / log|det J| 1e-9
+// (tests/test_coal_ir_gpu.py).  Further pins: the lpdf formulas (scipy / Boost elsewhere), the closed-form log|det J| per
+// move against a finite-difference Jacobian of the move maps (tests/test_coal_cpu.py) and against the LU of the IR's block
+// Jacobian on the device, and the statistical pins of rj-coal.ipynb (posterior mode of n in {2,3}).
 //
 // The only deviation from the IR: the IR evaluates log_det of the symbolic
 // block Jacobian numerically (LU of a (2n+1+|y|+aux)^2 matrix, v_0_446);
@@ -193,6 +195,43 @@ extern "C" int orc_coal_trans_ratio(int n, const double* s, const double* g, int
 // plus a `case`, IR bindings x_show_0_0..7); only the chosen move's are used, so drawing them lazily
 // leaves the transition kernel's law unchanged.
 // info[8] = {move, j, accepted, log ratio, f(y), u or x, z, f(x)}
+// the deterministic part of one transition, given the auxiliary draws of the chosen move and the accept uniform:
+// proposal (v_0_32 .. v_0_63), both densities (v_0_97, v_0_129), proposal/Jacobian ratio (v_0_131 .. v_0_446), decision
+static int rj_apply(int* n_io, double* s, double* g, const double* y, int ny, double t, int lam, int nmax, double a, double b,
+                    int move, int j, double aux, double z, double u_accept, double* info) {
+  const int n = *n_io;
+  int n2 = n;
+  std::vector<double> s2(s, s + n), g2(g, g + n + 1);
+  if (move == 1) {            // coalMoveH: g_j' = exp(log g_j + u)
+    g2[j - 1] = std::exp(aux + std::log(g[j - 1]));                                             // v_0_33, v_0_34
+  } else if (move == 2) {     // coalMoveP: s_j' = s(j-1) + (s(j+1) - s(j-1)) u
+    double lo = bound_s(s, n, j - 1, t), hi = bound_s(s, n, j + 1, t);
+    s2[j - 1] = lo + (hi - lo) * aux;                                                           // v_0_49 .. v_0_51
+  } else if (move == 3) {     // coalMoveBirth': x ~ U(0,t), u = exp z, insert
+    j = find_sorted_insert_index(aux, s, n);                                                    // v_0_53
+    s2.insert(s2.begin() + (j - 1), aux);                                                       // v_0_54
+    g2.insert(g2.begin() + j, std::exp(z) * g[j - 1]);                                          // v_0_56 .. v_0_58
+    n2 = n + 1;
+  } else {                    // coalMoveDeath'
+    s2.erase(s2.begin() + (j - 1));                                                             // v_0_60
+    g2.erase(g2.begin() + j);                                                                   // v_0_62
+    n2 = n - 1;
+  }
+  const double fy = coal_logp(n2, s2.data(), g2.data(), y, ny, t, lam, a, b);                   // v_0_97
+  const double fx = coal_logp(n, s, g, y, ny, t, lam, a, b);                                    // v_0_129
+  Trans tr = trans_ratio(n, s, g, n2, s2.data(), g2.data(), t, lam, nmax);
+  const double logr = ((fy - fx) + (tr.lu_rev - tr.lu_fwd)) + tr.logdet;                         // v_0_448
+  const double ratio = std::fmin(1.0, std::exp(logr));                                           // v_0_450
+  const int accept = u_accept < ratio ? 1 : 0;                                                   // bernoulli, CC.hs:290
+  if (info) { info[0] = move; info[1] = j; info[2] = accept; info[3] = logr; info[4] = fy; info[5] = aux; info[6] = z; info[7] = fx; }
+  if (accept) {
+    *n_io = n2;
+    std::memcpy(s, s2.data(), sizeof(double) * n2);
+    std::memcpy(g, g2.data(), sizeof(double) * (n2 + 1));
+  }
+  return accept;
+}
+
 extern "C" int orc_coal_rj_step(int* n_io, double* s, double* g, const double* y, int ny, double t, int lam,
                                 int nmax, double a, double b, uint64_t seed, uint64_t chain, uint64_t step,
                                 double* info) {
@@ -207,41 +246,36 @@ extern "C" int orc_coal_rj_step(int* n_io, double* s, double* g, const double* y
   double ua = uA * tot, acc = 0.0; int move = 4;
   for (int i = 0; i < 4; ++i) { acc += pr[i]; if (ua < acc) { move = i + 1; break; } }
   auto dunif = [&](int lo, int hi) { int m = hi - lo + 1; int k = (int)std::floor(uC * (double)m); if (k >= m) k = m - 1; return lo + k; };
-  int n2 = n, j = 0; double aux = 0.0, z = 0.0;
-  std::vector<double> s2(s, s + n), g2(g, g + n + 1);
-  if (move == 1) {            // coalMoveH: g_j' = exp(log g_j + u)
-    j = dunif(1, n + 1); aux = -0.5 + (0.5 - (-0.5)) * uD;
-    g2[j - 1] = std::exp(aux + std::log(g[j - 1]));                                             // v_0_33, v_0_34
-  } else if (move == 2) {     // coalMoveP: s_j' = s(j-1) + (s(j+1) - s(j-1)) u
-    j = dunif(1, n); aux = 0.0 + (1.0 - 0.0) * uD;
-    double lo = bound_s(s, n, j - 1, t), hi = bound_s(s, n, j + 1, t);
-    s2[j - 1] = lo + (hi - lo) * aux;                                                           // v_0_49 .. v_0_51
-  } else if (move == 3) {     // coalMoveBirth': x ~ U(0,t), u = exp z, insert
-    aux = 0.0 + (t - 0.0) * uD;
-    double z1, z2; orc_normal2(seed, chain, step, 2, &z1, &z2); z = z1;
-    j = find_sorted_insert_index(aux, s, n);                                                    // v_0_53
-    s2.insert(s2.begin() + (j - 1), aux);                                                       // v_0_54
-    g2.insert(g2.begin() + j, std::exp(z) * g[j - 1]);                                          // v_0_56 .. v_0_58
-    n2 = n + 1;
-  } else {                    // coalMoveDeath'
-    j = dunif(1, n);
-    s2.erase(s2.begin() + (j - 1));                                                             // v_0_60
-    g2.erase(g2.begin() + j);                                                                   // v_0_62
-    n2 = n - 1;
-  }
-  const double fy = coal_logp(n2, s2.data(), g2.data(), y, ny, t, lam, a, b);                   // v_0_97
-  const double fx = coal_logp(n, s, g, y, ny, t, lam, a, b);                                    // v_0_129
-  Trans tr = trans_ratio(n, s, g, n2, s2.data(), g2.data(), t, lam, nmax);
-  const double logr = ((fy - fx) + (tr.lu_rev - tr.lu_fwd)) + tr.logdet;                         // v_0_448
-  const double ratio = std::fmin(1.0, std::exp(logr));                                           // v_0_450
-  const int accept = uB < ratio ? 1 : 0;                                                         // bernoulli, CC.hs:290
-  if (info) { info[0] = move; info[1] = j; info[2] = accept; info[3] = logr; info[4] = fy; info[5] = aux; info[6] = z; info[7] = fx; }
-  if (accept) {
-    *n_io = n2;
-    std::memcpy(s, s2.data(), sizeof(double) * n2);
-    std::memcpy(g, g2.data(), sizeof(double) * (n2 + 1));
-  }
-  return accept;
+  int j = 0; double aux = 0.0, z = 0.0;
+  if (move == 1) { j = dunif(1, n + 1); aux = -0.5 + (0.5 - (-0.5)) * uD; }
+  else if (move == 2) { j = dunif(1, n); aux = 0.0 + (1.0 - 0.0) * uD; }
+  else if (move == 3) { aux = 0.0 + (t - 0.0) * uD; double z1, z2; orc_normal2(seed, chain, step, 2, &z1, &z2); z = z1; }
+  else j = dunif(1, n);
+  return rj_apply(n_io, s, g, y, ny, t, lam, nmax, a, b, move, j, aux, z, uB, info);
+}
+
+// The same transition with the draws of the GENERATED kernel (stkc lowering of the printed IR, tests/golden/ir/coal_rj.txt):
+// `mixture'` draws the auxiliaries of all four moves every transition (PNodes x_show_0_0 .. x_show_0_7) and the accept
+// bernoulli is x_show_0_8; PNode x_<ns>_0_<P> draws with Philox counter word c2 ^ (P << 12), blocks from 0 (csrc/stkc.cpp).
+extern "C" int orc_coal_rj_step_ir(int* n_io, double* s, double* g, const double* y, int ny, double t, int lam,
+                                   int nmax, double a, double b, uint64_t seed, uint64_t chain, uint64_t step,
+                                   double* info) {
+  const int n = *n_io;
+  auto gen = [&](uint32_t P) { orc_rng r; orc_rng_init(&r, seed, chain, step); r.c2 ^= (P << 12); r.slot = 0; return r; };
+  double pr[4];
+  move_probs(n, lam, nmax, pr);
+  orc_rng r0 = gen(0); const int move = orc_draw_pmf(&r0, pr, 4);                               // x_show_0_0
+  orc_rng r1 = gen(1); const int j_rate = orc_draw_discrete_uniform(&r1, 1, n + 1);             // x_show_0_1
+  orc_rng r2 = gen(2); const double u_rate = -0.5 + (0.5 - (-0.5)) * orc_u01(&r2);              // x_show_0_2
+  orc_rng r3 = gen(3); const int j_pos = orc_draw_discrete_uniform(&r3, 1, n);                  // x_show_0_3
+  orc_rng r4 = gen(4); const double u_pos = 0.0 + (1.0 - 0.0) * orc_u01(&r4);                   // x_show_0_4
+  orc_rng r5 = gen(5); const double x_birth = 0.0 + (t - 0.0) * orc_u01(&r5);                   // x_show_0_5
+  orc_rng r6 = gen(6); const double z_birth = 0.0 + 1.0 * orc_normal(&r6);                      // x_show_0_6
+  orc_rng r7 = gen(7); const int j_death = orc_draw_discrete_uniform(&r7, 1, n);                // x_show_0_7
+  orc_rng r8 = gen(8); const double u_acc = orc_u01(&r8);                                       // x_show_0_8 = (u < p)
+  int j = move == 1 ? j_rate : move == 2 ? j_pos : move == 4 ? j_death : 0;
+  double aux = move == 1 ? u_rate : move == 2 ? u_pos : move == 3 ? x_birth : 0.0;
+  return rj_apply(n_io, s, g, y, ny, t, lam, nmax, a, b, move, j, aux, z_birth, u_acc, info);
 }
 
 // coalPrior (app/rj/Main.hs:115-122): n ~ truncated 1 nMax (poisson lam) by rejection (CC.hs:282-286),

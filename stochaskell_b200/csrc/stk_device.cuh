@@ -246,12 +246,18 @@ STK_DEV int find_sorted_insert_index(double e, const double* v, int n) {
 // ---- vectors of the generated (stkc) kernels ---------------------------------
 // A view: 1-based `at`, element stride in elements (n_chains for a state field stored [len][chain], 1 for
 // a per-thread buffer).  Matrix<.., Dynamic, 1> of the C++ backend (CC.hs:77), without ownership.
+// `at` is bounds-checked: the reference's interpreter evaluates lazily, so a printed IR may index a vector at a position that
+// exists only under the guard that uses the value (e.g. `log input!v` with v = -1 "no differing element" in the coal kernel,
+// rj-coal.ipynb cell 8 v_0_172..v_0_176); an out-of-range read yields NaN (reals) / 0 (integers) instead of touching memory.
+template <class T> STK_DEV T oob_value();
+template <> STK_DEV double oob_value<double>() { return __longlong_as_double(0x7ff8000000000000ULL); }
+template <> STK_DEV int oob_value<int>() { return 0; }
 template <class T>
 struct Vec {
   T* p; long long stride; int len;
   STK_DEV Vec() : p(nullptr), stride(1), len(0) {}
   STK_DEV Vec(T* p_, long long s_, int n_) : p(p_), stride(s_), len(n_) {}
-  STK_DEV T at(int i) const { return p[(long long)(i - 1) * stride]; }
+  STK_DEV T at(int i) const { return (i >= 1 && i <= len) ? p[(long long)(i - 1) * stride] : oob_value<T>(); }
 };
 typedef Vec<double> VecD;
 typedef Vec<int> VecI;
@@ -273,6 +279,32 @@ STK_DEV void store_vec(const Vec<T>& v, T* dst, long long stride, int cap, int* 
   const int n = cap_len(v.len, cap, err, 2);
   if (v.p != dst) for (int i = 0; i < n; ++i) dst[(long long)i * stride] = v.p[(long long)i * v.stride];
   *len_out = n;
+}
+// vector equality (`a == b` on two vectors: same length, same elements)
+template <class T>
+STK_DEV bool vec_eq(const Vec<T>& a, const Vec<T>& b) {
+  if (a.len != b.len) return false;
+  for (int i = 1; i <= a.len; ++i) if (!(a.at(i) == b.at(i))) return false;
+  return true;
+}
+// log |det A| of a dense n x n matrix stored row-major with pitch n, by LU with partial pivoting, in place (the interpreter's
+// logDet = fst . snd . invlndet, Data/Array/Abstract.hs:329-331; LOG_DET of CC.hs:420-421 covers the positive-definite case).
+// A singular matrix gives -inf.
+STK_DEV double log_abs_det(double* A, int n) {
+  double acc = 0.0;
+  for (int k = 0; k < n; ++k) {
+    int piv = k; double best = fabs(A[k * n + k]);
+    for (int i = k + 1; i < n; ++i) { const double v = fabs(A[i * n + k]); if (v > best) { best = v; piv = i; } }
+    if (!(best > 0.0)) return best == 0.0 ? neg_inf() : oob_value<double>();
+    if (piv != k) for (int j = k; j < n; ++j) { const double t = A[k * n + j]; A[k * n + j] = A[piv * n + j]; A[piv * n + j] = t; }
+    const double d = A[k * n + k];
+    acc += log(fabs(d));
+    for (int i = k + 1; i < n; ++i) {
+      const double f = A[i * n + k] / d;
+      if (f != 0.0) for (int j = k + 1; j < n; ++j) A[i * n + j] -= f * A[k * n + j];
+    }
+  }
+  return acc;
 }
 STK_DEV int find_sorted_insert_index_v(double e, const VecD& v) {     // CC.hs:192-197
   int j = v.len + 1;

@@ -26,6 +26,7 @@
 #include <cctype>
 #include <cstdio>
 #include <cstring>
+#include <functional>
 #include <map>
 #include <memory>
 #include <set>
@@ -125,13 +126,22 @@ static std::vector<Tok> lex(const std::string& src) {
 // ---------------------------------------------------------------------------------------------
 struct Ref;
 using RefP = std::shared_ptr<Ref>;
+struct Body;
+struct PCData;
 struct Ref {
-  enum K { Var, Num, Index, Extract, TagOf, Data, List } k = Var;
+  // Cond: `{ c => v, .. }` (mutually exclusive guards, Expression.hs:79-80); BlockVec: `(block array (lo,hi) [(i,ref),..] :: T)`
+  // (a 1-D BlockArray: the concatenation of its scalar / vector blocks); BlockMat: `block[[a,b],[c,d]]` (isBlockMatrix,
+  // Expression.hs:100-104); PC: PartiallyConstrained `( key -> value | i <- lo...hi )` (:82, :158-160); Let: a whole
+  // let-expression printed where a reference is expected (the DExpr bounds / keys / values inside a PartiallyConstrained)
+  enum K { Var, Num, Index, Extract, TagOf, Data, List, Cond, BlockVec, BlockMat, PC, Let } k = Var;
   std::string name;          // Var: id; Num: literal text
   RefP base;                 // Index / Extract / TagOf
-  std::vector<RefP> args;    // Index: subscripts (outermost first); Data: fields; List: elements
-  int tag = 0, field = 0;    // Extract (.tag_field), Data (C<tag>)
-  Type type;                 // Data: the annotated union type
+  std::vector<RefP> args;    // Index: subscripts (outermost first); Data: fields; List: elements; Cond: c1, v1, c2, v2, ..;
+                             // BlockVec: blocks in order; BlockMat: blocks row-major (`field` rows x `tag` columns)
+  int tag = 0, field = 0;    // Extract (.tag_field), Data (C<tag>), BlockMat (columns, rows)
+  Type type;                 // Data: the annotated union type; BlockVec: its annotation
+  std::shared_ptr<Body> let; // Let
+  std::shared_ptr<PCData> pc;
 };
 struct Def;
 struct PNode;
@@ -140,9 +150,13 @@ struct Body {                // `let defs in (do pnodes return rets | rets)`
   std::vector<PNode> pnodes;
   std::vector<RefP> rets;
 };
+struct PCData {              // one `key -> value` entry over a 1-D index range
+  std::shared_ptr<Body> key, val;
+  std::string param; RefP lo, hi;
+};
 struct Alt { std::vector<std::string> inputs; Body body; };
 struct Node {
-  enum K { Apply, Array, Fold, Case } k = Apply;
+  enum K { Apply, Array, Fold, Case, Function } k = Apply;   // Function: `\i.. -> body` (Expression.hs:204-205; interpreter only in the reference)
   std::string f;                                  // Apply name; Fold: foldl/foldr/scanl/scanr
   std::vector<RefP> args;                         // Apply args; Fold: seed, list; Case: head
   std::vector<std::string> params;                // Array: index ids; Fold: acc, elem
@@ -199,6 +213,12 @@ struct Parser {
     if (x.s == "ZMat" || x.s == "RMat") { Type m; m.k = Type::Mat; m.sub.push_back(scalarT(x.s[0] == 'Z' ? Type::Z : Type::R)); return m; }
     if (x.s == "vector") return vecT(type());
     if (x.s == "matrix") { Type m; m.k = Type::Mat; m.sub.push_back(type()); return m; }
+    if (x.s == "Array" && is("[")) {  // `Array [(lo,hi)] T`: how the 2019 build behind rj-coal.ipynb printed a 1-D array type
+      next(); expect("("); ref(); expect(","); ref(); expect(")");
+      if (accept(",")) fail("multi-dimensional Array types are not supported by the CUDA lowering");
+      expect("]");
+      return vecT(type());
+    }
     if (x.s == "Array") {            // Array lo...hi[, lo...hi] T   (1-D only)
       ref(); expect("..."); ref();
       if (accept(",")) fail("multi-dimensional Array types are not supported by the CUDA lowering");
@@ -228,7 +248,43 @@ struct Parser {
   // primary [.T_F | .?]* [! primary[.T_F]*]*
   RefP atom() {
     RefP r = std::make_shared<Ref>();
-    if (accept("(")) {
+    if (is("{")) {                                                   // Cond: { c => v, c => v }
+      next(); r->k = Ref::Cond;
+      if (!accept("}")) {
+        do { r->args.push_back(ref()); expect("=>"); r->args.push_back(ref()); } while (accept(","));
+        expect("}");
+      }
+    } else if (is("block") && is("[", 1)) {                          // block[[a,b],[c,d]]
+      next(); next(); r->k = Ref::BlockMat;
+      int rows = 0, cols = -1;
+      do {
+        expect("["); int c = 0;
+        do { r->args.push_back(ref()); ++c; } while (accept(","));
+        expect("]");
+        if (cols >= 0 && c != cols) fail("ragged block matrix");
+        cols = c; ++rows;
+      } while (accept(","));
+      expect("]");
+      r->field = rows; r->tag = cols;
+    } else if (is("(") && is("let", 1)) {                            // PartiallyConstrained: ( key -> value | i <- lo...hi )
+      next(); r->k = Ref::PC; r->pc = std::make_shared<PCData>();
+      r->pc->key = std::make_shared<Body>(letexpr()); expect("->");
+      r->pc->val = std::make_shared<Body>(letexpr());
+      if (is(",")) fail("PartiallyConstrained references with several entries are not supported by the CUDA lowering");
+      expect("|");
+      Tok i = next(); if (i.k != Tok::Id) fail("expected an index id");
+      r->pc->param = i.s; expect("<-"); r->pc->lo = ref_or_let(); expect("..."); r->pc->hi = ref_or_let();
+      if (is(",")) fail("multi-dimensional PartiallyConstrained references are not supported by the CUDA lowering");
+      expect(")");
+    } else if (is("(") && is("block", 1) && is("array", 2)) {        // (block array ([1],[n]) [([1],a),([2],b),..] :: T)
+      next(); next(); next(); r->k = Ref::BlockVec;
+      expect("("); expect("["); next(); if (is(",")) fail("only 1-D block arrays are supported"); expect("]"); expect(",");
+      expect("["); next(); expect("]"); expect(")");
+      expect("[");
+      do { expect("("); expect("["); next(); expect("]"); expect(","); r->args.push_back(ref()); expect(")"); } while (accept(","));
+      expect("]");
+      expect("::"); r->type = type(); expect(")");
+    } else if (accept("(")) {
       int tag;
       if (peek().k == Tok::Id && ctor_name(peek().s, &tag)) {       // (C<k> fields :: Union[..])
         next(); r->k = Ref::Data; r->tag = tag;
@@ -255,6 +311,18 @@ struct Parser {
       if (is(".?")) { next(); RefP e = std::make_shared<Ref>(); e->k = Ref::TagOf; e->base = r; r = e; continue; }
       break;
     }
+    return r;
+  }
+  // a let-expression where a reference is expected (DExpr printed inside a PartiallyConstrained reference)
+  Body letexpr() {
+    Body b;
+    if (accept("let")) { while (!is("in")) b.defs.push_back(def()); expect("in"); }
+    b.rets.push_back(ref());
+    return b;
+  }
+  RefP ref_or_let() {
+    if (!is("let")) return ref();
+    RefP r = std::make_shared<Ref>(); r->k = Ref::Let; r->let = std::make_shared<Body>(letexpr());
     return r;
   }
   RefP ref() {
@@ -339,8 +407,11 @@ struct Parser {
     } else if (accept("case")) {
       n.k = Node::Case; n.args.push_back(ref()); expect("of");
       n.alts = alts(false);
-    } else if (is("\\")) {
-      fail("Function nodes are not supported by the CUDA lowering");
+    } else if (is("\\")) {                           // Function: \i_1_1 .. -> body
+      next(); n.k = Node::Function;
+      while (!is("->")) { Tok i = next(); if (i.k != Tok::Id) fail("expected a lambda parameter"); n.params.push_back(i.s); }
+      expect("->");
+      n.lam = std::make_shared<Body>(body(false));
     } else {
       n.k = Node::Apply;
       size_t save = p;
@@ -368,6 +439,7 @@ struct Parser {
   }
 
   RefP last_sub_lo, last_sub_hi;   // bounds of the most recently parsed Subrange type
+  std::string input_name;          // `\input ->`: the kernel's inputs are input.0_0, input.0_1, ..
 
   PNode pnode() {
     PNode q; Tok id = next();
@@ -404,7 +476,8 @@ struct Parser {
   void dist(PNode* q) {
     Tok f = next(); if (f.k != Tok::Id) { --p; fail("expected a distribution name"); }
     q->k = PNode::Dist; q->dist = f.s;
-    if (is("(") && peek(1).k == Tok::Id && !ctor_name(peek(1).s, nullptr) && peek(1).s.find('_') == std::string::npos) {
+    if (is("(") && peek(1).k == Tok::Id && !ctor_name(peek(1).s, nullptr) && peek(1).s.find('_') == std::string::npos &&
+        !is("block", 1) && !is("let", 1)) {
       // HODist: `d (inner dist args :: P T) args :: P T'` (Show PNode, Program.hs:146)
       if (f.s != "orderedSample") fail("higher-order distributions (" + f.s + ") are not supported by the CUDA lowering");
       next();
@@ -424,7 +497,7 @@ struct Parser {
 
   Body program() {
     if (is("[") && peek(1).s == "runStep") { next(); next(); expect("]"); }
-    if (is("\\")) { next(); next(); expect("->"); }      // `\input ->` header of Show (a -> P b)
+    if (is("\\")) { next(); input_name = next().s; expect("->"); }      // `\input ->` header of Show (a -> P b)
     Body b = body(true);
     if (peek().k != Tok::End) fail("trailing input after the program");
     return b;
@@ -471,12 +544,29 @@ static UnionLayout union_layout(const std::string& prefix, const Type& u) {
 // ---------------------------------------------------------------------------------------------
 // code generator
 // ---------------------------------------------------------------------------------------------
+// a matrix kept as an expression (Eigen-style lazy evaluation): dimensions and an element accessor over C index expressions
+// (1-based); `prepare` emits, at the point of use, whatever the accessor needs in storage (products are materialised)
+struct Mat {
+  std::string rows, cols;
+  std::function<std::string(const std::string&, const std::string&)> at;
+  std::function<void()> prepare;
+  bool zeros = false, eye = false;
+};
+struct VA {                // anything that can be read like a vector: length + element accessor (1-based index expression)
+  std::string len;
+  std::function<std::string(const std::string&)> at;
+};
 struct Val {               // what an IR id denotes in the emitted code
   Type type;
   std::string expr;        // scalar: C expression; vector: name of a VecD/VecI view; union: name of a struct variable
   const Node* array = nullptr;   // un-materialised Array node (inlined at its use)
   std::vector<std::string> tuple;  // Case with several returns: one expr per member
+  std::shared_ptr<Mat> mat;        // matrix-typed definition
+  std::shared_ptr<VA> lazy;        // vector-typed definition kept as an accessor (a row of a matrix)
+  const Node* fn = nullptr;        // Function node
+  int mat_scope = -1;              // materialised array: id of the C scope that holds its storage
 };
+struct NotInlinable {};    // thrown when a lambda body that is being turned into one C expression needs a statement
 
 struct Gen {
   std::ostringstream out, decls;   // decls: per-thread vector buffers, hoisted to function scope
@@ -487,9 +577,13 @@ struct Gen {
   std::map<std::string, UnionLayout> unions;   // by type string
   std::map<std::string, std::string> union_cname;
 
-  void line(const std::string& s) { out << std::string(ind, ' ') << s << "\n"; }
-  void push() { scopes.emplace_back(); }
-  void pop() { scopes.pop_back(); }
+  bool inline_mode = false;        // lowering a lambda body into ONE expression: no statements may be emitted
+  int rename_depth = 0;            // > 0 inside a nested let-expression (its ids v_0_k clash with the enclosing block's)
+  std::vector<int> scope_ids; int next_scope_id = 0;
+  void line(const std::string& s) { if (inline_mode) throw NotInlinable(); out << std::string(ind, ' ') << s << "\n"; }
+  void push() { scopes.emplace_back(); scope_ids.push_back(next_scope_id++); }
+  void pop() { scopes.pop_back(); scope_ids.pop_back(); }
+  bool scope_live(int id) const { for (int s : scope_ids) if (s == id) return true; return false; }
   void bind(const std::string& id, const Val& v) { scopes.back()[id] = v; }
   const Val& lookup(const std::string& id) const {
     for (size_t i = scopes.size(); i-- > 0;) { auto it = scopes[i].find(id); if (it != scopes[i].end()) return it->second; }
@@ -525,26 +619,46 @@ struct Gen {
     switch (r->k) {
       case Ref::Num: { bool isreal = r->name.find_first_of(".eEIN") != std::string::npos; return scalarT(isreal ? Type::R : Type::Z); }
       case Ref::Var: return lookup(r->name).type;
-      case Ref::Index: { Type b = type_of(r->base); if (b.k != Type::Vec) die("indexing a non-vector (" + b.str() + ")"); return b.sub[0]; }
+      case Ref::Index: {
+        Type b = type_of(r->base);
+        if (b.k == Type::Mat) { if (r->args.size() == 1) return vecT(b.sub[0]); return b.sub[0]; }
+        if (b.k != Type::Vec) die("indexing a non-vector (" + b.str() + ")");
+        return b.sub[0];
+      }
       case Ref::Extract: { Type b = type_of(r->base); if (b.k == Type::Tuple) return b.sub.at(r->field); if (r->field == 0) return b; die("Extract of a non-tuple"); }
       case Ref::TagOf: return scalarT(Type::Z);
       case Ref::Data: return r->type;
-      case Ref::List: return vecT(r->args.empty() ? scalarT(Type::R) : type_of(r->args[0]));
+      case Ref::List: {
+        if (!r->args.empty() && r->args[0]->k == Ref::List) { Type m; m.k = Type::Mat; m.sub.push_back(scalarT(Type::R)); return m; }
+        return vecT(r->args.empty() ? scalarT(Type::R) : type_of(r->args[0]));
+      }
+      case Ref::Cond: return r->args.size() >= 2 ? type_of(r->args[1]) : scalarT(Type::R);
+      case Ref::BlockVec: return r->type.k == Type::Vec ? r->type : vecT(scalarT(Type::R));
+      case Ref::BlockMat: { Type m; m.k = Type::Mat; m.sub.push_back(scalarT(Type::R)); return m; }
+      case Ref::PC: return vecT(scalarT(Type::R));
+      case Ref::Let: return scalarT(Type::Z);
     }
     return Type();
+  }
+
+  Val* find_val(const std::string& name) {
+    for (size_t i = scopes.size(); i-- > 0;) { auto it = scopes[i].find(name); if (it != scopes[i].end()) return &it->second; }
+    return nullptr;
   }
 
   // scalar / view expression for a reference (ccNodeRef, CC.hs:47-60)
   // An Array comprehension used as a value (returned, stored, passed to a vector operation) is materialised once, where
   // it is first needed, into per-thread storage — the resize + loops of CC.hs:231-235; its other uses stay inlined.
   std::string materialise(const std::string& name) {
-    Val* vp = nullptr;
-    for (size_t i = scopes.size(); i-- > 0 && !vp;) { auto it = scopes[i].find(name); if (it != scopes[i].end()) vp = &it->second; }
+    if (inline_mode) throw NotInlinable();
+    Val* vp = find_val(name);
+    if (!vp->array && vp->mat_scope >= 0) return vp->expr;
     const Node& an = *vp->array;
     if (an.params.size() != 1) die("array " + name + " has " + std::to_string(an.params.size()) + " dimensions; only vectors can be materialised");
     Type et = vp->type.k == Type::Vec ? vp->type.sub[0] : scalarT(Type::R);
     if (!et.scalar()) die("array " + name + " of " + et.str() + " cannot be materialised");
     bool real = et.k == Type::R;
+    prematerialise(*an.lam);                        // arrays its body reads by index get their storage before the loop
     std::string buf = fresh(name + "_buf"), lo = fresh("lo"), n = fresh("n"), vec = fresh(name + "_m");
     const std::string& iv = an.params[0];
     decls << "  " << (real ? "double" : "int") << " " << buf << "[STK_VECCAP];\n";
@@ -563,10 +677,182 @@ struct Gen {
     for (size_t i = scopes.size(); i-- > 0;) {
       auto it = scopes[i].find(name);
       if (it == scopes[i].end()) continue;
-      if (i + 1 == scopes.size()) { it->second.array = nullptr; it->second.type = vt; it->second.expr = vec; }
+      if (i + 1 == scopes.size()) { it->second.array = nullptr; it->second.type = vt; it->second.expr = vec; it->second.mat_scope = scope_ids[i]; }
       break;
     }
     return vec;
+  }
+
+  // Before a loop is emitted: every comprehension that the loop body reads (by index, as a whole vector, through a block
+  // vector or a Function it calls) and that cannot be folded into one expression is given storage HERE, outside the loop.
+  std::set<const Body*> premat_seen;
+  void prematerialise_ref(const RefP& r) {
+    if (!r) return;
+    if (r->k == Ref::Var) {
+      Val* v = find_val(r->name);
+      if (!v) return;
+      if (v->fn && v->fn->lam) { prematerialise(*v->fn->lam); return; }
+      if (v->array) {
+        prematerialise(*v->array->lam);
+        if (v->array->params.size() == 1 && !pure_inlinable(*v->array)) {
+          // only arrays defined in the current C scope keep their storage; others are materialised where they are read
+          for (size_t i = scopes.size(); i-- > 0;) {
+            auto it = scopes[i].find(r->name);
+            if (it == scopes[i].end()) continue;
+            if (i + 1 == scopes.size()) materialise(r->name);
+            break;
+          }
+        }
+      }
+      return;
+    }
+    prematerialise_ref(r->base);
+    for (auto& a : r->args) prematerialise_ref(a);
+    if (r->let) prematerialise(*r->let);
+  }
+  void prematerialise(const Body& b) {
+    if (inline_mode || premat_seen.count(&b)) return;
+    premat_seen.insert(&b);
+    for (const Def& d : b.defs) {
+      for (auto& a : d.node.args) prematerialise_ref(a);
+      if (d.node.lam && d.node.k != Node::Array && d.node.k != Node::Function) prematerialise(*d.node.lam);
+      for (auto& al : d.node.alts) prematerialise(al.body);
+    }
+    for (auto& r : b.rets) prematerialise_ref(r);
+    premat_seen.erase(&b);
+  }
+
+  // can element `idx` of the comprehension be written as ONE C expression (no statement needed)?
+  bool pure_inlinable(const Node& an) {
+    if (an.params.size() != 1) return false;
+    std::string e;
+    return try_inline_array_at(an, "0", &e);
+  }
+  bool try_inline_array_at(const Node& a, const std::string& idx, std::string* out_e, bool want_real = false) {
+    if (a.params.size() != 1) return false;
+    const bool saved = inline_mode; const size_t depth = scopes.size();
+    inline_mode = true;
+    try {
+      push(); Val v; v.type = scalarT(Type::Z); v.expr = "(" + idx + ")"; bind(a.params[0], v);
+      for (const Def& ad : a.lam->defs) def(ad);
+      *out_e = rv(a.lam->rets.at(0), want_real);
+      pop(); inline_mode = saved;
+      return true;
+    } catch (const NotInlinable&) {
+      while (scopes.size() > depth) pop();
+      inline_mode = saved;
+      return false;
+    }
+  }
+
+  // vector-like access to a reference: a state / buffer view, a comprehension (inlined or materialised), a row of a
+  // matrix, a literal list
+  VA va(const RefP& r) {
+    VA a;
+    if (r->k == Ref::Var) {
+      const Val& v = lookup(r->name);
+      if (v.lazy) return *v.lazy;
+      if (v.array) {
+        const Node* an = v.array;
+        if (an->params.size() != 1) die("multi-dimensional array used as a vector");
+        if (pure_inlinable(*an)) {
+          a.len = "(" + rv(an->shape[0].second) + " - " + rv(an->shape[0].first) + " + 1)";
+          std::string lo = rv(an->shape[0].first);
+          a.at = [this, an, lo](const std::string& i) {
+            std::string e;
+            if (!try_inline_array_at(*an, lo == "1" ? i : "(" + i + ") + " + lo + " - 1", &e)) die("internal: array stopped being inlinable");
+            return e;
+          };
+          return a;
+        }
+        std::string m = materialise(r->name);
+        a.len = m + ".len"; a.at = [m](const std::string& i) { return m + ".at(" + i + ")"; };
+        return a;
+      }
+    }
+    if (r->k == Ref::List) {
+      std::vector<std::string> es; for (auto& e : r->args) es.push_back(rv(e, true));
+      a.len = std::to_string(es.size());
+      a.at = [es](const std::string& i) {
+        if (es.size() == 1) return es[0];
+        std::string e = es.back();
+        for (size_t k = es.size() - 1; k-- > 0;) e = "((" + i + ") == " + std::to_string(k + 1) + " ? " + es[k] + " : " + e + ")";
+        return e;
+      };
+      return a;
+    }
+    if (r->k == Ref::Index && type_of(r->base).k == Type::Mat && r->args.size() == 1) {     // M!i: row i of a matrix
+      std::shared_ptr<Mat> m = mat_of(r->base);
+      if (!inline_mode) m->prepare();
+      std::string row = rv(r->args[0]);
+      a.len = m->cols; a.at = [m, row](const std::string& j) { return m->at(row, j); };
+      return a;
+    }
+    if (r->k == Ref::BlockVec) {
+      std::vector<VA> parts; std::vector<bool> scalar;
+      for (auto& e : r->args) {
+        Type t = type_of(e);
+        if (t.scalar()) { VA p; p.len = "1"; std::string x = rv(e, true); p.at = [x](const std::string&) { return x; }; parts.push_back(p); }
+        else if (t.k == Type::Vec) parts.push_back(va(e));
+        else die("block vector element of type " + t.str() + " is not supported");
+      }
+      std::string tot;
+      for (auto& p : parts) tot += (tot.empty() ? "" : " + ") + p.len;
+      a.len = "(" + tot + ")";
+      a.at = [parts](const std::string& i) {
+        // walk the blocks: element i lives in the first block whose running end reaches i
+        std::string e = parts.back().at("(" + i + ")" + offset_of(parts, parts.size() - 1));
+        for (size_t k = parts.size() - 1; k-- > 0;) {
+          std::string end; for (size_t j = 0; j <= k; ++j) end += (j ? " + " : "") + parts[j].len;
+          e = "((" + i + ") <= " + end + " ? " + parts[k].at("(" + i + ")" + offset_of(parts, k)) + " : " + e + ")";
+        }
+        return e;
+      };
+      return a;
+    }
+    Type t = type_of(r);
+    if (t.k != Type::Vec) die("a vector was expected, got " + t.str());
+    std::string m = rv(r);
+    a.len = m + ".len"; a.at = [m](const std::string& i) { return m + ".at(" + i + ")"; };
+    return a;
+  }
+  static std::string offset_of(const std::vector<VA>& parts, size_t k) {
+    std::string o; for (size_t j = 0; j < k; ++j) o += " - " + parts[j].len;
+    return o;
+  }
+
+  // value of a guarded reference { c => v, .. } (mutually exclusive guards): nested selects; no guard true -> NaN / 0
+  std::string cond_expr(const RefP& r, bool want_real) {
+    Type t = type_of(r);
+    bool real = want_real || t.k == Type::R;
+    std::string e = real ? "stk::oob_value<double>()" : "0";
+    for (size_t i = r->args.size(); i >= 2; i -= 2)
+      e = "(" + rv(r->args[i - 2]) + " ? " + rv(r->args[i - 1], real) + " : " + e + ")";
+    return e;
+  }
+
+  // element `idx` of a PartiallyConstrained array ( key -> value | i <- lo...hi ): the value whose key equals idx
+  // (Expression.hs:82: an array known only at the positions its keys name; elsewhere unknown = NaN)
+  std::string pc_lookup(const Ref& pr, const std::string& idx) {
+    if (inline_mode) throw NotInlinable();
+    const PCData& pc = *pr.pc;
+    std::string res = fresh("pc"), i = fresh("pi"), ix = fresh("px");
+    line("double " + res + " = stk::oob_value<double>();");
+    line("{ const int " + ix + " = " + idx + ";");
+    ind += 2; push(); ++rename_depth;
+    std::string lo = rv(pc.lo), hi = rv(pc.hi);
+    line("for (int " + i + " = " + lo + "; " + i + " <= " + hi + "; ++" + i + ") {");
+    ind += 2; push();
+    Val iv; iv.type = scalarT(Type::Z); iv.expr = i; bind(pc.param, iv);
+    for (const Def& d : pc.key->defs) def(d);
+    line("if (" + rv(pc.key->rets.at(0)) + " == " + ix + ") {");
+    ind += 2; push();
+    for (const Def& d : pc.val->defs) def(d);
+    line(res + " = " + rv(pc.val->rets.at(0), true) + "; break;");
+    pop(); ind -= 2; line("}");
+    pop(); ind -= 2; line("}");
+    --rename_depth; pop(); ind -= 2; line("}");
+    return res;
   }
 
   std::string rv(const RefP& r, bool want_real = false) {
@@ -575,43 +861,73 @@ struct Gen {
       case Ref::Var: {
         const Val& v = lookup(r->name);
         if (v.array) return materialise(r->name);
+        if (v.mat || v.fn) die(r->name + " is a matrix / function: it cannot be used as a scalar or vector value here");
+        if (v.lazy) die(r->name + " is a lazily evaluated vector: it cannot be used as a stored vector here");
         if (want_real && v.type.integral()) return "(double)" + v.expr;
         return v.expr;
       }
       case Ref::Index: {
-        if (r->args.size() != 1) die("only 1-D indexing is supported");
         RefP b = r->base;
-        if (b->k == Ref::Var && lookup(b->name).array) {
-          const Node& an = *lookup(b->name).array;
-          if (an.lam->defs.empty() && an.params.size() == 1) return inline_array_at(an, rv(r->args[0]));
-          std::string e = materialise(b->name) + ".at(" + rv(r->args[0]) + ")";     // a computed array: indexed through its storage
-          if (want_real && type_of(r).integral()) return "(double)" + e;
-          return e;
+        Type bt = type_of(b);
+        if (bt.k == Type::Mat) {
+          if (r->args.size() != 2) die("a matrix row used as a scalar");
+          std::shared_ptr<Mat> m = mat_of(b);
+          m->prepare();                                          // a product among its operands gets its storage here
+          return m->at(rv(r->args[1]), rv(r->args[0]));       // printed innermost index first (showNodeRef reverses)
         }
-        std::string e = rv(b) + ".at(" + rv(r->args[0]) + ")";
+        if (r->args.size() != 1) die("only 1-D indexing of vectors is supported");
+        std::string e;
+        if (b->k == Ref::PC) e = pc_lookup(*b, rv(r->args[0]));
+        else if (b->k == Ref::BlockVec || b->k == Ref::List) e = va(b).at(rv(r->args[0]));
+        else if (b->k == Ref::Var && lookup(b->name).lazy) e = lookup(b->name).lazy->at(rv(r->args[0]));
+        else if (b->k == Ref::Var && lookup(b->name).array) {
+          const Node& an = *lookup(b->name).array;
+          std::string idx = rv(r->args[0]);
+          // a comprehension read at one index: folded into the expression when its body needs no statement, else read
+          // from its storage
+          if (!try_inline_array_at(an, idx, &e, want_real && type_of(r).integral()))
+            e = materialise(b->name) + ".at(" + idx + ")";
+        } else e = rv(b) + ".at(" + rv(r->args[0]) + ")";
         if (want_real && type_of(r).integral()) return "(double)" + e;
         return e;
       }
       case Ref::Extract: {
         if (r->base->k == Ref::Var) {
           const Val& v = lookup(r->base->name);
-          if (!v.tuple.empty()) return v.tuple.at(r->field);
-          if (r->field == 0) return v.expr;
+          std::string e;
+          if (!v.tuple.empty()) e = v.tuple.at(r->field);
+          else if (r->field == 0) e = v.expr;
+          else die("unsupported Extract");
+          if (want_real && type_of(r).integral()) return "(double)" + e;
+          return e;
         }
         die("unsupported Extract");
       }
       case Ref::TagOf: return rv(r->base) + ".tag";
       case Ref::Data: die("union construction is only supported as an ifThenElse branch or a return value");
       case Ref::List: die("list literal is only supported as a pmf argument");
+      case Ref::Cond: return cond_expr(r, want_real);
+      case Ref::BlockVec: die("a block vector can only be indexed or used as a probability table");
+      case Ref::BlockMat: die("a block matrix can only be the argument of log_det");
+      case Ref::PC: die("a partially constrained array can only be indexed");
+      case Ref::Let: {
+        // a whole let-expression in reference position: its definitions are value-numbered against the enclosing block
+        // (they restate, under their own ids, nodes the enclosing DAG already holds) and emitted under fresh C names.
+        // They are bound in the CURRENT scope: the caller (pc_lookup) opens one for them.
+        ++rename_depth;
+        for (const Def& d : r->let->defs) def(d);
+        std::string e = rv(r->let->rets.at(0), want_real);
+        --rename_depth;
+        return e;
+      }
     }
     return "";
   }
 
   // Array node evaluated at one index without materialising it (only for bodies that are a bare reference)
   std::string inline_array_at(const Node& a, const std::string& idx) {
-    if (!a.lam->defs.empty() || a.params.size() != 1) die("indexing a computed array is not supported");
-    push(); Val v; v.type = scalarT(Type::Z); v.expr = "(" + idx + ")"; bind(a.params[0], v);
-    std::string e = rv(a.lam->rets[0]); pop();
+    std::string e;
+    if (!try_inline_array_at(a, idx, &e)) die("indexing a computed array is not supported here");
     return e;
   }
 
@@ -652,18 +968,83 @@ struct Gen {
     return e + ")";
   }
 
+  // ---- value numbering -------------------------------------------------------------------------------------------------
+  // A let-expression printed in reference position (the DExprs inside a PartiallyConstrained reference) restates, under
+  // its own ids v_0_0.., nodes that the enclosing block already defines — the reference hash-conses each DAG separately
+  // (Expression.hs:301-330).  Lowering it, every definition is first looked up by (function, lowered operands, type)
+  // among the definitions already emitted in live scopes; a hit aliases the existing C variable instead of recomputing.
+  std::string key_of(const RefP& r) {
+    switch (r->k) {
+      case Ref::Num: return r->name;
+      case Ref::Var: {
+        const Val& v = lookup(r->name);
+        if (v.array || v.mat || v.fn || v.lazy) { char b[32]; snprintf(b, sizeof b, "@%p", (const void*)(v.array ? (const void*)v.array : v.fn ? (const void*)v.fn : v.mat ? (const void*)v.mat.get() : (const void*)v.lazy.get())); return b; }
+        if (!v.tuple.empty()) { std::string k = "<"; for (auto& t : v.tuple) k += t + ","; return k + ">"; }
+        return v.expr;
+      }
+      case Ref::Index: { std::string k = key_of(r->base); for (auto& a : r->args) k += "!" + key_of(a); return k; }
+      case Ref::Extract: {
+        if (r->base->k == Ref::Var) { const Val& v = lookup(r->base->name); if (!v.tuple.empty()) return v.tuple.at(r->field); if (r->field == 0) return v.expr; }
+        return key_of(r->base) + "." + std::to_string(r->tag) + "_" + std::to_string(r->field);
+      }
+      case Ref::TagOf: return key_of(r->base) + ".?";
+      case Ref::Cond: case Ref::List: case Ref::BlockVec: case Ref::BlockMat: case Ref::Data: {
+        std::string k = std::string("#") + std::to_string((int)r->k) + "[";
+        for (auto& a : r->args) k += key_of(a) + ",";
+        return k + "]";
+      }
+      default: return "";
+    }
+  }
+  std::string cse_key(const Node& n) {
+    if (n.k == Node::Apply) {
+      if (n.f == "getExternal") return "";
+      std::string k = "#cse:" + n.f + "(";
+      for (auto& a : n.args) { std::string ka = key_of(a); if (ka.empty()) return ""; k += ka + ";"; }
+      return k + ")::" + n.type.str();
+    }
+    if (n.k == Node::Case) {
+      std::string k = "#cse:case(" + key_of(n.args.at(0)) + ")";
+      for (auto& al : n.alts) {
+        if (!al.body.defs.empty() || !al.inputs.empty()) return "";
+        k += "{";
+        for (auto& r : al.body.rets) { std::string kr = key_of(r); if (kr.empty()) return ""; k += kr + ";"; }
+        k += "}";
+      }
+      return k;
+    }
+    return "";
+  }
+
   void def(const Def& d) {
+    const Node& n = d.node;
+    if (inline_mode || n.k == Node::Array || n.k == Node::Function || n.k == Node::Fold ||
+        (n.k == Node::Apply && n.f == "getExternal")) { def_impl(d); return; }
+    std::string key;
+    try { key = cse_key(n); } catch (const Error&) { key.clear(); }
+    if (rename_depth > 0) {
+      if (!key.empty()) if (Val* hit = find_val(key)) { Val v = *hit; bind(d.id, v); return; }
+      Def dd = d; dd.id = fresh(d.id);              // nested let: its ids clash with the enclosing block's, C names must not
+      def_impl(dd);
+      Val v = lookup(dd.id); bind(d.id, v);
+    } else def_impl(d);
+    if (!key.empty()) { Val v = lookup(d.id); bind(key, v); }
+  }
+
+  void def_impl(const Def& d) {
     const Node& n = d.node;
     Val v; v.type = n.type;
     if (n.k == Node::Array) {                      // kept symbolic; consumers inline it (CC.hs:231-235 materialises)
       if (v.type.k == Type::Unknown) v.type = vecT(scalarT(Type::R));
       v.array = &n; bind(d.id, v); return;
     }
+    if (n.k == Node::Function) { v.fn = &n; bind(d.id, v); return; }     // applied where it is used (poissonProcess_lpdf)
     if (n.k == Node::Fold) { fold(d); return; }
     if (n.k == Node::Case) { case_node(d); return; }
     const std::string& f = n.f;
     auto arg = [&](size_t i, bool real = false) { return rv(n.args.at(i), real); };
     bool rt = n.type.k == Type::R;
+    if (n.type.k == Type::Mat) { mat_def(d); return; }
     if (f == "getExternal") {                      // alias of a PNode's value (CC.hs:124-125 emits the draw here)
       ensure_drawn(n.args.at(0)->name);
       bind(d.id, lookup(n.args.at(0)->name)); return;
@@ -686,13 +1067,18 @@ struct Gen {
       for (size_t i = 0; i < n.args.size(); ++i) e = i ? "(" + e + op + arg(i, rt) + ")" : arg(i, rt);
     } else if (f == "/" && rt) e = "(double)" + arg(0) + " / (double)" + arg(1);          // CC.hs:133-134
     else if (f == "/") e = arg(0) + " / " + arg(1);
+    else if ((f == "==" || f == "/=") && type_of(n.args.at(0)).k == Type::Vec) {          // vector equality
+      Type t0 = type_of(n.args.at(0));
+      std::string a0 = vec_value(n.args.at(0)), a1 = vec_value(n.args.at(1));
+      e = std::string(f == "==" ? "" : "!") + "stk::vec_eq(" + a0 + ", " + a1 + ")";
+    }
     else if (const char* op = c_binop(f)) {
       bool anyreal = type_of(n.args.at(0)).k == Type::R || type_of(n.args.at(1)).k == Type::R;
       e = arg(0, anyreal) + " " + op + " " + arg(1, anyreal);
     }
     else if (f == "**") e = "pow(" + arg(0, true) + ", " + arg(1, true) + ")";             // CC.hs:155-156
     else if (f == "ifThenElse") e = arg(0) + " ? " + arg(1, rt) + " : " + arg(2, rt);      // CC.hs:141-143
-    else if (f == "negate") e = "-" + arg(0);
+    else if (f == "negate") e = "-(" + arg(0) + ")";
     else if (f == "id") e = arg(0, rt);
     else if (f == "not") e = "!" + arg(0);
     else if (f == "min" || f == "max") {
@@ -707,17 +1093,22 @@ struct Gen {
       if (a->k == Ref::Var && lookup(a->name).array) {
         const Node& an = *lookup(a->name).array;
         e = "(" + rv(an.shape[0].second) + " - " + rv(an.shape[0].first) + " + 1)";
-      } else e = arg(0) + ".len";
+      } else if (a->k == Ref::Var && lookup(a->name).lazy) e = lookup(a->name).lazy->len;
+      else e = arg(0) + ".len";
     }
-    else if (f == "findSortedInsertIndex") e = "stk::find_sorted_insert_index_v(" + arg(0, true) + ", " + arg(1) + ")";   // CC.hs:192-197
+    else if (f == "matrixCols") e = mat_of(n.args.at(0))->cols;
+    else if (f == "matrixRows") e = mat_of(n.args.at(0))->rows;
+    else if (f == "log_det") { log_det_node(d); return; }
+    else if (f == "poissonProcess_lpdf") { poisson_process_node(d); return; }
+    else if (f == "findSortedInsertIndex") e = "stk::find_sorted_insert_index_v(" + arg(0, true) + ", " + vec_value(n.args.at(1)) + ")";   // CC.hs:192-197
     else if (f == "logFactorial") e = "stk::log_factorial(" + arg(0) + ")";               // CC.hs:167-168
     else if (f == "pmf_lpdf" || f == "categorical_lpdf") {                                 // Const.hs:94
       const RefP& ps = n.args.at(1);
-      if (ps->k != Ref::List) die(f + " needs a literal probability list");
-      std::string tab = fresh("ps");
-      std::string init; for (size_t i = 0; i < ps->args.size(); ++i) init += (i ? ", " : "") + rv(ps->args[i], true);
-      line("const double " + tab + "[] = {" + init + "};");
-      e = "stk::pmf_lpdf(" + arg(0) + ", " + tab + ")";
+      if (ps->k != Ref::List && ps->k != Ref::BlockVec) die(f + " needs a literal probability list");
+      for (auto& pe : ps->args) if (!type_of(pe).scalar()) die(f + ": probability table with a non-scalar block");
+      // log ps[k] (Const.hs:94); k is a literal in the IRs the rjmc builder emits, so the table folds into a select
+      VA tab = va(ps);
+      e = "log(" + tab.at(arg(0)) + ")";
     }
     else if (f == "normals_lpdf" || f == "uniforms_lpdf" || f == "cauchys_lpdf" || f == "bernoulliLogits_lpdf" || f == "poissons_lpdf" || f == "bernoullis_lpdf") {
       // vectorised log-densities: the loop of CC.hs:214-220 (`normals_lpdf`; 1-D only, as there), summed in index order
@@ -747,17 +1138,31 @@ struct Gen {
         e = (f == "abs" ? std::string(rt ? "fabs" : "abs") : f) + "(" + arg(0, rt) + ")";    // CC.hs:229-230 (generic call)
       } else die("node `" + f + "` is not supported by the CUDA lowering");
     }
+    if (inline_mode) { v.expr = "(" + e + ")"; bind(d.id, v); return; }     // folded into the consuming expression
     line("const " + ctype(n.type) + " " + d.id + " = " + e + ";");
     v.expr = d.id; bind(d.id, v);
   }
 
+  // a vector operand as a stored view (VecD / VecI): state fields, buffers, materialised comprehensions
+  std::string vec_value(const RefP& r) {
+    if (r->k == Ref::Var && lookup(r->name).array) return materialise(r->name);
+    return rv(r);
+  }
+
   // vectors that must exist as storage: replaceIndex / insertIndex / deleteIndex (CC.hs:169-191)
   void vector_node(const Def& d) {
+    if (inline_mode) throw NotInlinable();
     const Node& n = d.node; const std::string& f = n.f;
     bool real = n.type.sub[0].k == Type::R;
+    if (f == "ifThenElse") {                        // a select between two views: no copy
+      std::string a1 = vec_value(n.args.at(1)), a2 = vec_value(n.args.at(2));
+      line("const " + ctype(n.type) + " " + d.id + " = (" + rv(n.args.at(0)) + ") ? " + a1 + " : " + a2 + ";");
+      Val v; v.type = n.type; v.expr = d.id; bind(d.id, v);
+      return;
+    }
     std::string ct = real ? "double" : "int", buf = fresh(d.id + "_buf");
     decls << "  " << ct << " " << buf << "[STK_VECCAP];\n";
-    std::string src = rv(n.args.at(0)), i = fresh("i"), ln = fresh("n");
+    std::string src = vec_value(n.args.at(0)), i = fresh("i"), ln = fresh("n");
     // every copy into per-thread storage is bounded by STK_VECCAP; an overflow sets the module's err flag
     if (f == "replaceIndex") {
       std::string j = fresh("j");
@@ -788,7 +1193,10 @@ struct Gen {
   // scan (CC.hs:256-259 builds "loc-1" from the string "idx-1"), i.e. reads one element before the seed: the interpreter
   // is the reference here.
   void fold(const Def& d) {
+    if (inline_mode) throw NotInlinable();
     const Node& n = d.node;
+    prematerialise(*n.lam);
+    if (n.args.at(1)->k == Ref::Var) if (Val* lv = find_val(n.args[1]->name)) if (lv->array) prematerialise(*lv->array->lam);
     const bool scan = n.f == "scanl" || n.f == "scanr";
     const bool left = n.f == "foldl" || n.f == "scanl";
     if (n.f != "foldl" && n.f != "foldr" && !scan) die("`" + n.f + "` is not supported by the CUDA lowering");
@@ -862,16 +1270,28 @@ struct Gen {
 
   // Case on an integer head, alternatives 1..n (CC.hs:263-273)
   void case_node(const Def& d) {
+    if (inline_mode) throw NotInlinable();
     const Node& n = d.node;
     std::vector<Type> ts;
     if (n.type.k == Type::Tuple) ts = n.type.sub; else if (n.type.k != Type::Unknown) ts.push_back(n.type);
-    else { push(); for (auto& r : n.alts[0].body.rets) ts.push_back(r->k == Ref::Num ? type_of(r) : scalarT(Type::R)); pop(); }
+    else {
+      // no annotation: take the member types from the first alternative whose returns are all typed in this scope
+      // (alternatives without definitions of their own); scalars default to R
+      const Alt& a0 = n.alts[0];
+      for (auto& r : a0.body.rets) {
+        Type t = scalarT(Type::R);
+        if (r->k == Ref::Num) t = type_of(r);
+        else if (a0.body.defs.empty() && a0.inputs.empty()) { try { t = type_of(r); } catch (const Error&) {} }
+        ts.push_back(t);
+      }
+    }
     Val v; v.type = n.type.k == Type::Unknown ? (ts.size() == 1 ? ts[0] : Type()) : n.type;
     if (v.type.k == Type::Unknown) { v.type.k = Type::Tuple; v.type.sub = ts; }
     for (size_t j = 0; j < ts.size(); ++j) {
-      if (!ts[j].scalar()) die("case alternatives returning " + ts[j].str() + " are not supported");
       std::string nm = ts.size() == 1 ? d.id : d.id + "_" + std::to_string(j);
-      line(ctype(ts[j]) + " " + nm + " = 0;");
+      if (ts[j].k == Type::Vec && ts[j].sub[0].scalar()) line(ctype(ts[j]) + " " + nm + ";");      // a view, re-pointed per alternative
+      else if (!ts[j].scalar()) die("case alternatives returning " + ts[j].str() + " are not supported");
+      else line(ctype(ts[j]) + " " + nm + " = 0;");
       v.tuple.push_back(nm);
     }
     v.expr = v.tuple[0];
@@ -883,11 +1303,263 @@ struct Gen {
       for (const Def& bd : n.alts[a].body.defs) def(bd);
       if (n.alts[a].body.rets.size() != ts.size()) die("case alternative arity mismatch");
       for (size_t j = 0; j < ts.size(); ++j)
-        line((ts.size() == 1 ? d.id : d.id + "_" + std::to_string(j)) + " = " + rv(n.alts[a].body.rets[j], ts[j].k == Type::R) + ";");
+        line((ts.size() == 1 ? d.id : d.id + "_" + std::to_string(j)) + " = " +
+             (ts[j].k == Type::Vec ? vec_value(n.alts[a].body.rets[j]) : rv(n.alts[a].body.rets[j], ts[j].k == Type::R)) + ";");
       line("break;"); pop(); ind -= 2; line("}");
     }
     line("}");
     bind(d.id, v);
+  }
+
+  // ---- matrices (ccNode's Eigen one-liners, CC.hs:155-166; the interpreter's hmatrix primitives, Const.hs:56-66) ------------
+  // One chain = one thread, so a matrix is not an Eigen object but an EXPRESSION: dimensions + an element accessor, composed
+  // node by node (zeros / eye / asRow / scalar and element-wise arithmetic / row replace-insert-delete / select) and
+  // evaluated where a consumer needs elements.  Products `<>` are the one node whose elements are re-read many times:
+  // they are materialised into per-thread storage, lazily, at the first consumer (so a product that only one branch of a
+  // guarded log_det uses is computed only when that branch runs).
+  std::shared_ptr<Mat> mat_of(const RefP& r) {
+    if (r->k == Ref::Var) {
+      const Val& v = lookup(r->name);
+      if (!v.mat) die(r->name + " is not a matrix");
+      return v.mat;
+    }
+    if (r->k == Ref::List && !r->args.empty() && r->args[0]->k == Ref::List) {        // literal [[a,b],[c,d]]
+      auto m = std::make_shared<Mat>();
+      size_t R = r->args.size(), C = r->args[0]->args.size();
+      std::vector<std::string> es;
+      for (auto& row : r->args) { if (row->k != Ref::List || row->args.size() != C) die("ragged matrix literal"); for (auto& e : row->args) es.push_back(rv(e, true)); }
+      m->rows = std::to_string(R); m->cols = std::to_string(C);
+      m->at = [es, C](const std::string& i, const std::string& j) {
+        if (es.size() == 1) return es[0];
+        std::string k = "((" + i + ") - 1) * " + std::to_string(C) + " + (" + j + ")", e = es.back();
+        for (size_t t = es.size() - 1; t-- > 0;) e = "(" + k + " == " + std::to_string(t + 1) + " ? " + es[t] + " : " + e + ")";
+        return e;
+      };
+      m->prepare = [] {};
+      return m;
+    }
+    die("a matrix was expected");
+  }
+
+  void mat_def(const Def& d) {
+    const Node& n = d.node; const std::string& f = n.f;
+    auto m = std::make_shared<Mat>();
+    m->prepare = [] {};
+    auto is_mat = [&](size_t i) { return type_of(n.args.at(i)).k == Type::Mat; };
+    auto sc = [&](size_t i) { return "(" + rv(n.args.at(i), true) + ")"; };
+    auto both_prepare = [](std::shared_ptr<Mat> a, std::shared_ptr<Mat> b) { return [a, b] { a->prepare(); if (b) b->prepare(); }; };
+    if (f == "zeros") { m->rows = "(" + rv(n.args.at(0)) + ")"; m->cols = "(" + rv(n.args.at(1)) + ")"; m->zeros = true; m->at = [](const std::string&, const std::string&) { return std::string("0.0"); }; }
+    else if (f == "eye") { m->rows = m->cols = "(" + rv(n.args.at(0)) + ")"; m->eye = true; m->at = [](const std::string& i, const std::string& j) { return "((" + i + ") == (" + j + ") ? 1.0 : 0.0)"; }; }
+    else if (f == "asRow" || f == "asColumn") {
+      VA v = va(n.args.at(0));
+      const bool row = f == "asRow";
+      m->rows = row ? "1" : v.len; m->cols = row ? v.len : "1";
+      m->at = [v, row](const std::string& i, const std::string& j) { return v.at(row ? j : i); };
+    }
+    else if (f == "negate") { auto a = mat_of(n.args.at(0)); *m = *a; m->eye = false; m->at = [a](const std::string& i, const std::string& j) { return "(-" + a->at(i, j) + ")"; }; }
+    else if (f == "id") { *m = *mat_of(n.args.at(0)); }
+    else if (f == "tr'" || f == "tr") { auto a = mat_of(n.args.at(0)); *m = *a; m->rows = a->cols; m->cols = a->rows; m->at = [a](const std::string& i, const std::string& j) { return a->at(j, i); }; }
+    else if ((f == "*" || f == "/") && n.args.size() == 2 && is_mat(0) != is_mat(1)) {       // matrix (*|/) scalar, scalar * matrix
+      const size_t mi = is_mat(0) ? 0 : 1;
+      auto a = mat_of(n.args.at(mi)); std::string s = sc(1 - mi);
+      *m = *a; m->eye = false;
+      if (f == "/" && mi != 0) die("scalar / matrix is not supported by the CUDA lowering");
+      const std::string op = f == "*" ? " * " : " / ";
+      if (!a->zeros) m->at = [a, s, op, mi](const std::string& i, const std::string& j) { return mi == 0 ? "(" + a->at(i, j) + op + s + ")" : "(" + s + op + a->at(i, j) + ")"; };
+    }
+    else if (f == "+" || f == "-" || f == "+s" || f == "*") {                                 // element-wise
+      std::vector<std::shared_ptr<Mat>> ms;
+      for (auto& a : n.args) ms.push_back(mat_of(a));
+      m->rows = ms[0]->rows; m->cols = ms[0]->cols;
+      const std::string op = f == "-" ? " - " : f == "*" ? " * " : " + ";
+      if (f != "*") {                                  // a + 0 = a: static zeros drop out of sums (not out of a - b's first operand)
+        bool all_zero = true; for (auto& a : ms) all_zero = all_zero && a->zeros;
+        m->zeros = all_zero;
+      }
+      m->prepare = [ms] { for (auto& a : ms) a->prepare(); };
+      m->at = [ms, op, f](const std::string& i, const std::string& j) {
+        std::string e;
+        for (size_t k = 0; k < ms.size(); ++k) {
+          if (f != "*" && ms[k]->zeros && (k > 0 || ms.size() > 1) && !(f == "-" && k == 0 && ms.size() == 2 && !ms[1]->zeros && false)) {
+            if (!(f == "-" && k == 0)) continue;       // keep `0 - b` explicit
+          }
+          std::string t = ms[k]->at(i, j);
+          e = e.empty() ? t : "(" + e + op + t + ")";
+        }
+        return e.empty() ? std::string("0.0") : e;
+      };
+    }
+    else if (f == "<>") {                               // matrix product: materialised at its first consumer
+      auto a = mat_of(n.args.at(0)), b = mat_of(n.args.at(1));
+      m->rows = a->rows; m->cols = b->cols;
+      m->zeros = a->zeros || b->zeros;
+      if (m->zeros) m->at = [](const std::string&, const std::string&) { return std::string("0.0"); };
+      else {
+        const bool one_row = a->rows == "1";
+        std::string buf = fresh(d.id + "_prod"), pitch = fresh("pc");
+        decls << "  double " << buf << (one_row ? "[STK_MATCAP];\n" : "[STK_MATCAP * STK_MATCAP];\n");
+        decls << "  int " << pitch << " = 0;\n";
+        auto state = std::make_shared<int>(-1);       // id of the scope the product was last materialised in
+        m->prepare = [this, a, b, buf, pitch, state, one_row] {
+          if (*state >= 0 && scope_live(*state)) return;
+          if (inline_mode) throw NotInlinable();
+          a->prepare(); b->prepare();
+          std::string i = fresh("i"), j = fresh("j"), k = fresh("k"), acc = fresh("acc"), R = fresh("R"), C = fresh("C"), K = fresh("K");
+          line("{ const int " + R + " = stk::cap_len(" + a->rows + ", " + (one_row ? "1" : "STK_MATCAP") + ", err_, 3), " + C + " = stk::cap_len(" + b->cols +
+               ", STK_MATCAP, err_, 3), " + K + " = " + a->cols + "; " + pitch + " = " + C + ";");
+          line("  for (int " + i + " = 1; " + i + " <= " + R + "; ++" + i + ") for (int " + j + " = 1; " + j + " <= " + C + "; ++" + j + ") {");
+          line("    double " + acc + " = 0.0;");
+          line("    for (int " + k + " = 1; " + k + " <= " + K + "; ++" + k + ") " + acc + " += " + a->at(i, k) + " * " + b->at(k, j) + ";");
+          line("    " + buf + "[(" + i + " - 1) * " + C + " + " + j + " - 1] = " + acc + ";");
+          line("  }");
+          line("}");
+          *state = scope_ids.back();
+        };
+        m->at = [buf, pitch](const std::string& i, const std::string& j) { return buf + "[((" + i + ") - 1) * " + pitch + " + (" + j + ") - 1]"; };
+      }
+    }
+    else if (f == "replaceIndex" || f == "insertIndex" || f == "deleteIndex") {              // row operations (CC.hs:169-191 on a matrix)
+      auto a = mat_of(n.args.at(0));
+      std::string at = "(" + rv(n.args.at(1)) + ")";
+      VA row; if (f != "deleteIndex") row = va(n.args.at(2));
+      m->cols = a->cols;
+      m->rows = f == "replaceIndex" ? a->rows : f == "insertIndex" ? "(" + a->rows + " + 1)" : "(" + a->rows + " - 1)";
+      m->prepare = [a] { a->prepare(); };
+      if (f == "replaceIndex") m->at = [a, at, row](const std::string& i, const std::string& j) { return "((" + i + ") == " + at + " ? " + row.at(j) + " : " + a->at(i, j) + ")"; };
+      else if (f == "insertIndex") m->at = [a, at, row](const std::string& i, const std::string& j) {
+        return "((" + i + ") < " + at + " ? " + a->at(i, j) + " : ((" + i + ") == " + at + " ? " + row.at(j) + " : " + a->at("(" + i + ") - 1", j) + "))"; };
+      else m->at = [a, at](const std::string& i, const std::string& j) { return "((" + i + ") < " + at + " ? " + a->at(i, j) + " : " + a->at("(" + i + ") + 1", j) + ")"; };
+    }
+    else if (f == "ifThenElse") {
+      std::string c = "(" + rv(n.args.at(0)) + ")";
+      auto a = mat_of(n.args.at(1)), b = mat_of(n.args.at(2));
+      m->rows = a->rows; m->cols = a->cols;
+      m->prepare = both_prepare(a, b);
+      m->at = [c, a, b](const std::string& i, const std::string& j) { return "(" + c + " ? " + a->at(i, j) + " : " + b->at(i, j) + ")"; };
+    }
+    else die("matrix node `" + f + "` is not supported by the CUDA lowering");
+    Val v; v.type = n.type; v.mat = m; bind(d.id, v);
+  }
+
+  // log_det (CC.hs:165-166 / Const.hs:65; log |det| by LU as the interpreter's invlndet).  The argument may be a guarded
+  // choice of block matrices (the Jacobian of a reversible-jump move, rjmcTransRatio', Program.hs:1306-1347): one branch per
+  // guard.  A (nested) block matrix is flattened to one grid of blocks, then reduced SYMBOLICALLY before anything is
+  // evaluated: a block row (column) whose only non-zero block is an identity contributes a factor +-1 to the determinant and
+  // is removed together with that block's column (row) — the same kind of rule the reference's own simplifier applies
+  // (log_det (eye) = 0, Expression.hs:1180-1181).  What is left is written into per-thread storage and LU-factorised.
+  struct Grid { int R = 0, C = 0; std::vector<std::shared_ptr<Mat>> b; std::shared_ptr<Mat>& at(int r, int c) { return b[(size_t)r * C + c]; } };
+  Grid flatten(const RefP& r) {
+    Grid g;
+    if (r->k != Ref::BlockMat) { g.R = g.C = 1; g.b.push_back(mat_of(r)); return g; }
+    const int R = r->field, C = r->tag;
+    std::vector<Grid> sub;
+    for (auto& e : r->args) sub.push_back(flatten(e));
+    std::vector<int> rh(R, 0), cw(C, 0);
+    for (int i = 0; i < R; ++i) for (int j = 0; j < C; ++j) {
+      const Grid& s = sub[(size_t)i * C + j];
+      if ((rh[i] && rh[i] != s.R) || (cw[j] && cw[j] != s.C)) die("nested block matrix whose inner partitions do not line up");
+      rh[i] = s.R; cw[j] = s.C;
+    }
+    for (int i = 0; i < R; ++i) g.R += rh[i];
+    for (int j = 0; j < C; ++j) g.C += cw[j];
+    g.b.resize((size_t)g.R * g.C);
+    int ro = 0;
+    for (int i = 0; i < R; ++i) {
+      int co = 0;
+      for (int j = 0; j < C; ++j) {
+        Grid& s = sub[(size_t)i * C + j];
+        for (int a = 0; a < s.R; ++a) for (int b = 0; b < s.C; ++b) g.at(ro + a, co + b) = s.at(a, b);
+        co += cw[j];
+      }
+      ro += rh[i];
+    }
+    return g;
+  }
+  static void reduce(Grid& g) {
+    for (bool changed = true; changed;) {
+      changed = false;
+      for (int pass = 0; pass < 2 && !changed; ++pass) {         // pass 0: rows, pass 1: columns
+        const int N = pass == 0 ? g.R : g.C, M = pass == 0 ? g.C : g.R;
+        for (int i = 0; i < N && !changed; ++i) {
+          int eye_at = -1; bool ok = true;
+          for (int j = 0; j < M && ok; ++j) {
+            const Mat& m = pass == 0 ? *g.at(i, j) : *g.at(j, i);
+            if (m.eye) { if (eye_at >= 0) ok = false; eye_at = j; }
+            else if (!m.zeros) ok = false;
+          }
+          if (!ok || eye_at < 0) continue;
+          const int dr = pass == 0 ? i : eye_at, dc = pass == 0 ? eye_at : i;
+          Grid h; h.R = g.R - 1; h.C = g.C - 1;
+          for (int r = 0; r < g.R; ++r) for (int c = 0; c < g.C; ++c) if (r != dr && c != dc) h.b.push_back(g.at(r, c));
+          g = h; changed = true;
+        }
+      }
+    }
+  }
+  void log_det_branch(const std::string& out_var, const RefP& r) {
+    Grid g = flatten(r);
+    reduce(g);
+    if (g.R == 0 && g.C == 0) { line(out_var + " = 0.0;"); return; }            // nothing but identity blocks
+    if (g.R == 0 || g.C == 0) die("log_det of a block matrix that is not square in blocks after reduction");
+    need_matbuf = true;
+    for (auto& m : g.b) m->prepare();
+    std::vector<std::string> ro(g.R + 1), co(g.C + 1);
+    std::string decl = "int ";
+    for (int i = 0; i <= g.R; ++i) { ro[i] = fresh("ro"); decl += ro[i] + " = " + (i ? ro[i - 1] + " + " + g.at(i - 1, 0)->rows : std::string("0")) + ", "; }
+    for (int j = 0; j <= g.C; ++j) { co[j] = fresh("co"); decl += co[j] + " = " + (j ? co[j - 1] + " + " + g.at(0, j - 1)->cols : std::string("0")) + (j < g.C ? ", " : ";"); }
+    line(decl);
+    const std::string& dim = ro[g.R];
+    line("if (" + dim + " != " + co[g.C] + " || " + dim + " > STK_MATCAP) { *err_ = 3; } else {");
+    ind += 2;
+    std::string t = fresh("t");
+    line("for (int " + t + " = 0; " + t + " < " + dim + " * " + dim + "; ++" + t + ") mat_[" + t + "] = 0.0;");
+    for (int i = 0; i < g.R; ++i) for (int j = 0; j < g.C; ++j) {
+      const Mat& m = *g.at(i, j);
+      if (m.zeros) continue;
+      std::string a = fresh("i"), b = fresh("j");
+      if (m.eye) line("for (int " + a + " = 1; " + a + " <= " + m.rows + "; ++" + a + ") mat_[(" + ro[i] + " + " + a + " - 1) * " + dim + " + " + co[j] + " + " + a + " - 1] = 1.0;");
+      else line("for (int " + a + " = 1; " + a + " <= " + m.rows + "; ++" + a + ") for (int " + b + " = 1; " + b + " <= " + m.cols + "; ++" + b + ") mat_[(" + ro[i] + " + " + a + " - 1) * " + dim + " + " + co[j] + " + " + b + " - 1] = " + m.at(a, b) + ";");
+    }
+    line(out_var + " = stk::log_abs_det(mat_, " + dim + ");");
+    ind -= 2; line("}");
+  }
+  bool need_matbuf = false;
+  void log_det_node(const Def& d) {
+    if (inline_mode) throw NotInlinable();
+    const RefP& a = d.node.args.at(0);
+    line("double " + d.id + " = stk::oob_value<double>();");
+    if (a->k == Ref::Cond) {
+      for (size_t i = 0; i + 1 < a->args.size(); i += 2) {
+        line(std::string(i ? "else " : "") + "if (" + rv(a->args[i]) + ") {");
+        ind += 2; push(); log_det_branch(d.id, a->args[i + 1]); pop(); ind -= 2;
+        line("}");
+      }
+    } else { line("{"); ind += 2; push(); log_det_branch(d.id, a); pop(); ind -= 2; line("}"); }
+    Val v; v.type = scalarT(Type::R); v.expr = d.id; bind(d.id, v);
+  }
+
+  // poissonProcess_lpdf y t rate mean (evalNode, Eval.hs:185-190): sum_i log (rate y_i) - mean, the rate being a Function
+  // node of the block, applied to each observed point in order
+  void poisson_process_node(const Def& d) {
+    if (inline_mode) throw NotInlinable();
+    const Node& n = d.node;
+    const RefP& fr = n.args.at(2);
+    if (fr->k != Ref::Var || !lookup(fr->name).fn) die("poissonProcess_lpdf: the rate must be a Function node");
+    const Node& fn = *lookup(fr->name).fn;
+    if (fn.params.size() != 1) die("poissonProcess_lpdf: the rate takes one argument");
+    prematerialise(*fn.lam);
+    std::string y = vec_value(n.args.at(0)), k = fresh("k"), acc = fresh("acc");
+    line("double " + acc + " = 0.0;");
+    line("for (int " + k + " = 1; " + k + " <= " + y + ".len; ++" + k + ") {");
+    ind += 2; push();
+    std::string p = fresh(fn.params[0]);
+    line("const double " + p + " = " + y + ".at(" + k + ");");
+    Val pv; pv.type = scalarT(Type::R); pv.expr = p; bind(fn.params[0], pv);
+    for (const Def& bd : fn.lam->defs) def(bd);
+    line(acc + " += log(" + rv(fn.lam->rets.at(0), true) + ");");
+    pop(); ind -= 2; line("}");
+    line("const double " + d.id + " = " + acc + " - " + rv(n.args.at(3), true) + ";");
+    Val v; v.type = scalarT(Type::R); v.expr = d.id; bind(d.id, v);
   }
 
   // ---- PNodes (ccPNode', CC.hs:276-321) ------------------------------------------------------------
@@ -945,9 +1617,12 @@ struct Gen {
     else if (f == "beta") e = "stk::draw_beta(" + g + ", " + arg(0) + ", " + arg(1) + ")";
     else if (f == "pmf" || f == "categorical") {                                                          // :292-293
       const RefP& ps = q.args.at(0);
-      if (ps->k != Ref::List) die("pmf needs a literal probability list");
+      if (ps->k != Ref::List && ps->k != Ref::BlockVec) die("pmf needs a literal probability list");
       std::string tab = fresh("ps"), init;
-      for (size_t i = 0; i < ps->args.size(); ++i) init += (i ? ", " : "") + rv(ps->args[i], true);
+      for (size_t i = 0; i < ps->args.size(); ++i) {
+        if (!type_of(ps->args[i]).scalar()) die("pmf: probability table with a non-scalar block");
+        init += (i ? ", " : "") + rv(ps->args[i], true);
+      }
       line("const double " + tab + "[] = {" + init + "};");
       e = "stk::draw_pmf(" + g + ", " + tab + ", " + std::to_string(ps->args.size()) + ")";
     } else die("distribution `" + f + "` is not supported by the CUDA lowering");
@@ -1209,6 +1884,7 @@ static std::string generate(const std::string& ir, const std::string& input_type
   std::string name = opt.count("name") ? opt["name"] : "ir";
   int veccap = opt.count("veccap") ? atoi(opt["veccap"].c_str()) : 64;
   int block = opt.count("block") ? atoi(opt["block"].c_str()) : 128;
+  int matcap = opt.count("matcap") ? atoi(opt["matcap"].c_str()) : 64;
   bool kernel = !its.empty();
   if (level < 0) {                                  // find the Dummy level of the inputs: i_0_k (compileCC) or i_9_k (runStep)
     level = ir.find("i_9_0") != std::string::npos ? 9 : 0;
@@ -1265,6 +1941,10 @@ static std::string generate(const std::string& ir, const std::string& input_type
     } else die("kernel input of type " + t.str() + " is not supported by the CUDA lowering");
     g.bind(id, v); in_names.push_back(id);
   }
+  if (!P.input_name.empty() && !its.empty()) {      // `\input ->`: the inputs are the members of one tuple, input.0_k
+    Val iv; iv.type.k = Type::Tuple; iv.type.sub = its; iv.tuple = in_names;
+    g.bind(P.input_name, iv);
+  }
   // ---- the transition body ----
   g.ind = 4;
   g.body(prog);
@@ -1302,13 +1982,25 @@ static std::string generate(const std::string& ir, const std::string& input_type
       rec << " " << nm;
     }
   }
+  // probe=<id>,<id>..: the value of these top-level definitions after the last transition of a launch, as state fields
+  // probe<k> — how the parity tests read intermediate quantities (log acceptance ratio, densities) of a generated kernel
+  if (opt.count("probe")) {
+    std::istringstream ps(opt["probe"]); std::string id; int k = 0;
+    while (std::getline(ps, id, ',')) {
+      if (id.empty()) continue;
+      auto r = std::make_shared<Ref>(); r->k = Ref::Var; r->name = id;
+      std::string nm = "probe" + std::to_string(k++);
+      out_fields.push_back({nm, false, "1"});
+      g.line("((double*)a.field[F_" + nm + "])[chain] = " + g.rv(r, true) + ";");
+    }
+  }
   for (auto& f : out_fields) fields.push_back(f);
   { Field ef{"err", true, "1"}; ef.kind = "work"; fields.push_back(ef); }   // overflow flag, checked by the runtime after the launch
   if ((int)fields.size() > 24) die("too many state fields");
 
   std::ostringstream o;
   o << "// generated by stkc (libstk_cuda, Language.CUDA lowering) — do not edit\n";
-  o << "#define STK_VECCAP " << veccap << "\n";
+  o << "#define STK_VECCAP " << veccap << "\n#define STK_MATCAP " << matcap << "\n";
   o << "#include \"stk_device.cuh\"\nusing namespace stk;\n";
   o << "enum {";
   for (size_t i = 0; i < fields.size(); ++i) o << (i ? ", " : " ") << "F_" << fields[i].name << " = " << i;
@@ -1324,6 +2016,7 @@ static std::string generate(const std::string& ir, const std::string& input_type
   o << "  const long long chain = (long long)blockIdx.x * blockDim.x + threadIdx.x;\n  if (chain >= a.n_chains) return;\n";
   o << "  int* const err_ = (int*)a.field[F_err];\n";
   o << load.str() << g.decls.str();
+  if (g.need_matbuf) o << "  double mat_[STK_MATCAP * STK_MATCAP];\n";
   if (kernel) {
     o << "  for (long long t_ = 0; t_ < a.n_steps; ++t_) {\n";
     o << "    Rng rng; rng.init(a.seed, (u64)(a.chain0 + chain), a.step0 + (u64)t_);\n";

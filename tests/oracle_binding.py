@@ -60,6 +60,8 @@ class Oracle:
         l.orc_coal_trans_ratio.argtypes = [I, P, P, I, P, P, D, I, I, P]
         l.orc_coal_rj_step.restype = I
         l.orc_coal_rj_step.argtypes = [P, P, P, P, I, D, I, I, D, D, U, U, U, P]
+        l.orc_coal_rj_step_ir.restype = I
+        l.orc_coal_rj_step_ir.argtypes = [P, P, P, P, I, D, I, I, D, D, U, U, U, P]
         l.orc_coal_simulate.restype = None
         l.orc_coal_simulate.argtypes = [U, U, D, I, I, D, D, P, P, P]
         l.orc_coal_rj_run.restype = C.c_longlong
@@ -219,6 +221,15 @@ class Oracle:
         nn = C.c_int(int(n)); info = np.empty(8)
         self.l.orc_coal_rj_step(C.byref(nn), _p(s), _p(g), _p(y), len(y), k["t"], k["lam"], k["nmax"], k["a"], k["b"],
                                 seed, chain, step, _p(info))
+        return nn.value, info
+
+    def coal_rj_step_ir(self, n, s, g, y, seed, chain, step, **kw):
+        """coal_rj_step with the draws of the stkc-generated kernel (PNodes x_show_0_0 .. 0_8 of the printed IR)"""
+        k = dict(self.COAL, **kw)
+        y = np.ascontiguousarray(y, dtype=np.float64)
+        nn = C.c_int(int(n)); info = np.empty(8)
+        self.l.orc_coal_rj_step_ir(C.byref(nn), _p(s), _p(g), _p(y), len(y), k["t"], k["lam"], k["nmax"], k["a"], k["b"],
+                                   seed, chain, step, _p(info))
         return nn.value, info
 
     def coal_simulate(self, seed, chain, **kw):

@@ -155,8 +155,52 @@ def test_parse_errors_carry_position():
     assert "line" in str(e.value)
 
 
-def test_coal_kernel_ir_is_refused_not_mislowered():
-    """the 719-line coal kernel IR (rj-coal.ipynb cell 8) contains PartiallyConstrained / Function nodes that only the
-    reference's interpreter can run (SURVEY 8a'); the lowering must refuse it (the hand-tuned builtin:coal covers C2)"""
-    with pytest.raises(StkError):
-        ir_to_cuda(ir("coal_rj"), ["Z", "RVec", "RVec", "RVec"])
+def test_coal_kernel_ir_lowers_and_compiles(tmp_path):
+    """the 719-line coal RJ kernel IR (rj-coal.ipynb cell 8): Function nodes + poissonProcess_lpdf (Eval.hs:185-190), a
+    PartiallyConstrained array, guarded references, block vectors, the symbolic block Jacobian and log_det
+    (rjmcTransRatio', Program.hs:1306-1347) — only the reference's interpreter can run it; stkc lowers it and NVRTC compiles it"""
+    src = ir_to_cuda(ir("coal_rj"), ["Z", "RVec", "RVec", "RVec"], name="coal_rj_ir", probe="v_0_448")
+    # the nine PNodes of mixture' + the accept bernoulli, each with its own Philox counter word
+    for p in range(9):
+        assert f".c2 ^= {p << 12}u;" in src
+    assert "stk::draw_pmf(g_0, ps_1, 4)" in src and "stk::draw_bernoulli(g_" in src
+    # Case returning (Z, RVec, RVec, RVec): views re-pointed per alternative
+    assert "VecD v_0_63_1;" in src and "v_0_63_1 = v_0_54;" in src
+    # value numbering: the let-expressions printed inside the PartiallyConstrained reference alias the enclosing block's
+    # nodes, so the lookup reads the proposal's change points directly
+    assert "= v_0_63_1.at(pi_" in src and "for (int pi_" in src
+    # poissonProcess_lpdf: the rate Function applied to every event, log-summed, minus the integral
+    assert "acc_" in src and "stk::find_sorted_insert_index_v(i_1_1_" in src and "const double v_0_96 = acc_" in src
+    # log_det of the guarded block Jacobians: one LU per move kind, identity blocks (191 x 191 for the events) reduced away
+    assert src.count("stk::log_abs_det(mat_, ") == 4 and "double mat_[STK_MATCAP * STK_MATCAP];" in src
+    assert "i_0_3.len" in src and "mat_[" in src and "v_0_285)" not in src.split("double v_0_446")[1].split("const double v_0_447")[0]
+    assert "field probe0 state f64 1" in src and "field err work i32 1" in src
+    cubin = compile_source(src, str(tmp_path))
+    assert os.path.getsize(cubin) > 20000
+
+
+def test_matrix_nodes_lower_lazily():
+    """matrix nodes as expressions (CC.hs:155-166 uses Eigen objects): eye / zeros / asRow / scalar arithmetic / <> /
+    row replacement / log_det of a block matrix; a block row [0 I] is removed before anything is evaluated"""
+    text = ("let v_0_0 = vectorSize i_0_0 :: Z\n"
+            "    v_0_1 = eye v_0_0 :: matrix R\n"
+            "    v_0_2 = zeros v_0_0 v_0_0 :: matrix R\n"
+            "    v_0_3 = asRow i_0_0 :: matrix R\n"
+            "    v_0_4 = v_0_3 * 2.0 :: matrix R\n"
+            "    v_0_5 = replaceIndex v_0_1 1 v_0_4!1 :: matrix R\n"
+            "    v_0_6 = v_0_3 <> v_0_5 :: matrix R\n"
+            "    v_0_7 = log_det block[[v_0_5,v_0_2],[v_0_2,v_0_1]] :: R\n"
+            "    v_0_8 = v_0_6!1!1 + v_0_7 :: R\n"
+            "    v_0_9 = replaceIndex i_0_0 1 v_0_8 :: RVec\n"
+            " in [v_0_9]\n")
+    src = ir_to_cuda(text, ["RVec"], name="mats")
+    assert src.count("stk::log_abs_det(mat_, ") == 1
+    assert "_prod_" in src and "STK_MATCAP" in src
+    lu = src.split("double v_0_7")[1].split("stk::log_abs_det")[0]
+    assert lu.count("for (int i_") == 1            # only the v_0_5 block is written: [0 I] row and column were removed
+
+
+def test_unsupported_matrix_node_is_refused():
+    with pytest.raises(StkError) as e:
+        ir_to_cuda("let v_0_0 = eye 3 :: matrix R\n    v_0_1 = qr v_0_0 :: matrix R\n    v_0_2 = log_det v_0_1 :: R\n in [v_0_2]\n", [])
+    assert e.value.code == -5 and "qr" in str(e.value)

@@ -24,6 +24,7 @@
 #include "../../include/stk_cuda.h"
 
 #include <cctype>
+#include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <functional>
@@ -1875,10 +1876,16 @@ static std::map<std::string, std::string> parse_opts(const char* o) {
   return m;
 }
 
+#include "stkc_grad.inc"
+
 static std::string generate(const std::string& ir, const std::string& input_types, const char* options) {
   auto opt = parse_opts(options);
   Parser P(ir);
   Body prog = P.program();
+  if (opt.count("mode") && opt["mode"] == "density") {     // log-density + gradient + HMC module of a model `P t`
+    GradGen gg;
+    return gg.generate(prog, opt);
+  }
   std::vector<Type> its = parse_types(input_types);
   int level = opt.count("level") ? atoi(opt["level"].c_str()) : -1;
   std::string name = opt.count("name") ? opt["name"] : "ir";

@@ -31,6 +31,17 @@ METRIC = "mcmc_chain_transitions_per_sec"
 UNIT = "transitions/s"
 
 
+def ncu_facts(workload):
+    """counter facts of a workload's dominant kernel from the committed ncu export (profiles/r02_ncu_facts.json)"""
+    p = os.path.join(ROOT, "profiles", "r02_ncu_facts.json")
+    if not os.path.exists(p):
+        return None
+    try:
+        return json.load(open(p)).get(workload)
+    except Exception:
+        return None
+
+
 def measured_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -143,6 +154,8 @@ class LinregHMC:
         # per logp+grad evaluation per chain: 8(nd+n) data + 8*2P state
         self.bytes_per_eval = 8 * (self.n * self.d + self.n) + 8 * 2 * (self.d + 2)
         self.bytes_per_transition = (self.L + 1) * self.bytes_per_eval
+        # fp64 work of one logp+grad evaluation: n (2d + 3) fused multiply-adds (dot product, residual, d + 1 gradient sums, r^2)
+        self.fp64_flops_per_transition = (self.L + 1) * 2.0 * self.n * (2 * self.d + 3)
         self.describe = (f"C1 linreg n={self.n} d={self.d}, static HMC eps={self.eps} L={self.L} unit_e "
                          f"(configs[0] shape at 4096 chains/GPU)")
 
@@ -198,6 +211,7 @@ class LinregNUTS(LinregHMC):
         self.post = np.array(g["post_mean"]); self.post[-1] = np.log(self.post[-1])
         self.evals = float(np.mean(g["n_leapfrog_mean"])) + 1.0   # leapfrogs + the evaluation that opens a transition
         self.bytes_per_transition = self.evals * self.bytes_per_eval
+        self.fp64_flops_per_transition = self.evals * 2.0 * self.n * (2 * self.d + 3)
         self.describe = (f"C1 linreg n={self.n} d={self.d}, NUTS diag_e max_depth 10 after warm-up (hmcStan default; adapted "
                          f"eps={self.eps0:.3f}, {self.evals - 1:.2f} leapfrogs/transition in the reference's own runs)")
         self.roofline_note = ("algorithmic bytes = (mean leapfrogs per transition of the reference's sampler + 1) x 88,192 B; "
@@ -240,8 +254,6 @@ class CoalRJ:
     state_fields = ("n", "s", "g")
     # state read+write 2*492 B + one pass over y (191*8 B) per transition
     bytes_per_transition = 2 * 492 + 1528
-    # ncu (profiles/r01_coal_rj.md): dram read+write of coal_rj2_4 per launch of 4096 chains x 2000 transitions
-    ncu_traffic_bytes = 525034496 + 4091904
     roofline_note = ("latency-bound kernel (one warp per scheduler, 4.95 cycles per issued instruction): the chain state "
                      "lives in shared memory for the whole launch and a move re-evaluates only the <= 2 segments it "
                      "touches, so the SURVEY 8d accounting unit (2,512 algorithmic B/transition = full state r/w + a pass "
@@ -593,9 +605,7 @@ class GPRMH:
     def roofline(self, C, T, ms_per_launch, peaks):
         tf = C * T * self.flops_per_transition / (ms_per_launch * 1e-3) / 1e12
         peak = peaks.get("bf16_tflops_sustained") or peaks.get("bf16_tflops") or 1365.0
-        # dram__bytes_read + dram__bytes_write of one gpr_chol launch: 159 MB + 15.8 MB per matrix in the ncu capture of
-        # profiles/r01_gpr.md (592 chains), scaled to this launch's chains (the kernel is persistent: per-matrix traffic is flat)
-        return dict(bound="tensor", achieved=tf, peak=peak, unit="TFLOP/s", frac=tf / peak, traffic=int(C * (158.7e6 + 15.8e6)),
+        return dict(bound="tensor", achieved=tf, peak=peak, unit="TFLOP/s", frac=tf / peak, traffic=None,
                     kernel="gpr_chol", peak_source=peaks["source"], useful_flops_per_transition_per_chain=self.flops_per_transition,
                     fp64_pipe_peak_tflops=37.0, frac_of_fp64_pipe=tf / 37.0,
                     note="useful flops = n^3/3 per chain and transition (SURVEY 8d, the Cholesky; covariance exps and the solve not "
@@ -604,7 +614,166 @@ class GPRMH:
                          "construction, `frac_of_fp64_pipe` is the meaningful one")
 
 
-WORKLOADS = {"gp_hmc_tc": GPHMCTC, "linreg_hmc": LinregHMC, "linreg_nuts": LinregNUTS, "coal_rj": CoalRJ, "birats_hmc": BiratsHMC, "birats_nuts": BiratsNUTS, "dp_gibbs": DPGibbs, "gp_hmc": GPHMC, "gpr_mh": GPRMH}
+
+class LinregHMCIR(LinregHMC):
+    """C1 through the CODE GENERATOR: the same model as `linreg_hmc`, but the module is generated from the model's IR
+    (tests/golden/ir/linreg_model.txt -> stk_ir_to_cuda mode=density: density + reverse-mode gradient + fused static HMC,
+    csrc/stkc_grad.inc) instead of the hand-tuned builtin:linreg; same data, same chains, same Philox stream."""
+    name = "linreg_hmc_ir"
+    symbol = "stk_ir_hmc"
+    generated_from = "linreg_hmc"
+    logpdf_populations = None
+    data_keys = ("x_stan_0_0", "x_stan_0_4")
+
+    def __init__(self):
+        super().__init__()
+        from stochaskell_b200 import model_to_module
+        ir = open(os.path.join(ROOT, "tests", "golden", "ir", "linreg_model.txt")).read()
+        assert self.n == 1000 and self.d == 10
+        self.module = model_to_module(ir, self.data_keys, name="linreg_ir", slices=int(os.environ.get("STK_IR_SLICES", "12")))
+        self.describe = self.describe.replace("C1 linreg", "C1 linreg, module GENERATED from the model IR (stkc gradient lowering),")
+
+    def data(self):
+        return dict(x_stan_0_0=self.X, x_stan_0_4=self.y)
+
+
+class CoalRJIR(CoalRJ):
+    """C2 through the CODE GENERATOR: the kernel IR that `runStep` printed for `coal t 'rjmc' coalMove' t` (rj-coal.ipynb
+    cell 8, tests/golden/ir/coal_rj.txt) lowered by stkc — one thread per chain, the reference's own node-by-node evaluation
+    (full re-evaluation of both densities, 2 x 191 sorted searches, LU of the block Jacobian) — against the hand-tuned
+    builtin:coal on the same model: the generated-vs-hand-tuned ratio."""
+    name = "coal_rj_ir"
+    kernel = "step"
+    symbol = "stk_ir_step"
+    generated_from = "coal_rj"
+    transitions_per_step = 100
+    burnin = 200
+    diag_thin = 10
+    state_fields = ("in0", "in1", "in1_len", "in2", "in2_len")
+    e2e_fields = ("in0", "in1", "in1_len", "in2", "in2_len")
+    ncu_traffic_bytes = None
+    roofline_note = ("generated kernel, one thread per chain: state vectors are read from HBM / L2 through strided views, every "
+                     "transition re-evaluates both densities in full as the printed IR does; bound: latency of one thread per chain")
+
+    def __init__(self):
+        super().__init__()
+        from stochaskell_b200 import ir_to_cuda
+        ir = open(os.path.join(ROOT, "tests", "golden", "ir", "coal_rj.txt")).read()
+        self.module = ir_to_cuda(ir, ["Z", "RVec", "RVec", "RVec"], name="coal_rj_ir")
+        self.describe = self.describe.replace("C2 coal-mining RJMCMC (rj-coal)", "C2 coal-mining RJMCMC, kernel GENERATED from the printed IR of rj-coal.ipynb cell 8 (stkc)")
+
+    def data(self):
+        return {}
+
+    def init_state(self, C, chain0):
+        st = super().init_state(C, chain0)
+        n = st["n"].reshape(1, C).astype(np.int32)
+        return dict(in0=n, in1=st["s"], in1_len=n.copy(), in2=st["g"], in2_len=(n + 1).astype(np.int32),
+                    in3=np.ascontiguousarray(np.repeat(self.y.reshape(-1, 1), C, axis=1)), in3_len=np.full((1, C), len(self.y), dtype=np.int32))
+
+    def cpu_run(self, orc, state, T, seed, chain0, step0, nthreads):
+        return orc.coal_rj_run(state["in0"].reshape(-1), state["in1"], state["in2"], self.y, T, seed, chain0, step0, nthreads)
+
+
+class SoccerRJ:
+    """The one program for which the reference's OWN generated C++ exists: `soccer n 'rjmcC' soccerJump` (rj.ipynb cell 10),
+    a reversible jump between a Poisson and a negative-binomial model of n = 1040 match scores.  GPU arm: the kernel stkc
+    generates from the same printed IR (tests/golden/ir/soccer_rj.txt), 4096 chains.  CPU arm (`kind: reference`): the
+    program Language.CC emitted, compiled as compileCC compiles it (oracle/_ref/rj_soccer_plain), one chain per host core —
+    (i) spawned once per transition with its state as text, exactly compileCC's closure (CC.hs:494-498), and (ii) its main()
+    called in a loop inside one process (oracle/ref_soccer_loop.cc): arithmetic + text formatting without the spawn."""
+    name = "soccer_rj"
+    kernel = "step"
+    symbol = "stk_ir_step"
+    dtype = "f64"
+    chains = 4096
+    transitions_per_step = 50
+    ny = 1040
+    state_fields = ("in0_tag", "in0_r0", "in0_r1")
+    e2e_fields = ("in0_tag", "in0_r0", "in0_r1")
+    diag_thin = 5
+    diag_warmup = 50
+    cpu_kind = "reference"
+    stan_exe = os.path.join(ROOT, "oracle", "_ref", "rj_soccer_loop")
+    roofline_note = ("generated kernel, one thread per chain; algorithmic bytes = union state r/w (tag, lambda, kappa) + one pass over "
+                     "the 1040 int32 scores per transition; the scores are per-chain state read through a strided view, both "
+                     "models' likelihoods (poisson and negative-binomial lpdf: lgamma, log) are evaluated per transition: fp64 "
+                     "special-function issue bound")
+
+    def __init__(self):
+        from stochaskell_b200 import ir_to_cuda
+        rng = np.random.default_rng(20261104)
+        self.y = rng.poisson(2.6, self.ny).astype(np.int32)
+        ir = open(os.path.join(ROOT, "tests", "golden", "ir", "soccer_rj.txt")).read()
+        self.module = ir_to_cuda(ir, ["Union[(R, ZVec), (R, R, ZVec)]"], name="soccer_rj")
+        self.bytes_per_transition = 2 * (4 + 8 + 8) + 4 * self.ny
+        self.describe = (f"soccer RJ (rj.ipynb): Poisson vs negative-binomial model of n={self.ny} scores, kernel generated by stkc from "
+                         f"the IR of `soccer n `rjmcC` soccerJump`, {self.chains} chains/GPU")
+
+    def data(self):
+        return {}
+
+    def params(self):
+        return {}
+
+    def init_state(self, C, chain0):
+        rng = np.random.default_rng(55 + chain0)
+        tag = rng.integers(0, 2, C).astype(np.int32)
+        lam = rng.uniform(2.3, 2.9, C)
+        kap = np.where(tag == 1, rng.uniform(0.005, 0.1, C), 0.0)
+        return dict(in0_tag=tag.reshape(1, C), in0_r0=lam.reshape(1, C), in0_r1=kap.reshape(1, C),
+                    in0_zv0=np.ascontiguousarray(np.repeat(self.y.reshape(-1, 1), C, axis=1)),
+                    in0_zv0_len=np.full((1, C), self.ny, dtype=np.int32))
+
+    def cpu_run(self, orc, state, T, seed, chain0, step0, nthreads):
+        C = state["in0_tag"].shape[1]
+        for c in range(C):
+            t, k = int(state["in0_tag"][0, c]), float(state["in0_r1"][0, c])
+            for s_ in range(T):
+                t, k, _ = orc.soccer_rj_step(t, float(state["in0_r0"][0, c]), k, self.y, seed, chain0 + c, step0 + s_)
+            state["in0_tag"][0, c] = t; state["in0_r1"][0, c] = k
+
+    def reference_baseline(self, nt):
+        """the reference's own generated program on the host cores, one chain per core"""
+        loop = self.stan_exe
+        plain = os.path.join(ROOT, "oracle", "_ref", "rj_soccer_plain")
+        if not os.path.exists(loop):
+            return None
+        line = "0 2.6 " + str(self.ny) + " " + " ".join(str(int(v)) for v in self.y) + "\n"
+        # (ii) in-process loop
+        T = 4000
+        t0 = time.perf_counter()
+        procs = [subprocess.Popen([loop, str(T)], stdin=subprocess.PIPE, stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True) for _ in range(nt)]
+        for pr in procs:
+            pr.stdin.write(line); pr.stdin.close()
+        rate = 0.0
+        for pr in procs:
+            tok = pr.stdout.read().split(); pr.wait()
+            rate += int(tok[0]) / max(float(tok[1]), 1e-9)
+        dt_loop = time.perf_counter() - t0
+        # (i) one process per transition, state through text (compileCC's closure)
+        spawn_rate = None
+        if os.path.exists(plain):
+            from concurrent.futures import ThreadPoolExecutor
+            Ts = 150
+
+            def chain(_):
+                st = line
+                for _t in range(Ts):
+                    st = subprocess.run([plain], input=st, capture_output=True, text=True).stdout
+                return Ts
+            t0 = time.perf_counter()
+            with ThreadPoolExecutor(nt) as ex:
+                done = sum(ex.map(chain, range(nt)))
+            spawn_rate = done / (time.perf_counter() - t0)
+        return dict(value=rate, unit=UNIT, cores=nt, kind="reference", spawn_per_transition=spawn_rate,
+                    sample=(f"oracle/_ref/rj_soccer_loop: the C++ that Language.CC generated for this kernel (rj.ipynb cell 10), built as "
+                            f"compileCC builds it (-O2), {nt} processes x {T} transitions of one chain each with main() called in a loop "
+                            f"(in-process time as each reports it, {dt_loop:.1f} s wall) = `value`; `spawn_per_transition` = the same program "
+                            f"spawned once per transition with text state exactly as compileCC's closure (CC.hs:494-498), {nt} chains x 150 transitions"))
+
+
+WORKLOADS = {"linreg_hmc_ir": LinregHMCIR, "coal_rj_ir": CoalRJIR, "soccer_rj": SoccerRJ, "gp_hmc_tc": GPHMCTC, "linreg_hmc": LinregHMC, "linreg_nuts": LinregNUTS, "coal_rj": CoalRJ, "birats_hmc": BiratsHMC, "birats_nuts": BiratsNUTS, "dp_gibbs": DPGibbs, "gp_hmc": GPHMC, "gpr_mh": GPRMH}
 DEFAULT_WORKLOAD = "coal_rj"
 
 
@@ -762,11 +931,14 @@ def logpdf_arm(args, wl, rank, world, local, torch, dist):
                      "shared by the chains of a CTA and staged in shared memory, so the figure exceeds physical DRAM traffic")
 
 
-def run_native(args, wl, rank, world, local, torch, dist):
-    """One workload on this rank's GPU; returns the result dict on rank 0 (None elsewhere)."""
+def run_native(args, wl, rank, world, local, torch, dist, light=False):
+    """One workload on this rank's GPU; returns the result dict on rank 0 (None elsewhere).  light = timing only (no
+    diagnostics, no logpdf leg, no clock sampling): the chains-per-GPU sweep."""
     from stochaskell_b200 import Sampler, diag_finish, lib
     dev = torch.device("cuda", local)
     C, K, W = (args.chains or getattr(wl, "chains", 4096)), args.steps, args.warmup
+    if args.scaling == "strong":
+        C = max(1, C // world)                    # the configuration's chain count is the TOTAL; every GPU takes its share
     T = args.transitions if args.transitions > 0 else getattr(wl, "transitions_per_step", 100)
     kernel = args.kernel or wl.kernel
     chain0 = rank * C
@@ -791,7 +963,7 @@ def run_native(args, wl, rank, world, local, torch, dist):
     with torch.cuda.stream(stream):
         if getattr(wl, "burnin", 0):
             ch.step(kernel, wl.burnin)          # reach the stationary mix of dimensions before timing
-        clocks = ClockSampler(local) if rank == 0 else None
+        clocks = ClockSampler(local) if rank == 0 and not light else None
         if clocks:
             clocks.start()                      # nvidia-smi needs ~0.2 s to come up: start it before the warm-up
         for _ in range(W):
@@ -856,11 +1028,31 @@ def run_native(args, wl, rank, world, local, torch, dist):
         te = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(te, op=dist.ReduceOp.MAX)
-        e2e = dict(value=world * C * T * K / float(te[0]), unit=UNIT, h2d_bytes_per_step=h2d, d2h_bytes_per_step=d2h)
+        e2e = dict(value=world * C * T * K / float(te[0]), unit=UNIT, h2d_bytes_per_step=h2d, d2h_bytes_per_step=d2h,
+                   transitions_per_round_trip=T)
+        # the reference's own loop shape: ONE transition per round trip (runCC / compileCC's closure, CC.hs:494-498: state in,
+        # one transition, state out)
+        T_keep, T = T, 1
+        K1 = max(K, 20)
+        for _ in range(2):
+            e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(K1):
+            e2e_step()
+        barrier()
+        t1 = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t1, op=dist.ReduceOp.MAX)
+        T = T_keep
+        e2e["one_transition_per_round_trip"] = dict(value=world * C * K1 / float(t1[0]), unit=UNIT, steps=K1,
+                                                    us_per_round_trip=float(t1[0]) * 1e6 / K1)
 
     # ---- cross-chain diagnostics: the ONE collective of the path (R-hat/ESS moments) --
     diag = None
     try:
+        if light:
+            raise RuntimeError("skipped (light run)")
         thin = getattr(wl, "diag_thin", 4)
         ch.step(kernel, getattr(wl, "diag_warmup", 300))  # move off the synthetic init before judging mixing
         nd = getattr(wl, "diag_draws", 32)
@@ -885,7 +1077,7 @@ def run_native(args, wl, rank, world, local, torch, dist):
         diag = dict(error=str(e)[:200])
 
     logpdf = None
-    if getattr(wl, "logpdf_populations", None) and not args.no_e2e:
+    if getattr(wl, "logpdf_populations", None) and not args.no_e2e and not light:
         try:
             logpdf = logpdf_arm(args, wl, rank, world, local, torch, dist)
         except Exception as e:
@@ -897,11 +1089,28 @@ def run_native(args, wl, rank, world, local, torch, dist):
     alg_bytes = C * T * wl.bytes_per_transition
     achieved = alg_bytes / (ms_per_launch * 1e-3) / 1e9
     roofline = wl.roofline(C, T, ms_per_launch, peaks) if hasattr(wl, "roofline") else dict(bound="hbm", achieved=achieved, peak=peaks["hbm_gbs"], unit="GB/s", frac=achieved / peaks["hbm_gbs"],
-                    traffic=getattr(wl, "ncu_traffic_bytes", None), kernel=wl.symbol if not args.kernel else f"{wl.module[8:]}_{kernel}",
+                    traffic=None, kernel=wl.symbol if not args.kernel else f"{wl.module[8:]}_{kernel}",
                     peak_source=peaks["source"],
                     algorithmic_bytes_per_transition=wl.bytes_per_transition,
                     note=getattr(wl, "roofline_note", "observed data is shared by all chains and staged in shared "
                                  "memory once per launch, so algorithmic bytes exceed physical DRAM traffic"))
+    # what the hardware counters say bounds the kernel: read from the committed ncu export of this workload (profiles/,
+    # written by scripts/ncu_facts.py from an `ncu --set full` capture; carries the commit it was taken at) — never typed in
+    facts = ncu_facts(wl.name)
+    if facts:
+        per = facts.get("dram_bytes_per_chain_transition")
+        if per is not None:
+            roofline["traffic"] = int(per * C * T)
+        roofline["ncu"] = {k: facts[k] for k in ("commit", "kernel", "chains", "transitions", "duration_us", "dram_gbs", "issue_slots_busy_pct",
+                                                 "eligible_warps_per_scheduler", "warps_active_pct", "fp64_pipe_pct", "tensor_pipe_pct",
+                                                 "registers", "top_stall") if k in facts}
+    if hasattr(wl, "fp64_flops_per_transition"):
+        # algorithmic fp64 work against the DFMA pipe (148 SMs x 64 DFMA / clk at the SM clock sampled under load)
+        mhz = (clk or {}).get("sm_mhz") or 1965.0
+        fp64_peak = 148 * 64 * 2 * mhz * 1e6 / 1e12
+        tf = value / world * wl.fp64_flops_per_transition / 1e12
+        roofline["fp64_pipe"] = dict(achieved_tflops=tf, peak_tflops=fp64_peak, frac_of_fp64_pipe=tf / fp64_peak,
+                                     flops_per_transition=wl.fp64_flops_per_transition, sm_mhz=mhz)
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
         from tests.oracle_binding import oracle
@@ -917,8 +1126,8 @@ def run_native(args, wl, rank, world, local, torch, dist):
             cpu = dict(value=v, unit=UNIT, cores=nt, kind=wl_kind(wl),
                        sample=f"{Cs} chains x {Ts} transitions of the same workload on {nt} host threads ({dt:.1f} s)")
     return dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=K, warmup=W, ms_per_step=ms_per_launch,
-                higher_is_better=True, scaling="weak", vs_baseline=None, dtype=wl.dtype, data="synthetic",
-                config=dict(workload=wl.describe, chains_per_gpu=C, transitions_per_step=T, parallelism=f"chains-sharded x{world}",
+                higher_is_better=True, scaling=args.scaling, vs_baseline=None, dtype=wl.dtype, data="synthetic",
+                config=dict(workload=wl.describe, chains_per_gpu=C, chains_total=C * world, transitions_per_step=T, parallelism=f"chains-sharded x{world}",
                             l2="flushed (256 MiB memset) before every step, outside the per-step CUDA events",
                             wall_ms_per_step_incl_flush=wall_ms / K),
                 roofline=roofline, cpu_baseline=cpu, e2e=e2e, gpu_launches=int(launches), clocks=clk, diagnostics=diag,
@@ -937,6 +1146,11 @@ def main():
     ap.add_argument("--kernel", default="", help="transition kernel variant of the module (e.g. rj16, rj8)")
     ap.add_argument("--chains", type=int, default=0, help="chains per GPU (0 = the workload's configuration: 4096, birats 1024)")
     ap.add_argument("--transitions", type=int, default=0, help="fused transitions per step (0 = workload default)")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: the workload's chains PER GPU (BASELINE's 4096 chains on every GPU); strong: that many chains in TOTAL, "
+                         "split over the GPUs (4096 -> 512 per GPU at 8)")
+    ap.add_argument("--chains-sweep", default="auto", help="comma list of chains-per-GPU values timed after the headline workload "
+                    "(auto = 16384,65536 for the default workload at N = 1; none = off)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     args = ap.parse_args()
@@ -965,6 +1179,20 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     out = run_native(args, wl, rank, world, local, torch, dist)
+    # occupancy sweep of the headline kernel: the same step at more chains per GPU (the 4096-chain configuration fills about
+    # half of a B200 with a latency-bound kernel; this shows where the throughput saturates)
+    sweep = {}
+    sweep_list = ([16384, 65536] if (args.chains_sweep == "auto" and args.workload == DEFAULT_WORKLOAD and world == 1 and not args.chains
+                                     and not args.kernel and args.transitions <= 0) else
+                  [int(v) for v in args.chains_sweep.split(",") if v.strip().isdigit()])
+    for Cs in sweep_list:
+        a2 = argparse.Namespace(**vars(args)); a2.chains = Cs; a2.no_e2e = True; a2.no_cpu_baseline = True; a2.steps = max(3, min(args.steps, 5))
+        r = run_native(a2, WORKLOADS[args.workload](), rank, world, local, torch, dist, light=True)
+        if r is not None:
+            sweep[str(Cs)] = dict(value=r["value"], ms_per_step=r["ms_per_step"], gpu_launches=r["gpu_launches"])
+    if rank == 0 and sweep:
+        out["config"]["chains_per_gpu_sweep"] = dict({str(out["config"]["chains_per_gpu"]): dict(value=out["value"], ms_per_step=out["ms_per_step"])}, **sweep)
+        out["gpu_launches"] += sum(v["gpu_launches"] for v in sweep.values())
     also = [w for w in WORKLOADS if w != args.workload] if (args.also == "auto" and args.workload == DEFAULT_WORKLOAD
                                                           and not args.kernel and args.transitions <= 0) \
         else [w for w in args.also.split(",") if w in WORKLOADS and w != args.workload]
@@ -978,6 +1206,32 @@ def main():
         if extra:
             out["gpu_launches"] += sum(v["gpu_launches"] for v in extra.values())
             out["also"] = extra
+            # the driver keeps `config` verbatim: a compact copy of every other workload's headline numbers lives there
+            # [device-timed transitions/s, e2e transitions/s, roofline.frac (algorithmic), worst-parameter ESS/s, R-hat max,
+            #  fraction of the fp64 pipe or null, cpu baseline transitions/s, cpu baseline kind]
+            def compact(r):
+                d = r.get("diagnostics") or {}
+                rf = r.get("roofline") or {}
+                cb = r.get("cpu_baseline") or {}
+                return [r.get("value"), (r.get("e2e") or {}).get("value"), rf.get("frac"), d.get("ess_per_sec_min"), d.get("rhat_max"),
+                        (rf.get("fp64_pipe") or {}).get("frac_of_fp64_pipe", rf.get("frac_of_fp64_pipe")), cb.get("value"), cb.get("kind")]
+            out["config"]["also"] = {k: compact(v) for k, v in extra.items()}
+            out["config"]["also_columns"] = ["transitions_per_s", "e2e_transitions_per_s", "roofline_frac_algorithmic", "ess_per_s_min",
+                                             "rhat_max", "frac_of_fp64_pipe", "cpu_baseline_transitions_per_s", "cpu_baseline_kind"]
+            # generated (stkc) kernels against the hand-tuned module of the same model
+            allr = dict(extra, **{args.workload: out})
+            gen = {}
+            for k in allr:
+                src = getattr(WORKLOADS[k], "generated_from", None)
+                if src in allr and allr[src].get("value"):
+                    gen[k] = dict(hand_tuned=src, ratio=allr[k]["value"] / allr[src]["value"])
+            if gen:
+                out["config"]["generated_vs_hand_tuned"] = gen
+        d0 = out.get("diagnostics") or {}
+        out["config"]["sampler_note"] = ("transitions/s is kernel throughput; whether the configured sampler MIXES is in diagnostics.rhat_max "
+                                         "(static HMC at the benchmark's eps = 0.01 / 0.02, L = 10 and the random-walk samplers do not "
+                                         "converge within the recorded draws; the NUTS workloads do, and carry the ESS/s)")
+        out["config"]["ess_per_sec_min"] = d0.get("ess_per_sec_min"); out["config"]["rhat_max"] = d0.get("rhat_max")
         print(json.dumps(out), file=real_stdout, flush=True)
     if world > 1:
         dist.destroy_process_group()

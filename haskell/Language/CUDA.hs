@@ -12,10 +12,12 @@
 -- every generated file (CC.hs:400-402) — plus the input types, and drives the C-ABI of include/stk_cuda.h.
 --
 -- NOTE: GHC is not available in the build image of this repository, so this module is written against the reference's
--- sources (Data.Program, Data.Expression, Data.Expression.Const) but has NOT been compiled; the same calls are
--- exercised from Python (stochaskell_b200/api.py) by the test suite.  INTEGRATION.md lists what a maintainer adds.
+-- sources (Data.Program, Data.Expression, Data.Expression.Const) but has NOT been compiled; every call it makes, the
+-- state layout (flattenInput / unflattenOutput = stochaskell_b200/layout.py, tests/test_layout_cpu.py) and both entry
+-- shapes (compileCUDA's closure on values = api.CompiledKernel; hmcCUDA on a conditioned model = api.hmcCUDA with IR text)
+-- are exercised from Python by the test suite.  INTEGRATION.md lists what a maintainer adds.
 module Language.CUDA
-  ( compileCUDA, runCUDA, hmcCUDA, CudaMethod(..), CudaEngine(..), defaultCudaMethod, stanDefaultMethod
+  ( compileCUDA, runCUDA, hmcCUDA, hmcCUDAModule, CudaMethod(..), CudaEngine(..), defaultCudaMethod, stanDefaultMethod
   , StkCtx, StkModule, StkChains, withCtx
   ) where
 
@@ -25,7 +27,9 @@ import Data.Either.Utils (fromRight')
 import Data.Expression
 import Data.Expression.Const
 import Data.Expression.Eval (evalTuple, emptyEnv)
-import Data.List (intercalate)
+import Data.List (intercalate, isPrefixOf)
+import qualified Data.Map as Map
+import Data.Maybe (fromJust)
 import Data.Program
 import Foreign
 import Foreign.C.String
@@ -51,6 +55,8 @@ foreign import ccall unsafe "stk_chains_destroy" c_chains_destroy :: StkChains -
 foreign import ccall unsafe "stk_set_data"     c_set_data     :: StkChains -> CInt -> Ptr () -> CSize -> IO CInt
 foreign import ccall unsafe "stk_set_state"    c_set_state    :: StkChains -> CInt -> Ptr () -> CSize -> CInt -> IO CInt
 foreign import ccall unsafe "stk_get_state"    c_get_state    :: StkChains -> CInt -> Ptr () -> CSize -> IO CInt
+foreign import ccall unsafe "stk_device_ptr"   c_device_ptr   :: StkChains -> CInt -> Ptr (Ptr ()) -> Ptr CSize -> IO CInt
+foreign import ccall unsafe "stk_num_params"   c_num_params   :: StkChains -> IO CInt
 foreign import ccall unsafe "stk_set_param"    c_set_param    :: StkChains -> CString -> CDouble -> IO CInt
 foreign import ccall safe   "stk_step"         c_step         :: StkChains -> CInt -> Int64 -> Ptr () -> IO CInt
 foreign import ccall safe   "stk_simulate"     c_simulate     :: StkChains -> Ptr () -> IO CInt
@@ -106,17 +112,56 @@ flattenInput k t cs = case t of
   SubrangeT t' _ _ -> flattenInput k t' cs
   ArrayT _ [_] RealT -> [FieldR nm (transposeTo cap $ map toDouble . toList <$> cs), lenField nm]
   ArrayT _ [_] _     -> [FieldZ nm (transposeTo cap $ map (fromIntegral . toInteger) . toList <$> cs), lenField nm]
-  UnionT tss ->
-    FieldZ (nm ++"_tag") [[c | Tagged c _ <- cs]] :
-    concat [ slotFields (nm ++"_"++ slot) ty [ if c == ctor then Just (fs !! j) else Nothing | Tagged c fs <- cs ]
-           | (slot, ty, ctor, j) <- unionSlots tss ]
+  UnionT tss -> unionFields nm tss cs
   _ -> error $ "Language.CUDA: input of type "++ show t ++" is not supported"
   where nm = "in"++ show k
         cap = maximum (length . toList <$> cs)
         lenField n = FieldZ (n ++"_len") [[length (toList c) | c <- cs]]
         transposeTo n rows = [ [ if i < length r then r !! i else 0 | r <- rows ] | i <- [0..n-1] ]
-        slotFields = error "slotFields: one Field per slot, Nothing -> 0 (see flattenInput in stochaskell_b200/api.py)"
-        unionSlots = error "unionSlots: (slot name, type, constructor, field index) in first-occurrence order"
+
+-- | kind of a union field as the lowering classifies it (csrc/stkc.cpp union_layout): r / z scalars, rv / zv vectors
+slotKind :: Type -> String
+slotKind RealT = "r"
+slotKind IntT  = "z"
+slotKind (SubrangeT t _ _) = slotKind t
+slotKind (ArrayT _ [_] t) = slotKind t ++ "v"
+slotKind t = error $ "Language.CUDA: union field of type "++ show t ++" is not supported"
+
+-- | the slots of a union, in first-occurrence order, and for every constructor the slot of each of its fields:
+-- field j of constructor c that is the i-th field of its kind IN THAT CONSTRUCTOR uses slot <kind><i>; constructors share
+-- slots (stochaskell_b200/layout.py union_slots is the same function; tests/test_layout_cpu.py pins it to the lowering)
+unionSlots :: [[Type]] -> ([(String, Type)], [[Int]])
+unionSlots tss = foldl ctor ([], []) tss
+  where ctor (slots, cmap) ts =
+          let (slots', fmap, _) = foldl field (slots, [], []) ts in (slots', cmap ++ [fmap])
+        field (slots, fmap, used) t =
+          let k = slotKind t
+              i = length (filter (== k) used)
+              name = k ++ show i
+          in case lookup name (zip (map fst slots) [0..]) of
+               Just si -> (slots, fmap ++ [si], used ++ [k])
+               Nothing -> (slots ++ [(name, t)], fmap ++ [length slots], used ++ [k])
+
+-- | one Field (two for a vector: data + length) per slot; a chain whose constructor does not use the slot holds 0 / empty
+slotFields :: String -> Type -> [Maybe ConstVal] -> [Field]
+slotFields name t ms = case slotKind t of
+  "r"  -> [FieldR name [[maybe 0 toDouble m | m <- ms]]]
+  "z"  -> [FieldZ name [[maybe 0 (fromIntegral . toInteger) m | m <- ms]]]
+  "rv" -> [FieldR name (pad [maybe [] (map toDouble . toList) m | m <- ms]), lens]
+  _    -> [FieldZ name (pad [maybe [] (map (fromIntegral . toInteger) . toList) m | m <- ms]), lens]
+  where lens = FieldZ (name ++"_len") [[maybe 0 (length . toList) m | m <- ms]]
+        pad :: Num a => [[a]] -> [[a]]
+        pad rows = let n = maximum (1 : map length rows)
+                   in [ [ if i < length r then r !! i else 0 | r <- rows ] | i <- [0..n-1] ]
+
+-- | fields of a union-typed input: tag + slots
+unionFields :: String -> [[Type]] -> [ConstVal] -> [Field]
+unionFields nm tss cs =
+  FieldZ (nm ++"_tag") [[c | Tagged c _ <- cs]] :
+  concat [ slotFields (nm ++"_"++ sname) sty
+             [ case [fs !! j | (j, s) <- zip [0..] (cmap !! c), s == si] of { (v:_) -> Just v; [] -> Nothing } | Tagged c fs <- cs ]
+         | (si, (sname, sty)) <- zip [0..] slots ]
+  where (slots, cmap) = unionSlots tss
 
 -- | compile a probabilistic program to a resident GPU module (compileCC's counterpart, CC.hs:465-498).
 -- The closure runs `n` fused transitions of every chain in `xs` and returns the new states; with a single chain and
@@ -152,7 +197,58 @@ compileCUDA prog = do
             i <- c_module_field m cn
             withArrayLen (realToFrac <$> concat rows :: [CDouble]) $ \len p ->
               check ("stk_set_state "++ name) $ c_set_state ch i (castPtr p) (fromIntegral $ 8 * len) 0
-        downloadStates = error "downloadStates: stk_get_state per field, inverse of flattenInput"
+
+-- | readCC's counterpart (CC.hs:446-456): the state fields of output k of type t, downloaded with stk_get_state, back to
+-- one ConstVal per chain — the inverse of 'flattenInput' (stochaskell_b200/layout.py unflatten_output)
+downloadStates :: StkModule -> StkChains -> [Type] -> Int -> IO [[ConstVal]]
+downloadStates m ch ts nChains = do
+  cols <- forM (zip [0..] ts) $ \(k,t) -> unflattenOutput m ch nChains ("in"++ show (k :: Int)) t
+  return $ foldr (zipWith (:)) (repeat []) cols        -- [output][chain] -> [chain][output]
+
+getZ :: StkModule -> StkChains -> Int -> String -> IO [[Int]]          -- [element][chain]
+getZ m ch nChains name = withCString name $ \cn -> do
+  i <- c_module_field m cn
+  len <- fieldLength ch i nChains 4
+  allocaArray (len * nChains) $ \(p :: Ptr Int32) -> do
+    check ("stk_get_state "++ name) $ c_get_state ch i (castPtr p) (fromIntegral $ 4 * len * nChains)
+    chunk nChains . map fromIntegral <$> peekArray (len * nChains) p
+
+getR :: StkModule -> StkChains -> Int -> String -> IO [[Double]]
+getR m ch nChains name = withCString name $ \cn -> do
+  i <- c_module_field m cn
+  len <- fieldLength ch i nChains 8
+  allocaArray (len * nChains) $ \(p :: Ptr CDouble) -> do
+    check ("stk_get_state "++ name) $ c_get_state ch i (castPtr p) (fromIntegral $ 8 * len * nChains)
+    chunk nChains . map realToFrac <$> peekArray (len * nChains) p
+
+-- | per-chain length of a state field: its byte size (stk_device_ptr) / element size / chains
+fieldLength :: StkChains -> CInt -> Int -> Int -> IO Int
+fieldLength ch i nChains esize = alloca $ \pp -> alloca $ \pb -> do
+  check "stk_device_ptr" $ c_device_ptr ch i pp pb
+  bytes <- peek pb
+  return $ fromIntegral bytes `div` (esize * nChains)
+
+chunk :: Int -> [a] -> [[a]]
+chunk _ [] = []
+chunk k xs = let (a,b) = splitAt k xs in a : chunk k b
+
+unflattenOutput :: StkModule -> StkChains -> Int -> String -> Type -> IO [ConstVal]
+unflattenOutput m ch n nm t = case t of
+  IntT  -> map fromIntegral . head <$> getZ m ch n nm
+  RealT -> map fromDouble . head <$> getR m ch n nm
+  SubrangeT t' _ _ -> unflattenOutput m ch n nm t'
+  ArrayT _ [_] RealT -> do
+    rows <- getR m ch n nm; [lens] <- getZ m ch n (nm ++"_len")
+    return [ fromList [ fromDouble (rows !! i !! c) | i <- [0 .. l-1] ] | (c,l) <- zip [0..] lens ]
+  ArrayT _ [_] _ -> do
+    rows <- getZ m ch n nm; [lens] <- getZ m ch n (nm ++"_len")
+    return [ fromList [ fromIntegral (rows !! i !! c) | i <- [0 .. l-1] ] | (c,l) <- zip [0..] lens ]
+  UnionT tss -> do
+    [tags] <- getZ m ch n (nm ++"_tag")
+    let (slots, cmap) = unionSlots tss
+    slotVals <- forM slots $ \(sname, sty) -> unflattenOutput m ch n (nm ++"_"++ sname) sty
+    return [ Tagged c [ slotVals !! si !! chain | si <- cmap !! c ] | (chain, c) <- zip [0..] tags ]
+  _ -> error $ "Language.CUDA: output of type "++ show t ++" is not supported"
 
 -- | sample a probabilistic program via 'compileCUDA' (runCC's counterpart, CC.hs:459-462)
 runCUDA :: (ExprTuple s, ExprTuple t) => (s -> P t) -> s -> IO t
@@ -193,10 +289,58 @@ defaultCudaMethod = CudaSample
 stanDefaultMethod :: Int -> CudaMethod
 stanDefaultMethod n = defaultCudaMethod { numSamples = n, numWarmup = n, hmcStepSize = 1, engine = CudaNuts }
 
--- | static HMC on a builtin module ("builtin:linreg", ...): draws[sample][param][chain] on the unconstrained scale.
--- hmcStan / hmcStanInit (Stan.hs:493-500) return [t]; here every chain's draws come back, chains x draws.
-hmcCUDA :: CudaMethod -> String -> [(String, [Double])] -> Maybe [Double] -> IO [[[Double]]]
-hmcCUDA CudaSample{..} spec dat initq = withCtx 0 $ \ctx ->
+-- | hmcStan's counterpart in the reference's own shape (runStan :: StanMethod -> P t -> Maybe t -> IO [t], Stan.hs:443;
+-- hmcStan / hmcStanInit, Stan.hs:493-500): the conditioned model goes in, chains x draws of `t` come out.
+--   * the program is printed with showPBlock and lowered by stk_ir_to_cuda in `mode=density` (csrc/stkc_grad.inc): data =
+--     the PNodes of the PBlock's `given` map, parameters = the others (stanProgram's split, Stan.hs:325-344);
+--   * the observed values are uploaded as the data fields named after their PNodes (stanDump's role, Stan.hs:346-363);
+--   * the unconstrained draws come back through the module's `qmap` lines (the constraining transform per parameter
+--     block) and are turned into `t` by evaluating the program's return expressions (stanRead + evalPBlock, Stan.hs:365-371, 487).
+hmcCUDA :: forall t. (ExprTuple t) => CudaMethod -> P t -> Maybe t -> IO [[t]]
+hmcCUDA method prog initial = do
+  let (rets, pb@(PBlock _ _ given _)) = runProgExprs "stan" prog
+      ir = showPBlock pb $ show rets
+      givenIds = [ show i | (LVar i, _) <- Map.toAscList given ]
+      opts = "mode=density given="++ intercalate "," givenIds
+  code <- withCString ir $ \cir -> withCString "" $ \ctys -> withCString opts $ \copt -> alloca $ \pn -> do
+    check "stk_ir_to_cuda" $ c_ir_to_cuda cir ctys copt nullPtr 0 pn
+    n <- peek pn
+    allocaBytes (fromIntegral n) $ \buf -> check "stk_ir_to_cuda" (c_ir_to_cuda cir ctys copt buf n nullPtr) >> peekCString buf
+  let dat = [ (show i, toDouble <$> elems' c) | (LVar i, (c,_)) <- Map.toAscList given ]   -- row-major, as the data fields expect
+      qmaps = [ words l | l <- lines code, take 8 (dropWhile (`elem` " \"") l) == "qmap x_s" || "qmap " `isPrefixOf` dropWhile (`elem` " \"") l ]
+  -- initial values (hmcStanInit): the constrained value of every parameter block, pushed through the inverse transforms
+  let initq = unconstrainInit qmaps pb rets <$> initial
+  draws <- hmcCUDAModule method code dat initq
+  -- draws [sample][param][chain] -> per chain, per sample: the parameter values on the model's scale -> t
+  return [ [ fromRight' . evalPBlock pb rets $ constrainEnv qmaps pb [ draws !! sIdx !! j !! c | j <- [0 .. length (head (head draws)) - 1] ]
+           | sIdx <- [0 .. length draws - 1] ]
+         | c <- [0 .. numChains method - 1] ]
+  where elems' = map fromRational . toList . toRationalArray
+        -- qmap <PNode> <offset> <rows> <cols> <lower|-> <upper|->  (descriptor lines of a generated module)
+        constrainEnv qmaps pb q = Map.fromList
+          [ (LVar (pnodeId pb name), reshape rows cols [ con lo hi (q !! (off + k)) | k <- [0 .. max 1 rows * max 1 cols - 1] ])
+          | (_:name:offS:rowsS:colsS:lo:hi:_) <- qmaps, let off = read offS; rows = read rowsS; cols = read colsS ]
+        con "-" "-" x = x
+        con lo  "-" x = read lo + exp x
+        con "-" hi  x = read hi - exp x
+        con lo  hi  x = read lo + (read hi - read lo) / (1 + exp (negate x))
+        unc "-" "-" v = v
+        unc lo  "-" v = log (v - read lo)
+        unc "-" hi  v = log (read hi - v)
+        unc lo  hi  v = let u = (v - read lo) / (read hi - read lo) in log (u / (1 - u))
+        unconstrainInit qmaps pb rets t0 =
+          let env = unifyTuple (definitions pb) rets t0 emptyEnv          -- the values the caller gave, by PNode (as runStan does, Stan.hs:449-450)
+          in concat [ [ unc lo hi v | v <- toDouble <$> elems' (fromJust $ Map.lookup (LVar (pnodeId pb name)) env) ]
+                    | (_:name:_:_:_:lo:hi:_) <- qmaps ]
+        reshape 0 _ [x] = fromDouble x
+        reshape r 0 xs  = fromList (fromDouble <$> xs)
+        reshape r c xs  = fromMatrix' r c xs
+        pnodeId pb name = head [ i | i <- Map.keys (pnodes pb), show i == name ]
+
+-- | static HMC / adaptive HMC / NUTS on a module given by name ("builtin:linreg", ...) or as generated CUDA text:
+-- draws[sample][param][chain] on the unconstrained scale of the module's `q` field.
+hmcCUDAModule :: CudaMethod -> String -> [(String, [Double])] -> Maybe [Double] -> IO [[[Double]]]
+hmcCUDAModule CudaSample{..} spec dat initq = withCtx 0 $ \ctx ->
   withCString spec $ \cspec -> withCString "cache/cuda" $ \cdir -> alloca $ \pm -> alloca $ \pc -> do
     check "stk_module_load" $ c_module_load ctx cspec cdir pm
     m <- peek pm
@@ -223,12 +367,10 @@ hmcCUDA CudaSample{..} spec dat initq = withCtx 0 $ \ctx ->
     when (numWarmup > 0) $ check "warmup" $ c_step ch kid (fromIntegral numWarmup) nullPtr
     check "stk_record" $ c_record ch (fromIntegral numSamples) (fromIntegral thin)
     check "stk_step" $ c_step ch kid (fromIntegral $ numSamples * thin) nullPtr
-    let p = length (maybe [] id initq)   -- callers normally query stk_num_params
-        n = numSamples * p * numChains
+    p <- fromIntegral <$> c_num_params ch
+    let n = numSamples * p * numChains
     draws <- allocaArray n $ \buf -> alloca $ \pn -> do
       check "stk_get_draws" $ c_get_draws ch buf (fromIntegral $ 8 * n) pn
       map realToFrac <$> peekArray n buf
     _ <- c_chains_destroy ch
     return $ chunk p . chunk numChains $ draws
-  where chunk k [] = []
-        chunk k xs = let (a,b) = splitAt k xs in a : chunk k b

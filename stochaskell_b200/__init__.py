@@ -2,10 +2,12 @@
 
 Only what the hot path needs: the C-ABI library + CUDA kernels in
 csrc/, the host-side mirror of compileCC/runCC/runStep/simulate/hmcStan in api.py,
-the IR -> CUDA code generator in stkc.py, and the diagnostics plumbing.
+the IR -> CUDA code generator (native: csrc/stkc.cpp + csrc/stkc_grad.inc, C-ABI entry stk_ir_to_cuda, wrapped by
+api.ir_to_cuda / api.model_to_module), and the diagnostics plumbing.
 """
 from ._lib import LIB_PATH, StkError, lib  # noqa: F401
-from .api import (Chains, Context, CudaMethod, Module, Sampler, compile_source,  # noqa: F401
-                  compileCUDA, diag_finish, hmcCUDA, ir_to_cuda, runCUDA, runStanCUDA)
+from .api import (Chains, CompiledKernel, Context, CudaMethod, Module, Sampler, compile_source,  # noqa: F401
+                  compileCUDA, constrain_draws, diag_finish, hmcCUDA, ir_to_cuda, model_to_module, runCUDA,
+                  runStanCUDA)
 from .io import (rdump_dumps, rdump_load, rdump_loads, read_stan_csv, stan_columns,  # noqa: F401
                  write_stan_csv)

@@ -293,8 +293,49 @@ class Sampler:
         return {k: self.chains.get_state(k) for k, f in self.module.fields.items() if f["state"]}
 
 
-def compileCUDA(module_spec: str, n_chains: int = 1, data: Optional[dict] = None, **kw) -> Sampler:
-    """compileCC analogue (CC.hs:465-498); n_chains = 1 degenerates to its exact shape."""
+class CompiledKernel:
+    """What `compileCUDA :: (s -> P t) -> IO (Int -> [s] -> IO [t])` returns (haskell/Language/CUDA.hs; compileCC's closure,
+    CC.hs:465-498, batched): call it with n and one input tuple per chain, get one output tuple per chain back.  The values
+    travel as SoA state fields (stochaskell_b200/layout.py), not as text; the module and its chains stay resident."""
+
+    def __init__(self, ir_text: str, input_types: Sequence[str], device: int = 0, seed: int = 1, ctx: Optional[Context] = None,
+                 cache_dir: Optional[str] = None, **options):
+        self.types = list(input_types)
+        self.ctx = ctx or Context(device)
+        self.module = Module(self.ctx, ir_to_cuda(ir_text, self.types, **options), cache_dir=cache_dir)
+        self.seed = seed
+        self.chains: Optional[Chains] = None
+        self._caps: Dict[str, int] = {}
+
+    def __call__(self, n: int, xs: Sequence[Sequence]) -> list:
+        from .layout import flatten_input, unflatten_output
+        C = len(xs)
+        if self.chains is None or self.chains.n != C:
+            self.chains = Chains(self.module, C, self.seed)
+            self._caps = {}
+        fields = {}
+        for k, t in enumerate(self.types):
+            f = flatten_input(k, t, [x[k] for x in xs])
+            for name, a in f.items():
+                # a vector field keeps the capacity of its first upload: pad later (shorter) uploads up to it
+                cap = self._caps.setdefault(name, a.shape[0])
+                if a.shape[0] < cap:
+                    a = np.concatenate([a, np.zeros((cap - a.shape[0], a.shape[1]), dtype=a.dtype)], axis=0)
+                fields[name] = a
+        for name, a in fields.items():
+            self.chains.set_state(name, np.ascontiguousarray(a))
+        self.chains.step("step", n)
+        got = {name: self.chains.get_state(name) for name in fields}
+        outs = [unflatten_output(k, t, got) for k, t in enumerate(self.types)]
+        return [tuple(o[c] for o in outs) for c in range(C)]
+
+
+def compileCUDA(module_spec: str, n_chains: int = 1, data: Optional[dict] = None, input_types: Optional[Sequence[str]] = None, **kw):
+    """compileCC analogue (CC.hs:465-498).  Given a kernel `s -> P t` as IR text and the types of its inputs it returns the
+    closure `n -> [s] -> [t]` (CompiledKernel: values in, values out, n fused transitions, one chain per input); given a
+    module ('builtin:<name>', CUDA text, a .cubin) it returns a Sampler over `n_chains` chains."""
+    if input_types is not None and is_ir_text(module_spec):
+        return CompiledKernel(module_spec, input_types, **kw)
     return Sampler(module_spec, n_chains, data, **kw)
 
 
@@ -303,10 +344,51 @@ def runCUDA(module_spec: str, state: dict, n_chains: int = 1, data: Optional[dic
     return compileCUDA(module_spec, n_chains, data, **kw)(state)
 
 
+def is_ir_text(spec: str) -> bool:
+    """a program in showPBlock syntax (as opposed to 'builtin:<name>', a .cubin path or CUDA source text)"""
+    if spec.startswith("builtin:") or spec.endswith(".cubin") or "__global__" in spec:
+        return False
+    t = spec.lstrip()
+    return t.startswith(("let", "do ", "\\", "[runStep]", "/*")) and ("<-" in spec or " in " in spec)
+
+
+def model_to_module(model_ir: str, given: Sequence[str], name: str = "ir_model", **options) -> str:
+    """`stanProgram` analogue (Stan.hs:325-344): a conditioned model `P t` -> CUDA source of a module with logp / logp_grad
+    entries and a static-HMC kernel (csrc/stkc_grad.inc); `given` = the ids of the PNodes that are conditioned on"""
+    return ir_to_cuda(model_ir, [], name=name, mode="density", given=",".join(given), **options)
+
+
+def constrain_draws(descriptor: str, draws: np.ndarray) -> Dict[str, np.ndarray]:
+    """draws [num_samples][P][num_chains] on the unconstrained scale -> {PNode id: [num_samples][shape..][num_chains]} on the
+    model's own scale, by the `qmap` lines of a generated module's descriptor (lb: lo + exp q; ub: hi - exp q; lub: logistic)"""
+    out = {}
+    for line in descriptor.splitlines():
+        t = line.split()
+        if not t or t[0] != "qmap":
+            continue
+        ident, off, rows, cols, lo, hi = t[1], int(t[2]), int(t[3]), int(t[4]), t[5], t[6]
+        n = max(1, rows) * max(1, cols)
+        x = draws[:, off:off + n, :]
+        if lo != "-" and hi == "-":
+            x = float(lo) + np.exp(x)
+        elif lo == "-" and hi != "-":
+            x = float(hi) - np.exp(x)
+        elif lo != "-" and hi != "-":
+            x = float(lo) + (float(hi) - float(lo)) / (1.0 + np.exp(-x))
+        shape = (draws.shape[0],) + ((rows, cols) if cols else (rows,) if rows else ()) + (draws.shape[2],)
+        out[ident] = x.reshape(shape)
+    return out
+
+
 def hmcCUDA(method: CudaMethod, module_spec: str, data: dict, init: Optional[Sequence[float]] = None,
             first_global_chain: int = 0) -> np.ndarray:
-    """hmcStan / hmcStanInit analogue (Stan.hs:493-500): returns draws [num_samples][P][num_chains]
-    on the unconstrained scale of the module's `q` field."""
+    """hmcStan / hmcStanInit analogue (Stan.hs:493-500).  `module_spec` is either a module ('builtin:<name>', CUDA text, a
+    .cubin) or — the reference's own shape `hmcStan :: Int -> P t -> IO [t]` — the conditioned model itself as IR text
+    (showPBlock syntax): `data` then maps the conditioned PNodes' ids to their observed values, and the module is generated
+    (density + gradient + HMC kernel, csrc/stkc_grad.inc) and compiled on the fly.  Returns draws [num_samples][P][num_chains]
+    on the unconstrained scale of the module's `q` field (`constrain_draws` maps them back for a generated module)."""
+    if is_ir_text(module_spec):
+        module_spec = model_to_module(module_spec, list(data.keys()))
     s = Sampler(module_spec, method.num_chains, data, seed=method.seed, device=method.device,
                 first_global_chain=first_global_chain)
     ch = s.chains

@@ -155,7 +155,7 @@ struct PCData {              // one `key -> value` entry over a 1-D index range
   std::shared_ptr<Body> key, val;
   std::string param; RefP lo, hi;
 };
-struct Alt { std::vector<std::string> inputs; Body body; };
+struct Alt { std::vector<std::string> inputs; Body body; int tag = -1; /* constructor alternative `C<tag> fields ->` */ };
 struct Node {
   enum K { Apply, Array, Fold, Case, Function } k = Apply;   // Function: `\i.. -> body` (Expression.hs:204-205; interpreter only in the reference)
   std::string f;                                  // Apply name; Fold: foldl/foldr/scanl/scanr
@@ -380,6 +380,7 @@ struct Parser {
       bool ctor_alt = h.k == Tok::Id && ctor_name(h.s, &tag) && h.first;
       if (!int_alt && !ctor_alt) break;
       Alt a; next();
+      if (ctor_alt) a.tag = tag;
       if (ctor_alt) while (!is("->")) { Tok i = next(); if (i.k != Tok::Id) fail("expected a constructor field id"); a.inputs.push_back(i.s); }
       expect("->");
       a.body = body(!probabilistic);
@@ -1297,10 +1298,30 @@ struct Gen {
     }
     v.expr = v.tuple[0];
     if (ts.size() == 1) v.tuple.clear();
-    line("switch (" + rv(n.args[0]) + ") {");
+    // Case over an algebraic data type (`caseD`, what pdfPNode emits for a Switch, Program.hs:1003-1012; the C++ template
+    // refuses it, CC.hs:268): the head is a tagged union, alternative C<k> binds the constructor's fields from its slots
+    const bool adt = n.alts[0].tag >= 0;
+    Type ut; std::string hd = rv(n.args[0]);
+    if (adt) {
+      ut = type_of(n.args[0]);
+      if (ut.k != Type::Union) die("case over constructors needs a union-typed head, got " + ut.str());
+      union_struct(ut);
+    }
+    line("switch (" + hd + (adt ? ".tag" : "") + ") {");
     for (size_t a = 0; a < n.alts.size(); ++a) {
-      if (!n.alts[a].inputs.empty()) die("case over an algebraic data type is not supported (CC.hs:268 neither)");
-      line("case " + std::to_string(a + 1) + ": {"); ind += 2; push();
+      if ((n.alts[a].tag >= 0) != adt) die("case mixing integer and constructor alternatives");
+      line("case " + std::to_string(adt ? n.alts[a].tag : (int)a + 1) + ": {"); ind += 2; push();
+      if (adt) {
+        const UnionLayout& L = unions[ut.str()];
+        const int c = n.alts[a].tag;
+        if (c >= (int)L.ctor.size() || n.alts[a].inputs.size() != L.ctor[c].size()) die("case alternative C" + std::to_string(c) + " does not fit " + ut.str());
+        for (size_t j = 0; j < n.alts[a].inputs.size(); ++j) {
+          const Slot& sl = L.slots[L.ctor[c][j]];
+          std::string cn = fresh(n.alts[a].inputs[j]);
+          line("const " + ctype(sl.type) + " " + cn + " = " + hd + "." + sl.name + ";");
+          Val iv; iv.type = sl.type; iv.expr = cn; bind(n.alts[a].inputs[j], iv);
+        }
+      }
       for (const Def& bd : n.alts[a].body.defs) def(bd);
       if (n.alts[a].body.rets.size() != ts.size()) die("case alternative arity mismatch");
       for (size_t j = 0; j < ts.size(); ++j)
@@ -1892,7 +1913,10 @@ static std::string generate(const std::string& ir, const std::string& input_type
   int veccap = opt.count("veccap") ? atoi(opt["veccap"].c_str()) : 64;
   int block = opt.count("block") ? atoi(opt["block"].c_str()) : 128;
   int matcap = opt.count("matcap") ? atoi(opt["matcap"].c_str()) : 64;
-  bool kernel = !its.empty();
+  // entry=logp: the program is a log-density `s -> R` (what `lpdf` / `lpdfAux` build, Program.hs:893-1030, and what one runCC
+  // call of it returns): its inputs are the state fields, its single real return goes to the module's `logp` entry
+  const bool lp_entry = opt.count("entry") && opt["entry"] == "logp";
+  bool kernel = !its.empty() && !lp_entry;
   if (level < 0) {                                  // find the Dummy level of the inputs: i_0_k (compileCC) or i_9_k (runStep)
     level = ir.find("i_9_0") != std::string::npos ? 9 : 0;
   }
@@ -1974,6 +1998,9 @@ static std::string generate(const std::string& ir, const std::string& input_type
           else feed << "    " << in_names[k] << "." << s.name << " = " << nx << "." << s.name << ";\n";
         }
       } else feed << "    " << in_names[k] << " = " << nx << ";\n";
+    } else if (lp_entry) {
+      if (prog.rets.size() != 1 || !rt.scalar()) die("entry=logp: the program must return one scalar (a log-density), got " + rt.str());
+      g.line("a.out_lp[chain] = " + g.rv(prog.rets[k], true) + ";");
     } else {
       std::string nm = "out" + std::to_string(k);
       if (rt.k == Type::Vec && rt.sub[0].scalar()) {   // a joint's draws: [veccap][chains] + the length
@@ -2018,7 +2045,7 @@ static std::string generate(const std::string& ir, const std::string& input_type
     for (const Slot& s : L.slots) o << " " << Gen::ctype(s.type) << " " << s.name << ";";
     o << " };   // " << kv.first << "\n";
   }
-  const char* sym = kernel ? "stk_ir_step" : "stk_ir_simulate";
+  const char* sym = kernel ? "stk_ir_step" : lp_entry ? "stk_ir_logp" : "stk_ir_simulate";
   o << "extern \"C\" __global__ void __launch_bounds__(" << block << ") " << sym << "(const __grid_constant__ StkArgs a) {\n";
   o << "  const long long chain = (long long)blockIdx.x * blockDim.x + threadIdx.x;\n  if (chain >= a.n_chains) return;\n";
   o << "  int* const err_ = (int*)a.field[F_err];\n";
@@ -2036,7 +2063,7 @@ static std::string generate(const std::string& ir, const std::string& input_type
   for (auto& f : fields) o << "  \"field " << f.name << " " << f.kind << " " << (f.i32 ? "i32" : "f64") << " " << f.len << "\\n\"\n";
   if (!rec.str().empty()) o << "  \"record" << rec.str() << "\\n\"\n";
   if (kernel) o << "  \"kernel step " << sym << " " << block << " " << block << " 0 - 0\\n\";\n";
-  else o << "  \"entry simulate " << sym << " " << block << " " << block << " 0 - 0\\n\";\n";
+  else o << "  \"entry " << (lp_entry ? "logp " : "simulate ") << sym << " " << block << " " << block << " 0 - 0\\n\";\n";
   return o.str();
 }
 

@@ -112,3 +112,24 @@ def test_small_unrolled_model_gradient_by_finite_differences(ctx, tmp_path):
     ch.set_param("eps", 0.05); ch.set_param("L", 5)
     ch.step("hmc", 20)
     assert np.all(np.isfinite(ch.get_state("q")))
+
+
+def test_hmcCUDA_takes_the_conditioned_model_itself(ctx, tmp_path):
+    """hmcStan's own shape (Stan.hs:493-500: `hmcStan :: Int -> P t -> IO [t]`): the conditioned model as IR text + the
+    observed values of its conditioned PNodes; the posterior agrees with the ridge solution within Monte-Carlo error and the
+    draws come back on the model's scale (sigma > 0 through the qmap of the generated module)"""
+    from stochaskell_b200 import CudaMethod, constrain_draws, hmcCUDA
+    n = 120
+    rng = np.random.default_rng(5)
+    X = rng.standard_normal((n, 10)); w = rng.standard_normal(10)
+    y = X @ w + 0.5 + 0.7 * rng.standard_normal(n)
+    m = CudaMethod(num_chains=256, num_samples=200, num_warmup=200, step_size=0.03, num_leapfrog=20, seed=3)
+    draws = hmcCUDA(m, model_ir(n), {"x_stan_0_0": X, "x_stan_0_4": y})
+    assert draws.shape == (200, 12, 256)
+    cons = constrain_draws(hmcCUDA.last_sampler.module.descriptor, draws)
+    assert set(cons) == {"x_stan_0_1", "x_stan_0_2", "x_stan_0_3"} and cons["x_stan_0_2"].shape == (200, 10, 256)
+    assert (cons["x_stan_0_3"] > 0).all() and abs(cons["x_stan_0_3"].mean() - 0.7) < 0.1
+    A = np.c_[np.ones(n), X]
+    ridge = np.linalg.solve(A.T @ A + (0.49 / 100.0) * np.eye(11), A.T @ y)
+    post = np.r_[cons["x_stan_0_1"].mean(), cons["x_stan_0_2"].mean(axis=(0, 2))]
+    assert np.max(np.abs(post - ridge)) < 0.03, (post, ridge)

@@ -204,3 +204,16 @@ def test_unsupported_matrix_node_is_refused():
     with pytest.raises(StkError) as e:
         ir_to_cuda("let v_0_0 = eye 3 :: matrix R\n    v_0_1 = qr v_0_0 :: matrix R\n    v_0_2 = log_det v_0_1 :: R\n in [v_0_2]\n", [])
     assert e.value.code == -5 and "qr" in str(e.value)
+
+
+def test_lpdf_program_with_adt_case_lowers_to_a_logp_entry(tmp_path):
+    """a log-density program `s -> R` (what `lpdf` builds: pdfPNode of a Switch is a Case over the constructors,
+    Program.hs:1003-1012, which CC.hs:268 cannot generate) becomes the module's `logp` entry (entry=logp)"""
+    src = ir_to_cuda(ir("soccer_lpdf"), [SOCCER_T], entry="logp", name="soccer_lpdf")
+    assert "entry logp stk_ir_logp" in src and "kernel step" not in src
+    assert "switch (i_0_0.tag)" in src and "case 0: {" in src and "case 1: {" in src
+    assert "= i_0_0.f_r1;" in src and "a.out_lp[chain] = v_0_0;" in src
+    assert "stk::neg_binomial_lpdf(" in src and "stk::poisson_lpdf(" in src
+    compile_source(src, str(tmp_path))
+    with pytest.raises(StkError):
+        ir_to_cuda(ir("soccer_rj"), [SOCCER_T], entry="logp")          # a kernel returning a state is not a log-density

@@ -689,6 +689,7 @@ class SoccerRJ:
     chains = 4096
     transitions_per_step = 50
     ny = 1040
+    lanes = 8             # lanes per chain: the two sums over the 1040 scores are split over them (stkc `lanes` option)
     state_fields = ("in0_tag", "in0_r0", "in0_r1")
     e2e_fields = ("in0_tag", "in0_r0", "in0_r1")
     diag_thin = 5
@@ -705,10 +706,10 @@ class SoccerRJ:
         rng = np.random.default_rng(20261104)
         self.y = rng.poisson(2.6, self.ny).astype(np.int32)
         ir = open(os.path.join(ROOT, "tests", "golden", "ir", "soccer_rj.txt")).read()
-        self.module = ir_to_cuda(ir, ["Union[(R, ZVec), (R, R, ZVec)]"], name="soccer_rj")
+        self.module = ir_to_cuda(ir, ["Union[(R, ZVec), (R, R, ZVec)]"], name=self.name, lanes=self.lanes)
         self.bytes_per_transition = 2 * (4 + 8 + 8) + 4 * self.ny
         self.describe = (f"soccer RJ (rj.ipynb): Poisson vs negative-binomial model of n={self.ny} scores, kernel generated by stkc from "
-                         f"the IR of `soccer n `rjmcC` soccerJump`, {self.chains} chains/GPU")
+                         f"the IR of `soccer n `rjmcC` soccerJump`, {self.lanes} lane(s) per chain, {self.chains} chains/GPU")
 
     def data(self):
         return {}
@@ -773,7 +774,16 @@ class SoccerRJ:
                             f"spawned once per transition with text state exactly as compileCC's closure (CC.hs:494-498), {nt} chains x 150 transitions"))
 
 
-WORKLOADS = {"linreg_hmc_ir": LinregHMCIR, "coal_rj_ir": CoalRJIR, "soccer_rj": SoccerRJ, "gp_hmc_tc": GPHMCTC, "linreg_hmc": LinregHMC, "linreg_nuts": LinregNUTS, "coal_rj": CoalRJ, "birats_hmc": BiratsHMC, "birats_nuts": BiratsNUTS, "dp_gibbs": DPGibbs, "gp_hmc": GPHMC, "gpr_mh": GPRMH}
+class SoccerRJSeq(SoccerRJ):
+    """the same generated kernel with ONE lane per chain (the plain sequential folds of CC.hs:236-262): the "before" of the
+    lane-parallel folds"""
+    name = "soccer_rj_seq"
+    lanes = 1
+    skip_cpu = True            # the CPU arm is soccer_rj's
+    stan_exe = None
+
+
+WORKLOADS = {"linreg_hmc_ir": LinregHMCIR, "coal_rj_ir": CoalRJIR, "soccer_rj": SoccerRJ, "soccer_rj_seq": SoccerRJSeq, "gp_hmc_tc": GPHMCTC, "linreg_hmc": LinregHMC, "linreg_nuts": LinregNUTS, "coal_rj": CoalRJ, "birats_hmc": BiratsHMC, "birats_nuts": BiratsNUTS, "dp_gibbs": DPGibbs, "gp_hmc": GPHMC, "gpr_mh": GPRMH}
 DEFAULT_WORKLOAD = "coal_rj"
 
 
@@ -931,12 +941,22 @@ def logpdf_arm(args, wl, rank, world, local, torch, dist):
                      "shared by the chains of a CTA and staged in shared memory, so the figure exceeds physical DRAM traffic")
 
 
+_T0 = time.perf_counter()
+
+
+def log(msg):
+    """progress on stderr (stdout carries exactly one JSON line)"""
+    print(f"[bench {time.perf_counter() - _T0:7.1f}s] {msg}", file=sys.stderr, flush=True)
+
+
 def run_native(args, wl, rank, world, local, torch, dist, light=False):
     """One workload on this rank's GPU; returns the result dict on rank 0 (None elsewhere).  light = timing only (no
     diagnostics, no logpdf leg, no clock sampling): the chains-per-GPU sweep."""
     from stochaskell_b200 import Sampler, diag_finish, lib
     dev = torch.device("cuda", local)
     C, K, W = (args.chains or getattr(wl, "chains", 4096)), args.steps, args.warmup
+    if rank == 0:
+        log(f"{wl.name}: start (chains {C}{', light' if light else ''})")
     if args.scaling == "strong":
         C = max(1, C // world)                    # the configuration's chain count is the TOTAL; every GPU takes its share
     T = args.transitions if args.transitions > 0 else getattr(wl, "transitions_per_step", 100)
@@ -995,6 +1015,8 @@ def run_native(args, wl, rank, world, local, torch, dist, light=False):
     dev_ms, wall_ms = float(tm[0]), float(tm[1])
     value = world * C * T * K / (dev_ms * 1e-3)
 
+    if rank == 0:
+        log(f"{wl.name}: device-timed {value:.4g} transitions/s ({dev_ms / K:.3f} ms/step)")
     # ---- e2e: public API, HOST (pinned) buffers, H2D + kernel + D2H inside the timed region -----
     e2e = None
     if not args.no_e2e:
@@ -1048,6 +1070,8 @@ def run_native(args, wl, rank, world, local, torch, dist, light=False):
         e2e["one_transition_per_round_trip"] = dict(value=world * C * K1 / float(t1[0]), unit=UNIT, steps=K1,
                                                     us_per_round_trip=float(t1[0]) * 1e6 / K1)
 
+    if rank == 0 and e2e:
+        log(f"{wl.name}: e2e {e2e['value']:.4g}, one transition per round trip {e2e['one_transition_per_round_trip']['value']:.4g}")
     # ---- cross-chain diagnostics: the ONE collective of the path (R-hat/ESS moments) --
     diag = None
     try:
@@ -1062,17 +1086,28 @@ def run_native(args, wl, rank, world, local, torch, dist, light=False):
         ch.sync()
         dt_draws = time.perf_counter() - t0
         max_lag = nd - 1
-        buf = torch.from_numpy(ch.diag_partial(max_lag)).to(dev)
-        if world > 1:
-            dist.all_reduce(buf, op=dist.ReduceOp.SUM)  # NCCL over NVLink
         P = lib().stk_num_recorded_values(ch._h)
-        r = diag_finish(buf.cpu().numpy(), P, nd, max_lag)
+        collective = "none (1 GPU)"
+        if world > 1:
+            # the one collective of the path, inside the library: stk_moments_nccl all-reduces the additive buffer over NVLink
+            # (ncclAllReduce sum fp64); torch.distributed only ships rank 0's 128-byte NCCL unique id
+            from stochaskell_b200 import NcclComm
+            idt = torch.zeros(128, dtype=torch.uint8, device=dev)
+            if rank == 0:
+                idt.copy_(torch.frombuffer(bytearray(NcclComm.unique_id()), dtype=torch.uint8))
+            dist.broadcast(idt, 0)
+            comm = NcclComm(s.ctx, world, rank, bytes(idt.cpu().numpy().tobytes()))
+            r = ch.moments_nccl(comm)
+            comm.close()
+            collective = "stk_moments_nccl: ncclAllReduce(sum, f64) of [P*(4+max_lag+1)] inside libstk_cuda"
+        else:
+            r = diag_finish(ch.diag_partial(max_lag), P, nd, max_lag)
         ok = np.isfinite(r["rhat"]) & np.isfinite(r["ess"])
         diag = dict(rhat_max=float(np.max(r["rhat"][ok])) if ok.any() else None,
                     ess_min=float(np.min(r["ess"][ok])) if ok.any() else None,
                     ess_per_sec_min=float(np.min(r["ess"][ok]) / dt_draws) if ok.any() else None,
                     params_finite=int(ok.sum()), params=int(P), draws=nd, thin=thin, chains=world * C,
-                    collective="nccl all_reduce(sum) of [P*(4+max_lag+1)] f64" if world > 1 else "none (1 GPU)")
+                    collective=collective)
     except Exception as e:  # diagnostics are not part of the timed path
         diag = dict(error=str(e)[:200])
 
@@ -1084,6 +1119,7 @@ def run_native(args, wl, rank, world, local, torch, dist, light=False):
             logpdf = dict(error=str(e)[:200])
     if rank != 0:
         return None
+    log(f"{wl.name}: diagnostics + logpdf leg done")
     peaks = measured_peaks()
     ms_per_launch = dev_ms / K
     alg_bytes = C * T * wl.bytes_per_transition
@@ -1112,7 +1148,7 @@ def run_native(args, wl, rank, world, local, torch, dist, light=False):
         roofline["fp64_pipe"] = dict(achieved_tflops=tf, peak_tflops=fp64_peak, frac_of_fp64_pipe=tf / fp64_peak,
                                      flops_per_transition=wl.fp64_flops_per_transition, sm_mhz=mhz)
     cpu = None
-    if world == 1 and not args.no_cpu_baseline:
+    if world == 1 and not args.no_cpu_baseline and not getattr(wl, "skip_cpu", False):
         from tests.oracle_binding import oracle
         orc = oracle()
         nt = host_threads()
@@ -1125,6 +1161,7 @@ def run_native(args, wl, rank, world, local, torch, dist, light=False):
             v, dt = cpu_arm(wl, orc, Cs, Ts, 1, 0, nt)
             cpu = dict(value=v, unit=UNIT, cores=nt, kind=wl_kind(wl),
                        sample=f"{Cs} chains x {Ts} transitions of the same workload on {nt} host threads ({dt:.1f} s)")
+    log(f"{wl.name}: cpu baseline {(cpu or {}).get('value')}")
     return dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=K, warmup=W, ms_per_step=ms_per_launch,
                 higher_is_better=True, scaling=args.scaling, vs_baseline=None, dtype=wl.dtype, data="synthetic",
                 config=dict(workload=wl.describe, chains_per_gpu=C, chains_total=C * world, transitions_per_step=T, parallelism=f"chains-sharded x{world}",
@@ -1135,6 +1172,9 @@ def run_native(args, wl, rank, world, local, torch, dist, light=False):
 
 
 def main():
+    if os.environ.get("STK_BENCH_WATCHDOG"):       # debugging aid: Python stacks on stderr every N seconds
+        import faulthandler
+        faulthandler.dump_traceback_later(int(os.environ["STK_BENCH_WATCHDOG"]), repeat=True, file=sys.stderr)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)

@@ -160,6 +160,23 @@ int stk_moments(stk_chains* ch, double* mean, double* var, double* rhat,
 int stk_diag_partial(stk_chains* ch, int64_t max_lag, double* buf, size_t bytes);
 int stk_diag_finish(const double* buf, int P, int64_t n_draws, int64_t max_lag,
                     double* mean, double* var, double* rhat, double* ess);
+/* The same diagnostics over SEVERAL chain sets — the shards of one job, each on its own context / device (the
+ * `devices` of CudaMethod; SURVEY 8e: chains are sharded contiguously, data replicated, this buffer is the one exchange).
+ * One process driving several GPUs needs no collective library: every shard's additive buffer is computed on its device
+ * and summed on the host.  With one process per GPU the ranks all-reduce stk_diag_partial's buffer instead (NCCL / gloo,
+ * as bench.py does) and any rank calls stk_diag_finish.  All shards must have recorded the same number of draws of the
+ * same module. */
+int stk_moments_multi(stk_chains* const* shards, int n_shards, double* mean, double* var, double* rhat, double* ess);
+/* One process per GPU (the reference-side driver launches one rank per device): the additive buffer is all-reduced by
+ * NCCL over NVLink INSIDE the library (ncclAllReduce sum, fp64, on the context's stream; libnccl.so.2 is dlopen()ed on first
+ * use, so the library has no link-time dependency on it).  Rank 0 calls stk_nccl_unique_id and sends the 128 bytes to the
+ * other ranks by whatever means the host program has (MPI, a socket, torch.distributed); every rank then creates its
+ * communicator and calls stk_moments_nccl collectively. */
+typedef struct stk_comm stk_comm;
+int stk_nccl_unique_id(void* id128);
+int stk_nccl_comm_create(stk_ctx* ctx, int n_ranks, int rank, const void* id128, stk_comm** out);
+int stk_nccl_comm_destroy(stk_comm* comm);
+int stk_moments_nccl(stk_chains* ch, stk_comm* comm, double* mean, double* var, double* rhat, double* ess);
 int stk_sync(stk_chains* ch);
 /* doubles per recorded draw per chain (P_rec), valid after stk_record */
 int stk_num_recorded_values(stk_chains* ch);

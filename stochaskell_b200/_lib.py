@@ -54,6 +54,11 @@ SIGNATURES = {
     "stk_record": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64]),
     "stk_get_draws": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_int64)]),
     "stk_moments": (C.c_int, [C.c_void_p] + [C.c_void_p] * 5),
+    "stk_moments_multi": (C.c_int, [C.c_void_p, C.c_int] + [C.c_void_p] * 4),
+    "stk_nccl_unique_id": (C.c_int, [C.c_void_p]),
+    "stk_nccl_comm_create": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.POINTER(C.c_void_p)]),
+    "stk_nccl_comm_destroy": (C.c_int, [C.c_void_p]),
+    "stk_moments_nccl": (C.c_int, [C.c_void_p, C.c_void_p] + [C.c_void_p] * 4),
     "stk_diag_partial": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_size_t]),
     "stk_diag_finish": (C.c_int, [C.c_void_p, C.c_int, C.c_int64, C.c_int64] + [C.c_void_p] * 4),
     "stk_sync": (C.c_int, [C.c_void_p]),

@@ -210,6 +210,13 @@ class Chains:
         check(lib().stk_moments(self._h, _ptr(mean), _ptr(var), _ptr(rhat), _ptr(ess), _ptr(m4)))
         return dict(mean=mean, var=var, rhat=rhat, ess=ess, moments4=m4)
 
+    def moments_nccl(self, comm: "NcclComm"):
+        """R-hat / ESS over the chains of ALL ranks: the library all-reduces the additive buffer with NCCL (collective call)"""
+        p = lib().stk_num_recorded_values(self._h)
+        mean, var, rhat, ess = (np.empty(p) for _ in range(4))
+        check(lib().stk_moments_nccl(self._h, comm._h, _ptr(mean), _ptr(var), _ptr(rhat), _ptr(ess)))
+        return dict(mean=mean, var=var, rhat=rhat, ess=ess)
+
     def diag_partial(self, max_lag: int) -> np.ndarray:
         p = lib().stk_num_recorded_values(self._h)
         buf = np.empty(p * (4 + max_lag + 1))
@@ -222,6 +229,27 @@ class Chains:
     def close(self):
         if self._h:
             lib().stk_chains_destroy(self._h)
+            self._h = None
+
+
+class NcclComm:
+    """An NCCL communicator owned by the library (stk_nccl_comm_create): one per rank of a one-process-per-GPU job.  Rank 0
+    makes the unique id (`NcclComm.unique_id()`), the host program ships the 128 bytes to the other ranks."""
+
+    @staticmethod
+    def unique_id() -> bytes:
+        buf = C.create_string_buffer(128)
+        check(lib().stk_nccl_unique_id(buf))
+        return buf.raw
+
+    def __init__(self, ctx: Context, n_ranks: int, rank: int, unique_id: bytes):
+        h = C.c_void_p()
+        check(lib().stk_nccl_comm_create(ctx._h, n_ranks, rank, C.create_string_buffer(unique_id, 128), C.byref(h)))
+        self._h = h
+
+    def close(self):
+        if self._h:
+            lib().stk_nccl_comm_destroy(self._h)
             self._h = None
 
 
@@ -248,6 +276,7 @@ class CudaMethod:
     num_leapfrog: int = 10
     seed: int = 1
     device: int = 0
+    devices: Optional[Sequence[int]] = None   # several GPUs of one box driven by this process: chains sharded over them (MultiSampler)
     kernel: str = "hmc"
     # adapt=True: Stan's `adapt engaged=1` for the static engine with a diagonal metric (adapt_diag_e_static_hmc):
     # every chain tunes its own step size (dual averaging towards `delta`) and metric over num_warmup transitions,
@@ -330,6 +359,67 @@ class CompiledKernel:
         return [tuple(o[c] for o in outs) for c in range(C)]
 
 
+class MultiSampler:
+    """One job over several devices (CudaMethod.devices): the chains are sharded contiguously, shard d owning the
+    global chains [d C/D, (d+1) C/D) on its own context, the data is replicated, launches are issued to every device before
+    any is waited for, and the only exchange is the diagnostics buffer (stk_moments_multi).  Philox counters carry the
+    GLOBAL chain index, so the draws are bit-identical to a single-device run of the same chain count."""
+
+    def __init__(self, module_spec: str, n_chains: int, data: Optional[dict] = None, seed: int = 1,
+                 devices: Sequence[int] = (0,), first_global_chain: int = 0):
+        D = len(devices)
+        if D < 1 or n_chains < D:
+            raise StkError(-1, "need at least one device and one chain per device")
+        self.devices = list(devices)
+        self.bounds = [n_chains * d // D for d in range(D + 1)]
+        self.shards = [Sampler(module_spec, self.bounds[d + 1] - self.bounds[d], data, seed=seed, device=dev,
+                               first_global_chain=first_global_chain + self.bounds[d]) for d, dev in enumerate(self.devices)]
+        self.module = self.shards[0].module
+        self.n = n_chains
+
+    def set_param(self, name, v):
+        for s in self.shards:
+            s.chains.set_param(name, v)
+
+    def set_state(self, name, value, broadcast=False):
+        a = np.asarray(value)
+        for d, s in enumerate(self.shards):
+            s.chains.set_state(name, a if broadcast else np.ascontiguousarray(a[..., self.bounds[d]:self.bounds[d + 1]]), broadcast=broadcast)
+
+    def get_state(self, name):
+        return np.concatenate([s.chains.get_state(name) for s in self.shards], axis=-1)
+
+    def step(self, kernel, n=1):
+        for s in self.shards:            # stk_step returns once the launches are queued: the devices run concurrently
+            s.chains.step(kernel, n)
+
+    def simulate(self):
+        for s in self.shards:
+            s.chains.simulate()
+
+    def sync(self):
+        for s in self.shards:
+            s.chains.sync()
+
+    def record(self, n_slots, thin=1):
+        for s in self.shards:
+            s.chains.record(n_slots, thin)
+
+    def draws(self):
+        return np.concatenate([s.chains.draws() for s in self.shards], axis=-1)
+
+    def logp(self):
+        return np.concatenate([s.chains.logp() for s in self.shards])
+
+    def moments(self):
+        """R-hat / ESS over ALL shards (stk_moments_multi)"""
+        P = lib().stk_num_recorded_values(self.shards[0].chains._h)
+        mean, var, rhat, ess = (np.empty(P) for _ in range(4))
+        hs = (C.c_void_p * len(self.shards))(*[s.chains._h for s in self.shards])
+        check(lib().stk_moments_multi(hs, len(self.shards), _ptr(mean), _ptr(var), _ptr(rhat), _ptr(ess)))
+        return dict(mean=mean, var=var, rhat=rhat, ess=ess)
+
+
 def compileCUDA(module_spec: str, n_chains: int = 1, data: Optional[dict] = None, input_types: Optional[Sequence[str]] = None, **kw):
     """compileCC analogue (CC.hs:465-498).  Given a kernel `s -> P t` as IR text and the types of its inputs it returns the
     closure `n -> [s] -> [t]` (CompiledKernel: values in, values out, n fused transitions, one chain per input); given a
@@ -389,7 +479,9 @@ def hmcCUDA(method: CudaMethod, module_spec: str, data: dict, init: Optional[Seq
     on the unconstrained scale of the module's `q` field (`constrain_draws` maps them back for a generated module)."""
     if is_ir_text(module_spec):
         module_spec = model_to_module(module_spec, list(data.keys()))
-    s = Sampler(module_spec, method.num_chains, data, seed=method.seed, device=method.device,
+    if method.devices and len(method.devices) > 1:
+        return _hmc_multi(method, module_spec, data, init, first_global_chain)
+    s = Sampler(module_spec, method.num_chains, data, seed=method.seed, device=(method.devices[0] if method.devices else method.device),
                 first_global_chain=first_global_chain)
     ch = s.chains
     if "eps" in s.module.params:
@@ -421,6 +513,23 @@ def hmcCUDA(method: CudaMethod, module_spec: str, data: dict, init: Optional[Seq
     out = ch.draws()
     s.last_chains = ch
     hmcCUDA.last_sampler = s
+    return out
+
+
+def _hmc_multi(method: CudaMethod, module_spec: str, data: dict, init, first_global_chain: int) -> np.ndarray:
+    """hmcCUDA over several devices of one box (static engine): the chains sharded over CudaMethod.devices"""
+    if method.adapt or method.engine != "static":
+        raise StkError(-1, "multi-device hmcCUDA supports the static engine; run adaptive engines one process per GPU")
+    ms = MultiSampler(module_spec, method.num_chains, data, seed=method.seed, devices=method.devices, first_global_chain=first_global_chain)
+    ms.set_param("eps", method.step_size); ms.set_param("L", method.num_leapfrog)
+    if init is not None:
+        ms.set_state("q", np.asarray(init, dtype=np.float64), broadcast=True)
+    if method.num_warmup:
+        ms.step(method.kernel, method.num_warmup)
+    ms.record(method.num_samples, method.thin)
+    ms.step(method.kernel, method.num_samples * method.thin)
+    out = ms.draws()
+    hmcCUDA.last_sampler = ms
     return out
 
 

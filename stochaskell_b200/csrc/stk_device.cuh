@@ -290,18 +290,25 @@ STK_DEV bool vec_eq(const Vec<T>& a, const Vec<T>& b) {
 // log |det A| of a dense n x n matrix stored row-major with pitch n, by LU with partial pivoting, in place (the interpreter's
 // logDet = fst . snd . invlndet, Data/Array/Abstract.hs:329-331; LOG_DET of CC.hs:420-421 covers the positive-definite case).
 // A singular matrix gives -inf.
-STK_DEV double log_abs_det(double* A, int n) {
+// NOT inlined, single exit: inlined four times into the divergent branches of a generated reversible-jump kernel (one LU per
+// move kind, early returns out of the pivot loop), ptxas -O1..-O3 (CUDA 12.9, sm_100a) produced code in which warps whose lanes
+// took different branches never reconverged — the kernel hung on B200 while -O0 / -G builds and a host build of the same source
+// ran to completion (profiles/r02_coal_ir_hang.md).  As a real function call the control flow of the factorisation is isolated.
+__device__ __noinline__ double log_abs_det(double* A, int n) {
   double acc = 0.0;
-  for (int k = 0; k < n; ++k) {
+  bool done = false;
+  for (int k = 0; k < n && !done; ++k) {
     int piv = k; double best = fabs(A[k * n + k]);
     for (int i = k + 1; i < n; ++i) { const double v = fabs(A[i * n + k]); if (v > best) { best = v; piv = i; } }
-    if (!(best > 0.0)) return best == 0.0 ? neg_inf() : oob_value<double>();
-    if (piv != k) for (int j = k; j < n; ++j) { const double t = A[k * n + j]; A[k * n + j] = A[piv * n + j]; A[piv * n + j] = t; }
-    const double d = A[k * n + k];
-    acc += log(fabs(d));
-    for (int i = k + 1; i < n; ++i) {
-      const double f = A[i * n + k] / d;
-      if (f != 0.0) for (int j = k + 1; j < n; ++j) A[i * n + j] -= f * A[k * n + j];
+    if (!(best > 0.0)) { acc = best == 0.0 ? neg_inf() : oob_value<double>(); done = true; }
+    else {
+      if (piv != k) for (int j = k; j < n; ++j) { const double t = A[k * n + j]; A[k * n + j] = A[piv * n + j]; A[piv * n + j] = t; }
+      const double d = A[k * n + k];
+      acc += log(fabs(d));
+      for (int i = k + 1; i < n; ++i) {
+        const double f = A[i * n + k] / d;
+        if (f != 0.0) for (int j = k + 1; j < n; ++j) A[i * n + j] -= f * A[k * n + j];
+      }
     }
   }
   return acc;
@@ -318,6 +325,14 @@ template <int G>
 STK_DEV double group_sum(double v) {
 #pragma unroll
   for (int o = G / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+// the same over an explicit lane mask (the G lanes of ONE chain's group): usable in divergent code, where other groups of the
+// warp are elsewhere; every lane of the group ends with the same value (xor butterfly, fixed order)
+template <int G>
+STK_DEV double group_sum_masked(double v, unsigned mask) {
+#pragma unroll
+  for (int o = G / 2; o > 0; o >>= 1) v += __shfl_xor_sync(mask, v, o);
   return v;
 }
 template <int G>

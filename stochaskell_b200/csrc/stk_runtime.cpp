@@ -595,7 +595,7 @@ int stk_compile(const char* cuda_src, const char* cache_dir, const char* include
   std::string devlib, abi;
   read_file(inc + "/stk_device.cuh", &devlib);
   read_file(inc + "/stk_abi.h", &abi);
-  std::string key = Sha1::hex(src + "\n//--\n" + devlib + "\n//--\n" + abi);
+  std::string key = Sha1::hex(src + "\n//--\n" + devlib + "\n//--\n" + abi + "\n//--\n" + (getenv("STK_NVRTC_FLAGS") ? getenv("STK_NVRTC_FLAGS") : ""));
   std::string path = dir + "/stk_" + key + ".cubin";
   if ((size_t)path.size() + 1 > path_cap) return fail(STK_ERR_ARG, "path buffer too small");
   if (!file_exists(path)) {
@@ -604,9 +604,14 @@ int stk_compile(const char* cuda_src, const char* cache_dir, const char* include
     if (nvrtcCreateProgram(&prog, src.c_str(), "stk_model.cu", 0, nullptr, nullptr) != NVRTC_SUCCESS)
       return fail(STK_ERR_COMPILE, "nvrtcCreateProgram failed");
     std::string iopt = "-I" + inc;
-    const char* opts[] = {"--gpu-architecture=sm_100a", "--std=c++17", "-lineinfo", "--fmad=true",
-                          "-default-device", iopt.c_str(), "-I/usr/local/cuda/include"};
-    nvrtcResult r = nvrtcCompileProgram(prog, (int)(sizeof opts / sizeof opts[0]), opts);
+    std::vector<std::string> extra;                     // STK_NVRTC_FLAGS: extra compiler options (debugging knob, e.g. "-G")
+    if (const char* xf = getenv("STK_NVRTC_FLAGS")) { std::istringstream xs(xf); std::string t; while (xs >> t) extra.push_back(t); }
+    std::vector<const char*> opts = {"--gpu-architecture=sm_100a", "--std=c++17", "--fmad=true",
+                                     "-default-device", iopt.c_str(), "-I/usr/local/cuda/include"};
+    bool debug = false; for (auto& t : extra) if (t == "-G" || t == "--device-debug") debug = true;
+    if (!debug) { if (getenv("STK_NVRTC_OLDORDER")) opts.insert(opts.begin() + 2, "-lineinfo"); else opts.push_back("-lineinfo"); }
+    for (auto& t : extra) opts.push_back(t.c_str());
+    nvrtcResult r = nvrtcCompileProgram(prog, (int)opts.size(), opts.data());
     if (r != NVRTC_SUCCESS) {
       size_t n = 0; nvrtcGetProgramLogSize(prog, &n);
       std::string log(n, '\0'); if (n) nvrtcGetProgramLog(prog, &log[0]);
@@ -1023,12 +1028,10 @@ static int load_diag(stk_ctx* ctx) {
   return STK_OK;
 }
 
-extern "C" {
-
 // additive diagnostics buffer of this shard: [4][P] moments then [P][max_lag+1]
 // mean-over-chains autocovariance SUMS.  bytes = 8 * P * (4 + max_lag + 1).
-int stk_diag_partial(stk_chains* c, int64_t max_lag, double* buf, size_t bytes) {
-  if (!c || !buf) return fail(STK_ERR_ARG, "null argument");
+// Left on the device (*d_out, caller frees) so that a collective can reduce it in place before it is read.
+static int diag_partial_device(stk_chains* c, int64_t* max_lag_io, double** d_out, size_t* bytes_out) {
   if (!c->draws || c->recorded < 2) return fail(STK_ERR_ARG, "need at least 2 recorded draws (stk_record + stk_step)");
   int rc = need_device(c->mod->ctx);
   if (rc) return rc;
@@ -1036,9 +1039,10 @@ int stk_diag_partial(stk_chains* c, int64_t max_lag, double* buf, size_t bytes) 
   if ((rc = load_diag(ctx))) return rc;
   if (c->last && c->last != ctx->stream) CU(cudaStreamSynchronize(c->last));
   long long N = c->recorded, C = c->n; int P = (int)c->nrec;
+  long long max_lag = *max_lag_io;
   if (max_lag < 0 || max_lag > N - 1) max_lag = N - 1;
+  *max_lag_io = max_lag;
   size_t want = sizeof(double) * (size_t)P * (size_t)(4 + max_lag + 1);
-  if (bytes != want) return fail(STK_ERR_ARG, "diag buffer must be %zu bytes, got %zu", want, bytes);
   double *d_buf = nullptr, *d_mean = nullptr;
   CU(cudaMalloc((void**)&d_buf, want));
   cudaError_t e = cudaMalloc((void**)&d_mean, sizeof(double) * (size_t)P * (size_t)C);
@@ -1065,11 +1069,102 @@ int stk_diag_partial(stk_chains* c, int64_t max_lag, double* buf, size_t bytes) 
     if (e == cudaSuccess) e = cudaLaunchKernel((const void*)ctx->k_acov, grid, dim3(256), args, smem, st);
     g_launches.fetch_add(1);
   }
-  if (e == cudaSuccess) e = cudaMemcpyAsync(buf, d_buf, want, cudaMemcpyDeviceToHost, st);
-  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-  cudaFree(d_buf); cudaFree(d_mean);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);      // d_mean is only needed by the two kernels
+  cudaFree(d_mean);
+  if (e != cudaSuccess) { cudaFree(d_buf); return fail(STK_ERR_CUDA, "diagnostics: %s", cudaGetErrorString(e)); }
+  *d_out = d_buf; *bytes_out = want;
+  return STK_OK;
+}
+
+extern "C" {
+
+int stk_diag_partial(stk_chains* c, int64_t max_lag, double* buf, size_t bytes) {
+  if (!c || !buf) return fail(STK_ERR_ARG, "null argument");
+  double* d_buf = nullptr; size_t want = 0;
+  {
+    long long N = c->recorded; int P = (int)c->nrec;
+    long long ml = (max_lag < 0 || max_lag > N - 1) ? N - 1 : max_lag;
+    if (c->draws && N >= 2 && bytes != sizeof(double) * (size_t)P * (size_t)(4 + ml + 1))
+      return fail(STK_ERR_ARG, "diag buffer must be %zu bytes, got %zu", sizeof(double) * (size_t)P * (size_t)(4 + ml + 1), bytes);
+  }
+  int rc = diag_partial_device(c, &max_lag, &d_buf, &want);
+  if (rc) return rc;
+  cudaError_t e = cudaMemcpy(buf, d_buf, want, cudaMemcpyDeviceToHost);
+  cudaFree(d_buf);
   if (e != cudaSuccess) return fail(STK_ERR_CUDA, "diagnostics: %s", cudaGetErrorString(e));
   return STK_OK;
+}
+
+// ---- the one collective of the path behind the C-ABI: NCCL through dlopen (no link-time dependency: the library loads
+// and every other entry point works on a machine without NCCL) -------------------------------------------------------------
+struct Id128 { char b[128]; };           // ncclUniqueId (NCCL_UNIQUE_ID_BYTES = 128), passed BY VALUE to ncclCommInitRank
+namespace {
+struct NcclApi {
+  void* h = nullptr;
+  int (*GetUniqueId)(void*) = nullptr;
+  int (*CommInitRank)(void**, int, Id128, int) = nullptr;
+  int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+  int (*CommDestroy)(void*) = nullptr;
+  const char* (*GetErrorString)(int) = nullptr;
+};
+}  // namespace
+static NcclApi g_nccl;
+static int nccl_load() {
+  if (g_nccl.h) return STK_OK;
+  const char* names[] = {"libnccl.so.2", "libnccl.so", nullptr};
+  void* h = nullptr;
+  for (int i = 0; names[i] && !h; ++i) h = dlopen(names[i], RTLD_NOW | RTLD_GLOBAL);
+  if (!h) return fail(STK_ERR_UNSUPPORTED, "NCCL is not available (dlopen libnccl.so.2: %s)", dlerror());
+  *(void**)&g_nccl.GetUniqueId = dlsym(h, "ncclGetUniqueId");
+  *(void**)&g_nccl.CommInitRank = dlsym(h, "ncclCommInitRank");
+  *(void**)&g_nccl.AllReduce = dlsym(h, "ncclAllReduce");
+  *(void**)&g_nccl.CommDestroy = dlsym(h, "ncclCommDestroy");
+  *(void**)&g_nccl.GetErrorString = dlsym(h, "ncclGetErrorString");
+  if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.AllReduce || !g_nccl.CommDestroy) return fail(STK_ERR_UNSUPPORTED, "libnccl lacks an expected symbol");
+  g_nccl.h = h;
+  return STK_OK;
+}
+struct stk_comm { void* comm; stk_ctx* ctx; int n_ranks, rank; };
+#define NC(call) do { int r_ = (call); if (r_ != 0) return fail(STK_ERR_CUDA, "%s: %s", #call, g_nccl.GetErrorString ? g_nccl.GetErrorString(r_) : "nccl error"); } while (0)
+
+int stk_nccl_unique_id(void* id128) {
+  if (!id128) return fail(STK_ERR_ARG, "null id");
+  int rc = nccl_load(); if (rc) return rc;
+  NC(g_nccl.GetUniqueId(id128));
+  return STK_OK;
+}
+int stk_nccl_comm_create(stk_ctx* ctx, int n_ranks, int rank, const void* id128, stk_comm** out) {
+  if (!ctx || !id128 || !out || n_ranks < 1 || rank < 0 || rank >= n_ranks) return fail(STK_ERR_ARG, "bad argument");
+  int rc = nccl_load(); if (rc) return rc;
+  if ((rc = need_device(ctx))) return rc;
+  Id128 id; memcpy(&id, id128, sizeof id);
+  void* comm = nullptr;
+  NC(g_nccl.CommInitRank(&comm, n_ranks, id, rank));
+  *out = new stk_comm{comm, ctx, n_ranks, rank};
+  return STK_OK;
+}
+int stk_nccl_comm_destroy(stk_comm* c) {
+  if (!c) return STK_OK;
+  if (g_nccl.h && c->comm) g_nccl.CommDestroy(c->comm);
+  delete c;
+  return STK_OK;
+}
+// R-hat / ESS over the chains of ALL ranks: the local additive buffer is all-reduced (sum, fp64) in place on the device over
+// NVLink, then finished on the host of every rank ("stk_moments: local + NCCL-reduced diagnostics")
+int stk_moments_nccl(stk_chains* c, stk_comm* comm, double* mean, double* var, double* rhat, double* ess) {
+  if (!c || !comm) return fail(STK_ERR_ARG, "null argument");
+  int64_t max_lag = -1; double* d_buf = nullptr; size_t bytes = 0;
+  int rc = diag_partial_device(c, &max_lag, &d_buf, &bytes);
+  if (rc) return rc;
+  cudaStream_t st = c->mod->ctx->stream;
+  int r = g_nccl.AllReduce(d_buf, d_buf, bytes / sizeof(double), /* ncclFloat64 */ 8, /* ncclSum */ 0, comm->comm, st);
+  std::vector<double> buf(bytes / sizeof(double));
+  cudaError_t e = r == 0 ? cudaMemcpyAsync(buf.data(), d_buf, bytes, cudaMemcpyDeviceToHost, st) : cudaSuccess;
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  cudaFree(d_buf);
+  if (r != 0) return fail(STK_ERR_CUDA, "ncclAllReduce: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "nccl error");
+  if (e != cudaSuccess) return fail(STK_ERR_CUDA, "diagnostics: %s", cudaGetErrorString(e));
+  return stk_diag_finish(buf.data(), (int)c->nrec, c->recorded, max_lag, mean, var, rhat, ess);
 }
 
 // host-side finish on an (all-reduced) additive buffer.  Pure arithmetic on
@@ -1124,6 +1219,24 @@ int stk_moments(stk_chains* c, double* mean, double* var, double* rhat, double* 
   if (rc) return rc;
   if (moments4) memcpy(moments4, buf.data(), sizeof(double) * 4 * (size_t)P);
   return stk_diag_finish(buf.data(), P, N, max_lag, mean, var, rhat, ess);
+}
+
+int stk_moments_multi(stk_chains* const* shards, int n_shards, double* mean, double* var, double* rhat, double* ess) {
+  if (!shards || n_shards <= 0) return fail(STK_ERR_ARG, "no shards");
+  for (int i = 0; i < n_shards; ++i) if (!shards[i]) return fail(STK_ERR_ARG, "null shard %d", i);
+  const long long N = shards[0]->recorded; const int P = (int)shards[0]->nrec;
+  if (N < 4) return fail(STK_ERR_ARG, "need at least 4 recorded draws");
+  for (int i = 1; i < n_shards; ++i)
+    if (shards[i]->recorded != N || (int)shards[i]->nrec != P)
+      return fail(STK_ERR_ARG, "shard %d recorded %lld draws of %d values, shard 0 %lld of %d", i, shards[i]->recorded, (int)shards[i]->nrec, N, P);
+  const long long max_lag = N - 1;
+  std::vector<double> sum((size_t)P * (size_t)(4 + max_lag + 1), 0.0), buf(sum.size());
+  for (int i = 0; i < n_shards; ++i) {
+    int rc = stk_diag_partial(shards[i], max_lag, buf.data(), buf.size() * sizeof(double));
+    if (rc) return rc;
+    for (size_t k = 0; k < sum.size(); ++k) sum[k] += buf[k];          // shard order is fixed: the result does not depend on timing
+  }
+  return stk_diag_finish(sum.data(), P, N, max_lag, mean, var, rhat, ess);
 }
 
 }  // extern "C"

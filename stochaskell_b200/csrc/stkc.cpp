@@ -579,6 +579,7 @@ struct Gen {
   std::map<std::string, UnionLayout> unions;   // by type string
   std::map<std::string, std::string> union_cname;
 
+  int lanes = 1;                   // lanes per chain (option `lanes`): additive folds are split over them and combined by shuffles
   bool inline_mode = false;        // lowering a lambda body into ONE expression: no statements may be emitted
   int rename_depth = 0;            // > 0 inside a nested let-expression (its ids v_0_k clash with the enclosing block's)
   std::vector<int> scope_ids; int next_scope_id = 0;
@@ -1189,7 +1190,48 @@ struct Gen {
     Val v; v.type = n.type; v.expr = d.id; bind(d.id, v);
   }
 
+  static bool mentions(const RefP& r, const std::string& id) {
+    if (!r) return false;
+    if (r->k == Ref::Var && r->name == id) return true;
+    if (mentions(r->base, id)) return true;
+    for (auto& a : r->args) if (mentions(a, id)) return true;
+    if (r->let) return mentions_body(*r->let, id);
+    if (r->pc) return mentions_body(*r->pc->key, id) || mentions_body(*r->pc->val, id) || mentions(r->pc->lo, id) || mentions(r->pc->hi, id);
+    return false;
+  }
+  static bool mentions_body(const Body& b, const std::string& id) {
+    for (const Def& d : b.defs) {
+      for (auto& a : d.node.args) if (mentions(a, id)) return true;
+      for (auto& sh : d.node.shape) if (mentions(sh.first, id) || mentions(sh.second, id)) return true;
+      if (d.node.lam && mentions_body(*d.node.lam, id)) return true;
+      for (auto& al : d.node.alts) if (mentions_body(al.body, id)) return true;
+    }
+    for (auto& r : b.rets) if (mentions(r, id)) return true;
+    return false;
+  }
+  // an ADDITIVE fold: the body returns `acc + term` (or `term + acc`) and reads the accumulator nowhere else — a sum, whose
+  // terms can be evaluated in any order.  Returns the index of the final definition and of its non-accumulator operand.
+  static bool additive_fold(const Node& n, const std::string& acc, int* def_ix, int* term_arg) {
+    const Body& b = *n.lam;
+    if (b.defs.empty() || b.rets.size() != 1 || b.rets[0]->k != Ref::Var) return false;
+    const Def& last = b.defs.back();
+    if (last.id != b.rets[0]->name || last.node.k != Node::Apply || last.node.f != "+" || last.node.args.size() != 2) return false;
+    int ai = -1;
+    for (int k = 0; k < 2; ++k) if (last.node.args[k]->k == Ref::Var && last.node.args[k]->name == acc) ai = k;
+    if (ai < 0 || mentions(last.node.args[1 - ai], acc)) return false;
+    for (size_t k = 0; k + 1 < b.defs.size(); ++k) {
+      Body one; one.defs.push_back(b.defs[k]);
+      if (mentions_body(one, acc)) return false;
+    }
+    *def_ix = (int)b.defs.size() - 1; *term_arg = 1 - ai;
+    return true;
+  }
+
   // FoldScan (CC.hs:236-262): sequential loop, left/right; the list is a vector view or an inlined Array.
+  // With `lanes` > 1 lanes per chain an additive fold over reals (a sum of log-density terms over the observations — the
+  // `foldl (+)` that `lpdf` of a joint builds) is split over the lanes: lane s takes the elements s, s + lanes, ..., the partial
+  // sums are combined by an xor-butterfly of shuffles over the chain's lane group (every lane ends with the same value, fixed order:
+  // deterministic) and the seed is added once.  Everything else runs redundantly on the lanes of a chain.
   // Scans keep every partial result (interpreter semantics, Eval.hs:213-221 = Haskell's scanl / scanr: n + 1 elements,
   // the seed first for scanl, last for scanr) in per-thread storage.  The CC template indexes `name[idx-1-1]` for a left
   // scan (CC.hs:256-259 builds "loc-1" from the string "idx-1"), i.e. reads one element before the seed: the interpreter
@@ -1230,7 +1272,15 @@ struct Gen {
       hi = "(" + lo + ") + " + len + " - 1";
       line(buf + "[" + (left ? "0" : len) + "] = " + cur + ";");
     }
-    if (left) line("for (int " + it + " = " + lo + "; " + it + " <= " + hi + "; ++" + it + ") {");
+    int add_def = -1, add_arg = -1;
+    const bool par = lanes > 1 && !scan && rt && additive_fold(n, acc, &add_def, &add_arg);
+    std::string part;
+    if (par) {
+      part = fresh("part");
+      line("double " + part + " = 0.0;");
+      line("for (int " + it + " = (" + lo + ") + sub_; " + it + " <= " + hi + "; " + it + " += STK_LANES) {");
+    }
+    else if (left) line("for (int " + it + " = " + lo + "; " + it + " <= " + hi + "; ++" + it + ") {");
     else line("for (int " + it + " = " + hi + "; " + it + " >= " + lo + "; --" + it + ") {");
     ind += 2; push();
     Val ev;
@@ -1255,6 +1305,12 @@ struct Gen {
       line("const " + ctype(ev.type) + " " + elem + " = " + rv(ls) + ".at(" + it + ");");
     }
     ev.expr = elem; bind(elem, ev);
+    if (par) {
+      for (int k = 0; k < add_def; ++k) def(n.lam->defs[k]);
+      line(part + " += " + rv(n.lam->defs[add_def].node.args[add_arg], true) + ";");
+      pop(); ind -= 2; line("}");
+      line(cur + " += stk::group_sum_masked<STK_LANES>(" + part + ", gmask_);");
+    } else {
     Val av; av.type = at; av.expr = acc;
     line("const " + ctype(at) + " " + acc + " = " + cur + ";");
     bind(acc, av);
@@ -1262,6 +1318,7 @@ struct Gen {
     line(cur + " = " + rv(n.lam->rets[0], rt) + ";");
     if (scan) line(buf + "[" + it + " - (" + lo + ")" + (left ? " + 1" : "") + "] = " + cur + ";");
     pop(); ind -= 2; line("}");
+    }
     Val v;
     if (scan) {
       v.type = vecT(at);
@@ -1572,7 +1629,8 @@ struct Gen {
     prematerialise(*fn.lam);
     std::string y = vec_value(n.args.at(0)), k = fresh("k"), acc = fresh("acc");
     line("double " + acc + " = 0.0;");
-    line("for (int " + k + " = 1; " + k + " <= " + y + ".len; ++" + k + ") {");
+    if (lanes > 1) line("for (int " + k + " = 1 + sub_; " + k + " <= " + y + ".len; " + k + " += STK_LANES) {");      // the events split over the chain's lanes
+    else line("for (int " + k + " = 1; " + k + " <= " + y + ".len; ++" + k + ") {");
     ind += 2; push();
     std::string p = fresh(fn.params[0]);
     line("const double " + p + " = " + y + ".at(" + k + ");");
@@ -1580,6 +1638,7 @@ struct Gen {
     for (const Def& bd : fn.lam->defs) def(bd);
     line(acc + " += log(" + rv(fn.lam->rets.at(0), true) + ");");
     pop(); ind -= 2; line("}");
+    if (lanes > 1) line(acc + " = stk::group_sum_masked<STK_LANES>(" + acc + ", gmask_);");
     line("const double " + d.id + " = " + acc + " - " + rv(n.args.at(3), true) + ";");
     Val v; v.type = scalarT(Type::R); v.expr = d.id; bind(d.id, v);
   }
@@ -1911,7 +1970,9 @@ static std::string generate(const std::string& ir, const std::string& input_type
   int level = opt.count("level") ? atoi(opt["level"].c_str()) : -1;
   std::string name = opt.count("name") ? opt["name"] : "ir";
   int veccap = opt.count("veccap") ? atoi(opt["veccap"].c_str()) : 64;
-  int block = opt.count("block") ? atoi(opt["block"].c_str()) : 128;
+  // one warp per CTA by default: a generated kernel is a latency-bound instruction stream per chain, and 4096 chains are only
+  // 128 warps — as CTAs of 128 threads they would sit on 32 of the 148 SMs (measured: profiles/r02_ncu_facts.json, grid 32)
+  int block = opt.count("block") ? atoi(opt["block"].c_str()) : 32;
   int matcap = opt.count("matcap") ? atoi(opt["matcap"].c_str()) : 64;
   // entry=logp: the program is a log-density `s -> R` (what `lpdf` / `lpdfAux` build, Program.hs:893-1030, and what one runCC
   // call of it returns): its inputs are the state fields, its single real return goes to the module's `logp` entry
@@ -1921,6 +1982,8 @@ static std::string generate(const std::string& ir, const std::string& input_type
     level = ir.find("i_9_0") != std::string::npos ? 9 : 0;
   }
   Gen g; g.veccap = veccap;
+  g.lanes = opt.count("lanes") ? atoi(opt["lanes"].c_str()) : 1;
+  if (g.lanes < 1 || g.lanes > 32 || (g.lanes & (g.lanes - 1)) || block % g.lanes) die("lanes must be a power of two <= 32 that divides the block size");
   g.push();
   // ---- state fields ----
   std::vector<Field> fields;
@@ -2034,7 +2097,7 @@ static std::string generate(const std::string& ir, const std::string& input_type
 
   std::ostringstream o;
   o << "// generated by stkc (libstk_cuda, Language.CUDA lowering) — do not edit\n";
-  o << "#define STK_VECCAP " << veccap << "\n#define STK_MATCAP " << matcap << "\n";
+  o << "#define STK_VECCAP " << veccap << "\n#define STK_MATCAP " << matcap << "\n#define STK_LANES " << g.lanes << "\n";
   o << "#include \"stk_device.cuh\"\nusing namespace stk;\n";
   o << "enum {";
   for (size_t i = 0; i < fields.size(); ++i) o << (i ? ", " : " ") << "F_" << fields[i].name << " = " << i;
@@ -2047,7 +2110,14 @@ static std::string generate(const std::string& ir, const std::string& input_type
   }
   const char* sym = kernel ? "stk_ir_step" : lp_entry ? "stk_ir_logp" : "stk_ir_simulate";
   o << "extern \"C\" __global__ void __launch_bounds__(" << block << ") " << sym << "(const __grid_constant__ StkArgs a) {\n";
-  o << "  const long long chain = (long long)blockIdx.x * blockDim.x + threadIdx.x;\n  if (chain >= a.n_chains) return;\n";
+  if (g.lanes > 1) {
+    // STK_LANES consecutive lanes per chain: they run the same instruction stream on the same state and draws, and split the
+    // terms of additive folds between them (Gen::fold)
+    o << "  const long long gtid_ = (long long)blockIdx.x * blockDim.x + threadIdx.x;\n";
+    o << "  const long long chain = gtid_ / STK_LANES; const int sub_ = (int)(gtid_ % STK_LANES);\n";
+    o << "  const unsigned gmask_ = (STK_LANES == 32 ? 0xffffffffu : ((1u << STK_LANES) - 1u) << ((threadIdx.x & 31) & ~(STK_LANES - 1)));\n";
+    o << "  (void)sub_; (void)gmask_;\n  if (chain >= a.n_chains) return;\n";
+  } else o << "  const long long chain = (long long)blockIdx.x * blockDim.x + threadIdx.x;\n  if (chain >= a.n_chains) return;\n";
   o << "  int* const err_ = (int*)a.field[F_err];\n";
   o << load.str() << g.decls.str();
   if (g.need_matbuf) o << "  double mat_[STK_MATCAP * STK_MATCAP];\n";
@@ -2062,8 +2132,8 @@ static std::string generate(const std::string& ir, const std::string& input_type
   o << "extern \"C\" __device__ const char stk_desc[] =\n  \"stk-module 1\\n\"\n  \"name " << name << "\\n\"\n  \"nparam 0\\n\"\n";
   for (auto& f : fields) o << "  \"field " << f.name << " " << f.kind << " " << (f.i32 ? "i32" : "f64") << " " << f.len << "\\n\"\n";
   if (!rec.str().empty()) o << "  \"record" << rec.str() << "\\n\"\n";
-  if (kernel) o << "  \"kernel step " << sym << " " << block << " " << block << " 0 - 0\\n\";\n";
-  else o << "  \"entry " << (lp_entry ? "logp " : "simulate ") << sym << " " << block << " " << block << " 0 - 0\\n\";\n";
+  if (kernel) o << "  \"kernel step " << sym << " " << block << " " << block / g.lanes << " 0 - 0\\n\";\n";
+  else o << "  \"entry " << (lp_entry ? "logp " : "simulate ") << sym << " " << block << " " << block / g.lanes << " 0 - 0\\n\";\n";
   return o.str();
 }
 

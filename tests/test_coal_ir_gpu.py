@@ -129,3 +129,31 @@ def test_generated_density_equals_builtin_coal_logp(ctx, mod):
     b.chains.set_state("n", n0.reshape(1, C)); b.chains.set_state("s", s0); b.chains.set_state("g", g0)
     lp = b.chains.logp()
     np.testing.assert_allclose(fx, lp, rtol=1e-10)
+
+
+def test_generated_kernel_long_run_all_chains(ctx, orc, tmp_path):
+    """the configuration that hung before `log_abs_det` became a real function call (profiles/r02_coal_ir_hang.md): 4096 chains,
+    1500 transitions of the bench's seed — every lane mix of move kinds shares warps; chains against the oracle at the end"""
+    from stochaskell_b200 import Chains, Module, ir_to_cuda
+    from stochaskell_b200.fixtures import coal_days
+    import time
+    y = coal_days()
+    src = ir_to_cuda(open(os.path.join(IR, "coal_rj.txt")).read(), TYPES, name="coal_rj_ir")     # the bench's module (no probes)
+    m = Module(ctx, src, cache_dir=str(tmp_path))
+    C, T, seed = 4096, 1500, 20261104
+    n0, s0, g0 = prior_states(C, 4321)
+    ch = Chains(m, C, seed=seed)
+    upload(ch, n0, s0, g0, y)
+    t0 = time.perf_counter()
+    for _ in range(15):
+        ch.step("step", 100)
+    ch.sync()
+    assert time.perf_counter() - t0 < 30.0
+    n1 = ch.get_state("in0")[0]; s1 = ch.get_state("in1")
+    for c in (0, 2831, 4095):
+        nn = int(n0[c]); sc = np.ascontiguousarray(s0[:, c]); gc = np.ascontiguousarray(g0[:, c])
+        for t in range(T):
+            nn, _ = orc.coal_rj_step_ir(nn, sc, gc, y, seed, c, t)
+        assert n1[c] == nn, (c, n1[c], nn)
+        np.testing.assert_allclose(s1[:nn, c], sc[:nn], rtol=1e-8)
+    assert 2.0 < n1.mean() < 6.0

@@ -49,7 +49,7 @@ def test_small_models_are_unrolled_one_thread_per_chain(tmp_path):
             "       x_m_0_3 <- uniform -1.0 2.0 :: P Subrange R -1.0 2.0\n"
             "       return [x_m_0_0,x_m_0_1,x_m_0_2,x_m_0_3]\n")
     src = ir_to_cuda(text, [], name="small", mode="density", given="x_m_0_2")
-    assert "#define NP 5" in src and "one thread per chain" in src and "kernel hmc stk_ir_hmc 128 128 0 - 0" in src
+    assert "#define NP 5" in src and "one thread per chain" in src and "kernel hmc stk_ir_hmc 32 32 0 - 0" in src
     assert "field x_m_0_2 data f64 3" in src and "for (int i_" not in src
     compile_source(src, str(tmp_path))
 

@@ -200,3 +200,31 @@ def test_errors_are_loud(ctx):
     big = sampler(ctx, 8, *make_data(4000, 10))
     with pytest.raises(StkError):  # 4000 rows do not fit the 227 KB staging budget
         big.chains.logp()
+
+
+def test_multi_device_sampler_equals_single_device(ctx):
+    """CudaMethod.devices / MultiSampler / stk_moments_multi (SURVEY 8e inside the product): the chains sharded over several
+    contexts (here two contexts on device 0; on a multi-GPU box one per device) give bit-identical draws to one context with
+    all the chains, and the cross-shard diagnostics equal the single-context ones"""
+    from stochaskell_b200 import CudaMethod, MultiSampler, hmcCUDA
+    X, y = make_data(300, 10)
+    C = 192
+    q0 = 0.1 * np.random.default_rng(3).standard_normal((12, C))
+    one = sampler(ctx, C, X, y, seed=9)
+    two = MultiSampler("builtin:linreg", C, dict(X=X, y=y), seed=9, devices=[0, 0])
+    assert [s.chains.n for s in two.shards] == [96, 96]
+    for s in (one.chains, two):
+        s.set_param("eps", 0.02); s.set_param("L", 8)
+        s.set_state("q", q0)
+        s.step("hmc", 30)
+        s.record(16, 2)
+        s.step("hmc", 32)
+    assert np.array_equal(one.chains.get_state("q"), two.get_state("q"))
+    assert np.array_equal(one.chains.draws(), two.draws())
+    m1, m2 = one.chains.moments(), two.moments()
+    for k in ("mean", "var", "rhat", "ess"):
+        np.testing.assert_allclose(m2[k], m1[k], rtol=1e-10)
+    d = hmcCUDA(CudaMethod(num_chains=64, num_samples=8, num_warmup=4, step_size=0.02, num_leapfrog=5, seed=2, devices=[0, 0]),
+                "builtin:linreg", dict(X=X, y=y))
+    d1 = hmcCUDA(CudaMethod(num_chains=64, num_samples=8, num_warmup=4, step_size=0.02, num_leapfrog=5, seed=2), "builtin:linreg", dict(X=X, y=y))
+    assert np.array_equal(d, d1)

@@ -728,6 +728,257 @@ __device__ __forceinline__ void rj2_body(const StkArgs& a) {
 #undef ROW
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// v4: `coal_rj3<LPW, CPL>` — CPL chains per LANE (round 2).  v3 is bound by the in-order issue of ONE dependent
+// instruction stream per warp (≈ 440 instructions at 4.95 cycles each for a true dependent chain of ≈ 500 cycles,
+// 1.7 warps per scheduler at 4096 chains): the schedulers have nothing else to issue.  Here every lane carries CPL
+// independent chains and a transition of all of them is written as two phases: phase A (select move, neighbourhood
+// loads, proposal, the two logs, log r, the decision) for all CPL chains with NO shared-memory store in between, so
+// that the compiler interleaves the CPL independent streams (instruction-level parallelism instead of warps); then
+// phase B (commit, record).  Same draws, same arithmetic per chain as v3: bit-identical trajectories.
+// Chain of a lane: local index c * LPW + lane of the CTA's LPW * CPL chains.
+// ---------------------------------------------------------------------------------------------------------
+template <int LPW, int CPL>
+__device__ __forceinline__ void rj3_body(const StkArgs& a) {
+  constexpr int CPW = LPW * CPL;
+  extern __shared__ __align__(16) double smem[];
+  const int lane = threadIdx.x;
+  const int ny = (int)a.flen[F_Y];
+  double* ysm = smem;                                   // [ny + 4]
+  Tabs* T = reinterpret_cast<Tabs*>(smem + 196);
+  Tabs2* T2 = reinterpret_cast<Tabs2*>(smem + 196 + TAB_DOUBLES);
+  double* fm = smem + 196 + TAB_DOUBLES + 64;
+  double2* P = reinterpret_cast<double2*>(fm + kFmTableDoubles);             // [R1][CPW] (s, #events below s)
+  double2* Q = P + R1 * CPW;                                                 // (g, log g)
+  double* LW = reinterpret_cast<double*>(Q + R1 * CPW);                      // log((s_i - s_{i-1}) / t)
+  double2* ring = reinterpret_cast<double2*>(LW + R1 * CPW + ((R1 * CPW) & 1));   // [4][CPW][4] double2: draws in flight
+  int* btab = reinterpret_cast<int*>(ring + 4 * CPW * 4);                    // [NB + 1]
+  Consts k;
+  k.t = a.par[PAR_T]; k.a = a.par[PAR_A]; k.b = a.par[PAR_B]; k.ny = ny;
+  k.alb = k.a * log(k.b) - lgamma(k.a); k.am1 = k.a - 1.0;
+  const int lam = (int)a.par[PAR_LAM], nmax = min((int)a.par[PAR_NMAX], SMAX);
+  const double* Y = (const double*)a.field[F_Y];
+  for (int i = lane; i < ny + 4; i += 32) ysm[i] = i < ny ? Y[i] : pos_inf();
+  build_tabs(T, k.t, lam, nmax);
+  fm_build_tables(fm, lane, 32);
+  __syncwarp();
+  const double log_inv_t = log(1.0 / (k.t - 0.0));
+  const double inv_t = 1.0 / k.t;
+  {
+    const int n = lane;
+    const int nu = min(n + 1, 31), nd = max(n - 1, 0);
+    T2->birthC[n] = ((T->lpr[nu][3] + T->logdinv[nu]) - ((T->lpr[n][2] + log_inv_t) - kHalfLog2Pi)) + (T->head[nu] - T->head[n]);
+    T2->deathC[n] = (((T->lpr[nd][2] + log_inv_t) - kHalfLog2Pi) - (T->lpr[n][3] + T->logdinv[n])) + (T->head[nd] - T->head[n]);
+  }
+  const double nb_over_t = (double)NB / k.t;
+  for (int b = lane; b <= NB; b += 32) btab[b] = count_below(ysm, ny, (double)b * (k.t / (double)NB));
+  __syncwarp();
+  if (lane >= LPW) return;
+
+#define ROWC(A, i, c) A[(i) * CPW + (c) * LPW + lane]
+  long long chain[CPL], cidx[CPL]; bool active[CPL]; int n[CPL]; double lp[CPL]; unsigned long long n_acc[CPL];
+  auto full_lp = [&](int c, int nn) {
+    double acc = 0.0; bool bad = false;
+    for (int i = 1; i <= nn + 1; ++i) {
+      const double2 p1 = ROWC(P, i, c), p0 = ROWC(P, i - 1, c), q = ROWC(Q, i, c);
+      acc += ROWC(LW, i, c) + ((k.alb + k.am1 * q.y) - k.b * q.x) + ((p1.y - p0.y) * q.y - (p1.x - p0.x) * q.x);
+      if (i <= nn && (p1.x < 0.0 || k.t < p1.x)) bad = true;
+    }
+    return bad ? neg_inf() : acc + T->head[nn];
+  };
+#pragma unroll
+  for (int c = 0; c < CPL; ++c) {
+    chain[c] = (long long)blockIdx.x * CPW + c * LPW + lane;
+    active[c] = chain[c] < a.n_chains;
+    cidx[c] = active[c] ? chain[c] : a.n_chains - 1;
+    int nn = ((const int*)a.field[F_N])[cidx[c]];
+    nn = max(0, min(nn, SMAX));
+    n[c] = nn;
+    const double* Sg = (const double*)a.field[F_S];
+    const double* Gg = (const double*)a.field[F_G];
+    ROWC(P, 0, c) = make_double2(0.0, 0.0); ROWC(Q, 0, c) = make_double2(0.0, 0.0); ROWC(LW, 0, c) = 0.0;
+    double sprev = 0.0;
+    for (int i = 1; i < R1; ++i) {
+      const double si = i <= nn ? Sg[(long long)(i - 1) * a.n_chains + cidx[c]] : k.t;
+      const double gi = i <= nn + 1 ? Gg[(long long)(i - 1) * a.n_chains + cidx[c]] : 1.0;
+      ROWC(P, i, c) = make_double2(si, (double)(i <= nn ? count_below(ysm, ny, si) : ny));
+      ROWC(Q, i, c) = make_double2(gi, log(gi));
+      ROWC(LW, i, c) = log((si - sprev) * inv_t);
+      sprev = si;
+    }
+    lp[c] = full_lp(c, nn);
+    n_acc[c] = 0;
+  }
+  const long long NC4 = a.n_chains * 4;
+  auto fetch = [&](long long tr) {
+    if (tr < a.n_steps) {
+#pragma unroll
+      for (int c = 0; c < CPL; ++c) {
+        const double2* p = reinterpret_cast<const double2*>(a.scratch) + cidx[c] * 4 + tr * NC4;
+        const unsigned dst = (unsigned)__cvta_generic_to_shared(ring + (((tr & 3) * CPW) + c * LPW + lane) * 4);
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + q * 16), "l"(p + q) : "memory");
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  fetch(0); fetch(1); fetch(2);
+  bool rec[CPL];
+#pragma unroll
+  for (int c = 0; c < CPL; ++c) rec[c] = active[c] && a.draws && a.draw_slots > 0;
+
+  for (long long tr = 0; tr < a.n_steps; ++tr) {
+    fetch(tr + 3);
+    asm volatile("cp.async.wait_group 3;" ::: "memory");
+    // ---- phase A: everything up to the decision, for all CPL chains, without a shared-memory store.  Written as a sequence of
+    // short sub-phases, each looping over the CPL chains: ptxas schedules inside basic blocks, so the rare-path branches (rank
+    // search of a birth, event-count scan, fast_log's fallback) are kept in sub-phases of their own and the long fp64 chains
+    // (two logs, four segment terms, log r) of all the chains sit side by side in branch-free blocks. ------------------------
+    int mv[CPL], jj[CPL]; bool acc[CPL];
+    double gnv[CPL], lgnv[CPL], snewv[CPL], cnv[CPL], wAv[CPL], wBv[CPL], g0v[CPL], lg0v[CPL], dfv[CPL];
+    double luBv[CPL], uDv[CPL], zv[CPL], hz2v[CPL], xv[CPL], eAv[CPL], eBv[CPL];
+#pragma unroll
+    for (int c = 0; c < CPL; ++c) {                      // A1: draws, move type, index
+      const double2* dr = ring + (((tr & 3) * CPW) + c * LPW + lane) * 4;
+      const double2 dA = dr[0], dC = dr[1], dZ = dr[2], dE = dr[3];
+      const int nn = n[c];
+      const double2 pa = *reinterpret_cast<const double2*>(&T->pr[nn][0]), pb = *reinterpret_cast<const double2*>(&T->pr[nn][2]);
+      const double ua = dA.x * (((pa.x + pa.y) + pb.x) + pb.y);
+      const double c1 = pa.x, c2 = c1 + pa.y, c3 = c2 + pb.x;
+      const int move = ua < c1 ? 1 : (ua < c2 ? 2 : (ua < c3 ? 3 : 4));
+      const int m = max((move == 1) ? nn + 1 : nn, 1);
+      int j = (int)(dC.x * (double)m); if (j >= m) j = m - 1; j += 1;
+      mv[c] = move; jj[c] = j; luBv[c] = dA.y; uDv[c] = dC.y; zv[c] = dZ.x; hz2v[c] = dZ.y; eAv[c] = dE.x; eBv[c] = dE.y;
+      xv[c] = 0.0 + (k.t - 0.0) * dC.y;
+    }
+#pragma unroll
+    for (int c = 0; c < CPL; ++c) if (mv[c] == 3) {      // A2: findSortedInsertIndex x s (birth only)
+      int lo = 1, hi = n[c] + 1;
+      while (lo < hi) { const int mid = (lo + hi) >> 1; if (xv[c] < ROWC(P, mid, c).x) hi = mid; else lo = mid + 1; }
+      jj[c] = lo;
+    }
+    double sm1v[CPL], s0v[CPL], sp1v[CPL], cm1v[CPL], c0v[CPL], cp1v[CPL], g1v[CPL], lg1v[CPL], lw0v[CPL], lw1v[CPL], dsAv[CPL], dsBv[CPL];
+#pragma unroll
+    for (int c = 0; c < CPL; ++c) {                      // A3: neighbourhood of rank j, the proposal
+      const int j = jj[c];
+      const double2 Pm1 = ROWC(P, j - 1, c), P0 = ROWC(P, j, c), Pp1 = ROWC(P, j + 1, c);
+      const double2 Q0 = ROWC(Q, j, c), Q1 = ROWC(Q, j + 1, c);
+      lw0v[c] = ROWC(LW, j, c); lw1v[c] = ROWC(LW, j + 1, c);
+      sm1v[c] = Pm1.x; s0v[c] = P0.x; sp1v[c] = Pp1.x; cm1v[c] = Pm1.y; c0v[c] = P0.y; cp1v[c] = Pp1.y;
+      g0v[c] = Q0.x; lg0v[c] = Q0.y; g1v[c] = Q1.x; lg1v[c] = Q1.y;
+      const bool m1 = mv[c] == 1, m2 = mv[c] == 2, m4 = mv[c] == 4;
+      const double u = -0.5 + (0.5 - (-0.5)) * uDv[c];
+      lgnv[c] = (m1 ? u : zv[c]) + lg0v[c];
+      gnv[c] = (m1 ? eAv[c] : eBv[c]) * g0v[c];
+      snewv[c] = m2 ? sm1v[c] + (sp1v[c] - sm1v[c]) * (0.0 + (1.0 - 0.0) * uDv[c]) : xv[c];
+      const double hiA = m1 ? s0v[c] : (m4 ? sp1v[c] : snewv[c]), hiB = m2 ? sp1v[c] : s0v[c];
+      dsAv[c] = hiA - sm1v[c]; dsBv[c] = hiB - snewv[c];
+    }
+    {                                                    // A4: events below the new point: bucket start + four probes, branch-free;
+      int cb[CPL]; bool rare = false;                    // the rare paths (bucket rounding, > 4 events in the scan) fall back to the loop version
+#pragma unroll
+      for (int c = 0; c < CPL; ++c) { int b = (int)(snewv[c] * nb_over_t); b = max(0, min(b, NB - 1)); cb[c] = btab[b]; }
+#pragma unroll
+      for (int c = 0; c < CPL; ++c) {
+        const double v = snewv[c]; const int c0i = cb[c];
+        rare = rare || (c0i > 0 && !(ysm[c0i - 1] < v));
+        const int kq = (int)(ysm[c0i] < v) + (int)(ysm[c0i + 1] < v) + (int)(ysm[c0i + 2] < v) + (int)(ysm[c0i + 3] < v);
+        rare = rare || kq == 4;
+        cnv[c] = (double)(c0i + kq);
+      }
+      if (rare) {
+#pragma unroll
+        for (int c = 0; c < CPL; ++c) cnv[c] = (double)count_below_tab(ysm, btab, ny, snewv[c], nb_over_t);
+      }
+    }
+    {                                                    // A5: the two logs of every chain, one branch-free block
+      double la[CPL], lb[CPL]; bool oka = true;
+#pragma unroll
+      for (int c = 0; c < CPL; ++c) { la[c] = dsAv[c] * inv_t; lb[c] = dsBv[c] * inv_t; oka = oka && fast_log_ok(la[c]) && fast_log_ok(lb[c]); }
+#pragma unroll
+      for (int c = 0; c < CPL; ++c) { wAv[c] = fast_log_core(la[c], fm); wBv[c] = fast_log_core(lb[c], fm); }
+      if (!oka) {                                        // a zero / negative / non-finite width (an impossible proposal): the library's answer
+#pragma unroll
+        for (int c = 0; c < CPL; ++c) { wAv[c] = fast_log(la[c], fm); wBv[c] = fast_log(lb[c], fm); }
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < CPL; ++c) {                      // A6: f(y) - f(x) from the touched segments, log r, the decision
+      const bool m1 = mv[c] == 1, m2 = mv[c] == 2, m3 = mv[c] == 3, m4 = mv[c] == 4;
+      const double sm1 = sm1v[c], s0 = s0v[c], sp1 = sp1v[c], cm1 = cm1v[c], c0 = c0v[c], cp1 = cp1v[c];
+      const double g0 = g0v[c], lg0 = lg0v[c], g1 = g1v[c], lg1 = lg1v[c], lgn = lgnv[c], gn = gnv[c], cn = cnv[c], wA = wAv[c], wB = wBv[c];
+      const double u = -0.5 + (0.5 - (-0.5)) * uDv[c];
+      const double bC = T2->birthC[n[c]], dCn = T2->deathC[n[c]];
+      const double old0 = seg_term(lw0v[c], lg0, g0, 0, 0.0, k) + ((c0 - cm1) * lg0 - (s0 - sm1) * g0);
+      const double old1 = seg_term(lw1v[c], lg1, g1, 0, 0.0, k) + ((cp1 - c0) * lg1 - (sp1 - s0) * g1);
+      const double chA = m1 ? c0 : (m4 ? cp1 : cn);
+      const double lgA = m1 ? lgn : lg0, gA = m1 ? gn : g0, lwA = m1 ? lw0v[c] : wA;
+      const double tA = seg_term(lwA, lgA, gA, 0, 0.0, k) + ((chA - cm1) * lgA - dsAv[c] * gA);
+      const double chB = m2 ? cp1 : c0, lgB = m2 ? lg1 : lgn, gB = m2 ? g1 : gn;
+      const double tB = (m2 || m3) ? seg_term(wB, lgB, gB, 0, 0.0, k) + ((chB - cn) * lgB - dsBv[c] * gB) : 0.0;
+      const double told = (m2 || m4) ? old0 + old1 : old0;
+      const double zr = lg1 - lg0;
+      const double extra = m1 ? u : (m2 ? 0.0 : (m3 ? (bC + hz2v[c]) + lgn : (dCn - 0.5 * zr * zr) - lg1));
+      const double df = (tA + tB) - told;
+      const double logr = df + extra;
+      acc[c] = luBv[c] < logr;
+      dfv[c] = df;
+    }
+    // ---- phase B: commit + record ---------------------------------------------------------------------------------
+#pragma unroll
+    for (int c = 0; c < CPL; ++c) {
+      const int j = jj[c];
+      if (acc[c]) {
+        const int move = mv[c];
+        int nn = n[c];
+        if (move == 1) ROWC(Q, j, c) = make_double2(gnv[c], lgnv[c]);
+        else if (move == 2) { ROWC(P, j, c) = make_double2(snewv[c], cnv[c]); ROWC(LW, j, c) = wAv[c]; ROWC(LW, j + 1, c) = wBv[c]; }
+        else if (move == 3) {
+          for (int i = nn + 1; i >= j; --i) {
+            const double2 p = ROWC(P, i, c), q = ROWC(Q, i, c); const double w = ROWC(LW, i, c);
+            ROWC(P, i + 1, c) = p; ROWC(Q, i + 1, c) = q; ROWC(LW, i + 1, c) = w;
+          }
+          ROWC(P, j, c) = make_double2(snewv[c], cnv[c]); ROWC(LW, j, c) = wAv[c];
+          ROWC(Q, j + 1, c) = make_double2(gnv[c], lgnv[c]); ROWC(LW, j + 1, c) = wBv[c];
+          ++nn;
+        } else {
+          for (int i = j; i <= nn; ++i) {
+            const double2 p = ROWC(P, i + 1, c), q = ROWC(Q, i + 1, c); const double w = ROWC(LW, i + 1, c);
+            ROWC(P, i, c) = p; ROWC(Q, i, c) = q; ROWC(LW, i, c) = w;
+          }
+          ROWC(Q, j, c) = make_double2(g0v[c], lg0v[c]); ROWC(LW, j, c) = wAv[c];
+          --nn;
+        }
+        n[c] = nn;
+        lp[c] += dfv[c] + (move == 3 ? T->head[nn] - T->head[nn - 1] : (move == 4 ? T->head[nn] - T->head[nn + 1] : 0.0));
+        ++n_acc[c];
+      }
+      long long slot;
+      if (rec[c] && record_slot(a, tr, &slot)) {
+        record_value(a, slot, 0, chain[c], (double)n[c]);
+        for (int i = 1; i <= SMAX + 1; ++i) {
+          if (i <= SMAX) record_value(a, slot, i, chain[c], i <= n[c] ? ROWC(P, i, c).x : 0.0);
+          record_value(a, slot, SMAX + i, chain[c], i <= n[c] + 1 ? ROWC(Q, i, c).x : 0.0);
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < CPL; ++c) if (active[c]) {
+    double* Sg = (double*)a.field[F_S];
+    double* Gg = (double*)a.field[F_G];
+    for (int i = 1; i <= SMAX + 1; ++i) {
+      if (i <= SMAX) Sg[(long long)(i - 1) * a.n_chains + chain[c]] = i <= n[c] ? ROWC(P, i, c).x : 0.0;
+      Gg[(long long)(i - 1) * a.n_chains + chain[c]] = i <= n[c] + 1 ? ROWC(Q, i, c).x : 0.0;
+    }
+    ((int*)a.field[F_N])[chain[c]] = n[c];
+    ((double*)a.field[F_LP])[chain[c]] = full_lp(c, n[c]);
+    if (a.accept) a.accept[chain[c]] += n_acc[c];
+  }
+#undef ROWC
+}
+
 // smem: (196 + TAB_DOUBLES + 64 + fast-math tables) doubles + rows (40 B per row and chain) + ring + (NB+1) ints
 constexpr int rj2_smem(int lpw) { return (196 + TAB_DOUBLES + 64 + kFmTableDoubles) * 8 + R1 * lpw * 40 + 8 + 4 * lpw * 64 + (NB + 1) * 4; }
 static_assert(rj2_smem(8) == 23740 && rj2_smem(4) == 17276 && rj2_smem(16) == 36668 && rj2_smem(32) == 62524, "rj2 smem");
@@ -740,6 +991,13 @@ extern "C" __global__ void __launch_bounds__(32) coal_rj2_2(const __grid_constan
 extern "C" __global__ void __launch_bounds__(32) coal_rj2_1(const __grid_constant__ StkArgs a) { rj2_body<1>(a); }
 extern "C" __global__ void __launch_bounds__(32) coal_rj2_16(const __grid_constant__ StkArgs a) { rj2_body<16>(a); }
 extern "C" __global__ void __launch_bounds__(32) coal_rj2_32(const __grid_constant__ StkArgs a) { rj2_body<32>(a); }
+// v4: <lanes per warp> x <chains per lane>; shared memory = rj2_smem(lanes * chains per lane)
+extern "C" __global__ void __launch_bounds__(32) coal_rj3_4x2(const __grid_constant__ StkArgs a) { rj3_body<4, 2>(a); }
+extern "C" __global__ void __launch_bounds__(32) coal_rj3_2x2(const __grid_constant__ StkArgs a) { rj3_body<2, 2>(a); }
+extern "C" __global__ void __launch_bounds__(32) coal_rj3_2x4(const __grid_constant__ StkArgs a) { rj3_body<2, 4>(a); }
+extern "C" __global__ void __launch_bounds__(32) coal_rj3_4x4(const __grid_constant__ StkArgs a) { rj3_body<4, 4>(a); }
+extern "C" __global__ void __launch_bounds__(32) coal_rj3_1x4(const __grid_constant__ StkArgs a) { rj3_body<1, 4>(a); }
+extern "C" __global__ void __launch_bounds__(32) coal_rj3_8x2(const __grid_constant__ StkArgs a) { rj3_body<8, 2>(a); }
 
 // G = 8 lanes per chain is the default (`rj`): at 4096 chains per GPU it is the best trade between lanes that idle
 // when n+1 < G and warps per scheduler (B200: G=32 874 M, G=16 1168 M, G=8 1285 M, G=4 1000 M transitions/s;
@@ -820,6 +1078,12 @@ extern "C" __device__ const char stk_desc[] =
     "kernel rj2x1 coal_rj2_1 32 1 12428 - 0 pre coal_draws 256 8\n"
     "kernel rj2x16 coal_rj2_16 32 16 36668 - 0 pre coal_draws 256 8\n"
     "kernel rj2x32 coal_rj2_32 32 32 62524 - 0 pre coal_draws 256 8\n"
+    "kernel rj3_4x2 coal_rj3_4x2 32 8 23740 - 0 pre coal_draws 256 8\n"
+    "kernel rj3_2x2 coal_rj3_2x2 32 4 17276 - 0 pre coal_draws 256 8\n"
+    "kernel rj3_2x4 coal_rj3_2x4 32 8 23740 - 0 pre coal_draws 256 8\n"
+    "kernel rj3_4x4 coal_rj3_4x4 32 16 36668 - 0 pre coal_draws 256 8\n"
+    "kernel rj3_1x4 coal_rj3_1x4 32 4 17276 - 0 pre coal_draws 256 8\n"
+    "kernel rj3_8x2 coal_rj3_8x2 32 16 36668 - 0 pre coal_draws 256 8\n"
     "kernel rj32 coal_rj32 128 4 4640 y 8\n"
     "kernel rj16 coal_rj16 128 8 6688 y 8\n"
     "kernel rj4 coal_rj4 128 32 18976 y 8\n"

@@ -47,6 +47,35 @@ STK_FM void fm_build_tables(double* tab, int idx, int stride) {
   for (int j = idx; j < kFmExpCells; j += stride) tab[2 * kFmLogCells + j] = exp2((double)j / 256.0);
 }
 
+// branch-free core of fast_log for x known to be a positive normal number (no fallback path: the caller patches the
+// other cases with a select).  Same arithmetic as fast_log, so the results are bit-identical where both apply.
+STK_FM double fast_log_core(double x, const double* tab) {
+  const unsigned long long b = STK_FM_BITS(x);
+  const int hi = (int)(b >> 32);
+  int e = (hi >> 20) - 1023;
+  const int up = (hi >> 19) & 1;
+  e += up;
+  const double m = STK_FM_DBL((b & 0x000fffffffffffffULL) | ((unsigned long long)(1023 - up) << 52));
+  const int top = (hi >> 12) & 0xff;
+  const int cell = (up ? (top >> 1) - 64 : 64 + top) & 255;          // masked: a wild input cannot index outside the table
+  const double inv = tab[2 * cell], lc = tab[2 * cell + 1];
+  const double r = STK_FM_FMA(m, inv, -1.0);
+  const double r2 = r * r;
+  const double p01 = STK_FM_FMA(r, 0.33333333333333333, -0.5);
+  const double p23 = STK_FM_FMA(r, 0.2, -0.25);
+  const double p45 = STK_FM_FMA(r, 0.14285714285714285, -0.16666666666666666);
+  const double r4 = r2 * r2;
+  const double q = STK_FM_FMA(r2, p23, p01);
+  const double s = STK_FM_FMA(r4, p45, q);
+  const double lp = STK_FM_FMA(r2, s, r);
+  const double ed = (double)e;
+  const double hi_part = STK_FM_FMA(ed, 0.693147180369123816490, lc);
+  return hi_part + STK_FM_FMA(ed, 1.90821492927058770002e-10, lp);
+}
+STK_FM bool fast_log_ok(double x) {          // positive normal finite
+  const int hi = (int)(STK_FM_BITS(x) >> 32);
+  return hi >= 0x00100000 && hi < 0x7ff00000;
+}
 STK_FM double fast_log(double x, const double* tab) {
   const unsigned long long b = STK_FM_BITS(x);
   const int hi = (int)(b >> 32);

@@ -75,7 +75,7 @@ def test_logp_unsorted_data_and_invalid_state(ctx, orc):
             assert abs(lp[c] - want) <= 1e-10 * abs(want)
 
 
-@pytest.mark.parametrize("kernel", ["rj", "rj8", "rj32", "rj16", "rj4", "rj1", "rj2", "rj2x2", "rj2x1", "rj2x16", "rj2x32"])
+@pytest.mark.parametrize("kernel", ["rj", "rj8", "rj32", "rj16", "rj4", "rj1", "rj2", "rj2x2", "rj2x1", "rj2x16", "rj2x32", "rj3_4x2", "rj3_2x2", "rj3_2x4", "rj3_4x4", "rj3_1x4", "rj3_8x2"])
 def test_rj_trajectory_parity(ctx, orc, kernel):
     y = coal_days()
     C, steps, seed = 203, 400, 99

@@ -53,7 +53,7 @@
 #ifndef STK_ABI_H
 #define STK_ABI_H
 
-#define STK_MAX_FIELDS 24
+#define STK_MAX_FIELDS 48
 #define STK_MAX_PARAMS 16
 
 struct StkArgs {

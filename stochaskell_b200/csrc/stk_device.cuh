@@ -313,6 +313,81 @@ __device__ __noinline__ double log_abs_det(double* A, int n) {
   }
   return acc;
 }
+// ---- small dense linear algebra on per-thread storage (the Eigen one-liners of ccNode, CC.hs:157-166, 221-225; the interpreter's
+// hmatrix primitives, Data/Array/Abstract.hs:310-333).  Row-major, pitch = n.  Real function calls (see log_abs_det). -----------
+// lower Cholesky factor in place (`chol`, CC.hs:161-162: m.llt().matrixL()); the strict upper triangle is zeroed; a non-positive
+// pivot poisons the factor with NaN (the reference's `chol` raises an error there)
+__device__ __noinline__ void chol_lower(double* A, int n) {
+  bool bad = false;
+  for (int j = 0; j < n; ++j) {
+    double d = A[j * n + j];
+    for (int k = 0; k < j; ++k) d -= A[j * n + k] * A[j * n + k];
+    if (!(d > 0.0)) bad = true;
+    const double l = sqrt(d);
+    A[j * n + j] = l;
+    for (int i = j + 1; i < n; ++i) {
+      double v = A[i * n + j];
+      for (int k = 0; k < j; ++k) v -= A[i * n + k] * A[j * n + k];
+      A[i * n + j] = v / l;
+    }
+    for (int i = 0; i < j; ++i) A[i * n + j] = 0.0;
+  }
+  if (bad) for (int i = 0; i < n * n; ++i) A[i] = oob_value<double>();
+}
+// forward substitution L x = b, in place on b (b has m columns, row-major n x m)
+__device__ __noinline__ void tri_solve_lower(const double* L, int n, double* b, int m) {
+  for (int c = 0; c < m; ++c)
+    for (int i = 0; i < n; ++i) {
+      double v = b[i * m + c];
+      for (int k = 0; k < i; ++k) v -= L[i * n + k] * b[k * m + c];
+      b[i * m + c] = v / L[i * n + i];
+    }
+}
+// A X = B by LU with partial pivoting (`<\>`, CC.hs:159-160: colPivHouseholderQr().solve; `inv`, :163-164); A is destroyed, the
+// solution replaces B (n x m, row-major).  A singular matrix gives NaN.
+__device__ __noinline__ void lu_solve(double* A, int n, double* B, int m) {
+  bool bad = false;
+  for (int k = 0; k < n; ++k) {
+    int piv = k; double best = fabs(A[k * n + k]);
+    for (int i = k + 1; i < n; ++i) { const double v = fabs(A[i * n + k]); if (v > best) { best = v; piv = i; } }
+    if (!(best > 0.0)) bad = true;
+    if (piv != k) {
+      for (int j = 0; j < n; ++j) { const double t = A[k * n + j]; A[k * n + j] = A[piv * n + j]; A[piv * n + j] = t; }
+      for (int j = 0; j < m; ++j) { const double t = B[k * m + j]; B[k * m + j] = B[piv * m + j]; B[piv * m + j] = t; }
+    }
+    const double d = A[k * n + k];
+    for (int i = k + 1; i < n; ++i) {
+      const double f = A[i * n + k] / d;
+      if (f != 0.0) {
+        for (int j = k + 1; j < n; ++j) A[i * n + j] -= f * A[k * n + j];
+        for (int j = 0; j < m; ++j) B[i * m + j] -= f * B[k * m + j];
+      }
+    }
+  }
+  for (int c = 0; c < m; ++c)
+    for (int i = n - 1; i >= 0; --i) {
+      double v = B[i * m + c];
+      for (int k = i + 1; k < n; ++k) v -= A[i * n + k] * B[k * m + c];
+      B[i * m + c] = v / A[i * n + i];
+    }
+  if (bad) for (int i = 0; i < n * m; ++i) B[i] = oob_value<double>();
+}
+// determinant by the same factorisation (`det`)
+__device__ __noinline__ double det_lu(double* A, int n) {
+  double det = 1.0;
+  for (int k = 0; k < n; ++k) {
+    int piv = k; double best = fabs(A[k * n + k]);
+    for (int i = k + 1; i < n; ++i) { const double v = fabs(A[i * n + k]); if (v > best) { best = v; piv = i; } }
+    if (piv != k) { det = -det; for (int j = k; j < n; ++j) { const double t = A[k * n + j]; A[k * n + j] = A[piv * n + j]; A[piv * n + j] = t; } }
+    const double d = A[k * n + k];
+    det *= d;
+    if (d != 0.0) for (int i = k + 1; i < n; ++i) {
+      const double f = A[i * n + k] / d;
+      if (f != 0.0) for (int j = k + 1; j < n; ++j) A[i * n + j] -= f * A[k * n + j];
+    }
+  }
+  return det;
+}
 STK_DEV int find_sorted_insert_index_v(double e, const VecD& v) {     // CC.hs:192-197
   int j = v.len + 1;
   for (int i = 1; i <= v.len; ++i) if (e < v.at(i)) { j = i; break; }

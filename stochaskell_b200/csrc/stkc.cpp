@@ -213,7 +213,7 @@ struct Parser {
     if (x.s == "ZVec" || x.s == "RVec" || x.s == "BVec") return vecT(scalarT(x.s[0] == 'Z' ? Type::Z : x.s[0] == 'R' ? Type::R : Type::B));
     if (x.s == "ZMat" || x.s == "RMat") { Type m; m.k = Type::Mat; m.sub.push_back(scalarT(x.s[0] == 'Z' ? Type::Z : Type::R)); return m; }
     if (x.s == "vector") return vecT(type());
-    if (x.s == "matrix") { Type m; m.k = Type::Mat; m.sub.push_back(type()); return m; }
+    if (x.s == "matrix" || x.s == "corr_matrix" || x.s == "cov_matrix") { Type m; m.k = Type::Mat; m.sub.push_back(type()); return m; }
     if (x.s == "Array" && is("[")) {  // `Array [(lo,hi)] T`: how the 2019 build behind rj-coal.ipynb printed a 1-D array type
       next(); expect("("); ref(); expect(","); ref(); expect(")");
       if (accept(",")) fail("multi-dimensional Array types are not supported by the CUDA lowering");
@@ -1102,6 +1102,29 @@ struct Gen {
     else if (f == "matrixCols") e = mat_of(n.args.at(0))->cols;
     else if (f == "matrixRows") e = mat_of(n.args.at(0))->rows;
     else if (f == "log_det") { log_det_node(d); return; }
+    else if (f == "det") {
+      std::string R, C, mb = mat_store(mat_of(n.args.at(0)), d.id, &R, &C);
+      e = "stk::det_lu(" + mb + ", " + R + ")";
+    }
+    else if (f == "<.>") {                                                                // dot product
+      VA x = va(n.args.at(0)), y = va(n.args.at(1));
+      std::string k = fresh("k");
+      line("double " + d.id + " = 0.0;");
+      line("for (int " + k + " = 1; " + k + " <= " + x.len + "; ++" + k + ") " + d.id + " += " + x.at(k) + " * " + y.at(k) + ";");
+      v.expr = d.id; bind(d.id, v); return;
+    }
+    else if (f == "multi_normal_lpdf") {
+      // ccNode's template (CC.hs:221-225): -0.5 * ((L^-1 (z - m)).squaredNorm() + log(2 pi) n + LOG_DET(C)), L = chol C
+      VA z = va(n.args.at(0)), mu = va(n.args.at(1));
+      std::string R, C, cb = mat_store(mat_of(n.args.at(2)), d.id, &R, &C), rb = fresh(d.id + "_r"), i = fresh("i"), ss = fresh("ss"), ld = fresh("ld");
+      decls << "  double " << rb << "[STK_MATCAP];\n";
+      line("stk::chol_lower(" + cb + ", " + R + ");");
+      line("for (int " + i + " = 1; " + i + " <= " + R + "; ++" + i + ") " + rb + "[" + i + " - 1] = " + z.at(i) + " - " + mu.at(i) + ";");
+      line("stk::tri_solve_lower(" + cb + ", " + R + ", " + rb + ", 1);");
+      line("double " + ss + " = 0.0, " + ld + " = 0.0;");
+      line("for (int " + i + " = 0; " + i + " < " + R + "; ++" + i + ") { " + ss + " += " + rb + "[" + i + "] * " + rb + "[" + i + "]; " + ld + " += log(" + cb + "[" + i + " * " + R + " + " + i + "]); }");
+      e = "-0.5 * (" + ss + " + stk::kLog2Pi * (double)" + R + " + 2.0 * " + ld + ")";
+    }
     else if (f == "poissonProcess_lpdf") { poisson_process_node(d); return; }
     else if (f == "findSortedInsertIndex") e = "stk::find_sorted_insert_index_v(" + arg(0, true) + ", " + vec_value(n.args.at(1)) + ")";   // CC.hs:192-197
     else if (f == "logFactorial") e = "stk::log_factorial(" + arg(0) + ")";               // CC.hs:167-168
@@ -1165,6 +1188,26 @@ struct Gen {
     }
     std::string ct = real ? "double" : "int", buf = fresh(d.id + "_buf");
     decls << "  " << ct << " " << buf << "[STK_VECCAP];\n";
+    if (f == "#>" || (f == "<\\>" && type_of(n.args.at(0)).k == Type::Mat)) {
+      // matrix #> vector (CC.hs:157-158) and matrix <\> vector (CC.hs:159-160: the solution of M x = v)
+      std::shared_ptr<Mat> m = mat_of(n.args.at(0));
+      VA x = va(n.args.at(1));
+      std::string ln = fresh("n"), i = fresh("i"), k = fresh("k"), acc = fresh("acc");
+      if (f == "#>") {
+        m->prepare();
+        line("const int " + ln + " = stk::cap_len(" + m->rows + ", STK_VECCAP, err_);");
+        line("for (int " + i + " = 1; " + i + " <= " + ln + "; ++" + i + ") { double " + acc + " = 0.0; for (int " + k + " = 1; " + k + " <= " + m->cols + "; ++" + k + ") " +
+             acc + " += " + m->at(i, k) + " * " + x.at(k) + "; " + buf + "[" + i + " - 1] = " + acc + "; }");
+      } else {
+        std::string R, C, mb = mat_store(m, d.id, &R, &C);
+        line("const int " + ln + " = stk::cap_len(" + R + ", STK_VECCAP, err_);");
+        line("for (int " + i + " = 1; " + i + " <= " + ln + "; ++" + i + ") " + buf + "[" + i + " - 1] = " + x.at(i) + ";");
+        line("stk::lu_solve(" + mb + ", " + R + ", " + buf + ", 1);");
+      }
+      line("const " + ctype(n.type) + " " + d.id + "(" + buf + ", 1, " + ln + ");");
+      Val v; v.type = n.type; v.expr = d.id; bind(d.id, v);
+      return;
+    }
     std::string src = vec_value(n.args.at(0)), i = fresh("i"), ln = fresh("n");
     // every copy into per-thread storage is bounded by STK_VECCAP; an overflow sets the module's err flag
     if (f == "replaceIndex") {
@@ -1420,8 +1463,54 @@ struct Gen {
     die("a matrix was expected");
   }
 
+  // write a matrix expression into per-thread storage (row-major, pitch = its column count); returns the buffer and the names of
+  // the int variables holding its dimensions
+  std::string mat_store(const std::shared_ptr<Mat>& m, const std::string& hint, std::string* R, std::string* C) {
+    if (inline_mode) throw NotInlinable();
+    m->prepare();
+    std::string buf = fresh(hint + "_mat"), i = fresh("i"), j = fresh("j");
+    *R = fresh("R"); *C = fresh("C");
+    decls << "  double " << buf << "[STK_MATCAP * STK_MATCAP];\n";
+    line("const int " + *R + " = stk::cap_len(" + m->rows + ", STK_MATCAP, err_, 3), " + *C + " = stk::cap_len(" + m->cols + ", STK_MATCAP, err_, 3);");
+    if (m->zeros) line("for (int " + i + " = 0; " + i + " < " + *R + " * " + *C + "; ++" + i + ") " + buf + "[" + i + "] = 0.0;");
+    else line("for (int " + i + " = 1; " + i + " <= " + *R + "; ++" + i + ") for (int " + j + " = 1; " + j + " <= " + *C + "; ++" + j + ") " + buf + "[(" + i + " - 1) * " + *C + " + " + j + " - 1] = " + m->at(i, j) + ";");
+    return buf;
+  }
+  static std::shared_ptr<Mat> stored_mat(const std::string& buf, const std::string& R, const std::string& C) {
+    auto m = std::make_shared<Mat>();
+    m->rows = R; m->cols = C; m->prepare = [] {};
+    m->at = [buf, C](const std::string& i, const std::string& j) { return buf + "[((" + i + ") - 1) * " + C + " + (" + j + ") - 1]"; };
+    return m;
+  }
+
   void mat_def(const Def& d) {
     const Node& n = d.node; const std::string& f = n.f;
+    if (f == "chol" || f == "inv" || (f == "<\\>" && n.args.size() == 2)) {
+      // factorisations: the operand is written into per-thread storage at the definition and factorised / solved in place
+      // (`chol` CC.hs:161-162, `inv` :163-164, `<\>` :159-160)
+      std::string R, C, buf = mat_store(mat_of(n.args.at(0)), d.id, &R, &C);
+      if (f == "chol") { line("stk::chol_lower(" + buf + ", " + R + ");"); Val v; v.type = n.type; v.mat = stored_mat(buf, R, R); bind(d.id, v); return; }
+      std::string R2, C2, rhs;
+      if (f == "inv") {
+        auto eye = std::make_shared<Mat>(); eye->rows = eye->cols = R; eye->eye = true; eye->prepare = [] {};
+        eye->at = [](const std::string& i, const std::string& j) { return "((" + i + ") == (" + j + ") ? 1.0 : 0.0)"; };
+        rhs = mat_store(eye, d.id + "_rhs", &R2, &C2);
+      } else rhs = mat_store(mat_of(n.args.at(1)), d.id + "_rhs", &R2, &C2);
+      line("stk::lu_solve(" + buf + ", " + R + ", " + rhs + ", " + C2 + ");");
+      Val v; v.type = n.type; v.mat = stored_mat(rhs, R2, C2); bind(d.id, v); return;
+    }
+    if (f == "diag") {
+      VA dv = va(n.args.at(0));
+      auto m = std::make_shared<Mat>(); m->rows = m->cols = dv.len; m->prepare = [] {};
+      m->at = [dv](const std::string& i, const std::string& j) { return "((" + i + ") == (" + j + ") ? " + dv.at(i) + " : 0.0)"; };
+      Val v; v.type = n.type; v.mat = m; bind(d.id, v); return;
+    }
+    if (f == "outer") {
+      VA a = va(n.args.at(0)), b = va(n.args.at(1));
+      auto m = std::make_shared<Mat>(); m->rows = a.len; m->cols = b.len; m->prepare = [] {};
+      m->at = [a, b](const std::string& i, const std::string& j) { return "(" + a.at(i) + " * " + b.at(j) + ")"; };
+      Val v; v.type = n.type; v.mat = m; bind(d.id, v); return;
+    }
     auto m = std::make_shared<Mat>();
     m->prepare = [] {};
     auto is_mat = [&](size_t i) { return type_of(n.args.at(i)).k == Type::Mat; };
@@ -1845,6 +1934,64 @@ struct Gen {
            (elem.empty() ? std::string("0u") : "(unsigned)" + elem + " << 16") + ";";
   }
 
+  // draws whose arguments or values are matrices (only the reference's interpreter samples them: samplePNode,
+  // Program.hs:1114-1157; definitions Data/Random/Distribution/Abstract.hs:91-98, 172-189), on per-thread storage:
+  //   multi_normal m S   x = m + chol(S) #> w, w_k ~ normal 0 1 (element k of the PNode's counter range)
+  //   wishart n V        Bartlett as the reference writes it: A lower triangular, A_ii = chiSquare (n - i + 1) (the draw itself,
+  //                      not its square root — restated faithfully), A_ij ~ normal 0 1 (i > j), L = chol V, L A (L A)^T
+  //   inv_wishart n W    inv (wishart n (inv W))
+  //   lkj_corr v         2 x 2 only, as the reference: [[1, r], [r, 1]], r = 2 beta(v, v) - 1
+  bool matrix_dist_node(const PNode& q, const std::string& slot) {
+    const std::string& f = q.dist;
+    if (f == "multi_normal" || ((f == "normal" || f == "normals") && q.type.k == Type::Vec && q.args.size() == 2 && type_of(q.args[1]).k == Type::Mat)) {
+      VA m = va(q.args.at(0));
+      std::string R, C, L = mat_store(mat_of(q.args.at(1)), q.id + "_S", &R, &C);
+      std::string buf = fresh(q.id + "_buf"), wb = fresh(q.id + "_w"), n = fresh("n"), i = fresh("i"), k = fresh("k"), g = fresh("g"), acc = fresh("acc");
+      decls << "  double " << buf << "[STK_VECCAP];\n  double " << wb << "[STK_VECCAP];\n";
+      line("stk::chol_lower(" + L + ", " + R + ");");
+      line("const int " + n + " = stk::cap_len(" + R + ", STK_VECCAP, err_);");
+      line("for (int " + k + " = 1; " + k + " <= " + n + "; ++" + k + ") { " + gen_decl(g, slot, k) + " " + wb + "[" + k + " - 1] = stk::draw_normal(" + g + ", 0.0, 1.0); }");
+      line("for (int " + i + " = 1; " + i + " <= " + n + "; ++" + i + ") { double " + acc + " = " + m.at(i) + "; for (int " + k + " = 1; " + k + " <= " + i + "; ++" + k + ") " +
+           acc + " += " + L + "[(" + i + " - 1) * " + R + " + " + k + " - 1] * " + wb + "[" + k + " - 1]; " + buf + "[" + i + " - 1] = " + acc + "; }");
+      Type vt = vecT(scalarT(Type::R));
+      line("const VecD " + q.id + "(" + buf + ", 1, " + n + ");");
+      Val v; v.type = vt; v.expr = q.id; bind(q.id, v);
+      return true;
+    }
+    if (f == "wishart" || f == "inv_wishart") {
+      const bool inv = f == "inv_wishart";
+      std::string df = rv(q.args.at(0));
+      std::string R, C, V = mat_store(mat_of(q.args.at(1)), q.id + "_V", &R, &C);
+      std::string A = fresh(q.id + "_A"), B = fresh(q.id + "_B"), W = fresh(q.id + "_W"), i = fresh("i"), j = fresh("j"), k = fresh("k"), g = fresh("g"), acc = fresh("acc");
+      decls << "  double " << A << "[STK_MATCAP * STK_MATCAP];\n  double " << B << "[STK_MATCAP * STK_MATCAP];\n  double " << W << "[STK_MATCAP * STK_MATCAP];\n";
+      auto ident = [&](const std::string& buf) { line("for (int " + i + " = 0; " + i + " < " + R + "; ++" + i + ") for (int " + j + " = 0; " + j + " < " + R + "; ++" + j + ") " + buf + "[" + i + " * " + R + " + " + j + "] = " + i + " == " + j + " ? 1.0 : 0.0;"); };
+      if (inv) { ident(B); line("stk::lu_solve(" + V + ", " + R + ", " + B + ", " + R + ");"); line("for (int " + i + " = 0; " + i + " < " + R + " * " + R + "; ++" + i + ") " + V + "[" + i + "] = " + B + "[" + i + "];"); }
+      line("stk::chol_lower(" + V + ", " + R + ");");
+      // element (i, j) of A draws with element index (i - 1) p + j of the PNode's counter range
+      line("for (int " + i + " = 1; " + i + " <= " + R + "; ++" + i + ") for (int " + j + " = 1; " + j + " <= " + R + "; ++" + j + ") { " + gen_decl(g, slot, "((" + i + " - 1) * " + R + " + " + j + ")") +
+           " " + A + "[(" + i + " - 1) * " + R + " + " + j + " - 1] = " + i + " == " + j + " ? stk::draw_gamma(" + g + ", 0.5 * (double)(" + df + " - " + i + " + 1), 0.5) : (" + i + " > " + j + " ? stk::draw_normal(" + g + ", 0.0, 1.0) : 0.0); }");
+      auto matmul = [&](const std::string& out, const std::string& X, const std::string& Y, bool yt) {      // out = X Y or X Y^T
+        line("for (int " + i + " = 0; " + i + " < " + R + "; ++" + i + ") for (int " + j + " = 0; " + j + " < " + R + "; ++" + j + ") { double " + acc + " = 0.0; for (int " + k + " = 0; " + k + " < " + R + "; ++" + k + ") " +
+             acc + " += " + X + "[" + i + " * " + R + " + " + k + "] * " + Y + (yt ? "[" + j + " * " + R + " + " + k + "]" : "[" + k + " * " + R + " + " + j + "]") + "; " + out + "[" + i + " * " + R + " + " + j + "] = " + acc + "; }");
+      };
+      matmul(B, V, A, false);              // B = L A
+      matmul(W, B, B, true);               // W = B B^T = L A A^T L^T
+      if (inv) { ident(B); line("stk::lu_solve(" + W + ", " + R + ", " + B + ", " + R + ");"); line("for (int " + i + " = 0; " + i + " < " + R + " * " + R + "; ++" + i + ") " + W + "[" + i + "] = " + B + "[" + i + "];"); }
+      Val v; v.type = q.type; v.mat = stored_mat(W, R, R); bind(q.id, v);
+      return true;
+    }
+    if (f == "lkj_corr") {
+      std::string g = fresh("g"), r = fresh(q.id + "_r");
+      line(gen_decl(g, slot, ""));
+      line("const double " + r + " = stk::draw_lkj_corr2(" + g + ", " + rv(q.args.at(0), true) + ");");
+      auto m = std::make_shared<Mat>(); m->rows = m->cols = "2"; m->prepare = [] {};
+      m->at = [r](const std::string& i, const std::string& j) { return "((" + i + ") == (" + j + ") ? 1.0 : " + r + ")"; };
+      Val v; v.type = q.type; v.mat = m; bind(q.id, v);
+      return true;
+    }
+    return false;
+  }
+
   void pnode(const PNode& q) {
     int level, ptr; id_level_ptr(q.id, &level, &ptr);
     // the PNode's own word of the Philox counter (slots of different PNodes must not be reachable from one another)
@@ -1857,6 +2004,7 @@ struct Gen {
     if (q.k == PNode::Ordered) { ordered_node(q, slot); return; }
     if (vectorised_node(q, slot)) return;
     for (auto& a : q.args) need(a);
+    if (matrix_dist_node(q, slot)) return;
     std::string g = fresh("g");
     line(gen_decl(g, slot, ""));
     std::string e = draw_expr(q, g);
@@ -2073,6 +2221,16 @@ static std::string generate(const std::string& ir, const std::string& input_type
                ", (int*)a.field[F_" + nm + "_len] + chain, err_);");
         continue;
       }
+      if (rt.k == Type::Mat) {                         // a matrix value: [matcap * matcap][chains] row-major + its dimensions
+        std::shared_ptr<Mat> m = g.mat_of(prog.rets[k]);
+        m->prepare();
+        out_fields.push_back({nm, false, std::to_string(matcap * matcap)}); out_fields.push_back({nm + "_rows", true, "1"}); out_fields.push_back({nm + "_cols", true, "1"});
+        std::string R = g.fresh("R"), C = g.fresh("C"), i = g.fresh("i"), j = g.fresh("j");
+        g.line("{ const int " + R + " = stk::cap_len(" + m->rows + ", STK_MATCAP, err_, 3), " + C + " = stk::cap_len(" + m->cols + ", STK_MATCAP, err_, 3);");
+        g.line("  for (int " + i + " = 1; " + i + " <= " + R + "; ++" + i + ") for (int " + j + " = 1; " + j + " <= " + C + "; ++" + j + ") ((double*)a.field[F_" + nm + "])[(long long)((" + i + " - 1) * " + C + " + " + j + " - 1) * a.n_chains + chain] = " + m->at(i, j) + ";");
+        g.line("  ((int*)a.field[F_" + nm + "_rows])[chain] = " + R + "; ((int*)a.field[F_" + nm + "_cols])[chain] = " + C + "; }");
+        continue;
+      }
       if (!rt.scalar()) die("simulate: return of type " + rt.str() + " is not supported");
       out_fields.push_back({nm, rt.k != Type::R, "1"});
       g.line("((" + std::string(rt.k != Type::R ? "int" : "double") + "*)a.field[F_" + nm + "])[chain] = " + g.rv(prog.rets[k], rt.k == Type::R) + ";");
@@ -2093,7 +2251,7 @@ static std::string generate(const std::string& ir, const std::string& input_type
   }
   for (auto& f : out_fields) fields.push_back(f);
   { Field ef{"err", true, "1"}; ef.kind = "work"; fields.push_back(ef); }   // overflow flag, checked by the runtime after the launch
-  if ((int)fields.size() > 24) die("too many state fields");
+  if ((int)fields.size() > 48) die("too many state fields (the module ABI carries 48, stk_abi.h)");
 
   std::ostringstream o;
   o << "// generated by stkc (libstk_cuda, Language.CUDA lowering) — do not edit\n";

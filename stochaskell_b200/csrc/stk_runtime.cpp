@@ -356,7 +356,8 @@ int check_err(stk_chains* c) {
   return fail(STK_ERR_ARG, "module %s: a kernel reported error %d (%s); the chain state is not valid — rebuild the module with a larger "
               "veccap / upload the state field with more rows", c->mod->name.c_str(), code,
               code == 1 ? "a vector outgrew the per-thread storage STK_VECCAP" : code == 2 ? "a vector outgrew the capacity of its state field" :
-              code == 3 ? "a matrix outgrew the per-thread storage STK_MATCAP" : "unknown");
+              code == 3 ? "a matrix outgrew the per-thread storage STK_MATCAP" :
+              code == 4 ? "a program's conditions (guard) were not met in 65536 attempts" : "unknown");
 }
 
 // data fields declared with a length expression (e.g. `field X data f64 @y*10`) must have exactly that many elements

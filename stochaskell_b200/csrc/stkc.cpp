@@ -2249,6 +2249,16 @@ static std::string generate(const std::string& ir, const std::string& input_type
       g.line("((double*)a.field[F_" + nm + "])[chain] = " + g.rv(r, true) + ";");
     }
   }
+  std::string guard_cond;
+  if (opt.count("guard")) {
+    if (kernel) die("guard= applies to simulate programs (a kernel's conditions are part of its acceptance ratio)");
+    std::istringstream gs(opt["guard"]); std::string id;
+    while (std::getline(gs, id, ',')) {
+      if (id.empty()) continue;
+      auto r = std::make_shared<Ref>(); r->k = Ref::Var; r->name = id;
+      guard_cond += (guard_cond.empty() ? "(" : " && (") + g.rv(r) + ")";
+    }
+  }
   for (auto& f : out_fields) fields.push_back(f);
   { Field ef{"err", true, "1"}; ef.kind = "work"; fields.push_back(ef); }   // overflow flag, checked by the runtime after the launch
   if ((int)fields.size() > 48) die("too many state fields (the module ABI carries 48, stk_abi.h)");
@@ -2285,6 +2295,13 @@ static std::string generate(const std::string& ir, const std::string& input_type
     o << g.out.str() << feed.str();
     o << "  }\n" << store.str() << "}\n";
   } else {
+    if (!guard_cond.empty()) {
+      // conditions of the program (`guard`, Program.hs:745-760): samplePBlock re-draws the WHOLE program until every condition holds
+      // (Program.hs:1046-1058).  Attempt k draws from the streams of transition 2^64 - 1 - k; the loop gives up after 2^16 attempts
+      // and reports it through the err flag (code 4) instead of hanging the device.
+      o << "  unsigned try_ = 0;\n  for (; try_ < 65536u; ++try_) {\n    Rng rng; rng.init(a.seed, (u64)(a.chain0 + chain), ~0ULL - (u64)try_);\n"
+        << g.out.str() << "    if (" << guard_cond << ") break;\n  }\n  if (try_ == 65536u) *err_ = 4;\n}\n";
+    } else
     o << "  {\n    Rng rng; rng.init(a.seed, (u64)(a.chain0 + chain), ~0ULL);\n" << g.out.str() << "  }\n}\n";
   }
   o << "extern \"C\" __device__ const char stk_desc[] =\n  \"stk-module 1\\n\"\n  \"name " << name << "\\n\"\n  \"nparam 0\\n\"\n";

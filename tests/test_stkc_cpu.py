@@ -220,3 +220,16 @@ def test_lpdf_program_with_adt_case_lowers_to_a_logp_entry(tmp_path):
     compile_source(src, str(tmp_path))
     with pytest.raises(StkError):
         ir_to_cuda(ir("soccer_rj"), [SOCCER_T], entry="logp")          # a kernel returning a state is not a log-density
+
+
+def test_guard_conditions_become_a_rejection_loop(tmp_path):
+    """`guard` conditions of a simulate program (linreg.ipynb cell 2: `guard $ sigma < 2`): samplePBlock re-draws the whole
+    program until every condition holds (Program.hs:1046-1058); here a bounded retry loop with its own Philox streams"""
+    text = ("let v_0_0 = getExternal x_s_0_0 :: R\n    v_0_1 = x_s_0_0 < 2.0 :: B\n    v_0_2 = 0.5 < x_s_0_0 :: B\n"
+            " in do x_s_0_0 <- gamma 2.0 1.0 :: P R\n       return [v_0_0]\n")
+    src = ir_to_cuda(text, [], name="guarded", guard="v_0_1,v_0_2")
+    assert "for (; try_ < 65536u; ++try_)" in src and "~0ULL - (u64)try_" in src and "if ((v_0_1) && (v_0_2)) break;" in src
+    assert "*err_ = 4" in src
+    compile_source(src, str(tmp_path))
+    with pytest.raises(StkError):
+        ir_to_cuda(ir("mh_sym"), ["R"], guard="v_0_1")      # kernels have no guard

@@ -177,6 +177,20 @@ int stk_nccl_unique_id(void* id128);
 int stk_nccl_comm_create(stk_ctx* ctx, int n_ranks, int rank, const void* id128, stk_comm** out);
 int stk_nccl_comm_destroy(stk_comm* comm);
 int stk_moments_nccl(stk_chains* ch, stk_comm* comm, double* mean, double* var, double* rhat, double* ess);
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (CUDA graph capture, tight serving loops, harnesses that forbid allocation).  stk_diag_partial's additive buffer, computed by
+ * variant kernels (csrc/stk_noalloc.cu) whose per-chain scratch (the [n_values][n_chains] chain means) is a static __device__
+ * array of 512*1024 doubles (4 MiB, held by every GPU that loads the library) — the call allocates and frees nothing.
+ *   d_draws  DEVICE pointer, [n_draws][n_values][n_chains] (the layout of stk_get_draws)
+ *   d_buf    DEVICE pointer, bytes = 8*n_values*(4+max_lag+1) (max_lag < 0 or > n_draws-1 means n_draws-1), cleared here
+ *   stream   cudaStream_t of the CURRENT device (NULL = its default stream); the memset and the two kernels are enqueued on
+ *            it and the call returns without synchronising; read d_buf after the stream has reached this point and
+ *            finish with stk_diag_finish.
+ * Limits: n_values*n_chains <= 524288 (STK_ERR_UNSUPPORTED beyond it), n_draws <= 25600, n_values <= 65535.  The first call
+ * on a device looks the array's address up (cudaGetSymbolAddress) — make it before starting a capture.  All calls on a device
+ * share the one array, which keeps the last call's contents: calls that overlap on the GPU race, serialise them. */
+int stk_diag_partial_noalloc(const double* d_draws, int64_t n_draws, int n_values, int64_t n_chains, int64_t max_lag,
+                             double* d_buf, size_t bytes, stk_stream stream);
 int stk_sync(stk_chains* ch);
 /* doubles per recorded draw per chain (P_rec), valid after stk_record */
 int stk_num_recorded_values(stk_chains* ch);

@@ -61,6 +61,7 @@ SIGNATURES = {
     "stk_moments_nccl": (C.c_int, [C.c_void_p, C.c_void_p] + [C.c_void_p] * 4),
     "stk_diag_partial": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_size_t]),
     "stk_diag_finish": (C.c_int, [C.c_void_p, C.c_int, C.c_int64, C.c_int64] + [C.c_void_p] * 4),
+    "stk_diag_partial_noalloc": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_size_t, C.c_void_p]),
     "stk_sync": (C.c_int, [C.c_void_p]),
     "stk_num_params": (C.c_int, [C.c_void_p]),
     "stk_num_chains": (C.c_int64, [C.c_void_p]),

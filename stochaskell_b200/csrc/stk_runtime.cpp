@@ -1243,3 +1243,7 @@ int stk_moments_multi(stk_chains* const* shards, int n_shards, double* mean, dou
 }  // extern "C"
 
 extern "C" int stk_num_recorded_values(stk_chains* c) { return c ? (int)c->nrec : fail(STK_ERR_ARG, "null chains"); }
+
+// hooks for stk_noalloc.cu (a separate nvcc translation unit): the thread-local error text and the launch counter live here
+extern "C" int stk_fail_(int code, const char* msg) { return fail(code, "%s", msg ? msg : ""); }
+extern "C" void stk_count_launches_(int n) { g_launches.fetch_add(n); }

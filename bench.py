@@ -637,6 +637,27 @@ class LinregHMCIR(LinregHMC):
         return dict(x_stan_0_0=self.X, x_stan_0_4=self.y)
 
 
+class BiratsHMCIR(BiratsHMC):
+    """C4 through the CODE GENERATOR: the birats model's IR (tests/golden/ir/birats_model.txt: corr_matrix parameter, multivariate
+    normal rows of a joint, matrix algebra) lowered by the gradient lowering — one thread per chain, 66 parameters in registers /
+    local memory — against the hand-tuned builtin:birats (a warp per four chains) on the same data, start and Philox stream."""
+    name = "birats_hmc_ir"
+    symbol = "stk_ir_hmc"
+    generated_from = "birats_hmc"
+    logpdf_populations = None
+    ncu_traffic_bytes = None
+
+    def __init__(self):
+        super().__init__()
+        from stochaskell_b200 import model_to_module
+        ir = open(os.path.join(ROOT, "tests", "golden", "ir", "birats_model.txt")).read()
+        self.module = model_to_module(ir, ("x_stan_0_0", "x_stan_0_6"), name="birats_ir")
+        self.describe = self.describe.replace("C4 birats", "C4 birats, module GENERATED from the model IR (stkc gradient lowering),")
+
+    def data(self):
+        return dict(x_stan_0_0=self.x, x_stan_0_6=self.y)
+
+
 class CoalRJIR(CoalRJ):
     """C2 through the CODE GENERATOR: the kernel IR that `runStep` printed for `coal t 'rjmc' coalMove' t` (rj-coal.ipynb
     cell 8, tests/golden/ir/coal_rj.txt) lowered by stkc — one thread per chain, the reference's own node-by-node evaluation
@@ -783,7 +804,7 @@ class SoccerRJSeq(SoccerRJ):
     stan_exe = None
 
 
-WORKLOADS = {"linreg_hmc_ir": LinregHMCIR, "coal_rj_ir": CoalRJIR, "soccer_rj": SoccerRJ, "soccer_rj_seq": SoccerRJSeq, "gp_hmc_tc": GPHMCTC, "linreg_hmc": LinregHMC, "linreg_nuts": LinregNUTS, "coal_rj": CoalRJ, "birats_hmc": BiratsHMC, "birats_nuts": BiratsNUTS, "dp_gibbs": DPGibbs, "gp_hmc": GPHMC, "gpr_mh": GPRMH}
+WORKLOADS = {"linreg_hmc_ir": LinregHMCIR, "birats_hmc_ir": BiratsHMCIR, "coal_rj_ir": CoalRJIR, "soccer_rj": SoccerRJ, "soccer_rj_seq": SoccerRJSeq, "gp_hmc_tc": GPHMCTC, "linreg_hmc": LinregHMC, "linreg_nuts": LinregNUTS, "coal_rj": CoalRJ, "birats_hmc": BiratsHMC, "birats_nuts": BiratsNUTS, "dp_gibbs": DPGibbs, "gp_hmc": GPHMC, "gpr_mh": GPRMH}
 DEFAULT_WORKLOAD = "coal_rj"
 
 

@@ -457,6 +457,9 @@ def constrain_draws(descriptor: str, draws: np.ndarray) -> Dict[str, np.ndarray]
         if not t or t[0] != "qmap":
             continue
         ident, off, rows, cols, lo, hi = t[1], int(t[2]), int(t[3]), int(t[4]), t[5], t[6]
+        if lo == "corr":
+            out[ident] = _corr_matrix_constrain(draws[:, off:off + rows * (rows - 1) // 2, :], rows)
+            continue
         n = max(1, rows) * max(1, cols)
         x = draws[:, off:off + n, :]
         if lo != "-" and hi == "-":
@@ -465,9 +468,33 @@ def constrain_draws(descriptor: str, draws: np.ndarray) -> Dict[str, np.ndarray]
             x = float(hi) - np.exp(x)
         elif lo != "-" and hi != "-":
             x = float(lo) + (float(hi) - float(lo)) / (1.0 + np.exp(-x))
-        shape = (draws.shape[0],) + ((rows, cols) if cols else (rows,) if rows else ()) + (draws.shape[2],)
-        out[ident] = x.reshape(shape)
+        if cols:            # a matrix block is column-major in q (Stan's order): [S][cols][rows][C] -> [S][rows][cols][C]
+            out[ident] = x.reshape(draws.shape[0], cols, rows, draws.shape[2]).transpose(0, 2, 1, 3)
+        else:
+            out[ident] = x.reshape((draws.shape[0],) + ((rows,) if rows else ()) + (draws.shape[2],))
     return out
+
+
+def _corr_matrix_constrain(y: np.ndarray, K: int) -> np.ndarray:
+    """[S][K(K-1)/2][C] unconstrained values -> [S][K][K][C] correlation matrices: tanh -> canonical partial correlations ->
+    Cholesky factor -> L L' (Stan's corr_matrix_constrain / read_corr_L, the transform lkj_node of csrc/stkc_grad.inc applies)"""
+    z = np.tanh(y)
+    S, _, C = y.shape
+    L = np.zeros((S, K, K, C))
+    acc = np.ones((S, K - 1, C))
+    L[:, 0, 0] = 1.0
+    L[:, 1:, 0] = z[:, :K - 1]
+    acc[:] = 1.0 - z[:, :K - 1] ** 2
+    position, pull = 0, K - 1
+    for i in range(1, K - 1):
+        position += pull
+        pull -= 1
+        cpc = z[:, position:position + pull]
+        L[:, i, i] = np.sqrt(acc[:, i - 1])
+        L[:, K - pull:, i] = cpc * np.sqrt(acc[:, K - 1 - pull:])
+        acc[:, K - 1 - pull:] *= 1.0 - cpc ** 2
+    L[:, K - 1, K - 1] = np.sqrt(acc[:, K - 2])
+    return np.einsum("sikc,sjkc->sijc", L, L)
 
 
 def hmcCUDA(method: CudaMethod, module_spec: str, data: dict, init: Optional[Sequence[float]] = None,

@@ -220,9 +220,13 @@ struct Parser {
       expect("]");
       return vecT(type());
     }
-    if (x.s == "Array") {            // Array lo...hi[, lo...hi] T   (1-D only)
+    if (x.s == "Array") {            // Array lo...hi[, lo...hi] T   (showType of ArrayT Nothing, Expression.hs:444-445: what `joint` builds, Program.hs:711-721)
       ref(); expect("..."); ref();
-      if (accept(",")) fail("multi-dimensional Array types are not supported by the CUDA lowering");
+      if (accept(",")) {
+        ref(); expect("..."); ref();
+        if (accept(",")) fail("Array types of more than two dimensions are not supported by the CUDA lowering");
+        Type m; m.k = Type::Mat; m.sub.push_back(type()); return m;
+      }
       return vecT(type());
     }
     if (x.s == "Subrange") {       // Subrange T lo hi (showType, Expression.hs:442-443); `Nothing` = unbounded

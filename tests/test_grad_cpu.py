@@ -68,3 +68,72 @@ def test_gradient_lowering_refuses_what_it_cannot_differentiate():
     with pytest.raises(StkError) as e:        # everything conditioned on: nothing to sample
         ir_to_cuda(base, [], mode="density", given="x_stan_0_0,x_stan_0_1,x_stan_0_2,x_stan_0_3,x_stan_0_4")
     assert "no free parameter" in str(e.value)
+
+
+def test_birats_model_matches_the_reference_backend_on_the_host(tmp_path):
+    """birats (app/benchmark/Main.hs:106-125, birats.ipynb cell 6) lowered from IR: corr_matrix parameter through Stan's CPC
+    transform, multivariate-normal rows of a joint, matrix algebra (tr', asColumn, asRow, <>, broadcast +, quad_form_diag).
+    The emitted stk_eval / stk_eval_grad, compiled as host code (tests/gen_host.py), against log_prob_grad of the vendored
+    CmdStan 2.20 on the notebook's Stan program (tests/golden/birats_stan.npz): 1e-10 relative (north_star, fp64 tier).
+    The parameter layout is the reference's: betaMu[2], tau[2] UNTRANSFORMED (a joint is declared `vector[2]`, Stan.hs:105-106
+    + Program.hs:709, so its truncation is only T[0,]), 1 CPC, beta column-major, log sigma."""
+    import numpy as np
+    from tests.gen_host import host_eval
+    src = ir_to_cuda(ir("birats_model"), [], name="birats_ir", mode="density", given="x_stan_0_0,x_stan_0_6")
+    assert "#define NP 66" in src and "one thread per chain" in src
+    assert "qmap x_stan_0_2 2 2 0 - -" in src and "qmap x_stan_0_3 4 2 2 corr -" in src and "qmap x_stan_0_4 5 30 2 - -" in src
+    assert "qmap x_stan_0_5 65 0 0 0.0 -" in src
+    g = np.load(os.path.join(os.path.dirname(IR), "birats_stan.npz"))
+    f = host_eval(src, dict(x_stan_0_0=g["x"], x_stan_0_6=g["y"]), str(tmp_path))
+    for k in range(len(g["q"])):
+        lp, gr = f(g["q"][k])
+        assert abs(lp - g["lp"][k]) <= 1e-10 * abs(g["lp"][k]), k
+        assert abs(f(g["q"][k], grad=False) - g["lp"][k]) <= 1e-10 * abs(g["lp"][k])
+        assert np.max(np.abs(gr - g["grad"][k])) <= 1e-10 * max(1.0, np.max(np.abs(g["grad"][k]))), k
+    q = g["q"][0].copy(); q[3] = -0.5                   # tau_2 < 0: outside T[0,], zero density
+    assert f(q)[0] == -np.inf
+
+
+LKJ3 = """let v_0_0 = [ 0.5 | i_1_1 <- 1...3 ] :: RVec
+    v_0_1 = quad_form_diag x_m_0_0 x_m_0_1 :: RMat
+ in do x_m_0_0 <- lkj_corr 1.5 :: P corr_matrix R
+       x_m_0_1 <- [ gamma 2.0 1.0 :: P R | i_1_1 <- 1...3 ] :: Array 1...3 R
+       x_m_0_2 <- multi_normal v_0_0 v_0_1 :: P RVec
+       return [x_m_0_0,x_m_0_1,x_m_0_2]
+"""
+
+
+def test_lkj_corr_of_dimension_three_against_a_numpy_restatement(tmp_path):
+    """K = 3 (option dim.<id>): Stan's corr_matrix transform with its two Jacobian parts, lkj_corr_lpdf with eta != 1, and a
+    3-variate normal through the unrolled Cholesky factor, against numpy / scipy; the gradient against central differences"""
+    import numpy as np
+    from scipy import stats
+    from scipy.special import gammaln
+    from stochaskell_b200.api import _corr_matrix_constrain
+    from tests.gen_host import host_eval
+    src = ir_to_cuda(LKJ3, [], name="lkj3", mode="density", given="x_m_0_2", **{"dim.x_m_0_0": 3})
+    assert "#define NP 6" in src and "qmap x_m_0_0 0 3 3 corr -" in src and "qmap x_m_0_1 3 3 0 - -" in src
+    yobs = np.array([0.3, -0.7, 1.1])
+    f = host_eval(src, dict(x_m_0_2=yobs), str(tmp_path))
+    eta, K = 1.5, 3
+
+    def want(q):
+        z = np.tanh(q[:3])
+        Om = _corr_matrix_constrain(q[:3].reshape(1, 3, 1), 3)[0, :, :, 0]
+        tau = q[3:6]
+        lp = np.log1p(-z ** 2).sum() + 0.5 * (np.log1p(-z[0] ** 2) + np.log1p(-z[1] ** 2))      # corr_constrain + read_corr_L
+        const = (K - 1) * gammaln(eta + 0.5 * (K - 1)) - sum(0.5 * k * np.log(np.pi) + gammaln(eta + 0.5 * (K - 1 - k)) for k in range(1, K))
+        lp += const + (eta - 1.0) * np.linalg.slogdet(Om)[1]
+        lp += stats.gamma.logpdf(tau, 2.0, scale=1.0).sum()
+        lp += stats.multivariate_normal.logpdf(yobs, 0.5 * np.ones(3), np.diag(tau) @ Om @ np.diag(tau))
+        return lp
+    rng = np.random.default_rng(5)
+    for _ in range(6):
+        q = np.r_[0.6 * rng.standard_normal(3), 0.5 + rng.random(3)]
+        lp, gr = f(q)
+        assert np.isclose(lp, want(q), rtol=1e-11, atol=1e-11)
+        Om = _corr_matrix_constrain(q[:3].reshape(1, 3, 1), 3)[0, :, :, 0]
+        assert np.allclose(np.diag(Om), 1.0) and np.all(np.linalg.eigvalsh(Om) > 0)
+        h = 1e-6
+        fd = np.array([(f(q + h * e, grad=False) - f(q - h * e, grad=False)) / (2 * h) for e in np.eye(6)])
+        assert np.allclose(gr, fd, rtol=1e-6, atol=1e-6)

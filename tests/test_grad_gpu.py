@@ -133,3 +133,51 @@ def test_hmcCUDA_takes_the_conditioned_model_itself(ctx, tmp_path):
     ridge = np.linalg.solve(A.T @ A + (0.49 / 100.0) * np.eye(11), A.T @ y)
     post = np.r_[cons["x_stan_0_1"].mean(), cons["x_stan_0_2"].mean(axis=(0, 2))]
     assert np.max(np.abs(post - ridge)) < 0.03, (post, ridge)
+
+
+def test_generated_birats_matches_stan_and_the_builtin(ctx, tmp_path):
+    """config C4 from IR (tests/golden/ir/birats_model.txt; app/benchmark/Main.hs:106-125): the generated module on B200
+    against (a) log_prob_grad of the vendored CmdStan on the notebook's Stan program (tests/golden/birats_stan.npz), 1e-10;
+    (b) the hand-tuned builtin:birats on the same points; then a short fused-HMC run from the notebook-like start, whose draws
+    come back on the model's scale through the qmap (corr_matrix rebuilt from its CPC, beta [30][2] from column-major q)."""
+    from stochaskell_b200 import Chains, Module, Sampler, constrain_draws, ir_to_cuda
+    g = np.load(os.path.join(HERE, "golden", "birats_stan.npz"))
+    ir = open(os.path.join(HERE, "golden", "ir", "birats_model.txt")).read()
+    m = Module(ctx, ir_to_cuda(ir, [], name="birats_ir", mode="density", given="x_stan_0_0,x_stan_0_6"), cache_dir=str(tmp_path))
+    K, C = len(g["q"]), 40
+    ch = Chains(m, C, seed=11)
+    ch.set_data("x_stan_0_0", g["x"]); ch.set_data("x_stan_0_6", np.ascontiguousarray(g["y"]))
+    q0 = np.ascontiguousarray(np.stack([g["q"][c % K] for c in range(C)], axis=1))
+    ch.set_state("q", q0)
+    lp, gr = ch.logp_grad()
+    lp_only = ch.logp()
+    b = Sampler("builtin:birats", C, dict(x=g["x"], y=g["y"]), seed=11, ctx=ctx)
+    b.chains.set_state("q", q0)
+    lpb, grb = b.chains.logp_grad()
+    for c in range(C):
+        k = c % K
+        assert abs(lp[c] - g["lp"][k]) <= 1e-10 * abs(g["lp"][k]), (c, lp[c], g["lp"][k])
+        assert abs(lp_only[c] - g["lp"][k]) <= 1e-10 * abs(g["lp"][k])
+        assert np.max(np.abs(gr[:, c] - g["grad"][k])) <= 1e-10 * max(1.0, np.max(np.abs(g["grad"][k]))), c
+        assert abs(lp[c] - lpb[c]) <= 1e-10 * abs(lpb[c])
+        assert np.max(np.abs(gr[:, c] - grb[:, c])) <= 1e-9 * max(1.0, np.max(np.abs(grb[:, c])))
+    # zero density outside T[0,] of the untransformed tau: -inf and a zero gradient, as the builtin reports it
+    q1 = q0.copy(); q1[2, 3] = -0.25
+    ch.set_state("q", q1)
+    lp1, gr1 = ch.logp_grad()
+    assert lp1[3] == -np.inf and np.all(gr1[:, 3] == 0.0) and np.isfinite(lp1[2])
+    # fused static HMC from a posterior-scale start (golden q[0]): a short stable trajectory
+    ch.set_state("q", np.ascontiguousarray(np.repeat(g["q"][0][:, None], C, axis=1)))
+    ch.set_param("eps", 0.02); ch.set_param("L", 10)
+    ch.record(20, 5)
+    ch.step("hmc", 100)
+    dr = ch.draws()
+    assert dr.shape == (20, 66, C) and np.all(np.isfinite(dr))
+    assert np.std(dr[-1, 0, :]) > 0                           # the chains moved and differ
+    moved = np.mean(np.any(dr[1:] != dr[:-1], axis=1))        # a recorded state differs from the previous one: some accept in between
+    assert moved > 0.5, moved
+    out = constrain_draws(m.descriptor, dr)
+    assert out["x_stan_0_1"].shape == (20, 2, C) and out["x_stan_0_4"].shape == (20, 30, 2, C) and out["x_stan_0_5"].shape == (20, C)
+    Om = out["x_stan_0_3"]
+    assert Om.shape == (20, 2, 2, C) and np.allclose(Om[:, 0, 0], 1.0) and np.allclose(Om[:, 0, 1], np.tanh(dr[:, 4, :]))
+    assert np.array_equal(out["x_stan_0_4"][:, :, 1, :], dr[:, 35:65, :]) and np.all(out["x_stan_0_5"] > 0)

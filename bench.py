@@ -639,8 +639,8 @@ class LinregHMCIR(LinregHMC):
 
 class BiratsHMCIR(BiratsHMC):
     """C4 through the CODE GENERATOR: the birats model's IR (tests/golden/ir/birats_model.txt: corr_matrix parameter, multivariate
-    normal rows of a joint, matrix algebra) lowered by the gradient lowering — one thread per chain, 66 parameters in registers /
-    local memory — against the hand-tuned builtin:birats (a warp per four chains) on the same data, start and Philox stream."""
+    normal rows of a joint, matrix algebra) lowered by the gradient lowering — the 150 observation terms and 30 multivariate-normal rows re-rolled into
+    two loops whose instances are split over 16 lanes per chain, state distributed over the lanes — against the hand-tuned builtin:birats (a warp per four chains) on the same data, start and Philox stream."""
     name = "birats_hmc_ir"
     symbol = "stk_ir_hmc"
     generated_from = "birats_hmc"
@@ -651,7 +651,7 @@ class BiratsHMCIR(BiratsHMC):
         super().__init__()
         from stochaskell_b200 import model_to_module
         ir = open(os.path.join(ROOT, "tests", "golden", "ir", "birats_model.txt")).read()
-        self.module = model_to_module(ir, ("x_stan_0_0", "x_stan_0_6"), name="birats_ir")
+        self.module = model_to_module(ir, ("x_stan_0_0", "x_stan_0_6"), name="birats_ir", lanes=int(os.environ.get("STK_IR_LANES", "16")), unroll=int(os.environ.get("STK_IR_UNROLL", "1")))
         self.describe = self.describe.replace("C4 birats", "C4 birats, module GENERATED from the model IR (stkc gradient lowering),")
 
     def data(self):

@@ -70,7 +70,8 @@ def test_gradient_lowering_refuses_what_it_cannot_differentiate():
     assert "no free parameter" in str(e.value)
 
 
-def test_birats_model_matches_the_reference_backend_on_the_host(tmp_path):
+@pytest.mark.parametrize("roll", ["4", "0"], ids=["rerolled", "unrolled"])
+def test_birats_model_matches_the_reference_backend_on_the_host(tmp_path, roll):
     """birats (app/benchmark/Main.hs:106-125, birats.ipynb cell 6) lowered from IR: corr_matrix parameter through Stan's CPC
     transform, multivariate-normal rows of a joint, matrix algebra (tr', asColumn, asRow, <>, broadcast +, quad_form_diag).
     The emitted stk_eval / stk_eval_grad, compiled as host code (tests/gen_host.py), against log_prob_grad of the vendored
@@ -79,8 +80,14 @@ def test_birats_model_matches_the_reference_backend_on_the_host(tmp_path):
     + Program.hs:709, so its truncation is only T[0,]), 1 CPC, beta column-major, log sigma."""
     import numpy as np
     from tests.gen_host import host_eval
-    src = ir_to_cuda(ir("birats_model"), [], name="birats_ir", mode="density", given="x_stan_0_0,x_stan_0_6")
+    src = ir_to_cuda(ir("birats_model"), [], name="birats_ir", mode="density", given="x_stan_0_0,x_stan_0_6", roll=roll, lanes=1)
     assert "#define NP 66" in src and "one thread per chain" in src
+    if roll == "0":
+        assert "re-rolled" not in src and len(src) > 150000
+    else:
+        # the 150 observation terms and the 30 multivariate-normal rows are each ONE loop over tables of leaf indices
+        assert "2 re-rolled term group(s)" in src and len(src) < 30000
+        assert "for (int i_ = slice; i_ < 150; i_ += NSLICE)" in src and "for (int i_ = slice; i_ < 30; i_ += NSLICE)" in src
     assert "qmap x_stan_0_2 2 2 0 - -" in src and "qmap x_stan_0_3 4 2 2 corr -" in src and "qmap x_stan_0_4 5 30 2 - -" in src
     assert "qmap x_stan_0_5 65 0 0 0.0 -" in src
     g = np.load(os.path.join(os.path.dirname(IR), "birats_stan.npz"))
@@ -111,7 +118,7 @@ def test_lkj_corr_of_dimension_three_against_a_numpy_restatement(tmp_path):
     from scipy.special import gammaln
     from stochaskell_b200.api import _corr_matrix_constrain
     from tests.gen_host import host_eval
-    src = ir_to_cuda(LKJ3, [], name="lkj3", mode="density", given="x_m_0_2", **{"dim.x_m_0_0": 3})
+    src = ir_to_cuda(LKJ3, [], name="lkj3", mode="density", given="x_m_0_2", lanes=1, **{"dim.x_m_0_0": 3})
     assert "#define NP 6" in src and "qmap x_m_0_0 0 3 3 corr -" in src and "qmap x_m_0_1 3 3 0 - -" in src
     yobs = np.array([0.3, -0.7, 1.1])
     f = host_eval(src, dict(x_m_0_2=yobs), str(tmp_path))

@@ -135,7 +135,8 @@ def test_hmcCUDA_takes_the_conditioned_model_itself(ctx, tmp_path):
     assert np.max(np.abs(post - ridge)) < 0.03, (post, ridge)
 
 
-def test_generated_birats_matches_stan_and_the_builtin(ctx, tmp_path):
+@pytest.mark.parametrize("opt", [dict(lanes=1), dict(), dict(lanes=32), dict(lanes=1, roll=0)], ids=["one_thread", "default_lanes8", "lanes32", "unrolled"])
+def test_generated_birats_matches_stan_and_the_builtin(ctx, tmp_path, opt):
     """config C4 from IR (tests/golden/ir/birats_model.txt; app/benchmark/Main.hs:106-125): the generated module on B200
     against (a) log_prob_grad of the vendored CmdStan on the notebook's Stan program (tests/golden/birats_stan.npz), 1e-10;
     (b) the hand-tuned builtin:birats on the same points; then a short fused-HMC run from the notebook-like start, whose draws
@@ -143,7 +144,7 @@ def test_generated_birats_matches_stan_and_the_builtin(ctx, tmp_path):
     from stochaskell_b200 import Chains, Module, Sampler, constrain_draws, ir_to_cuda
     g = np.load(os.path.join(HERE, "golden", "birats_stan.npz"))
     ir = open(os.path.join(HERE, "golden", "ir", "birats_model.txt")).read()
-    m = Module(ctx, ir_to_cuda(ir, [], name="birats_ir", mode="density", given="x_stan_0_0,x_stan_0_6"), cache_dir=str(tmp_path))
+    m = Module(ctx, ir_to_cuda(ir, [], name="birats_ir", mode="density", given="x_stan_0_0,x_stan_0_6", **opt), cache_dir=str(tmp_path))
     K, C = len(g["q"]), 40
     ch = Chains(m, C, seed=11)
     ch.set_data("x_stan_0_0", g["x"]); ch.set_data("x_stan_0_6", np.ascontiguousarray(g["y"]))
@@ -181,3 +182,28 @@ def test_generated_birats_matches_stan_and_the_builtin(ctx, tmp_path):
     Om = out["x_stan_0_3"]
     assert Om.shape == (20, 2, 2, C) and np.allclose(Om[:, 0, 0], 1.0) and np.allclose(Om[:, 0, 1], np.tanh(dr[:, 4, :]))
     assert np.array_equal(out["x_stan_0_4"][:, :, 1, :], dr[:, 35:65, :]) and np.all(out["x_stan_0_5"] > 0)
+
+
+def test_generated_birats_lanes_take_the_same_trajectories(ctx, tmp_path):
+    """the instances of a re-rolled term group split over the lanes of a chain (lanes = 2, 8, 32; chain counts that leave idle lanes
+    and a ragged last warp): same Philox stream, so the same accept decisions as the one-thread-per-chain module and states equal up
+    to the order of the lane sums (1e-8 after 30 transitions of 10 leapfrogs, the tolerance of the other trajectory tests)"""
+    from stochaskell_b200 import Chains, Module, ir_to_cuda
+    g = np.load(os.path.join(HERE, "golden", "birats_stan.npz"))
+    ir = open(os.path.join(HERE, "golden", "ir", "birats_model.txt")).read()
+    C, T = 37, 30
+    rng = np.random.default_rng(4)
+    q0 = np.ascontiguousarray(g["q"][0][:, None] * (1 + 0.01 * rng.standard_normal((66, C))))
+    res = {}
+    for lanes in (1, 2, 8, 32):
+        m = Module(ctx, ir_to_cuda(ir, [], name=f"birats_l{lanes}", mode="density", given="x_stan_0_0,x_stan_0_6", lanes=lanes), cache_dir=str(tmp_path))
+        ch = Chains(m, C, seed=19)
+        ch.set_data("x_stan_0_0", g["x"]); ch.set_data("x_stan_0_6", np.ascontiguousarray(g["y"]))
+        ch.set_state("q", q0)
+        ch.set_param("eps", 0.02); ch.set_param("L", 10)
+        ch.step("hmc", T)
+        res[lanes] = (ch.get_state("q"), ch.get_state("lp"))
+    assert np.any(res[1][0] != q0)
+    for lanes in (2, 8, 32):
+        assert np.allclose(res[lanes][0], res[1][0], rtol=1e-8, atol=1e-8), lanes
+        assert np.allclose(res[lanes][1], res[1][1], rtol=1e-9), lanes

@@ -442,6 +442,34 @@ def is_ir_text(spec: str) -> bool:
     return t.startswith(("let", "do ", "\\", "[runStep]", "/*")) and ("<-" in spec or " in " in spec)
 
 
+def simulateCUDA(program_ir: str, n_draws: int = 1, seed: int = 1, device: int = 0, ctx: Optional[Context] = None,
+                 input_types: Sequence[str] = (), **options) -> list:
+    """`simulate :: P t -> IO t` (Program.hs:1038) for a program given as IR text, `n_draws` independent draws at once (one chain
+    each; chain c draws from the Philox streams of global chain c).  Returns the program's returned values in order: a scalar as
+    an array [n_draws], a vector as a list of n_draws 1-D arrays, a matrix as a list of n_draws 2-D arrays.  The same model text
+    lowers to the HMC module through `model_to_module` / `hmcCUDA`: data and initial values of the reference's benchmarks
+    (`simulate (birats n t)`, app/benchmark/Main.hs:220-226) come from the model itself."""
+    c = ctx or Context(device)
+    m = Module(c, ir_to_cuda(program_ir, input_types, **options))
+    ch = Chains(m, n_draws, seed)
+    ch.simulate(); ch.sync()
+    out = []
+    k = 0
+    while f"out{k}" in m.fields:
+        a = ch.get_state(f"out{k}")
+        if f"out{k}_rows" in m.fields:
+            r, cc = ch.get_state(f"out{k}_rows")[0], ch.get_state(f"out{k}_cols")[0]
+            out.append([a[:r[i] * cc[i], i].reshape(r[i], cc[i]) for i in range(n_draws)])
+        elif f"out{k}_len" in m.fields:
+            ln = ch.get_state(f"out{k}_len")[0]
+            out.append([a[:ln[i], i].copy() for i in range(n_draws)])
+        else:
+            out.append(a[0].copy())
+        k += 1
+    ch.close()
+    return out
+
+
 def model_to_module(model_ir: str, given: Sequence[str], name: str = "ir_model", **options) -> str:
     """`stanProgram` analogue (Stan.hs:325-344): a conditioned model `P t` -> CUDA source of a module with logp / logp_grad
     entries and a static-HMC kernel (csrc/stkc_grad.inc); `given` = the ids of the PNodes that are conditioned on"""
@@ -473,6 +501,45 @@ def constrain_draws(descriptor: str, draws: np.ndarray) -> Dict[str, np.ndarray]
         else:
             out[ident] = x.reshape((draws.shape[0],) + ((rows,) if rows else ()) + (draws.shape[2],))
     return out
+
+
+def unconstrain_values(descriptor: str, values: Dict[str, np.ndarray]) -> np.ndarray:
+    """the inverse of `constrain_draws` for ONE point: {PNode id: value on the model's scale} -> q[P] (what CmdStan does with the
+    `init=` file of hmcStanInit, Stan.hs:498-500: lb / ub / lub free transforms, matrices column-major, a corr_matrix through
+    corr_matrix_free: Cholesky factor -> canonical partial correlations -> atanh)"""
+    out = []
+    for line in descriptor.splitlines():
+        t = line.split()
+        if not t or t[0] != "qmap":
+            continue
+        ident, off, rows, cols, lo, hi = t[1], int(t[2]), int(t[3]), int(t[4]), t[5], t[6]
+        if ident not in values:
+            raise StkError(-1, f"initial value of {ident} missing")
+        x = np.asarray(values[ident], dtype=np.float64)
+        if lo == "corr":
+            if x.shape != (rows, rows):
+                raise StkError(-1, f"initial value of {ident} must be a {rows} x {rows} correlation matrix")
+            L = np.linalg.cholesky(x)
+            z = []
+            for j in range(rows - 1):
+                for i in range(j + 1, rows):
+                    z.append(L[i, j] / np.sqrt(1.0 - np.sum(L[i, :j] ** 2)))
+            q = np.arctanh(np.array(z))
+        else:
+            want = (rows, cols) if cols else (rows,) if rows else ()
+            if x.shape != want:
+                raise StkError(-1, f"initial value of {ident} has shape {x.shape}, the model says {want}")
+            q = (x.T if cols else x).reshape(-1)
+            if lo != "-" and hi == "-":
+                q = np.log(q - float(lo))
+            elif lo == "-" and hi != "-":
+                q = np.log(float(hi) - q)
+            elif lo != "-" and hi != "-":
+                u = (q - float(lo)) / (float(hi) - float(lo))
+                q = np.log(u / (1.0 - u))
+        assert off == sum(len(o) for o in out)
+        out.append(np.atleast_1d(q))
+    return np.concatenate(out)
 
 
 def _corr_matrix_constrain(y: np.ndarray, K: int) -> np.ndarray:
@@ -531,6 +598,8 @@ def hmcCUDA(method: CudaMethod, module_spec: str, data: dict, init: Optional[Seq
         # exp(x_bar) = 1 like the reference's `adapt engaged=0 ... engine=nuts` does NOT; keep the caller's step size
         raise StkError(-1, "engine='nuts' needs adapt=True (the reference's default); fixed-step NUTS is not exposed")
     method = dataclasses.replace(method, kernel=kernel)
+    if isinstance(init, dict):                     # hmcStanInit's shape: values of the unobserved PNodes on the model's scale
+        init = unconstrain_values(s.module.descriptor, init)
     if init is not None:
         ch.set_state("q", np.asarray(init, dtype=np.float64), broadcast=True)
     if method.num_warmup:

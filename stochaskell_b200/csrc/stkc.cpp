@@ -752,6 +752,58 @@ struct Gen {
     }
   }
 
+  // a 2-D comprehension `[ body | i <- a...b, j <- c...d ] :: matrix` (CC.hs:231-235 with two loops): a matrix expression whose
+  // element is the body with the indices substituted when the body needs no statement, else filled into per-thread storage
+  bool try_inline_array2_at(const Node& a, const std::string& i, const std::string& j, std::string* out_e) {
+    const bool saved = inline_mode; const size_t depth = scopes.size();
+    inline_mode = true;
+    try {
+      push();
+      Val vi; vi.type = scalarT(Type::Z); vi.expr = "(" + i + ")"; bind(a.params[0], vi);
+      Val vj; vj.type = scalarT(Type::Z); vj.expr = "(" + j + ")"; bind(a.params[1], vj);
+      for (const Def& ad : a.lam->defs) def(ad);
+      *out_e = rv(a.lam->rets.at(0), true);
+      pop(); inline_mode = saved;
+      return true;
+    } catch (const NotInlinable&) {
+      while (scopes.size() > depth) pop();
+      inline_mode = saved;
+      return false;
+    }
+  }
+  void array2_def(const Def& d) {
+    const Node& n = d.node;
+    const Node* np = &n;
+    if (!inline_mode) { for (auto& sh : n.shape) { need(sh.first); need(sh.second); } need_body(*n.lam); }
+    std::string lo0 = rv(n.shape[0].first), hi0 = rv(n.shape[0].second), lo1 = rv(n.shape[1].first), hi1 = rv(n.shape[1].second);
+    auto m = std::make_shared<Mat>();
+    m->rows = "(" + hi0 + " - " + lo0 + " + 1)"; m->cols = "(" + hi1 + " - " + lo1 + " + 1)"; m->prepare = [] {};
+    std::string probe;
+    if (try_inline_array2_at(n, "1", "1", &probe)) {
+      m->at = [this, np, lo0, lo1](const std::string& i, const std::string& j) {
+        std::string e;
+        if (!try_inline_array2_at(*np, lo0 == "1" ? i : "(" + i + ") + " + lo0 + " - 1", lo1 == "1" ? j : "(" + j + ") + " + lo1 + " - 1", &e)) die("internal: 2-D array stopped being inlinable");
+        return e;
+      };
+    } else {
+      if (inline_mode) throw NotInlinable();
+      std::string buf = fresh(d.id + "_mat"), R = fresh("R"), C = fresh("C");
+      decls << "  double " << buf << "[STK_MATCAP * STK_MATCAP];\n";
+      line("const int " + R + " = stk::cap_len(" + m->rows + ", STK_MATCAP, err_, 3), " + C + " = stk::cap_len(" + m->cols + ", STK_MATCAP, err_, 3);");
+      const std::string &iv = n.params[0], &jv = n.params[1];
+      line("for (int " + iv + " = " + lo0 + "; " + iv + " < " + lo0 + " + " + R + "; ++" + iv + ") for (int " + jv + " = " + lo1 + "; " + jv + " < " + lo1 + " + " + C + "; ++" + jv + ") {");
+      ind += 2; push();
+      Val vi; vi.type = scalarT(Type::Z); vi.expr = iv; bind(iv, vi);
+      Val vj; vj.type = scalarT(Type::Z); vj.expr = jv; bind(jv, vj);
+      for (const Def& ad : n.lam->defs) def(ad);
+      line(buf + "[(" + iv + " - " + lo0 + ") * " + C + " + " + jv + " - " + lo1 + "] = " + rv(n.lam->rets.at(0), true) + ";");
+      pop(); ind -= 2; line("}");
+      m = stored_mat(buf, R, C);
+    }
+    Val v; v.type = n.type; if (v.type.k != Type::Mat) { v.type = Type(); v.type.k = Type::Mat; v.type.sub.push_back(scalarT(Type::R)); }
+    v.mat = m; bind(d.id, v);
+  }
+
   // vector-like access to a reference: a state / buffer view, a comprehension (inlined or materialised), a row of a
   // matrix, a literal list
   VA va(const RefP& r) {
@@ -1041,6 +1093,7 @@ struct Gen {
   void def_impl(const Def& d) {
     const Node& n = d.node;
     Val v; v.type = n.type;
+    if (n.k == Node::Array && n.params.size() == 2) { array2_def(d); return; }
     if (n.k == Node::Array) {                      // kept symbolic; consumers inline it (CC.hs:231-235 materialises)
       if (v.type.k == Type::Unknown) v.type = vecT(scalarT(Type::R));
       v.array = &n; bind(d.id, v); return;
@@ -1065,6 +1118,24 @@ struct Gen {
       } else if (f == "id") assign_union(d.id, n.type, n.args[0]);
       else die("node `" + f + "` producing a union is not supported");
       v.expr = d.id; bind(d.id, v); return;
+    }
+    if (n.type.k == Type::Vec && n.type.sub[0].k == Type::R && (f == "+" || f == "-" || f == "*" || f == "/" || f == "*>" || f == "+s" || f == "negate") && !n.args.empty()) {
+      // element-wise vector arithmetic (scalars broadcast; CC.hs:92-107 on Eigen vectors): kept as an accessor, evaluated by its consumer
+      std::vector<VA> vs; std::vector<std::string> sc; std::string len;
+      for (auto& a : n.args) {
+        if (type_of(a).k == Type::Vec) { vs.push_back(va(a)); sc.push_back(""); if (len.empty()) len = vs.back().len; }
+        else { vs.push_back(VA()); sc.push_back("(" + rv(a, true) + ")"); }
+      }
+      if (len.empty()) die("vector node `" + f + "` without a vector operand");
+      const std::string op = f == "-" ? " - " : f == "/" ? " / " : (f == "*" || f == "*>") ? " * " : " + ";
+      auto lz = std::make_shared<VA>(); lz->len = len;
+      const bool neg = f == "negate";
+      lz->at = [vs, sc, op, neg](const std::string& i) {
+        std::string e;
+        for (size_t k = 0; k < vs.size(); ++k) { std::string t = sc[k].empty() ? vs[k].at(i) : sc[k]; e = e.empty() ? t : "(" + e + op + t + ")"; }
+        return neg ? "(-" + e + ")" : e;
+      };
+      v.lazy = lz; bind(d.id, v); return;
     }
     if (n.type.k == Type::Vec) { vector_node(d); return; }
     if (!n.type.scalar()) die("definition " + d.id + " has unsupported type " + n.type.str());
@@ -1509,6 +1580,12 @@ struct Gen {
       m->at = [dv](const std::string& i, const std::string& j) { return "((" + i + ") == (" + j + ") ? " + dv.at(i) + " : 0.0)"; };
       Val v; v.type = n.type; v.mat = m; bind(d.id, v); return;
     }
+    if (f == "quad_form_diag" || f == "qfDiag") {          // diag(v) M diag(v)  (covPrior, app/benchmark/Main.hs:112)
+      auto a = mat_of(n.args.at(0)); VA dv = va(n.args.at(1));
+      auto m = std::make_shared<Mat>(); m->rows = a->rows; m->cols = a->cols; m->prepare = [a] { a->prepare(); };
+      m->at = [a, dv](const std::string& i, const std::string& j) { return "(" + dv.at(i) + " * " + a->at(i, j) + " * " + dv.at(j) + ")"; };
+      Val v; v.type = n.type; v.mat = m; bind(d.id, v); return;
+    }
     if (f == "outer") {
       VA a = va(n.args.at(0)), b = va(n.args.at(1));
       auto m = std::make_shared<Mat>(); m->rows = a.len; m->cols = b.len; m->prepare = [] {};
@@ -1542,7 +1619,19 @@ struct Gen {
     else if (f == "+" || f == "-" || f == "+s" || f == "*") {                                 // element-wise
       std::vector<std::shared_ptr<Mat>> ms;
       for (auto& a : n.args) ms.push_back(mat_of(a));
+      // a column (cols == 1) or a row against a full matrix is replicated (rep_matrix in the reference's Stan output)
       m->rows = ms[0]->rows; m->cols = ms[0]->cols;
+      for (auto& a : ms) { if (m->rows == "1" && a->rows != "1") m->rows = a->rows; if (m->cols == "1" && a->cols != "1") m->cols = a->cols; }
+      {
+        const std::string RR = m->rows, CC = m->cols;
+        for (auto& a : ms) {
+          const bool br = a->rows == "1" && RR != "1", bc = a->cols == "1" && CC != "1";
+          if (!br && !bc) continue;
+          auto src = a; auto b = std::make_shared<Mat>(); *b = *src; b->rows = RR; b->cols = CC; b->eye = false;
+          b->at = [src, br, bc](const std::string& i, const std::string& j) { return src->at(br ? "1" : i, bc ? "1" : j); };
+          a = b;
+        }
+      }
       const std::string op = f == "-" ? " - " : f == "*" ? " * " : " + ";
       if (f != "*") {                                  // a + 0 = a: static zeros drop out of sums (not out of a - b's first operand)
         bool all_zero = true; for (auto& a : ms) all_zero = all_zero && a->zeros;
@@ -1747,10 +1836,30 @@ struct Gen {
     *ptr = atoi(id.c_str() + b + 1); *level = atoi(id.c_str() + a + 1);
   }
 
+  // definitions of the body being lowered that have not been reached yet: a PNode may read a definition that is printed after the
+  // one that needs the PNode (the interpreter evaluates by need, Program.hs:1046-1091), so such a definition is lowered on demand —
+  // only while no inner scope is open, where its statements would land inside a loop
+  struct PendingDefs { std::map<std::string, const Def*> defs; size_t depth; };
+  std::vector<PendingDefs> pending_defs;
+  void run_def(const Def& d) {
+    for (auto& a : d.node.args) need(a);
+    for (auto& sh : d.node.shape) { need(sh.first); need(sh.second); }
+    if (d.node.k != Node::Array && d.node.lam) need_body(*d.node.lam);
+    for (auto& al : d.node.alts) need_body(al.body);
+    if (d.node.k == Node::Fold && d.node.args[1]->k == Ref::Var) {
+      const Val& lv = lookup(d.node.args[1]->name);
+      if (lv.array) { need_body(*lv.array->lam); for (auto& sh : lv.array->shape) { need(sh.first); need(sh.second); } }
+    }
+    def(d);
+  }
   void ensure_drawn(const std::string& id) {
     for (size_t i = pending_stack.size(); i-- > 0;) {
       auto it = pending_stack[i].find(id);
       if (it != pending_stack[i].end()) { const PNode* q = it->second; pending_stack[i].erase(it); pnode(*q); return; }
+    }
+    if (!pending_defs.empty() && pending_defs.back().depth == scopes.size() && !inline_mode) {
+      auto it = pending_defs.back().defs.find(id);
+      if (it != pending_defs.back().defs.end()) { const Def* d = it->second; pending_defs.back().defs.erase(it); run_def(*d); }
     }
   }
   void need(const RefP& r) {       // draw any PNode the reference depends on before it is used
@@ -1807,10 +1916,14 @@ struct Gen {
   // Program.hs:1171-1181): the elements are drawn in index order into per-thread storage; element k (0-based) of the
   // PNode with slot s uses Philox slot s + (k + 1) * 2^16, so every element has its own counter range and the stream
   // does not depend on the order of evaluation.
+  // A 2-D joint over a scalar distribution fills a per-thread matrix, element (i, j) from the element index (i - 1) cols + j of the
+  // PNode's counter range; a 1-D joint over a vector-valued multivariate normal (`joint (designMatrix k) [ normal m S | i <- 1...n ]`,
+  // app/benchmark/Main.hs:119) fills row i with m + chol(S) #> w, w_k from element index (i - 1) k + k'.
   void loop_node(const PNode& q, const std::string& slot) {
-    if (q.params.size() != 1) die("multi-dimensional joint (Loop) PNodes are not supported by the CUDA lowering");
+    if (q.params.size() > 2) die("joint (Loop) PNodes of more than two dimensions are not supported by the CUDA lowering");
     const PNode& in = *q.inner;
-    if (in.k != PNode::Dist || !in.type.scalar()) die("joint (Loop) over a non-scalar distribution is not supported");
+    if (in.k != PNode::Dist) die("joint (Loop) over a non-primitive distribution is not supported");
+    if (q.params.size() == 2 || !in.type.scalar()) { loop_node_matrix(q, slot); return; }
     need(q.shape[0].first); need(q.shape[0].second);
     need_body(*q.lam);
     for (auto& a : in.args) need(a);
@@ -1826,11 +1939,70 @@ struct Gen {
     for (const Def& d : q.lam->defs) def(d);
     std::string g = fresh("g");
     line(gen_decl(g, slot, "(" + iv + " - " + lo + " + 1)"));
-    line(buf + "[" + iv + " - " + lo + "] = " + draw_expr(in, g) + ";");
+    elem_draw(in, buf + "[" + iv + " - " + lo + "]", g);
     pop(); ind -= 2; line("}");
     Type vt = vecT(in.type);
     line("const " + ctype(vt) + " " + q.id + "(" + buf + ", 1, " + hi + " < " + lo + " ? 0 : " + hi + " - " + lo + " + 1);");
     Val r; r.type = vt; r.expr = q.id; bind(q.id, r);
+  }
+
+  // `dst = draw` of one element of a joint; an element distribution on a SubrangeT is redrawn until it is in range
+  // (samplePNode on a SubrangeT, Program.hs:1081-1090, reached through the Loop's element), at most 2^16 times
+  void elem_draw(const PNode& in, const std::string& dst, const std::string& g) {
+    std::string e = draw_expr(in, g);
+    if (!in.sub_lo && !in.sub_hi) { line(dst + " = " + e + ";"); return; }
+    need(in.sub_lo); need(in.sub_hi);
+    const bool real = in.type.k == Type::R;
+    std::string cond, tries = fresh("tries");
+    if (in.sub_lo) cond = dst + " < " + rv(in.sub_lo, real);
+    if (in.sub_hi) cond += (cond.empty() ? "" : " || ") + dst + " > " + rv(in.sub_hi, real);
+    line("{ int " + tries + " = 0; do { " + dst + " = " + e + "; } while ((" + cond + ") && ++" + tries + " < 65536); }");
+  }
+  void loop_node_matrix(const PNode& q, const std::string& slot) {
+    const PNode& in = *q.inner;
+    const bool two = q.params.size() == 2;
+    for (auto& sh : q.shape) { need(sh.first); need(sh.second); }
+    need_body(*q.lam);
+    for (auto& a : in.args) need(a);
+    std::string buf = fresh(q.id + "_mat"), R = fresh("R"), C = fresh("C"), lo0 = fresh("lo"), lo1 = fresh("lo");
+    decls << "  double " << buf << "[STK_MATCAP * STK_MATCAP];\n";
+    line("const int " + lo0 + " = " + rv(q.shape[0].first) + ", " + R + " = stk::cap_len(" + rv(q.shape[0].second) + " - " + lo0 + " + 1, STK_MATCAP, err_, 3);");
+    const std::string& iv = q.params[0];
+    if (two) {
+      if (!in.type.scalar()) die("2-D joint over a non-scalar distribution is not supported");
+      const std::string& jv = q.params[1];
+      line("const int " + lo1 + " = " + rv(q.shape[1].first) + ", " + C + " = stk::cap_len(" + rv(q.shape[1].second) + " - " + lo1 + " + 1, STK_MATCAP, err_, 3);");
+      line("if ((long long)" + R + " * " + C + " > 65535) *err_ = 3;");        // the element index has 16 bits of the block counter
+      line("for (int " + iv + " = " + lo0 + "; " + iv + " < " + lo0 + " + " + R + "; ++" + iv + ") for (int " + jv + " = " + lo1 + "; " + jv + " < " + lo1 + " + " + C + "; ++" + jv + ") {");
+      ind += 2; push();
+      Val vi; vi.type = scalarT(Type::Z); vi.expr = iv; bind(iv, vi);
+      Val vj; vj.type = scalarT(Type::Z); vj.expr = jv; bind(jv, vj);
+      for (const Def& d : q.lam->defs) def(d);
+      std::string g = fresh("g");
+      line(gen_decl(g, slot, "((" + iv + " - " + lo0 + ") * " + C + " + " + jv + " - " + lo1 + " + 1)"));
+      elem_draw(in, buf + "[(" + iv + " - " + lo0 + ") * " + C + " + " + jv + " - " + lo1 + "]", g);
+      pop(); ind -= 2; line("}");
+    } else {
+      const bool mvn = (in.dist == "multi_normal" || in.dist == "normal" || in.dist == "normals") && in.args.size() == 2 && type_of(in.args[1]).k == Type::Mat;
+      if (!mvn || in.type.k != Type::Vec) die("joint (Loop) over the vector-valued distribution `" + in.dist + "` is not supported");
+      // the covariance and mean must not depend on the row index: factorised once
+      for (const Def& d : q.lam->defs) def(d);
+      VA mean = va(in.args.at(0));
+      std::string RS, CS, L = mat_store(mat_of(in.args.at(1)), q.id + "_S", &RS, &CS);
+      std::string wb = fresh(q.id + "_w"), k = fresh("k"), t = fresh("t"), g = fresh("g"), acc = fresh("acc");
+      decls << "  double " << wb << "[STK_MATCAP];\n";
+      line("stk::chol_lower(" + L + ", " + RS + ");");
+      line("const int " + C + " = " + RS + ";");
+      line("if ((long long)" + R + " * " + C + " > 65535) *err_ = 3;");
+      line("for (int " + iv + " = " + lo0 + "; " + iv + " < " + lo0 + " + " + R + "; ++" + iv + ") {");
+      ind += 2;
+      line("for (int " + k + " = 1; " + k + " <= " + C + "; ++" + k + ") { " + gen_decl(g, slot, "((" + iv + " - " + lo0 + ") * " + C + " + " + k + ")") + " " + wb + "[" + k + " - 1] = stk::draw_normal(" + g + ", 0.0, 1.0); }");
+      line("for (int " + k + " = 1; " + k + " <= " + C + "; ++" + k + ") { double " + acc + " = " + mean.at(k) + "; for (int " + t + " = 1; " + t + " <= " + k + "; ++" + t + ") " +
+           acc + " += " + L + "[(" + k + " - 1) * " + C + " + " + t + " - 1] * " + wb + "[" + t + " - 1]; " + buf + "[(" + iv + " - " + lo0 + ") * " + C + " + " + k + " - 1] = " + acc + "; }");
+      ind -= 2; line("}");
+    }
+    Type mt; mt.k = Type::Mat; mt.sub.push_back(scalarT(Type::R));
+    Val r; r.type = mt; r.mat = stored_mat(buf, R, C); bind(q.id, r);
   }
 
   // Chain PNode (ccPNode (Chain ..), CC.hs:314-320: `name = x; for i in lo..hi { j = name; <body>; name = ret; }`;
@@ -1903,6 +2075,29 @@ struct Gen {
       {"bernoulliLogits", "bernoulliLogit"}, {"bernoullis", "bernoulli"}, {"poissons", "poisson"}};
     auto it = scalar_of.find(q.dist);
     if (it == scalar_of.end()) return false;
+    if (q.type.k == Type::Mat && q.type.sub[0].k == Type::R) {       // `normals M S :: P RMat`: element (i, j) at the (i, j) elements of the argument matrices
+      for (auto& a : q.args) need(a);
+      std::vector<std::shared_ptr<Mat>> ms;
+      for (auto& a : q.args) { ms.push_back(mat_of(a)); ms.back()->prepare(); }
+      std::string buf = fresh(q.id + "_mat"), R = fresh("R"), C = fresh("C"), i = fresh("i"), j = fresh("j"), g = fresh("g");
+      decls << "  double " << buf << "[STK_MATCAP * STK_MATCAP];\n";
+      line("const int " + R + " = stk::cap_len(" + ms[0]->rows + ", STK_MATCAP, err_, 3), " + C + " = stk::cap_len(" + ms[0]->cols + ", STK_MATCAP, err_, 3);");
+      line("if ((long long)" + R + " * " + C + " > 65535) *err_ = 3;");
+      line("for (int " + i + " = 1; " + i + " <= " + R + "; ++" + i + ") for (int " + j + " = 1; " + j + " <= " + C + "; ++" + j + ") {");
+      ind += 2; push();
+      PNode el; el.k = PNode::Dist; el.dist = it->second; el.type = scalarT(Type::R); el.id = q.id;
+      for (size_t a = 0; a < ms.size(); ++a) {                     // the element's arguments as fresh scalar bindings
+        std::string an = fresh("arg");
+        line("const double " + an + " = " + ms[a]->at(i, j) + ";");
+        Val av; av.type = scalarT(Type::R); av.expr = an; bind(an, av);
+        auto ar = std::make_shared<Ref>(); ar->k = Ref::Var; ar->name = an; el.args.push_back(ar);
+      }
+      line(gen_decl(g, slot, "((" + i + " - 1) * " + C + " + " + j + ")"));
+      line(buf + "[(" + i + " - 1) * " + C + " + " + j + " - 1] = " + draw_expr(el, g) + ";");
+      pop(); ind -= 2; line("}");
+      Val r; r.type = q.type; r.mat = stored_mat(buf, R, C); bind(q.id, r);
+      return true;
+    }
     if (q.type.k != Type::Vec || !q.type.sub[0].scalar()) die("`" + q.dist + "` of type " + q.type.str() + " is not supported by the CUDA lowering (vectors only)");
     for (auto& a : q.args) need(a);
     bool real = q.type.sub[0].k == Type::R;
@@ -1910,7 +2105,7 @@ struct Gen {
     decls << "  " << (real ? "double" : "int") << " " << buf << "[STK_VECCAP];\n";
     auto length = [&](const RefP& a) -> std::string {
       if (a->k == Ref::Var && lookup(a->name).array) { const Node& an = *lookup(a->name).array; return "(" + rv(an.shape[0].second) + " - " + rv(an.shape[0].first) + " + 1)"; }
-      return rv(a) + ".len";
+      return "(" + va(a).len + ")";
     };
     line("const int " + n + " = stk::cap_len(" + length(q.args.at(0)) + ", STK_VECCAP, err_);");
     line("for (int " + k + " = 1; " + k + " <= " + n + "; ++" + k + ") {");
@@ -2072,18 +2267,15 @@ struct Gen {
   void body(const Body& b) {
     pending_stack.emplace_back();
     for (const PNode& q : b.pnodes) pending_stack.back()[q.id] = &q;
+    pending_defs.push_back({{}, scopes.size()});
+    if (rename_depth == 0) for (const Def& d : b.defs) pending_defs.back().defs[d.id] = &d;
     for (const Def& d : b.defs) {
-      for (auto& a : d.node.args) need(a);
-      if (d.node.k != Node::Array && d.node.lam) need_body(*d.node.lam);
-      for (auto& al : d.node.alts) need_body(al.body);
-      if (d.node.k == Node::Fold && d.node.args[1]->k == Ref::Var) {
-        const Val& lv = lookup(d.node.args[1]->name);
-        if (lv.array) { need_body(*lv.array->lam); for (auto& sh : lv.array->shape) { need(sh.first); need(sh.second); } }
-      }
-      def(d);
+      if (rename_depth == 0) { auto it = pending_defs.back().defs.find(d.id); if (it == pending_defs.back().defs.end()) continue; pending_defs.back().defs.erase(it); }
+      run_def(d);
     }
     for (const PNode& q : b.pnodes) ensure_drawn(q.id);
     for (auto& r : b.rets) need(r);
+    pending_defs.pop_back();
     pending_stack.pop_back();
   }
 };

@@ -144,3 +144,20 @@ def test_lkj_corr_of_dimension_three_against_a_numpy_restatement(tmp_path):
         h = 1e-6
         fd = np.array([(f(q + h * e, grad=False) - f(q - h * e, grad=False)) / (2 * h) for e in np.eye(6)])
         assert np.allclose(gr, fd, rtol=1e-6, atol=1e-6)
+
+
+def test_initial_values_on_the_model_scale_round_trip():
+    """hmcStanInit's `init` (Stan.hs:498-500) is given on the model's scale; `unconstrain_values` is the free transform per qmap line
+    (lb / lub, column-major matrices, corr_matrix_free for K = 3) and inverts `constrain_draws` exactly"""
+    import numpy as np
+    from stochaskell_b200 import constrain_draws, unconstrain_values
+    desc = ("qmap a 0 2 0 - -\nqmap t 2 2 0 - -\nqmap om 4 3 3 corr -\nqmap b 7 4 2 - -\nqmap s 15 0 0 0.0 -\nqmap u 16 0 0 1.0 3.0\n"
+            "qmap w 17 0 0 - 2.0\n")
+    q = np.random.default_rng(1).standard_normal(18)
+    vals = {k: v[0, ..., 0] for k, v in constrain_draws(desc, q.reshape(1, 18, 1)).items()}
+    assert vals["om"].shape == (3, 3) and np.allclose(np.diag(vals["om"]), 1.0) and vals["b"].shape == (4, 2)
+    assert vals["s"] > 0 and 1.0 < vals["u"] < 3.0 and vals["w"] < 2.0
+    assert np.array_equal(vals["b"][:, 1], q[11:15])                 # column-major
+    assert np.allclose(unconstrain_values(desc, vals), q, rtol=0, atol=1e-13)
+    with pytest.raises(StkError):
+        unconstrain_values(desc, {k: v for k, v in vals.items() if k != "om"})

@@ -207,3 +207,25 @@ def test_generated_birats_lanes_take_the_same_trajectories(ctx, tmp_path):
     for lanes in (2, 8, 32):
         assert np.allclose(res[lanes][0], res[1][0], rtol=1e-8, atol=1e-8), lanes
         assert np.allclose(res[lanes][1], res[1][1], rtol=1e-9), lanes
+
+
+def test_birats_benchmark_flow_from_one_ir_text(ctx, tmp_path):
+    """the flow of `birats'` (app/benchmark/Main.hs:217-233) from ONE model text: `simulate` for the data and for the initial
+    values (simulateCUDA: the program lowered as a simulate kernel), then the conditioned model through hmcCUDA in hmcStanInit's
+    shape — data by PNode id, init on the model's scale — and the draws back on the model's scale"""
+    from stochaskell_b200 import CudaMethod, constrain_draws, hmcCUDA, simulateCUDA, unconstrain_values
+    ir = open(os.path.join(HERE, "golden", "ir", "birats_model.txt")).read()
+    sim = simulateCUDA(ir, 2, seed=3, ctx=ctx, matcap=30, veccap=32)
+    x, bm, tau, om, beta, ys, y = (v[0] for v in sim)             # draw 0: the data
+    _, bm1, tau1, om1, beta1, ys1, _ = (v[1] for v in sim)        # draw 1: the initial values (initF, Main.hs:224-226)
+    assert x.shape == (5,) and y.shape == (30, 5) and om1.shape == (2, 2) and beta1.shape == (30, 2) and ys1 > 0 and (tau1 > 0).all()
+    init = dict(x_stan_0_1=bm1, x_stan_0_2=tau1, x_stan_0_3=om1, x_stan_0_4=beta1, x_stan_0_5=ys1)
+    method = CudaMethod(num_chains=64, num_samples=20, num_warmup=0, step_size=1e-4, num_leapfrog=5, seed=8)
+    dr = hmcCUDA(method, ir, dict(x_stan_0_0=x, x_stan_0_6=y), init)
+    s = hmcCUDA.last_sampler
+    assert dr.shape == (20, 66, 64) and np.all(np.isfinite(dr))
+    q0 = unconstrain_values(s.module.descriptor, init)
+    assert np.allclose(q0[:2], bm1) and q0[65] == pytest.approx(np.log(ys1)) and np.allclose(q0[35:65], beta1[:, 1])
+    out = constrain_draws(s.module.descriptor, dr)
+    assert out["x_stan_0_4"].shape == (20, 30, 2, 64) and np.all(out["x_stan_0_5"] > 0)
+    assert np.any(dr[-1] != q0[:, None])                          # the chains left the start

@@ -233,3 +233,17 @@ def test_guard_conditions_become_a_rejection_loop(tmp_path):
     compile_source(src, str(tmp_path))
     with pytest.raises(StkError):
         ir_to_cuda(ir("mh_sym"), ["R"], guard="v_0_1")      # kernels have no guard
+
+
+def test_model_irs_lower_as_simulate_programs(tmp_path):
+    """the SAME model IRs that the gradient lowering turns into HMC modules (linreg_model, birats_model) lower as `simulate`
+    programs (what the reference benchmark calls for data and initial values, app/benchmark/Main.hs:196, 220): 2-D joints, a joint
+    over a vector-valued multivariate normal, `normals` over matrices, 2-D comprehensions, broadcast +, quad_form_diag, vector
+    arithmetic; definitions a PNode needs are lowered on demand"""
+    lin = ir_to_cuda(ir("linreg_model").replace("1...1000", "1...20"), [], name="linreg_sim", matcap=20, veccap=32)
+    assert "entry simulate stk_ir_simulate" in lin and "field out0_rows" in lin and "draw_normal" in lin
+    bi = ir_to_cuda(ir("birats_model"), [], name="birats_sim", matcap=30, veccap=32)
+    assert "draw_lkj_corr2" in bi and "chol_lower" in bi and bi.count("draw_cauchy") == 2
+    assert bi.count("do {") == 2                       # both truncated cauchys are rejection loops: the scalar and the joint's elements
+    for src in (lin, bi):
+        assert os.path.getsize(compile_source(src, str(tmp_path))) > 5000

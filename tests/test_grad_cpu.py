@@ -87,7 +87,7 @@ def test_birats_model_matches_the_reference_backend_on_the_host(tmp_path, roll):
     else:
         # the 150 observation terms and the 30 multivariate-normal rows are each ONE loop over tables of leaf indices
         assert "2 re-rolled term group(s)" in src and len(src) < 30000
-        assert "for (int i_ = slice; i_ < 150; i_ += NSLICE)" in src and "for (int i_ = slice; i_ < 30; i_ += NSLICE)" in src
+        assert "for (int i_ = slice; i_ < 150; i_ += 1)" in src and "for (int i_ = slice; i_ < 30; i_ += 1)" in src
     assert "qmap x_stan_0_2 2 2 0 - -" in src and "qmap x_stan_0_3 4 2 2 corr -" in src and "qmap x_stan_0_4 5 30 2 - -" in src
     assert "qmap x_stan_0_5 65 0 0 0.0 -" in src
     g = np.load(os.path.join(os.path.dirname(IR), "birats_stan.npz"))

@@ -658,6 +658,44 @@ class BiratsHMCIR(BiratsHMC):
         return dict(x_stan_0_0=self.x, x_stan_0_6=self.y)
 
 
+class LinregNUTSIR(LinregNUTS):
+    """C1 under hmcStan's DEFAULT sampler through the CODE GENERATOR: the module lowered from the model IR, its `nuts` kernel =
+    the generic adapt_diag_e_nuts of csrc/stk_hmc_generic.cuh over the generated evaluation (K slice threads per chain as replicas)."""
+    name = "linreg_nuts_ir"
+    symbol = "stk_ir_nuts"
+    generated_from = "linreg_nuts"
+    data_keys = ("x_stan_0_0", "x_stan_0_4")
+
+    def __init__(self):
+        super().__init__()
+        from stochaskell_b200 import model_to_module
+        ir = open(os.path.join(ROOT, "tests", "golden", "ir", "linreg_model.txt")).read()
+        self.module = model_to_module(ir, self.data_keys, name="linreg_ir", slices=int(os.environ.get("STK_IR_SLICES", "8")))
+        self.describe = self.describe.replace("C1 linreg", "C1 linreg, module GENERATED from the model IR (stkc gradient lowering + generic NUTS),")
+
+    def data(self):
+        return dict(x_stan_0_0=self.X, x_stan_0_4=self.y)
+
+
+class BiratsNUTSIR(BiratsNUTS):
+    """C4 under hmcStan's DEFAULT sampler (birats.ipynb cell 8) through the CODE GENERATOR: generic NUTS over the re-rolled
+    evaluation of the module lowered from tests/golden/ir/birats_model.txt, one thread per chain."""
+    name = "birats_nuts_ir"
+    symbol = "stk_ir_nuts"
+    generated_from = "birats_nuts"
+    ncu_traffic_bytes = None
+
+    def __init__(self):
+        super().__init__()
+        from stochaskell_b200 import model_to_module
+        ir = open(os.path.join(ROOT, "tests", "golden", "ir", "birats_model.txt")).read()
+        self.module = model_to_module(ir, ("x_stan_0_0", "x_stan_0_6"), name="birats_ir")
+        self.describe = self.describe.replace("C4 birats", "C4 birats, module GENERATED from the model IR (stkc gradient lowering + generic NUTS),")
+
+    def data(self):
+        return dict(x_stan_0_0=self.x, x_stan_0_6=self.y)
+
+
 class CoalRJIR(CoalRJ):
     """C2 through the CODE GENERATOR: the kernel IR that `runStep` printed for `coal t 'rjmc' coalMove' t` (rj-coal.ipynb
     cell 8, tests/golden/ir/coal_rj.txt) lowered by stkc — one thread per chain, the reference's own node-by-node evaluation
@@ -804,7 +842,7 @@ class SoccerRJSeq(SoccerRJ):
     stan_exe = None
 
 
-WORKLOADS = {"linreg_hmc_ir": LinregHMCIR, "birats_hmc_ir": BiratsHMCIR, "coal_rj_ir": CoalRJIR, "soccer_rj": SoccerRJ, "soccer_rj_seq": SoccerRJSeq, "gp_hmc_tc": GPHMCTC, "linreg_hmc": LinregHMC, "linreg_nuts": LinregNUTS, "coal_rj": CoalRJ, "birats_hmc": BiratsHMC, "birats_nuts": BiratsNUTS, "dp_gibbs": DPGibbs, "gp_hmc": GPHMC, "gpr_mh": GPRMH}
+WORKLOADS = {"linreg_hmc_ir": LinregHMCIR, "birats_hmc_ir": BiratsHMCIR, "linreg_nuts_ir": LinregNUTSIR, "birats_nuts_ir": BiratsNUTSIR, "coal_rj_ir": CoalRJIR, "soccer_rj": SoccerRJ, "soccer_rj_seq": SoccerRJSeq, "gp_hmc_tc": GPHMCTC, "linreg_hmc": LinregHMC, "linreg_nuts": LinregNUTS, "coal_rj": CoalRJ, "birats_hmc": BiratsHMC, "birats_nuts": BiratsNUTS, "dp_gibbs": DPGibbs, "gp_hmc": GPHMC, "gpr_mh": GPRMH}
 DEFAULT_WORKLOAD = "coal_rj"
 
 

@@ -718,7 +718,8 @@ class CoalRJIR(CoalRJ):
         super().__init__()
         from stochaskell_b200 import ir_to_cuda
         ir = open(os.path.join(ROOT, "tests", "golden", "ir", "coal_rj.txt")).read()
-        self.module = ir_to_cuda(ir, ["Z", "RVec", "RVec", "RVec"], name="coal_rj_ir")
+        lanes = int(os.environ.get("STK_COAL_IR_LANES", "4"))
+        self.module = ir_to_cuda(ir, ["Z", "RVec", "RVec", "RVec"], name="coal_rj_ir", **(dict(lanes=lanes) if lanes > 1 else {}))
         self.describe = self.describe.replace("C2 coal-mining RJMCMC (rj-coal)", "C2 coal-mining RJMCMC, kernel GENERATED from the printed IR of rj-coal.ipynb cell 8 (stkc)")
 
     def data(self):

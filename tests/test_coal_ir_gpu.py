@@ -157,3 +157,29 @@ def test_generated_kernel_long_run_all_chains(ctx, orc, tmp_path):
         assert n1[c] == nn, (c, n1[c], nn)
         np.testing.assert_allclose(s1[:nn, c], sc[:nn], rtol=1e-8)
     assert 2.0 < n1.mean() < 6.0
+
+
+@pytest.mark.parametrize("lanes", [4, 8])
+def test_generated_kernel_with_lanes_per_chain(ctx, orc, tmp_path, lanes):
+    """the coal kernel IR with several lanes per chain (stkc `lanes`: the additive folds over the state's segments and the event sum
+    of poissonProcess_lpdf split over the lanes, xor-butterfly combine): dimension trajectory bit-exact against the oracle over 200
+    fused transitions, s / g at 1e-8 (the lane sums reorder the log-density's additions)"""
+    from stochaskell_b200 import Chains, Module, ir_to_cuda
+    from stochaskell_b200.fixtures import coal_days
+    y = coal_days()
+    C, T, seed = 70, 200, 7                                # 70 chains: a ragged last warp
+    m = Module(ctx, ir_to_cuda(open(os.path.join(IR, "coal_rj.txt")).read(), TYPES, name=f"coal_rj_ir_l{lanes}", lanes=lanes), cache_dir=str(tmp_path))
+    n0, s0, g0 = prior_states(C, 11)
+    ch = Chains(m, C, seed=seed)
+    upload(ch, n0, s0, g0, y)
+    ch.step("step", T)
+    n1 = ch.get_state("in0")[0]; s1 = ch.get_state("in1"); g1 = ch.get_state("in2")
+    agree = 0
+    for c in range(0, C, 3):
+        nn = int(n0[c]); sc = np.ascontiguousarray(s0[:, c]); gc = np.ascontiguousarray(g0[:, c])
+        for t in range(T):
+            nn, _ = orc.coal_rj_step_ir(nn, sc, gc, y, seed, c, t)
+        if n1[c] == nn and np.allclose(s1[:nn, c], sc[:nn], rtol=1e-8) and np.allclose(g1[:nn + 1, c], gc[:nn + 1], rtol=1e-8):
+            agree += 1
+    # a reordered sum can flip an accept decision that sits within 1e-13 of its uniform: allow one chain in 24
+    assert agree >= 23, agree

@@ -470,6 +470,27 @@ def simulateCUDA(program_ir: str, n_draws: int = 1, seed: int = 1, device: int =
     return out
 
 
+def densityCUDA(program_ir: str, points: Dict[str, np.ndarray], device: int = 0, ctx: Optional[Context] = None, **options) -> np.ndarray:
+    """`density'` (Program.hs:940-944) of a program at MANY points at once: `points` maps every PNode id to an array whose first
+    axis indexes the points (scalar PNode: [n]; vector: [n][len]; matrix: [n][rows][cols]); returns the joint log-density of each
+    point [n].  The program is lowered with every PNode given per chain (`joint=1`, csrc/stkc_grad.inc): one chain = one point,
+    long vectors are summed by the sliced sum loops of the gradient lowering, the values are read from HBM coalesced over points."""
+    ids = list(points.keys())
+    n = len(np.asarray(points[ids[0]]))
+    src = ir_to_cuda(program_ir, [], mode="density", given=",".join(ids), perchain=",".join(ids), joint=1, **options)
+    c = ctx or Context(device)
+    m = Module(c, src)
+    ch = Chains(m, n, 1)
+    for k in ids:
+        v = np.asarray(points[k])
+        if v.shape[0] != n:
+            raise StkError(-1, f"{k}: {v.shape[0]} points, expected {n}")
+        ch.set_state(k, np.ascontiguousarray(v.reshape(n, -1).T, dtype=m.fields[k]["dtype"]))      # [len][n]: element-major, point-minor
+    lp = ch.logp()
+    ch.close()
+    return lp
+
+
 def model_to_module(model_ir: str, given: Sequence[str], name: str = "ir_model", **options) -> str:
     """`stanProgram` analogue (Stan.hs:325-344): a conditioned model `P t` -> CUDA source of a module with logp / logp_grad
     entries and a static-HMC kernel (csrc/stkc_grad.inc); `given` = the ids of the PNodes that are conditioned on"""

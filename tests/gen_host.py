@@ -35,6 +35,8 @@ def host_eval(src: str, data: dict, workdir: str):
     P = int(re.search(r"#define NP (\d+)", body).group(1))
     args = ", ".join(f"const {t}* d{i}" for i, (t, _) in enumerate(names))
     fill = " ".join(f"D.{n} = d{i};" for i, (_, n) in enumerate(names))
+    if "long long nch;" in body:
+        fill += " D.nch = 1;"                  # one point: per-chain values are read with stride 1
     harness = (f'extern "C" double host_lp_grad(const double* q_, double* g_{", " if names else ""}{args}) {{\n'
                f"  Data D; {fill}\n  double q[NP], g[NP]; for (int j = 0; j < NP; ++j) q[j] = q_[j];\n"
                "  int flip = 0; double lp = stk_eval_grad(D, q, g, nullptr, flip, 0, 0);\n"

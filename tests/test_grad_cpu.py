@@ -161,3 +161,28 @@ def test_initial_values_on_the_model_scale_round_trip():
     assert np.allclose(unconstrain_values(desc, vals), q, rtol=0, atol=1e-13)
     with pytest.raises(StkError):
         unconstrain_values(desc, {k: v for k, v in vals.items() if k != "om"})
+
+
+def test_joint_density_of_a_fully_observed_program(tmp_path):
+    """`density'` (Program.hs:940-944: the product of every PNode's density at given values) as a device module: `joint=1` with all
+    PNodes given and `perchain` (one point per chain, state fields) gives a module whose only entry is `logp`.  The emitted
+    evaluation, compiled as host code, against scipy on the linreg program (n = 20): X, b, w, the truncated sigma and y all count."""
+    import numpy as np
+    from scipy import stats
+    from tests.gen_host import host_eval
+    allp = "x_stan_0_0,x_stan_0_1,x_stan_0_2,x_stan_0_3,x_stan_0_4"
+    text = ir("linreg_model").replace("1...1000", "1...20")
+    src = ir_to_cuda(text, [], name="linreg_joint", mode="density", given=allp, perchain=allp, joint=1)
+    assert "nparam 0" in src and "entry logp stk_ir_logp" in src and "kernel hmc" not in src and "field q " not in src
+    assert "field x_stan_0_0 state f64 200" in src and "field x_stan_0_3 state f64 1" in src
+    rng = np.random.default_rng(2)
+    X = rng.standard_normal((20, 10)); b = 3.0; w = 2.0 * rng.standard_normal(10); sig = 1.7
+    y = b + X @ w + sig * rng.standard_normal(20)
+    f = host_eval(src, dict(x_stan_0_0=X, x_stan_0_1=[b], x_stan_0_2=w, x_stan_0_3=[sig], x_stan_0_4=y), str(tmp_path))
+    want = (stats.norm.logpdf(X).sum() + stats.norm.logpdf(b, 0, 10) + stats.norm.logpdf(w, 0, 10).sum()
+            + stats.cauchy.logpdf(sig, 0, 5) + np.log(2.0) + stats.norm.logpdf(y, b + X @ w, sig).sum())
+    assert f(np.zeros(1), grad=False) == pytest.approx(want, rel=1e-12)
+    with pytest.raises(StkError, match="no free parameter"):
+        ir_to_cuda(text, [], name="x", mode="density", given=allp)
+    with pytest.raises(StkError, match="perchain"):
+        ir_to_cuda(text, [], name="x", mode="density", given="x_stan_0_0", perchain="x_stan_0_4")

@@ -229,3 +229,22 @@ def test_birats_benchmark_flow_from_one_ir_text(ctx, tmp_path):
     out = constrain_draws(s.module.descriptor, dr)
     assert out["x_stan_0_4"].shape == (20, 30, 2, 64) and np.all(out["x_stan_0_5"] > 0)
     assert np.any(dr[-1] != q0[:, None])                          # the chains left the start
+
+
+@pytest.mark.parametrize("n,C", [(20, 70), (1000, 300)])
+def test_joint_density_over_a_population_of_points(ctx, n, C):
+    """`density'` (Program.hs:940-944) evaluated on the device for many points at once (`densityCUDA`: every PNode given per chain):
+    the linreg program at n = 20 (unrolled and re-rolled terms) and n = 1000 (sum loops over per-chain long data, 8 observation
+    slices per point), against scipy"""
+    from scipy import stats
+    from stochaskell_b200 import densityCUDA
+    text = open(os.path.join(HERE, "golden", "ir", "linreg_model.txt")).read().replace("1...1000", f"1...{n}")
+    rng = np.random.default_rng(n)
+    X = rng.standard_normal((C, n, 10)); b = 3.0 * rng.standard_normal(C); w = 2.0 * rng.standard_normal((C, 10))
+    sig = 0.5 + rng.random(C); y = b[:, None] + np.einsum("cnd,cd->cn", X, w) + sig[:, None] * rng.standard_normal((C, n))
+    lp = densityCUDA(text, dict(x_stan_0_0=X, x_stan_0_1=b, x_stan_0_2=w, x_stan_0_3=sig, x_stan_0_4=y), ctx=ctx)
+    assert lp.shape == (C,)
+    for c in range(0, C, 7):
+        want = (stats.norm.logpdf(X[c]).sum() + stats.norm.logpdf(b[c], 0, 10) + stats.norm.logpdf(w[c], 0, 10).sum()
+                + stats.cauchy.logpdf(sig[c], 0, 5) + np.log(2.0) + stats.norm.logpdf(y[c], b[c] + X[c] @ w[c], sig[c]).sum())
+        assert lp[c] == pytest.approx(want, rel=1e-11), c

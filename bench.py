@@ -995,10 +995,68 @@ def logpdf_arm(args, wl, rank, world, local, torch, dist):
         del s, ch
     peaks = measured_peaks()
     best = max(v["logpdf_gbs"] for v in out.values()) / world
-    return dict(unit="GB/s", kernel=wl.module[8:] + "_logp_grad", algorithmic_bytes_per_eval=wl.bytes_per_eval, steps=K, warmup=W,
+    per_point = None
+    if wl.name == "linreg_hmc":
+        try:
+            per_point = per_point_density_leg(args, wl, rank, world, local, torch, dist, flush, peaks)
+        except Exception as e:                      # noqa: BLE001 — an extra leg must not lose the line
+            per_point = dict(error=str(e)[:200])
+    return dict(unit="GB/s", **(dict(per_point_data=per_point) if per_point else {}), kernel=wl.module[8:] + "_logp_grad", algorithmic_bytes_per_eval=wl.bytes_per_eval, steps=K, warmup=W,
                 populations=out, frac_of_hbm_peak_best=best / peaks["hbm_gbs"], peak=peaks["hbm_gbs"],
                 note="algorithmic bytes (SURVEY 8d: the data a one-chain evaluation streams + its state); the observed data is "
                      "shared by the chains of a CTA and staged in shared memory, so the figure exceeds physical DRAM traffic")
+
+
+def per_point_density_leg(args, wl, rank, world, local, torch, dist, flush, peaks):
+    """logpdf GB/s where the bytes are PHYSICAL: the joint density of the linreg program (`density'`, Program.hs:940-944) over a
+    population of points that each carry their own data — the module generated with joint=1 / perchain (csrc/stkc_grad.inc); one
+    launch streams n*d + n + d + 2 doubles per point from HBM exactly once, so algorithmic bytes = DRAM bytes and the fraction of
+    the HBM peak is the kernel's real roofline figure."""
+    from stochaskell_b200 import Chains, Context, Module, ir_to_cuda
+    dev = torch.device("cuda", local)
+    ids = ["x_stan_0_0", "x_stan_0_1", "x_stan_0_2", "x_stan_0_3", "x_stan_0_4"]
+    ir = open(os.path.join(ROOT, "tests", "golden", "ir", "linreg_model.txt")).read()
+    src = ir_to_cuda(ir, [], name="linreg_joint", mode="density", given=",".join(ids), perchain=",".join(ids), joint=1,
+                     slices=int(os.environ.get("STK_JOINT_SLICES", "4")), unroll=int(os.environ.get("STK_JOINT_UNROLL", "4")))
+    C = int(os.environ.get("STK_JOINT_POINTS", "131072"))
+    n, d = wl.n, wl.d
+    ctx = Context(local)
+    m = Module(ctx, src)
+    ch = Chains(m, C, 1, rank * C)
+    rng = np.random.default_rng(7 + rank)
+    ch.set_state("x_stan_0_0", rng.standard_normal((n * d, C)))
+    ch.set_state("x_stan_0_1", rng.standard_normal((1, C)))
+    ch.set_state("x_stan_0_2", rng.standard_normal((d, C)))
+    ch.set_state("x_stan_0_3", 0.5 + rng.random((1, C)))
+    ch.set_state("x_stan_0_4", rng.standard_normal((n, C)))
+    K, W = max(args.steps, 10), max(args.warmup, 3)
+    stream = torch.cuda.ExternalStream(ctx.stream, device=dev)
+    with torch.cuda.stream(stream):
+        for _ in range(W):
+            flush.zero_(); ch.logp(host=False)
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+        for k in range(K):
+            flush.zero_()
+            ev[k][0].record(stream); ch.logp(host=False); ev[k][1].record(stream)
+        torch.cuda.synchronize(dev)
+        ms = sum(a.elapsed_time(b) for a, b in ev)
+    lp = ch.logp()
+    tm = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+    bytes_per_point = 8 * (n * d + n + d + 2)
+    evals = world * C * K / (float(tm[0]) * 1e-3)
+    gbs = evals * bytes_per_point / 1e9
+    ch.close()
+    return dict(kernel="stk_ir_logp (generated: joint density, per-point data)", points_per_gpu=C, bytes_per_point=bytes_per_point,
+                evals_per_sec=evals, logpdf_gbs=gbs, us_per_launch=float(tm[0]) * 1e3 / K, frac_of_hbm_peak=gbs / world / peaks["hbm_gbs"],
+                finite=bool(np.isfinite(lp).all()), state_bytes_per_gpu=int(C) * bytes_per_point,
+                roofline=dict(bound="hbm", achieved=gbs / world, peak=peaks["hbm_gbs"], unit="GB/s", frac=gbs / world / peaks["hbm_gbs"],
+                              traffic=(lambda f: (f["dram_bytes_read"] + f["dram_bytes_write"]) if f and f.get("chains") == C else None)(ncu_facts("linreg_joint_density")),
+                              algorithmic_bytes_per_launch=int(C) * bytes_per_point, ncu=ncu_facts("linreg_joint_density")))
 
 
 _T0 = time.perf_counter()

@@ -168,7 +168,10 @@ class Chains:
         check(lib().stk_set_param(self._h, name.encode(), float(value)))
 
     # -- compute --------------------------------------------------------------
-    def logp(self) -> np.ndarray:
+    def logp(self, host: bool = True) -> Optional[np.ndarray]:
+        if not host:                                 # evaluate on the device only (the result stays in the `lp` field / out_lp)
+            check(lib().stk_logp(self._h, None))
+            return None
         out = np.empty(self.n)
         check(lib().stk_logp(self._h, _ptr(out)))
         return out

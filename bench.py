@@ -1023,12 +1023,22 @@ def per_point_density_leg(args, wl, rank, world, local, torch, dist, flush, peak
     ctx = Context(local)
     m = Module(ctx, src)
     ch = Chains(m, C, 1, rank * C)
-    rng = np.random.default_rng(7 + rank)
-    ch.set_state("x_stan_0_0", rng.standard_normal((n * d, C)))
-    ch.set_state("x_stan_0_1", rng.standard_normal((1, C)))
-    ch.set_state("x_stan_0_2", rng.standard_normal((d, C)))
-    ch.set_state("x_stan_0_3", 0.5 + rng.random((1, C)))
-    ch.set_state("x_stan_0_4", rng.standard_normal((n, C)))
+    # the 11.5 GB of points are drawn ON the device and copied into the library's state fields device-to-device (the pointers come
+    # from stk_device_ptr): a host copy of the population would cost 10 GB of host memory per rank
+    import ctypes
+    rt = ctypes.CDLL("libcudart.so.12")
+    gen = torch.Generator(device=dev); gen.manual_seed(7 + rank)
+    for name, rows, shift in (("x_stan_0_0", n * d, 0.0), ("x_stan_0_1", 1, 0.0), ("x_stan_0_2", d, 0.0), ("x_stan_0_3", 1, None), ("x_stan_0_4", n, 0.0)):
+        t = (torch.randn((rows, C), dtype=torch.float64, device=dev, generator=gen) if shift is not None
+             else 0.5 + torch.rand((rows, C), dtype=torch.float64, device=dev, generator=gen))
+        ptr, nb = ch.device_ptr(name)
+        assert nb == t.numel() * 8, (name, nb, t.numel())
+        torch.cuda.synchronize(dev)
+        rc = rt.cudaMemcpy(ctypes.c_void_p(ptr), ctypes.c_void_p(t.data_ptr()), ctypes.c_size_t(nb), ctypes.c_int(3))      # cudaMemcpyDeviceToDevice
+        if rc != 0:
+            raise RuntimeError(f"cudaMemcpy D2D rc={rc}")
+        del t
+    torch.cuda.empty_cache()
     K, W = max(args.steps, 10), max(args.warmup, 3)
     stream = torch.cuda.ExternalStream(ctx.stream, device=dev)
     with torch.cuda.stream(stream):

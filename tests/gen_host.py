@@ -37,10 +37,11 @@ def host_eval(src: str, data: dict, workdir: str):
     fill = " ".join(f"D.{n} = d{i};" for i, (_, n) in enumerate(names))
     if "long long nch;" in body:
         fill += " D.nch = 1;"                  # one point: per-chain values are read with stride 1
-    harness = (f'extern "C" double host_lp_grad(const double* q_, double* g_{", " if names else ""}{args}) {{\n'
-               f"  Data D; {fill}\n  double q[NP], g[NP]; for (int j = 0; j < NP; ++j) q[j] = q_[j];\n"
-               "  int flip = 0; double lp = stk_eval_grad(D, q, g, nullptr, flip, 0, 0);\n"
-               "  for (int j = 0; j < NP; ++j) g_[j] = g[j];\n  return lp;\n}\n"
+    has_grad = "stk_eval_grad(" in body                  # a density-only module (joint=1, everything given) has no gradient form
+    harness = ((f'extern "C" double host_lp_grad(const double* q_, double* g_{", " if names else ""}{args}) {{\n'
+                f"  Data D; {fill}\n  double q[NP], g[NP]; for (int j = 0; j < NP; ++j) q[j] = q_[j];\n"
+                "  int flip = 0; double lp = stk_eval_grad(D, q, g, nullptr, flip, 0, 0);\n"
+                "  for (int j = 0; j < NP; ++j) g_[j] = g[j];\n  return lp;\n}\n") if has_grad else "") + (
                f'extern "C" double host_lp(const double* q_{", " if names else ""}{args}) {{\n'
                f"  Data D; {fill}\n  double q[NP]; for (int j = 0; j < NP; ++j) q[j] = q_[j];\n"
                "  int flip = 0; return stk_eval(D, q, nullptr, flip, 0, 0);\n}\n")
@@ -52,7 +53,8 @@ def host_eval(src: str, data: dict, workdir: str):
         cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
         subprocess.run([cxx, "-O1", "-ffp-contract=off", "-shared", "-fPIC", "-o", so, cpp], check=True)
     lib = C.CDLL(so)
-    lib.host_lp_grad.restype = C.c_double
+    if has_grad:
+        lib.host_lp_grad.restype = C.c_double
     lib.host_lp.restype = C.c_double
     arrs = [np.ascontiguousarray(data[n], dtype=np.int32 if t == "int" else np.float64) for t, n in names]
     ptrs = [x.ctypes.data_as(C.c_void_p) for x in arrs]

@@ -2308,6 +2308,7 @@ static std::string generate(const std::string& ir, const std::string& input_type
   Body prog = P.program();
   if (opt.count("mode") && opt["mode"] == "density") {     // log-density + gradient + HMC module of a model `P t`
     GradGen gg;
+    if (opt.count("exact_div") && opt["exact_div"] != "0") gg.G.recip_div = false;      // keep every quotient a correctly rounded division
     return gg.generate(prog, opt);
   }
   std::vector<Type> its = parse_types(input_types);

@@ -630,7 +630,7 @@ class LinregHMCIR(LinregHMC):
         from stochaskell_b200 import model_to_module
         ir = open(os.path.join(ROOT, "tests", "golden", "ir", "linreg_model.txt")).read()
         assert self.n == 1000 and self.d == 10
-        self.module = model_to_module(ir, self.data_keys, name="linreg_ir", slices=int(os.environ.get("STK_IR_SLICES", "12")))
+        self.module = model_to_module(ir, self.data_keys, name="linreg_ir", slices=int(os.environ.get("STK_IR_SLICES", "16")))
         self.describe = self.describe.replace("C1 linreg", "C1 linreg, module GENERATED from the model IR (stkc gradient lowering),")
 
     def data(self):

@@ -630,7 +630,7 @@ class LinregHMCIR(LinregHMC):
         from stochaskell_b200 import model_to_module
         ir = open(os.path.join(ROOT, "tests", "golden", "ir", "linreg_model.txt")).read()
         assert self.n == 1000 and self.d == 10
-        self.module = model_to_module(ir, self.data_keys, name="linreg_ir", slices=int(os.environ.get("STK_IR_SLICES", "16")))
+        self.module = model_to_module(ir, self.data_keys, name="linreg_ir", slices=int(os.environ.get("STK_IR_SLICES", "12")))
         self.describe = self.describe.replace("C1 linreg", "C1 linreg, module GENERATED from the model IR (stkc gradient lowering),")
 
     def data(self):
@@ -689,7 +689,7 @@ class BiratsNUTSIR(BiratsNUTS):
         super().__init__()
         from stochaskell_b200 import model_to_module
         ir = open(os.path.join(ROOT, "tests", "golden", "ir", "birats_model.txt")).read()
-        self.module = model_to_module(ir, ("x_stan_0_0", "x_stan_0_6"), name="birats_ir")
+        self.module = model_to_module(ir, ("x_stan_0_0", "x_stan_0_6"), name="birats_ir", **(dict(ablock=int(os.environ["STK_IR_ABLOCK"])) if "STK_IR_ABLOCK" in os.environ else {}))
         self.describe = self.describe.replace("C4 birats", "C4 birats, module GENERATED from the model IR (stkc gradient lowering + generic NUTS),")
 
     def data(self):

@@ -689,7 +689,8 @@ class BiratsNUTSIR(BiratsNUTS):
         super().__init__()
         from stochaskell_b200 import model_to_module
         ir = open(os.path.join(ROOT, "tests", "golden", "ir", "birats_model.txt")).read()
-        self.module = model_to_module(ir, ("x_stan_0_0", "x_stan_0_6"), name="birats_ir", **(dict(ablock=int(os.environ["STK_IR_ABLOCK"])) if "STK_IR_ABLOCK" in os.environ else {}))
+        self.module = model_to_module(ir, ("x_stan_0_0", "x_stan_0_6"), name="birats_ir", **(dict(ablock=int(os.environ["STK_IR_ABLOCK"])) if "STK_IR_ABLOCK" in os.environ else {}),
+                                      **(dict(lanes=int(os.environ["STK_IR_LANES_NUTS"])) if "STK_IR_LANES_NUTS" in os.environ else {}))
         self.describe = self.describe.replace("C4 birats", "C4 birats, module GENERATED from the model IR (stkc gradient lowering + generic NUTS),")
 
     def data(self):

@@ -353,5 +353,227 @@ STK_DEV void gen_nuts(const StkArgs& a, const GenFields& f, const double* par_ad
   }
 }
 
+// ---- adapt_diag_e_nuts with the chain's state DISTRIBUTED over the G lanes of a chain (lanes modules of the gradient lowering) --------
+// The same sampler as gen_nuts — same phases, same Philox blocks, same uniforms in the same order — for a CTA of one warp = CPB chains
+// x G lanes.  The 21 P-vectors of a chain (position, metric, Welford estimator, evaluation point and gradient, trajectory ends, sample,
+// rho and the candidate of the subtree being built) live in SHARED memory [array][j][chain in CTA]; coordinate pair (2b, 2b + 1)
+// belongs to lane b mod G (the ownership of the lane-parallel evaluation), which does all element-wise work on it; dot products are
+// partial sums combined by an xor butterfly over the chain's lanes (bitwise identical on them, so every lane takes the same
+// decision); scalars and the adaptation state are replicated in registers; the stack of pending left siblings is distributed too
+// (each lane keeps its own coordinates, in local memory: it is touched once or twice per leapfrog).  Chains of one warp sit in different
+// phases, so everything inside a phase uses the chain's own lane mask; the evaluation is the one warp-wide step of a tick.
+//   ev() -> lp   evaluates at the array QE (the evaluation reads it through its position mirror) and leaves each lane's gradient
+//                entries in GE; called by all 32 lanes together.
+enum { GA_Q = 0, GA_MINV, GA_WM, GA_WM2, GA_QE, GA_GE, GA_G0, GA_ZQ, GA_ZP, GA_ZG, GA_EQ0, GA_EQ1, GA_EP0, GA_EP1, GA_EG0, GA_EG1, GA_QS, GA_RHO,
+       GA_CRHO, GA_CPSL, GA_CQ, GA_COUNT };
+
+template <int P, int G, int CPB, class Eval>
+STK_DEV void gen_nuts_lanes(const StkArgs& a, const GenFields& f, const double* par_adapt, double max_depth_par, long long chain, long long cidx,
+                            bool active, int slice, int c, double* sm, Eval&& ev) {
+  constexpr int NPAIR = (P + 1) / 2, NO = 2 * ((NPAIR + G - 1) / G);
+  const long long nc = a.n_chains;
+  const unsigned gmask = (G == 32 ? 0xffffffffu : ((1u << G) - 1u)) << ((threadIdx.x / G) * G);
+  const bool writer = slice == 0 && active;
+  AdaptCfg cfg; cfg.init(par_adapt);
+  int max_depth = (int)max_depth_par;
+  max_depth = max_depth < 1 ? 1 : (max_depth > GEN_NUTS_MAXD ? GEN_NUTS_MAXD : max_depth);
+#define GAT(arr, j) sm[((arr) * P + (j)) * CPB + c]
+#define GOWN(k) (2 * (slice + ((k) >> 1) * G) + ((k) & 1))
+#define GEACH(k, j) for (int k = 0; k < NO; ++k) if (const int j = GOWN(k); j < P)
+  auto gsum = [&](double v) { return group_sum_masked<G>(v, gmask); };
+  double ad[STK_AD_LEN];
+  double st_rho[GEN_NUTS_MAXD][NO], st_psl[GEN_NUTS_MAXD][NO], st_q[GEN_NUTS_MAXD][NO], st_lsw[GEN_NUTS_MAXD], st_lp[GEN_NUTS_MAXD];
+  double lp0 = 0.0, lps = 0.0, lp = 0.0, lsw = 0.0, H0 = 0.0, sum_metro = 0.0, eps = 0.0, H0t = 0.0, teps = 0.0;
+  double stat_depth = 0.0, stat_leaps = 0.0, stat_div = 0.0, stat_acc = 0.0;
+  int phase = a.n_steps > 0 ? GPH_START : GPH_DONE, depth = 0, leaf = 0, sgn = 1, n_leap = 0, tdir = 0;
+  bool divergent = false, from_update = false;
+  long long t = 0;
+  unsigned long long n_acc = 0;
+  Rng rng; rng.init(a.seed, (u64)(a.chain0 + cidx), a.step0);
+  GEACH(k, j) {
+    GAT(GA_Q, j) = f.Q[j * nc + cidx]; GAT(GA_MINV, j) = f.MINV[j * nc + cidx]; GAT(GA_WM, j) = f.WM[j * nc + cidx]; GAT(GA_WM2, j) = f.WM2[j * nc + cidx];
+    GAT(GA_QE, j) = GAT(GA_Q, j);
+  }
+  for (int j = 0; j < STK_AD_LEN; ++j) ad[j] = f.AD[j * nc + cidx];
+
+  auto kinetic = [&](int parr) { double ke = 0.0; GEACH(k, j) ke = fma(GAT(GA_MINV, j) * GAT(parr, j), GAT(parr, j), ke); return 0.5 * gsum(ke); };
+  auto sample_p = [&](int parr) {                       // pair b of the momenta is Philox block (current slot + b), drawn by its owner
+    const u32 s0 = rng.slot;
+    for (int kk = 0; kk < NO / 2; ++kk) {
+      const int b = slice + kk * G, j = 2 * b;
+      if (j < P) {
+        rng.slot = s0 + (u32)b;
+        double z0, z1; rng.normal2(z0, z1);
+        GAT(parr, j) = z0 / sqrt(GAT(GA_MINV, j)); if (j + 1 < P) GAT(parr, j + 1) = z1 / sqrt(GAT(GA_MINV, j + 1));
+      }
+    }
+    rng.slot = s0 + (u32)NPAIR;
+  };
+  auto half_step = [&](int qfrom, int gfrom, double e) {
+    GEACH(k, j) { GAT(GA_ZP, j) = fma(0.5 * e, GAT(gfrom, j), GAT(GA_ZP, j)); GAT(GA_QE, j) = fma(e * GAT(GA_MINV, j), GAT(GA_ZP, j), GAT(qfrom, j)); }
+  };
+  auto prepare_leaf = [&]() { half_step(GA_ZQ, GA_ZG, sgn * eps); phase = GPH_LEAF; };
+  auto start_subtree = [&]() {
+    sgn = rng.u01() > 0.5 ? 1 : -1;
+    const int eq = sgn > 0 ? GA_EQ1 : GA_EQ0, ep = sgn > 0 ? GA_EP1 : GA_EP0, eg = sgn > 0 ? GA_EG1 : GA_EG0;
+    GEACH(k, j) { GAT(GA_ZQ, j) = GAT(eq, j); GAT(GA_ZP, j) = GAT(ep, j); GAT(GA_ZG, j) = GAT(eg, j); }
+    leaf = 0;
+    prepare_leaf();
+  };
+  auto prepare_trial = [&]() { sample_p(GA_ZP); H0t = -lp0 + kinetic(GA_ZP); half_step(GA_Q, GA_G0, teps); phase = GPH_TRIAL; };
+  auto begin_transition = [&]() {
+    const unsigned long long step = a.step0 + (u64)t;
+    if (ad[9] == 1.0 && (double)step >= cfg.num_warmup) { ad[0] = exp(ad[3]); ad[9] = 2.0; }  // complete_adaptation
+    eps = ad[0];
+    sample_p(GA_ZP);
+    GEACH(k, j) {
+      const double qj = GAT(GA_Q, j), pj = GAT(GA_ZP, j), gj = GAT(GA_G0, j);
+      GAT(GA_EQ0, j) = qj; GAT(GA_EQ1, j) = qj; GAT(GA_EP0, j) = pj; GAT(GA_EP1, j) = pj; GAT(GA_EG0, j) = gj; GAT(GA_EG1, j) = gj;
+      GAT(GA_QS, j) = qj; GAT(GA_RHO, j) = pj;
+    }
+    lps = lp0; lsw = 0.0; H0 = -lp0 + kinetic(GA_ZP);
+    depth = 0; n_leap = 0; sum_metro = 0.0; divergent = false;
+    start_subtree();
+  };
+  auto begin_init_stepsize = [&](bool upd) {
+    from_update = upd; teps = ad[0]; tdir = 0;
+    if (teps == 0.0 || teps > 1e7) return false;
+    prepare_trial();
+    return true;
+  };
+  auto next_transition = [&]() {
+    ++t;
+    if (t >= a.n_steps) { phase = GPH_DONE; return; }
+    rng.init(a.seed, (u64)(a.chain0 + cidx), a.step0 + (u64)t);
+    GEACH(k, j) GAT(GA_QE, j) = GAT(GA_Q, j);
+    phase = GPH_START;
+  };
+  auto end_transition = [&]() {
+    const double accept_prob = sum_metro / (double)n_leap;
+    GEACH(k, j) GAT(GA_Q, j) = GAT(GA_QS, j);
+    lp = lps;
+    ++n_acc;
+    stat_depth = depth; stat_leaps += n_leap; stat_div += divergent ? 1.0 : 0.0; stat_acc = accept_prob;
+    long long slot;
+    if (active && record_slot(a, t, &slot)) GEACH(k, j) record_value(a, slot, j, chain, GAT(GA_Q, j));
+    bool update = false;
+    if (ad[9] == 1.0) {
+      adapt_learn_stepsize(ad, cfg, accept_prob > 1.0 ? 1.0 : accept_prob);
+      const bool in_w = adapt_in_window(ad, cfg), ends = adapt_window_ends(ad, cfg);
+      if (in_w) { ad[8] += 1.0; GEACH(k, j) welford_add(ad[8], GAT(GA_Q, j), GAT(GA_WM, j), GAT(GA_WM2, j)); }
+      if (ends) {
+        adapt_next_window(ad, cfg);
+        GEACH(k, j) { GAT(GA_MINV, j) = adapt_window_var(ad[8], GAT(GA_WM2, j), GAT(GA_MINV, j)); GAT(GA_WM, j) = 0.0; GAT(GA_WM2, j) = 0.0; }
+        ad[8] = 0.0;
+        update = true;
+      }
+      ad[5] += 1.0;
+    }
+    if (update) { GEACH(k, j) GAT(GA_QE, j) = GAT(GA_Q, j); phase = GPH_UPD; }
+    else next_transition();
+  };
+
+  for (;;) {
+    const bool busy = phase != GPH_DONE;
+    if (!__any_sync(0xffffffffu, busy)) break;
+    const double lpe = ev();                       // warp-wide: reads QE of every chain of the warp, fills GE
+    if (!busy) continue;
+    if (phase == GPH_START || phase == GPH_UPD) {
+      lp0 = lpe; lp = lpe;
+      GEACH(k, j) GAT(GA_G0, j) = GAT(GA_GE, j);
+      if (phase == GPH_START) {
+        bool trials = false;
+        if (ad[9] == 0.0) {
+          GEACH(k, j) { GAT(GA_MINV, j) = 1.0; GAT(GA_WM, j) = 0.0; GAT(GA_WM2, j) = 0.0; }
+          adapt_reset(ad, cfg);
+          trials = begin_init_stepsize(false);
+        }
+        if (!trials) begin_transition();
+      } else if (!begin_init_stepsize(true)) {
+        ad[1] = log(10.0 * ad[0]); ad[2] = 0.0; ad[3] = 0.0; ad[4] = 0.0;
+        next_transition();
+      }
+    } else if (phase == GPH_TRIAL) {
+      GEACH(k, j) GAT(GA_ZP, j) = fma(0.5 * teps, GAT(GA_GE, j), GAT(GA_ZP, j));
+      double h = -lpe + kinetic(GA_ZP);
+      if (isnan(h)) h = pos_inf();
+      if (!init_stepsize_update(teps, tdir, H0t - h)) prepare_trial();
+      else {
+        ad[0] = teps;
+        if (from_update) { ad[1] = log(10.0 * ad[0]); ad[2] = 0.0; ad[3] = 0.0; ad[4] = 0.0; next_transition(); }
+        else begin_transition();
+      }
+    } else {  // GPH_LEAF
+      const double e = sgn * eps;
+      GEACH(k, j) { GAT(GA_ZQ, j) = GAT(GA_QE, j); GAT(GA_ZG, j) = GAT(GA_GE, j); GAT(GA_ZP, j) = fma(0.5 * e, GAT(GA_GE, j), GAT(GA_ZP, j)); }
+      ++n_leap;
+      double h = -lpe + kinetic(GA_ZP);
+      if (isnan(h)) h = pos_inf();
+      if (h - H0 > 1000.0) divergent = true;
+      double c_lsw = H0 - h, c_lp = lpe;
+      sum_metro += (H0 - h > 0.0) ? 1.0 : exp(H0 - h);
+      GEACH(k, j) { GAT(GA_CRHO, j) = GAT(GA_ZP, j); GAT(GA_CPSL, j) = GAT(GA_MINV, j) * GAT(GA_ZP, j); GAT(GA_CQ, j) = GAT(GA_ZQ, j); }
+      bool valid = !divergent;
+      int kk = 0;
+      while (valid && ((leaf >> kk) & 1)) {
+        const double l_lsw = st_lsw[kk];
+        const double sub = gen_log_sum_exp2(l_lsw, c_lsw);
+        bool take_right = c_lsw > sub;
+        if (!take_right) take_right = rng.u01() < exp(c_lsw - sub);
+        double dl = 0.0, dr = 0.0;
+        GEACH(k, j) {
+          const double r = st_rho[kk][k] + GAT(GA_CRHO, j);
+          GAT(GA_CRHO, j) = r;
+          GAT(GA_CPSL, j) = st_psl[kk][k];
+          if (!take_right) GAT(GA_CQ, j) = st_q[kk][k];
+          dr = fma(GAT(GA_MINV, j) * GAT(GA_ZP, j), r, dr); dl = fma(GAT(GA_CPSL, j), r, dl);
+        }
+        dr = gsum(dr); dl = gsum(dl);
+        if (!take_right) c_lp = st_lp[kk];
+        c_lsw = sub;
+        valid = dr > 0.0 && dl > 0.0;
+        ++kk;
+      }
+      if (!valid) end_transition();
+      else if (leaf + 1 == (1 << depth)) {
+        const int eq = sgn > 0 ? GA_EQ1 : GA_EQ0, ep = sgn > 0 ? GA_EP1 : GA_EP0, eg = sgn > 0 ? GA_EG1 : GA_EG0;
+        GEACH(k, j) { GAT(eq, j) = GAT(GA_ZQ, j); GAT(ep, j) = GAT(GA_ZP, j); GAT(eg, j) = GAT(GA_ZG, j); }
+        ++depth;
+        bool take = c_lsw > lsw;
+        if (!take) take = rng.u01() < exp(c_lsw - lsw);
+        lsw = gen_log_sum_exp2(lsw, c_lsw);
+        double dp = 0.0, dm = 0.0;
+        GEACH(k, j) {
+          if (take) GAT(GA_QS, j) = GAT(GA_CQ, j);
+          const double r = GAT(GA_RHO, j) + GAT(GA_CRHO, j);
+          GAT(GA_RHO, j) = r;
+          dp = fma(GAT(GA_MINV, j) * GAT(GA_EP1, j), r, dp); dm = fma(GAT(GA_MINV, j) * GAT(GA_EP0, j), r, dm);
+        }
+        dp = gsum(dp); dm = gsum(dm);
+        if (take) lps = c_lp;
+        if (!(dp > 0.0 && dm > 0.0) || depth >= max_depth) end_transition();
+        else start_subtree();
+      } else {
+        GEACH(k, j) { st_rho[kk][k] = GAT(GA_CRHO, j); st_psl[kk][k] = GAT(GA_CPSL, j); st_q[kk][k] = GAT(GA_CQ, j); }
+        st_lsw[kk] = c_lsw; st_lp[kk] = c_lp;
+        ++leaf;
+        prepare_leaf();
+      }
+    }
+  }
+  if (active) {
+    GEACH(k, j) { f.Q[j * nc + chain] = GAT(GA_Q, j); f.MINV[j * nc + chain] = GAT(GA_MINV, j); f.WM[j * nc + chain] = GAT(GA_WM, j); f.WM2[j * nc + chain] = GAT(GA_WM2, j); }
+  }
+  if (writer) {
+    for (int j = 0; j < STK_AD_LEN; ++j) f.AD[j * nc + chain] = ad[j];
+    f.NS[0 * nc + chain] = stat_depth; f.NS[1 * nc + chain] += stat_leaps; f.NS[2 * nc + chain] += stat_div; f.NS[3 * nc + chain] = stat_acc;
+    f.LP[chain] = lp;
+    if (a.accept) a.accept[chain] += n_acc;
+  }
+#undef GAT
+#undef GOWN
+#undef GEACH
+}
+
 }  // namespace stk
 #endif

@@ -109,3 +109,38 @@ def test_hmcstan_default_sampler_from_ir_text(ctx):
     est = np.r_[out["x_stan_0_1"].mean(), out["x_stan_0_2"].mean(axis=(0, 2))]
     assert np.allclose(est, ridge, atol=0.03), (est, ridge)
     assert abs(np.mean(out["x_stan_0_3"]) - 0.7) < 0.1
+
+
+SCHOOLS = """let v_0_0 = [ x_m_0_0 | i_1_1 <- 1...7 ] :: RVec
+    v_0_1 = [ x_m_0_1 | i_1_1 <- 1...7 ] :: RVec
+    v_0_2 = [ 1.5 | i_1_1 <- 1...7 ] :: RVec
+ in do x_m_0_0 <- normal 0.0 10.0 :: P R
+       x_m_0_1 <- cauchy 0.0 5.0 :: P Subrange R 0.0 Nothing
+       x_m_0_2 <- normals v_0_0 v_0_1 :: P RVec
+       x_m_0_3 <- normals x_m_0_2 v_0_2 :: P RVec
+       return [x_m_0_0,x_m_0_1,x_m_0_2,x_m_0_3]
+"""
+
+
+@pytest.mark.parametrize("lanes", [2, 4, 8])
+def test_distributed_nuts_equals_the_one_thread_sampler(ctx, tmp_path, lanes):
+    """a small hierarchical model with an ODD number of parameters (P = 9: the last coordinate pair is half empty, some lanes own
+    nothing at 8 lanes): the NUTS kernel with the chain's state distributed over its lanes (gen_nuts_lanes) against the one-thread
+    NUTS of the same generated module (nuts_lanes=0) in lockstep — same Philox blocks, so depth / leapfrog counts exact and states
+    at 1e-8 per transition through warm-up, both window ends and after"""
+    from stochaskell_b200 import Chains, Module, ir_to_cuda
+    y = np.array([2.8, 0.8, -0.3, 0.7, -0.1, 0.1, 1.8])
+    C, seed = 45, 3                                            # 45 chains: a ragged last warp at every lane count
+    mods = [Module(ctx, ir_to_cuda(SCHOOLS, [], name=f"schools_{tag}", mode="density", given="x_m_0_3", lanes=lanes, **opt), cache_dir=str(tmp_path))
+            for tag, opt in (("lanes", {}), ("one", dict(nuts_lanes=0)))]
+    assert mods[0].nparam == 9
+    gen, ref = (Chains(m, C, seed=seed) for m in mods)
+    q0 = 0.3 * np.random.default_rng(1).standard_normal((9, C))
+    cfg = dict(CFG, num_warmup=150, stepsize=0.5)
+    for ch in (gen, ref):
+        ch.set_data("x_m_0_3", y)
+        for k, v in cfg.items():
+            ch.set_param(k, float(v))
+        ch.set_state("q", q0)
+    last = lockstep(gen, ref, "nuts", list(range(1, 7)) + [74, 75, 76, 99, 100, 101, 149, 150, 151, 152, 170])
+    assert np.all(last["ad"][9] == 2.0)

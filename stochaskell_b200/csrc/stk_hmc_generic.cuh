@@ -575,5 +575,124 @@ STK_DEV void gen_nuts_lanes(const StkArgs& a, const GenFields& f, const double* 
 #undef GEACH
 }
 
+// ---- adapt_diag_e_static_hmc with the chain's state distributed over its lanes (the same layout and ownership as gen_nuts_lanes; arrays
+// GA_Q, GA_MINV, GA_WM, GA_WM2, GA_QE = evaluation point, GA_GE = its gradient, GA_ZP = momenta, GA_G0 = gradient at the start of a
+// trial, GA_QS = start of the trajectory).  All chains of a warp run the same loops to the warp's maximum trip count around the warp-wide
+// evaluation, as gen_hmc_adapt does around a CTA-wide one.
+template <int P, int G, int CPB, class Eval>
+STK_DEV void gen_hmc_adapt_lanes(const StkArgs& a, const GenFields& f, const double* par_adapt, long long chain, long long cidx, bool active,
+                                 int slice, int c, double* sm, Eval&& ev) {
+  constexpr int NPAIR = (P + 1) / 2, NO = 2 * ((NPAIR + G - 1) / G);
+  const long long nc = a.n_chains;
+  const unsigned gmask = (G == 32 ? 0xffffffffu : ((1u << G) - 1u)) << ((threadIdx.x / G) * G);
+  const bool writer = slice == 0 && active;
+  AdaptCfg cfg; cfg.init(par_adapt);
+#define GAT(arr, j) sm[((arr) * P + (j)) * CPB + c]
+#define GOWN(k) (2 * (slice + ((k) >> 1) * G) + ((k) & 1))
+#define GEACH(k, j) for (int k = 0; k < NO; ++k) if (const int j = GOWN(k); j < P)
+  auto gsum = [&](double v) { return group_sum_masked<G>(v, gmask); };
+  auto any = [&](bool b) { return (bool)__any_sync(0xffffffffu, b); };
+  double ad[STK_AD_LEN];
+  GEACH(k, j) { GAT(GA_Q, j) = f.Q[j * nc + cidx]; GAT(GA_MINV, j) = f.MINV[j * nc + cidx]; GAT(GA_QE, j) = GAT(GA_Q, j); }
+  for (int j = 0; j < STK_AD_LEN; ++j) ad[j] = f.AD[j * nc + cidx];
+  unsigned long long n_acc = 0;
+  double lp = 0.0;
+  auto sample_p = [&](Rng& rng) {
+    const u32 s0 = rng.slot;
+    for (int kk = 0; kk < NO / 2; ++kk) {
+      const int b = slice + kk * G, j = 2 * b;
+      if (j < P) {
+        rng.slot = s0 + (u32)b;
+        double z0, z1; rng.normal2(z0, z1);
+        GAT(GA_ZP, j) = z0 / sqrt(GAT(GA_MINV, j)); if (j + 1 < P) GAT(GA_ZP, j + 1) = z1 / sqrt(GAT(GA_MINV, j + 1));
+      }
+    }
+    rng.slot = s0 + (u32)NPAIR;
+  };
+  auto kinetic = [&]() { double ke = 0.0; GEACH(k, j) ke = fma(GAT(GA_MINV, j) * GAT(GA_ZP, j), GAT(GA_ZP, j), ke); return 0.5 * gsum(ke); };
+  // evaluate at GA_Q (the evaluation point array is the mirror the evaluation reads)
+  auto eval_at_q = [&]() { GEACH(k, j) GAT(GA_QE, j) = GAT(GA_Q, j); return ev(); };
+  // base_hmc::init_stepsize; lp / GA_GE hold the density and gradient at q on entry and on exit
+  auto init_stepsize = [&](Rng& rng, bool want) {
+    double eps = ad[0];
+    int dir = 0;
+    bool done = !want || eps == 0.0 || eps > 1e7;
+    const double lp0 = lp;
+    GEACH(k, j) GAT(GA_G0, j) = GAT(GA_GE, j);
+    while (any(!done)) {
+      if (!done) sample_p(rng);
+      const double H0 = -lp0 + kinetic();
+      GEACH(k, j) { GAT(GA_ZP, j) = fma(0.5 * eps, GAT(GA_G0, j), GAT(GA_ZP, j)); GAT(GA_QE, j) = fma(eps * GAT(GA_MINV, j), GAT(GA_ZP, j), GAT(GA_Q, j)); }
+      const double lpt = ev();
+      GEACH(k, j) GAT(GA_ZP, j) = fma(0.5 * eps, GAT(GA_GE, j), GAT(GA_ZP, j));
+      double h = -lpt + kinetic();
+      if (isnan(h)) h = pos_inf();
+      if (!done) done = init_stepsize_update(eps, dir, H0 - h);
+    }
+    if (want) ad[0] = eps;
+    GEACH(k, j) GAT(GA_GE, j) = GAT(GA_G0, j);
+  };
+  for (long long t = 0; t < a.n_steps; ++t) {
+    const unsigned long long step = a.step0 + (u64)t;
+    Rng rng; rng.init(a.seed, (u64)(a.chain0 + cidx), step);
+    const bool fresh = ad[9] == 0.0;
+    if (fresh) { GEACH(k, j) GAT(GA_MINV, j) = 1.0; adapt_reset(ad, cfg); }
+    lp = eval_at_q();
+    if (any(fresh)) init_stepsize(rng, fresh);
+    if (ad[9] == 1.0 && (double)step >= cfg.num_warmup) { ad[0] = exp(ad[3]); ad[9] = 2.0; }  // complete_adaptation
+    const double eps = ad[0];
+    const int L = adapt_leaps(cfg.int_time, eps);
+    sample_p(rng);
+    const double H0 = -lp + kinetic();
+    const double lp0 = lp;
+    GEACH(k, j) GAT(GA_QS, j) = GAT(GA_Q, j);
+    for (int l = 0; any(l < L); ++l) {
+      const bool on = l < L;
+      if (on) GEACH(k, j) { GAT(GA_ZP, j) = fma(0.5 * eps, GAT(GA_GE, j), GAT(GA_ZP, j)); GAT(GA_Q, j) = fma(eps * GAT(GA_MINV, j), GAT(GA_ZP, j), GAT(GA_Q, j)); }
+      lp = eval_at_q();
+      if (on) GEACH(k, j) GAT(GA_ZP, j) = fma(0.5 * eps, GAT(GA_GE, j), GAT(GA_ZP, j));
+    }
+    double H = -lp + kinetic();
+    if (isnan(H)) H = pos_inf();
+    double accept_prob = exp(H0 - H);
+    const double u = rng.u01();
+    if (accept_prob < 1.0 && u > accept_prob) { GEACH(k, j) GAT(GA_Q, j) = GAT(GA_QS, j); lp = lp0; } else ++n_acc;
+    if (accept_prob > 1.0) accept_prob = 1.0;
+    bool update = false;
+    if (ad[9] == 1.0) {
+      adapt_learn_stepsize(ad, cfg, accept_prob);
+      const bool in_w = adapt_in_window(ad, cfg), ends = adapt_window_ends(ad, cfg);
+      if (in_w || ends) {
+        // the Welford estimator stays in the module's wm / wm2 fields: every coordinate is read and written by its owner only
+        GEACH(k, j) {
+          double wm = f.WM[j * nc + cidx], wm2 = f.WM2[j * nc + cidx];
+          if (in_w) welford_add(ad[8] + 1.0, GAT(GA_Q, j), wm, wm2);
+          if (ends) { GAT(GA_MINV, j) = adapt_window_var(ad[8] + (in_w ? 1.0 : 0.0), wm2, GAT(GA_MINV, j)); wm = 0.0; wm2 = 0.0; }
+          if (active) { f.WM[j * nc + chain] = wm; f.WM2[j * nc + chain] = wm2; }
+        }
+        if (in_w) ad[8] += 1.0;
+        if (ends) { adapt_next_window(ad, cfg); ad[8] = 0.0; update = true; }
+      }
+      ad[5] += 1.0;
+    }
+    if (any(update)) {
+      lp = eval_at_q();
+      init_stepsize(rng, update);
+      if (update) { ad[1] = log(10.0 * ad[0]); ad[2] = 0.0; ad[3] = 0.0; ad[4] = 0.0; }
+    }
+    long long slot;
+    if (active && record_slot(a, t, &slot)) GEACH(k, j) record_value(a, slot, j, chain, GAT(GA_Q, j));
+  }
+  if (active) GEACH(k, j) { f.Q[j * nc + chain] = GAT(GA_Q, j); f.MINV[j * nc + chain] = GAT(GA_MINV, j); }
+  if (writer) {
+    for (int j = 0; j < STK_AD_LEN; ++j) f.AD[j * nc + chain] = ad[j];
+    f.LP[chain] = lp;
+    if (a.accept) a.accept[chain] += n_acc;
+  }
+#undef GAT
+#undef GOWN
+#undef GEACH
+}
+
 }  // namespace stk
 #endif

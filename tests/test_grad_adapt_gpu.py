@@ -122,11 +122,12 @@ SCHOOLS = """let v_0_0 = [ x_m_0_0 | i_1_1 <- 1...7 ] :: RVec
 """
 
 
+@pytest.mark.parametrize("kernel", ["nuts", "hmc_adapt"])
 @pytest.mark.parametrize("lanes", [2, 4, 8])
-def test_distributed_nuts_equals_the_one_thread_sampler(ctx, tmp_path, lanes):
+def test_distributed_nuts_equals_the_one_thread_sampler(ctx, tmp_path, lanes, kernel):
     """a small hierarchical model with an ODD number of parameters (P = 9: the last coordinate pair is half empty, some lanes own
-    nothing at 8 lanes): the NUTS kernel with the chain's state distributed over its lanes (gen_nuts_lanes) against the one-thread
-    NUTS of the same generated module (nuts_lanes=0) in lockstep — same Philox blocks, so depth / leapfrog counts exact and states
+    nothing at 8 lanes): the NUTS and adaptive static-HMC kernels with the chain's state distributed over its lanes (gen_nuts_lanes,
+    gen_hmc_adapt_lanes) against the one-thread samplers of the same generated module (nuts_lanes=0) in lockstep — same Philox blocks, so depth / leapfrog counts exact and states
     at 1e-8 per transition through warm-up, both window ends and after"""
     from stochaskell_b200 import Chains, Module, ir_to_cuda
     y = np.array([2.8, 0.8, -0.3, 0.7, -0.1, 0.1, 1.8])
@@ -142,5 +143,5 @@ def test_distributed_nuts_equals_the_one_thread_sampler(ctx, tmp_path, lanes):
         for k, v in cfg.items():
             ch.set_param(k, float(v))
         ch.set_state("q", q0)
-    last = lockstep(gen, ref, "nuts", list(range(1, 7)) + [74, 75, 76, 99, 100, 101, 149, 150, 151, 152, 170])
+    last = lockstep(gen, ref, kernel, list(range(1, 7)) + [74, 75, 76, 99, 100, 101, 149, 150, 151, 152, 170])
     assert np.all(last["ad"][9] == 2.0)

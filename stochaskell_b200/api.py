@@ -678,6 +678,8 @@ def runStanCUDA(method: CudaMethod, module_spec: str, data_file: str, init_file:
     (`<output_file stem>_<chain>.csv`, CmdStan's per-chain layout: lp__, the constrained parameters) that `stanRead`
     and stansummary read; returns the constrained draws [num_samples][P][num_chains]."""
     from .io import rdump_load, stan_columns, write_stan_csv
+    if is_ir_text(module_spec):
+        return _run_stan_ir(method, module_spec, data_file, init_file, output_file, csv_chains)
     b = STAN_BINDINGS.get(module_spec)
     if b is None:
         raise StkError(-1, f"no Stan identifier binding for {module_spec}")
@@ -719,4 +721,50 @@ def runStanCUDA(method: CudaMethod, module_spec: str, data_file: str, init_file:
                 comment += (f"\nAdaptation terminated\nStep size = {eps[c]:.6g}\nDiagonal elements of inverse mass matrix:\n"
                             + ", ".join(f"{x:.6g}" for x in minv[:, c]))
             write_stan_csv(f"{stem}_{c + 1}.csv", names, np.concatenate([lp, cons[:, :, c]], axis=1), comment=comment)
+    return cons
+
+
+def _run_stan_ir(method: CudaMethod, model_ir: str, data_file: str, init_file: Optional[str], output_file: Optional[str],
+                 csv_chains: int) -> np.ndarray:
+    """runStanCUDA for a model given as IR text: the identifiers of the Stan program `stanProgram` generates ARE the PNode ids
+    (stanId, Stan.hs:43-57), so no binding table is needed — the PNodes that appear in the data file are the conditioned ones, the
+    init file holds the others on the model's scale, and the CSV columns are the qmap blocks in program order, elements column-major
+    (a corr_matrix as its K x K entries), exactly CmdStan's layout."""
+    import re as _re
+    from .io import rdump_load, stan_columns, write_stan_csv
+    env = rdump_load(data_file)
+    ids = _re.findall(r"^\s*(?:in do\s+)?(\w+)\s*<-", model_ir, _re.M)
+    given = [i for i in ids if i in env]
+    if not given:
+        raise StkError(-1, f"{data_file}: none of the program's PNodes {ids} is in the data file")
+    data = {i: np.ascontiguousarray(env[i], dtype=np.float64) for i in given}
+    init = None
+    if init_file:
+        ienv = rdump_load(init_file)
+        init = {i: np.asarray(ienv[i], dtype=np.float64) for i in ids if i in ienv}
+    draws = hmcCUDA(method, model_ir, data, init=init)
+    s = hmcCUDA.last_sampler
+    ch = s.chains
+    vals = constrain_draws(s.module.descriptor, draws)
+    names, cols = ["lp__"], []
+    for ident, v in vals.items():                      # qmap order = program order = the parameters block
+        shape = v.shape[1:-1]
+        names += stan_columns(ident, shape)
+        S, Cn = v.shape[0], v.shape[-1]
+        cols.append(v.reshape(S, -1, Cn) if len(shape) < 2 else v.transpose(0, 2, 1, 3).reshape(S, -1, Cn))      # column-major elements
+    cons = np.concatenate(cols, axis=1) if cols else draws
+    if output_file:
+        stem = output_file[:-4] if output_file.endswith(".csv") else output_file
+        eps = ch.get_state("ad")[0] if method.adapt else None
+        minv = ch.get_state("minv") if method.adapt else None
+        q_last = ch.get_state("q")
+        lps = np.stack([(ch.set_state("q", np.ascontiguousarray(draws[t])), ch.logp())[1] for t in range(draws.shape[0])]) \
+            if draws.shape[0] else np.zeros((0, draws.shape[2]))
+        ch.set_state("q", q_last)
+        for c in range(min(csv_chains, draws.shape[2])):
+            comment = f"model = {s.module.name} (generated from IR)\nalgorithm = hmc, engine = {method.engine}, chains = {method.num_chains}, chain = {c + 1}"
+            if eps is not None:
+                comment += (f"\nAdaptation terminated\nStep size = {eps[c]:.6g}\nDiagonal elements of inverse mass matrix:\n"
+                            + ", ".join(f"{x:.6g}" for x in minv[:, c]))
+            write_stan_csv(f"{stem}_{c + 1}.csv", names, np.concatenate([lps[:, c:c + 1], cons[:, :, c]], axis=1), comment=comment)
     return cons

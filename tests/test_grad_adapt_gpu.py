@@ -145,3 +145,40 @@ def test_distributed_nuts_equals_the_one_thread_sampler(ctx, tmp_path, lanes, ke
         ch.set_state("q", q0)
     last = lockstep(gen, ref, kernel, list(range(1, 7)) + [74, 75, 76, 99, 100, 101, 149, 150, 151, 152, 170])
     assert np.all(last["ad"][9] == 2.0)
+
+
+def test_runstan_file_protocol_on_model_ir(ctx, tmp_path):
+    """`runStan`'s file protocol (Stan.hs:443-490) for a model given as IR text: R-dump data / init files keyed by the PNode ids (= the
+    identifiers of the Stan program stanProgram generates), Stan CSV out.  linreg: the files the vendored CmdStan consumed
+    (tests/golden/wire), columns and posterior as the builtin's run of the same protocol; birats: corr_matrix and matrix parameters
+    in CmdStan's column order."""
+    from stochaskell_b200 import CudaMethod, read_stan_csv, runStanCUDA
+    from stochaskell_b200.io import rdump_dumps
+    W = os.path.join(HERE, "golden", "wire")
+    lin = open(os.path.join(HERE, "golden", "ir", "linreg_model.txt")).read().replace("1...1000", "1...6")
+    m = CudaMethod(num_chains=256, num_samples=100, num_warmup=150, step_size=1.0, adapt=True, engine="nuts", seed=5)
+    out = str(tmp_path / "lin.csv")
+    cons = runStanCUDA(m, lin, os.path.join(W, "linreg_tiny.data.R"), os.path.join(W, "linreg_tiny.init.R"), out, csv_chains=2)
+    ref = runStanCUDA(m, "builtin:linreg", os.path.join(W, "linreg_tiny.data.R"), os.path.join(W, "linreg_tiny.init.R"), str(tmp_path / "ref.csv"), csv_chains=2)
+    assert cons.shape == ref.shape == (100, 12, 256) and np.all(cons[:, -1, :] > 0)
+    names, v, comments = read_stan_csv(str(tmp_path / "lin_2.csv"))
+    rnames, _, _ = read_stan_csv(str(tmp_path / "ref_2.csv"))
+    assert names == rnames and np.array_equal(v[:, 1:], cons[:, :, 1]) and "Step size" in comments
+    sd = ref.std(axis=(0, 2))
+    assert np.all(np.abs(cons.mean(axis=(0, 2)) - ref.mean(axis=(0, 2))) < 0.1 * sd + 1e-9)      # same posterior, 25,600 draws each
+    # birats
+    g = np.load(os.path.join(HERE, "golden", "birats_stan.npz"))
+    bir = open(os.path.join(HERE, "golden", "ir", "birats_model.txt")).read()
+    q0 = g["q"][0]; z = np.tanh(q0[4])
+    (tmp_path / "b.data.R").write_text(rdump_dumps(dict(x_stan_0_0=g["x"], x_stan_0_6=g["y"])))
+    (tmp_path / "b.init.R").write_text(rdump_dumps(dict(x_stan_0_1=q0[0:2], x_stan_0_2=q0[2:4], x_stan_0_3=np.array([[1, z], [z, 1.0]]),
+                                                        x_stan_0_4=np.stack([q0[5:35], q0[35:65]], axis=1), x_stan_0_5=float(np.exp(q0[65])))))
+    mb = CudaMethod(num_chains=64, num_samples=40, num_warmup=100, step_size=1.0, adapt=True, engine="nuts", seed=6)
+    cb = runStanCUDA(mb, bir, str(tmp_path / "b.data.R"), str(tmp_path / "b.init.R"), str(tmp_path / "b.csv"), csv_chains=1)
+    assert cb.shape == (40, 2 + 2 + 4 + 60 + 1, 64)
+    bn, bv, _ = read_stan_csv(str(tmp_path / "b_1.csv"))
+    assert bn[0] == "lp__" and bn[1:3] == ["x_stan_0_1.1", "x_stan_0_1.2"] and bn[5:9] == ["x_stan_0_3.1.1", "x_stan_0_3.2.1", "x_stan_0_3.1.2", "x_stan_0_3.2.2"]
+    assert bn[9] == "x_stan_0_4.1.1" and bn[10] == "x_stan_0_4.2.1" and bn[39] == "x_stan_0_4.1.2" and bn[-1] == "x_stan_0_5"
+    assert np.allclose(bv[:, 5], 1.0) and np.allclose(bv[:, 6], bv[:, 7]) and np.all(np.abs(bv[:, 6]) < 1) and np.all(bv[:, -1] > 0)
+    # the posterior the reference's own run printed (birats.ipynb cell 8): betaMu ~ (104.6, 6.33), sigma ~ 6.85
+    assert abs(cb[:, 0].mean() - 106.0) < 4.0 and abs(cb[:, 1].mean() - 6.2) < 0.5 and abs(cb[:, -1].mean() - 6.2) < 1.5

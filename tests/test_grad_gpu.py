@@ -272,3 +272,36 @@ def test_generated_linreg_beyond_the_shared_memory_budget(ctx, orc, tmp_path):
     ch.set_param("eps", 1e-3); ch.set_param("L", 5)
     ch.step("hmc", 3)
     assert np.all(np.isfinite(ch.get_state("q"))) and np.any(ch.get_state("q") != q0)
+
+
+@pytest.mark.parametrize("name", ["logit", "poisson", "schools"])
+@pytest.mark.parametrize("lanes", [1, 4])
+def test_small_models_on_the_device_equal_their_host_build(ctx, tmp_path, name, lanes):
+    """the small models of tests/test_grad_cpu.py (Poisson regression on integer data with a logistic-transformed parameter,
+    logistic regression on a short given matrix, a hierarchy with an odd parameter count) on B200, one thread and four lanes per chain:
+    lp and gradient against the host build of the same lowering (which the CPU suite checks against finite differences), then a few
+    fused HMC transitions and NUTS transitions run to finite states"""
+    from stochaskell_b200 import Chains, Module, ir_to_cuda
+    from tests.gen_host import host_eval
+    from tests.test_grad_cpu import MODELS
+    text, given, data, P = MODELS[name]
+    host = host_eval(ir_to_cuda(text, [], name=f"{name}_h", mode="density", given=given, lanes=1), data, str(tmp_path))
+    m = Module(ctx, ir_to_cuda(text, [], name=f"{name}_d{lanes}", mode="density", given=given, lanes=lanes), cache_dir=str(tmp_path))
+    C = 37
+    ch = Chains(m, C, seed=3)
+    for k, v in data.items():
+        ch.set_data(k, np.ascontiguousarray(v, dtype=m.fields[k]["dtype"]))
+    q0 = np.ascontiguousarray(0.5 * np.random.default_rng(5).standard_normal((P, C)))
+    ch.set_state("q", q0)
+    lp, g = ch.logp_grad()
+    for c in range(C):
+        lph, gh = host(q0[:, c])
+        assert abs(lp[c] - lph) <= 1e-11 * max(1.0, abs(lph)), (c, lp[c], lph)
+        assert np.max(np.abs(g[:, c] - gh)) <= 1e-10 * max(1.0, np.max(np.abs(gh))), c
+    ch.set_param("eps", 0.01); ch.set_param("L", 5)
+    ch.step("hmc", 20)
+    for k, v in dict(stepsize=0.5, num_warmup=30.0, max_depth=6.0).items():
+        ch.set_param(k, v)
+    ch.step("nuts", 40)
+    q = ch.get_state("q")
+    assert np.all(np.isfinite(q)) and np.any(q != q0) and np.all(ch.get_state("ad")[9] == 2.0)

@@ -16,7 +16,10 @@ PRELUDE = r"""
 #define __device__
 #define __forceinline__ inline
 #define __restrict__
-namespace stk { inline double pos_inf() { return INFINITY; } inline double neg_inf() { return -INFINITY; } }
+namespace stk { inline double pos_inf() { return INFINITY; } inline double neg_inf() { return -INFINITY; }
+inline double digamma(double x) { double r = 0.0; while (x < 6.0) { r -= 1.0 / x; x += 1.0; } const double f = 1.0 / (x * x);
+  const double t = f * (-1.0 / 12.0 + f * (1.0 / 120.0 + f * (-1.0 / 252.0 + f * (1.0 / 240.0 + f * (-1.0 / 132.0 + f * (691.0 / 32760.0 + f * (-1.0 / 12.0)))))));
+  return r + log(x) - 0.5 / x + t; } }
 using namespace stk;
 """
 

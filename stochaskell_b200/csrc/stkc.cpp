@@ -105,7 +105,7 @@ static std::vector<Tok> lex(const std::string& src) {
     }
     if (ch == '-' && prev_space && src.compare(i, 9, "-Infinity") == 0) { adv(9); push("-Infinity", Tok::Num, c0); continue; }
     // punctuation and operators
-    static const char* multi[] = {"...", "::", "<-", "->", "=>", "==", "/=", "<=", ">=", "&&s", "&&", "||", "**", "<>", "#>", "<.>", "<\\>", "+s", "*s", ".?", nullptr};
+    static const char* multi[] = {"...", "::", "<-", "->", "=>", "==", "/=", "<=", ">=", "&&s", "&&", "||", "**", "<>", "#>", "*>", "<.>", "<\\>", "+s", "*s", ".?", nullptr};
     bool done = false;
     for (int m = 0; multi[m]; ++m) {
       size_t L = strlen(multi[m]);
@@ -341,7 +341,7 @@ struct Parser {
   }
 
   static bool binop(const std::string& s) {
-    static const char* ops[] = {"+", "-", "*", "/", "**", "==", "/=", "<", "<=", ">", ">=", "&&", "||", "<>", "#>", "<.>", "<\\>", nullptr};
+    static const char* ops[] = {"+", "-", "*", "/", "**", "==", "/=", "<", "<=", ">", ">=", "&&", "||", "<>", "#>", "*>", "<.>", "<\\>", nullptr};
     for (int i = 0; ops[i]; ++i) if (s == ops[i]) return true;
     return false;
   }
@@ -1137,6 +1137,17 @@ struct Gen {
       };
       v.lazy = lz; bind(d.id, v); return;
     }
+    {
+      static const std::map<std::string, std::string> vun = {{"square", "stk_sq"}, {"exp", "exp"}, {"log", "log"}, {"sqrt", "sqrt"}, {"abs", "fabs"}, {"tanh", "tanh"}, {"log1p", "log1p"}};
+      auto vu = vun.find(f);
+      if (n.type.k == Type::Vec && n.type.sub[0].k == Type::R && vu != vun.end() && n.args.size() == 1 && type_of(n.args[0]).k == Type::Vec) {
+        VA src = va(n.args[0]);                       // element-wise unary function of a vector: an accessor, evaluated by its consumer
+        const std::string fn = vu->second;
+        auto lz = std::make_shared<VA>(); lz->len = src.len;
+        lz->at = [src, fn](const std::string& i) { return fn == "stk_sq" ? "((" + src.at(i) + ") * (" + src.at(i) + "))" : fn + "(" + src.at(i) + ")"; };
+        v.lazy = lz; bind(d.id, v); return;
+      }
+    }
     if (n.type.k == Type::Vec) { vector_node(d); return; }
     if (!n.type.scalar()) die("definition " + d.id + " has unsupported type " + n.type.str());
     std::string e;
@@ -1608,17 +1619,29 @@ struct Gen {
     else if (f == "negate") { auto a = mat_of(n.args.at(0)); *m = *a; m->eye = false; m->at = [a](const std::string& i, const std::string& j) { return "(-" + a->at(i, j) + ")"; }; }
     else if (f == "id") { *m = *mat_of(n.args.at(0)); }
     else if (f == "tr'" || f == "tr") { auto a = mat_of(n.args.at(0)); *m = *a; m->rows = a->cols; m->cols = a->rows; m->at = [a](const std::string& i, const std::string& j) { return a->at(j, i); }; }
-    else if ((f == "*" || f == "/") && n.args.size() == 2 && is_mat(0) != is_mat(1)) {       // matrix (*|/) scalar, scalar * matrix
+    else if ((f == "exp" || f == "log" || f == "sqrt" || f == "square") && n.args.size() == 1) {      // element-wise unary function
+      auto a = mat_of(n.args.at(0)); const std::string fn = f;
+      *m = *a; m->eye = false; m->zeros = false;
+      m->at = [a, fn](const std::string& i, const std::string& j) { return fn == "square" ? "((" + a->at(i, j) + ") * (" + a->at(i, j) + "))" : fn + "(" + a->at(i, j) + ")"; };
+    }
+    else if ((f == "*" || f == "/" || f == "*>") && n.args.size() == 2 && is_mat(0) != is_mat(1)) {       // matrix (*|/) scalar, scalar * matrix
       const size_t mi = is_mat(0) ? 0 : 1;
       auto a = mat_of(n.args.at(mi)); std::string s = sc(1 - mi);
       *m = *a; m->eye = false;
       if (f == "/" && mi != 0) die("scalar / matrix is not supported by the CUDA lowering");
-      const std::string op = f == "*" ? " * " : " / ";
+      const std::string op = f == "/" ? " / " : " * ";
       if (!a->zeros) m->at = [a, s, op, mi](const std::string& i, const std::string& j) { return mi == 0 ? "(" + a->at(i, j) + op + s + ")" : "(" + s + op + a->at(i, j) + ")"; };
     }
     else if (f == "+" || f == "-" || f == "+s" || f == "*") {                                 // element-wise
       std::vector<std::shared_ptr<Mat>> ms;
-      for (auto& a : n.args) ms.push_back(mat_of(a));
+      for (auto& a : n.args) {
+        if (type_of(a).k == Type::Mat) { ms.push_back(mat_of(a)); continue; }
+        // a scalar operand (`cast lsv - M`): a 1 x 1 matrix, replicated by the broadcast rule below
+        auto sm = std::make_shared<Mat>(); sm->rows = sm->cols = "1"; sm->prepare = [] {};
+        const std::string e = "(" + rv(a, true) + ")";
+        sm->at = [e](const std::string&, const std::string&) { return e; };
+        ms.push_back(sm);
+      }
       // a column (cols == 1) or a row against a full matrix is replicated (rep_matrix in the reference's Stan output)
       m->rows = ms[0]->rows; m->cols = ms[0]->cols;
       for (auto& a : ms) { if (m->rows == "1" && a->rows != "1") m->rows = a->rows; if (m->cols == "1" && a->cols != "1") m->cols = a->cols; }

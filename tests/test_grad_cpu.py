@@ -292,3 +292,35 @@ def test_gamma_density_with_a_parameter_as_shape(tmp_path):
         h = 1e-6
         fd = np.array([(f(q + h * e, grad=False) - f(q - h * e, grad=False)) / (2 * h) for e in np.eye(2)])
         assert np.allclose(g, fd, rtol=1e-7, atol=1e-7)
+
+
+def test_gp_classifier_with_latent_hyperparameters_from_ir(tmp_path):
+    """config C3 in the `gpc` form (gpc.ipynb cells 5-12: kernelSE' lsv lls2 1e-6 as matrix algebra, normalChol = mu + chol cov #> w,
+    bernoulliLogit per point; posterior over (lsv, lls2, w) given x and z) lowered from IR at n = 8: the Cholesky factor is unrolled
+    into the graph, so its adjoint — the piece the hand-tuned modules do not have — comes out of the graph differentiation.  Host
+    build against a numpy restatement and central differences; re-rolled and unrolled forms agree."""
+    import numpy as np
+    from tests.gen_host import host_eval
+    text = ir("gpc_model")
+    rng = np.random.default_rng(4)
+    x = np.sort(10.0 * rng.random(8)); z = (rng.random(8) < 0.5).astype(np.int32)
+    data = dict(x_g_0_2=x, x_g_0_4=z)
+    f = host_eval(ir_to_cuda(text, [], name="gpc", mode="density", given="x_g_0_2,x_g_0_4", lanes=1), data, str(tmp_path))
+    fu = host_eval(ir_to_cuda(text, [], name="gpc_u", mode="density", given="x_g_0_2,x_g_0_4", lanes=1, roll=0, exact_div=1), data, str(tmp_path))
+
+    def want(q):
+        lsv, lls2, w = q[0], q[1], q[2:]
+        K = np.exp(lsv - (x[:, None] - x[None, :]) ** 2 / (2 * np.exp(lls2))) + 1e-6 * np.eye(8)
+        fv = np.linalg.cholesky(K) @ w
+        s = 2.0 * z - 1.0
+        return (-0.5 * lsv ** 2 - 0.5 * np.log(2 * np.pi) - 0.5 * ((lls2 - np.log(100.0)) / 2.0) ** 2 - np.log(2.0) - 0.5 * np.log(2 * np.pi)
+                - 0.5 * w @ w - 4.0 * np.log(2 * np.pi) - np.log1p(np.exp(-s * fv)).sum())
+    for _ in range(5):
+        q = np.r_[0.3 * rng.standard_normal(), np.log(100.0) - 3.0 + rng.standard_normal(), rng.standard_normal(8)]
+        lp, g = f(q)
+        assert lp == pytest.approx(want(q), rel=1e-11, abs=1e-11)
+        lpu, gu = fu(q)
+        assert abs(lp - lpu) <= 1e-11 * max(1.0, abs(lpu)) and np.max(np.abs(g - gu)) <= 1e-9 * max(1.0, np.max(np.abs(gu)))
+        h = 1e-6
+        fd = np.array([(f(q + h * e, grad=False) - f(q - h * e, grad=False)) / (2 * h) for e in np.eye(10)])
+        assert np.allclose(g, fd, rtol=1e-5, atol=1e-6), (g, fd)

@@ -305,3 +305,39 @@ def test_small_models_on_the_device_equal_their_host_build(ctx, tmp_path, name, 
     ch.step("nuts", 40)
     q = ch.get_state("q")
     assert np.all(np.isfinite(q)) and np.any(q != q0) and np.all(ch.get_state("ad")[9] == 2.0)
+
+
+def test_gp_classifier_from_ir_simulates_and_samples(ctx, orc, tmp_path):
+    """config C3 in the `gpc` form (gpc.ipynb cells 5-12) from ONE IR text at n = 8: `simulate` (x ~ uniforms, w ~ joint normal,
+    f = chol K(x; lsv, lls2) #> w, z_i ~ bernoulliLogit f_i — every draw restated from the returned values and the oracle's Philox
+    primitives) and the conditioned model [ (lsv, lls2, w) | x, z ] under NUTS: lp / gradient on B200 equal the host build of the
+    lowering (which the CPU suite pins to a numpy restatement and finite differences: the Cholesky adjoint is graph differentiation)"""
+    from stochaskell_b200 import Chains, CudaMethod, Module, constrain_draws, hmcCUDA, ir_to_cuda, simulateCUDA
+    from tests.gen_host import host_eval
+    text = open(os.path.join(HERE, "golden", "ir", "gpc_model.txt")).read()
+    C, seed = 24, 9
+    STEP = (1 << 64) - 1
+    lsv, lls2, xs, ws, zs = simulateCUDA(text, C, seed=seed, ctx=ctx, matcap=8, veccap=8)
+    for c in range(0, C, 2):
+        x, w, z = xs[c], ws[c], zs[c]
+        assert x.shape == (8,) and (0 <= x).all() and (x <= 10).all()
+        K = np.exp(lsv[c] - (x[:, None] - x[None, :]) ** 2 / (2 * np.exp(lls2[c]))) + 1e-6 * np.eye(8)
+        f = np.linalg.cholesky(K) @ w
+        zo = [orc.draw("bernoulli", seed, c, STEP ^ ((4 << 12) << 32), (i + 1) << 16, 1.0 / (1.0 + np.exp(-f[i]))) for i in range(8)]
+        assert list(z) == zo, (c, z, zo)
+    # the conditioned model on draw 0's (x, z)
+    data = dict(x_g_0_2=xs[0], x_g_0_4=zs[0].astype(np.int32))
+    host = host_eval(ir_to_cuda(text, [], name="gpc_h", mode="density", given="x_g_0_2,x_g_0_4", lanes=1), data, str(tmp_path))
+    m = Module(ctx, ir_to_cuda(text, [], name="gpc_d", mode="density", given="x_g_0_2,x_g_0_4"), cache_dir=str(tmp_path))
+    ch = Chains(m, 33, seed=2)
+    for k, v in data.items():
+        ch.set_data(k, np.ascontiguousarray(v, dtype=m.fields[k]["dtype"]))
+    q0 = np.ascontiguousarray(np.r_[0.0, np.log(100.0) - 3.0, np.zeros(8)][:, None] + 0.5 * np.random.default_rng(1).standard_normal((10, 33)))
+    ch.set_state("q", q0)
+    lp, g = ch.logp_grad()
+    for c in range(33):
+        lph, gh = host(q0[:, c])
+        assert abs(lp[c] - lph) <= 1e-10 * max(1.0, abs(lph)) and np.max(np.abs(g[:, c] - gh)) <= 1e-9 * max(1.0, np.max(np.abs(gh))), c
+    dr = hmcCUDA(CudaMethod(num_chains=64, num_samples=50, num_warmup=100, step_size=1.0, adapt=True, engine="nuts", seed=3), text, data)
+    out = constrain_draws(hmcCUDA.last_sampler.module.descriptor, dr)
+    assert out["x_g_0_3"].shape == (50, 8, 64) and np.all(np.isfinite(dr)) and abs(out["x_g_0_0"].mean()) < 1.0

@@ -225,6 +225,19 @@ MODELS = {
        x_g_0_2 <- gammas v_0_0 v_0_1 :: P RVec
        return [x_g_0_0,x_g_0_1,x_g_0_2]
 """, "x_g_0_2", dict(x_g_0_2=[0.8, 1.9, 0.4, 2.2, 1.1, 0.7, 3.0, 1.4]), 2),
+    # negative-binomial counts whose shape is a trigonometric function of parameters (lgamma(a + k): digamma; sin / cos / tan)
+    "negbin": ("""let v_0_0 = sin x_n_0_2 :: R
+    v_0_1 = cos x_n_0_2 :: R
+    v_0_2 = v_0_0 * v_0_1 :: R
+    v_0_3 = tan v_0_2 :: R
+    v_0_4 = 2.0 + v_0_3 :: R
+    v_0_5 = x_n_0_0 * v_0_4 :: R
+ in do x_n_0_0 <- gamma 2.0 1.0 :: P Subrange R 0.0 Nothing
+       x_n_0_1 <- gamma 2.0 2.0 :: P Subrange R 0.0 Nothing
+       x_n_0_2 <- normal 0.0 1.0 :: P R
+       x_n_0_3 <- [ neg_binomial v_0_5 x_n_0_1 :: P Z | i_1_1 <- 1...9 ] :: Array 1...9 Z
+       return [x_n_0_0,x_n_0_1,x_n_0_2,x_n_0_3]
+""", "x_n_0_3", dict(x_n_0_3=[0, 3, 1, 7, 2, 2, 5, 0, 4]), 3),
     # logistic regression: a short given matrix, #>, bernoulliLogits
     "logit": ("""let v_0_0 = [ 0.0 | i_1_1 <- 1...3 ] :: RVec
     v_0_1 = [ 2.5 | i_1_1 <- 1...3 ] :: RVec
@@ -324,3 +337,40 @@ def test_gp_classifier_with_latent_hyperparameters_from_ir(tmp_path):
         h = 1e-6
         fd = np.array([(f(q + h * e, grad=False) - f(q - h * e, grad=False)) / (2 * h) for e in np.eye(10)])
         assert np.allclose(g, fd, rtol=1e-5, atol=1e-6), (g, fd)
+
+
+def test_neg_binomial_and_trigonometric_nodes(tmp_path):
+    """the rest of the densities / functions the reference's Stan backend lists for scalar models (Stan.hs:136-170): neg_binomial with
+    its shape and inverse scale as parameters (lpdfNegBinomial, Abstract.hs:113-115; lgamma(a + k) differentiates through digamma) and
+    sin / cos / tan — against scipy (nbinom with n = a, p = b / (b + 1)) and central differences"""
+    import numpy as np
+    from scipy import stats
+    from tests.gen_host import host_eval
+    text = """let v_0_0 = sin x_n_0_2 :: R
+    v_0_1 = cos x_n_0_2 :: R
+    v_0_2 = v_0_0 * v_0_1 :: R
+    v_0_3 = tan v_0_2 :: R
+    v_0_4 = 2.0 + v_0_3 :: R
+    v_0_5 = x_n_0_0 * v_0_4 :: R
+ in do x_n_0_0 <- gamma 2.0 1.0 :: P Subrange R 0.0 Nothing
+       x_n_0_1 <- gamma 2.0 2.0 :: P Subrange R 0.0 Nothing
+       x_n_0_2 <- normal 0.0 1.0 :: P R
+       x_n_0_3 <- [ neg_binomial v_0_5 x_n_0_1 :: P Z | i_1_1 <- 1...9 ] :: Array 1...9 Z
+       return [x_n_0_0,x_n_0_1,x_n_0_2,x_n_0_3]
+"""
+    y = np.array([0, 3, 1, 7, 2, 2, 5, 0, 4], dtype=np.int32)
+    src = ir_to_cuda(text, [], name="nb", mode="density", given="x_n_0_3", lanes=1)
+    assert "digamma(" in src and "sin(" in src and "cos(" in src
+    f = host_eval(src, dict(x_n_0_3=y), str(tmp_path))
+    rng = np.random.default_rng(12)
+    for _ in range(5):
+        q = 0.4 * rng.standard_normal(3)
+        a0, b, t = np.exp(q[0]), np.exp(q[1]), q[2]
+        a = a0 * (2.0 + np.tan(np.sin(t) * np.cos(t)))
+        want = (stats.gamma.logpdf(a0, 2.0) + stats.gamma.logpdf(b, 2.0, scale=0.5) + q[0] + q[1] + stats.norm.logpdf(t)
+                + stats.nbinom.logpmf(y, a, b / (b + 1.0)).sum())
+        lp, g = f(q)
+        assert lp == pytest.approx(want, rel=1e-11)
+        h = 1e-6
+        fd = np.array([(f(q + h * e, grad=False) - f(q - h * e, grad=False)) / (2 * h) for e in np.eye(3)])
+        assert np.allclose(g, fd, rtol=1e-6, atol=1e-6)

@@ -1385,6 +1385,12 @@ def main():
                 return [r.get("value"), (r.get("e2e") or {}).get("value"), rf.get("frac"), d.get("ess_per_sec_min"), d.get("rhat_max"),
                         (rf.get("fp64_pipe") or {}).get("frac_of_fp64_pipe", rf.get("frac_of_fp64_pipe")), cb.get("value"), cb.get("kind")]
             out["config"]["also"] = {k: compact(v) for k, v in extra.items()}
+            pp = ((extra.get("linreg_hmc") or {}).get("logpdf") or {}).get("per_point_data") or {}
+            if pp.get("logpdf_gbs"):       # the one physically HBM-bound kernel (generated joint density over points with their own data)
+                out["config"]["hbm_bound_logpdf"] = dict(kernel=pp["kernel"], points_per_gpu=pp["points_per_gpu"], gbs=pp["logpdf_gbs"],
+                                                         frac_of_hbm_peak=pp["frac_of_hbm_peak"], evals_per_sec=pp["evals_per_sec"],
+                                                         dram_bytes_ncu=(pp.get("roofline") or {}).get("traffic"),
+                                                         algorithmic_bytes=(pp.get("roofline") or {}).get("algorithmic_bytes_per_launch"))
             out["config"]["also_columns"] = ["transitions_per_s", "e2e_transitions_per_s", "roofline_frac_algorithmic", "ess_per_s_min",
                                              "rhat_max", "frac_of_fp64_pipe", "cpu_baseline_transitions_per_s", "cpu_baseline_kind"]
             # generated (stkc) kernels against the hand-tuned module of the same model

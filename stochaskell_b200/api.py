@@ -512,6 +512,17 @@ def constrain_draws(descriptor: str, draws: np.ndarray) -> Dict[str, np.ndarray]
         if lo == "corr":
             out[ident] = _corr_matrix_constrain(draws[:, off:off + rows * (rows - 1) // 2, :], rows)
             continue
+        if lo == "cov":            # cov_matrix_constrain: K(K+1)/2 values row by row, the diagonal through exp, W = L L'
+            K = rows
+            y = draws[:, off:off + K * (K + 1) // 2, :]
+            L = np.zeros((y.shape[0], K, K, y.shape[2]))
+            i = 0
+            for m in range(K):
+                for n in range(m):
+                    L[:, m, n] = y[:, i]; i += 1
+                L[:, m, m] = np.exp(y[:, i]); i += 1
+            out[ident] = np.einsum("sikc,sjkc->sijc", L, L)
+            continue
         n = max(1, rows) * max(1, cols)
         x = draws[:, off:off + n, :]
         if lo != "-" and hi == "-":
@@ -549,6 +560,11 @@ def unconstrain_values(descriptor: str, values: Dict[str, np.ndarray]) -> np.nda
                 for i in range(j + 1, rows):
                     z.append(L[i, j] / np.sqrt(1.0 - np.sum(L[i, :j] ** 2)))
             q = np.arctanh(np.array(z))
+        elif lo == "cov":
+            if x.shape != (rows, rows):
+                raise StkError(-1, f"initial value of {ident} must be a {rows} x {rows} covariance matrix")
+            L = np.linalg.cholesky(x)
+            q = np.array([np.log(L[m, n]) if m == n else L[m, n] for m in range(rows) for n in range(m + 1)])
         else:
             want = (rows, cols) if cols else (rows,) if rows else ()
             if x.shape != want:

@@ -47,6 +47,7 @@ struct Error : std::runtime_error { using std::runtime_error::runtime_error; };
 struct Type {
   enum K { Z, R, B, Vec, Mat, Tuple, Union, Unknown } k = Unknown;
   std::vector<Type> sub;  // Vec/Mat: element; Tuple: members; Union: one Tuple per constructor
+  bool cov = false;       // printed as `cov_matrix T` (ArrayT (Just "cov_matrix"), Expression.hs:449): Stan declares it cov_matrix[K]
   bool scalar() const { return k == Z || k == R || k == B; }
   bool integral() const { return k == Z || k == B; }
   std::string str() const {
@@ -213,7 +214,7 @@ struct Parser {
     if (x.s == "ZVec" || x.s == "RVec" || x.s == "BVec") return vecT(scalarT(x.s[0] == 'Z' ? Type::Z : x.s[0] == 'R' ? Type::R : Type::B));
     if (x.s == "ZMat" || x.s == "RMat") { Type m; m.k = Type::Mat; m.sub.push_back(scalarT(x.s[0] == 'Z' ? Type::Z : Type::R)); return m; }
     if (x.s == "vector") return vecT(type());
-    if (x.s == "matrix" || x.s == "corr_matrix" || x.s == "cov_matrix") { Type m; m.k = Type::Mat; m.sub.push_back(type()); return m; }
+    if (x.s == "matrix" || x.s == "corr_matrix" || x.s == "cov_matrix") { Type m; m.k = Type::Mat; m.cov = x.s == "cov_matrix"; m.sub.push_back(type()); return m; }
     if (x.s == "Array" && is("[")) {  // `Array [(lo,hi)] T`: how the 2019 build behind rj-coal.ipynb printed a 1-D array type
       next(); expect("("); ref(); expect(","); ref(); expect(")");
       if (accept(",")) fail("multi-dimensional Array types are not supported by the CUDA lowering");

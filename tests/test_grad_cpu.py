@@ -374,3 +374,39 @@ def test_neg_binomial_and_trigonometric_nodes(tmp_path):
         h = 1e-6
         fd = np.array([(f(q + h * e, grad=False) - f(q - h * e, grad=False)) / (2 * h) for e in np.eye(3)])
         assert np.allclose(g, fd, rtol=1e-6, atol=1e-6)
+
+
+def test_wishart_densities_and_the_cov_matrix_transform(tmp_path):
+    """the last two of stanBuiltinDistributions (Stan.hs:157-170): Sigma ~ inv_wishart 6 S as a cov_matrix PARAMETER (Stan's
+    cov_matrix_constrain with its Jacobian) and W ~ wishart 5 Sigma observed — against scipy.stats.invwishart / wishart and central
+    differences; the qmap round trip of a covariance matrix"""
+    import numpy as np
+    from scipy import stats
+    from stochaskell_b200 import constrain_draws, unconstrain_values
+    from tests.gen_host import host_eval
+    text = """let v_0_0 = diag [1.0,2.0,1.5] :: RMat
+    v_0_1 = outer [0.3,0.5,0.2] [0.3,0.5,0.2] :: RMat
+    v_0_2 = v_0_0 + v_0_1 :: RMat
+ in do x_w_0_0 <- inv_wishart 6.0 v_0_2 :: P cov_matrix R
+       x_w_0_1 <- wishart 5.0 x_w_0_0 :: P RMat
+       return [x_w_0_0,x_w_0_1]
+"""
+    S = np.diag([1.0, 2.0, 1.5]) + np.outer([0.3, 0.5, 0.2], [0.3, 0.5, 0.2])
+    W2 = stats.wishart.rvs(df=5, scale=S, random_state=3)
+    src = ir_to_cuda(text, [], name="wish", mode="density", given="x_w_0_1", lanes=1)
+    assert "#define NP 6\n" in src and "qmap x_w_0_0 0 3 3 cov -" in src
+    assert os.path.getsize(compile_source(ir_to_cuda(text, [], name="wish_d", mode="density", given="x_w_0_1"), str(tmp_path))) > 10000   # the CUDA module
+    f = host_eval(src, dict(x_w_0_1=W2), str(tmp_path))
+    rng = np.random.default_rng(2)
+    for _ in range(5):
+        q = 0.4 * rng.standard_normal(6)
+        Sig = constrain_draws("qmap x_w_0_0 0 3 3 cov -\n", q.reshape(1, 6, 1))["x_w_0_0"][0, :, :, 0]
+        L = np.linalg.cholesky(Sig)
+        jac = 3 * np.log(2.0) + sum((3 - k + 1) * np.log(L[k, k]) for k in range(3))
+        want = stats.invwishart.logpdf(Sig, df=6, scale=S) + jac + stats.wishart.logpdf(W2, df=5, scale=Sig)
+        lp, g = f(q)
+        assert lp == pytest.approx(want, rel=1e-11)
+        assert np.allclose(unconstrain_values("qmap x_w_0_0 0 3 3 cov -\n", dict(x_w_0_0=Sig)), q, atol=1e-12)
+        h = 1e-6
+        fd = np.array([(f(q + h * e, grad=False) - f(q - h * e, grad=False)) / (2 * h) for e in np.eye(6)])
+        assert np.allclose(g, fd, rtol=1e-6, atol=1e-6)

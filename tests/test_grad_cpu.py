@@ -238,6 +238,14 @@ MODELS = {
        x_n_0_3 <- [ neg_binomial v_0_5 x_n_0_1 :: P Z | i_1_1 <- 1...9 ] :: Array 1...9 Z
        return [x_n_0_0,x_n_0_1,x_n_0_2,x_n_0_3]
 """, "x_n_0_3", dict(x_n_0_3=[0, 3, 1, 7, 2, 2, 5, 0, 4]), 3),
+    # a cov_matrix parameter under inv_wishart with a wishart observation (cov_matrix_constrain, both matrix densities)
+    "wishart": ("""let v_0_0 = diag [1.0,2.0,1.5] :: RMat
+    v_0_1 = outer [0.3,0.5,0.2] [0.3,0.5,0.2] :: RMat
+    v_0_2 = v_0_0 + v_0_1 :: RMat
+ in do x_w_0_0 <- inv_wishart 6.0 v_0_2 :: P cov_matrix R
+       x_w_0_1 <- wishart 5.0 x_w_0_0 :: P RMat
+       return [x_w_0_0,x_w_0_1]
+""", "x_w_0_1", dict(x_w_0_1=[[5.1, 1.2, 0.4], [1.2, 9.8, 1.1], [0.4, 1.1, 6.3]]), 6),
     # logistic regression: a short given matrix, #>, bernoulliLogits
     "logit": ("""let v_0_0 = [ 0.0 | i_1_1 <- 1...3 ] :: RVec
     v_0_1 = [ 2.5 | i_1_1 <- 1...3 ] :: RVec

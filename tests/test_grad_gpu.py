@@ -274,7 +274,7 @@ def test_generated_linreg_beyond_the_shared_memory_budget(ctx, orc, tmp_path):
     assert np.all(np.isfinite(ch.get_state("q"))) and np.any(ch.get_state("q") != q0)
 
 
-@pytest.mark.parametrize("name", ["gamma", "logit", "negbin", "poisson", "schools"])
+@pytest.mark.parametrize("name", ["gamma", "logit", "negbin", "poisson", "schools", "wishart"])
 @pytest.mark.parametrize("lanes", [1, 4])
 def test_small_models_on_the_device_equal_their_host_build(ctx, tmp_path, name, lanes):
     """the small models of tests/test_grad_cpu.py (Poisson regression on integer data with a logistic-transformed parameter,
